@@ -1,0 +1,190 @@
+/*
+ * nanotensor_b200.h -- C ABI of the B200-native NanoTensor BLSTM basecall forward.
+ *
+ * The reference (BD2KGenomics/nanopore-RNN) has NO FFI on this path: its forward is a chain of
+ * TensorFlow-1.4 op calls built in nanotensor/network.py and driven by
+ * nanotensor/run_nanotensor.py.  Each entry point below replaces one of those call sites (cited
+ * per function); INTEGRATION.md shows the ctypes binding a maintainer would add.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; no torch / TF types.  `stream` is a cudaStream_t passed as
+ *    void* (NULL = legacy default stream).  Pointers suffixed _dev are device pointers on the
+ *    current CUDA device, _host are host pointers.
+ *  - the library never allocates device memory: callers size buffers with the *_bytes()
+ *    queries and pass them in (the Python host side uses torch's caching allocator).
+ *  - every function returns 0 on success, a negative NTB_E* code otherwise;
+ *    ntb_last_error() returns a thread-local message.  There is no CPU fallback: without an
+ *    sm_100 device every compute entry point returns NTB_ENODEVICE.
+ *  - all arithmetic is float32 in / float32 accumulate; the dense contractions on the tensor
+ *    cores use bf16x3 split operands (hi*hi + lo*hi + hi*lo), see DESIGN.md.
+ *  - activations are row-major [window][t][channel]; "row" = window * seq_len + t.
+ */
+#ifndef NANOTENSOR_B200_H
+#define NANOTENSOR_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define NTB_API __attribute__((visibility("default")))
+#else
+#define NTB_API
+#endif
+
+#define NTB_OK 0
+#define NTB_EINVAL (-1)    /* bad argument / unsupported shape */
+#define NTB_ENODEVICE (-2) /* no sm_100 CUDA device */
+#define NTB_ECUDA (-3)     /* CUDA runtime error (message has the cudaError string) */
+#define NTB_ENOMEM (-4)    /* caller-provided buffer too small */
+
+#define NTB_LAYER_RESIDUAL 1   /* network.py:153-163, 385-400 */
+#define NTB_LAYER_BLSTM 2      /* network.py:131-137, 266-288 */
+#define NTB_LAYER_CHIRON_FNN 3 /* network.py:164-175 */
+
+#define NTB_GRAPH_CROSS_ENTROPY 0 /* network.py:452-473 : argmax labels      */
+#define NTB_GRAPH_CTC 1           /* network.py:476-533 : ctc greedy labels  */
+
+#define NTB_MAX_LAYER_TENSORS 12
+
+/* One entry of the config's "network" list plus HOST pointers to its variables in the TF
+ * checkpoint layouts (tf.train.Saver.restore, run_nanotensor.py:337-338):
+ *  RESIDUAL   w[0] conv1  [1,1,Cin,C]   w[1] conv1_bn_scale [C] (NULL unless batchnorm) w[2] conv1_bn_offset
+ *             w[3] conv2a [1,1,Cin,C]   w[4] conv2a_bn_scale    w[5] conv2a_bn_offset
+ *             w[6] conv2b [1,3,C,C]     w[7] conv2b_bn_scale    w[8] conv2b_bn_offset
+ *             w[9] conv2c [1,1,C,C]     w[10] conv2c_bn_scale   w[11] conv2c_bn_offset
+ *  BLSTM      w[0] fw kernel [D+H,4H] (gate column blocks i|j|f|o)  w[1] fw bias [4H]
+ *             w[2] bw kernel [D+H,4H]                               w[3] bw bias [4H]
+ *  CHIRON_FNN w[0] weights [2,H]  w[1] bias [H]
+ */
+typedef struct ntb_layer {
+    int32_t type;        /* NTB_LAYER_*                                  */
+    int32_t in_dim;      /* channels entering the layer                  */
+    int32_t size;        /* "size" (H) or "out_channel" (C)              */
+    int32_t batchnorm;   /* residual: "batchnorm" (BN on branch1)        */
+    float forget_bias;   /* blstm: the layer's "bias" key (network.py:135) */
+    const float *w[NTB_MAX_LAYER_TENSORS];
+} ntb_layer;
+
+typedef struct ntb_model_desc {
+    int32_t graph;       /* NTB_GRAPH_*                                          */
+    int32_t seq_len;     /* T                                                    */
+    int32_t len_x;       /* input features per timestep (1 for CtcLoss graphs)   */
+    int32_t n_classes;   /* C (CtcLoss: len_y + 1, blank = C-1, network.py:495)  */
+    int32_t n_layers;
+    const ntb_layer *layers;
+    const float *out_w;  /* host [F, C]  fulconn_layer weights (network.py:291-309) */
+    const float *out_b;  /* host [C]                                              */
+} ntb_model_desc;
+
+typedef struct ntb_model ntb_model; /* opaque */
+
+NTB_API const char *ntb_last_error(void);
+/* "major.minor.patch"; also reports the gencode the kernels were built for. */
+NTB_API const char *ntb_version(void);
+/* 1 if the current device is compute capability 10.x, else 0 (never errors). */
+NTB_API int ntb_device_ok(void);
+
+/* ---- model life cycle (replaces Saver.restore + graph construction, network.py:32-103) ---- */
+/* Device bytes needed for the repacked, GPU-resident weight tiles of `desc`. */
+NTB_API int64_t ntb_model_weight_bytes(const ntb_model_desc *desc);
+/* Uploads the TF-layout host tensors and repacks them on the device into `weights_dev`
+ * (gate-interleaved fp32 recurrence tiles, K-major bf16 hi/lo GEMM tiles).  The buffer must
+ * stay alive until ntb_model_destroy. */
+NTB_API int ntb_model_create(const ntb_model_desc *desc, void *weights_dev, int64_t weights_bytes,
+                     void *stream, ntb_model **out);
+NTB_API void ntb_model_destroy(ntb_model *m);
+/* Scratch bytes for one forward over `n_windows` windows split in `n_groups` BN groups. */
+NTB_API int64_t ntb_model_workspace_bytes(const ntb_model *m, int64_t n_windows, int64_t n_groups);
+
+/* ---- the forward (replaces sess.run([prediction]) of run_nanotensor.py:345) -------------
+ * x_dev        [n_windows, T, len_x] float32
+ * len_dev      [n_windows] int32  (dynamic_rnn sequence_length)
+ * group_off_dev[n_groups+1] int32 : window offsets of the BN groups (= the reference's
+ *              batches: moments are taken over each batch, network.py:339-349); ascending,
+ *              group_off[0]=0, group_off[n_groups]=n_windows.  May be NULL when the network
+ *              has no residual layer.
+ * logits_dev   optional [n_windows*T, C] float32 ("output_layer", network.py:114-118/507-513)
+ * labels_dev   CrossEntropy: [n_windows*T] int32 argmax (first max);
+ *              CTC: [n_windows, T] int32 greedy-decoded, padded with -1
+ * label_len_dev CTC: [n_windows] int32 decoded length (NULL allowed for CrossEntropy)
+ */
+NTB_API int ntb_model_forward(ntb_model *m, const float *x_dev, const int32_t *len_dev,
+                      const int32_t *group_off_dev, int64_t n_windows, int64_t n_groups,
+                      void *workspace_dev, int64_t workspace_bytes, float *logits_dev,
+                      int32_t *labels_dev, int32_t *label_len_dev, void *stream);
+
+/* Same call with HOST buffers (pinned or pageable): copies inputs host->device into the
+ * workspace, runs the forward, copies labels (and logits if non-NULL) back and synchronises
+ * the stream.  This is the end-to-end entry the reference-facing plugin uses. */
+NTB_API int ntb_model_forward_host(ntb_model *m, const float *x_host, const int32_t *len_host,
+                           const int32_t *group_off_host, int64_t n_windows, int64_t n_groups,
+                           void *workspace_dev, int64_t workspace_bytes, float *logits_host,
+                           int32_t *labels_host, int32_t *label_len_host, void *stream);
+/* Workspace bytes for ntb_model_forward_host (forward scratch + staged inputs/outputs). */
+NTB_API int64_t ntb_model_workspace_bytes_host(const ntb_model *m, int64_t n_windows, int64_t n_groups,
+                                       int want_logits);
+
+/* Number of kernel launches the last ntb_model_forward on this model issued. */
+NTB_API int64_t ntb_model_last_launches(const ntb_model *m);
+/* Per-stage device time (ms) of the last forward when profiling was enabled with
+ * ntb_model_set_profile(m, 1): stages are 0 conv/BN front-end, 1 LSTM input projections,
+ * 2 LSTM recurrences, 3 readout.  Returns the number of stages written. */
+NTB_API int ntb_model_set_profile(ntb_model *m, int enable);
+NTB_API int ntb_model_stage_ms(const ntb_model *m, float *ms_out, int max_stages);
+
+/* ---- op-level entry points (kernel-boundary parity tests; same kernels the model uses) ---- */
+
+/* FullSignalSequence.load_data_inference + read_signal(normalize=True)
+ * (dataset.py:435-445, chiron/chiron/chiron_input.py:220-230): z-score every read with the
+ * mean / population std of the WHOLE read (float64 accumulation), drop start_index samples,
+ * cut windows of seq_len every `step`, zero pad.
+ * raw_dev [total_samples] int16; read_off_dev [n_reads+1] int64 sample offsets;
+ * win_off_dev [n_reads+1] int64 window offsets (host computes ceil((len-start)/step));
+ * x_dev [n_windows, seq_len] float32; len_dev [n_windows] int32. */
+NTB_API int ntb_pack_windows(const int16_t *raw_dev, const int64_t *read_off_dev,
+                     const int64_t *win_off_dev, int64_t n_reads, int64_t n_windows,
+                     int32_t seq_len, int32_t step, int32_t start_index, float *x_dev,
+                     int32_t *len_dev, void *stream);
+
+/* conv_layer + simple_global_bn (+ReLU) (network.py:312-349): y = conv(in) (k = 1 or 3, SAME,
+ * no bias), then per-group batch moments and normalisation.  in_dev [n_windows*T, Cin],
+ * filt_dev = TF filter [1,k,Cin,Cout] on the device; scale/offset NULL = no BN.
+ * out_dev [n_windows*T, Cout]. */
+NTB_API int ntb_conv_bn(const float *in_dev, const float *filt_dev, const float *scale_dev,
+                const float *offset_dev, const int32_t *group_off_dev, int64_t n_windows,
+                int64_t n_groups, int32_t T, int32_t Cin, int32_t Cout, int32_t ksize, int32_t relu,
+                void *workspace_dev, int64_t workspace_bytes, float *out_dev, void *stream);
+NTB_API int64_t ntb_conv_bn_workspace_bytes(int64_t n_windows, int64_t n_groups, int32_t T, int32_t Cin,
+                                    int32_t Cout, int32_t ksize);
+
+/* blstm (network.py:266-288): both directions of tf.nn.bidirectional_dynamic_rnn over
+ * rnn.LSTMCell, fw|bw concatenated.  kernels/biases are DEVICE pointers in the TF layouts.
+ * in_dev [n_windows*T, D] -> out_dev [n_windows*T, 2H]. */
+NTB_API int ntb_blstm(const float *in_dev, const int32_t *len_dev, const float *kernel_fw_dev,
+              const float *bias_fw_dev, const float *kernel_bw_dev, const float *bias_bw_dev,
+              float forget_bias, int64_t n_windows, int32_t T, int32_t D, int32_t H,
+              void *workspace_dev, int64_t workspace_bytes, float *out_dev, void *stream);
+NTB_API int64_t ntb_blstm_workspace_bytes(int64_t n_windows, int32_t T, int32_t D, int32_t H);
+
+/* tf.nn.ctc_greedy_decoder(merge_repeated=True) + sparse_tensor_to_dense(-1)
+ * (network.py:528-533) / tf.argmax (network.py:208-211) on given logits [n_windows*T, C]. */
+NTB_API int ntb_decode(const float *logits_dev, const int32_t *len_dev, int64_t n_windows, int32_t T,
+               int32_t C, int32_t graph, int32_t *labels_dev, int32_t *label_len_dev,
+               void *stream);
+
+/* Dense GEMM used by the conv / projection stages, exposed for roofline measurement and
+ * parity tests: out[M,N] = A[M,K] @ B[K,N] (+ bias[N]), float32 in/out.
+ * impl 0 = fp32 SIMT, 1 = tcgen05 bf16x3 (TMA + TMEM), 2 = tcgen05 single-pass bf16. */
+NTB_API int ntb_gemm(const float *a_dev, const float *b_dev, const float *bias_dev, int64_t M, int32_t N,
+             int32_t K, int32_t impl, void *workspace_dev, int64_t workspace_bytes,
+             float *out_dev, void *stream);
+NTB_API int64_t ntb_gemm_workspace_bytes(int64_t M, int32_t N, int32_t K, int32_t impl);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NANOTENSOR_B200_H */

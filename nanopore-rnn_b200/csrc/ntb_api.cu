@@ -1,0 +1,708 @@
+// C ABI of nanotensor_b200 (include/nanotensor_b200.h): model life cycle, the chunk forward and
+// the op-level entry points.  Host-side orchestration only; the kernels live in the .cuh files.
+#include <new>
+#include <vector>
+
+#include "ntb_common.cuh"
+#include "ntb_gemm_tc.cuh"
+#include "ntb_kernels.cuh"
+#include "ntb_lstm.cuh"
+
+namespace ntb {
+
+thread_local char g_err[512] = "";
+
+static int check_device() {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail(NTB_ENODEVICE, "no CUDA device: %s", cudaGetErrorString(e));
+    int major = 0;
+    e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+    if (e != cudaSuccess || major != 10)
+        return fail(NTB_ENODEVICE, "nanotensor_b200 needs an sm_100 device (found cc major %s%lld)", "",
+                    (long long)major);
+    return NTB_OK;
+}
+
+struct LayerDev {
+    int type = 0, in_dim = 0, size = 0, batchnorm = 0;
+    float forget_bias = 0.f;
+    // residual: TF filters [taps][Cin][C] and BN scale/offset, raw on the device
+    const float *conv[4] = {nullptr, nullptr, nullptr, nullptr};      // conv1, conv2a, conv2b, conv2c
+    const float *bn_scale[4] = {nullptr, nullptr, nullptr, nullptr};
+    const float *bn_offset[4] = {nullptr, nullptr, nullptr, nullptr};
+    GemmWeights convw[4];   // tensor-core tiles (bf16 hi/lo, K-major) where the shape allows
+    // blstm
+    int Hp = 0;
+    float *wih = nullptr, *bias = nullptr, *whh = nullptr;
+    GemmWeights wihw;
+    // chiron_fnn
+    const float *fnn_w = nullptr, *fnn_b = nullptr;
+};
+
+}  // namespace ntb
+
+struct ntb_model {
+    int graph, T, len_x, C, F_final;
+    std::vector<ntb::LayerDev> layers;
+    const float *out_w = nullptr, *out_b = nullptr;
+    ntb::GemmWeights outw;
+    int max_res_c = 0, max_act_c = 0, max_proj_n = 0;
+    bool has_res = false;
+    int64_t launches = 0;
+    int profile = 0;
+    float stage_ms[4] = {0, 0, 0, 0};
+    int sm_count = 148;
+};
+
+namespace ntb {
+
+// ------------------------------------------------------------------ launch helpers
+struct Ctx {
+    cudaStream_t st;
+    ntb_model *m;   // may be null (op-level calls)
+    int64_t launches = 0;
+    void count() { ++launches; if (m) ++m->launches; }
+};
+
+static int launch_conv_gemm(Ctx &cx, const ConvGemmParams &p) {
+    dim3 grid(cdiv(p.rows, 64), cdiv(p.N, 64));
+    k_conv_gemm_simt<64, 64, 16, 4, 4><<<grid, 256, 0, cx.st>>>(p);
+    cx.count();
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+static int launch_bn_stats(Ctx &cx, const float *y, int C, int T, const int32_t *group_off, int64_t n_groups,
+                           const float *scale, const float *offset, float *a, float *b) {
+    dim3 grid((unsigned)n_groups, cdiv(C, 256));
+    k_bn_stats<<<grid, C < 256 ? (int)align_up(C, 32) : 256, 0, cx.st>>>(y, C, T, group_off, scale, offset, 1e-5f, a, b);
+    cx.count();
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+static int elementwise_grid(int64_t total, int sm_count) {
+    int64_t blocks = (total + 255) / 256;
+    int64_t cap = (int64_t)sm_count * 16;
+    return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
+}
+
+static int launch_lstm(Ctx &cx, const LstmParams &p, int sm_count) {
+    (void)sm_count;
+    const int UG = p.Hp / LSTM_UPT;
+    if (UG * LSTM_WG > 256)
+        return fail(NTB_EINVAL, "blstm: hidden size %s%lld needs the cluster recurrence (H <= 128 supported)", "",
+                    (long long)p.H);
+    const bool w_smem = lstm_smem_bytes(p.H, p.Hp, true) <= 227 * 1024;
+    const int64_t smem = lstm_smem_bytes(p.H, p.Hp, w_smem);
+    dim3 grid(cdiv(p.n_windows, LSTM_BT), 2);
+    const int threads = lstm_threads(p.Hp);
+    if (w_smem) {
+        NTB_CUDA(cudaFuncSetAttribute(k_lstm_recurrence<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_lstm_recurrence<true><<<grid, threads, smem, cx.st>>>(p);
+    } else {
+        NTB_CUDA(cudaFuncSetAttribute(k_lstm_recurrence<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_lstm_recurrence<false><<<grid, threads, smem, cx.st>>>(p);
+    }
+    cx.count();
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+static inline int pad_hidden(int H) { return (int)align_up(H, LSTM_UPT); }
+
+// Dense [rows,K] x [K,N] (+bias): tensor-core path when the packed tiles exist, SIMT otherwise.
+static int dense(Ctx &cx, const float *A, int lda, int64_t rows, int K, int N, const float *W_kn,
+                 const GemmWeights *tc, const float *bias, float *out, int ldo, GemmScratch *scratch) {
+    if (tc && tc->valid && scratch && scratch->valid) {
+        return gemm_tc_run(cx.st, A, lda, rows, *tc, bias, out, ldo, *scratch, &cx.launches);
+    }
+    ConvGemmParams p{};
+    p.A = A; p.lda = lda; p.W = W_kn; p.bias = bias; p.out = out; p.ldo = ldo;
+    p.rows = rows; p.K = K; p.N = N; p.taps = 1; p.T = 1; p.relu_in = 0;
+    return launch_conv_gemm(cx, p);
+}
+
+}  // namespace ntb
+
+using namespace ntb;
+
+// ====================================================================== misc
+extern "C" const char *ntb_last_error(void) { return g_err; }
+extern "C" const char *ntb_version(void) { return "0.1.0 (sm_100a)"; }
+extern "C" int ntb_device_ok(void) { return check_device() == NTB_OK ? 1 : 0; }
+
+// ====================================================================== model life cycle
+static int validate_desc(const ntb_model_desc *d) {
+    if (!d || !d->layers || d->n_layers <= 0) return fail(NTB_EINVAL, "model desc: no layers%s", "");
+    if (d->graph != NTB_GRAPH_CROSS_ENTROPY && d->graph != NTB_GRAPH_CTC)
+        return fail(NTB_EINVAL, "model desc: graph must be NTB_GRAPH_CROSS_ENTROPY or NTB_GRAPH_CTC%s", "");
+    if (d->seq_len <= 0 || d->len_x <= 0 || d->n_classes <= 0 || !d->out_w || !d->out_b)
+        return fail(NTB_EINVAL, "model desc: bad seq_len/len_x/n_classes/out weights%s", "");
+    int dim = d->len_x;
+    for (int i = 0; i < d->n_layers; ++i) {
+        const ntb_layer &l = d->layers[i];
+        if (l.in_dim != dim)
+            return fail(NTB_EINVAL, "layer %s%lld: in_dim %lld does not match the previous layer's output", "",
+                        (long long)i, (long long)l.in_dim);
+        if (l.type == NTB_LAYER_RESIDUAL) {
+            if (l.size <= 0 || l.size % 4) return fail(NTB_EINVAL, "residual layer: out_channel must be a multiple of 4%s", "");
+            for (int k : {0, 3, 4, 5, 6, 7, 8, 9, 10, 11})
+                if (!l.w[k]) return fail(NTB_EINVAL, "residual layer %s%lld: missing tensor %lld", "", (long long)i, (long long)k);
+            if (l.batchnorm && (!l.w[1] || !l.w[2])) return fail(NTB_EINVAL, "residual layer: batchnorm set but conv1_bn tensors missing%s", "");
+            dim = l.size;
+        } else if (l.type == NTB_LAYER_BLSTM) {
+            if (l.size <= 0) return fail(NTB_EINVAL, "blstm layer: size must be positive%s", "");
+            for (int k = 0; k < 4; ++k)
+                if (!l.w[k]) return fail(NTB_EINVAL, "blstm layer %s%lld: missing tensor %lld", "", (long long)i, (long long)k);
+            dim = 2 * l.size;
+        } else if (l.type == NTB_LAYER_CHIRON_FNN) {
+            if (dim % 2 || !l.w[0] || !l.w[1]) return fail(NTB_EINVAL, "chiron_fnn layer: needs an even input width and 2 tensors%s", "");
+            dim = dim / 2;
+        } else {
+            return fail(NTB_EINVAL, "layer %s%lld: unsupported type %lld", "", (long long)i, (long long)l.type);
+        }
+    }
+    return NTB_OK;
+}
+
+static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &ar, cudaStream_t st, bool upload) {
+    // Walks the layer list once; with upload=false only sizes the arena.
+    auto put = [&](const float *host, int64_t n) -> const float * {
+        float *dst = ar.take<float>(n);
+        if (upload && ar.ok()) cudaMemcpyAsync(dst, host, n * sizeof(float), cudaMemcpyHostToDevice, st);
+        return dst;
+    };
+    int dim = d->len_x;
+    for (int i = 0; i < d->n_layers; ++i) {
+        const ntb_layer &l = d->layers[i];
+        LayerDev ld;
+        ld.type = l.type; ld.in_dim = l.in_dim; ld.size = l.size; ld.batchnorm = l.batchnorm;
+        ld.forget_bias = l.forget_bias;
+        if (l.type == NTB_LAYER_RESIDUAL) {
+            const int C = l.size, Cin = dim;
+            const int taps[4] = {1, 1, 3, 1};
+            const int kin[4] = {Cin, Cin, C, C};
+            const int widx[4] = {0, 3, 6, 9};
+            for (int c = 0; c < 4; ++c) {
+                ld.conv[c] = put(l.w[widx[c]], (int64_t)taps[c] * kin[c] * C);
+                if (c > 0 || l.batchnorm) {
+                    ld.bn_scale[c] = put(l.w[widx[c] + 1], C);
+                    ld.bn_offset[c] = put(l.w[widx[c] + 2], C);
+                }
+                gemm_tc_plan_weights(ld.convw[c], taps[c], kin[c], C, ar);
+            }
+            dim = C;
+        } else if (l.type == NTB_LAYER_BLSTM) {
+            const int H = l.size, D = dim, Hp = pad_hidden(H);
+            ld.Hp = Hp;
+            const float *kf = put(l.w[0], (int64_t)(D + H) * 4 * H);
+            const float *bf = put(l.w[1], 4 * H);
+            const float *kb = put(l.w[2], (int64_t)(D + H) * 4 * H);
+            const float *bb = put(l.w[3], 4 * H);
+            ld.wih = ar.take<float>((int64_t)D * 8 * Hp);
+            ld.bias = ar.take<float>(8 * Hp);
+            ld.whh = ar.take<float>(2LL * H * Hp * 4);
+            gemm_tc_plan_weights(ld.wihw, 1, D, 8 * Hp, ar);
+            if (upload && ar.ok()) {
+                k_repack_lstm<<<256, 256, 0, st>>>(kf, bf, kb, bb, l.forget_bias, D, H, Hp, ld.wih, ld.bias, ld.whh);
+            }
+            dim = 2 * H;
+        } else {
+            ld.fnn_w = put(l.w[0], dim);
+            ld.fnn_b = put(l.w[1], dim / 2);
+            dim = dim / 2;
+        }
+        if (m) m->layers.push_back(ld);
+    }
+    const float *ow = put(d->out_w, (int64_t)dim * d->n_classes);
+    const float *ob = put(d->out_b, d->n_classes);
+    GemmWeights outw;
+    gemm_tc_plan_weights(outw, 1, dim, d->n_classes, ar);
+    if (m) { m->out_w = ow; m->out_b = ob; m->F_final = dim; m->outw = outw; }
+    return ar.off;
+}
+
+extern "C" int64_t ntb_model_weight_bytes(const ntb_model_desc *desc) {
+    if (validate_desc(desc) != NTB_OK) return NTB_EINVAL;
+    Arena ar(nullptr, 0);
+    return model_weight_plan(desc, nullptr, ar, nullptr, false);
+}
+
+extern "C" int ntb_model_create(const ntb_model_desc *desc, void *weights_dev, int64_t weights_bytes,
+                                void *stream, ntb_model **out) {
+    if (!out) return fail(NTB_EINVAL, "ntb_model_create: out is NULL%s", "");
+    *out = nullptr;
+    NTB_TRY(validate_desc(desc));
+    NTB_TRY(check_device());
+    if (!weights_dev) return fail(NTB_EINVAL, "ntb_model_create: weights_dev is NULL%s", "");
+    cudaStream_t st = (cudaStream_t)stream;
+    ntb_model *m = new (std::nothrow) ntb_model();
+    if (!m) return fail(NTB_ENOMEM, "out of host memory%s", "");
+    m->graph = desc->graph; m->T = desc->seq_len; m->len_x = desc->len_x; m->C = desc->n_classes;
+    Arena ar(weights_dev, weights_bytes);
+    model_weight_plan(desc, m, ar, st, true);
+    if (!ar.ok()) {
+        delete m;
+        return fail(NTB_ENOMEM, "weights buffer too small: need %s%lld bytes, have %lld", "", (long long)ar.off,
+                    (long long)weights_bytes);
+    }
+    // tensor-core tiles: split the fp32 TF tensors into K-major bf16 hi/lo planes
+    for (auto &ld : m->layers) {
+        if (ld.type == NTB_LAYER_RESIDUAL) {
+            for (int c = 0; c < 4; ++c)
+                if (ld.convw[c].valid) gemm_tc_pack_weights(st, ld.conv[c], ld.convw[c]);
+            m->has_res = true;
+            if (ld.size > m->max_res_c) m->max_res_c = ld.size;
+            if (ld.size > m->max_act_c) m->max_act_c = ld.size;
+        } else if (ld.type == NTB_LAYER_BLSTM) {
+            if (ld.wihw.valid) gemm_tc_pack_weights(st, ld.wih, ld.wihw);
+            if (2 * ld.size > m->max_act_c) m->max_act_c = 2 * ld.size;
+            if (8 * ld.Hp > m->max_proj_n) m->max_proj_n = 8 * ld.Hp;
+        } else {
+            if (ld.in_dim / 2 > m->max_act_c) m->max_act_c = ld.in_dim / 2;
+        }
+    }
+    if (m->outw.valid) gemm_tc_pack_weights(st, m->out_w, m->outw);
+    cudaError_t e = cudaStreamSynchronize(st);   // host tensors may be freed by the caller after return
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        delete m;
+        return fail(NTB_ECUDA, "ntb_model_create: %s", cudaGetErrorString(e));
+    }
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, dev);
+    *out = m;
+    return NTB_OK;
+}
+
+extern "C" void ntb_model_destroy(ntb_model *m) {
+    if (!m) return;
+    delete m;
+}
+
+// ====================================================================== workspace plan
+namespace ntb {
+struct Workspace {
+    int32_t *win_group;
+    float *act[2];
+    float *y1, *y2a, *y2b;
+    float *aff[8];
+    float *xproj;
+    float *logits;
+    GemmScratch gs;
+};
+
+static int64_t plan_workspace(const ntb_model *m, int64_t n, int64_t n_groups, bool own_logits, Arena &ar,
+                              Workspace &ws) {
+    const int64_t rows = n * m->T;
+    ws.win_group = ar.take<int32_t>(n > 0 ? n : 1);
+    const int actc = m->max_act_c > 0 ? m->max_act_c : 1;
+    ws.act[0] = ar.take<float>(rows * actc);
+    ws.act[1] = ar.take<float>(rows * actc);
+    if (m->has_res) {
+        ws.y1 = ar.take<float>(rows * m->max_res_c);
+        ws.y2a = ar.take<float>(rows * m->max_res_c);
+        ws.y2b = ar.take<float>(rows * m->max_res_c);
+        for (auto &a : ws.aff) a = ar.take<float>((n_groups > 0 ? n_groups : 1) * (int64_t)m->max_res_c);
+    } else {
+        ws.y1 = ws.y2a = ws.y2b = nullptr;
+        for (auto &a : ws.aff) a = nullptr;
+    }
+    ws.xproj = m->max_proj_n ? ar.take<float>(rows * m->max_proj_n) : nullptr;
+    const bool small_c = m->C <= 8;
+    ws.logits = (!small_c && own_logits) ? ar.take<float>(rows * m->C) : nullptr;
+    int maxk = m->len_x;
+    for (auto &ld : m->layers) {
+        if (ld.in_dim > maxk) maxk = ld.in_dim;
+        if (ld.type == NTB_LAYER_RESIDUAL && ld.size > maxk) maxk = ld.size;
+    }
+    if (m->F_final > maxk) maxk = m->F_final;
+    gemm_tc_plan_scratch(ws.gs, rows, maxk, ar);
+    return ar.off;
+}
+}  // namespace ntb
+
+extern "C" int64_t ntb_model_workspace_bytes(const ntb_model *m, int64_t n_windows, int64_t n_groups) {
+    if (!m || n_windows < 0) return NTB_EINVAL;
+    Arena ar(nullptr, 0);
+    Workspace ws;
+    return plan_workspace(m, n_windows, n_groups, true, ar, ws);
+}
+
+// ====================================================================== the forward
+static int residual_forward(Ctx &cx, ntb_model *m, const LayerDev &ld, const float *in, int Cin, int64_t n,
+                            const int32_t *group_off, int64_t n_groups, Workspace &ws, float *out) {
+    const int C = ld.size, T = m->T;
+    const int64_t rows = n * T;
+    float *ys[4] = {ws.y1, ws.y2a, ws.y2b, ws.y2a};   // conv2c reuses conv2a's buffer
+    const int taps[4] = {1, 1, 3, 1};
+    const int src_of[4] = {-1, -1, 1, 2};             // conv2b reads bn+relu(conv2a), conv2c reads bn+relu(conv2b)
+    float *aa[4] = {ws.aff[0], ws.aff[2], ws.aff[4], ws.aff[6]};
+    float *bb[4] = {ws.aff[1], ws.aff[3], ws.aff[5], ws.aff[7]};
+    for (int c = 0; c < 4; ++c) {
+        if (c == 3) { aa[3] = ws.aff[2]; bb[3] = ws.aff[3]; }   // conv2a's affine is dead by now
+        const float *A = src_of[c] < 0 ? in : ys[src_of[c]];
+        const int K = src_of[c] < 0 ? Cin : C;
+        const float *fa = src_of[c] < 0 ? nullptr : aa[src_of[c]];
+        const float *fb = src_of[c] < 0 ? nullptr : bb[src_of[c]];
+        if (ld.convw[c].valid && ws.gs.valid) {
+            NTB_TRY(gemm_tc_conv(cx.st, A, K, rows, T, fa, fb, ws.win_group, src_of[c] >= 0, ld.convw[c], ys[c], C,
+                                 ws.gs, &cx.launches));
+        } else {
+            ConvGemmParams p{};
+            p.A = A; p.lda = K; p.W = ld.conv[c]; p.bias = nullptr;
+            p.aff_a = fa; p.aff_b = fb; p.win_group = ws.win_group;
+            p.out = ys[c]; p.ldo = C; p.rows = rows; p.K = K; p.N = C; p.taps = taps[c]; p.T = T;
+            p.relu_in = src_of[c] >= 0;
+            NTB_TRY(launch_conv_gemm(cx, p));
+        }
+        if (ld.bn_scale[c])
+            NTB_TRY(launch_bn_stats(cx, ys[c], C, T, group_off, n_groups, ld.bn_scale[c], ld.bn_offset[c], aa[c], bb[c]));
+    }
+    const int64_t total4 = rows * C / 4;
+    k_residual_combine<<<elementwise_grid(total4, m->sm_count), 256, 0, cx.st>>>(
+        (const float4 *)ws.y1, ld.bn_scale[0] ? aa[0] : nullptr, ld.bn_scale[0] ? bb[0] : nullptr,
+        (const float4 *)ys[3], aa[3], bb[3], ws.win_group, T, C, total4, (float4 *)out);
+    cx.count();
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const int32_t *group_off, int64_t n,
+                        int64_t n_groups, Workspace &ws, float *logits_out, int32_t *labels, int32_t *label_len,
+                        cudaStream_t st) {
+    Ctx cx{st, m};
+    m->launches = 0;
+    const int T = m->T;
+    const int64_t rows = n * T;
+    if (n == 0) return NTB_OK;
+    int stage = -1;   // 0 conv, 1 projection, 2 recurrence, 3 readout
+    std::vector<std::pair<int, cudaEvent_t>> marks;
+    auto mark = [&](int s) -> int {
+        if (!m->profile) return NTB_OK;
+        if (s == stage) return NTB_OK;
+        stage = s;
+        cudaEvent_t e;
+        NTB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDefault));
+        NTB_CUDA(cudaEventRecord(e, st));
+        marks.push_back({s, e});
+        return NTB_OK;
+    };
+    if (m->has_res) {
+        if (!group_off || n_groups <= 0) return fail(NTB_EINVAL, "forward: residual layers need group_off (BN groups)%s", "");
+        k_window_groups<<<(unsigned)n_groups, 128, 0, st>>>(group_off, (int)n_groups, ws.win_group);
+        cx.count();
+        NTB_LAUNCH_CHECK();
+    }
+    const float *cur = x;
+    int dim = m->len_x;
+    int flip = 0;
+    const size_t nl = m->layers.size();
+    const bool small_c = m->C <= 8;
+    const LayerDev *fused_fnn = nullptr;
+    for (size_t li = 0; li < nl; ++li) {
+        const LayerDev &ld = m->layers[li];
+        float *out = ws.act[flip];
+        if (ld.type == NTB_LAYER_RESIDUAL) {
+            NTB_TRY(mark(0));
+            NTB_TRY(residual_forward(cx, m, ld, cur, dim, n, group_off, n_groups, ws, out));
+            dim = ld.size;
+        } else if (ld.type == NTB_LAYER_BLSTM) {
+            NTB_TRY(mark(1));
+            const int N = 8 * ld.Hp;
+            NTB_TRY(dense(cx, cur, dim, rows, dim, N, ld.wih, &ld.wihw, ld.bias, ws.xproj, N, &ws.gs));
+            NTB_TRY(mark(2));
+            LstmParams p{};
+            p.xproj = ws.xproj; p.ldx = N; p.whh = ld.whh; p.lens = lens; p.out = out; p.ldo = 2 * ld.size;
+            p.n_windows = n; p.T = T; p.H = ld.size; p.Hp = ld.Hp;
+            NTB_TRY(launch_lstm(cx, p, m->sm_count));
+            dim = 2 * ld.size;
+        } else {   // chiron_fnn
+            NTB_TRY(mark(3));
+            if (li + 1 == nl && small_c) { fused_fnn = &ld; continue; }   // fused into the readout
+            const int64_t total = rows * (dim / 2);
+            k_chiron_fnn<<<elementwise_grid(total, m->sm_count), 256, 0, st>>>(cur, ld.fnn_w, ld.fnn_b, dim / 2, rows, out);
+            cx.count();
+            NTB_LAUNCH_CHECK();
+            dim = dim / 2;
+        }
+        cur = out;
+        flip ^= 1;
+    }
+    NTB_TRY(mark(3));
+    if (small_c) {
+        const int F = fused_fnn ? dim / 2 : dim;
+        const size_t smem = sizeof(float) * ((size_t)F * m->C + (fused_fnn ? 3 * F : 0));
+        if (smem > 200 * 1024) return fail(NTB_EINVAL, "readout: dense weights do not fit shared memory%s", "");
+        NTB_CUDA(cudaFuncSetAttribute(k_readout_small<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_readout_small<8><<<cdiv(n, 8), 256, smem, st>>>(cur, dim, fused_fnn ? fused_fnn->fnn_w : nullptr,
+                                                          fused_fnn ? fused_fnn->fnn_b : nullptr, m->out_w, m->out_b,
+                                                          lens, n, T, m->C, m->graph, logits_out, labels, label_len);
+        cx.count();
+        NTB_LAUNCH_CHECK();
+    } else {
+        float *lg = logits_out ? logits_out : ws.logits;
+        if (!lg) return fail(NTB_ENOMEM, "forward: no logits buffer for a large-C readout%s", "");
+        NTB_TRY(dense(cx, cur, dim, rows, dim, m->C, m->out_w, &m->outw, m->out_b, lg, m->C, &ws.gs));
+        const int64_t warps = m->graph == NTB_GRAPH_CROSS_ENTROPY ? rows : n;
+        k_decode<<<cdiv(warps, 8), 256, 0, st>>>(lg, lens, n, T, m->C, m->graph, labels, label_len);
+        cx.count();
+        NTB_LAUNCH_CHECK();
+    }
+    if (m->profile) {
+        cudaEvent_t e;
+        NTB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDefault));
+        NTB_CUDA(cudaEventRecord(e, st));
+        marks.push_back({4, e});
+        NTB_CUDA(cudaStreamSynchronize(st));
+        float acc[4] = {0, 0, 0, 0};
+        for (size_t i = 0; i + 1 < marks.size(); ++i) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, marks[i].second, marks[i + 1].second);
+            if (marks[i].first >= 0 && marks[i].first < 4) acc[marks[i].first] += ms;
+        }
+        for (auto &mk : marks) cudaEventDestroy(mk.second);
+        for (int i = 0; i < 4; ++i) m->stage_ms[i] = acc[i];
+    }
+    m->launches = cx.launches;
+    return NTB_OK;
+}
+
+extern "C" int ntb_model_forward(ntb_model *m, const float *x_dev, const int32_t *len_dev,
+                                 const int32_t *group_off_dev, int64_t n_windows, int64_t n_groups,
+                                 void *workspace_dev, int64_t workspace_bytes, float *logits_dev,
+                                 int32_t *labels_dev, int32_t *label_len_dev, void *stream) {
+    if (!m || !x_dev || !len_dev || !labels_dev || n_windows < 0)
+        return fail(NTB_EINVAL, "ntb_model_forward: NULL argument%s", "");
+    NTB_TRY(check_device());
+    Arena ar(workspace_dev, workspace_bytes);
+    Workspace ws;
+    plan_workspace(m, n_windows, n_groups, logits_dev == nullptr, ar, ws);
+    if (!workspace_dev || !ar.ok())
+        return fail(NTB_ENOMEM, "workspace too small: need %s%lld bytes, have %lld", "", (long long)ar.off,
+                    (long long)workspace_bytes);
+    return forward_impl(m, x_dev, len_dev, group_off_dev, n_windows, n_groups, ws, logits_dev, labels_dev,
+                        label_len_dev, (cudaStream_t)stream);
+}
+
+namespace ntb {
+struct HostStage {
+    float *x;
+    int32_t *len, *group_off, *labels, *label_len;
+    float *logits;
+};
+static int64_t plan_host_stage(const ntb_model *m, int64_t n, int64_t n_groups, int want_logits, Arena &ar,
+                               HostStage &hs) {
+    const int64_t rows = n * m->T;
+    hs.x = ar.take<float>(rows * m->len_x);
+    hs.len = ar.take<int32_t>(n > 0 ? n : 1);
+    hs.group_off = ar.take<int32_t>(n_groups + 1);
+    hs.labels = ar.take<int32_t>(rows > 0 ? rows : 1);
+    hs.label_len = ar.take<int32_t>(n > 0 ? n : 1);
+    hs.logits = want_logits ? ar.take<float>(rows * m->C) : nullptr;
+    return ar.off;
+}
+}  // namespace ntb
+
+extern "C" int64_t ntb_model_workspace_bytes_host(const ntb_model *m, int64_t n_windows, int64_t n_groups,
+                                                  int want_logits) {
+    if (!m || n_windows < 0) return NTB_EINVAL;
+    Arena ar(nullptr, 0);
+    HostStage hs;
+    plan_host_stage(m, n_windows, n_groups, want_logits, ar, hs);
+    Workspace ws;
+    return plan_workspace(m, n_windows, n_groups, !want_logits, ar, ws);
+}
+
+extern "C" int ntb_model_forward_host(ntb_model *m, const float *x_host, const int32_t *len_host,
+                                      const int32_t *group_off_host, int64_t n_windows, int64_t n_groups,
+                                      void *workspace_dev, int64_t workspace_bytes, float *logits_host,
+                                      int32_t *labels_host, int32_t *label_len_host, void *stream) {
+    if (!m || !x_host || !len_host || !labels_host || n_windows < 0)
+        return fail(NTB_EINVAL, "ntb_model_forward_host: NULL argument%s", "");
+    NTB_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    Arena ar(workspace_dev, workspace_bytes);
+    HostStage hs;
+    plan_host_stage(m, n_windows, n_groups, logits_host != nullptr, ar, hs);
+    Workspace ws;
+    plan_workspace(m, n_windows, n_groups, logits_host == nullptr, ar, ws);
+    if (!workspace_dev || !ar.ok())
+        return fail(NTB_ENOMEM, "workspace too small: need %s%lld bytes, have %lld", "", (long long)ar.off,
+                    (long long)workspace_bytes);
+    const int64_t rows = n_windows * m->T;
+    if (n_windows == 0) return NTB_OK;
+    NTB_CUDA(cudaMemcpyAsync(hs.x, x_host, rows * m->len_x * sizeof(float), cudaMemcpyHostToDevice, st));
+    NTB_CUDA(cudaMemcpyAsync(hs.len, len_host, n_windows * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    if (group_off_host && n_groups > 0)
+        NTB_CUDA(cudaMemcpyAsync(hs.group_off, group_off_host, (n_groups + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    NTB_TRY(forward_impl(m, hs.x, hs.len, (group_off_host && n_groups > 0) ? hs.group_off : nullptr, n_windows,
+                         n_groups, ws, hs.logits, hs.labels, hs.label_len, st));
+    NTB_CUDA(cudaMemcpyAsync(labels_host, hs.labels, rows * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    if (label_len_host && m->graph == NTB_GRAPH_CTC)
+        NTB_CUDA(cudaMemcpyAsync(label_len_host, hs.label_len, n_windows * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    if (logits_host)
+        NTB_CUDA(cudaMemcpyAsync(logits_host, hs.logits, rows * m->C * sizeof(float), cudaMemcpyDeviceToHost, st));
+    NTB_CUDA(cudaStreamSynchronize(st));
+    return NTB_OK;
+}
+
+extern "C" int64_t ntb_model_last_launches(const ntb_model *m) { return m ? m->launches : 0; }
+extern "C" int ntb_model_set_profile(ntb_model *m, int enable) {
+    if (!m) return NTB_EINVAL;
+    m->profile = enable ? 1 : 0;
+    return NTB_OK;
+}
+extern "C" int ntb_model_stage_ms(const ntb_model *m, float *ms_out, int max_stages) {
+    if (!m || !ms_out) return 0;
+    int k = max_stages < 4 ? max_stages : 4;
+    for (int i = 0; i < k; ++i) ms_out[i] = m->stage_ms[i];
+    return k;
+}
+
+// ====================================================================== op-level entry points
+extern "C" int ntb_pack_windows(const int16_t *raw_dev, const int64_t *read_off_dev, const int64_t *win_off_dev,
+                                int64_t n_reads, int64_t n_windows, int32_t seq_len, int32_t step,
+                                int32_t start_index, float *x_dev, int32_t *len_dev, void *stream) {
+    // needs a per-read (mean, std) scratch: carved from the tail of x_dev is not possible -> caller
+    // passes nothing; we keep a small stream-ordered allocation instead.
+    if (!raw_dev || !read_off_dev || !win_off_dev || !x_dev || !len_dev || seq_len <= 0 || step <= 0 || start_index < 0)
+        return fail(NTB_EINVAL, "ntb_pack_windows: bad argument%s", "");
+    NTB_TRY(check_device());
+    if (n_reads == 0 || n_windows == 0) return NTB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    double *ms = nullptr;
+    NTB_CUDA(cudaMallocAsync((void **)&ms, sizeof(double) * 2 * n_reads, st));
+    k_read_moments<<<(unsigned)n_reads, 256, 0, st>>>(raw_dev, read_off_dev, ms);
+    k_pack_windows<<<cdiv(n_windows, 8), 256, 0, st>>>(raw_dev, read_off_dev, win_off_dev, ms, n_reads, n_windows,
+                                                       seq_len, step, start_index, x_dev, len_dev);
+    cudaError_t e = cudaGetLastError();
+    cudaFreeAsync(ms, st);
+    if (e != cudaSuccess) return fail(NTB_ECUDA, "ntb_pack_windows: %s", cudaGetErrorString(e));
+    return NTB_OK;
+}
+
+extern "C" int64_t ntb_conv_bn_workspace_bytes(int64_t n_windows, int64_t n_groups, int32_t T, int32_t Cin,
+                                               int32_t Cout, int32_t ksize) {
+    (void)Cin; (void)ksize;
+    Arena ar(nullptr, 0);
+    ar.take<int32_t>(n_windows);
+    ar.take<float>(n_windows * T * (int64_t)Cout);
+    ar.take<float>(n_groups * (int64_t)Cout);
+    ar.take<float>(n_groups * (int64_t)Cout);
+    return ar.off;
+}
+
+extern "C" int ntb_conv_bn(const float *in_dev, const float *filt_dev, const float *scale_dev,
+                           const float *offset_dev, const int32_t *group_off_dev, int64_t n_windows,
+                           int64_t n_groups, int32_t T, int32_t Cin, int32_t Cout, int32_t ksize, int32_t relu,
+                           void *workspace_dev, int64_t workspace_bytes, float *out_dev, void *stream) {
+    if (!in_dev || !filt_dev || !out_dev || (ksize != 1 && ksize != 3) || T <= 0 || Cin <= 0 || Cout <= 0)
+        return fail(NTB_EINVAL, "ntb_conv_bn: bad argument%s", "");
+    if ((scale_dev == nullptr) != (offset_dev == nullptr)) return fail(NTB_EINVAL, "ntb_conv_bn: scale/offset must both be set%s", "");
+    if (scale_dev && (!group_off_dev || n_groups <= 0)) return fail(NTB_EINVAL, "ntb_conv_bn: BN needs group_off%s", "");
+    NTB_TRY(check_device());
+    Ctx cx{(cudaStream_t)stream, nullptr};
+    Arena ar(workspace_dev, workspace_bytes);
+    int32_t *win_group = ar.take<int32_t>(n_windows);
+    float *y = ar.take<float>(n_windows * T * (int64_t)Cout);
+    float *a = ar.take<float>(n_groups * (int64_t)Cout);
+    float *b = ar.take<float>(n_groups * (int64_t)Cout);
+    if (!workspace_dev || !ar.ok()) return fail(NTB_ENOMEM, "ntb_conv_bn: workspace too small (need %s%lld)", "", (long long)ar.off);
+    const int64_t rows = n_windows * T;
+    if (rows == 0) return NTB_OK;
+    ConvGemmParams p{};
+    p.A = in_dev; p.lda = Cin; p.W = filt_dev; p.out = scale_dev ? y : out_dev; p.ldo = Cout;
+    p.rows = rows; p.K = Cin; p.N = Cout; p.taps = ksize; p.T = T;
+    NTB_TRY(launch_conv_gemm(cx, p));
+    if (scale_dev) {
+        k_window_groups<<<(unsigned)n_groups, 128, 0, cx.st>>>(group_off_dev, (int)n_groups, win_group);
+        NTB_TRY(launch_bn_stats(cx, y, Cout, T, group_off_dev, n_groups, scale_dev, offset_dev, a, b));
+        k_bn_apply<<<elementwise_grid(rows * Cout, 148), 256, 0, cx.st>>>(y, a, b, win_group, T, Cout, rows * Cout, relu, out_dev);
+    } else if (relu) {
+        k_bn_apply<<<elementwise_grid(rows * Cout, 148), 256, 0, cx.st>>>(out_dev, nullptr, nullptr, nullptr, T, Cout, rows * Cout, 1, out_dev);
+    }
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+extern "C" int64_t ntb_blstm_workspace_bytes(int64_t n_windows, int32_t T, int32_t D, int32_t H) {
+    const int Hp = pad_hidden(H);
+    Arena ar(nullptr, 0);
+    ar.take<float>((int64_t)D * 8 * Hp);
+    ar.take<float>(8 * Hp);
+    ar.take<float>(2LL * H * Hp * 4);
+    ar.take<float>(n_windows * T * 8LL * Hp);
+    return ar.off;
+}
+
+extern "C" int ntb_blstm(const float *in_dev, const int32_t *len_dev, const float *kernel_fw_dev,
+                         const float *bias_fw_dev, const float *kernel_bw_dev, const float *bias_bw_dev,
+                         float forget_bias, int64_t n_windows, int32_t T, int32_t D, int32_t H,
+                         void *workspace_dev, int64_t workspace_bytes, float *out_dev, void *stream) {
+    if (!in_dev || !len_dev || !kernel_fw_dev || !bias_fw_dev || !kernel_bw_dev || !bias_bw_dev || !out_dev ||
+        T <= 0 || D <= 0 || H <= 0)
+        return fail(NTB_EINVAL, "ntb_blstm: bad argument%s", "");
+    NTB_TRY(check_device());
+    Ctx cx{(cudaStream_t)stream, nullptr};
+    const int Hp = pad_hidden(H);
+    Arena ar(workspace_dev, workspace_bytes);
+    float *wih = ar.take<float>((int64_t)D * 8 * Hp);
+    float *bias = ar.take<float>(8 * Hp);
+    float *whh = ar.take<float>(2LL * H * Hp * 4);
+    float *xproj = ar.take<float>(n_windows * T * 8LL * Hp);
+    if (!workspace_dev || !ar.ok()) return fail(NTB_ENOMEM, "ntb_blstm: workspace too small (need %s%lld)", "", (long long)ar.off);
+    if (n_windows == 0) return NTB_OK;
+    k_repack_lstm<<<256, 256, 0, cx.st>>>(kernel_fw_dev, bias_fw_dev, kernel_bw_dev, bias_bw_dev, forget_bias, D, H, Hp, wih, bias, whh);
+    NTB_LAUNCH_CHECK();
+    NTB_TRY(dense(cx, in_dev, D, n_windows * T, D, 8 * Hp, wih, nullptr, bias, xproj, 8 * Hp, nullptr));
+    LstmParams p{};
+    p.xproj = xproj; p.ldx = 8 * Hp; p.whh = whh; p.lens = len_dev; p.out = out_dev; p.ldo = 2 * H;
+    p.n_windows = n_windows; p.T = T; p.H = H; p.Hp = Hp;
+    return launch_lstm(cx, p, 148);
+}
+
+extern "C" int ntb_decode(const float *logits_dev, const int32_t *len_dev, int64_t n_windows, int32_t T, int32_t C,
+                          int32_t graph, int32_t *labels_dev, int32_t *label_len_dev, void *stream) {
+    if (!logits_dev || !labels_dev || T <= 0 || C <= 0 || (graph == NTB_GRAPH_CTC && !len_dev))
+        return fail(NTB_EINVAL, "ntb_decode: bad argument%s", "");
+    NTB_TRY(check_device());
+    if (n_windows == 0) return NTB_OK;
+    const int64_t warps = graph == NTB_GRAPH_CROSS_ENTROPY ? n_windows * T : n_windows;
+    k_decode<<<cdiv(warps, 8), 256, 0, (cudaStream_t)stream>>>(logits_dev, len_dev, n_windows, T, C, graph, labels_dev, label_len_dev);
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+extern "C" int64_t ntb_gemm_workspace_bytes(int64_t M, int32_t N, int32_t K, int32_t impl) {
+    if (impl == 0) return 256;
+    Arena ar(nullptr, 0);
+    GemmWeights w;
+    gemm_tc_plan_weights(w, 1, K, N, ar);
+    GemmScratch gs;
+    gemm_tc_plan_scratch(gs, M, K, ar);
+    return ar.off + 256;
+}
+
+extern "C" int ntb_gemm(const float *a_dev, const float *b_dev, const float *bias_dev, int64_t M, int32_t N,
+                        int32_t K, int32_t impl, void *workspace_dev, int64_t workspace_bytes, float *out_dev,
+                        void *stream) {
+    if (!a_dev || !b_dev || !out_dev || M < 0 || N <= 0 || K <= 0) return fail(NTB_EINVAL, "ntb_gemm: bad argument%s", "");
+    NTB_TRY(check_device());
+    if (M == 0) return NTB_OK;
+    Ctx cx{(cudaStream_t)stream, nullptr};
+    if (impl == 0) return dense(cx, a_dev, K, M, K, N, b_dev, nullptr, bias_dev, out_dev, N, nullptr);
+    Arena ar(workspace_dev, workspace_bytes);
+    GemmWeights w;
+    gemm_tc_plan_weights(w, 1, K, N, ar);
+    GemmScratch gs;
+    gemm_tc_plan_scratch(gs, M, K, ar);
+    if (!w.valid || !gs.valid) return fail(NTB_EINVAL, "ntb_gemm: shape not supported by the tcgen05 path (K %% 16, N %% 16)%s", "");
+    if (!workspace_dev || !ar.ok()) return fail(NTB_ENOMEM, "ntb_gemm: workspace too small (need %s%lld)", "", (long long)ar.off);
+    w.single_pass = impl == 2;
+    NTB_TRY(gemm_tc_pack_weights(cx.st, b_dev, w));
+    return gemm_tc_run(cx.st, a_dev, K, M, w, bias_dev, out_dev, N, gs, &cx.launches);
+}

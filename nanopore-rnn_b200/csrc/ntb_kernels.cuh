@@ -1,0 +1,439 @@
+// Streaming / small-shape kernels of the NanoTensor forward: window packer, fp32 SIMT conv-GEMM
+// (odd shapes: Cin = 1, len_x = 12, H = 5), batch-statistics BN, residual combine, readout.
+// Reference semantics are cited per kernel (paths relative to the reference repository).
+#pragma once
+#include "ntb_common.cuh"
+
+namespace ntb {
+
+// ------------------------------------------------------------------------------------------
+// window -> BN group id   (group = one reference batch: network.py:339-349 takes moments over it)
+// ------------------------------------------------------------------------------------------
+__global__ void k_window_groups(const int32_t *__restrict__ group_off, int n_groups,
+                                int32_t *__restrict__ win_group) {
+    int g = blockIdx.x;
+    if (g >= n_groups) return;
+    int w0 = group_off[g], w1 = group_off[g + 1];
+    for (int w = w0 + threadIdx.x; w < w1; w += blockDim.x) win_group[w] = g;
+}
+
+// ------------------------------------------------------------------------------------------
+// K1  read z-score + windowing + zero pad
+//     dataset.py:435-445 (FullSignalSequence.load_data_inference), chiron_input.py:220-230
+//     (read_signal: (x - mean) / np.std over the WHOLE read, float64), dataset.py:157-169 (padding)
+// ------------------------------------------------------------------------------------------
+// pass 1: per-read mean and population std in float64, fixed reduction order (bit-stable)
+__global__ void __launch_bounds__(256) k_read_moments(const int16_t *__restrict__ raw,
+                                                      const int64_t *__restrict__ read_off,
+                                                      double *__restrict__ mean_std) {
+    __shared__ double sh[256];
+    const int r = blockIdx.x;
+    const int64_t s0 = read_off[r], s1 = read_off[r + 1];
+    const int64_t n = s1 - s0;
+    double acc = 0.0;
+    for (int64_t i = s0 + threadIdx.x; i < s1; i += 256) acc += (double)raw[i];
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    const double mean = n > 0 ? sh[0] / (double)n : 0.0;
+    __syncthreads();
+    acc = 0.0;
+    for (int64_t i = s0 + threadIdx.x; i < s1; i += 256) {
+        double d = (double)raw[i] - mean;
+        acc += d * d;
+    }
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        mean_std[2 * r] = mean;
+        mean_std[2 * r + 1] = n > 0 ? sqrt(sh[0] / (double)n) : 1.0;
+    }
+}
+
+// pass 2: one warp per window, coalesced reads of int16, float32 stores
+__global__ void __launch_bounds__(256) k_pack_windows(const int16_t *__restrict__ raw,
+                                                      const int64_t *__restrict__ read_off,
+                                                      const int64_t *__restrict__ win_off,
+                                                      const double *__restrict__ mean_std,
+                                                      int64_t n_reads, int64_t n_windows, int seq_len,
+                                                      int step, int start_index,
+                                                      float *__restrict__ x, int32_t *__restrict__ lens) {
+    const int64_t w = (int64_t)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+    const int lane = threadIdx.x & 31;
+    if (w >= n_windows) return;
+    // binary search: read r with win_off[r] <= w < win_off[r+1]
+    int64_t lo = 0, hi = n_reads;
+    while (hi - lo > 1) {
+        int64_t mid = (lo + hi) >> 1;
+        if (win_off[mid] <= w) lo = mid; else hi = mid;
+    }
+    const int64_t r = lo;
+    const int64_t s0 = read_off[r] + start_index, s1 = read_off[r + 1];
+    const int64_t first = s0 + (w - win_off[r]) * (int64_t)step;
+    int64_t valid = s1 - first;
+    valid = valid < 0 ? 0 : (valid > seq_len ? seq_len : valid);
+    const double mean = mean_std[2 * r], sd = mean_std[2 * r + 1];
+    for (int t = lane; t < seq_len; t += 32) {
+        float v = 0.0f;
+        if (t < valid) v = (float)(((double)raw[first + t] - mean) / sd);  // f64 then cast, as the tf feed does
+        x[w * seq_len + t] = v;
+    }
+    if (lane == 0) lens[w] = (int32_t)valid;
+}
+
+// ------------------------------------------------------------------------------------------
+// fp32 SIMT conv-as-GEMM with the producer's BN(+ReLU) applied on load
+//     out[r, n] = sum_tap sum_c f(A[r + tap - left, c]) * W[tap][c][n] (+ bias[n])
+//     f(v) = relu?(v * aff_a[g, c] + aff_b[g, c]) with g = BN group of the source row, and 0
+//     outside the window (tf.nn.conv2d SAME zero-pads the activated tensor, network.py:327-329)
+// Used for Cin = 1 convs, len_x = 12 / H = 5 event shapes and as the GPU-side check of the
+// tcgen05 path.
+// ------------------------------------------------------------------------------------------
+struct ConvGemmParams {
+    const float *A; int lda;          // [rows, K]
+    const float *W;                   // [taps, K, N]
+    const float *bias;                // [N] or null
+    const float *aff_a, *aff_b;       // [n_groups, K] or null
+    const int32_t *win_group;         // [n_windows] (only with aff)
+    float *out; int ldo;              // [rows, N]
+    int64_t rows; int K, N, taps, T, relu_in;
+};
+
+template <int BM, int BN, int BK, int TM, int TN>
+__global__ void __launch_bounds__((BM / TM) * (BN / TN)) k_conv_gemm_simt(ConvGemmParams p) {
+    constexpr int NT = (BM / TM) * (BN / TN);
+    __shared__ float As[BK][BM + 4];
+    __shared__ float Bs[BK][BN];
+    const int tid = threadIdx.x;
+    const int tx = tid % (BN / TN), ty = tid / (BN / TN);
+    const int64_t m0 = (int64_t)blockIdx.x * BM;
+    const int n0 = blockIdx.y * BN;
+    const int left = (p.taps - 1) / 2;
+    float acc[TM][TN];
+#pragma unroll
+    for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = 0.0f;
+
+    for (int tap = 0; tap < p.taps; ++tap) {
+        for (int k0 = 0; k0 < p.K; k0 += BK) {
+            for (int idx = tid; idx < BM * BK; idx += NT) {
+                const int m = idx / BK, kk = idx % BK;
+                const int64_t r = m0 + m;
+                const int c = k0 + kk;
+                float v = 0.0f;
+                if (r < p.rows && c < p.K) {
+                    const int t = (int)(r % p.T) + tap - left;
+                    if (t >= 0 && t < p.T) {
+                        const int64_t rr = r + tap - left;
+                        v = p.A[rr * p.lda + c];
+                        if (p.aff_a) {
+                            const int g = p.win_group[rr / p.T];
+                            v = v * p.aff_a[(int64_t)g * p.K + c] + p.aff_b[(int64_t)g * p.K + c];
+                        }
+                        if (p.relu_in) v = fmaxf(v, 0.0f);
+                    }
+                }
+                As[kk][m] = v;
+            }
+            for (int idx = tid; idx < BK * BN; idx += NT) {
+                const int kk = idx / BN, n = idx % BN;
+                const int c = k0 + kk;
+                float v = 0.0f;
+                if (c < p.K && n0 + n < p.N) v = p.W[((int64_t)tap * p.K + c) * p.N + n0 + n];
+                Bs[kk][n] = v;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int kk = 0; kk < BK; ++kk) {
+                float a[TM], b[TN];
+#pragma unroll
+                for (int i = 0; i < TM; ++i) a[i] = As[kk][ty * TM + i];
+#pragma unroll
+                for (int j = 0; j < TN; ++j) b[j] = Bs[kk][tx * TN + j];
+#pragma unroll
+                for (int i = 0; i < TM; ++i)
+#pragma unroll
+                    for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+            }
+            __syncthreads();
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < TM; ++i) {
+        const int64_t r = m0 + ty * TM + i;
+        if (r >= p.rows) continue;
+#pragma unroll
+        for (int j = 0; j < TN; ++j) {
+            const int n = n0 + tx * TN + j;
+            if (n < p.N) p.out[r * p.ldo + n] = acc[i][j] + (p.bias ? p.bias[n] : 0.0f);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// simple_global_bn statistics (network.py:339-349): tf.nn.moments over axes [0,1,2] of ONE
+// reference batch (= BN group; padded positions included), then the affine form
+// tf.nn.batch_normalization uses:  a = rsqrt(var + eps) * scale ; b = offset - mean * a.
+// One thread per (group, channel); float64 accumulation in fixed row order -> bit-stable.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_bn_stats(const float *__restrict__ y, int C, int T,
+                                                  const int32_t *__restrict__ group_off,
+                                                  const float *__restrict__ scale,
+                                                  const float *__restrict__ offset, float eps,
+                                                  float *__restrict__ aff_a, float *__restrict__ aff_b) {
+    const int g = blockIdx.x;
+    const int c = blockIdx.y * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const int64_t r0 = (int64_t)group_off[g] * T, r1 = (int64_t)group_off[g + 1] * T;
+    const int64_t n = r1 - r0;
+    const float *p = y + r0 * C + c;
+    double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+    int64_t i = 0;
+    for (; i + 4 <= n; i += 4) {
+        s0 += (double)p[(i + 0) * C];
+        s1 += (double)p[(i + 1) * C];
+        s2 += (double)p[(i + 2) * C];
+        s3 += (double)p[(i + 3) * C];
+    }
+    for (; i < n; ++i) s0 += (double)p[i * C];
+    const double mean = n > 0 ? ((s0 + s1) + (s2 + s3)) / (double)n : 0.0;
+    s0 = s1 = s2 = s3 = 0;
+    for (i = 0; i + 4 <= n; i += 4) {
+        double d0 = (double)p[(i + 0) * C] - mean, d1 = (double)p[(i + 1) * C] - mean;
+        double d2 = (double)p[(i + 2) * C] - mean, d3 = (double)p[(i + 3) * C] - mean;
+        s0 += d0 * d0; s1 += d1 * d1; s2 += d2 * d2; s3 += d3 * d3;
+    }
+    for (; i < n; ++i) { double d = (double)p[i * C] - mean; s0 += d * d; }
+    const double var = n > 0 ? ((s0 + s1) + (s2 + s3)) / (double)n : 0.0;
+    const float a = (1.0f / sqrtf((float)var + eps)) * scale[c];
+    aff_a[(int64_t)g * C + c] = a;
+    aff_b[(int64_t)g * C + c] = offset[c] - (float)mean * a;
+}
+
+// out = relu?( y*a + b )   -- materialised BN(+ReLU) (op-level entry point / odd shapes)
+__global__ void __launch_bounds__(256) k_bn_apply(const float *__restrict__ y, const float *__restrict__ a,
+                                                  const float *__restrict__ b,
+                                                  const int32_t *__restrict__ win_group, int T, int C,
+                                                  int64_t total, int relu, float *__restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < total; i += stride) {
+        const int64_t r = i / C;
+        const int c = (int)(i % C);
+        float v = y[i];
+        if (a) {
+            const int g = win_group[r / T];
+            v = v * a[(int64_t)g * C + c] + b[(int64_t)g * C + c];
+        }
+        out[i] = relu ? fmaxf(v, 0.0f) : v;
+    }
+}
+
+// residual_layer tail (network.py:398-399): relu( bn?(branch1) + bn(conv2c) ), float4 streaming
+__global__ void __launch_bounds__(256) k_residual_combine(
+    const float4 *__restrict__ y1, const float *__restrict__ a1, const float *__restrict__ b1,
+    const float4 *__restrict__ y2, const float *__restrict__ a2, const float *__restrict__ b2,
+    const int32_t *__restrict__ win_group, int T, int C, int64_t total4, float4 *__restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int C4 = C / 4;
+    for (; i < total4; i += stride) {
+        const int64_t r = i / C4;
+        const int c = (int)(i % C4) * 4;
+        const int g = win_group[r / T];
+        float4 u = y1[i], v = y2[i];
+        const float4 va = *(const float4 *)(a2 + (int64_t)g * C + c);
+        const float4 vb = *(const float4 *)(b2 + (int64_t)g * C + c);
+        v.x = v.x * va.x + vb.x; v.y = v.y * va.y + vb.y; v.z = v.z * va.z + vb.z; v.w = v.w * va.w + vb.w;
+        if (a1) {
+            const float4 ua = *(const float4 *)(a1 + (int64_t)g * C + c);
+            const float4 ub = *(const float4 *)(b1 + (int64_t)g * C + c);
+            u.x = u.x * ua.x + ub.x; u.y = u.y * ua.y + ub.y; u.z = u.z * ua.z + ub.z; u.w = u.w * ua.w + ub.w;
+        }
+        float4 o;
+        o.x = fmaxf(u.x + v.x, 0.0f); o.y = fmaxf(u.y + v.y, 0.0f);
+        o.z = fmaxf(u.z + v.z, 0.0f); o.w = fmaxf(u.w + v.w, 0.0f);
+        out[i] = o;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// chiron_fnn (network.py:164-175): out[r,h] = v[r,h]*w[0,h] + v[r,H+h]*w[1,h] + b[h]
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_chiron_fnn(const float *__restrict__ v, const float *__restrict__ w,
+                                                    const float *__restrict__ b, int H, int64_t rows,
+                                                    float *__restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x, total = rows * H;
+    for (; i < total; i += stride) {
+        const int64_t r = i / H;
+        const int h = (int)(i % H);
+        out[i] = v[r * 2 * H + h] * w[h] + v[r * 2 * H + H + h] * w[H + h] + b[h];
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Fused readout for small C (the CTC configs: C = 4..6): one warp per window walks t,
+//   [chiron_fnn] -> dense (network.py:291-309) -> argmax (first max) -> CTC greedy merge
+//   (tf.nn.ctc_greedy_decoder merge_repeated=True, blank = C-1, prev updated every step;
+//    sparse_tensor_to_dense default -1; network.py:528-533) or plain argmax (network.py:208-211).
+// Dense applies to ALL positions (padded ones too) so the optional logits match the reference's
+// output_layer; decoding stops at len[b].
+// ------------------------------------------------------------------------------------------
+template <int MAXC>
+__global__ void __launch_bounds__(256) k_readout_small(
+    const float *__restrict__ v, int F_in,                       // [rows, F_in]; F_in = 2H with fnn, else F
+    const float *__restrict__ fnn_w, const float *__restrict__ fnn_b,   // null = no fnn
+    const float *__restrict__ out_w, const float *__restrict__ out_b,   // [F, C], [C]
+    const int32_t *__restrict__ lens, int64_t n_windows, int T, int C, int graph,
+    float *__restrict__ logits, int32_t *__restrict__ labels, int32_t *__restrict__ label_len) {
+    extern __shared__ float sm[];
+    const int F = fnn_w ? F_in / 2 : F_in;
+    float *sw = sm;                 // [F][C]
+    float *sf = sw + F * C;         // fnn_w [2][F], fnn_b [F]
+    for (int i = threadIdx.x; i < F * C; i += blockDim.x) sw[i] = out_w[i];
+    if (fnn_w) {
+        for (int i = threadIdx.x; i < 2 * F; i += blockDim.x) sf[i] = fnn_w[i];
+        for (int i = threadIdx.x; i < F; i += blockDim.x) sf[2 * F + i] = fnn_b[i];
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int64_t w = (int64_t)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+    if (w >= n_windows) return;
+    const int len = lens[w];
+    int prev = -1, cnt = 0;
+    for (int t = 0; t < T; ++t) {
+        const float *row = v + (w * T + t) * (int64_t)F_in;
+        float part[MAXC];
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) part[c] = 0.0f;
+        for (int f = lane; f < F; f += 32) {
+            float y = fnn_w ? row[f] * sf[f] + row[F + f] * sf[F + f] + sf[2 * F + f] : row[f];
+#pragma unroll
+            for (int c = 0; c < MAXC; ++c)
+                if (c < C) part[c] = fmaf(y, sw[f * C + c], part[c]);
+        }
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) part[c] += __shfl_xor_sync(0xffffffffu, part[c], o);
+        }
+        int best = 0;
+        float bv = 0.0f;
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) {
+            if (c < C) {
+                const float lg = part[c] + out_b[c];
+                if (logits && lane == c % 32) logits[(w * T + t) * (int64_t)C + c] = lg;
+                if (c == 0 || lg > bv) { bv = lg; best = c; }   // strict > : first max wins
+            }
+        }
+        if (graph == NTB_GRAPH_CTC) {
+            if (t < len) {
+                if (best != C - 1 && best != prev) {
+                    if (lane == 0) labels[w * T + cnt] = best;
+                    ++cnt;
+                }
+                prev = best;
+            }
+        } else if (lane == 0) {
+            labels[w * T + t] = best;
+        }
+    }
+    if (graph == NTB_GRAPH_CTC) {
+        for (int i = cnt + lane; i < T; i += 32) labels[w * T + i] = -1;
+        if (lane == 0 && label_len) label_len[w] = cnt;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Decode for large C (event model, C = 1025): logits already materialised by the dense GEMM.
+// argmax: one warp per row; CTC: one warp per window walking t.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int warp_argmax_first(const float *row, int C, int lane) {
+    float bv = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int c = lane; c < C; c += 32) {
+        const float x = row[c];
+        if (x > bv || (x == bv && c < bi)) { bv = x; bi = c; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    }
+    return bi == 0x7fffffff ? 0 : bi;   // all-NaN row -> 0 like a first-max scan
+}
+
+__global__ void __launch_bounds__(256) k_decode(const float *__restrict__ logits,
+                                                const int32_t *__restrict__ lens, int64_t n_windows,
+                                                int T, int C, int graph, int32_t *__restrict__ labels,
+                                                int32_t *__restrict__ label_len) {
+    const int lane = threadIdx.x & 31;
+    const int64_t gw = (int64_t)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+    if (graph == NTB_GRAPH_CROSS_ENTROPY) {
+        if (gw >= n_windows * T) return;
+        const int best = warp_argmax_first(logits + gw * C, C, lane);
+        if (lane == 0) labels[gw] = best;
+        return;
+    }
+    if (gw >= n_windows) return;
+    const int len = lens[gw];
+    int prev = -1, cnt = 0;
+    for (int t = 0; t < len && t < T; ++t) {
+        const int best = warp_argmax_first(logits + (gw * T + t) * (int64_t)C, C, lane);
+        if (best != C - 1 && best != prev) {
+            if (lane == 0) labels[gw * T + cnt] = best;
+            ++cnt;
+        }
+        prev = best;
+    }
+    for (int i = cnt + lane; i < T; i += 32) labels[gw * T + i] = -1;
+    if (lane == 0 && label_len) label_len[gw] = cnt;
+}
+
+// ------------------------------------------------------------------------------------------
+// Weight repack (device side, once per model): TF LSTMCell kernel [D+H, 4H] with gate column
+// blocks i|j|f|o (network.py:275-282; rnn_cell_impl.LSTMCell) ->
+//   wih  [D, 2*4*Hp]  projection B operand, column = dir*4Hp + u*4 + g  (gate-interleaved)
+//   bias [2*4*Hp]     bias with forget_bias folded into the f slot (TF adds it at run time)
+//   whh  [2][H][4][UG][4]  recurrence tile: float4 (i,j,f,o) of unit u = ug*4 + q at [k][q][ug]
+// Pad units (u >= H) get zero weights and zero bias.
+// ------------------------------------------------------------------------------------------
+__global__ void k_repack_lstm(const float *__restrict__ kernel_fw, const float *__restrict__ bias_fw,
+                              const float *__restrict__ kernel_bw, const float *__restrict__ bias_bw,
+                              float forget_bias, int D, int H, int Hp, float *__restrict__ wih,
+                              float *__restrict__ bias, float *__restrict__ whh) {
+    const int N = 2 * 4 * Hp;
+    const int UG = Hp / 4;
+    const int64_t total = (int64_t)(D + 1 + H) * N;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int row = (int)(i / N), col = (int)(i % N);
+        const int dir = col / (4 * Hp), u = (col % (4 * Hp)) / 4, g = col % 4;
+        const float *kern = dir ? kernel_bw : kernel_fw;
+        const float *bs = dir ? bias_bw : bias_fw;
+        const bool real = u < H;
+        if (row < D) {
+            wih[(int64_t)row * N + col] = real ? kern[(int64_t)row * 4 * H + g * H + u] : 0.0f;
+        } else if (row == D) {
+            bias[col] = real ? bs[g * H + u] + (g == 2 ? forget_bias : 0.0f) : 0.0f;
+        } else {
+            const int k = row - D - 1;
+            const int ug = u / 4, q = u % 4;
+            whh[(((int64_t)dir * H + k) * 4 + q) * UG * 4 + ug * 4 + g] =
+                real ? kern[(int64_t)(D + k) * 4 * H + g * H + u] : 0.0f;
+        }
+    }
+}
+
+}  // namespace ntb

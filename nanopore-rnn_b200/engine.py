@@ -1,0 +1,265 @@
+"""Host-side engine: owns the GPU-resident repacked weights (through the C ABI), plans
+BN-group-aligned chunks of windows and drives ``ntb_model_forward`` / ``_forward_host``.
+
+torch is used for device memory, streams and pinned host buffers only."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import (NTB_GRAPH_CROSS_ENTROPY, NTB_GRAPH_CTC, NTB_LAYER_BLSTM, NTB_LAYER_CHIRON_FNN,
+                   NTB_LAYER_RESIDUAL, NtbLayer, NtbModelDesc)
+
+GRAPHS = {"CrossEntropy": NTB_GRAPH_CROSS_ENTROPY, "CtcLoss": NTB_GRAPH_CTC}
+# recurrence tile = 64 windows x 2 directions; 74 tiles x 2 = one wave of 148 SMs
+_WAVE_WINDOWS = 64 * 74
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _stream_ptr(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def group_offsets(read_window_counts, batch_size):
+    """BN groups = the reference's batches: consecutive ``batch_size`` windows of ONE read, last
+    batch of a read short (dataset.py:374-377 ``dataset.batch(batch_size)`` per file,
+    run_nanotensor.py:339-347).  Returns int32 offsets [n_groups+1]."""
+    offs = [0]
+    pos = 0
+    for n in read_window_counts:
+        n = int(n)
+        full, rem = divmod(n, batch_size)
+        sizes = [batch_size] * full + ([rem] if rem else [])
+        for s in sizes:
+            pos += s
+            offs.append(pos)
+    return np.asarray(offs, dtype=np.int32)
+
+
+def plan_chunks(group_off, max_windows):
+    """Split [0, n_groups) into runs of whole groups with <= max_windows windows each, preferring
+    a multiple of one recurrence wave (64 windows x 74 tiles x 2 directions = 148 CTAs)."""
+    group_off = np.asarray(group_off, dtype=np.int64)
+    n_groups = len(group_off) - 1
+    total = int(group_off[-1])
+    if total <= max_windows:
+        return [(0, n_groups)]
+    target = max_windows
+    if max_windows >= _WAVE_WINDOWS:
+        target = (max_windows // _WAVE_WINDOWS) * _WAVE_WINDOWS
+    chunks = []
+    g = 0
+    while g < n_groups:
+        limit = group_off[g] + target
+        h = int(np.searchsorted(group_off, limit, side="right")) - 1
+        if h <= g:
+            h = g + 1
+            if group_off[h] - group_off[g] > max_windows:
+                raise ValueError("a single BN group (%d windows) exceeds the chunk size %d"
+                                 % (group_off[h] - group_off[g], max_windows))
+        chunks.append((g, h))
+        g = h
+    return chunks
+
+
+class Model:
+    """GPU-resident NanoTensor network (config ``network`` list + TF-layout weights)."""
+
+    def __init__(self, network, weights, graph, seq_len, len_x, n_classes, device="cuda:0"):
+        self.lib = _lib.load()
+        if graph not in GRAPHS:
+            raise ValueError("graph must be one of %s" % sorted(GRAPHS))
+        self.network = [dict(l) for l in network]
+        self.graph = graph
+        self.T, self.len_x, self.C = int(seq_len), int(len_x), int(n_classes)
+        self.device = torch.device(device)
+        if self.device.type != "cuda" or not torch.cuda.is_available():
+            raise _lib.NtbError(-2, "nanotensor_b200 needs a CUDA sm_100 device; there is no CPU fallback")
+        self.has_residual = any(l["type"] == "residual_layer" for l in network)
+        keep = []   # host arrays referenced by the desc must outlive ntb_model_create
+
+        def arr(a):
+            a = np.ascontiguousarray(a, dtype=np.float32)
+            keep.append(a)
+            return _fp(a)
+
+        layers = (NtbLayer * len(network))()
+        dim = self.len_x
+        for i, (l, w) in enumerate(zip(network, weights["layers"])):
+            L = layers[i]
+            L.in_dim = dim
+            if l["type"] == "residual_layer":
+                L.type, L.size, L.batchnorm = NTB_LAYER_RESIDUAL, int(l["out_channel"]), int(bool(l.get("batchnorm")))
+                order = ["conv1", "conv1_bn_scale", "conv1_bn_offset", "conv2a", "conv2a_bn_scale",
+                         "conv2a_bn_offset", "conv2b", "conv2b_bn_scale", "conv2b_bn_offset", "conv2c",
+                         "conv2c_bn_scale", "conv2c_bn_offset"]
+                for k, name in enumerate(order):
+                    if name in w:
+                        L.w[k] = arr(w[name])
+                dim = L.size
+            elif l["type"] == "blstm":
+                if not l.get("concat", True):
+                    raise ValueError("blstm layer %r: concat must be true (network.py:284-287)" % l.get("name"))
+                L.type, L.size, L.forget_bias = NTB_LAYER_BLSTM, int(l["size"]), float(l["bias"])
+                for k, name in enumerate(["kernel_fw", "bias_fw", "kernel_bw", "bias_bw"]):
+                    L.w[k] = arr(w[name])
+                if w["kernel_fw"].shape != (dim + L.size, 4 * L.size):
+                    raise ValueError("blstm layer %r: kernel shape %s, expected %s"
+                                     % (l.get("name"), w["kernel_fw"].shape, (dim + L.size, 4 * L.size)))
+                dim = 2 * L.size
+            elif l["type"] == "chiron_fnn":
+                L.type, L.size = NTB_LAYER_CHIRON_FNN, dim // 2
+                L.w[0], L.w[1] = arr(w["weights"]), arr(w["bias"])
+                dim = dim // 2
+            else:
+                raise ValueError("layer type %r is not on the supported forward path" % l["type"])
+        if tuple(weights["out_w"].shape) != (dim, self.C):
+            raise ValueError("output layer weights %s, expected %s" % (weights["out_w"].shape, (dim, self.C)))
+        self.final_dim = dim
+        desc = NtbModelDesc(GRAPHS[graph], self.T, self.len_x, self.C, len(network), layers,
+                            arr(weights["out_w"]), arr(weights["out_b"]))
+        nbytes = self.lib.ntb_model_weight_bytes(C.byref(desc))
+        if nbytes < 0:
+            _lib.check(int(nbytes))
+        with torch.cuda.device(self.device):
+            self._weights = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+            handle = C.c_void_p()
+            _lib.check(self.lib.ntb_model_create(C.byref(desc), _ptr(self._weights), nbytes,
+                                                 _stream_ptr(self.device), C.byref(handle)))
+        self._h = handle
+        self._ws = None
+        del keep
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.ntb_model_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    # ------------------------------------------------------------------ workspace
+    def workspace_bytes(self, n_windows, n_groups, host=False, want_logits=False):
+        if host:
+            return int(self.lib.ntb_model_workspace_bytes_host(self._h, n_windows, n_groups, int(want_logits)))
+        return int(self.lib.ntb_model_workspace_bytes(self._h, n_windows, n_groups))
+
+    def _workspace(self, nbytes):
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = None
+            self._ws = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def max_chunk_windows(self, budget_bytes=None, groups_per_window=0.1):
+        """Largest chunk whose workspace fits ``budget_bytes`` (default: 60 % of free HBM)."""
+        if budget_bytes is None:
+            free, _ = torch.cuda.mem_get_info(self.device)
+            budget_bytes = int(free * 0.6)
+        per = self.workspace_bytes(4096, int(4096 * groups_per_window) + 1, host=True) / 4096.0
+        n = int(budget_bytes / per)
+        return max(64, min(n, 16 * _WAVE_WINDOWS))
+
+    # ------------------------------------------------------------------ forward, device-resident inputs
+    def forward_device(self, x, lens, group_off=None, want_logits=False, labels_out=None, label_len_out=None):
+        """One chunk with inputs already in HBM.  x [n,T(,len_x)] f32, lens [n] i32, group_off
+        [n_groups+1] i32 (all cuda tensors).  Returns (labels i32, label_len i32 | None, logits | None)."""
+        n = int(x.shape[0])
+        ng = int(group_off.numel()) - 1 if group_off is not None else 0
+        if self.has_residual and group_off is None:
+            raise ValueError("networks with residual layers need group_off (BN groups)")
+        rows = n * self.T
+        with torch.cuda.device(self.device):
+            ws = self._workspace(self.workspace_bytes(n, ng))
+            labels = labels_out if labels_out is not None else torch.empty(max(rows, 1), dtype=torch.int32, device=self.device)
+            llen = None
+            if self.graph == "CtcLoss":
+                llen = label_len_out if label_len_out is not None else torch.empty(max(n, 1), dtype=torch.int32, device=self.device)
+            logits = torch.empty((rows, self.C), dtype=torch.float32, device=self.device) if want_logits else None
+            _lib.check(self.lib.ntb_model_forward(
+                self._h, _ptr(x), _ptr(lens), _ptr(group_off), n, ng, _ptr(ws), ws.numel(),
+                _ptr(logits), _ptr(labels), _ptr(llen), _stream_ptr(self.device)))
+        return labels[:rows], (llen[:n] if llen is not None else None), logits
+
+    # ------------------------------------------------------------------ forward, host buffers (end to end)
+    def forward_host(self, x, lens, group_off=None, want_logits=False, max_windows=None):
+        """Whole job from HOST arrays (numpy or CPU torch tensors; pinned is faster): chunked on BN
+        group boundaries, host->device copies and device->host label reads inside.  Returns
+        (labels int32 [n*T] (CrossEntropy) or [n,T] (CtcLoss, -1 padded), label_len int32 [n] | None,
+        logits float32 [n*T, C] | None) as numpy arrays."""
+        x = _as_np(x, np.float32)
+        lens = _as_np(lens, np.int32)
+        n = int(x.shape[0])
+        if group_off is None:
+            if self.has_residual:
+                raise ValueError("networks with residual layers need group_off (BN groups)")
+            step = max_windows or self.max_chunk_windows()
+            group_off = np.arange(0, n + step, step, dtype=np.int64).clip(max=n)
+            group_off = np.unique(group_off).astype(np.int32)
+            if n == 0:
+                group_off = np.zeros(1, dtype=np.int32)
+            pass_groups = False
+        else:
+            group_off = _as_np(group_off, np.int32)
+            pass_groups = True
+        T, Cc = self.T, self.C
+        labels = np.empty((n * T,), dtype=np.int32)
+        llen = np.empty((n,), dtype=np.int32) if self.graph == "CtcLoss" else None
+        logits = np.empty((n * T, Cc), dtype=np.float32) if want_logits else None
+        if n == 0:
+            return self._shape_labels(labels, n), llen, logits
+        chunks = plan_chunks(group_off, max_windows or self.max_chunk_windows())
+        stream = _stream_ptr(self.device)
+        with torch.cuda.device(self.device):
+            wmax = max(int(group_off[h] - group_off[g]) for g, h in chunks)
+            gmax = max(h - g for g, h in chunks)
+            ws = self._workspace(self.workspace_bytes(wmax, gmax, host=True, want_logits=want_logits))
+            for g, h in chunks:
+                w0, w1 = int(group_off[g]), int(group_off[h])
+                nw = w1 - w0
+                goff = np.ascontiguousarray(group_off[g:h + 1] - group_off[g], dtype=np.int32)
+                xs = x[w0:w1]
+                ls = lens[w0:w1]
+                _lib.check(self.lib.ntb_model_forward_host(
+                    self._h, C.c_void_p(xs.ctypes.data), C.c_void_p(ls.ctypes.data),
+                    C.c_void_p(goff.ctypes.data) if pass_groups else C.c_void_p(0), nw,
+                    (h - g) if pass_groups else 0, _ptr(ws), ws.numel(),
+                    C.c_void_p(logits[w0 * T:].ctypes.data) if want_logits else C.c_void_p(0),
+                    C.c_void_p(labels[w0 * T:].ctypes.data),
+                    C.c_void_p(llen[w0:].ctypes.data) if llen is not None else C.c_void_p(0), stream))
+        return self._shape_labels(labels, n), llen, logits
+
+    def _shape_labels(self, labels, n):
+        return labels.reshape(n, self.T) if self.graph == "CtcLoss" else labels
+
+    # ------------------------------------------------------------------ introspection
+    def last_launches(self):
+        return int(self.lib.ntb_model_last_launches(self._h))
+
+    def set_profile(self, on):
+        self.lib.ntb_model_set_profile(self._h, int(bool(on)))
+
+    def stage_ms(self):
+        buf = (C.c_float * 4)()
+        k = self.lib.ntb_model_stage_ms(self._h, buf, 4)
+        return dict(zip(["conv_bn", "projection", "recurrence", "readout"][:k], list(buf)[:k]))
+
+
+def _as_np(a, dtype):
+    if isinstance(a, torch.Tensor):
+        a = a.detach().cpu().numpy()
+    return np.ascontiguousarray(a, dtype=dtype)
+
+
+def ctc_dense(labels, label_len):
+    """[n, T] -1-padded device/host labels -> the reference's dense int64 [n, max_decoded]
+    (tf.sparse_tensor_to_dense(default_value=-1), network.py:532)."""
+    labels = np.asarray(labels)
+    width = int(label_len.max()) if len(label_len) else 0
+    return labels[:, :width].astype(np.int64)

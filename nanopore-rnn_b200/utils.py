@@ -1,0 +1,54 @@
+"""Config helpers used by the driver (restates nanotensor/utils.py:158-163 DotDict, :217-223
+load_json, :44-66 list_dir, :150-155 merge_two_dicts of the reference)."""
+import json
+import os
+import time
+
+
+class DotDict(dict):
+    """dict with attribute access; nested dicts are wrapped on read."""
+
+    def __getattr__(self, name):
+        try:
+            v = self[name]
+        except KeyError as e:
+            raise AttributeError(name) from e
+        if isinstance(v, dict) and not isinstance(v, DotDict):
+            v = DotDict(v)
+            self[name] = v
+        return v
+
+    __setattr__ = dict.__setitem__
+    __delattr__ = dict.__delitem__
+
+
+def load_json(path):
+    with open(path) as fh:
+        return json.load(fh)
+
+
+def save_json(obj, path):
+    with open(path, "w") as fh:
+        json.dump(obj, fh, indent=2)
+    return path
+
+
+def list_dir(path, ext=""):
+    """Sorted absolute paths of the files in ``path`` ending with ``ext``."""
+    if ext:
+        names = [f for f in os.listdir(path) if f.endswith(ext)]
+    else:
+        names = [f for f in os.listdir(path) if os.path.isfile(os.path.join(path, f))]
+    return sorted(os.path.join(os.path.abspath(path), f) for f in names)
+
+
+def merge_two_dicts(a, b):
+    out = dict(a)
+    out.update(b)
+    return out
+
+
+def time_it(fn, *args, **kw):
+    t0 = time.perf_counter()
+    fn(*args, **kw)
+    return time.perf_counter() - t0
