@@ -288,3 +288,146 @@ def weights_for_network(variables, network, model_name=None):
     # output layer variables are created under a name_scope only -> un-scoped names
     # (network.py:79-80, 298-301)
     return {"layers": layers, "out_w": get("weights"), "out_b": get("bias")}
+
+
+# ---------------------------------------------------------------------------------------------
+# writer: emits the same bundle format (single shard, uncompressed blocks, masked CRC32C), so
+# synthetic / converted weights can be handed to the unmodified config keys
+# (trained_model_path / trained_model + use_checkpoint).
+# ---------------------------------------------------------------------------------------------
+_CRC_TABLE = None
+
+
+def _crc32c(data, crc=0):
+    global _CRC_TABLE
+    if _CRC_TABLE is None:
+        tab = []
+        for i in range(256):
+            c = i
+            for _ in range(8):
+                c = (c >> 1) ^ 0x82F63B78 if c & 1 else c >> 1
+            tab.append(c)
+        _CRC_TABLE = np.array(tab, dtype=np.uint32)
+    crc ^= 0xFFFFFFFF
+    tab = _CRC_TABLE
+    for b in bytes(data):
+        crc = int(tab[(crc ^ b) & 0xFF]) ^ (crc >> 8)
+    return crc ^ 0xFFFFFFFF
+
+
+def _mask_crc(crc):
+    return (((crc >> 15) | (crc << 17)) + 0xA282EAD8) & 0xFFFFFFFF
+
+
+def _enc_varint(v):
+    out = bytearray()
+    while True:
+        b = v & 0x7F
+        v >>= 7
+        if v:
+            out.append(b | 0x80)
+        else:
+            out.append(b)
+            return bytes(out)
+
+
+def _enc_field(field, wt, payload):
+    return _enc_varint((field << 3) | wt) + payload
+
+
+def _enc_entry(dtype_enum, shape, offset, size, crc):
+    shape_msg = b"".join(_enc_field(2, 2, _enc_varint(len(d)) + d)
+                         for d in (_enc_field(1, 0, _enc_varint(int(s))) for s in shape))
+    msg = _enc_field(1, 0, _enc_varint(dtype_enum))
+    msg += _enc_field(2, 2, _enc_varint(len(shape_msg)) + shape_msg)
+    if offset:
+        msg += _enc_field(4, 0, _enc_varint(offset))
+    msg += _enc_field(5, 0, _enc_varint(size))
+    msg += _enc_field(6, 5, struct.pack("<I", _mask_crc(crc)))
+    return msg
+
+
+def _build_block(items):
+    """items: [(key bytes, value bytes)] sorted; no prefix sharing, one restart per entry."""
+    body = bytearray()
+    restarts = []
+    for k, v in items:
+        restarts.append(len(body))
+        body += _enc_varint(0) + _enc_varint(len(k)) + _enc_varint(len(v)) + k + v
+    if not restarts:
+        restarts = [0]
+    for r in restarts:
+        body += struct.pack("<I", r)
+    body += struct.pack("<I", len(restarts))
+    return bytes(body)
+
+
+def save_checkpoint(prefix, variables):
+    """Write ``{name: array}`` as ``<prefix>.index`` + ``<prefix>.data-00000-of-00001``."""
+    enum_of = {np.dtype(v): k for k, v in _DTYPES.items()}
+    data = bytearray()
+    items = []
+    for name in sorted(variables, key=lambda s: s.encode("utf-8")):
+        arr = np.ascontiguousarray(variables[name])
+        if arr.dtype not in enum_of:
+            raise CheckpointError("variable %s: dtype %s not supported" % (name, arr.dtype))
+        raw = arr.astype(arr.dtype.newbyteorder("<"), copy=False).tobytes()
+        items.append((name.encode("utf-8"), _enc_entry(enum_of[arr.dtype], arr.shape, len(data), len(raw),
+                                                       _crc32c(raw))))
+        data += raw
+    # BundleHeaderProto {1: num_shards = 1, 2: endianness = LITTLE(0), 3: version{1: producer = 1}}
+    header = _enc_field(1, 0, _enc_varint(1)) + _enc_field(3, 2, _enc_varint(2) + _enc_field(1, 0, _enc_varint(1)))
+    items = [(b"", header)] + items
+    out = bytearray()
+
+    def emit(block):
+        off = len(out)
+        out.extend(block)
+        trailer_crc = _mask_crc(_crc32c(b"\x00", _crc32c(block)))
+        out.extend(b"\x00" + struct.pack("<I", trailer_crc))
+        return off, len(block)
+
+    d_off, d_size = emit(_build_block(items))
+    m_off, m_size = emit(_build_block([]))
+    handle = _enc_varint(d_off) + _enc_varint(d_size)
+    i_off, i_size = emit(_build_block([(items[-1][0] + b"\x00", handle)]))
+    footer = _enc_varint(m_off) + _enc_varint(m_size) + _enc_varint(i_off) + _enc_varint(i_size)
+    footer += b"\x00" * (40 - len(footer)) + struct.pack("<Q", _TABLE_MAGIC)
+    out.extend(footer)
+    with open(prefix + ".index", "wb") as fh:
+        fh.write(bytes(out))
+    with open(prefix + ".data-00000-of-00001", "wb") as fh:
+        fh.write(bytes(data))
+    with open(os.path.join(os.path.dirname(prefix) or ".", "checkpoint"), "w") as fh:
+        fh.write('model_checkpoint_path: "%s"\n' % os.path.basename(prefix))
+    return prefix
+
+
+def variables_from_weights(weights, network, model_name=None, old_names=False):
+    """Inverse of ``weights_for_network``: the TF variable names the reference's code creates
+    (network.py:165-172, 298-301, 315-347 and rnn.LSTMCell's kernel/bias)."""
+    pre = model_name + "/" if model_name else ""
+    kern, bias = ("weights", "biases") if old_names else ("kernel", "bias")
+    out = {}
+    for layer, w in zip(network, weights["layers"]):
+        nm = pre + layer["name"]
+        if layer["type"] == "blstm":
+            for d in ("fw", "bw"):
+                out["%s/bidirectional_rnn/%s/lstm_cell/%s" % (nm, d, kern)] = w["kernel_" + d]
+                out["%s/bidirectional_rnn/%s/lstm_cell/%s" % (nm, d, bias)] = w["bias_" + d]
+        elif layer["type"] == "residual_layer":
+            out[nm + "/branch1/conv1/weights"] = w["conv1"]
+            if layer.get("batchnorm"):
+                out[nm + "/branch1/conv1_bn/conv1_bn_scale"] = w["conv1_bn_scale"]
+                out[nm + "/branch1/conv1_bn/conv1_bn_offset"] = w["conv1_bn_offset"]
+            for c in ("conv2a", "conv2b", "conv2c"):
+                out["%s/branch2/%s/weights" % (nm, c)] = w[c]
+                out["%s/branch2/%s_bn/%s_bn_scale" % (nm, c, c)] = w[c + "_bn_scale"]
+                out["%s/branch2/%s_bn/%s_bn_offset" % (nm, c, c)] = w[c + "_bn_offset"]
+        elif layer["type"] == "chiron_fnn":
+            out[nm + "/weights"] = w["weights"]
+            out[nm + "/bias"] = w["bias"]
+    out[pre + "weights"] = weights["out_w"]
+    out[pre + "bias"] = weights["out_b"]
+    out[pre + "global_step"] = np.float32(0.0).reshape(())
+    return out

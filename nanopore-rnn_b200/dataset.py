@@ -138,7 +138,7 @@ class CreateDataset(object):
             try:
                 np.load(f, allow_pickle=True, encoding="latin1")
                 good.append(f)
-            except (IOError, ValueError, EOFError):
+            except Exception:   # unreadable / not an npy file (the reference catches IOError)
                 bad.append(f)
         return good, bad
 

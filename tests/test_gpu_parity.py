@@ -1,0 +1,299 @@
+"""GPU (-m gpu): parity of the CUDA path against the CPU oracle, called through the C ABI.
+
+Tolerances (BASELINE.json north_star): float32 logits within 1e-3 max-abs of the oracle at the
+reference's default-init scale, labels identical on >= 99.9 % of positions with every disagreement
+shown to be a near-tie; integer/index outputs (window lengths, decode of given logits) bit-exact."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle_np as A
+from nanopore_rnn_b200 import _lib, checkpoint as ckpt, engine, synthetic as syn
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+LOGIT_TOL = 1e-3
+
+
+def P(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def dev(a, dtype=None):
+    return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype).to(DEV)
+
+
+def stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def ws(nbytes):
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=DEV)
+
+
+@pytest.fixture(scope="module")
+def lib():
+    lib = _lib.load()
+    assert lib.ntb_device_ok() == 1, lib.ntb_last_error()
+    return lib
+
+
+def near_tie_report(logits_gpu, logits_ref, tol):
+    """Positions whose argmax differs must have a top-2 gap (in the oracle) below 2*tol."""
+    a, b = logits_gpu.argmax(-1), logits_ref.argmax(-1)
+    bad = np.argwhere(a != b)
+    report = []
+    for idx in bad:
+        row = logits_ref[tuple(idx)]
+        top = np.sort(row)[-2:]
+        report.append((tuple(int(i) for i in idx), float(top[1] - top[0])))
+    return report
+
+
+# ------------------------------------------------------------------ K1 packer
+def test_pack_windows_matches_oracle(lib):
+    rng = np.random.default_rng(3)
+    lens = [1000, 37, 2503, 100, 1]
+    raws = [rng.integers(200, 900, n).astype(np.int16) for n in lens]
+    T, step, start = 100, 70, 5
+    read_off = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    counts = [len(range(0, max(n - start, 0), step)) for n in lens]
+    win_off = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    n_win = int(win_off[-1])
+    x = torch.full((n_win, T), 7.0, dtype=torch.float32, device=DEV)
+    ln = torch.zeros(n_win, dtype=torch.int32, device=DEV)
+    raw_d, ro_d, wo_d = dev(np.concatenate(raws)), dev(read_off), dev(win_off)
+    _lib.check(lib.ntb_pack_windows(P(raw_d), P(ro_d), P(wo_d), len(lens), n_win, T, step, start, P(x), P(ln), stream()))
+    torch.cuda.synchronize()
+    xo, lo = [], []
+    for r in raws:
+        if len(r) - start > 0:
+            a, b = A.windows_of_read(r.astype(np.int64), T, step=step, start_index=start)
+            xo.append(a)
+            lo.append(b)
+    xo, lo = np.concatenate(xo), np.concatenate(lo)
+    assert np.array_equal(ln.cpu().numpy(), lo)                       # integer output: bit-exact
+    np.testing.assert_allclose(x.cpu().numpy(), xo, atol=2e-6, rtol=0)
+
+
+# ------------------------------------------------------------------ conv + BN
+@pytest.mark.parametrize("Cin,Cout,k,relu,bn", [(1, 256, 1, 1, 1), (256, 256, 3, 1, 1), (256, 256, 1, 0, 1),
+                                               (64, 32, 3, 0, 0), (12, 20, 1, 1, 1)])
+def test_conv_bn_matches_oracle(lib, Cin, Cout, k, relu, bn):
+    rng = np.random.default_rng(Cin + Cout + k)
+    T = 100
+    goff = np.array([0, 10, 13, 23], np.int32)
+    n = int(goff[-1])
+    v = rng.standard_normal((n, T, Cin)).astype(np.float32)
+    W = (rng.standard_normal((1, k, Cin, Cout)) / np.sqrt(k * Cin)).astype(np.float32)
+    sc = (1 + 0.1 * rng.standard_normal(Cout)).astype(np.float32)
+    of = (0.1 * rng.standard_normal(Cout)).astype(np.float32)
+    out = torch.empty((n * T, Cout), dtype=torch.float32, device=DEV)
+    w = ws(lib.ntb_conv_bn_workspace_bytes(n, len(goff) - 1, T, Cin, Cout, k))
+    v_d, W_d, sc_d, of_d, g_d = dev(v), dev(W), dev(sc), dev(of), dev(goff)
+    _lib.check(lib.ntb_conv_bn(P(v_d), P(W_d), P(sc_d) if bn else None, P(of_d) if bn else None, P(g_d), n,
+                               len(goff) - 1, T, Cin, Cout, k, relu, P(w), w.numel(), P(out), stream()))
+    torch.cuda.synchronize()
+    ref = []
+    for g in range(len(goff) - 1):
+        y = A.conv(v[goff[g]:goff[g + 1]], W)
+        if bn:
+            y = A.bn(y, sc, of)
+        ref.append(np.maximum(y, 0) if relu else y)
+    ref = np.concatenate(ref).reshape(n * T, Cout)
+    np.testing.assert_allclose(out.cpu().numpy(), ref, atol=2e-4, rtol=0)
+
+
+# ------------------------------------------------------------------ BLSTM
+@pytest.mark.parametrize("D,H,T,n", [(12, 5, 30, 80), (256, 100, 100, 70), (200, 100, 100, 130), (7, 33, 17, 65),
+                                     (16, 128, 12, 9)])
+def test_blstm_matches_oracle(lib, D, H, T, n):
+    rng = np.random.default_rng(D * H + T)
+    lim = np.sqrt(6.0 / (D + 5 * H))
+    w = {"kernel_fw": rng.uniform(-lim, lim, (D + H, 4 * H)).astype(np.float32),
+         "kernel_bw": rng.uniform(-lim, lim, (D + H, 4 * H)).astype(np.float32),
+         "bias_fw": (0.1 * rng.standard_normal(4 * H)).astype(np.float32),
+         "bias_bw": (0.1 * rng.standard_normal(4 * H)).astype(np.float32)}
+    x = rng.standard_normal((n, T, D)).astype(np.float32)
+    lens = rng.integers(0, T + 1, n).astype(np.int32)
+    lens[:3] = [T, 0, 1]
+    out = torch.full((n * T, 2 * H), 3.0, dtype=torch.float32, device=DEV)
+    wsb = ws(lib.ntb_blstm_workspace_bytes(n, T, D, H))
+    t = {k: dev(v) for k, v in w.items()}
+    x_d, l_d = dev(x), dev(lens)
+    _lib.check(lib.ntb_blstm(P(x_d), P(l_d), P(t["kernel_fw"]), P(t["bias_fw"]), P(t["kernel_bw"]), P(t["bias_bw"]),
+                             5.0, n, T, D, H, P(wsb), wsb.numel(), P(out), stream()))
+    torch.cuda.synchronize()
+    ref = A.blstm(x, lens, w, 5.0).reshape(n * T, 2 * H)
+    got = out.cpu().numpy()
+    np.testing.assert_allclose(got, ref, atol=2e-5, rtol=0)
+    mask = (np.arange(T)[None, :] >= lens[:, None]).reshape(-1)
+    assert np.all(got[mask] == 0.0)                    # dynamic_rnn zeros beyond seq_len, exactly
+
+
+# ------------------------------------------------------------------ decode (integer work: bit-exact)
+@pytest.mark.parametrize("graph,C", [(0, 1025), (1, 5), (1, 1025), (0, 3)])
+def test_decode_bit_exact_with_ties(lib, graph, C):
+    rng = np.random.default_rng(C + graph)
+    n, T = 37, 23
+    logits = rng.integers(-3, 4, (n, T, C)).astype(np.float32)        # many exact ties
+    lens = rng.integers(0, T + 1, n).astype(np.int32)
+    labels = torch.full((n * T,), -7, dtype=torch.int32, device=DEV)
+    llen = torch.zeros(n, dtype=torch.int32, device=DEV)
+    lg_d, l_d = dev(logits), dev(lens)
+    _lib.check(lib.ntb_decode(P(lg_d), P(l_d), n, T, C, graph, P(labels), P(llen), stream()))
+    torch.cuda.synchronize()
+    got = labels.cpu().numpy()
+    if graph == 0:
+        assert np.array_equal(got, A.argmax_first(logits.reshape(n * T, C)))
+    else:
+        dense, _ = A.ctc_greedy(logits, lens)
+        got = got.reshape(n, T)
+        k = llen.cpu().numpy()
+        assert np.array_equal(engine.ctc_dense(got, k), dense)
+        assert np.all(got[np.arange(T)[None, :] >= k[:, None]] == -1)
+
+
+# ------------------------------------------------------------------ GEMM implementations agree
+@pytest.mark.parametrize("M,N,K", [(1000, 256, 256), (4096, 800, 200), (513, 1040, 512), (300, 256, 768)])
+@pytest.mark.parametrize("impl", [0, 1])
+def test_gemm_matches_fp64(lib, M, N, K, impl):
+    rng = np.random.default_rng(M + N + K)
+    a = rng.standard_normal((M, K)).astype(np.float32)
+    b = (rng.standard_normal((K, N)) / np.sqrt(K)).astype(np.float32)
+    bias = rng.standard_normal(N).astype(np.float32)
+    out = torch.empty((M, N), dtype=torch.float32, device=DEV)
+    w = ws(lib.ntb_gemm_workspace_bytes(M, N, K, impl))
+    a_d, b_d, bias_d = dev(a), dev(b), dev(bias)
+    _lib.check(lib.ntb_gemm(P(a_d), P(b_d), P(bias_d), M, N, K, impl, P(w), w.numel(), P(out), stream()))
+    torch.cuda.synchronize()
+    ref = a.astype(np.float64) @ b.astype(np.float64) + bias
+    # fp32 SIMT ~1e-6; bf16x3 split operands keep ~16 mantissa bits -> ~3e-5 at |out| ~ 1
+    np.testing.assert_allclose(out.cpu().numpy(), ref, atol=1e-4 if impl else 2e-5, rtol=0)
+
+
+# ------------------------------------------------------------------ whole models
+def _run_model(net, w, graph, T, len_x, Cc, x, lens, goff, **kw):
+    m = engine.Model(net, w, graph, T, len_x, Cc, device=DEV)
+    labels, llen, logits = m.forward_host(x, lens, goff, want_logits=True, **kw)
+    return m, labels, llen, logits
+
+
+def test_event_fixture_model_matches_golden(golden_dir):
+    g = np.load(os.path.join(golden_dir, "event_fixture.npz"))
+    net = syn.NETWORKS["event_fixture"]
+    w = ckpt.weights_for_network(ckpt.load_checkpoint(os.path.join(golden_dir, "test_model-30")), net)
+    m, labels, llen, logits = _run_model(net, w, "CrossEntropy", 30, 12, 1025, g["x"], g["lens"], None)
+    assert np.abs(logits[:240] - g["logits_head"]).max() <= LOGIT_TOL
+    assert np.abs(logits.max(1) - g["logits_rowmax"]).max() <= LOGIT_TOL
+    agree = float((labels == g["labels"]).mean())
+    ref_logits, _ = A.forward_batch(g["x"], g["lens"], net, w, "CrossEntropy")
+    report = near_tie_report(logits, ref_logits, LOGIT_TOL)
+    assert agree >= 0.999, (agree, report[:10])
+    assert all(gap <= 2 * LOGIT_TOL for _, gap in report), report[:10]
+    assert m.last_launches() > 0
+
+
+@pytest.mark.parametrize("name,key", [("crnn_signal", "signal_CRNN"), ("crnn_run_nanotensor", "run_nanotensor")])
+def test_crnn_model_matches_golden(golden_dir, name, key):
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    net, Cc = syn.NETWORKS[key], int(g["n_classes"])
+    w = syn.random_weights(net, 1, Cc, seed=int(g["seed"]) + 2)
+    m, labels, llen, logits = _run_model(net, w, "CtcLoss", 100, 1, Cc, g["x"], g["lens"], g["group_off"])
+    ref = g["logits"].reshape(-1, Cc)
+    err = float(np.abs(logits - ref).max())
+    assert err <= LOGIT_TOL, err
+    report = near_tie_report(logits, ref, LOGIT_TOL)
+    agree = 1.0 - len(report) / float(ref.shape[0])
+    assert agree >= 0.999 and all(gap <= 2 * LOGIT_TOL for _, gap in report), (agree, report[:10])
+    if not report:                                      # identical argmax -> identical decode
+        assert np.array_equal(labels, g["labels"].astype(np.int32))
+        width = int(llen.max())
+        assert np.array_equal(engine.ctc_dense(labels, llen), g["labels"][:, :width].astype(np.int64))
+
+
+def test_label_agreement_with_diverse_labels():
+    # readout gain 8 spreads the logits (an untrained readout is nearly constant); the logits
+    # tolerance scales with the gain, the label criterion does not.
+    net, Cc, gain = syn.NETWORKS["signal_CRNN"], 6, 8.0
+    w = syn.random_weights(net, 1, Cc, seed=77, readout_gain=gain)
+    x, lens, _ = syn.synthetic_reads(3, 20, 100, seed=78)
+    goff = engine.group_offsets([20] * 3, 20)
+    m, labels, llen, logits = _run_model(net, w, "CtcLoss", 100, 1, Cc, x, lens, goff)
+    ref = np.concatenate([A.forward_batch(x[a:b], lens[a:b], net, w, "CtcLoss")[0]
+                          for a, b in zip(goff[:-1], goff[1:])]).reshape(-1, Cc)
+    assert np.abs(logits - ref).max() <= LOGIT_TOL * gain
+    hist = np.bincount(ref.argmax(1), minlength=Cc)
+    assert (hist > 50).sum() >= 3, hist                # the case really is diverse
+    report = near_tie_report(logits, ref, LOGIT_TOL * gain)
+    assert 1.0 - len(report) / float(len(ref)) >= 0.999
+    assert all(gap <= 2 * LOGIT_TOL * gain for _, gap in report), report[:10]
+
+
+def test_chunking_and_host_device_paths_are_bit_identical():
+    net, Cc = syn.NETWORKS["signal_CRNN"], 6
+    w = syn.random_weights(net, 1, Cc, seed=5)
+    x, lens, _ = syn.synthetic_reads(8, 25, 100, seed=6)
+    goff = engine.group_offsets([25] * 8, 20)
+    m = engine.Model(net, w, "CtcLoss", 100, 1, Cc, device=DEV)
+    l1, k1, g1 = m.forward_host(x, lens, goff, want_logits=True)
+    l2, k2, g2 = m.forward_host(x, lens, goff, want_logits=True, max_windows=64)     # 4 chunks
+    l3, k3, g3 = m.forward_host(x, lens, goff, want_logits=True)                     # run-to-run
+    assert np.array_equal(g1, g2) and np.array_equal(l1, l2) and np.array_equal(k1, k2)
+    assert np.array_equal(g1, g3) and np.array_equal(l1, l3)
+    ld, kd, gd = m.forward_device(dev(x), dev(lens), dev(goff), want_logits=True)
+    torch.cuda.synchronize()
+    assert np.array_equal(gd.cpu().numpy(), g1) and np.array_equal(ld.cpu().numpy().reshape(-1, 100), l1)
+
+
+def test_bn_groups_matter_and_are_respected():
+    # same windows, different BN grouping -> different logits (the reference's batch statistics)
+    net, Cc = syn.NETWORKS["signal_CRNN"], 6
+    w = syn.random_weights(net, 1, Cc, seed=5)
+    x, lens, _ = syn.synthetic_reads(1, 40, 100, seed=9)
+    m = engine.Model(net, w, "CtcLoss", 100, 1, Cc, device=DEV)
+    _, _, a = m.forward_host(x, lens, np.array([0, 20, 40], np.int32), want_logits=True)
+    _, _, b = m.forward_host(x, lens, np.array([0, 10, 20, 30, 40], np.int32), want_logits=True)
+    assert np.abs(a - b).max() > 1e-3
+    ref = A.forward_batch(x[10:20], lens[10:20], net, w, "CtcLoss")[0].reshape(-1, Cc)
+    assert np.abs(b[1000:2000] - ref).max() <= LOGIT_TOL
+
+
+def test_window_independence_at_scale():
+    # size-independent property at a larger size: a pure BLSTM model gives each window the same
+    # logits whatever its neighbours are (no cross-window coupling) -> permuting windows permutes rows.
+    net = [{"type": "blstm", "name": "b1", "size": 100, "bias": 5.0, "concat": True},
+           {"type": "blstm", "name": "b2", "size": 100, "bias": 5.0, "concat": True}]
+    w = syn.random_weights(net, 12, 8, seed=3, graph="CrossEntropy")
+    rng = np.random.default_rng(4)
+    n, T = 6000, 100
+    x = rng.standard_normal((n, T, 12)).astype(np.float32)
+    lens = rng.integers(1, T + 1, n).astype(np.int32)
+    m = engine.Model(net, w, "CrossEntropy", T, 12, 8, device=DEV)
+    _, _, a = m.forward_host(x, lens, None, want_logits=True, max_windows=4096)
+    perm = rng.permutation(n)
+    _, _, b = m.forward_host(x[perm], lens[perm], None, want_logits=True, max_windows=2048)
+    assert np.array_equal(a.reshape(n, T, 8)[perm], b.reshape(n, T, 8))
+    ref, _ = A.forward_batch(x[:64], lens[:64], net, w, "CrossEntropy")
+    assert np.abs(a[:64 * T] - ref).max() <= LOGIT_TOL
+
+
+def test_empty_and_error_paths(lib):
+    net, Cc = syn.NETWORKS["signal_CRNN"], 6
+    w = syn.random_weights(net, 1, Cc, seed=5)
+    m = engine.Model(net, w, "CtcLoss", 100, 1, Cc, device=DEV)
+    labels, llen, _ = m.forward_host(np.zeros((0, 100), np.float32), np.zeros((0,), np.int32), np.zeros(1, np.int32))
+    assert labels.shape == (0, 100) and llen.shape == (0,)
+    with pytest.raises(ValueError):
+        m.forward_host(np.zeros((4, 100), np.float32), np.full((4,), 100, np.int32), None)
+    x_d, l_d = dev(np.zeros((4, 100), np.float32)), dev(np.full((4,), 100, np.int32))
+    lab = torch.empty(400, dtype=torch.int32, device=DEV)
+    rc = lib.ntb_model_forward(m._h, P(x_d), P(l_d), None, 4, 0, P(lab), 16, None, P(lab), None, stream())
+    assert rc == -4 and b"workspace" in lib.ntb_last_error()
+    bad = [dict(l) for l in net]
+    bad[2]["concat"] = False
+    with pytest.raises(ValueError):
+        engine.Model(bad, w, "CtcLoss", 100, 1, Cc, device=DEV)
