@@ -1,0 +1,349 @@
+#!/usr/bin/env python
+"""bench.py -- signal samples/sec basecalled (NanoTensor BLSTM forward) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--windows M]
+
+A *step* is one pass of the hot path (conv/BN front-end, BLSTM projections +
+recurrences, fused chiron_fnn/dense/CTC-greedy readout) over one batch of synthetic windows of
+BASELINE.json configs[1]: the ``run_nanotensor.config.json`` network (3 residual(256) +
+3 BLSTM(100, forget_bias 5) + chiron_fnn, CtcLoss C=4, T=100), 1 048 576 windows in BN groups
+of 10 (the config's batch_size), the last window of every 1000-window read ragged.  Weak scaling:
+every rank processes its own ``--windows`` windows (reads shard across GPUs, no collective on
+the data path); ``value`` = valid samples of all ranks / max-over-ranks device time.
+
+One JSON line is printed by rank 0 (keys: see DESIGN.md "Measurement").  ``--impl reference``
+times the CPU restatement of the reference's TensorFlow forward (oracle/oracle_torch.py, all host
+threads) on a bounded sample of the same workload: TensorFlow 1.4 itself is unavailable on the
+box.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "signal samples/sec basecalled (BLSTM fwd)"
+UNIT = "samples/s"
+WORKLOAD = "run_nanotensor.config.json network, synthetic windows"
+T, BATCH, NCLASS, WIN_PER_READ = 100, 10, 4, 1000
+# algorithmic FLOPs per window (multiply-add = 2)
+FLOPS_CONV, FLOPS_PROJ, FLOPS_REC, FLOPS_READOUT = 209.8e6, 105.0e6, 48.0e6, 0.12e6
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--windows", type=int, default=1048576, help="windows per GPU per step")
+    ap.add_argument("--cpu-windows", type=int, default=0,
+                    help="windows in the CPU baseline sample (0 = auto-size to ~10-20 s)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end (host buffers) leg")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "src": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "src": "fallback"}
+
+
+# ---------------------------------------------------------------------------- workload
+def make_workload(n_windows, seed):
+    """Windows of synthetic z-scored reads + BN group offsets."""
+    from nanopore_rnn_b200 import engine, synthetic as syn
+    n_reads = max(1, -(-n_windows // WIN_PER_READ))
+    wpr = WIN_PER_READ if n_windows >= WIN_PER_READ else n_windows
+    x, lens, _ = syn.synthetic_reads(n_reads, wpr, T, seed=seed)
+    x, lens = x[:n_windows], lens[:n_windows]
+    counts = [wpr] * n_reads
+    counts[-1] -= n_reads * wpr - n_windows
+    goff = engine.group_offsets(counts, BATCH)
+    return x, lens, goff
+
+
+def network_and_weights():
+    from nanopore_rnn_b200 import synthetic as syn
+    net = syn.NETWORKS["run_nanotensor"]
+    return net, syn.random_weights(net, 1, NCLASS, seed=2)
+
+
+# ---------------------------------------------------------------------------- clocks
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons of one GPU through NVML while the timed region runs."""
+
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown",
+               0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown"}
+
+    def __init__(self, index, period=0.1):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.sm, self.reasons, self.sm_max = [], set(), None
+        self._stop_evt = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception as e:          # NVML missing: report it instead of inventing clocks
+            self.nv, self.err = None, repr(e)
+
+    def run(self):
+        if self.nv is None:
+            return
+        while not self._stop_evt.is_set():
+            try:
+                self.sm.append(int(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+                mask = int(self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop_evt.wait(self.period)
+
+    def finish(self):
+        self._stop_evt.set()
+        if self.is_alive():
+            self.join(timeout=2)
+        if self.nv is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "error": getattr(self, "err", "nvml")}
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.sm_max,
+                "reasons": sorted(self.reasons), "samples": len(self.sm)}
+
+
+# ---------------------------------------------------------------------------- CPU baseline
+def cpu_baseline(n_windows, seed=1234):
+    """Times oracle/oracle_torch.forward_job (the CPU restatement of the reference's TF forward,
+    all host threads, best-case large batch with per-batch BN kept) on a bounded sample."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import torch
+    import oracle_np as A
+    import oracle_torch as B
+    net, w = network_and_weights()
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+
+    def run(nw):
+        x, lens, _ = make_workload(nw, seed)
+        t0 = time.perf_counter()
+        logits = B.forward_job(x, lens, net, w, "CtcLoss", BATCH)
+        A.ctc_greedy(logits, lens)                       # the label output is part of the path
+        return time.perf_counter() - t0, int(lens.sum())
+
+    run(BATCH * 8)                                       # warm the thread pool / allocators
+    if n_windows <= 0:
+        dt, _ = run(BATCH * 64)
+        n_windows = int(max(BATCH * 64, min(65536, (12.0 / dt) * BATCH * 64)) // BATCH * BATCH)
+    dt, samples = run(n_windows)
+    return {"value": samples / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d windows (T=%d, BN groups of %d) of the same workload, %.1f s; torch-CPU restatement "
+                      "(oracle/oracle_torch.py), %d threads; TensorFlow 1.4 reference unavailable on this box"
+                      % (n_windows, T, BATCH, dt, cores)}
+
+
+# ---------------------------------------------------------------------------- reference arm
+def run_reference(args):
+    """--impl reference: the CPU restatement on the host cores; each step is a bounded sample of the
+    workload (a few seconds), rank 0 only."""
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return 0
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import torch
+    import oracle_np as A
+    import oracle_torch as B
+    net, w = network_and_weights()
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    nw = args.cpu_windows
+    if nw <= 0:
+        x, lens, _ = make_workload(BATCH * 64, 1234)
+        B.forward_job(x[:BATCH * 8], lens[:BATCH * 8], net, w, "CtcLoss", BATCH)
+        t0 = time.perf_counter()
+        B.forward_job(x, lens, net, w, "CtcLoss", BATCH)
+        dt = time.perf_counter() - t0
+        nw = int(max(BATCH * 64, min(32768, (5.0 / dt) * BATCH * 64)) // BATCH * BATCH)
+    x, lens, _ = make_workload(nw, 1234)
+    samples = int(lens.sum())
+
+    def step():
+        logits = B.forward_job(x, lens, net, w, "CtcLoss", BATCH)
+        A.ctc_greedy(logits, lens)
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = (time.perf_counter() - t0) / max(args.steps, 1)
+    value = samples / dt
+    sample = ("%d windows per step (T=%d, BN groups of %d), torch-CPU restatement of the TF forward "
+              "(oracle/oracle_torch.py), %d threads; TensorFlow 1.4 unavailable on this box" % (nw, T, BATCH, cores))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "windows_per_step": nw, "seq_len": T, "bn_group": BATCH,
+                       "n_classes": NCLASS},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------- B200 arm
+def run_b200(args):
+    import torch
+    import nanopore_rnn_b200  # noqa: F401
+    from nanopore_rnn_b200 import engine
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(v):
+        if dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # each rank owns its own reads (weak scaling): no collective on the data path
+    x, lens, goff = make_workload(args.windows, seed=100 + rank)
+    n = len(x)
+    samples = int(lens.sum())
+    net, w = network_and_weights()
+    m = engine.Model(net, w, "CtcLoss", T, 1, NCLASS, device=str(dev))
+
+    # ---- device-resident job: inputs already in HBM when the timed region starts
+    x_pin = torch.from_numpy(x).pin_memory()
+    lens_pin = torch.from_numpy(lens).pin_memory()
+    x_d, lens_d = x_pin.to(dev), lens_pin.to(dev)
+    chunks = engine.plan_chunks(goff, m.max_chunk_windows())
+    chunk_goff = [torch.from_numpy(np.ascontiguousarray(goff[g:h + 1] - goff[g], dtype=np.int32)).to(dev)
+                  for g, h in chunks]
+    labels_d = torch.empty(n * T, dtype=torch.int32, device=dev)
+    llen_d = torch.empty(n, dtype=torch.int32, device=dev)
+    launches = [0]
+
+    def step():
+        for (g, h), go in zip(chunks, chunk_goff):
+            w0, w1 = int(goff[g]), int(goff[h])
+            m.forward_device(x_d[w0:w1], lens_d[w0:w1], go, labels_out=labels_d[w0 * T:w1 * T],
+                             label_len_out=llen_d[w0:w1])
+            launches[0] += m.last_launches()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches[0] = 0
+    m.set_profile(True)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    barrier()
+    clocks = sampler.finish()
+    ms_total = max_over_ranks(ev0.elapsed_time(ev1))
+    stage = m.stage_ms()
+    m.set_profile(False)
+    n_launch = launches[0]
+    ms_step = ms_total / max(args.steps, 1)
+    total_samples = sum_over_ranks(samples)
+    value = total_samples / (ms_step * 1e-3)
+
+    # ---- end to end through the public API with HOST buffers (pinned), copies inside
+    e2e = None
+    if not args.no_e2e:
+        xh, lh = x_pin.numpy(), lens_pin.numpy()
+        m.forward_host(xh, lh, goff)                      # warm (pinned result buffers, workspace)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            labels, llen, _ = m.forward_host(xh, lh, goff)
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0) / max(args.steps, 1)
+        e2e = {"value": total_samples / dt, "unit": UNIT,
+               "h2d_bytes_per_step": int(x.nbytes + lens.nbytes + goff.nbytes),
+               "d2h_bytes_per_step": int(labels.nbytes + llen.nbytes), "ms_per_step": dt * 1e3}
+
+    # ---- roofline of the dominant stage (stage marks = CUDA events on the forward's stream)
+    pk = peaks()
+    flops = {"conv_bn": FLOPS_CONV, "projection": FLOPS_PROJ, "recurrence": FLOPS_REC, "readout": FLOPS_READOUT}
+    top = max(stage, key=lambda k: stage[k]) if stage else None
+    roof = None
+    if top is not None and stage[top] > 0:
+        achieved = flops[top] * n * args.steps / (stage[top] * 1e-3) / 1e12
+        peak = pk["bf16_tflops_sustained"]
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get(top)
+        roof = {"bound": "tensor", "kernel": top, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                "frac": achieved / peak, "traffic": traffic, "peak_source": pk["src"] + " (sustained bf16)",
+                "stage_ms_per_step": {k: v / max(args.steps, 1) for k, v in stage.items()},
+                "stage_tflops": {k: (flops[k] * n * args.steps / (v * 1e-3) / 1e12 if v > 0 else None)
+                                 for k, v in stage.items()}}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu = cpu_baseline(args.cpu_windows)
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "windows_per_gpu": n, "seq_len": T, "bn_group": BATCH,
+                           "n_classes": NCLASS, "chunks_per_step": len(chunks),
+                           "l2": "inputs (%.0f MB) and activations larger than L2" % (x.nbytes / 1e6),
+                           "parallelism": "reads sharded over %d GPU(s), no collective" % world},
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(n_launch), "roofline": roof,
+                "cpu_baseline": cpu}
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -130,11 +130,13 @@ NTB_API int64_t ntb_model_workspace_bytes_host(const ntb_model *m, int64_t n_win
 
 /* Number of kernel launches the last ntb_model_forward on this model issued. */
 NTB_API int64_t ntb_model_last_launches(const ntb_model *m);
-/* Per-stage device time (ms) of the last forward when profiling was enabled with
- * ntb_model_set_profile(m, 1): stages are 0 conv/BN front-end, 1 LSTM input projections,
- * 2 LSTM recurrences, 3 readout.  Returns the number of stages written. */
+/* Per-stage device time (ms), summed over every forward issued since profiling was enabled with
+ * ntb_model_set_profile(m, 1) (or since the previous ntb_model_stage_ms call): stages are
+ * 0 conv/BN front-end, 1 LSTM input projections, 2 LSTM recurrences, 3 readout.  Stage marks are
+ * CUDA events recorded on the forward's stream WITHOUT synchronising; this call waits for the
+ * last one.  Returns the number of stages written. */
 NTB_API int ntb_model_set_profile(ntb_model *m, int enable);
-NTB_API int ntb_model_stage_ms(const ntb_model *m, float *ms_out, int max_stages);
+NTB_API int ntb_model_stage_ms(ntb_model *m, float *ms_out, int max_stages);
 
 /* ---- op-level entry points (kernel-boundary parity tests; same kernels the model uses) ---- */
 

@@ -52,6 +52,9 @@ struct ntb_model {
     int64_t launches = 0;
     int profile = 0;
     float stage_ms[4] = {0, 0, 0, 0};
+    // profile mode: (stage, event) marks of every forward since the last ntb_model_stage_ms();
+    // recorded without synchronising so that profiling does not perturb the timed region
+    std::vector<std::pair<int, cudaEvent_t>> marks;
     int sm_count = 148;
 };
 
@@ -278,8 +281,10 @@ extern "C" int ntb_model_create(const ntb_model_desc *desc, void *weights_dev, i
     return NTB_OK;
 }
 
+static void drop_marks(ntb_model *m);
 extern "C" void ntb_model_destroy(ntb_model *m) {
     if (!m) return;
+    drop_marks(m);
     delete m;
 }
 
@@ -380,7 +385,7 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
     const int64_t rows = n * T;
     if (n == 0) return NTB_OK;
     int stage = -1;   // 0 conv, 1 projection, 2 recurrence, 3 readout
-    std::vector<std::pair<int, cudaEvent_t>> marks;
+    auto &marks = m->marks;
     auto mark = [&](int s) -> int {
         if (!m->profile) return NTB_OK;
         if (s == stage) return NTB_OK;
@@ -457,15 +462,6 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
         NTB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDefault));
         NTB_CUDA(cudaEventRecord(e, st));
         marks.push_back({4, e});
-        NTB_CUDA(cudaStreamSynchronize(st));
-        float acc[4] = {0, 0, 0, 0};
-        for (size_t i = 0; i + 1 < marks.size(); ++i) {
-            float ms = 0;
-            cudaEventElapsedTime(&ms, marks[i].second, marks[i + 1].second);
-            if (marks[i].first >= 0 && marks[i].first < 4) acc[marks[i].first] += ms;
-        }
-        for (auto &mk : marks) cudaEventDestroy(mk.second);
-        for (int i = 0; i < 4; ++i) m->stage_ms[i] = acc[i];
     }
     m->launches = cx.launches;
     return NTB_OK;
@@ -551,13 +547,28 @@ extern "C" int ntb_model_forward_host(ntb_model *m, const float *x_host, const i
 }
 
 extern "C" int64_t ntb_model_last_launches(const ntb_model *m) { return m ? m->launches : 0; }
+static void drop_marks(ntb_model *m) {
+    for (auto &mk : m->marks) cudaEventDestroy(mk.second);
+    m->marks.clear();
+}
 extern "C" int ntb_model_set_profile(ntb_model *m, int enable) {
     if (!m) return NTB_EINVAL;
     m->profile = enable ? 1 : 0;
+    drop_marks(m);
     return NTB_OK;
 }
-extern "C" int ntb_model_stage_ms(const ntb_model *m, float *ms_out, int max_stages) {
+extern "C" int ntb_model_stage_ms(ntb_model *m, float *ms_out, int max_stages) {
     if (!m || !ms_out) return 0;
+    float acc[4] = {0, 0, 0, 0};
+    auto &marks = m->marks;
+    if (!marks.empty()) cudaEventSynchronize(marks.back().second);
+    for (size_t i = 0; i + 1 < marks.size(); ++i) {
+        if (marks[i].first < 0 || marks[i].first > 3) continue;   // 4 = end of one forward
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, marks[i].second, marks[i + 1].second) == cudaSuccess) acc[marks[i].first] += ms;
+    }
+    drop_marks(m);
+    for (int i = 0; i < 4; ++i) m->stage_ms[i] = acc[i];
     int k = max_stages < 4 ? max_stages : 4;
     for (int i = 0; i < k; ++i) ms_out[i] = m->stage_ms[i];
     return k;

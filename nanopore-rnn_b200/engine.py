@@ -209,9 +209,10 @@ class Model:
             group_off = _as_np(group_off, np.int32)
             pass_groups = True
         T, Cc = self.T, self.C
-        labels = np.empty((n * T,), dtype=np.int32)
-        llen = np.empty((n,), dtype=np.int32) if self.graph == "CtcLoss" else None
-        logits = np.empty((n * T, Cc), dtype=np.float32) if want_logits else None
+        # results land in pinned host memory (torch's caching host allocator recycles the blocks)
+        labels = _pinned((n * T,), torch.int32)
+        llen = _pinned((n,), torch.int32) if self.graph == "CtcLoss" else None
+        logits = _pinned((n * T, Cc), torch.float32) if want_logits else None
         if n == 0:
             return self._shape_labels(labels, n), llen, logits
         chunks = plan_chunks(group_off, max_windows or self.max_chunk_windows())
@@ -249,6 +250,12 @@ class Model:
         buf = (C.c_float * 4)()
         k = self.lib.ntb_model_stage_ms(self._h, buf, 4)
         return dict(zip(["conv_bn", "projection", "recurrence", "readout"][:k], list(buf)[:k]))
+
+
+def _pinned(shape, dtype):
+    if int(np.prod(shape)) == 0:
+        return np.empty(shape, dtype=torch.empty(0, dtype=dtype).numpy().dtype)
+    return torch.empty(shape, dtype=dtype, pin_memory=True).numpy()
 
 
 def _as_np(a, dtype):

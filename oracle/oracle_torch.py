@@ -92,3 +92,56 @@ def forward_batch(x, lens, network, weights, graph, dtype=torch.float32):
     if graph == "CtcLoss":
         logits = logits.reshape(B, T, -1)
     return logits.numpy()
+
+
+# ------------------------------------------------------------------ many reference batches at once
+def _bn_groups(y, scale, offset, group, eps=1e-5):
+    """bn() applied independently to consecutive groups of ``group`` windows (one reference batch
+    each, network.py:339-349), vectorised over the groups."""
+    n, T, C = y.shape
+    g = y.reshape(n // group, group * T, C)
+    mean = g.mean(dim=1, keepdim=True)
+    var = g.var(dim=1, unbiased=False, keepdim=True)
+    out = (g - mean) / torch.sqrt(var + eps) * torch.as_tensor(scale, dtype=y.dtype) \
+        + torch.as_tensor(offset, dtype=y.dtype)
+    return out.reshape(n, T, C)
+
+
+def forward_job(x, lens, network, weights, graph, group, dtype=torch.float32):
+    """Logits of MANY equal-sized reference batches in one pass: the CPU's best case (large GEMMs,
+    all threads) with the reference's per-batch BN statistics kept.  ``len(x)`` must be a multiple of
+    ``group`` (= the config's batch_size).  Used as the timed CPU baseline (bench.py) and checked
+    against forward_batch / oracle_np in tests/test_oracle.py."""
+    v = torch.as_tensor(np.asarray(x), dtype=dtype)
+    assert v.shape[0] % group == 0
+    if graph == "CtcLoss":
+        v = v.reshape(v.shape[0], v.shape[1], 1)
+
+    def gbn(y, w, name):
+        return _bn_groups(y, w[name + "_bn_scale"], w[name + "_bn_offset"], group)
+
+    with torch.no_grad():
+        for layer, w in zip(network, weights["layers"]):
+            t = layer["type"]
+            if t == "residual_layer":
+                a = conv(v, w["conv1"])
+                if layer.get("batchnorm"):
+                    a = gbn(a, w, "conv1")
+                b = F.relu(gbn(conv(v, w["conv2a"]), w, "conv2a"))
+                b = F.relu(gbn(conv(b, w["conv2b"]), w, "conv2b"))
+                b = gbn(conv(b, w["conv2c"]), w, "conv2c")
+                v = F.relu(a + b)
+            elif t == "blstm":
+                v = blstm(v, lens, w, layer["bias"])
+            elif t == "chiron_fnn":
+                H = v.shape[2] // 2
+                fw = torch.as_tensor(w["weights"], dtype=dtype)
+                v = v[:, :, :H] * fw[0] + v[:, :, H:] * fw[1] + torch.as_tensor(w["bias"], dtype=dtype)
+            else:
+                raise ValueError(t)
+        B, T, Fdim = v.shape
+        logits = v.reshape(B * T, Fdim) @ torch.as_tensor(weights["out_w"], dtype=dtype) \
+            + torch.as_tensor(weights["out_b"], dtype=dtype)
+        if graph == "CtcLoss":
+            logits = logits.reshape(B, T, -1)
+    return logits.numpy()
