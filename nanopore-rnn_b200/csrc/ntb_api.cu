@@ -325,7 +325,7 @@ static int64_t plan_workspace(const ntb_model *m, int64_t n, int64_t n_groups, b
         if (ld.type == NTB_LAYER_RESIDUAL && ld.size > maxk) maxk = ld.size;
     }
     if (m->F_final > maxk) maxk = m->F_final;
-    gemm_tc_plan_scratch(ws.gs, rows, maxk, ar);
+    gemm_tc_plan_scratch(ws.gs, rows, m->T, maxk, ar);
     return ar.off;
 }
 }  // namespace ntb
@@ -694,7 +694,7 @@ extern "C" int64_t ntb_gemm_workspace_bytes(int64_t M, int32_t N, int32_t K, int
     GemmWeights w;
     gemm_tc_plan_weights(w, 1, K, N, ar);
     GemmScratch gs;
-    gemm_tc_plan_scratch(gs, M, K, ar);
+    gemm_tc_plan_scratch(gs, M, 0, K, ar);
     return ar.off + 256;
 }
 
@@ -710,7 +710,7 @@ extern "C" int ntb_gemm(const float *a_dev, const float *b_dev, const float *bia
     GemmWeights w;
     gemm_tc_plan_weights(w, 1, K, N, ar);
     GemmScratch gs;
-    gemm_tc_plan_scratch(gs, M, K, ar);
+    gemm_tc_plan_scratch(gs, M, 0, K, ar);
     if (!w.valid || !gs.valid) return fail(NTB_EINVAL, "ntb_gemm: shape not supported by the tcgen05 path (K %% 16, N %% 16)%s", "");
     if (!workspace_dev || !ar.ok()) return fail(NTB_ENOMEM, "ntb_gemm: workspace too small (need %s%lld)", "", (long long)ar.off);
     w.single_pass = impl == 2;

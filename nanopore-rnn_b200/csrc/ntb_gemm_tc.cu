@@ -1,12 +1,458 @@
-// placeholder until the tcgen05 kernel lands: every shape reports "not supported" so the
-// callers take the fp32 SIMT path.
+// K2/K3  Dense contractions of the NanoTensor forward on the 5th-gen tensor cores:
+//   conv_layer (network.py:312-329: 1x1 / 1x3 SAME convs as GEMMs over all rows = window*T + t),
+//   the LSTM input projection x_t . kernel[0:D, :] (network.py:275-282) and fulconn_layer
+//   (network.py:291-309) when the class count is large.
+//
+// The reference computes these in float32.  bf16 tensor-core operands alone miss the 1e-3 logits
+// budget by two orders of magnitude (precision table), so every fp32 operand is split
+// into bf16 hi + bf16 lo planes and the product is accumulated in fp32 TMEM as
+//   A.B ~= Ahi.Bhi + Alo.Bhi + Ahi.Blo            (relative error ~2^-16, "bf16x3").
+//
+// Kernel: persistent, warp-specialised, one CTA per SM.
+//   warp 0      TMA producer: cp.async.bulk.tensor loads of the A hi/lo [128 x 64] and
+//               B hi/lo [BN x 64] tiles (128-byte swizzle) into a ring of smem stages
+//   warp 1      MMA issuer: one thread issues tcgen05.mma (M=128, N=BN, K=16) x 3 passes per
+//               k-step into one of two TMEM accumulators; tcgen05.commit frees the smem stage /
+//               publishes the accumulator
+//   warp 2      TMEM allocator (512 columns = 2 accumulators of up to 256 columns)
+//   warps 4-7   epilogue: tcgen05.ld 32 lanes x 32 columns -> registers -> (+bias) -> global fp32,
+//               overlapping the next tile's main loop through the second accumulator
+// 1x3 convs run as 3 taps accumulated into the same accumulator: the A planes use a row layout
+// padded per window ([window][T+2][K], zero rows at both ends) so a tap is a row offset of the
+// TMA coordinate and SAME zero padding falls out of the layout.
+#include <cuda.h>
+
 #include "ntb_gemm_tc.cuh"
+#include "ntb_tc_ptx.cuh"
+
 namespace ntb {
-void gemm_tc_plan_weights(GemmWeights &w, int taps, int K, int N, Arena &) { w = GemmWeights(); w.taps = taps; w.K = K; w.N = N; }
-int gemm_tc_pack_weights(cudaStream_t, const float *, GemmWeights &) { return NTB_OK; }
-void gemm_tc_plan_scratch(GemmScratch &gs, int64_t, int, Arena &) { gs = GemmScratch(); }
-int gemm_tc_run(cudaStream_t, const float *, int, int64_t, const GemmWeights &, const float *, float *, int,
-                const GemmScratch &, int64_t *) { return fail(NTB_EINVAL, "tcgen05 GEMM not built%s", ""); }
-int gemm_tc_conv(cudaStream_t, const float *, int, int64_t, int, const float *, const float *, const int32_t *, int,
-                 const GemmWeights &, float *, int, const GemmScratch &, int64_t *) { return fail(NTB_EINVAL, "tcgen05 GEMM not built%s", ""); }
+
+namespace {
+
+constexpr int BM = 128;        // rows per tile (TMEM lanes)
+constexpr int BK = 64;         // bf16 per smem row = one 128-byte swizzle span
+constexpr int TC_THREADS = 256;
+constexpr int TMEM_COLS = 512;
+constexpr int A_TILE_BYTES = BM * BK * 2;     // 16 KB
+constexpr int SMEM_BUDGET = 220 * 1024;
+
+struct TcParams {
+    int64_t m_tiles;       // ceil(plane_rows / 128)
+    int n_tiles, BN, Np, N;
+    int taps, k_blocks;    // k_blocks per tap = ceil(K / 64)
+    int k16_last;          // k16 steps in the last k block of a tap
+    int passes;            // 3 = bf16x3, 1 = plain bf16 (ablation only)
+    int stages;
+    int T, pad;            // pad = 1: plane rows are [window][T+2]
+    int64_t out_rows;      // rows of `out`
+    const float *bias;
+    float *out;
+    int ldo;
+};
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
+          const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
+          const TcParams p) {
+    using namespace ptx;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full_bar[8], empty_bar[8], acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_base_smem;
+
+    const uint32_t raw = smem_u32(smem_raw);
+    uint8_t *smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);     // 1024 B: swizzle-128B atoms
+    const int b_tile_bytes = p.BN * BK * 2;
+    const int stage_bytes = (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + b_tile_bytes);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t total_tiles = p.m_tiles * p.n_tiles;
+    const int kb_total = p.taps * p.k_blocks;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&map_a_hi); prefetch_tmap(&map_a_lo); prefetch_tmap(&map_b_hi); prefetch_tmap(&map_b_lo);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(&tmem_base_smem, TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_smem;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            const int left = (p.taps - 1) / 2;
+            for (int64_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const int n_tile = (int)(tile % p.n_tiles);
+                const int64_t m_tile = tile / p.n_tiles;
+                for (int tap = 0; tap < p.taps; ++tap) {
+                    const int row0 = (int)(m_tile * BM) + tap - left;
+                    const int brow0 = tap * p.Np + n_tile * p.BN;
+                    for (int kb = 0; kb < p.k_blocks; ++kb) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        uint8_t *s = smem + (size_t)stage * stage_bytes;
+                        mbar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+                        tma_load_2d(s, &map_a_hi, &full_bar[stage], kb * BK, row0);
+                        tma_load_2d(s + A_TILE_BYTES, &map_b_hi, &full_bar[stage], kb * BK, brow0);
+                        if (p.passes == 3) {
+                            tma_load_2d(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], kb * BK, row0);
+                            tma_load_2d(s + 2 * A_TILE_BYTES + b_tile_bytes, &map_b_lo, &full_bar[stage], kb * BK, brow0);
+                        }
+                        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc = idesc_bf16_f32(BM, p.BN);
+            int stage = 0; uint32_t phase = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            for (int64_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                mbar_wait(&acc_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
+                for (int kb = 0; kb < kb_total; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t s = smem_u32(smem + (size_t)stage * stage_bytes);
+                    const uint64_t a_hi = smem_desc_sw128(s);
+                    const uint64_t b_hi = smem_desc_sw128(s + A_TILE_BYTES);
+                    const uint64_t a_lo = smem_desc_sw128(s + A_TILE_BYTES + b_tile_bytes);
+                    const uint64_t b_lo = smem_desc_sw128(s + 2 * A_TILE_BYTES + b_tile_bytes);
+                    const int k16n = ((kb % p.k_blocks) == p.k_blocks - 1) ? p.k16_last : BK / 16;
+                    for (int k = 0; k < k16n; ++k) {
+                        umma_f16(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_hi, k), idesc,
+                                 (kb | k) != 0);
+                        if (p.passes == 3) {
+                            umma_f16(d_tmem, desc_advance_k16(a_lo, k), desc_advance_k16(b_hi, k), idesc, 1);
+                            umma_f16(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_lo, k), idesc, 1);
+                        }
+                    }
+                    umma_commit(&empty_bar[stage]);            // smem stage reusable once these MMAs retire
+                    if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&acc_full[acc]);                   // accumulator complete
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp >= 4) {
+        // ===================== epilogue =====================
+        const int q = warp & 3;                                // TMEM lane quarter this warp may access
+        int acc = 0; uint32_t acc_phase = 0;
+        const bool vec_ok = ((p.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
+        for (int64_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const int n_tile = (int)(tile % p.n_tiles);
+            const int64_t m_tile = tile / p.n_tiles;
+            mbar_wait(&acc_full[acc], acc_phase);
+            tc_fence_after();
+            const int64_t prow = m_tile * BM + q * 32 + lane;       // row in the A-plane layout
+            int64_t orow = prow;
+            bool row_ok = true;
+            if (p.pad) {
+                const int64_t w = prow / (p.T + 2);
+                const int tt = (int)(prow - w * (p.T + 2)) - 1;
+                row_ok = tt >= 0 && tt < p.T;
+                orow = w * p.T + tt;
+            }
+            row_ok = row_ok && orow < p.out_rows;
+            float *orow_ptr = p.out + orow * (int64_t)p.ldo;
+            const int n0 = n_tile * p.BN;
+            for (int c0 = 0; c0 < p.BN; c0 += 32) {
+                uint32_t r[32];
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256 + c0);
+                if (c0 + 32 <= p.BN) {
+                    tmem_ld_32x32(taddr, r);
+                } else {                                           // BN % 32 == 16 tail
+                    uint32_t h[16];
+                    tmem_ld_32x16(taddr, h);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) { r[i] = h[i]; r[i + 16] = 0; }
+                }
+                tmem_ld_wait();
+                if (row_ok) {
+                    const int nb = n0 + c0;
+                    if (vec_ok && nb + 32 <= p.N && c0 + 32 <= p.BN) {
+#pragma unroll
+                        for (int i = 0; i < 32; i += 4) {
+                            float4 v = make_float4(__uint_as_float(r[i]), __uint_as_float(r[i + 1]),
+                                                   __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+                            if (p.bias) {
+                                const float4 b = *reinterpret_cast<const float4 *>(p.bias + nb + i);
+                                v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+                            }
+                            *reinterpret_cast<float4 *>(orow_ptr + nb + i) = v;
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            const int n = nb + i;
+                            if (n < p.N && c0 + i < p.BN)
+                                orow_ptr[n] = __uint_as_float(r[i]) + (p.bias ? p.bias[n] : 0.0f);
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[acc]);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
 }
+
+// ------------------------------------------------------------------------------------------
+// fp32 -> bf16 hi/lo operand planes, with the producer's BN affine (+ReLU) applied on the way
+// (simple_global_bn + relu of the previous conv, network.py:330-349) and, for the 1x3 conv, the
+// per-window padded row layout.  8 channels per thread: two float4 loads, two 16-byte stores.
+// ------------------------------------------------------------------------------------------
+struct SplitParams {
+    const float *A; int lda;
+    int64_t rows;            // source rows (= n_windows * T when pad)
+    int K;                   // multiple of 8
+    const float *aff_a, *aff_b; const int32_t *win_group;
+    int T, relu, pad;
+    __nv_bfloat16 *hi, *lo;  // [plane_rows][K]
+    int64_t plane_rows;
+};
+
+__global__ void __launch_bounds__(256) k_split_bf16(const SplitParams p) {
+    const int K8 = p.K >> 3;
+    const int64_t total = p.plane_rows * K8;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t pr = i / K8;
+        const int c = (int)(i - pr * K8) << 3;
+        int64_t r = pr, w = 0;
+        bool real = true;
+        if (p.pad) {
+            w = pr / (p.T + 2);
+            const int tt = (int)(pr - w * (p.T + 2)) - 1;
+            real = tt >= 0 && tt < p.T;
+            r = w * p.T + tt;
+        } else if (p.aff_a) {
+            w = pr / p.T;
+        }
+        real = real && r < p.rows;
+        float v[8];
+        if (real) {
+            const float4 x0 = *reinterpret_cast<const float4 *>(p.A + r * p.lda + c);
+            const float4 x1 = *reinterpret_cast<const float4 *>(p.A + r * p.lda + c + 4);
+            v[0] = x0.x; v[1] = x0.y; v[2] = x0.z; v[3] = x0.w; v[4] = x1.x; v[5] = x1.y; v[6] = x1.z; v[7] = x1.w;
+            if (p.aff_a) {
+                const int g = p.win_group[w];
+                const float *a = p.aff_a + (int64_t)g * p.K + c, *b = p.aff_b + (int64_t)g * p.K + c;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = v[j] * a[j] + b[j];
+            }
+            if (p.relu) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.0f);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = 0.0f;
+        }
+        __align__(16) __nv_bfloat16 h[8], l[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ptx::split_bf16(v[j], h[j], l[j]);
+        *reinterpret_cast<uint4 *>(p.hi + pr * p.K + c) = *reinterpret_cast<const uint4 *>(h);
+        if (p.lo) *reinterpret_cast<uint4 *>(p.lo + pr * p.K + c) = *reinterpret_cast<const uint4 *>(l);
+    }
+}
+
+// TF weights [taps][K][N] fp32 -> K-major bf16 planes [taps][Np][Kp] (zero padded)
+__global__ void k_pack_weights(const float *__restrict__ w, int taps, int K, int N, int Kp, int Np,
+                               __nv_bfloat16 *__restrict__ hi, __nv_bfloat16 *__restrict__ lo) {
+    const int64_t total = (int64_t)taps * Np * Kp;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int k = (int)(i % Kp);
+        const int n = (int)((i / Kp) % Np);
+        const int tap = (int)(i / ((int64_t)Kp * Np));
+        const float v = (k < K && n < N) ? w[((int64_t)tap * K + k) * N + n] : 0.0f;
+        __nv_bfloat16 h, l;
+        ptx::split_bf16(v, h, l);
+        hi[i] = h;
+        lo[i] = l;
+    }
+}
+
+// ------------------------------------------------------------------------------------------ host
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess) p = nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+// bf16 [rows][K] row-major plane, box {64, box_rows}, 128-byte swizzle, zero fill out of bounds
+int make_map(CUtensorMap *m, const void *base, int64_t rows, int K, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return fail(NTB_ECUDA, "cuTensorMapEncodeTiled entry point not found%s", "");
+    cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+    cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(NTB_ECUDA, "cuTensorMapEncodeTiled failed (%s%lld) rows %lld", "", (long long)r, (long long)rows);
+    return NTB_OK;
+}
+
+int pick_bn(int N) {
+    // fewest N tiles first (A is re-read once per N tile), then least padding; BN % 16 == 0, <= 256
+    int best = 0, best_tiles = 1 << 30, best_pad = 1 << 30;
+    for (int bn = 16; bn <= 256; bn += 16) {
+        const int tiles = (N + bn - 1) / bn, padn = tiles * bn - N;
+        if (tiles < best_tiles || (tiles == best_tiles && padn < best_pad)) { best = bn; best_tiles = tiles; best_pad = padn; }
+    }
+    return best;
+}
+
+int sm_count() {
+    static int n = [] {
+        int dev = 0, v = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+        return v;
+    }();
+    return n;
+}
+
+int launch_split(cudaStream_t st, const SplitParams &sp, int64_t *launches) {
+    const int64_t total = sp.plane_rows * (sp.K >> 3);
+    int64_t blocks = (total + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    k_split_bf16<<<(unsigned)blocks, 256, 0, st>>>(sp);
+    if (launches) ++*launches;
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, int64_t plane_rows, int T, int pad,
+                int64_t out_rows, const float *bias, float *out, int ldo, int64_t *launches) {
+    CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
+    NTB_TRY(make_map(&ma_hi, gs.a_hi, plane_rows, w.K, BM));
+    NTB_TRY(make_map(&ma_lo, gs.a_lo, plane_rows, w.K, BM));
+    NTB_TRY(make_map(&mb_hi, w.hi, (int64_t)w.taps * w.Np, w.Kp, w.BN));
+    NTB_TRY(make_map(&mb_lo, w.lo, (int64_t)w.taps * w.Np, w.Kp, w.BN));
+    TcParams p{};
+    p.m_tiles = (plane_rows + BM - 1) / BM;
+    p.BN = w.BN; p.Np = w.Np; p.N = w.N; p.n_tiles = w.Np / w.BN;
+    p.taps = w.taps; p.k_blocks = (w.K + BK - 1) / BK;
+    p.k16_last = ((w.K - (p.k_blocks - 1) * BK) + 15) / 16;
+    p.passes = w.single_pass ? 1 : 3;
+    const int stage_bytes = (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + w.BN * BK * 2);
+    p.stages = SMEM_BUDGET / stage_bytes;
+    if (p.stages > 8) p.stages = 8;
+    if (p.stages < 2) return fail(NTB_EINVAL, "tcgen05 GEMM: tile does not fit shared memory%s", "");
+    p.T = T; p.pad = pad; p.out_rows = out_rows; p.bias = bias; p.out = out; p.ldo = ldo;
+    const size_t smem = (size_t)p.stages * stage_bytes + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        NTB_CUDA(cudaFuncSetAttribute(k_gemm_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET + 1024));
+        attr_set = true;
+    }
+    const int64_t tiles = p.m_tiles * p.n_tiles;
+    const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+    k_gemm_tc<<<grid, TC_THREADS, smem, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, p);
+    if (launches) ++*launches;
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------ interface
+void gemm_tc_plan_weights(GemmWeights &w, int taps, int K, int N, Arena &ar) {
+    w = GemmWeights();
+    w.taps = taps; w.K = K; w.N = N;
+    // the tensor-core path needs 16-byte rows in the A planes (K % 8) and a worthwhile shape;
+    // Cin = 1 convs, len_x = 12 / H = 5 event shapes and the tiny CTC readout stay on the SIMT path
+    if (K % 8 != 0 || K < 64 || N < 32) return;
+    w.Kp = (int)align_up(K, BK);
+    w.BN = pick_bn(N);
+    w.Np = (int)align_up(N, w.BN);
+    const int64_t n = (int64_t)taps * w.Np * w.Kp;
+    w.hi = ar.take<__nv_bfloat16>(n);
+    w.lo = ar.take<__nv_bfloat16>(n);
+    w.valid = true;
+}
+
+int gemm_tc_pack_weights(cudaStream_t st, const float *w_kn, GemmWeights &w) {
+    if (!w.valid) return NTB_OK;
+    const int64_t total = (int64_t)w.taps * w.Np * w.Kp;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > 1024) blocks = 1024;
+    k_pack_weights<<<blocks, 256, 0, st>>>(w_kn, w.taps, w.K, w.N, w.Kp, w.Np, w.hi, w.lo);
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+void gemm_tc_plan_scratch(GemmScratch &gs, int64_t rows, int T, int maxk, Arena &ar) {
+    gs = GemmScratch();
+    if (maxk < 64 || rows <= 0) return;
+    // padded layout upper bound: (T + 2) / T more rows, rounded up to whole tiles
+    const int64_t windows = T > 0 ? (rows + T - 1) / T : 0;
+    int64_t cap = rows + 2 * windows;
+    cap = align_up(cap, BM) + BM;
+    gs.rows_cap = cap;
+    gs.kp_cap = (int)align_up(maxk, 8);
+    gs.a_hi = ar.take<__nv_bfloat16>(cap * gs.kp_cap);
+    gs.a_lo = ar.take<__nv_bfloat16>(cap * gs.kp_cap);
+    gs.valid = true;
+}
+
+int gemm_tc_run(cudaStream_t st, const float *A, int lda, int64_t rows, const GemmWeights &w, const float *bias,
+                float *out, int ldo, const GemmScratch &gs, int64_t *launches) {
+    if (!w.valid || !gs.valid || rows > gs.rows_cap || w.K > gs.kp_cap || (lda & 3) ||
+        (reinterpret_cast<uintptr_t>(A) & 15))
+        return fail(NTB_EINVAL, "tcgen05 GEMM: operand not supported (rows %s%lld, K %lld)", "", (long long)rows,
+                    (long long)w.K);
+    if (w.taps != 1) return fail(NTB_EINVAL, "gemm_tc_run: taps must be 1%s", "");
+    SplitParams sp{};
+    sp.A = A; sp.lda = lda; sp.rows = rows; sp.K = w.K; sp.T = 1; sp.relu = 0; sp.pad = 0;
+    sp.hi = gs.a_hi; sp.lo = w.single_pass ? nullptr : gs.a_lo; sp.plane_rows = rows;
+    NTB_TRY(launch_split(st, sp, launches));
+    return launch_gemm(st, w, gs, rows, 1, 0, rows, bias, out, ldo, launches);
+}
+
+int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, const float *aff_a,
+                 const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
+                 int ldo, const GemmScratch &gs, int64_t *launches) {
+    const int pad = w.taps == 3;
+    const int64_t windows = rows / T;
+    const int64_t plane_rows = pad ? windows * (T + 2) : rows;
+    if (!w.valid || !gs.valid || plane_rows > gs.rows_cap || K != w.K || w.K > gs.kp_cap || rows % T)
+        return fail(NTB_EINVAL, "tcgen05 conv: operand not supported (rows %s%lld, K %lld)", "", (long long)rows,
+                    (long long)K);
+    SplitParams sp{};
+    sp.A = A; sp.lda = K; sp.rows = rows; sp.K = K; sp.aff_a = aff_a; sp.aff_b = aff_b; sp.win_group = win_group;
+    sp.T = T; sp.relu = relu_in; sp.pad = pad;
+    sp.hi = gs.a_hi; sp.lo = w.single_pass ? nullptr : gs.a_lo; sp.plane_rows = plane_rows;
+    NTB_TRY(launch_split(st, sp, launches));
+    return launch_gemm(st, w, gs, plane_rows, T, pad, rows, nullptr, out, ldo, launches);
+}
+
+}  // namespace ntb

@@ -1,4 +1,4 @@
-// tcgen05 / TMA / TMEM GEMM (bf16x3 split operands) -- interface; see ntb_gemm_tc_impl.cuh.
+// tcgen05 / TMA / TMEM GEMM (bf16x3 split operands) -- interface; implementation in ntb_gemm_tc.cu.
 #pragma once
 #include "ntb_common.cuh"
 
@@ -9,19 +9,19 @@ struct GemmWeights {
     bool valid = false;
     bool single_pass = false;   // hi*hi only (plain bf16; measurement / ablation only)
     int taps = 1, K = 0, N = 0, Kp = 0, Np = 0, BN = 0;
-    __nv_bfloat16 *hi = nullptr, *lo = nullptr;   // [taps][Np][Kp]
+    __nv_bfloat16 *hi = nullptr, *lo = nullptr;   // [taps][Np][Kp], Kp = K rounded up to 64
 };
 // bf16 hi/lo planes of the A operand for one GEMM (rewritten by every call).
 struct GemmScratch {
     bool valid = false;
     int64_t rows_cap = 0;
     int kp_cap = 0;
-    __nv_bfloat16 *a_hi = nullptr, *a_lo = nullptr;
+    __nv_bfloat16 *a_hi = nullptr, *a_lo = nullptr;   // [plane rows][K] of the GEMM in flight
 };
 
 void gemm_tc_plan_weights(GemmWeights &w, int taps, int K, int N, Arena &ar);
 int gemm_tc_pack_weights(cudaStream_t st, const float *w_kn, GemmWeights &w);
-void gemm_tc_plan_scratch(GemmScratch &gs, int64_t rows, int maxk, Arena &ar);
+void gemm_tc_plan_scratch(GemmScratch &gs, int64_t rows, int T, int maxk, Arena &ar);
 int gemm_tc_run(cudaStream_t st, const float *A, int lda, int64_t rows, const GemmWeights &w, const float *bias,
                 float *out, int ldo, const GemmScratch &gs, int64_t *launches);
 int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, const float *aff_a,
