@@ -7,6 +7,7 @@
 #include "ntb_gemm_tc.cuh"
 #include "ntb_kernels.cuh"
 #include "ntb_lstm.cuh"
+#include "ntb_lstm_tc.cuh"
 
 namespace ntb {
 
@@ -36,6 +37,9 @@ struct LayerDev {
     int Hp = 0;
     float *wih = nullptr, *bias = nullptr, *whh = nullptr;
     GemmWeights wihw;
+    const float *kernel_fw = nullptr, *kernel_bw = nullptr;   // raw TF kernels on the device
+    __nv_bfloat16 *whh_hi = nullptr, *whh_lo = nullptr;       // tensor-core recurrence planes (ntb_lstm_tc.cuh)
+    bool tc_rec = false;
     // chiron_fnn
     const float *fnn_w = nullptr, *fnn_b = nullptr;
 };
@@ -48,7 +52,7 @@ struct ntb_model {
     const float *out_w = nullptr, *out_b = nullptr;
     ntb::GemmWeights outw;
     int max_res_c = 0, max_act_c = 0, max_proj_n = 0;
-    bool has_res = false;
+    bool has_res = false, any_tc_rec = false;
     int64_t launches = 0;
     int profile = 0;
     float stage_ms[4] = {0, 0, 0, 0};
@@ -108,6 +112,20 @@ static int launch_lstm(Ctx &cx, const LstmParams &p, int sm_count) {
         NTB_CUDA(cudaFuncSetAttribute(k_lstm_recurrence<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_lstm_recurrence<false><<<grid, threads, smem, cx.st>>>(p);
     }
+    cx.count();
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+static int launch_lstm_tc(Ctx &cx, const LstmTcParams &p) {
+    const int64_t smem = lstm_tc_smem_bytes(p.H);
+    static bool attr_set = false;
+    if (!attr_set) {
+        NTB_CUDA(cudaFuncSetAttribute(k_lstm_recurrence_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+        attr_set = true;
+    }
+    dim3 grid((unsigned)p.n_tiles, 2);
+    k_lstm_recurrence_tc<<<grid, LSTM_TC_THREADS, smem, cx.st>>>(p);
     cx.count();
     NTB_LAUNCH_CHECK();
     return NTB_OK;
@@ -208,8 +226,16 @@ static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &a
             ld.bias = ar.take<float>(8 * Hp);
             ld.whh = ar.take<float>(2LL * H * Hp * 4);
             gemm_tc_plan_weights(ld.wihw, 1, D, 8 * Hp, ar);
+            ld.kernel_fw = kf; ld.kernel_bw = kb;
+            ld.tc_rec = ld.wihw.valid && Hp == H && lstm_tc_supported(H);
+            if (ld.tc_rec) {
+                ld.whh_hi = ar.take<__nv_bfloat16>(lstm_tc_whh_elems(H));
+                ld.whh_lo = ar.take<__nv_bfloat16>(lstm_tc_whh_elems(H));
+            }
             if (upload && ar.ok()) {
                 k_repack_lstm<<<256, 256, 0, st>>>(kf, bf, kb, bb, l.forget_bias, D, H, Hp, ld.wih, ld.bias, ld.whh);
+                if (ld.tc_rec)
+                    k_pack_whh_tc<<<256, 256, 0, st>>>(kf, kb, D, H, (int)align_up(H, 16), ld.whh_hi, ld.whh_lo);
             }
             dim = 2 * H;
         } else {
@@ -263,6 +289,7 @@ extern "C" int ntb_model_create(const ntb_model_desc *desc, void *weights_dev, i
             if (ld.wihw.valid) gemm_tc_pack_weights(st, ld.wih, ld.wihw);
             if (2 * ld.size > m->max_act_c) m->max_act_c = 2 * ld.size;
             if (8 * ld.Hp > m->max_proj_n) m->max_proj_n = 8 * ld.Hp;
+            if (ld.tc_rec) m->any_tc_rec = true;
         } else {
             if (ld.in_dim / 2 > m->max_act_c) m->max_act_c = ld.in_dim / 2;
         }
@@ -316,7 +343,9 @@ static int64_t plan_workspace(const ntb_model *m, int64_t n, int64_t n_groups, b
         ws.y1 = ws.y2a = ws.y2b = nullptr;
         for (auto &a : ws.aff) a = nullptr;
     }
-    ws.xproj = m->max_proj_n ? ar.take<float>(rows * m->max_proj_n) : nullptr;
+    // the tensor-core recurrence works on whole 128-window tiles (time-major), tail tile padded
+    const int64_t tile_rows = m->any_tc_rec ? align_up(n, LSTM_TC_ROWS) * m->T : 0;
+    ws.xproj = m->max_proj_n ? ar.take<float>((tile_rows > rows ? tile_rows : rows) * m->max_proj_n) : nullptr;
     const bool small_c = m->C <= 8;
     ws.logits = (!small_c && own_logits) ? ar.take<float>(rows * m->C) : nullptr;
     int maxk = m->len_x;
@@ -325,7 +354,7 @@ static int64_t plan_workspace(const ntb_model *m, int64_t n, int64_t n_groups, b
         if (ld.type == NTB_LAYER_RESIDUAL && ld.size > maxk) maxk = ld.size;
     }
     if (m->F_final > maxk) maxk = m->F_final;
-    gemm_tc_plan_scratch(ws.gs, rows, m->T, maxk, ar);
+    gemm_tc_plan_scratch(ws.gs, rows, m->T, maxk, ar, tile_rows);
     return ar.off;
 }
 }  // namespace ntb
@@ -418,12 +447,22 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
         } else if (ld.type == NTB_LAYER_BLSTM) {
             NTB_TRY(mark(1));
             const int N = 8 * ld.Hp;
-            NTB_TRY(dense(cx, cur, dim, rows, dim, N, ld.wih, &ld.wihw, ld.bias, ws.xproj, N, &ws.gs));
-            NTB_TRY(mark(2));
-            LstmParams p{};
-            p.xproj = ws.xproj; p.ldx = N; p.whh = ld.whh; p.lens = lens; p.out = out; p.ldo = 2 * ld.size;
-            p.n_windows = n; p.T = T; p.H = ld.size; p.Hp = ld.Hp;
-            NTB_TRY(launch_lstm(cx, p, m->sm_count));
+            if (ld.tc_rec && ws.gs.valid) {
+                NTB_TRY(gemm_tc_run_xproj(cx.st, cur, dim, n, T, ld.wihw, ld.bias, ws.xproj, ld.size, ws.gs, &cx.launches));
+                NTB_TRY(mark(2));
+                LstmTcParams p{};
+                p.xproj = (const float4 *)ws.xproj; p.whh_hi = ld.whh_hi; p.whh_lo = ld.whh_lo; p.lens = lens;
+                p.out = out; p.ldo = 2 * ld.size; p.n_windows = n; p.n_tiles = cdiv(n, LSTM_TC_ROWS);
+                p.T = T; p.H = ld.size; p.Hp = (int)align_up(ld.size, 16);
+                NTB_TRY(launch_lstm_tc(cx, p));
+            } else {
+                NTB_TRY(dense(cx, cur, dim, rows, dim, N, ld.wih, &ld.wihw, ld.bias, ws.xproj, N, &ws.gs));
+                NTB_TRY(mark(2));
+                LstmParams p{};
+                p.xproj = ws.xproj; p.ldx = N; p.whh = ld.whh; p.lens = lens; p.out = out; p.ldo = 2 * ld.size;
+                p.n_windows = n; p.T = T; p.H = ld.size; p.Hp = ld.Hp;
+                NTB_TRY(launch_lstm(cx, p, m->sm_count));
+            }
             dim = 2 * ld.size;
         } else {   // chiron_fnn
             NTB_TRY(mark(3));
@@ -640,14 +679,38 @@ extern "C" int ntb_conv_bn(const float *in_dev, const float *filt_dev, const flo
     return NTB_OK;
 }
 
-extern "C" int64_t ntb_blstm_workspace_bytes(int64_t n_windows, int32_t T, int32_t D, int32_t H) {
+namespace ntb {
+struct BlstmOpBufs {
+    float *wih, *bias, *whh, *xproj;
+    bool tc;
+    GemmWeights wihw;
+    GemmScratch gs;
+    __nv_bfloat16 *whh_hi, *whh_lo;
+};
+static int64_t plan_blstm_op(Arena &ar, int64_t n, int T, int D, int H, BlstmOpBufs &b) {
     const int Hp = pad_hidden(H);
-    Arena ar(nullptr, 0);
-    ar.take<float>((int64_t)D * 8 * Hp);
-    ar.take<float>(8 * Hp);
-    ar.take<float>(2LL * H * Hp * 4);
-    ar.take<float>(n_windows * T * 8LL * Hp);
+    b.wih = ar.take<float>((int64_t)D * 8 * Hp);
+    b.bias = ar.take<float>(8 * Hp);
+    b.whh = ar.take<float>(2LL * H * Hp * 4);
+    gemm_tc_plan_weights(b.wihw, 1, D, 8 * Hp, ar);
+    b.tc = b.wihw.valid && Hp == H && lstm_tc_supported(H);
+    const int64_t rows = n * T, tile_rows = b.tc ? align_up(n, LSTM_TC_ROWS) * T : 0;
+    b.xproj = ar.take<float>((tile_rows > rows ? tile_rows : rows) * 8LL * Hp);
+    b.whh_hi = b.whh_lo = nullptr;
+    b.gs = GemmScratch();
+    if (b.tc) {
+        b.whh_hi = ar.take<__nv_bfloat16>(lstm_tc_whh_elems(H));
+        b.whh_lo = ar.take<__nv_bfloat16>(lstm_tc_whh_elems(H));
+        gemm_tc_plan_scratch(b.gs, rows, T, D, ar, tile_rows);
+    }
     return ar.off;
+}
+}  // namespace ntb
+
+extern "C" int64_t ntb_blstm_workspace_bytes(int64_t n_windows, int32_t T, int32_t D, int32_t H) {
+    Arena ar(nullptr, 0);
+    BlstmOpBufs b;
+    return plan_blstm_op(ar, n_windows, T, D, H, b);
 }
 
 extern "C" int ntb_blstm(const float *in_dev, const int32_t *len_dev, const float *kernel_fw_dev,
@@ -661,17 +724,28 @@ extern "C" int ntb_blstm(const float *in_dev, const int32_t *len_dev, const floa
     Ctx cx{(cudaStream_t)stream, nullptr};
     const int Hp = pad_hidden(H);
     Arena ar(workspace_dev, workspace_bytes);
-    float *wih = ar.take<float>((int64_t)D * 8 * Hp);
-    float *bias = ar.take<float>(8 * Hp);
-    float *whh = ar.take<float>(2LL * H * Hp * 4);
-    float *xproj = ar.take<float>(n_windows * T * 8LL * Hp);
+    BlstmOpBufs b;
+    plan_blstm_op(ar, n_windows, T, D, H, b);
     if (!workspace_dev || !ar.ok()) return fail(NTB_ENOMEM, "ntb_blstm: workspace too small (need %s%lld)", "", (long long)ar.off);
     if (n_windows == 0) return NTB_OK;
-    k_repack_lstm<<<256, 256, 0, cx.st>>>(kernel_fw_dev, bias_fw_dev, kernel_bw_dev, bias_bw_dev, forget_bias, D, H, Hp, wih, bias, whh);
+    k_repack_lstm<<<256, 256, 0, cx.st>>>(kernel_fw_dev, bias_fw_dev, kernel_bw_dev, bias_bw_dev, forget_bias, D, H, Hp,
+                                          b.wih, b.bias, b.whh);
     NTB_LAUNCH_CHECK();
-    NTB_TRY(dense(cx, in_dev, D, n_windows * T, D, 8 * Hp, wih, nullptr, bias, xproj, 8 * Hp, nullptr));
+    if (b.tc && b.gs.valid) {
+        // same kernels the model uses for H = 100: tcgen05 projection + tensor-core recurrence
+        NTB_TRY(gemm_tc_pack_weights(cx.st, b.wih, b.wihw));
+        k_pack_whh_tc<<<256, 256, 0, cx.st>>>(kernel_fw_dev, kernel_bw_dev, D, H, (int)align_up(H, 16), b.whh_hi, b.whh_lo);
+        NTB_LAUNCH_CHECK();
+        NTB_TRY(gemm_tc_run_xproj(cx.st, in_dev, D, n_windows, T, b.wihw, b.bias, b.xproj, H, b.gs, &cx.launches));
+        LstmTcParams p{};
+        p.xproj = (const float4 *)b.xproj; p.whh_hi = b.whh_hi; p.whh_lo = b.whh_lo; p.lens = len_dev;
+        p.out = out_dev; p.ldo = 2 * H; p.n_windows = n_windows; p.n_tiles = cdiv(n_windows, LSTM_TC_ROWS);
+        p.T = T; p.H = H; p.Hp = (int)align_up(H, 16);
+        return launch_lstm_tc(cx, p);
+    }
+    NTB_TRY(dense(cx, in_dev, D, n_windows * T, D, 8 * Hp, b.wih, nullptr, b.bias, b.xproj, 8 * Hp, nullptr));
     LstmParams p{};
-    p.xproj = xproj; p.ldx = 8 * Hp; p.whh = whh; p.lens = len_dev; p.out = out_dev; p.ldo = 2 * H;
+    p.xproj = b.xproj; p.ldx = 8 * Hp; p.whh = b.whh; p.lens = len_dev; p.out = out_dev; p.ldo = 2 * H;
     p.n_windows = n_windows; p.T = T; p.H = H; p.Hp = Hp;
     return launch_lstm(cx, p, 148);
 }

@@ -48,6 +48,7 @@ struct TcParams {
     const float *bias;
     float *out;
     int ldo;
+    int xproj_H;           // > 0: out is the recurrence's unit-major projected-gates layout (ntb_lstm_tc.cuh)
 };
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -175,7 +176,25 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                     for (int i = 0; i < 16; ++i) { r[i] = h[i]; r[i + 16] = 0; }
                 }
                 tmem_ld_wait();
-                if (row_ok) {
+                if (p.xproj_H > 0) {
+                    // xproj[dir][m_tile][unit][row] float4 (i,j,f,o): a warp's 32 rows are contiguous
+                    float4 *out4 = reinterpret_cast<float4 *>(p.out);
+                    const int nb = n0 + c0, trow = q * 32 + lane;
+#pragma unroll
+                    for (int i = 0; i < 32; i += 4) {
+                        const int n = nb + i;
+                        if (n < p.N && c0 + i < p.BN) {
+                            const int Q = n >> 2, d = Q / p.xproj_H, u = Q - d * p.xproj_H;
+                            float4 v = make_float4(__uint_as_float(r[i]), __uint_as_float(r[i + 1]),
+                                                   __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+                            if (p.bias) {
+                                const float4 b = *reinterpret_cast<const float4 *>(p.bias + n);
+                                v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+                            }
+                            out4[(((int64_t)d * p.m_tiles + m_tile) * p.xproj_H + u) * BM + trow] = v;
+                        }
+                    }
+                } else if (row_ok) {
                     const int nb = n0 + c0;
                     if (vec_ok && nb + 32 <= p.N && c0 + 32 <= p.BN) {
 #pragma unroll
@@ -225,6 +244,7 @@ struct SplitParams {
     int T, relu, pad;
     __nv_bfloat16 *hi, *lo;  // [plane_rows][K]
     int64_t plane_rows;
+    int perm;                // 1: plane row (tile*T + t)*128 + wl <- source row (tile*128 + wl)*T + t
 };
 
 __global__ void __launch_bounds__(256) k_split_bf16(const SplitParams p) {
@@ -235,7 +255,14 @@ __global__ void __launch_bounds__(256) k_split_bf16(const SplitParams p) {
         const int c = (int)(i - pr * K8) << 3;
         int64_t r = pr, w = 0;
         bool real = true;
-        if (p.pad) {
+        if (p.perm) {
+            const int64_t mt = pr >> 7;
+            const int wl = (int)(pr & 127);
+            const int64_t tile = mt / p.T;
+            const int t = (int)(mt - tile * p.T);
+            w = tile * 128 + wl;
+            r = w * p.T + t;
+        } else if (p.pad) {
             w = pr / (p.T + 2);
             const int tt = (int)(pr - w * (p.T + 2)) - 1;
             real = tt >= 0 && tt < p.T;
@@ -351,7 +378,7 @@ int launch_split(cudaStream_t st, const SplitParams &sp, int64_t *launches) {
 }
 
 int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, int64_t plane_rows, int T, int pad,
-                int64_t out_rows, const float *bias, float *out, int ldo, int64_t *launches) {
+                int64_t out_rows, const float *bias, float *out, int ldo, int64_t *launches, int xproj_H = 0) {
     CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
     NTB_TRY(make_map(&ma_hi, gs.a_hi, plane_rows, w.K, BM));
     NTB_TRY(make_map(&ma_lo, gs.a_lo, plane_rows, w.K, BM));
@@ -368,6 +395,7 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     if (p.stages > 8) p.stages = 8;
     if (p.stages < 2) return fail(NTB_EINVAL, "tcgen05 GEMM: tile does not fit shared memory%s", "");
     p.T = T; p.pad = pad; p.out_rows = out_rows; p.bias = bias; p.out = out; p.ldo = ldo;
+    p.xproj_H = xproj_H;
     const size_t smem = (size_t)p.stages * stage_bytes + 1024;
     static bool attr_set = false;
     if (!attr_set) {
@@ -410,13 +438,14 @@ int gemm_tc_pack_weights(cudaStream_t st, const float *w_kn, GemmWeights &w) {
     return NTB_OK;
 }
 
-void gemm_tc_plan_scratch(GemmScratch &gs, int64_t rows, int T, int maxk, Arena &ar) {
+void gemm_tc_plan_scratch(GemmScratch &gs, int64_t rows, int T, int maxk, Arena &ar, int64_t min_rows) {
     gs = GemmScratch();
     if (maxk < 64 || rows <= 0) return;
     // padded layout upper bound: (T + 2) / T more rows, rounded up to whole tiles
     const int64_t windows = T > 0 ? (rows + T - 1) / T : 0;
     int64_t cap = rows + 2 * windows;
     cap = align_up(cap, BM) + BM;
+    if (cap < min_rows) cap = min_rows;
     gs.rows_cap = cap;
     gs.kp_cap = (int)align_up(maxk, 8);
     gs.a_hi = ar.take<__nv_bfloat16>(cap * gs.kp_cap);
@@ -436,6 +465,21 @@ int gemm_tc_run(cudaStream_t st, const float *A, int lda, int64_t rows, const Ge
     sp.hi = gs.a_hi; sp.lo = w.single_pass ? nullptr : gs.a_lo; sp.plane_rows = rows;
     NTB_TRY(launch_split(st, sp, launches));
     return launch_gemm(st, w, gs, rows, 1, 0, rows, bias, out, ldo, launches);
+}
+
+int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, const GemmWeights &w,
+                      const float *bias, float *xproj, int H, const GemmScratch &gs, int64_t *launches) {
+    const int64_t n_tiles = (n_windows + BM - 1) / BM;
+    const int64_t plane_rows = n_tiles * BM * T;
+    if (!w.valid || !gs.valid || plane_rows > gs.rows_cap || w.K > gs.kp_cap || (lda & 3) || w.taps != 1 ||
+        w.N != 8 * H || (reinterpret_cast<uintptr_t>(A) & 15))
+        return fail(NTB_EINVAL, "tcgen05 projection: operand not supported (windows %s%lld, K %lld)", "",
+                    (long long)n_windows, (long long)w.K);
+    SplitParams sp{};
+    sp.A = A; sp.lda = lda; sp.rows = n_windows * T; sp.K = w.K; sp.T = T; sp.relu = 0; sp.pad = 0; sp.perm = 1;
+    sp.hi = gs.a_hi; sp.lo = w.single_pass ? nullptr : gs.a_lo; sp.plane_rows = plane_rows;
+    NTB_TRY(launch_split(st, sp, launches));
+    return launch_gemm(st, w, gs, plane_rows, 1, 0, plane_rows, bias, xproj, 0, launches, H);
 }
 
 int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, const float *aff_a,

@@ -21,9 +21,14 @@ struct GemmScratch {
 
 void gemm_tc_plan_weights(GemmWeights &w, int taps, int K, int N, Arena &ar);
 int gemm_tc_pack_weights(cudaStream_t st, const float *w_kn, GemmWeights &w);
-void gemm_tc_plan_scratch(GemmScratch &gs, int64_t rows, int T, int maxk, Arena &ar);
+void gemm_tc_plan_scratch(GemmScratch &gs, int64_t rows, int T, int maxk, Arena &ar, int64_t min_rows = 0);
 int gemm_tc_run(cudaStream_t st, const float *A, int lda, int64_t rows, const GemmWeights &w, const float *bias,
                 float *out, int ldo, const GemmScratch &gs, int64_t *launches);
+// LSTM input projection for the tensor-core recurrence: A rows are permuted to time-major tiles
+// ([tile][t][128 windows]) and the output is the unit-major projected-gates layout of ntb_lstm_tc.cuh
+// (xproj must hold ceil(n_windows/128)*128*T*8H floats).
+int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, const GemmWeights &w,
+                      const float *bias, float *xproj, int H, const GemmScratch &gs, int64_t *launches);
 int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, const float *aff_a,
                  const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
                  int ldo, const GemmScratch &gs, int64_t *launches);

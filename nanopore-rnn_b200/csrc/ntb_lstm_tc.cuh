@@ -1,0 +1,292 @@
+// K4 (tensor-core form)  BLSTM recurrence on tcgen05 (network.py:266-288: rnn.LSTMCell x2 under
+// tf.nn.bidirectional_dynamic_rnn).  TF semantics restated in ntb_lstm.cuh; this file is the
+// sm_100a implementation used when 4H + Hp fits the 512 TMEM columns (H <= 100).
+//
+// One persistent CTA per (tile of 128 windows, direction); forward and backward tiles are CTAs
+// of one launch.  Per timestep the recurrent term is a [128 x Hp] x [Hp x 4H] GEMM:
+//   * B = W_hh^T, bf16 hi + lo planes, resident in shared memory for all T steps in the
+//     non-swizzled K-major core-matrix layout (2 * 4H * Hp * 2 bytes = 175 KB at H = 100);
+//   * A = h_{t-1}, bf16 hi + lo, lives in TENSOR MEMORY next to the accumulator ("TS" MMA):
+//     TMEM columns [0,4H) gate pre-activations (fp32), [4H, 4H+Hp/2) h hi, [.., 4H+Hp) h lo;
+//     the epilogue writes h_t straight back with tcgen05.st, so h never touches shared memory;
+//   * bf16x3: D = hhi.Whi + hlo.Whi + hhi.Wlo accumulated in fp32 (relative error ~2^-16; the
+//     recurrence has to hold the 1e-3 logits budget over 100 dependent steps).
+// Warp roles: warp 0 issues the MMAs (one thread) and prefetches the next step's projected gates
+// towards L2; warp 2 owns the TMEM allocation; warps 4-11 are the gate epilogue: thread = one
+// window (TMEM lane), two warps per lane quarter take alternate 32-column chunks (8 hidden
+// units x i,j,f,o), add the projected gates (coalesced float4 loads, layout below), apply the
+// fused cell update with the cell state in registers, and write h_t to TMEM (next step's A) and
+// to the layer output.
+// Both directions run on a uniform clock: step s handles t = s (fw) or t = T-1-s (bw) for every
+// window; a window is inactive while t >= len (state stays zero for bw, frozen-and-unused for
+// fw), which is equivalent to TF's reverse_sequence formulation.
+//
+// Projected-gates layout (written by the projection GEMM's epilogue, ntb_gemm_tc.cu):
+//   xproj[dir][tile*T + t][unit][row 0..127] float4 = (i, j, f, o) pre-activations with bias and
+//   forget_bias folded -- one timestep of one tile is a contiguous 128*H*16 bytes.
+#pragma once
+#include "ntb_common.cuh"
+#include "ntb_tc_ptx.cuh"
+
+namespace ntb {
+
+constexpr int LSTM_TC_ROWS = 128;       // windows per tile = TMEM lanes
+constexpr int LSTM_TC_THREADS = 384;    // 4 control warps + 8 epilogue warps
+constexpr int LSTM_TC_MAXCH = 7;        // chunks of 8 units per epilogue warp (13 chunks at H = 100)
+
+struct LstmTcParams {
+    const float4 *xproj;              // see layout above
+    const __nv_bfloat16 *whh_hi;      // [2][Hp/8][4H][8]  (K-chunk major, row n = unit*4 + gate)
+    const __nv_bfloat16 *whh_lo;
+    const int32_t *lens;              // [n_windows]
+    float *out;                       // [n_windows*T][ldo], column dir*H + unit
+    int ldo;
+    int64_t n_windows;
+    int n_tiles;                      // ceil(n_windows / 128)
+    int T, H, Hp;                     // Hp = H rounded up to 16
+};
+
+static inline bool lstm_tc_supported(int H) {
+    const int Hp = (int)align_up(H, 16);
+    return H >= 16 && H % 4 == 0 && 4 * H + Hp <= 512 && (4 * H <= 256 || (4 * H - 256) % 16 == 0) &&
+           (H + 7) / 8 <= 2 * LSTM_TC_MAXCH;
+}
+static inline int64_t lstm_tc_smem_bytes(int H) {
+    const int Hp = (int)align_up(H, 16);
+    return 2LL * 4 * H * Hp * 2 + 128;
+}
+static inline int64_t lstm_tc_whh_elems(int H) { return 2LL * align_up(H, 16) * 4 * H; }   // per plane, both dirs
+
+// TF LSTMCell kernel rows D..D+H-1 (the h part), gate column blocks i|j|f|o  ->  bf16 hi/lo
+// planes [dir][k/8][n = u*4+g][k%8], zero for k >= H.
+__global__ void k_pack_whh_tc(const float *__restrict__ kernel_fw, const float *__restrict__ kernel_bw, int D, int H,
+                              int Hp, __nv_bfloat16 *__restrict__ hi, __nv_bfloat16 *__restrict__ lo) {
+    const int N = 4 * H;
+    const int64_t per_dir = (int64_t)Hp * N;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < 2 * per_dir;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int dir = (int)(i / per_dir);
+        const int64_t j = i - dir * per_dir;
+        const int k8 = (int)(j % 8), n = (int)((j / 8) % N), kc = (int)(j / (8 * N));
+        const int k = kc * 8 + k8, u = n >> 2, g = n & 3;
+        const float *kern = dir ? kernel_bw : kernel_fw;
+        const float v = k < H ? kern[(int64_t)(D + k) * 4 * H + g * H + u] : 0.0f;
+        __nv_bfloat16 h, l;
+        ptx::split_bf16(v, h, l);
+        hi[i] = h;
+        lo[i] = l;
+    }
+}
+
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// c' = sigmoid(f) c + sigmoid(i) tanh(j) ; h' = sigmoid(o) tanh(c')  with 5 ex2 + 2 rcp (7 MUFU
+// instead of 10): the three sigmoid/tanh denominators of c' share one reciprocal.
+//   sigmoid(x) = 1/(1+e^-x), tanh(x) = (1-e^-2x)/(1+e^-2x); arguments are clamped so that the
+//   product of denominators stays below 2^120 (sigmoid(-27) ~ 2e-12: far below the fp32 noise).
+__device__ __forceinline__ void lstm_cell_update(float zi, float zj, float zf, float zo, float &c, float &h) {
+    const float L = 1.4426950408889634f;
+    const float A = ex2_approx(-L * fmaxf(zi, -27.0f));
+    const float B = ex2_approx(-2.0f * L * fmaxf(zj, -13.5f));
+    const float F = ex2_approx(-L * fmaxf(zf, -27.0f));
+    const float pf = 1.0f + F;
+    const float P = (1.0f + A) * (1.0f + B);
+    const float cn = fmaf(c, P, (1.0f - B) * pf) * rcp_approx(P * pf);
+    const float O = ex2_approx(-L * fmaxf(zo, -27.0f));
+    const float C2 = ex2_approx(-2.0f * L * fmaxf(cn, -13.5f));
+    h = (1.0f - C2) * rcp_approx((1.0f + O) * (1.0f + C2));
+    c = cn;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {   // a -> low half (even k)
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+
+__global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const LstmTcParams p) {
+    using namespace ptx;
+    extern __shared__ __align__(128) uint8_t smem_w[];          // [2 planes][Hp/8][4H][8] bf16
+    __shared__ uint64_t d_full, h_ready;
+    __shared__ uint32_t tmem_base_smem;
+
+    const int H = p.H, Hp = p.Hp, T = p.T, N = 4 * H;
+    const int dir = blockIdx.y, tile = blockIdx.x;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t plane_bytes = (uint32_t)N * Hp * 2;
+
+    // ---- one-time setup: W_hh^T hi/lo planes -> smem, barriers, TMEM
+    {
+        const uint4 *src_hi = reinterpret_cast<const uint4 *>(p.whh_hi + (int64_t)dir * N * Hp);
+        const uint4 *src_lo = reinterpret_cast<const uint4 *>(p.whh_lo + (int64_t)dir * N * Hp);
+        uint4 *dst = reinterpret_cast<uint4 *>(smem_w);
+        const int n16 = (int)(plane_bytes >> 4);
+        for (int i = threadIdx.x; i < n16; i += LSTM_TC_THREADS) {
+            dst[i] = __ldg(src_hi + i);
+            dst[n16 + i] = __ldg(src_lo + i);
+        }
+        fence_proxy_async_smem();          // generic-proxy stores -> visible to tcgen05.mma reads
+    }
+    if (threadIdx.x == 0) {
+        mbar_init(&d_full, 1);
+        mbar_init(&h_ready, 8);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(&tmem_base_smem, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_smem;
+    const uint32_t a_hi_col = (uint32_t)N, a_lo_col = (uint32_t)(N + Hp / 2);
+    const int64_t m_tiles = (int64_t)p.n_tiles * T;
+    const int64_t step_f4 = (int64_t)H * LSTM_TC_ROWS;           // float4 per (tile, t, dir)
+
+    if (warp == 0) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const int N1 = N < 256 ? N : 256, N2 = N - N1;
+            const uint32_t idesc1 = idesc_bf16_f32(128, N1), idesc2 = idesc_bf16_f32(128, N2 > 0 ? N2 : 16);
+            const uint32_t lbo = (uint32_t)N * 16, sbo = 128;     // K-chunk stride, 8-row group stride
+            const uint32_t w_hi = smem_u32(smem_w), w_lo = w_hi + plane_bytes;
+            const int k16n = Hp / 16;
+            const float4 *xp = p.xproj + ((int64_t)dir * m_tiles + (int64_t)tile * T) * step_f4;
+            for (int s = 0; s < T; ++s) {
+                mbar_wait(&h_ready, (uint32_t)(s & 1));
+                tc_fence_after();
+                for (int half = 0; half < 2; ++half) {
+                    const int Nn = half ? N2 : N1;
+                    if (Nn <= 0) break;
+                    const uint32_t d = tmem_base + (uint32_t)(half * 256);
+                    const uint32_t idesc = half ? idesc2 : idesc1;
+                    const uint32_t row_off = (uint32_t)(half * 256 / 8) * 128;
+                    for (int j = 0; j < k16n; ++j) {
+                        const uint32_t koff = (uint32_t)j * 2 * lbo + row_off;
+                        const uint64_t bh = smem_desc_nosw(w_hi + koff, lbo, sbo);
+                        const uint64_t bl = smem_desc_nosw(w_lo + koff, lbo, sbo);
+                        const uint32_t ah = tmem_base + a_hi_col + (uint32_t)(8 * j);
+                        const uint32_t al = tmem_base + a_lo_col + (uint32_t)(8 * j);
+                        umma_f16_ts(d, ah, bh, idesc, j != 0);
+                        umma_f16_ts(d, al, bh, idesc, 1);
+                        umma_f16_ts(d, ah, bl, idesc, 1);
+                    }
+                }
+                umma_commit(&d_full);
+                // next step's projected gates towards L2 while this step computes
+                if (s + 1 < T) {
+                    const int tn = dir ? T - 2 - s : s + 1;
+                    const char *g = reinterpret_cast<const char *>(xp + (int64_t)tn * step_f4);
+                    const uint32_t bytes = (uint32_t)step_f4 * 16, piece = (bytes / 4) & ~15u;
+                    for (int q = 0; q < 4; ++q)
+                        bulk_prefetch_l2(g + (size_t)q * piece, q == 3 ? bytes - 3 * piece : piece);
+                }
+            }
+        }
+    } else if (warp >= 4) {
+        // ===================== gate epilogue =====================
+        const int q = warp & 3, par = (warp - 4) >> 2;
+        const int r = q * 32 + lane;
+        const int64_t w = (int64_t)tile * LSTM_TC_ROWS + r;
+        const bool exists = w < p.n_windows;
+        int len = exists ? p.lens[w] : 0;
+        len = len > T ? T : len;
+        const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+        const int n_chunks = (H + 7) >> 3;
+        float cst[LSTM_TC_MAXCH][8];
+#pragma unroll
+        for (int ci = 0; ci < LSTM_TC_MAXCH; ++ci)
+#pragma unroll
+            for (int u = 0; u < 8; ++u) cst[ci][u] = 0.0f;
+        // h_0 = 0: clear the A columns (hi and lo, pad units included)
+        if (par == 0)
+            for (int c4 = 0; c4 < Hp; c4 += 4) tmem_st_32x4(lane_base + a_hi_col + (uint32_t)c4, 0u, 0u, 0u, 0u);
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&h_ready);
+
+        const float4 *xrow = p.xproj + ((int64_t)dir * m_tiles + (int64_t)tile * T) * step_f4 + r;
+        for (int s = 0; s < T; ++s) {
+            const int t = dir ? T - 1 - s : s;
+            const bool active = t < len;
+            const float4 *xs = xrow + (int64_t)t * step_f4;
+            float4 xv[8];
+            // first chunk's projected gates: independent of the MMA, issued before the wait
+            {
+                const int u0 = par * 8;
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    xv[u] = (u0 + u < H) ? __ldg(xs + (int64_t)(u0 + u) * LSTM_TC_ROWS) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            mbar_wait(&d_full, (uint32_t)(s & 1));
+            tc_fence_after();
+            float *orow = p.out + (w * T + t) * (int64_t)p.ldo + dir * H;
+#pragma unroll
+            for (int ci = 0; ci < LSTM_TC_MAXCH; ++ci) {
+                const int c = 2 * ci + par;
+                if (c < n_chunks) {
+                    uint32_t acc[32];
+                    tmem_ld_32x32(lane_base + (uint32_t)(32 * c), acc);
+                    tmem_ld_wait();
+                    float4 xn[8];
+                    const int un0 = (c + 2) * 8;
+                    if (c + 2 < n_chunks) {
+#pragma unroll
+                        for (int u = 0; u < 8; ++u)
+                            xn[u] = (un0 + u < H) ? __ldg(xs + (int64_t)(un0 + u) * LSTM_TC_ROWS)
+                                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                    float hv[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        float cc = cst[ci][u], hh;
+                        lstm_cell_update(__uint_as_float(acc[4 * u + 0]) + xv[u].x, __uint_as_float(acc[4 * u + 1]) + xv[u].y,
+                                         __uint_as_float(acc[4 * u + 2]) + xv[u].z, __uint_as_float(acc[4 * u + 3]) + xv[u].w,
+                                         cc, hh);
+                        const bool on = active && (c * 8 + u < H);
+                        cst[ci][u] = on ? cc : cst[ci][u];
+                        hv[u] = on ? hh : 0.0f;
+                    }
+                    uint32_t ph[4], pl[4];
+#pragma unroll
+                    for (int m = 0; m < 4; ++m) {
+                        ph[m] = pack_bf16x2(hv[2 * m], hv[2 * m + 1]);
+                        const float l0 = hv[2 * m] - __uint_as_float(ph[m] << 16);
+                        const float l1 = hv[2 * m + 1] - __uint_as_float(ph[m] & 0xffff0000u);
+                        pl[m] = pack_bf16x2(l0, l1);
+                    }
+                    tmem_st_32x4(lane_base + a_hi_col + (uint32_t)(4 * c), ph[0], ph[1], ph[2], ph[3]);
+                    tmem_st_32x4(lane_base + a_lo_col + (uint32_t)(4 * c), pl[0], pl[1], pl[2], pl[3]);
+                    if (exists) {
+                        *reinterpret_cast<float4 *>(orow + c * 8) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+                        if (c * 8 + 4 < H)
+                            *reinterpret_cast<float4 *>(orow + c * 8 + 4) = make_float4(hv[4], hv[5], hv[6], hv[7]);
+                    }
+                    if (c + 2 < n_chunks) {
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) xv[u] = xn[u];
+                    }
+                }
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&h_ready);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+}  // namespace ntb

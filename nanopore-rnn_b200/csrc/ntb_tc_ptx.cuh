@@ -92,6 +92,45 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar) {
                  : "memory");
 }
 
+// D[tmem] (+)= A[tmem] * B[smem desc]  ("TS" form: the A operand is read from tensor memory:
+// lane = row, 16-bit elements packed two per 32-bit column, K = 16 -> 8 columns per instruction)
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+// registers -> TMEM: this warp's 32 lanes x 4 consecutive 32-bit columns
+__device__ __forceinline__ void tmem_st_32x4(uint32_t taddr, uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(r0), "r"(r1),
+                 "r"(r2), "r"(r3)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// Pull a contiguous global range towards L2 (no smem destination, no completion to wait for).
+__device__ __forceinline__ void bulk_prefetch_l2(const void *gptr, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gptr), "r"(bytes) : "memory");
+}
+
+// K-major operand in the NON-swizzled canonical layout: 8-row x 16-byte core matrices (128 B
+// contiguous); `lbo` = byte distance between the two core matrices adjacent in K, `sbo` = byte
+// distance between adjacent 8-row groups (in uint128 units: ((8,n),2):((1,SBO),LBO)).
+__device__ __forceinline__ uint64_t smem_desc_nosw(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;
+    return d;
+}
+
 // TMEM -> registers: this warp's 32 lanes x 32 consecutive fp32 columns (lane = row of the tile)
 __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(

@@ -109,7 +109,7 @@ def test_conv_bn_matches_oracle(lib, Cin, Cout, k, relu, bn):
 
 # ------------------------------------------------------------------ BLSTM
 @pytest.mark.parametrize("D,H,T,n", [(12, 5, 30, 80), (256, 100, 100, 70), (200, 100, 100, 130), (7, 33, 17, 65),
-                                     (16, 128, 12, 9)])
+                                     (16, 128, 12, 9), (64, 64, 40, 300), (128, 68, 25, 129), (72, 96, 7, 1)])
 def test_blstm_matches_oracle(lib, D, H, T, n):
     rng = np.random.default_rng(D * H + T)
     lim = np.sqrt(6.0 / (D + 5 * H))
@@ -129,7 +129,11 @@ def test_blstm_matches_oracle(lib, D, H, T, n):
     torch.cuda.synchronize()
     ref = A.blstm(x, lens, w, 5.0).reshape(n * T, 2 * H)
     got = out.cpu().numpy()
-    np.testing.assert_allclose(got, ref, atol=2e-5, rtol=0)
+    # H = 100 shapes run the tcgen05 projection + tensor-core recurrence (bf16x3 split operands,
+    # ~2^-16 relative per product, 100 dependent steps): measured max error 8e-5; the fp32 SIMT
+    # shapes hold 2e-5.  Both are far inside the 1e-3 logits budget checked on whole models below.
+    tc_path = H % 4 == 0 and 16 <= H <= 100 and D % 8 == 0 and D >= 64
+    np.testing.assert_allclose(got, ref, atol=2e-4 if tc_path else 2e-5, rtol=0)
     mask = (np.arange(T)[None, :] >= lens[:, None]).reshape(-1)
     assert np.all(got[mask] == 0.0)                    # dynamic_rnn zeros beyond seq_len, exactly
 
