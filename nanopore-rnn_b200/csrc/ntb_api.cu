@@ -82,8 +82,8 @@ static int launch_conv_gemm(Ctx &cx, const ConvGemmParams &p) {
 
 static int launch_bn_stats(Ctx &cx, const float *y, int C, int T, const int32_t *group_off, int64_t n_groups,
                            const float *scale, const float *offset, float *a, float *b) {
-    dim3 grid((unsigned)n_groups, cdiv(C, 256));
-    k_bn_stats<<<grid, C < 256 ? (int)align_up(C, 32) : 256, 0, cx.st>>>(y, C, T, group_off, scale, offset, 1e-5f, a, b);
+    dim3 grid((unsigned)n_groups, cdiv(C, BN_CH4 * 4));
+    k_bn_stats<<<grid, BN_CH4 * BN_SLICES, 0, cx.st>>>(y, C, T, group_off, scale, offset, 1e-5f, a, b);
     cx.count();
     NTB_LAUNCH_CHECK();
     return NTB_OK;
@@ -383,8 +383,10 @@ static int residual_forward(Ctx &cx, ntb_model *m, const LayerDev &ld, const flo
         const float *fa = src_of[c] < 0 ? nullptr : aa[src_of[c]];
         const float *fb = src_of[c] < 0 ? nullptr : bb[src_of[c]];
         if (ld.convw[c].valid && ws.gs.valid) {
+            // conv1 and conv2a are both 1x1 convs of the layer input: one operand split serves both
+            const bool reuse = c == 1 && ld.convw[0].valid;
             NTB_TRY(gemm_tc_conv(cx.st, A, K, rows, T, fa, fb, ws.win_group, src_of[c] >= 0, ld.convw[c], ys[c], C,
-                                 ws.gs, &cx.launches));
+                                 ws.gs, &cx.launches, reuse));
         } else {
             ConvGemmParams p{};
             p.A = A; p.lda = K; p.W = ld.conv[c]; p.bias = nullptr;
@@ -654,6 +656,7 @@ extern "C" int ntb_conv_bn(const float *in_dev, const float *filt_dev, const flo
         return fail(NTB_EINVAL, "ntb_conv_bn: bad argument%s", "");
     if ((scale_dev == nullptr) != (offset_dev == nullptr)) return fail(NTB_EINVAL, "ntb_conv_bn: scale/offset must both be set%s", "");
     if (scale_dev && (!group_off_dev || n_groups <= 0)) return fail(NTB_EINVAL, "ntb_conv_bn: BN needs group_off%s", "");
+    if (scale_dev && (Cout % 4)) return fail(NTB_EINVAL, "ntb_conv_bn: BN needs Cout %% 4 == 0%s", "");
     NTB_TRY(check_device());
     Ctx cx{(cudaStream_t)stream, nullptr};
     Arena ar(workspace_dev, workspace_bytes);

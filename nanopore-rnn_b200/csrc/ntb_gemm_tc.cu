@@ -34,7 +34,8 @@ constexpr int BK = 64;         // bf16 per smem row = one 128-byte swizzle span
 constexpr int TC_THREADS = 256;
 constexpr int TMEM_COLS = 512;
 constexpr int A_TILE_BYTES = BM * BK * 2;     // 16 KB
-constexpr int SMEM_BUDGET = 220 * 1024;
+constexpr int EPI_STAGE_BYTES = 4 * 2 * 4096;   // 4 epilogue warps x 2 buffers x [32 rows][32 fp32], TMA-store staging
+constexpr int SMEM_BUDGET = 227 * 1024 - 1024 - EPI_STAGE_BYTES - 2048;   // operand ring
 
 struct TcParams {
     int64_t m_tiles;       // ceil(plane_rows / 128)
@@ -48,13 +49,14 @@ struct TcParams {
     const float *bias;
     float *out;
     int ldo;
+    int tma_store;         // plain row-major output through smem staging + cp.async.bulk.tensor stores
     int xproj_H;           // > 0: out is the recurrence's unit-major projected-gates layout (ntb_lstm_tc.cuh)
 };
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
           const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
-          const TcParams p) {
+          const __grid_constant__ CUtensorMap map_out, const TcParams p) {
     using namespace ptx;
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint64_t full_bar[8], empty_bar[8], acc_full[2], acc_empty[2];
@@ -70,6 +72,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&map_a_hi); prefetch_tmap(&map_a_lo); prefetch_tmap(&map_b_hi); prefetch_tmap(&map_b_lo);
+        if (p.tma_store) prefetch_tmap(&map_out);
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
@@ -147,6 +150,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
         const int q = warp & 3;                                // TMEM lane quarter this warp may access
         int acc = 0; uint32_t acc_phase = 0;
         const bool vec_ok = ((p.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
+        uint8_t *stage_buf = smem + (size_t)p.stages * stage_bytes + (size_t)q * 8192;   // 1024-B aligned
+        int stage_it = 0;
         for (int64_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             const int n_tile = (int)(tile % p.n_tiles);
             const int64_t m_tile = tile / p.n_tiles;
@@ -176,7 +181,31 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                     for (int i = 0; i < 16; ++i) { r[i] = h[i]; r[i + 16] = 0; }
                 }
                 tmem_ld_wait();
-                if (p.xproj_H > 0) {
+                if (p.tma_store) {
+                    // registers -> 128B-swizzled [32 rows][32 cols] staging tile -> one TMA store per warp
+                    uint8_t *buf = stage_buf + (stage_it & 1) * 4096;
+                    ++stage_it;
+                    if (lane == 0) bulk_wait_group_read<1>();       // the store that last read `buf` is done
+                    __syncwarp();
+                    const int nb = n0 + c0;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                               __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+                        if (p.bias) {
+                            const int n = nb + 4 * j;
+                            v.x += n + 0 < p.N ? p.bias[n + 0] : 0.0f; v.y += n + 1 < p.N ? p.bias[n + 1] : 0.0f;
+                            v.z += n + 2 < p.N ? p.bias[n + 2] : 0.0f; v.w += n + 3 < p.N ? p.bias[n + 3] : 0.0f;
+                        }
+                        *reinterpret_cast<float4 *>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) = v;
+                    }
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        tma_store_2d(&map_out, buf, nb, (int)(m_tile * BM) + q * 32);
+                        bulk_commit_group();
+                    }
+                } else if (p.xproj_H > 0) {
                     // xproj[dir][m_tile][unit][row] float4 (i,j,f,o): a warp's 32 rows are contiguous
                     float4 *out4 = reinterpret_cast<float4 *>(p.out);
                     const int nb = n0 + c0, trow = q * 32 + lane;
@@ -222,6 +251,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
             if (lane == 0) mbar_arrive(&acc_empty[acc]);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
+        if (p.tma_store && lane == 0) bulk_wait_group<0>();   // stores complete before smem goes away
     }
     tc_fence_before();
     __syncthreads();
@@ -298,6 +328,55 @@ __global__ void __launch_bounds__(256) k_split_bf16(const SplitParams p) {
     }
 }
 
+// Same transform with one CTA per window: the BN affine of the producer is constant over a window
+// (window -> group -> [a, b] per channel), so every thread keeps its 8 channels' a/b in registers
+// and walks the window's rows; no per-element index arithmetic.  Used for the conv operands.
+__global__ void __launch_bounds__(256) k_split_bf16_window(const SplitParams p) {
+    const int K8 = p.K >> 3;
+    const int rows_per_it = blockDim.x / K8;
+    const int cg = threadIdx.x % K8, rs = threadIdx.x / K8;
+    if (rs >= rows_per_it) return;
+    const int c = cg << 3;
+    const int64_t w = blockIdx.x;
+    float a[8], b[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { a[j] = 1.0f; b[j] = 0.0f; }
+    if (p.aff_a) {
+        const int g = p.win_group[w];
+        const float4 a0 = *reinterpret_cast<const float4 *>(p.aff_a + (int64_t)g * p.K + c);
+        const float4 a1 = *reinterpret_cast<const float4 *>(p.aff_a + (int64_t)g * p.K + c + 4);
+        const float4 b0 = *reinterpret_cast<const float4 *>(p.aff_b + (int64_t)g * p.K + c);
+        const float4 b1 = *reinterpret_cast<const float4 *>(p.aff_b + (int64_t)g * p.K + c + 4);
+        a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+        b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+    }
+    const int prow_n = p.pad ? p.T + 2 : p.T;              // plane rows of this window
+    const int64_t pr0 = w * prow_n;
+    const float *src = p.A + (w * p.T) * (int64_t)p.lda + c;
+    for (int i = rs; i < prow_n; i += rows_per_it) {
+        const int tt = p.pad ? i - 1 : i;
+        float v[8];
+        if (tt >= 0 && tt < p.T) {
+            const float4 x0 = *reinterpret_cast<const float4 *>(src + (int64_t)tt * p.lda);
+            const float4 x1 = *reinterpret_cast<const float4 *>(src + (int64_t)tt * p.lda + 4);
+            v[0] = x0.x; v[1] = x0.y; v[2] = x0.z; v[3] = x0.w; v[4] = x1.x; v[5] = x1.y; v[6] = x1.z; v[7] = x1.w;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                v[j] = fmaf(v[j], a[j], b[j]);
+                if (p.relu) v[j] = fmaxf(v[j], 0.0f);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = 0.0f;
+        }
+        __align__(16) __nv_bfloat16 h[8], l[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ptx::split_bf16(v[j], h[j], l[j]);
+        *reinterpret_cast<uint4 *>(p.hi + (pr0 + i) * p.K + c) = *reinterpret_cast<const uint4 *>(h);
+        if (p.lo) *reinterpret_cast<uint4 *>(p.lo + (pr0 + i) * p.K + c) = *reinterpret_cast<const uint4 *>(l);
+    }
+}
+
 // TF weights [taps][K][N] fp32 -> K-major bf16 planes [taps][Np][Kp] (zero padded)
 __global__ void k_pack_weights(const float *__restrict__ w, int taps, int K, int N, int Kp, int Np,
                                __nv_bfloat16 *__restrict__ hi, __nv_bfloat16 *__restrict__ lo) {
@@ -345,6 +424,22 @@ int make_map(CUtensorMap *m, const void *base, int64_t rows, int K, int box_rows
     return NTB_OK;
 }
 
+// fp32 [rows][ldo] row-major output, box {32 cols, 32 rows}, 128-byte swizzle (TMA-store epilogue)
+int make_map_out(CUtensorMap *m, const float *base, int64_t rows, int N, int ldo) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return fail(NTB_ECUDA, "cuTensorMapEncodeTiled entry point not found%s", "");
+    cuuint64_t dims[2] = {(cuuint64_t)N, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ldo * 4};
+    cuuint32_t box[2] = {32, 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(NTB_ECUDA, "cuTensorMapEncodeTiled (output) failed (%s%lld) rows %lld", "", (long long)r, (long long)rows);
+    return NTB_OK;
+}
+
 int pick_bn(int N) {
     // fewest N tiles first (A is re-read once per N tile), then least padding; BN % 16 == 0, <= 256
     int best = 0, best_tiles = 1 << 30, best_pad = 1 << 30;
@@ -366,6 +461,14 @@ int sm_count() {
 }
 
 int launch_split(cudaStream_t st, const SplitParams &sp, int64_t *launches) {
+    const int K8 = sp.K >> 3;
+    if (!sp.perm && sp.T > 1 && K8 <= 256 && sp.rows % sp.T == 0 && (sp.pad || sp.aff_a)) {
+        const int threads = (256 / K8) * K8;
+        k_split_bf16_window<<<(unsigned)(sp.rows / sp.T), threads, 0, st>>>(sp);
+        if (launches) ++*launches;
+        NTB_LAUNCH_CHECK();
+        return NTB_OK;
+    }
     const int64_t total = sp.plane_rows * (sp.K >> 3);
     int64_t blocks = (total + 255) / 256;
     const int64_t cap = (int64_t)sm_count() * 16;
@@ -396,15 +499,20 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     if (p.stages < 2) return fail(NTB_EINVAL, "tcgen05 GEMM: tile does not fit shared memory%s", "");
     p.T = T; p.pad = pad; p.out_rows = out_rows; p.bias = bias; p.out = out; p.ldo = ldo;
     p.xproj_H = xproj_H;
-    const size_t smem = (size_t)p.stages * stage_bytes + 1024;
+    // coalesced TMA-store epilogue for plain row-major outputs (N tiles of whole 32-column chunks)
+    p.tma_store = (!pad && xproj_H == 0 && w.BN % 32 == 0 && (ldo & 3) == 0 &&
+                   (reinterpret_cast<uintptr_t>(out) & 15) == 0) ? 1 : 0;
+    CUtensorMap mo = ma_hi;
+    if (p.tma_store) NTB_TRY(make_map_out(&mo, out, out_rows, w.N, ldo));
+    const size_t smem = (size_t)p.stages * stage_bytes + 1024 + EPI_STAGE_BYTES;
     static bool attr_set = false;
     if (!attr_set) {
-        NTB_CUDA(cudaFuncSetAttribute(k_gemm_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET + 1024));
+        NTB_CUDA(cudaFuncSetAttribute(k_gemm_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET + 1024 + EPI_STAGE_BYTES));
         attr_set = true;
     }
     const int64_t tiles = p.m_tiles * p.n_tiles;
     const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-    k_gemm_tc<<<grid, TC_THREADS, smem, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, p);
+    k_gemm_tc<<<grid, TC_THREADS, smem, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, mo, p);
     if (launches) ++*launches;
     NTB_LAUNCH_CHECK();
     return NTB_OK;
@@ -484,7 +592,7 @@ int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_window
 
 int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, const float *aff_a,
                  const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
-                 int ldo, const GemmScratch &gs, int64_t *launches) {
+                 int ldo, const GemmScratch &gs, int64_t *launches, bool reuse_planes) {
     const int pad = w.taps == 3;
     const int64_t windows = rows / T;
     const int64_t plane_rows = pad ? windows * (T + 2) : rows;
@@ -495,7 +603,7 @@ int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, co
     sp.A = A; sp.lda = K; sp.rows = rows; sp.K = K; sp.aff_a = aff_a; sp.aff_b = aff_b; sp.win_group = win_group;
     sp.T = T; sp.relu = relu_in; sp.pad = pad;
     sp.hi = gs.a_hi; sp.lo = w.single_pass ? nullptr : gs.a_lo; sp.plane_rows = plane_rows;
-    NTB_TRY(launch_split(st, sp, launches));
+    if (!reuse_planes) NTB_TRY(launch_split(st, sp, launches));   // else: the previous conv split the same input
     return launch_gemm(st, w, gs, plane_rows, T, pad, rows, nullptr, out, ldo, launches);
 }
 

@@ -31,6 +31,6 @@ int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_window
                       const float *bias, float *xproj, int H, const GemmScratch &gs, int64_t *launches);
 int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, const float *aff_a,
                  const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
-                 int ldo, const GemmScratch &gs, int64_t *launches);
+                 int ldo, const GemmScratch &gs, int64_t *launches, bool reuse_planes = false);
 
 }  // namespace ntb

@@ -182,40 +182,62 @@ __global__ void __launch_bounds__((BM / TM) * (BN / TN)) k_conv_gemm_simt(ConvGe
 // simple_global_bn statistics (network.py:339-349): tf.nn.moments over axes [0,1,2] of ONE
 // reference batch (= BN group; padded positions included), then the affine form
 // tf.nn.batch_normalization uses:  a = rsqrt(var + eps) * scale ; b = offset - mean * a.
-// One thread per (group, channel); float64 accumulation in fixed row order -> bit-stable.
+// ONE pass over the conv output: sum x and sum x^2 accumulate in float64 (fp32 inputs and their squares
+// are exact in fp64, so var = E[x^2] - mean^2 loses nothing visible in fp32), fixed order ->
+// bit-stable, no atomics.  Block = 64 channels x 4 row slices (a warp reads 128 contiguous
+// bytes of one row); the slices are combined through shared memory in slice order.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_bn_stats(const float *__restrict__ y, int C, int T,
-                                                  const int32_t *__restrict__ group_off,
-                                                  const float *__restrict__ scale,
-                                                  const float *__restrict__ offset, float eps,
-                                                  float *__restrict__ aff_a, float *__restrict__ aff_b) {
+constexpr int BN_CH4 = 64, BN_SLICES = 4;   // block = 64 float4 columns (256 channels) x 4 row slices
+__global__ void __launch_bounds__(BN_CH4 * BN_SLICES) k_bn_stats(const float *__restrict__ y, int C, int T,
+                                                                 const int32_t *__restrict__ group_off,
+                                                                 const float *__restrict__ scale,
+                                                                 const float *__restrict__ offset, float eps,
+                                                                 float *__restrict__ aff_a, float *__restrict__ aff_b) {
+    __shared__ double sh[2][BN_SLICES][BN_CH4 * 4];
     const int g = blockIdx.x;
-    const int c = blockIdx.y * blockDim.x + threadIdx.x;
-    if (c >= C) return;
+    const int cl = threadIdx.x % BN_CH4, sl = threadIdx.x / BN_CH4;
+    const int c = (blockIdx.y * BN_CH4 + cl) * 4;          // first of this thread's 4 channels
     const int64_t r0 = (int64_t)group_off[g] * T, r1 = (int64_t)group_off[g + 1] * T;
     const int64_t n = r1 - r0;
-    const float *p = y + r0 * C + c;
-    double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
-    int64_t i = 0;
-    for (; i + 4 <= n; i += 4) {
-        s0 += (double)p[(i + 0) * C];
-        s1 += (double)p[(i + 1) * C];
-        s2 += (double)p[(i + 2) * C];
-        s3 += (double)p[(i + 3) * C];
+    double s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0}, s2[4] = {0, 0, 0, 0}, q2[4] = {0, 0, 0, 0};
+    if (c < C) {
+        const float *p = y + r0 * C + c;
+        int64_t i = sl;
+        for (; i + BN_SLICES < n; i += 2 * BN_SLICES) {
+            const float4 u = *reinterpret_cast<const float4 *>(p + i * C);
+            const float4 v = *reinterpret_cast<const float4 *>(p + (i + BN_SLICES) * C);
+            const double u0 = u.x, u1 = u.y, u2 = u.z, u3 = u.w, v0 = v.x, v1 = v.y, v2 = v.z, v3 = v.w;
+            s[0] += u0; q[0] = fma(u0, u0, q[0]); s[1] += u1; q[1] = fma(u1, u1, q[1]);
+            s[2] += u2; q[2] = fma(u2, u2, q[2]); s[3] += u3; q[3] = fma(u3, u3, q[3]);
+            s2[0] += v0; q2[0] = fma(v0, v0, q2[0]); s2[1] += v1; q2[1] = fma(v1, v1, q2[1]);
+            s2[2] += v2; q2[2] = fma(v2, v2, q2[2]); s2[3] += v3; q2[3] = fma(v3, v3, q2[3]);
+        }
+        if (i < n) {
+            const float4 u = *reinterpret_cast<const float4 *>(p + i * C);
+            const double u0 = u.x, u1 = u.y, u2 = u.z, u3 = u.w;
+            s[0] += u0; q[0] = fma(u0, u0, q[0]); s[1] += u1; q[1] = fma(u1, u1, q[1]);
+            s[2] += u2; q[2] = fma(u2, u2, q[2]); s[3] += u3; q[3] = fma(u3, u3, q[3]);
+        }
     }
-    for (; i < n; ++i) s0 += (double)p[i * C];
-    const double mean = n > 0 ? ((s0 + s1) + (s2 + s3)) / (double)n : 0.0;
-    s0 = s1 = s2 = s3 = 0;
-    for (i = 0; i + 4 <= n; i += 4) {
-        double d0 = (double)p[(i + 0) * C] - mean, d1 = (double)p[(i + 1) * C] - mean;
-        double d2 = (double)p[(i + 2) * C] - mean, d3 = (double)p[(i + 3) * C] - mean;
-        s0 += d0 * d0; s1 += d1 * d1; s2 += d2 * d2; s3 += d3 * d3;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        sh[0][sl][cl * 4 + k] = s[k] + s2[k];
+        sh[1][sl][cl * 4 + k] = q[k] + q2[k];
     }
-    for (; i < n; ++i) { double d = (double)p[i * C] - mean; s0 += d * d; }
-    const double var = n > 0 ? ((s0 + s1) + (s2 + s3)) / (double)n : 0.0;
-    const float a = (1.0f / sqrtf((float)var + eps)) * scale[c];
-    aff_a[(int64_t)g * C + c] = a;
-    aff_b[(int64_t)g * C + c] = offset[c] - (float)mean * a;
+    __syncthreads();
+    // 256 threads finish the block's 256 channels: slices combined in slice order (bit-stable)
+    const int ch = blockIdx.y * BN_CH4 * 4 + threadIdx.x;
+    if (ch < C) {
+        double ss = 0, qq = 0;
+#pragma unroll
+        for (int k = 0; k < BN_SLICES; ++k) { ss += sh[0][k][threadIdx.x]; qq += sh[1][k][threadIdx.x]; }
+        const double mean = n > 0 ? ss / (double)n : 0.0;
+        double var = n > 0 ? qq / (double)n - mean * mean : 0.0;
+        var = var < 0.0 ? 0.0 : var;
+        const float a = (1.0f / sqrtf((float)var + eps)) * scale[ch];
+        aff_a[(int64_t)g * C + ch] = a;
+        aff_b[(int64_t)g * C + ch] = offset[ch] - (float)mean * a;
+    }
 }
 
 // out = relu?( y*a + b )   -- materialised BN(+ReLU) (op-level entry point / odd shapes)
