@@ -21,6 +21,7 @@
 // padded per window ([window][T+2][K], zero rows at both ends) so a tap is a row offset of the
 // TMA coordinate and SAME zero padding falls out of the layout.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "ntb_gemm_tc.cuh"
 #include "ntb_tc_ptx.cuh"
@@ -53,6 +54,10 @@ struct TcParams {
     int xproj_H;           // > 0: out is the recurrence's unit-major projected-gates layout (ntb_lstm_tc.cuh)
 };
 
+// CG = 1: one CTA per tile (M = 128).  CG = 2: CTA pair (cluster of 2, tcgen05 cta_group::2, M = 256): each CTA loads
+// its own 128 A rows and HALF of the B tile, the leader issues the MMAs for both SMs, so the B operand
+// traffic per output halves -- these GEMMs are operand-bandwidth bound (hi + lo planes of both operands).
+template <int CG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
           const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
@@ -64,10 +69,13 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
 
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t *smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);     // 1024 B: swizzle-128B atoms
-    const int b_tile_bytes = p.BN * BK * 2;
+    const int b_tile_bytes = (p.BN / CG) * BK * 2;               // this CTA's share of the B tile
     const int stage_bytes = (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + b_tile_bytes);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t total_tiles = p.m_tiles * p.n_tiles;
+    const int rank = CG == 2 ? (int)cluster_ctarank() : 0;      // 0 = leader of the pair
+    const int64_t m_groups = (p.m_tiles + CG - 1) / CG;         // a work item = CG consecutive M tiles x one N tile
+    const int64_t total_tiles = m_groups * p.n_tiles;
+    const int64_t first_tile = blockIdx.x / CG, tile_step = gridDim.x / CG;
     const int kb_total = p.taps * p.k_blocks;
 
     if (warp == 0 && lane == 0) {
@@ -76,12 +84,14 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4 * CG); }
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc(&tmem_base_smem, TMEM_COLS);
+    if (warp == 2) {
+        if (CG == 2) tmem_alloc_pair(&tmem_base_smem, TMEM_COLS); else tmem_alloc(&tmem_base_smem, TMEM_COLS);
+    }
     tc_fence_before();
-    __syncthreads();
+    if (CG == 2) cluster_sync_all(); else __syncthreads();     // peer barriers are initialised before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_smem;
 
@@ -90,21 +100,32 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
             const int left = (p.taps - 1) / 2;
-            for (int64_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            for (int64_t tile = first_tile; tile < total_tiles; tile += tile_step) {
                 const int n_tile = (int)(tile % p.n_tiles);
-                const int64_t m_tile = tile / p.n_tiles;
+                const int64_t m_tile = (tile / p.n_tiles) * CG + rank;
                 for (int tap = 0; tap < p.taps; ++tap) {
                     const int row0 = (int)(m_tile * BM) + tap - left;
-                    const int brow0 = tap * p.Np + n_tile * p.BN;
+                    const int brow0 = tap * p.Np + n_tile * p.BN + rank * (p.BN / CG);
                     for (int kb = 0; kb < p.k_blocks; ++kb) {
                         mbar_wait(&empty_bar[stage], phase ^ 1);
                         uint8_t *s = smem + (size_t)stage * stage_bytes;
-                        mbar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
-                        tma_load_2d(s, &map_a_hi, &full_bar[stage], kb * BK, row0);
-                        tma_load_2d(s + A_TILE_BYTES, &map_b_hi, &full_bar[stage], kb * BK, brow0);
-                        if (p.passes == 3) {
-                            tma_load_2d(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], kb * BK, row0);
-                            tma_load_2d(s + 2 * A_TILE_BYTES + b_tile_bytes, &map_b_lo, &full_bar[stage], kb * BK, brow0);
+                        if (CG == 1) {
+                            mbar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+                            tma_load_2d(s, &map_a_hi, &full_bar[stage], kb * BK, row0);
+                            tma_load_2d(s + A_TILE_BYTES, &map_b_hi, &full_bar[stage], kb * BK, brow0);
+                            if (p.passes == 3) {
+                                tma_load_2d(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], kb * BK, row0);
+                                tma_load_2d(s + 2 * A_TILE_BYTES + b_tile_bytes, &map_b_lo, &full_bar[stage], kb * BK, brow0);
+                            }
+                        } else {
+                            // both CTAs' bytes are credited to the LEADER's full barrier
+                            if (rank == 0) mbar_expect_tx(&full_bar[stage], (uint32_t)(2 * stage_bytes));
+                            tma_load_2d_pair(s, &map_a_hi, &full_bar[stage], kb * BK, row0);
+                            tma_load_2d_pair(s + A_TILE_BYTES, &map_b_hi, &full_bar[stage], kb * BK, brow0);
+                            if (p.passes == 3) {
+                                tma_load_2d_pair(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], kb * BK, row0);
+                                tma_load_2d_pair(s + 2 * A_TILE_BYTES + b_tile_bytes, &map_b_lo, &full_bar[stage], kb * BK, brow0);
+                            }
                         }
                         if (++stage == p.stages) { stage = 0; phase ^= 1; }
                     }
@@ -113,11 +134,11 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
-            const uint32_t idesc = idesc_bf16_f32(BM, p.BN);
+        if (lane == 0 && rank == 0) {
+            const uint32_t idesc = idesc_bf16_f32(BM * CG, p.BN);
             int stage = 0; uint32_t phase = 0;
             int acc = 0; uint32_t acc_phase = 0;
-            for (int64_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            for (int64_t tile = first_tile; tile < total_tiles; tile += tile_step) {
                 mbar_wait(&acc_empty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
@@ -131,17 +152,25 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                     const uint64_t b_lo = smem_desc_sw128(s + 2 * A_TILE_BYTES + b_tile_bytes);
                     const int k16n = ((kb % p.k_blocks) == p.k_blocks - 1) ? p.k16_last : BK / 16;
                     for (int k = 0; k < k16n; ++k) {
-                        umma_f16(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_hi, k), idesc,
-                                 (kb | k) != 0);
-                        if (p.passes == 3) {
-                            umma_f16(d_tmem, desc_advance_k16(a_lo, k), desc_advance_k16(b_hi, k), idesc, 1);
-                            umma_f16(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_lo, k), idesc, 1);
+                        if (CG == 1) {
+                            umma_f16(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_hi, k), idesc, (kb | k) != 0);
+                            if (p.passes == 3) {
+                                umma_f16(d_tmem, desc_advance_k16(a_lo, k), desc_advance_k16(b_hi, k), idesc, 1);
+                                umma_f16(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_lo, k), idesc, 1);
+                            }
+                        } else {
+                            umma_f16_pair(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_hi, k), idesc, (kb | k) != 0);
+                            if (p.passes == 3) {
+                                umma_f16_pair(d_tmem, desc_advance_k16(a_lo, k), desc_advance_k16(b_hi, k), idesc, 1);
+                                umma_f16_pair(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_lo, k), idesc, 1);
+                            }
                         }
                     }
-                    umma_commit(&empty_bar[stage]);            // smem stage reusable once these MMAs retire
+                    // smem stage reusable (in both CTAs) once these MMAs retire
+                    if (CG == 1) umma_commit(&empty_bar[stage]); else umma_commit_pair(&empty_bar[stage], 3);
                     if (++stage == p.stages) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(&acc_full[acc]);                   // accumulator complete
+                if (CG == 1) umma_commit(&acc_full[acc]); else umma_commit_pair(&acc_full[acc], 3);   // accumulator complete
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
@@ -152,9 +181,9 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
         const bool vec_ok = ((p.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
         uint8_t *stage_buf = smem + (size_t)p.stages * stage_bytes + (size_t)q * 8192;   // 1024-B aligned
         int stage_it = 0;
-        for (int64_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        for (int64_t tile = first_tile; tile < total_tiles; tile += tile_step) {
             const int n_tile = (int)(tile % p.n_tiles);
-            const int64_t m_tile = tile / p.n_tiles;
+            const int64_t m_tile = (tile / p.n_tiles) * CG + rank;
             mbar_wait(&acc_full[acc], acc_phase);
             tc_fence_after();
             const int64_t prow = m_tile * BM + q * 32 + lane;       // row in the A-plane layout
@@ -205,7 +234,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                         tma_store_2d(&map_out, buf, nb, (int)(m_tile * BM) + q * 32);
                         bulk_commit_group();
                     }
-                } else if (p.xproj_H > 0) {
+                } else if (p.xproj_H > 0 && m_tile < p.m_tiles) {
                     // xproj[dir][m_tile][unit][row] float4 (i,j,f,o): a warp's 32 rows are contiguous
                     float4 *out4 = reinterpret_cast<float4 *>(p.out);
                     const int nb = n0 + c0, trow = q * 32 + lane;
@@ -248,16 +277,18 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&acc_empty[acc]);
+            if (lane == 0) {                                   // the LEADER's MMA warp owns the accumulators of both SMs
+                if (CG == 1 || rank == 0) mbar_arrive(&acc_empty[acc]); else mbar_arrive_cluster(&acc_empty[acc], 0);
+            }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
         if (p.tma_store && lane == 0) bulk_wait_group<0>();   // stores complete before smem goes away
     }
     tc_fence_before();
-    __syncthreads();
+    if (CG == 2) cluster_sync_all(); else __syncthreads();
     if (warp == 2) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, TMEM_COLS);
+        if (CG == 2) tmem_dealloc_pair(tmem_base, TMEM_COLS); else tmem_dealloc(tmem_base, TMEM_COLS);
     }
 }
 
@@ -480,20 +511,30 @@ int launch_split(cudaStream_t st, const SplitParams &sp, int64_t *launches) {
     return NTB_OK;
 }
 
+int gemm_cta_group() {
+    // NTB_GEMM_CG=1 selects the single-CTA kernel (A/B measurement); default is the CTA-pair kernel
+    static int cg = [] {
+        const char *e = getenv("NTB_GEMM_CG");
+        return (e && e[0] == '1') ? 1 : 2;
+    }();
+    return cg;
+}
+
 int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, int64_t plane_rows, int T, int pad,
                 int64_t out_rows, const float *bias, float *out, int ldo, int64_t *launches, int xproj_H = 0) {
+    const int cg = gemm_cta_group();
     CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
     NTB_TRY(make_map(&ma_hi, gs.a_hi, plane_rows, w.K, BM));
     NTB_TRY(make_map(&ma_lo, gs.a_lo, plane_rows, w.K, BM));
-    NTB_TRY(make_map(&mb_hi, w.hi, (int64_t)w.taps * w.Np, w.Kp, w.BN));
-    NTB_TRY(make_map(&mb_lo, w.lo, (int64_t)w.taps * w.Np, w.Kp, w.BN));
+    NTB_TRY(make_map(&mb_hi, w.hi, (int64_t)w.taps * w.Np, w.Kp, w.BN / cg));
+    NTB_TRY(make_map(&mb_lo, w.lo, (int64_t)w.taps * w.Np, w.Kp, w.BN / cg));
     TcParams p{};
     p.m_tiles = (plane_rows + BM - 1) / BM;
     p.BN = w.BN; p.Np = w.Np; p.N = w.N; p.n_tiles = w.Np / w.BN;
     p.taps = w.taps; p.k_blocks = (w.K + BK - 1) / BK;
     p.k16_last = ((w.K - (p.k_blocks - 1) * BK) + 15) / 16;
     p.passes = w.single_pass ? 1 : 3;
-    const int stage_bytes = (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + w.BN * BK * 2);
+    const int stage_bytes = (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + (w.BN / cg) * BK * 2);   // per CTA
     p.stages = SMEM_BUDGET / stage_bytes;
     if (p.stages > 8) p.stages = 8;
     if (p.stages < 2) return fail(NTB_EINVAL, "tcgen05 GEMM: tile does not fit shared memory%s", "");
@@ -507,12 +548,28 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     const size_t smem = (size_t)p.stages * stage_bytes + 1024 + EPI_STAGE_BYTES;
     static bool attr_set = false;
     if (!attr_set) {
-        NTB_CUDA(cudaFuncSetAttribute(k_gemm_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET + 1024 + EPI_STAGE_BYTES));
+        NTB_CUDA(cudaFuncSetAttribute(k_gemm_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET + 1024 + EPI_STAGE_BYTES));
+        NTB_CUDA(cudaFuncSetAttribute(k_gemm_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET + 1024 + EPI_STAGE_BYTES));
         attr_set = true;
     }
-    const int64_t tiles = p.m_tiles * p.n_tiles;
-    const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-    k_gemm_tc<<<grid, TC_THREADS, smem, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, mo, p);
+    if (cg == 1) {
+        const int64_t tiles = p.m_tiles * p.n_tiles;
+        const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+        k_gemm_tc<1><<<grid, TC_THREADS, smem, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, mo, p);
+    } else {
+        const int64_t items = ((p.m_tiles + 1) / 2) * p.n_tiles;            // pairs of M tiles x N tiles
+        const int64_t pairs_hw = sm_count() / 2;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(2 * (items < pairs_hw ? items : pairs_hw)));
+        cfg.blockDim = dim3(TC_THREADS);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        NTB_CUDA(cudaLaunchKernelEx(&cfg, k_gemm_tc<2>, ma_hi, ma_lo, mb_hi, mb_lo, mo, p));
+    }
     if (launches) ++*launches;
     NTB_LAUNCH_CHECK();
     return NTB_OK;
