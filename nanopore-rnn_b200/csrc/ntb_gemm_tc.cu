@@ -90,6 +90,12 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
     if (warp == 2) {
         if (CG == 2) tmem_alloc_pair(&tmem_base_smem, TMEM_COLS); else tmem_alloc(&tmem_base_smem, TMEM_COLS);
     }
+    // xproj mode: the (unused) TMA-store staging area holds the bias vector, so the epilogue's bias reads
+    // are shared-memory broadcasts instead of global loads queued behind its own stores
+    float *bias_s = reinterpret_cast<float *>(smem + (size_t)p.stages * stage_bytes);
+    const bool bias_in_smem = p.xproj_H > 0 && p.bias && p.Np * 4 <= EPI_STAGE_BYTES;
+    if (bias_in_smem)
+        for (int i = threadIdx.x; i < p.Np; i += TC_THREADS) bias_s[i] = i < p.N ? p.bias[i] : 0.0f;
     tc_fence_before();
     if (CG == 2) cluster_sync_all(); else __syncthreads();     // peer barriers are initialised before anyone signals them
     tc_fence_after();
@@ -235,22 +241,29 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                         bulk_commit_group();
                     }
                 } else if (p.xproj_H > 0 && m_tile < p.m_tiles) {
-                    // xproj[dir][m_tile][unit][row] float4 (i,j,f,o): a warp's 32 rows are contiguous
+                    // xproj[dir][m_tile][unit][row] float4 (i,j,f,o): a warp's 32 rows are contiguous.
+                    // One division per chunk; (dir, unit) then advance incrementally.
                     float4 *out4 = reinterpret_cast<float4 *>(p.out);
-                    const int nb = n0 + c0, trow = q * 32 + lane;
+                    const int nb = n0 + c0, H = p.xproj_H;
+                    int d = (nb >> 2) / H, u = (nb >> 2) - d * H;
+                    const int64_t dir_stride = p.m_tiles * (int64_t)H * BM;
+                    float4 *dst = out4 + d * dir_stride + (m_tile * H + u) * (int64_t)BM + (q * 32 + lane);
+                    int lim = (p.N < n0 + p.BN ? p.N : n0 + p.BN) - nb;       // valid columns of this chunk
+                    lim = lim > 32 ? 32 : lim;
 #pragma unroll
                     for (int i = 0; i < 32; i += 4) {
-                        const int n = nb + i;
-                        if (n < p.N && c0 + i < p.BN) {
-                            const int Q = n >> 2, d = Q / p.xproj_H, u = Q - d * p.xproj_H;
+                        if (i < lim) {
                             float4 v = make_float4(__uint_as_float(r[i]), __uint_as_float(r[i + 1]),
                                                    __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
                             if (p.bias) {
-                                const float4 b = *reinterpret_cast<const float4 *>(p.bias + n);
+                                const float4 b = bias_in_smem ? *reinterpret_cast<const float4 *>(bias_s + nb + i)
+                                                              : __ldg(reinterpret_cast<const float4 *>(p.bias + nb + i));
                                 v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
                             }
-                            out4[(((int64_t)d * p.m_tiles + m_tile) * p.xproj_H + u) * BM + trow] = v;
+                            *dst = v;
                         }
+                        dst += BM;
+                        if (++u == H) { u = 0; dst += dir_stride - (int64_t)H * BM; }
                     }
                 } else if (row_ok) {
                     const int nb = n0 + c0;
