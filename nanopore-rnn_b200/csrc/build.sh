@@ -6,5 +6,5 @@ out="$here/../libnanotensor_b200.so"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 flags=(-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17
        -Xcompiler -fPIC,-O2,-Wall,-fvisibility=hidden -shared -cudart static)
-"$NVCC" "${flags[@]}" ${NTB_PTXAS_V:+-Xptxas -v} -o "$out" "$here/ntb_api.cu" "$here/ntb_gemm_tc.cu"
+"$NVCC" "${flags[@]}" ${NTB_PTXAS_V:+-Xptxas -v} ${NTB_DEBUG_SYNC:+-DNTB_DEBUG_SYNC} -o "$out" "$here/ntb_api.cu" "$here/ntb_gemm_tc.cu"
 echo "built $out"

@@ -1,6 +1,7 @@
 // C ABI of nanotensor_b200 (include/nanotensor_b200.h): model life cycle, the chunk forward and
 // the op-level entry points.  Host-side orchestration only; the kernels live in the .cuh files.
 #include <new>
+#include <stdlib.h>
 #include <vector>
 
 #include "ntb_common.cuh"
@@ -125,7 +126,11 @@ static int launch_lstm_tc(Ctx &cx, const LstmTcParams &p) {
         attr_set = true;
     }
     dim3 grid((unsigned)p.n_tiles, 2);
-    k_lstm_recurrence_tc<<<grid, LSTM_TC_THREADS, smem, cx.st>>>(p);
+    LstmTcParams pp = p;
+    if (const char *e = getenv("NTB_LSTM_FLAGS")) pp.flags = atoi(e);   // ablation switches (ntb_lstm_tc.cuh)
+    alignas(64) CUtensorMap map_x;
+    NTB_TRY(make_map_xproj(&map_x, reinterpret_cast<const float *>(p.xproj), 2LL * p.n_tiles * p.T * p.H));
+    k_lstm_recurrence_tc<<<grid, LSTM_TC_THREADS, smem, cx.st>>>(map_x, pp);
     cx.count();
     NTB_LAUNCH_CHECK();
     return NTB_OK;

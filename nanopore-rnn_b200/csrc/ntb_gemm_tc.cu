@@ -591,6 +591,23 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
 }  // namespace
 
 // ------------------------------------------------------------------------------------------ interface
+// Projected gates as a 3-D fp32 tensor {256 floats, 2, units_total}: one (dir, m_tile, unit) slab of 128 rows x float4
+// is 2 KB = {256, 2}; a box {256, 2, 8} is one 16 KB chunk of 8 units (ntb_lstm_tc.cuh x ring), no swizzle.
+int make_map_xproj(void *map_out, const float *xproj, int64_t units_total) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return fail(NTB_ECUDA, "cuTensorMapEncodeTiled entry point not found%s", "");
+    cuuint64_t dims[3] = {256, 2, (cuuint64_t)units_total};
+    cuuint64_t strides[2] = {1024, 2048};
+    cuuint32_t box[3] = {256, 2, 8};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn((CUtensorMap *)map_out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float *>(xproj), dims, strides,
+                    box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(NTB_ECUDA, "cuTensorMapEncodeTiled (xproj) failed (%s%lld) units %lld", "", (long long)r, (long long)units_total);
+    return NTB_OK;
+}
+
 void gemm_tc_plan_weights(GemmWeights &w, int taps, int K, int N, Arena &ar) {
     w = GemmWeights();
     w.taps = taps; w.K = K; w.N = N;

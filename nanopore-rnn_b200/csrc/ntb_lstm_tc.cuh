@@ -26,13 +26,15 @@
 //   forget_bias folded -- one timestep of one tile is a contiguous 128*H*16 bytes.
 #pragma once
 #include "ntb_common.cuh"
+#include <cuda.h>
+
 #include "ntb_tc_ptx.cuh"
 
 namespace ntb {
 
 constexpr int LSTM_TC_ROWS = 128;       // windows per tile = TMEM lanes
 constexpr int LSTM_TC_THREADS = 384;    // 4 control warps + 8 epilogue warps
-constexpr int LSTM_TC_MAXCH = 7;        // chunks of 8 units per epilogue warp (13 chunks at H = 100)
+constexpr int LSTM_TC_MAXCH = 13;       // chunks of 8 units (13 at H = 100); each epilogue warp takes half a chunk
 
 struct LstmTcParams {
     const float4 *xproj;              // see layout above
@@ -44,16 +46,19 @@ struct LstmTcParams {
     int64_t n_windows;
     int n_tiles;                      // ceil(n_windows / 128)
     int T, H, Hp;                     // Hp = H rounded up to 16
+    int flags;                        // debug/ablation: 1 = no x ring (direct global loads), 2 = no slice overlap
 };
 
 static inline bool lstm_tc_supported(int H) {
     const int Hp = (int)align_up(H, 16);
     return H >= 16 && H % 4 == 0 && 4 * H + Hp <= 512 && (4 * H <= 256 || (4 * H - 256) % 16 == 0) &&
-           (H + 7) / 8 <= 2 * LSTM_TC_MAXCH;
+           (H + 7) / 8 <= LSTM_TC_MAXCH;
 }
+constexpr int LSTM_TC_XSLOTS = 3;                  // ring of projected-gate chunks (8 units x 128 rows x float4)
+constexpr int LSTM_TC_XSLOT_BYTES = 8 * LSTM_TC_ROWS * 16;
 static inline int64_t lstm_tc_smem_bytes(int H) {
     const int Hp = (int)align_up(H, 16);
-    return 2LL * 4 * H * Hp * 2 + 128;
+    return align_up(2LL * 4 * H * Hp * 2, 128) + LSTM_TC_XSLOTS * LSTM_TC_XSLOT_BYTES + 128;
 }
 static inline int64_t lstm_tc_whh_elems(int H) { return 2LL * align_up(H, 16) * 4 * H; }   // per plane, both dirs
 
@@ -112,16 +117,21 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {   // a -> lo
     return *reinterpret_cast<uint32_t *>(&v);
 }
 
-__global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const LstmTcParams p) {
+__global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const __grid_constant__ CUtensorMap map_x,
+                                                                               const LstmTcParams p) {
     using namespace ptx;
-    extern __shared__ __align__(128) uint8_t smem_w[];          // [2 planes][Hp/8][4H][8] bf16
-    __shared__ uint64_t d_full, h_ready;
+    extern __shared__ __align__(128) uint8_t smem_w[];          // [2 planes][Hp/8][4H][8] bf16, then the x ring
+    __shared__ uint64_t d_full[2], h_ready, x_full[LSTM_TC_XSLOTS], x_empty[LSTM_TC_XSLOTS];
     __shared__ uint32_t tmem_base_smem;
 
     const int H = p.H, Hp = p.Hp, T = p.T, N = 4 * H;
     const int dir = blockIdx.y, tile = blockIdx.x;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t plane_bytes = (uint32_t)N * Hp * 2;
+    uint8_t *xring = smem_w + ((2 * plane_bytes + 127u) & ~127u);
+    const int n_chunks = (H + 7) >> 3;
+    const int N1 = N < 256 ? N : 256, N2 = N - N1;
+    const bool two = N2 > 0;                                   // second N slice (gate columns >= 256)
 
     // ---- one-time setup: W_hh^T hi/lo planes -> smem, barriers, TMEM
     {
@@ -136,8 +146,11 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
         fence_proxy_async_smem();          // generic-proxy stores -> visible to tcgen05.mma reads
     }
     if (threadIdx.x == 0) {
-        mbar_init(&d_full, 1);
+        prefetch_tmap(&map_x);
+        mbar_init(&d_full[0], 1);
+        mbar_init(&d_full[1], 1);
         mbar_init(&h_ready, 8);
+        for (int i = 0; i < LSTM_TC_XSLOTS; ++i) { mbar_init(&x_full[i], 1); mbar_init(&x_empty[i], 8); }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(&tmem_base_smem, 512);
@@ -148,22 +161,20 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
     const uint32_t a_hi_col = (uint32_t)N, a_lo_col = (uint32_t)(N + Hp / 2);
     const int64_t m_tiles = (int64_t)p.n_tiles * T;
     const int64_t step_f4 = (int64_t)H * LSTM_TC_ROWS;           // float4 per (tile, t, dir)
+    const float4 *xtile = p.xproj + ((int64_t)dir * m_tiles + (int64_t)tile * T) * step_f4;
 
     if (warp == 0) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
-            const int N1 = N < 256 ? N : 256, N2 = N - N1;
-            const uint32_t idesc1 = idesc_bf16_f32(128, N1), idesc2 = idesc_bf16_f32(128, N2 > 0 ? N2 : 16);
+            const uint32_t idesc1 = idesc_bf16_f32(128, N1), idesc2 = idesc_bf16_f32(128, two ? N2 : 16);
             const uint32_t lbo = (uint32_t)N * 16, sbo = 128;     // K-chunk stride, 8-row group stride
             const uint32_t w_hi = smem_u32(smem_w), w_lo = w_hi + plane_bytes;
             const int k16n = Hp / 16;
-            const float4 *xp = p.xproj + ((int64_t)dir * m_tiles + (int64_t)tile * T) * step_f4;
             for (int s = 0; s < T; ++s) {
-                mbar_wait(&h_ready, (uint32_t)(s & 1));
+                mbar_wait(&h_ready, (uint32_t)(s & 1), 1000 + s);
                 tc_fence_after();
                 for (int half = 0; half < 2; ++half) {
-                    const int Nn = half ? N2 : N1;
-                    if (Nn <= 0) break;
+                    if (half && !two) break;
                     const uint32_t d = tmem_base + (uint32_t)(half * 256);
                     const uint32_t idesc = half ? idesc2 : idesc1;
                     const uint32_t row_off = (uint32_t)(half * 256 / 8) * 128;
@@ -177,102 +188,148 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
                         umma_f16_ts(d, al, bh, idesc, 1);
                         umma_f16_ts(d, ah, bl, idesc, 1);
                     }
+                    if (!(p.flags & 2)) umma_commit(&d_full[half]);   // slice 0 goes to the epilogue while slice 1 still runs
                 }
-                umma_commit(&d_full);
+                if (p.flags & 2) { umma_commit(&d_full[0]); if (two) umma_commit(&d_full[1]); }
                 // next step's projected gates towards L2 while this step computes
-                if (s + 1 < T) {
+                if (s + 1 < T && !(p.flags & 16)) {
                     const int tn = dir ? T - 2 - s : s + 1;
-                    const char *g = reinterpret_cast<const char *>(xp + (int64_t)tn * step_f4);
+                    const char *g = reinterpret_cast<const char *>(xtile + (int64_t)tn * step_f4);
                     const uint32_t bytes = (uint32_t)step_f4 * 16, piece = (bytes / 4) & ~15u;
                     for (int q = 0; q < 4; ++q)
                         bulk_prefetch_l2(g + (size_t)q * piece, q == 3 ? bytes - 3 * piece : piece);
                 }
             }
         }
+    } else if (warp == 1) {
+        // ===================== x producer: projected-gate chunks -> smem ring (bulk async copies) ==========
+        if (lane == 0 && !(p.flags & 1)) {
+            uint32_t g = 0;
+            for (int s = 0; s < T; ++s) {
+                const int t = dir ? T - 1 - s : s;
+                const float4 *xs = xtile + (int64_t)t * step_f4;
+                for (int c = 0; c < n_chunks; ++c, ++g) {
+                    const uint32_t slot = g % LSTM_TC_XSLOTS, ph = (g / LSTM_TC_XSLOTS) & 1;
+                    mbar_wait(&x_empty[slot], ph ^ 1, 2000 + s);
+                    const int units = H - 8 * c < 8 ? H - 8 * c : 8;
+                    const uint32_t bytes = (uint32_t)units * LSTM_TC_ROWS * 16;
+                    if (p.flags & 8) {
+                        mbar_arrive(&x_full[slot]);
+                    } else if (p.flags & 32) {
+                        mbar_expect_tx(&x_full[slot], bytes);
+                        bulk_load_1d(xring + slot * LSTM_TC_XSLOT_BYTES, xs + (int64_t)c * 8 * LSTM_TC_ROWS, bytes, &x_full[slot]);
+                    } else {
+                        // TMA box {256 floats, 2, 8 units}: always 16 KB (a short last chunk over-reads the next
+                        // slab / zero-fills past the end; those units are never used)
+                        mbar_expect_tx(&x_full[slot], (uint32_t)LSTM_TC_XSLOT_BYTES);
+                        const int64_t unit0 = ((int64_t)dir * m_tiles + (int64_t)tile * T + t) * H + c * 8;
+                        tma_load_3d(xring + slot * LSTM_TC_XSLOT_BYTES, &map_x, &x_full[slot], 0, 0, (int)unit0);
+                    }
+                }
+            }
+        }
     } else if (warp >= 4) {
         // ===================== gate epilogue =====================
-        const int q = warp & 3, par = (warp - 4) >> 2;
+        // thread = one window (TMEM lane); the two warps of a lane quarter split every 8-unit chunk in
+        // halves (4 units = 16 accumulator columns each), so all 8 warps consume every ring slot in order
+        // (parity waits stay unambiguous) and share the MUFU work evenly.
+        const int q = warp & 3, half = (warp - 4) >> 2;
         const int r = q * 32 + lane;
         const int64_t w = (int64_t)tile * LSTM_TC_ROWS + r;
         const bool exists = w < p.n_windows;
         int len = exists ? p.lens[w] : 0;
         len = len > T ? T : len;
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
-        const int n_chunks = (H + 7) >> 3;
-        float cst[LSTM_TC_MAXCH][8];
+        float cst[LSTM_TC_MAXCH][4];
 #pragma unroll
         for (int ci = 0; ci < LSTM_TC_MAXCH; ++ci)
 #pragma unroll
-            for (int u = 0; u < 8; ++u) cst[ci][u] = 0.0f;
+            for (int u = 0; u < 4; ++u) cst[ci][u] = 0.0f;
         // h_0 = 0: clear the A columns (hi and lo, pad units included)
-        if (par == 0)
+        if (half == 0)
             for (int c4 = 0; c4 < Hp; c4 += 4) tmem_st_32x4(lane_base + a_hi_col + (uint32_t)c4, 0u, 0u, 0u, 0u);
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&h_ready);
 
-        const float4 *xrow = p.xproj + ((int64_t)dir * m_tiles + (int64_t)tile * T) * step_f4 + r;
+        uint32_t g = 0;                                          // ring position (chunks consumed so far)
         for (int s = 0; s < T; ++s) {
             const int t = dir ? T - 1 - s : s;
             const bool active = t < len;
-            const float4 *xs = xrow + (int64_t)t * step_f4;
-            float4 xv[8];
-            // first chunk's projected gates: independent of the MMA, issued before the wait
-            {
-                const int u0 = par * 8;
-#pragma unroll
-                for (int u = 0; u < 8; ++u)
-                    xv[u] = (u0 + u < H) ? __ldg(xs + (int64_t)(u0 + u) * LSTM_TC_ROWS) : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-            mbar_wait(&d_full, (uint32_t)(s & 1));
-            tc_fence_after();
             float *orow = p.out + (w * T + t) * (int64_t)p.ldo + dir * H;
+            uint32_t dh[8][2], dl[8][2];                         // h of the slice-0 chunks, written once slice 1 is done
+            mbar_wait(&d_full[0], (uint32_t)(s & 1), 3000 + s);
+            tc_fence_after();
 #pragma unroll
-            for (int ci = 0; ci < LSTM_TC_MAXCH; ++ci) {
-                const int c = 2 * ci + par;
-                if (c < n_chunks) {
-                    uint32_t acc[32];
-                    tmem_ld_32x32(lane_base + (uint32_t)(32 * c), acc);
-                    tmem_ld_wait();
-                    float4 xn[8];
-                    const int un0 = (c + 2) * 8;
-                    if (c + 2 < n_chunks) {
-#pragma unroll
-                        for (int u = 0; u < 8; ++u)
-                            xn[u] = (un0 + u < H) ? __ldg(xs + (int64_t)(un0 + u) * LSTM_TC_ROWS)
-                                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int c = 0; c < LSTM_TC_MAXCH; ++c) {
+                if (c == 8) {
+                    // chunks >= 8 live in N slice 1; once it is complete no MMA reads h_{t-1} any more,
+                    // so the deferred h_t of the slice-0 chunks may overwrite the A columns
+                    if (two) {
+                        mbar_wait(&d_full[1], (uint32_t)(s & 1), 4000 + s);
+                        tc_fence_after();
                     }
-                    float hv[8];
 #pragma unroll
-                    for (int u = 0; u < 8; ++u) {
-                        float cc = cst[ci][u], hh;
+                    for (int k = 0; k < 8; ++k) {
+                        if (k < n_chunks) {
+                            tmem_st_32x2(lane_base + a_hi_col + (uint32_t)(4 * k + 2 * half), dh[k][0], dh[k][1]);
+                            tmem_st_32x2(lane_base + a_lo_col + (uint32_t)(4 * k + 2 * half), dl[k][0], dl[k][1]);
+                        }
+                    }
+                }
+                if (c < n_chunks) {
+                    const int u0 = c * 8 + half * 4;             // this warp's 4 units of the chunk
+                    const uint32_t slot = g % LSTM_TC_XSLOTS, ph = (g / LSTM_TC_XSLOTS) & 1;
+                    ++g;
+                    float4 xv[4];
+                    if (p.flags & 1) {
+                        const float4 *xg = xtile + (int64_t)t * step_f4 + (int64_t)u0 * LSTM_TC_ROWS + r;
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            xv[u] = (u0 + u < H) ? __ldg(xg + u * LSTM_TC_ROWS) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    } else {
+                        mbar_wait(&x_full[slot], ph, 5000 + s);
+                        const float4 *xsm = reinterpret_cast<const float4 *>(xring + slot * LSTM_TC_XSLOT_BYTES) +
+                                            half * 4 * LSTM_TC_ROWS + r;
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            xv[u] = (u0 + u < H) ? xsm[u * LSTM_TC_ROWS] : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                    uint32_t acc[16];
+                    tmem_ld_32x16(lane_base + (uint32_t)(32 * c + 16 * half), acc);
+                    tmem_ld_wait();
+                    float hv[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        float cc = cst[c][u], hh;
                         lstm_cell_update(__uint_as_float(acc[4 * u + 0]) + xv[u].x, __uint_as_float(acc[4 * u + 1]) + xv[u].y,
                                          __uint_as_float(acc[4 * u + 2]) + xv[u].z, __uint_as_float(acc[4 * u + 3]) + xv[u].w,
                                          cc, hh);
-                        const bool on = active && (c * 8 + u < H);
-                        cst[ci][u] = on ? cc : cst[ci][u];
+                        const bool on = active && (u0 + u < H);
+                        cst[c][u] = on ? cc : cst[c][u];
                         hv[u] = on ? hh : 0.0f;
                     }
-                    uint32_t ph[4], pl[4];
+                    if (!(p.flags & 1)) {
+                        // every lane has consumed its x values (data dependence) -> the slot may be refilled
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&x_empty[slot]);
+                    }
+                    uint32_t ph2[2], pl2[2];
 #pragma unroll
-                    for (int m = 0; m < 4; ++m) {
-                        ph[m] = pack_bf16x2(hv[2 * m], hv[2 * m + 1]);
-                        const float l0 = hv[2 * m] - __uint_as_float(ph[m] << 16);
-                        const float l1 = hv[2 * m + 1] - __uint_as_float(ph[m] & 0xffff0000u);
-                        pl[m] = pack_bf16x2(l0, l1);
+                    for (int m = 0; m < 2; ++m) {
+                        ph2[m] = pack_bf16x2(hv[2 * m], hv[2 * m + 1]);
+                        const float l0 = hv[2 * m] - __uint_as_float(ph2[m] << 16);
+                        const float l1 = hv[2 * m + 1] - __uint_as_float(ph2[m] & 0xffff0000u);
+                        pl2[m] = pack_bf16x2(l0, l1);
                     }
-                    tmem_st_32x4(lane_base + a_hi_col + (uint32_t)(4 * c), ph[0], ph[1], ph[2], ph[3]);
-                    tmem_st_32x4(lane_base + a_lo_col + (uint32_t)(4 * c), pl[0], pl[1], pl[2], pl[3]);
-                    if (exists) {
-                        *reinterpret_cast<float4 *>(orow + c * 8) = make_float4(hv[0], hv[1], hv[2], hv[3]);
-                        if (c * 8 + 4 < H)
-                            *reinterpret_cast<float4 *>(orow + c * 8 + 4) = make_float4(hv[4], hv[5], hv[6], hv[7]);
+                    if (c < 8) {
+                        dh[c][0] = ph2[0]; dh[c][1] = ph2[1]; dl[c][0] = pl2[0]; dl[c][1] = pl2[1];
+                    } else {
+                        tmem_st_32x2(lane_base + a_hi_col + (uint32_t)(4 * c + 2 * half), ph2[0], ph2[1]);
+                        tmem_st_32x2(lane_base + a_lo_col + (uint32_t)(4 * c + 2 * half), pl2[0], pl2[1]);
                     }
-                    if (c + 2 < n_chunks) {
-#pragma unroll
-                        for (int u = 0; u < 8; ++u) xv[u] = xn[u];
-                    }
+                    if (exists && u0 < H) *reinterpret_cast<float4 *>(orow + u0) = make_float4(hv[0], hv[1], hv[2], hv[3]);
                 }
             }
             tmem_st_wait();

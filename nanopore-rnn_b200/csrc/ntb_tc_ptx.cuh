@@ -4,6 +4,7 @@
 #pragma once
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <stdio.h>
 
 namespace ntb {
 namespace ptx {
@@ -37,11 +38,19 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint64_t *bar, uint32_t parity
     return ok;
 }
 // Bounded wait: a protocol bug becomes a launch failure (trap) after ~2 s instead of a hung GPU.
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity, int tag = 0) {
     if (mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
     while (!mbar_try_wait(bar, parity)) {
+#ifdef NTB_DEBUG_SYNC
+        if (clock64() - t0 > 200000000LL) {   // debug build: report the stuck wait and carry on
+            printf("mbar timeout tag %d block (%d,%d) thread %d parity %u\n", tag, blockIdx.x, blockIdx.y, threadIdx.x, parity);
+            return;
+        }
+#else
+        (void)tag;
         if (clock64() - t0 > 4000000000LL) __trap();
+#endif
     }
 }
 
@@ -71,6 +80,19 @@ __device__ __forceinline__ void bulk_wait_group_read() {   // <= N groups still 
 template <int N>
 __device__ __forceinline__ void bulk_wait_group() {
     asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+// 1D bulk copy global -> shared, completes on an mbarrier (complete_tx::bytes); size % 16 == 0
+__device__ __forceinline__ void bulk_load_1d(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void *dst, const void *tmap, uint64_t *bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
 }
 // generic-proxy writes (st.shared) -> visible to the async proxy (tcgen05.mma / TMA reads)
 __device__ __forceinline__ void fence_proxy_async_smem() {
@@ -127,6 +149,9 @@ __device__ __forceinline__ void tmem_st_32x4(uint32_t taddr, uint32_t r0, uint32
     asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(r0), "r"(r1),
                  "r"(r2), "r"(r3)
                  : "memory");
+}
+__device__ __forceinline__ void tmem_st_32x2(uint32_t taddr, uint32_t r0, uint32_t r1) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(taddr), "r"(r0), "r"(r1) : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
