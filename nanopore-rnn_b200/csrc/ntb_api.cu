@@ -372,8 +372,12 @@ extern "C" int64_t ntb_model_workspace_bytes(const ntb_model *m, int64_t n_windo
 }
 
 // ====================================================================== the forward
+// in_planes: the operand planes already hold this layer's input (written by the previous layer's combine).
+// want_layout: operand-plane layout the NEXT layer consumes (0 none, 1 plain rows, 2 time-major tiles); when the
+// layer can emit it, the fp32 output is skipped and *got_layout is set.
 static int residual_forward(Ctx &cx, ntb_model *m, const LayerDev &ld, const float *in, int Cin, int64_t n,
-                            const int32_t *group_off, int64_t n_groups, Workspace &ws, float *out) {
+                            const int32_t *group_off, int64_t n_groups, Workspace &ws, float *out, bool in_planes,
+                            int want_layout, int *got_layout) {
     const int C = ld.size, T = m->T;
     const int64_t rows = n * T;
     float *ys[4] = {ws.y1, ws.y2a, ws.y2b, ws.y2a};   // conv2c reuses conv2a's buffer
@@ -381,7 +385,17 @@ static int residual_forward(Ctx &cx, ntb_model *m, const LayerDev &ld, const flo
     const int src_of[4] = {-1, -1, 1, 2};             // conv2b reads bn+relu(conv2a), conv2c reads bn+relu(conv2b)
     float *aa[4] = {ws.aff[0], ws.aff[2], ws.aff[4], ws.aff[6]};
     float *bb[4] = {ws.aff[1], ws.aff[3], ws.aff[5], ws.aff[7]};
-    for (int c = 0; c < 4; ++c) {
+    const bool tc_tail = ws.gs.valid && ld.convw[2].valid && ld.convw[3].valid && C % 8 == 0;
+    // Cin = 1: conv1 / conv2a are outer products folded into per-group affines of x (k_k1_affine)
+    const bool k1 = Cin == 1 && tc_tail;
+    if (k1) {
+        K1Conv c0{ld.conv[0], ld.bn_scale[0], ld.bn_offset[0], aa[0], bb[0]};
+        K1Conv c1{ld.conv[1], ld.bn_scale[1], ld.bn_offset[1], aa[1], bb[1]};
+        k_k1_affine<<<(unsigned)n_groups, 256, 0, cx.st>>>(in, T, group_off, C, 1e-5f, c0, c1);
+        cx.count();
+        NTB_LAUNCH_CHECK();
+    }
+    for (int c = k1 ? 2 : 0; c < 4; ++c) {
         if (c == 3) { aa[3] = ws.aff[2]; bb[3] = ws.aff[3]; }   // conv2a's affine is dead by now
         const float *A = src_of[c] < 0 ? in : ys[src_of[c]];
         const int K = src_of[c] < 0 ? Cin : C;
@@ -389,9 +403,10 @@ static int residual_forward(Ctx &cx, ntb_model *m, const LayerDev &ld, const flo
         const float *fb = src_of[c] < 0 ? nullptr : bb[src_of[c]];
         if (ld.convw[c].valid && ws.gs.valid) {
             // conv1 and conv2a are both 1x1 convs of the layer input: one operand split serves both
-            const bool reuse = c == 1 && ld.convw[0].valid;
-            NTB_TRY(gemm_tc_conv(cx.st, A, K, rows, T, fa, fb, ws.win_group, src_of[c] >= 0, ld.convw[c], ys[c], C,
-                                 ws.gs, &cx.launches, reuse));
+            const bool reuse = (c == 1 && ld.convw[0].valid) || (c == 0 && in_planes);
+            const bool expand = k1 && c == 2;
+            NTB_TRY(gemm_tc_conv(cx.st, expand ? in : A, K, rows, T, fa, fb, ws.win_group, src_of[c] >= 0, ld.convw[c],
+                                 ys[c], C, ws.gs, &cx.launches, reuse, expand));
         } else {
             ConvGemmParams p{};
             p.A = A; p.lda = K; p.W = ld.conv[c]; p.bias = nullptr;
@@ -402,6 +417,13 @@ static int residual_forward(Ctx &cx, ntb_model *m, const LayerDev &ld, const flo
         }
         if (ld.bn_scale[c])
             NTB_TRY(launch_bn_stats(cx, ys[c], C, T, group_off, n_groups, ld.bn_scale[c], ld.bn_offset[c], aa[c], bb[c]));
+    }
+    *got_layout = 0;
+    if (tc_tail) {
+        const bool bn1 = k1 || ld.bn_scale[0];
+        *got_layout = want_layout;
+        return gemm_tc_combine(cx.st, k1 ? in : ws.y1, k1, bn1 ? aa[0] : nullptr, bn1 ? bb[0] : nullptr, ys[3], aa[3], bb[3],
+                               ws.win_group, T, C, rows, want_layout ? nullptr : out, &ws.gs, want_layout, &cx.launches);
     }
     const int64_t total4 = rows * C / 4;
     k_residual_combine<<<elementwise_grid(total4, m->sm_count), 256, 0, cx.st>>>(
@@ -444,18 +466,28 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
     const size_t nl = m->layers.size();
     const bool small_c = m->C <= 8;
     const LayerDev *fused_fnn = nullptr;
+    int planes = 0;   // the GEMM operand planes hold the current activation: 1 plain rows, 2 time-major tiles
     for (size_t li = 0; li < nl; ++li) {
         const LayerDev &ld = m->layers[li];
         float *out = ws.act[flip];
         if (ld.type == NTB_LAYER_RESIDUAL) {
             NTB_TRY(mark(0));
-            NTB_TRY(residual_forward(cx, m, ld, cur, dim, n, group_off, n_groups, ws, out));
+            int want = 0;
+            if (li + 1 < nl && ws.gs.valid) {
+                const LayerDev &nx = m->layers[li + 1];
+                if (nx.type == NTB_LAYER_RESIDUAL && nx.convw[0].valid && nx.convw[1].valid) want = 1;
+                else if (nx.type == NTB_LAYER_BLSTM && nx.tc_rec) want = 2;
+            }
+            int got = 0;
+            NTB_TRY(residual_forward(cx, m, ld, cur, dim, n, group_off, n_groups, ws, out, planes == 1, want, &got));
+            planes = got;
             dim = ld.size;
         } else if (ld.type == NTB_LAYER_BLSTM) {
             NTB_TRY(mark(1));
             const int N = 8 * ld.Hp;
             if (ld.tc_rec && ws.gs.valid) {
-                NTB_TRY(gemm_tc_run_xproj(cx.st, cur, dim, n, T, ld.wihw, ld.bias, ws.xproj, ld.size, ws.gs, &cx.launches));
+                NTB_TRY(gemm_tc_run_xproj(cx.st, cur, dim, n, T, ld.wihw, ld.bias, ws.xproj, ld.size, ws.gs, &cx.launches,
+                                          planes == 2));
                 NTB_TRY(mark(2));
                 LstmTcParams p{};
                 p.xproj = (const float4 *)ws.xproj; p.whh_hi = ld.whh_hi; p.whh_lo = ld.whh_lo; p.lens = lens;
@@ -471,6 +503,7 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
                 NTB_TRY(launch_lstm(cx, p, m->sm_count));
             }
             dim = 2 * ld.size;
+            planes = 0;
         } else {   // chiron_fnn
             NTB_TRY(mark(3));
             if (li + 1 == nl && small_c) { fused_fnn = &ld; continue; }   // fused into the readout

@@ -319,6 +319,7 @@ struct SplitParams {
     __nv_bfloat16 *hi, *lo;  // [plane_rows][K]
     int64_t plane_rows;
     int perm;                // 1: plane row (tile*T + t)*128 + wl <- source row (tile*128 + wl)*T + t
+    int expand;              // 1: A is [rows] (a Cin = 1 conv folded into the affine): v[c] = A[r] * a[g][c] + b[g][c]
 };
 
 __global__ void __launch_bounds__(256) k_split_bf16(const SplitParams p) {
@@ -401,9 +402,15 @@ __global__ void __launch_bounds__(256) k_split_bf16_window(const SplitParams p) 
         const int tt = p.pad ? i - 1 : i;
         float v[8];
         if (tt >= 0 && tt < p.T) {
-            const float4 x0 = *reinterpret_cast<const float4 *>(src + (int64_t)tt * p.lda);
-            const float4 x1 = *reinterpret_cast<const float4 *>(src + (int64_t)tt * p.lda + 4);
-            v[0] = x0.x; v[1] = x0.y; v[2] = x0.z; v[3] = x0.w; v[4] = x1.x; v[5] = x1.y; v[6] = x1.z; v[7] = x1.w;
+            if (p.expand) {
+                const float xv = __ldg(p.A + w * p.T + tt);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = xv;
+            } else {
+                const float4 x0 = *reinterpret_cast<const float4 *>(src + (int64_t)tt * p.lda);
+                const float4 x1 = *reinterpret_cast<const float4 *>(src + (int64_t)tt * p.lda + 4);
+                v[0] = x0.x; v[1] = x0.y; v[2] = x0.z; v[3] = x0.w; v[4] = x1.x; v[5] = x1.y; v[6] = x1.z; v[7] = x1.w;
+            }
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 v[j] = fmaf(v[j], a[j], b[j]);
@@ -418,6 +425,82 @@ __global__ void __launch_bounds__(256) k_split_bf16_window(const SplitParams p) 
         for (int j = 0; j < 8; ++j) ptx::split_bf16(v[j], h[j], l[j]);
         *reinterpret_cast<uint4 *>(p.hi + (pr0 + i) * p.K + c) = *reinterpret_cast<const uint4 *>(h);
         if (p.lo) *reinterpret_cast<uint4 *>(p.lo + (pr0 + i) * p.K + c) = *reinterpret_cast<const uint4 *>(l);
+    }
+}
+
+// residual_layer tail (network.py:398-399)  out = relu( bn?(branch1) + bn(conv2c) )  emitted directly as
+// the NEXT GEMM's bf16 hi/lo operand planes (plain rows for the next residual layer's 1x1 convs, time-major
+// 128-window tiles for the LSTM projection) and/or as fp32.  8 channels per thread, one plane row per
+// K/8 threads.  y1_scalar: branch1 is a Cin = 1 conv folded into its affine (y1[r] * a1[g][c] + b1[g][c]).
+struct CombineParams {
+    const float *y1; int y1_scalar;
+    const float *a1, *b1;            // [n_groups][C] or null (branch1 without BN)
+    const float *y2, *a2, *b2;
+    const int32_t *win_group;
+    int T, C;
+    int64_t rows;                    // source rows = n_windows * T
+    float *out;                      // fp32 [rows][C] or null
+    __nv_bfloat16 *hi, *lo;          // planes or null
+    int64_t plane_rows;              // = rows unless perm (whole 128-window tiles)
+    int perm;
+};
+
+__global__ void __launch_bounds__(256) k_combine_split(const CombineParams p) {
+    const int K8 = p.C >> 3;
+    const int64_t total = p.plane_rows * K8;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t pr = i / K8;
+        const int c = (int)(i - pr * K8) << 3;
+        int64_t r = pr, w;
+        if (p.perm) {
+            const int64_t mt = pr >> 7;
+            const int wl = (int)(pr & 127);
+            const int64_t tile = mt / p.T;
+            const int t = (int)(mt - tile * p.T);
+            w = tile * 128 + wl;
+            r = w * p.T + t;
+        } else {
+            w = pr / p.T;
+        }
+        float v[8];
+        if (r < p.rows) {
+            const int g = p.win_group[w];
+            const float *a2 = p.a2 + (int64_t)g * p.C + c, *b2 = p.b2 + (int64_t)g * p.C + c;
+            const float4 y0 = *reinterpret_cast<const float4 *>(p.y2 + r * p.C + c);
+            const float4 y1 = *reinterpret_cast<const float4 *>(p.y2 + r * p.C + c + 4);
+            const float yy[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+            float u[8];
+            if (p.y1_scalar) {
+                const float xv = __ldg(p.y1 + r);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) u[j] = xv;
+            } else {
+                const float4 u0 = *reinterpret_cast<const float4 *>(p.y1 + r * p.C + c);
+                const float4 u1 = *reinterpret_cast<const float4 *>(p.y1 + r * p.C + c + 4);
+                u[0] = u0.x; u[1] = u0.y; u[2] = u0.z; u[3] = u0.w; u[4] = u1.x; u[5] = u1.y; u[6] = u1.z; u[7] = u1.w;
+            }
+            if (p.a1) {
+                const float *a1 = p.a1 + (int64_t)g * p.C + c, *b1 = p.b1 + (int64_t)g * p.C + c;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) u[j] = u[j] * a1[j] + b1[j];
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = fmaxf(u[j] + (yy[j] * a2[j] + b2[j]), 0.0f);
+            if (p.out) {
+                *reinterpret_cast<float4 *>(p.out + r * p.C + c) = make_float4(v[0], v[1], v[2], v[3]);
+                *reinterpret_cast<float4 *>(p.out + r * p.C + c + 4) = make_float4(v[4], v[5], v[6], v[7]);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = 0.0f;
+        }
+        if (p.hi) {
+            __align__(16) __nv_bfloat16 h[8], l[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ptx::split_bf16(v[j], h[j], l[j]);
+            *reinterpret_cast<uint4 *>(p.hi + pr * p.C + c) = *reinterpret_cast<const uint4 *>(h);
+            *reinterpret_cast<uint4 *>(p.lo + pr * p.C + c) = *reinterpret_cast<const uint4 *>(l);
+        }
     }
 }
 
@@ -663,7 +746,8 @@ int gemm_tc_run(cudaStream_t st, const float *A, int lda, int64_t rows, const Ge
 }
 
 int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, const GemmWeights &w,
-                      const float *bias, float *xproj, int H, const GemmScratch &gs, int64_t *launches) {
+                      const float *bias, float *xproj, int H, const GemmScratch &gs, int64_t *launches,
+                      bool planes_ready) {
     const int64_t n_tiles = (n_windows + BM - 1) / BM;
     const int64_t plane_rows = n_tiles * BM * T;
     if (!w.valid || !gs.valid || plane_rows > gs.rows_cap || w.K > gs.kp_cap || (lda & 3) || w.taps != 1 ||
@@ -673,13 +757,13 @@ int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_window
     SplitParams sp{};
     sp.A = A; sp.lda = lda; sp.rows = n_windows * T; sp.K = w.K; sp.T = T; sp.relu = 0; sp.pad = 0; sp.perm = 1;
     sp.hi = gs.a_hi; sp.lo = w.single_pass ? nullptr : gs.a_lo; sp.plane_rows = plane_rows;
-    NTB_TRY(launch_split(st, sp, launches));
+    if (!planes_ready) NTB_TRY(launch_split(st, sp, launches));   // else: the producer wrote the planes itself
     return launch_gemm(st, w, gs, plane_rows, 1, 0, plane_rows, bias, xproj, 0, launches, H);
 }
 
 int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, const float *aff_a,
                  const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
-                 int ldo, const GemmScratch &gs, int64_t *launches, bool reuse_planes) {
+                 int ldo, const GemmScratch &gs, int64_t *launches, bool reuse_planes, bool expand) {
     const int pad = w.taps == 3;
     const int64_t windows = rows / T;
     const int64_t plane_rows = pad ? windows * (T + 2) : rows;
@@ -688,10 +772,37 @@ int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, co
                     (long long)K);
     SplitParams sp{};
     sp.A = A; sp.lda = K; sp.rows = rows; sp.K = K; sp.aff_a = aff_a; sp.aff_b = aff_b; sp.win_group = win_group;
-    sp.T = T; sp.relu = relu_in; sp.pad = pad;
+    sp.T = T; sp.relu = relu_in; sp.pad = pad; sp.expand = expand ? 1 : 0;
+    if (expand) sp.lda = 1;
     sp.hi = gs.a_hi; sp.lo = w.single_pass ? nullptr : gs.a_lo; sp.plane_rows = plane_rows;
     if (!reuse_planes) NTB_TRY(launch_split(st, sp, launches));   // else: the previous conv split the same input
     return launch_gemm(st, w, gs, plane_rows, T, pad, rows, nullptr, out, ldo, launches);
+}
+
+int gemm_tc_combine(cudaStream_t st, const float *y1, bool y1_scalar, const float *a1, const float *b1,
+                    const float *y2, const float *a2, const float *b2, const int32_t *win_group, int T, int C,
+                    int64_t rows, float *out, const GemmScratch *planes, int layout, int64_t *launches) {
+    if (C % 8 || rows % T) return fail(NTB_EINVAL, "combine: C %% 8 and whole windows required%s", "");
+    CombineParams p{};
+    p.y1 = y1; p.y1_scalar = y1_scalar ? 1 : 0; p.a1 = a1; p.b1 = b1; p.y2 = y2; p.a2 = a2; p.b2 = b2;
+    p.win_group = win_group; p.T = T; p.C = C; p.rows = rows; p.out = out;
+    p.plane_rows = rows;
+    if (planes && layout) {
+        p.perm = layout == 2;
+        if (p.perm) p.plane_rows = align_up(rows / T, BM) * T;
+        if (!planes->valid || p.plane_rows > planes->rows_cap || C > planes->kp_cap)
+            return fail(NTB_EINVAL, "combine: operand planes too small (rows %s%lld)", "", (long long)p.plane_rows);
+        p.hi = planes->a_hi; p.lo = planes->a_lo;
+    }
+    const int64_t total = p.plane_rows * (C >> 3);
+    int64_t blocks = (total + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    k_combine_split<<<(unsigned)blocks, 256, 0, st>>>(p);
+    if (launches) ++*launches;
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
 }
 
 }  // namespace ntb

@@ -28,11 +28,18 @@ int gemm_tc_run(cudaStream_t st, const float *A, int lda, int64_t rows, const Ge
 // ([tile][t][128 windows]) and the output is the unit-major projected-gates layout of ntb_lstm_tc.cuh
 // (xproj must hold ceil(n_windows/128)*128*T*8H floats).
 int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, const GemmWeights &w,
-                      const float *bias, float *xproj, int H, const GemmScratch &gs, int64_t *launches);
+                      const float *bias, float *xproj, int H, const GemmScratch &gs, int64_t *launches,
+                      bool planes_ready = false);
 // CUtensorMap (128 bytes, 64-byte aligned) over the projected-gates buffer for the recurrence's TMA ring.
 int make_map_xproj(void *map_out, const float *xproj, int64_t units_total);
 int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, const float *aff_a,
                  const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
-                 int ldo, const GemmScratch &gs, int64_t *launches, bool reuse_planes = false);
+                 int ldo, const GemmScratch &gs, int64_t *launches, bool reuse_planes = false, bool expand = false);
+// residual_layer tail relu(bn?(branch1) + bn(conv2c)) written as fp32 (`out`, may be null) and/or straight into the
+// operand planes of the next GEMM: layout 0 = none, 1 = plain rows (next 1x1 convs), 2 = time-major tiles (projection).
+// y1_scalar: branch1 is a Cin = 1 conv folded into (a1, b1): value = y1[r] * a1[g][c] + b1[g][c].
+int gemm_tc_combine(cudaStream_t st, const float *y1, bool y1_scalar, const float *a1, const float *b1,
+                    const float *y2, const float *a2, const float *b2, const int32_t *win_group, int T, int C,
+                    int64_t rows, float *out, const GemmScratch *planes, int layout, int64_t *launches);
 
 }  // namespace ntb

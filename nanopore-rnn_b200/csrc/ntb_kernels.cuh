@@ -240,11 +240,65 @@ __global__ void __launch_bounds__(BN_CH4 * BN_SLICES) k_bn_stats(const float *__
     }
 }
 
+// Cin = 1 convs (the first residual layer of the CtcLoss graphs, network.py:515-518 reshapes x to [B,T,1]):
+// a 1x1 conv of a single channel is the outer product y[r][n] = x[r] * w[n], so it is never materialised.
+// Its batch moments are those of x scaled: mean_y = w mean_x, var_y = w^2 var_x, and BN(y) = A x + B with
+//   a = rsqrt(w^2 var_x + eps) * scale ; A = a * w ; B = offset - (w mean_x) * a        (no BN: A = w, B = 0).
+// One block per BN group: fp64 moments of x in a fixed order (bit-stable), then the per-channel (A, B) of up
+// to two convs of the same input (conv1 and conv2a).
+struct K1Conv {
+    const float *w, *scale, *offset;   // w [C]; scale/offset null = conv without BN
+    float *A, *B;                      // [n_groups][C]
+};
+__global__ void __launch_bounds__(256) k_k1_affine(const float *__restrict__ x, int T,
+                                                   const int32_t *__restrict__ group_off, int C, float eps,
+                                                   K1Conv c0, K1Conv c1) {
+    __shared__ double sh[2][256];
+    const int g = blockIdx.x;
+    const int64_t r0 = (int64_t)group_off[g] * T, r1 = (int64_t)group_off[g + 1] * T;
+    const int64_t n = r1 - r0;
+    double s = 0.0, q = 0.0;
+    for (int64_t i = r0 + threadIdx.x; i < r1; i += 256) {
+        const double v = x[i];
+        s += v;
+        q = fma(v, v, q);
+    }
+    sh[0][threadIdx.x] = s;
+    sh[1][threadIdx.x] = q;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) {
+            sh[0][threadIdx.x] += sh[0][threadIdx.x + o];
+            sh[1][threadIdx.x] += sh[1][threadIdx.x + o];
+        }
+        __syncthreads();
+    }
+    const double mean = n > 0 ? sh[0][0] / (double)n : 0.0;
+    double var = n > 0 ? sh[1][0] / (double)n - mean * mean : 0.0;
+    var = var < 0.0 ? 0.0 : var;
+    for (int ch = threadIdx.x; ch < C; ch += 256) {
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const K1Conv &cv = k ? c1 : c0;
+            if (!cv.w) continue;
+            const double w = cv.w[ch];
+            float A = (float)w, B = 0.0f;
+            if (cv.scale) {
+                const float a = (1.0f / sqrtf((float)(w * w * var) + eps)) * cv.scale[ch];
+                A = a * (float)w;
+                B = cv.offset[ch] - (float)(w * mean) * a;
+            }
+            cv.A[(int64_t)g * C + ch] = A;
+            cv.B[(int64_t)g * C + ch] = B;
+        }
+    }
+}
+
 // out = relu?( y*a + b )   -- materialised BN(+ReLU) (op-level entry point / odd shapes)
-__global__ void __launch_bounds__(256) k_bn_apply(const float *__restrict__ y, const float *__restrict__ a,
+__global__ void __launch_bounds__(256) k_bn_apply(const float *y, const float *__restrict__ a,
                                                   const float *__restrict__ b,
                                                   const int32_t *__restrict__ win_group, int T, int C,
-                                                  int64_t total, int relu, float *__restrict__ out) {
+                                                  int64_t total, int relu, float *out) {   // out may alias y
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (; i < total; i += stride) {

@@ -46,7 +46,7 @@ struct LstmTcParams {
     int64_t n_windows;
     int n_tiles;                      // ceil(n_windows / 128)
     int T, H, Hp;                     // Hp = H rounded up to 16
-    int flags;                        // debug/ablation: 1 = no x ring (direct global loads), 2 = no slice overlap
+    int flags;                        // debug/ablation: 1 = no x ring (direct global loads), 2 = no slice overlap, 16 = L2 prefetch of the next step
 };
 
 static inline bool lstm_tc_supported(int H) {
@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
                 }
                 if (p.flags & 2) { umma_commit(&d_full[0]); if (two) umma_commit(&d_full[1]); }
                 // next step's projected gates towards L2 while this step computes
-                if (s + 1 < T && !(p.flags & 16)) {
+                if (s + 1 < T && (p.flags & 16)) {   // off by default: measured slower (the TMA ring already runs ahead)
                     const int tn = dir ? T - 2 - s : s + 1;
                     const char *g = reinterpret_cast<const char *>(xtile + (int64_t)tn * step_f4);
                     const uint32_t bytes = (uint32_t)step_f4 * 16, piece = (bytes / 4) & ~15u;
