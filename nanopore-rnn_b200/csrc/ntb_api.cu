@@ -238,7 +238,8 @@ static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &a
                 ld.whh_lo = ar.take<__nv_bfloat16>(lstm_tc_whh_elems(H));
             }
             if (upload && ar.ok()) {
-                k_repack_lstm<<<256, 256, 0, st>>>(kf, bf, kb, bb, l.forget_bias, D, H, Hp, ld.wih, ld.bias, ld.whh);
+                k_repack_lstm<<<256, 256, 0, st>>>(kf, bf, kb, bb, l.forget_bias, D, H, Hp, ld.wih, ld.bias, ld.whh,
+                                                   ld.tc_rec ? 1 : 0);
                 if (ld.tc_rec)
                     k_pack_whh_tc<<<256, 256, 0, st>>>(kf, kb, D, H, (int)align_up(H, 16), ld.whh_hi, ld.whh_lo);
             }
@@ -485,7 +486,9 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
         } else if (ld.type == NTB_LAYER_BLSTM) {
             NTB_TRY(mark(1));
             const int N = 8 * ld.Hp;
-            if (ld.tc_rec && ws.gs.valid) {
+            if (ld.tc_rec) {
+                // the packed projection weights are pre-scaled for this recurrence: no SIMT detour from here
+                if (!ws.gs.valid) return fail(NTB_EINVAL, "blstm: operand planes missing for the tensor-core path%s", "");
                 NTB_TRY(gemm_tc_run_xproj(cx.st, cur, dim, n, T, ld.wihw, ld.bias, ws.xproj, ld.size, ws.gs, &cx.launches,
                                           planes == 2));
                 NTB_TRY(mark(2));
@@ -770,7 +773,7 @@ extern "C" int ntb_blstm(const float *in_dev, const int32_t *len_dev, const floa
     if (!workspace_dev || !ar.ok()) return fail(NTB_ENOMEM, "ntb_blstm: workspace too small (need %s%lld)", "", (long long)ar.off);
     if (n_windows == 0) return NTB_OK;
     k_repack_lstm<<<256, 256, 0, cx.st>>>(kernel_fw_dev, bias_fw_dev, kernel_bw_dev, bias_bw_dev, forget_bias, D, H, Hp,
-                                          b.wih, b.bias, b.whh);
+                                          b.wih, b.bias, b.whh, (b.tc && b.gs.valid) ? 1 : 0);
     NTB_LAUNCH_CHECK();
     if (b.tc && b.gs.valid) {
         // same kernels the model uses for H = 100: tcgen05 projection + tensor-core recurrence

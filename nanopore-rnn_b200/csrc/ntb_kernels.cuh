@@ -483,12 +483,13 @@ __global__ void __launch_bounds__(256) k_decode(const float *__restrict__ logits
 //   wih  [D, 2*4*Hp]  projection B operand, column = dir*4Hp + u*4 + g  (gate-interleaved)
 //   bias [2*4*Hp]     bias with forget_bias folded into the f slot (TF adds it at run time)
 //   whh  [2][H][4][UG][4]  recurrence tile: float4 (i,j,f,o) of unit u = ug*4 + q at [k][q][ug]
-// Pad units (u >= H) get zero weights and zero bias.
+// Pad units (u >= H) get zero weights and zero bias.  With prescale the SIMT tile `whh` is left unscaled
+// (it is not used by the tensor-core recurrence).
 // ------------------------------------------------------------------------------------------
 __global__ void k_repack_lstm(const float *__restrict__ kernel_fw, const float *__restrict__ bias_fw,
                               const float *__restrict__ kernel_bw, const float *__restrict__ bias_bw,
                               float forget_bias, int D, int H, int Hp, float *__restrict__ wih,
-                              float *__restrict__ bias, float *__restrict__ whh) {
+                              float *__restrict__ bias, float *__restrict__ whh, int prescale) {
     const int N = 2 * 4 * Hp;
     const int UG = Hp / 4;
     const int64_t total = (int64_t)(D + 1 + H) * N;
@@ -499,10 +500,13 @@ __global__ void k_repack_lstm(const float *__restrict__ kernel_fw, const float *
         const float *kern = dir ? kernel_bw : kernel_fw;
         const float *bs = dir ? bias_bw : bias_fw;
         const bool real = u < H;
+        // prescale (tensor-core recurrence): pre-activations are produced as -log2(e) z (i, f, o) and
+        // -2 log2(e) z (j), the arguments of the ex2 in sigmoid / tanh (ntb_lstm_tc.cuh)
+        const float sc = prescale ? (g == 1 ? -2.885390081777927f : -1.4426950408889634f) : 1.0f;
         if (row < D) {
-            wih[(int64_t)row * N + col] = real ? kern[(int64_t)row * 4 * H + g * H + u] : 0.0f;
+            wih[(int64_t)row * N + col] = real ? sc * kern[(int64_t)row * 4 * H + g * H + u] : 0.0f;
         } else if (row == D) {
-            bias[col] = real ? bs[g * H + u] + (g == 2 ? forget_bias : 0.0f) : 0.0f;
+            bias[col] = real ? sc * (bs[g * H + u] + (g == 2 ? forget_bias : 0.0f)) : 0.0f;
         } else {
             const int k = row - D - 1;
             const int ug = u / 4, q = u % 4;

@@ -46,7 +46,7 @@ struct LstmTcParams {
     int64_t n_windows;
     int n_tiles;                      // ceil(n_windows / 128)
     int T, H, Hp;                     // Hp = H rounded up to 16
-    int flags;                        // debug/ablation: 1 = no x ring (direct global loads), 2 = no slice overlap, 16 = L2 prefetch of the next step
+    int flags;                        // debug/ablation: 2 = no slice overlap, 16 = L2 prefetch of the next step, 64 = hi.hi pass only, 128 = no MMA (timing only)
 };
 
 static inline bool lstm_tc_supported(int H) {
@@ -75,7 +75,9 @@ __global__ void k_pack_whh_tc(const float *__restrict__ kernel_fw, const float *
         const int k8 = (int)(j % 8), n = (int)((j / 8) % N), kc = (int)(j / (8 * N));
         const int k = kc * 8 + k8, u = n >> 2, g = n & 3;
         const float *kern = dir ? kernel_bw : kernel_fw;
-        const float v = k < H ? kern[(int64_t)(D + k) * 4 * H + g * H + u] : 0.0f;
+        // pre-scaled by -log2(e) (i, f, o) / -2 log2(e) (j): the MMA yields the ex2 arguments directly
+        const float sc = g == 1 ? -2.885390081777927f : -1.4426950408889634f;
+        const float v = k < H ? sc * kern[(int64_t)(D + k) * 4 * H + g * H + u] : 0.0f;
         __nv_bfloat16 h, l;
         ptx::split_bf16(v, h, l);
         hi[i] = h;
@@ -96,18 +98,20 @@ __device__ __forceinline__ float rcp_approx(float x) {
 
 // c' = sigmoid(f) c + sigmoid(i) tanh(j) ; h' = sigmoid(o) tanh(c')  with 5 ex2 + 2 rcp (7 MUFU
 // instead of 10): the three sigmoid/tanh denominators of c' share one reciprocal.
-//   sigmoid(x) = 1/(1+e^-x), tanh(x) = (1-e^-2x)/(1+e^-2x); arguments are clamped so that the
-//   product of denominators stays below 2^120 (sigmoid(-27) ~ 2e-12: far below the fp32 noise).
-__device__ __forceinline__ void lstm_cell_update(float zi, float zj, float zf, float zo, float &c, float &h) {
-    const float L = 1.4426950408889634f;
-    const float A = ex2_approx(-L * fmaxf(zi, -27.0f));
-    const float B = ex2_approx(-2.0f * L * fmaxf(zj, -13.5f));
-    const float F = ex2_approx(-L * fmaxf(zf, -27.0f));
+//   sigmoid(z) = 1/(1+2^y), y = -log2(e) z ;  tanh(z) = (1-2^y)/(1+2^y), y = -2 log2(e) z.
+// The inputs ARE those y (weights and bias are pre-scaled at pack time).  y is clamped at 38.95
+// (z >= -27 resp. -13.5: sigmoid(-27) ~ 2e-12, far below the fp32 noise) so that the product of
+// denominators stays below 2^120.
+__device__ __forceinline__ void lstm_cell_update(float yi, float yj, float yf, float yo, float &c, float &h) {
+    const float CL = 38.95f;
+    const float A = ex2_approx(fminf(yi, CL));
+    const float B = ex2_approx(fminf(yj, CL));
+    const float F = ex2_approx(fminf(yf, CL));
     const float pf = 1.0f + F;
     const float P = (1.0f + A) * (1.0f + B);
     const float cn = fmaf(c, P, (1.0f - B) * pf) * rcp_approx(P * pf);
-    const float O = ex2_approx(-L * fmaxf(zo, -27.0f));
-    const float C2 = ex2_approx(-2.0f * L * fmaxf(cn, -13.5f));
+    const float O = ex2_approx(fminf(yo, CL));
+    const float C2 = ex2_approx(fminf(-2.885390081777927f * cn, CL));
     h = (1.0f - C2) * rcp_approx((1.0f + O) * (1.0f + C2));
     c = cn;
 }
@@ -171,7 +175,7 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
             const uint32_t w_hi = smem_u32(smem_w), w_lo = w_hi + plane_bytes;
             const int k16n = Hp / 16;
             for (int s = 0; s < T; ++s) {
-                mbar_wait(&h_ready, (uint32_t)(s & 1), 1000 + s);
+                mbar_wait_backoff(&h_ready, (uint32_t)(s & 1), 1000 + s);
                 tc_fence_after();
                 for (int half = 0; half < 2; ++half) {
                     if (half && !two) break;
@@ -184,7 +188,9 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
                         const uint64_t bl = smem_desc_nosw(w_lo + koff, lbo, sbo);
                         const uint32_t ah = tmem_base + a_hi_col + (uint32_t)(8 * j);
                         const uint32_t al = tmem_base + a_lo_col + (uint32_t)(8 * j);
+                        if (p.flags & 128) continue;              // timing ablation: no MMA at all
                         umma_f16_ts(d, ah, bh, idesc, j != 0);
+                        if (p.flags & 64) continue;               // timing ablation: hi.hi pass only
                         umma_f16_ts(d, al, bh, idesc, 1);
                         umma_f16_ts(d, ah, bl, idesc, 1);
                     }
@@ -202,29 +208,19 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
             }
         }
     } else if (warp == 1) {
-        // ===================== x producer: projected-gate chunks -> smem ring (bulk async copies) ==========
-        if (lane == 0 && !(p.flags & 1)) {
-            uint32_t g = 0;
+        // ===================== x producer: projected-gate chunks -> smem ring (TMA) ==========
+        if (lane == 0) {
+            uint32_t slot = 0, ph = 0;
             for (int s = 0; s < T; ++s) {
                 const int t = dir ? T - 1 - s : s;
-                const float4 *xs = xtile + (int64_t)t * step_f4;
-                for (int c = 0; c < n_chunks; ++c, ++g) {
-                    const uint32_t slot = g % LSTM_TC_XSLOTS, ph = (g / LSTM_TC_XSLOTS) & 1;
-                    mbar_wait(&x_empty[slot], ph ^ 1, 2000 + s);
-                    const int units = H - 8 * c < 8 ? H - 8 * c : 8;
-                    const uint32_t bytes = (uint32_t)units * LSTM_TC_ROWS * 16;
-                    if (p.flags & 8) {
-                        mbar_arrive(&x_full[slot]);
-                    } else if (p.flags & 32) {
-                        mbar_expect_tx(&x_full[slot], bytes);
-                        bulk_load_1d(xring + slot * LSTM_TC_XSLOT_BYTES, xs + (int64_t)c * 8 * LSTM_TC_ROWS, bytes, &x_full[slot]);
-                    } else {
-                        // TMA box {256 floats, 2, 8 units}: always 16 KB (a short last chunk over-reads the next
-                        // slab / zero-fills past the end; those units are never used)
-                        mbar_expect_tx(&x_full[slot], (uint32_t)LSTM_TC_XSLOT_BYTES);
-                        const int64_t unit0 = ((int64_t)dir * m_tiles + (int64_t)tile * T + t) * H + c * 8;
-                        tma_load_3d(xring + slot * LSTM_TC_XSLOT_BYTES, &map_x, &x_full[slot], 0, 0, (int)unit0);
-                    }
+                const int64_t unit_t = ((int64_t)dir * m_tiles + (int64_t)tile * T + t) * H;
+                for (int c = 0; c < n_chunks; ++c) {
+                    mbar_wait_backoff(&x_empty[slot], ph ^ 1, 2000 + s);
+                    // TMA box {256 floats, 2, 8 units}: always 16 KB (a short last chunk over-reads the next
+                    // slab / zero-fills past the end; those units are never used)
+                    mbar_expect_tx(&x_full[slot], (uint32_t)LSTM_TC_XSLOT_BYTES);
+                    tma_load_3d(xring + slot * LSTM_TC_XSLOT_BYTES, &map_x, &x_full[slot], 0, 0, (int)(unit_t + c * 8));
+                    if (++slot == LSTM_TC_XSLOTS) { slot = 0; ph ^= 1; }
                 }
             }
         }
@@ -232,7 +228,8 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
         // ===================== gate epilogue =====================
         // thread = one window (TMEM lane); the two warps of a lane quarter split every 8-unit chunk in
         // halves (4 units = 16 accumulator columns each), so all 8 warps consume every ring slot in order
-        // (parity waits stay unambiguous) and share the MUFU work evenly.
+        // (parity waits stay unambiguous) and share the MUFU work evenly.  H % 4 == 0, so a warp's 4 units
+        // are all real or all padding (padding: skipped; its A columns stay at their initial zero).
         const int q = warp & 3, half = (warp - 4) >> 2;
         const int r = q * 32 + lane;
         const int64_t w = (int64_t)tile * LSTM_TC_ROWS + r;
@@ -240,6 +237,8 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
         int len = exists ? p.lens[w] : 0;
         len = len > T ? T : len;
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+        const uint32_t d_col = lane_base + (uint32_t)(16 * half);
+        const uint32_t ah_col = lane_base + a_hi_col + (uint32_t)(2 * half), al_col = lane_base + a_lo_col + (uint32_t)(2 * half);
         float cst[LSTM_TC_MAXCH][4];
 #pragma unroll
         for (int ci = 0; ci < LSTM_TC_MAXCH; ++ci)
@@ -253,83 +252,83 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
         __syncwarp();
         if (lane == 0) mbar_arrive(&h_ready);
 
-        uint32_t g = 0;                                          // ring position (chunks consumed so far)
-        for (int s = 0; s < T; ++s) {
+        const float4 *xsm0 = reinterpret_cast<const float4 *>(xring) + half * 4 * LSTM_TC_ROWS + r;
+        uint32_t slot = 0, xph = 0;                              // ring position
+        float *orow = p.out + (w * T + (dir ? T - 1 : 0)) * (int64_t)p.ldo + dir * H + half * 4;
+        const int64_t ostep = dir ? -(int64_t)p.ldo : (int64_t)p.ldo;
+        for (int s = 0; s < T; ++s, orow += ostep) {
             const int t = dir ? T - 1 - s : s;
             const bool active = t < len;
-            float *orow = p.out + (w * T + t) * (int64_t)p.ldo + dir * H;
             uint32_t dh[8][2], dl[8][2];                         // h of the slice-0 chunks, written once slice 1 is done
             mbar_wait(&d_full[0], (uint32_t)(s & 1), 3000 + s);
             tc_fence_after();
+            uint32_t acc[16];
+            // software pipeline: the TMEM load of chunk c + 1 is in flight during the math of chunk c
+            tmem_ld_32x16(d_col, acc);
 #pragma unroll
             for (int c = 0; c < LSTM_TC_MAXCH; ++c) {
                 if (c == 8) {
                     // chunks >= 8 live in N slice 1; once it is complete no MMA reads h_{t-1} any more,
                     // so the deferred h_t of the slice-0 chunks may overwrite the A columns
-                    if (two) {
-                        mbar_wait(&d_full[1], (uint32_t)(s & 1), 4000 + s);
-                        tc_fence_after();
-                    }
 #pragma unroll
                     for (int k = 0; k < 8; ++k) {
-                        if (k < n_chunks) {
-                            tmem_st_32x2(lane_base + a_hi_col + (uint32_t)(4 * k + 2 * half), dh[k][0], dh[k][1]);
-                            tmem_st_32x2(lane_base + a_lo_col + (uint32_t)(4 * k + 2 * half), dl[k][0], dl[k][1]);
+                        if (k < n_chunks && 8 * k + 4 * half < H) {
+                            tmem_st_32x2(ah_col + (uint32_t)(4 * k), dh[k][0], dh[k][1]);
+                            tmem_st_32x2(al_col + (uint32_t)(4 * k), dl[k][0], dl[k][1]);
                         }
                     }
                 }
                 if (c < n_chunks) {
-                    const int u0 = c * 8 + half * 4;             // this warp's 4 units of the chunk
-                    const uint32_t slot = g % LSTM_TC_XSLOTS, ph = (g / LSTM_TC_XSLOTS) & 1;
-                    ++g;
+                    const bool real = c * 8 + half * 4 < H;     // warp-uniform
+                    mbar_wait(&x_full[slot], xph, 5000 + s);
                     float4 xv[4];
-                    if (p.flags & 1) {
-                        const float4 *xg = xtile + (int64_t)t * step_f4 + (int64_t)u0 * LSTM_TC_ROWS + r;
+                    uint32_t a[16];
+                    if (real) {
+                        const float4 *xsm = xsm0 + slot * (LSTM_TC_XSLOT_BYTES / 16);
 #pragma unroll
-                        for (int u = 0; u < 4; ++u)
-                            xv[u] = (u0 + u < H) ? __ldg(xg + u * LSTM_TC_ROWS) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    } else {
-                        mbar_wait(&x_full[slot], ph, 5000 + s);
-                        const float4 *xsm = reinterpret_cast<const float4 *>(xring + slot * LSTM_TC_XSLOT_BYTES) +
-                                            half * 4 * LSTM_TC_ROWS + r;
+                        for (int u = 0; u < 4; ++u) xv[u] = xsm[u * LSTM_TC_ROWS];
+                    }
+                    tmem_ld_wait_dep(acc);
 #pragma unroll
-                        for (int u = 0; u < 4; ++u)
-                            xv[u] = (u0 + u < H) ? xsm[u * LSTM_TC_ROWS] : make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int i = 0; i < 16; ++i) a[i] = acc[i];
+                    if (c + 1 < n_chunks) {
+                        if (c + 1 == 8 && two) {                 // next chunk is the first of slice 1
+                            mbar_wait(&d_full[1], (uint32_t)(s & 1), 4000 + s);
+                            tc_fence_after();
+                        }
+                        tmem_ld_32x16(d_col + (uint32_t)(32 * (c + 1)), acc);
                     }
-                    uint32_t acc[16];
-                    tmem_ld_32x16(lane_base + (uint32_t)(32 * c + 16 * half), acc);
-                    tmem_ld_wait();
-                    float hv[4];
+                    if (real) {
+                        float hv[4];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        float cc = cst[c][u], hh;
-                        lstm_cell_update(__uint_as_float(acc[4 * u + 0]) + xv[u].x, __uint_as_float(acc[4 * u + 1]) + xv[u].y,
-                                         __uint_as_float(acc[4 * u + 2]) + xv[u].z, __uint_as_float(acc[4 * u + 3]) + xv[u].w,
-                                         cc, hh);
-                        const bool on = active && (u0 + u < H);
-                        cst[c][u] = on ? cc : cst[c][u];
-                        hv[u] = on ? hh : 0.0f;
-                    }
-                    if (!(p.flags & 1)) {
-                        // every lane has consumed its x values (data dependence) -> the slot may be refilled
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&x_empty[slot]);
-                    }
-                    uint32_t ph2[2], pl2[2];
+                        for (int u = 0; u < 4; ++u) {
+                            float cc = cst[c][u], hh;
+                            lstm_cell_update(__uint_as_float(a[4 * u + 0]) + xv[u].x, __uint_as_float(a[4 * u + 1]) + xv[u].y,
+                                             __uint_as_float(a[4 * u + 2]) + xv[u].z, __uint_as_float(a[4 * u + 3]) + xv[u].w,
+                                             cc, hh);
+                            cst[c][u] = active ? cc : cst[c][u];
+                            hv[u] = active ? hh : 0.0f;
+                        }
+                        uint32_t ph2[2], pl2[2];
 #pragma unroll
-                    for (int m = 0; m < 2; ++m) {
-                        ph2[m] = pack_bf16x2(hv[2 * m], hv[2 * m + 1]);
-                        const float l0 = hv[2 * m] - __uint_as_float(ph2[m] << 16);
-                        const float l1 = hv[2 * m + 1] - __uint_as_float(ph2[m] & 0xffff0000u);
-                        pl2[m] = pack_bf16x2(l0, l1);
+                        for (int m = 0; m < 2; ++m) {
+                            ph2[m] = pack_bf16x2(hv[2 * m], hv[2 * m + 1]);
+                            const float l0 = hv[2 * m] - __uint_as_float(ph2[m] << 16);
+                            const float l1 = hv[2 * m + 1] - __uint_as_float(ph2[m] & 0xffff0000u);
+                            pl2[m] = pack_bf16x2(l0, l1);
+                        }
+                        if (c < 8) {
+                            dh[c][0] = ph2[0]; dh[c][1] = ph2[1]; dl[c][0] = pl2[0]; dl[c][1] = pl2[1];
+                        } else {
+                            tmem_st_32x2(ah_col + (uint32_t)(4 * c), ph2[0], ph2[1]);
+                            tmem_st_32x2(al_col + (uint32_t)(4 * c), pl2[0], pl2[1]);
+                        }
+                        if (exists) *reinterpret_cast<float4 *>(orow + 8 * c) = make_float4(hv[0], hv[1], hv[2], hv[3]);
                     }
-                    if (c < 8) {
-                        dh[c][0] = ph2[0]; dh[c][1] = ph2[1]; dl[c][0] = pl2[0]; dl[c][1] = pl2[1];
-                    } else {
-                        tmem_st_32x2(lane_base + a_hi_col + (uint32_t)(4 * c + 2 * half), ph2[0], ph2[1]);
-                        tmem_st_32x2(lane_base + a_lo_col + (uint32_t)(4 * c + 2 * half), pl2[0], pl2[1]);
-                    }
-                    if (exists && u0 < H) *reinterpret_cast<float4 *>(orow + u0) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+                    // every lane has consumed its x values (data dependence) -> the slot may be refilled
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&x_empty[slot]);
+                    if (++slot == LSTM_TC_XSLOTS) { slot = 0; xph ^= 1; }
                 }
             }
             tmem_st_wait();

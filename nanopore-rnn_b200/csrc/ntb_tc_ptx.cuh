@@ -26,31 +26,52 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
 }
 __device__ __forceinline__ uint32_t mbar_try_wait(uint64_t *bar, uint32_t parity) {
     uint32_t ok;
+    // potentially-blocking form with a suspend-time hint: the thread sleeps in hardware (no issue slots)
+    // until the phase completes or the hint expires
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
         "selp.u32 %0, 1, 0, p;\n"
         "}\n"
         : "=r"(ok)
-        : "r"(smem_u32(bar)), "r"(parity)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(1000u)
         : "memory");
     return ok;
 }
-// Bounded wait: a protocol bug becomes a launch failure (trap) after ~2 s instead of a hung GPU.
+// Bounded wait: a protocol bug becomes a launch failure (trap) instead of a hung GPU.  The bound is an
+// iteration count (no clock reads in the loop: spinning warps share issue slots with working ones).
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity, int tag = 0) {
     if (mbar_try_wait(bar, parity)) return;
-    const long long t0 = clock64();
+    uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
+        if (++spins > (1u << 24)) {
 #ifdef NTB_DEBUG_SYNC
-        if (clock64() - t0 > 200000000LL) {   // debug build: report the stuck wait and carry on
             printf("mbar timeout tag %d block (%d,%d) thread %d parity %u\n", tag, blockIdx.x, blockIdx.y, threadIdx.x, parity);
             return;
-        }
 #else
-        (void)tag;
-        if (clock64() - t0 > 4000000000LL) __trap();
+            (void)tag;
+            __trap();
 #endif
+        }
+    }
+}
+// Same, for single-thread control roles (TMA producer, MMA issuer) that wait for a long time next to
+// working warps on the same scheduler: back off with nanosleep between polls.
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t *bar, uint32_t parity, int tag = 0) {
+    if (mbar_try_wait(bar, parity)) return;
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        __nanosleep(32);
+        if (++spins > (1u << 24)) {
+#ifdef NTB_DEBUG_SYNC
+            printf("mbar timeout tag %d block (%d,%d) thread %d parity %u\n", tag, blockIdx.x, blockIdx.y, threadIdx.x, parity);
+            return;
+#else
+            (void)tag;
+            __trap();
+#endif
+        }
     }
 }
 
@@ -257,6 +278,15 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16])
         : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// wait::ld that also carries a data dependence on the loaded registers, so that uses of a load issued
+// several statements earlier (software pipelining) cannot be scheduled above the wait
+__device__ __forceinline__ void tmem_ld_wait_dep(uint32_t (&r)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+                 :
+                 : "memory");
+}
 
 // ------------------------------------------------------------------ descriptors
 // K-major operand tile stored as [rows][64 bf16] (128 B per row) with the 128-byte swizzle
