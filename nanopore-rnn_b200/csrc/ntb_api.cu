@@ -39,8 +39,11 @@ struct LayerDev {
     float *wih = nullptr, *bias = nullptr, *whh = nullptr;
     GemmWeights wihw;
     const float *kernel_fw = nullptr, *kernel_bw = nullptr;   // raw TF kernels on the device
-    __nv_bfloat16 *whh_hi = nullptr, *whh_lo = nullptr;       // tensor-core recurrence planes (ntb_lstm_tc.cuh)
-    bool tc_rec = false;
+    op16_t *whh_hi = nullptr, *whh_lo = nullptr;       // tensor-core recurrence planes (ntb_lstm_tc.cuh)
+    bool tc_rec = false;      // persistent tensor-core recurrence (H <= 100)
+    bool step_rec = false;    // one tcgen05 GEMM per timestep (larger H; ntb_gemm_tc.cu)
+    GemmWeights whhw;         // [2 dirs][4H][H] planes for step_rec
+    float *whh_stage = nullptr;
     // chiron_fnn
     const float *fnn_w = nullptr, *fnn_b = nullptr;
 };
@@ -52,7 +55,7 @@ struct ntb_model {
     std::vector<ntb::LayerDev> layers;
     const float *out_w = nullptr, *out_b = nullptr;
     ntb::GemmWeights outw;
-    int max_res_c = 0, max_act_c = 0, max_proj_n = 0;
+    int max_res_c = 0, max_act_c = 0, max_proj_n = 0, max_step_h = 0;
     bool has_res = false, any_tc_rec = false;
     int64_t launches = 0;
     int profile = 0;
@@ -234,14 +237,18 @@ static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &a
             ld.kernel_fw = kf; ld.kernel_bw = kb;
             ld.tc_rec = ld.wihw.valid && Hp == H && lstm_tc_supported(H);
             if (ld.tc_rec) {
-                ld.whh_hi = ar.take<__nv_bfloat16>(lstm_tc_whh_elems(H));
-                ld.whh_lo = ar.take<__nv_bfloat16>(lstm_tc_whh_elems(H));
+                ld.whh_hi = ar.take<op16_t>(lstm_tc_whh_elems(H));
+                ld.whh_lo = ar.take<op16_t>(lstm_tc_whh_elems(H));
+            } else if (Hp == H && gemm_tc_lstm_supported(H)) {
+                gemm_tc_plan_whh(ld.whhw, H, ar, &ld.whh_stage);
+                ld.step_rec = ld.whhw.valid;
             }
             if (upload && ar.ok()) {
                 k_repack_lstm<<<256, 256, 0, st>>>(kf, bf, kb, bb, l.forget_bias, D, H, Hp, ld.wih, ld.bias, ld.whh,
-                                                   ld.tc_rec ? 1 : 0);
+                                                   (ld.tc_rec || ld.step_rec) ? 1 : 0);
                 if (ld.tc_rec)
                     k_pack_whh_tc<<<256, 256, 0, st>>>(kf, kb, D, H, (int)align_up(H, 16), ld.whh_hi, ld.whh_lo);
+                if (ld.step_rec) gemm_tc_pack_whh(st, kf, kb, D, H, ld.whh_stage, ld.whhw);
             }
             dim = 2 * H;
         } else {
@@ -296,6 +303,7 @@ extern "C" int ntb_model_create(const ntb_model_desc *desc, void *weights_dev, i
             if (2 * ld.size > m->max_act_c) m->max_act_c = 2 * ld.size;
             if (8 * ld.Hp > m->max_proj_n) m->max_proj_n = 8 * ld.Hp;
             if (ld.tc_rec) m->any_tc_rec = true;
+            if (ld.step_rec && ld.size > m->max_step_h) m->max_step_h = ld.size;
         } else {
             if (ld.in_dim / 2 > m->max_act_c) m->max_act_c = ld.in_dim / 2;
         }
@@ -329,6 +337,7 @@ struct Workspace {
     float *y1, *y2a, *y2b;
     float *aff[8];
     float *xproj;
+    float *cstate;
     float *logits;
     GemmScratch gs;
 };
@@ -352,15 +361,18 @@ static int64_t plan_workspace(const ntb_model *m, int64_t n, int64_t n_groups, b
     // the tensor-core recurrence works on whole 128-window tiles (time-major), tail tile padded
     const int64_t tile_rows = m->any_tc_rec ? align_up(n, LSTM_TC_ROWS) * m->T : 0;
     ws.xproj = m->max_proj_n ? ar.take<float>((tile_rows > rows ? tile_rows : rows) * m->max_proj_n) : nullptr;
+    ws.cstate = m->max_step_h ? ar.take<float>(gemm_tc_lstm_state_floats(n, m->max_step_h)) : nullptr;
     const bool small_c = m->C <= 8;
     ws.logits = (!small_c && own_logits) ? ar.take<float>(rows * m->C) : nullptr;
-    int maxk = m->len_x;
+    int maxk = m->len_x > m->max_step_h ? m->len_x : m->max_step_h;
     for (auto &ld : m->layers) {
         if (ld.in_dim > maxk) maxk = ld.in_dim;
         if (ld.type == NTB_LAYER_RESIDUAL && ld.size > maxk) maxk = ld.size;
     }
     if (m->F_final > maxk) maxk = m->F_final;
-    gemm_tc_plan_scratch(ws.gs, rows, m->T, maxk, ar, tile_rows);
+    // the per-timestep recurrence keeps its h operand planes (2 parities x 2 dirs x padded windows x H) in the same scratch
+    const int64_t step_rows = m->max_step_h ? cdiv(4 * align_up(n, 256) * m->max_step_h, align_up(maxk, 8)) : 0;
+    gemm_tc_plan_scratch(ws.gs, rows, m->T, maxk, ar, tile_rows > step_rows ? tile_rows : step_rows);
     return ar.off;
 }
 }  // namespace ntb
@@ -497,6 +509,12 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
                 p.out = out; p.ldo = 2 * ld.size; p.n_windows = n; p.n_tiles = cdiv(n, LSTM_TC_ROWS);
                 p.T = T; p.H = ld.size; p.Hp = (int)align_up(ld.size, 16);
                 NTB_TRY(launch_lstm_tc(cx, p));
+            } else if (ld.step_rec) {
+                if (!ws.gs.valid) return fail(NTB_EINVAL, "blstm: operand planes missing for the tensor-core path%s", "");
+                NTB_TRY(dense(cx, cur, dim, rows, dim, N, ld.wih, &ld.wihw, ld.bias, ws.xproj, N, &ws.gs));
+                NTB_TRY(mark(2));
+                NTB_TRY(gemm_tc_lstm_layer(cx.st, ld.whhw, ws.xproj, N, lens, n, T, ld.size, ws.cstate, out, 2 * ld.size,
+                                           ws.gs, &cx.launches));
             } else {
                 NTB_TRY(dense(cx, cur, dim, rows, dim, N, ld.wih, &ld.wihw, ld.bias, ws.xproj, N, &ws.gs));
                 NTB_TRY(mark(2));
@@ -727,9 +745,12 @@ namespace ntb {
 struct BlstmOpBufs {
     float *wih, *bias, *whh, *xproj;
     bool tc;
+    bool step = false;
+    GemmWeights whhw;
+    float *whh_stage = nullptr, *cstate = nullptr;
     GemmWeights wihw;
     GemmScratch gs;
-    __nv_bfloat16 *whh_hi, *whh_lo;
+    op16_t *whh_hi, *whh_lo;
 };
 static int64_t plan_blstm_op(Arena &ar, int64_t n, int T, int D, int H, BlstmOpBufs &b) {
     const int Hp = pad_hidden(H);
@@ -743,9 +764,15 @@ static int64_t plan_blstm_op(Arena &ar, int64_t n, int T, int D, int H, BlstmOpB
     b.whh_hi = b.whh_lo = nullptr;
     b.gs = GemmScratch();
     if (b.tc) {
-        b.whh_hi = ar.take<__nv_bfloat16>(lstm_tc_whh_elems(H));
-        b.whh_lo = ar.take<__nv_bfloat16>(lstm_tc_whh_elems(H));
+        b.whh_hi = ar.take<op16_t>(lstm_tc_whh_elems(H));
+        b.whh_lo = ar.take<op16_t>(lstm_tc_whh_elems(H));
         gemm_tc_plan_scratch(b.gs, rows, T, D, ar, tile_rows);
+    } else if (Hp == H && gemm_tc_lstm_supported(H)) {
+        gemm_tc_plan_whh(b.whhw, H, ar, &b.whh_stage);
+        b.cstate = ar.take<float>(gemm_tc_lstm_state_floats(n, H));
+        const int kcap = D > H ? D : H;
+        gemm_tc_plan_scratch(b.gs, rows, T, kcap, ar, cdiv(4 * align_up(n, 256) * H, align_up(kcap, 8)));
+        b.step = b.whhw.valid && b.gs.valid;
     }
     return ar.off;
 }
@@ -773,7 +800,7 @@ extern "C" int ntb_blstm(const float *in_dev, const int32_t *len_dev, const floa
     if (!workspace_dev || !ar.ok()) return fail(NTB_ENOMEM, "ntb_blstm: workspace too small (need %s%lld)", "", (long long)ar.off);
     if (n_windows == 0) return NTB_OK;
     k_repack_lstm<<<256, 256, 0, cx.st>>>(kernel_fw_dev, bias_fw_dev, kernel_bw_dev, bias_bw_dev, forget_bias, D, H, Hp,
-                                          b.wih, b.bias, b.whh, (b.tc && b.gs.valid) ? 1 : 0);
+                                          b.wih, b.bias, b.whh, ((b.tc && b.gs.valid) || b.step) ? 1 : 0);
     NTB_LAUNCH_CHECK();
     if (b.tc && b.gs.valid) {
         // same kernels the model uses for H = 100: tcgen05 projection + tensor-core recurrence
@@ -786,6 +813,14 @@ extern "C" int ntb_blstm(const float *in_dev, const int32_t *len_dev, const floa
         p.out = out_dev; p.ldo = 2 * H; p.n_windows = n_windows; p.n_tiles = cdiv(n_windows, LSTM_TC_ROWS);
         p.T = T; p.H = H; p.Hp = (int)align_up(H, 16);
         return launch_lstm_tc(cx, p);
+    }
+    if (b.step) {
+        // H beyond the persistent kernel: one tcgen05 GEMM per timestep (same path the model takes)
+        if (b.wihw.valid) NTB_TRY(gemm_tc_pack_weights(cx.st, b.wih, b.wihw));
+        NTB_TRY(gemm_tc_pack_whh(cx.st, kernel_fw_dev, kernel_bw_dev, D, H, b.whh_stage, b.whhw));
+        NTB_TRY(dense(cx, in_dev, D, n_windows * T, D, 8 * Hp, b.wih, &b.wihw, b.bias, b.xproj, 8 * Hp, &b.gs));
+        return gemm_tc_lstm_layer(cx.st, b.whhw, b.xproj, 8 * Hp, len_dev, n_windows, T, H, b.cstate, out_dev, 2 * H, b.gs,
+                                  &cx.launches);
     }
     NTB_TRY(dense(cx, in_dev, D, n_windows * T, D, 8 * Hp, b.wih, nullptr, b.bias, b.xproj, 8 * Hp, nullptr));
     LstmParams p{};

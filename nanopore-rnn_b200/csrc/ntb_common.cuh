@@ -1,7 +1,7 @@
 // Shared helpers for the nanotensor_b200 kernels (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
-#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
@@ -9,6 +9,8 @@
 #include "../../include/nanotensor_b200.h"
 
 namespace ntb {
+
+typedef __half op16_t;   // storage type of the split tensor-core operands (fp16 hi / lo planes)
 
 extern thread_local char g_err[512];
 

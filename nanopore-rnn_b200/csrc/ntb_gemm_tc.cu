@@ -6,7 +6,7 @@
 // The reference computes these in float32.  bf16 tensor-core operands alone miss the 1e-3 logits
 // budget by two orders of magnitude (precision table), so every fp32 operand is split
 // into bf16 hi + bf16 lo planes and the product is accumulated in fp32 TMEM as
-//   A.B ~= Ahi.Bhi + Alo.Bhi + Ahi.Blo            (relative error ~2^-16, "bf16x3").
+//   A.B ~= Ahi.Bhi + Alo.Bhi + Ahi.Blo            (relative error ~2^-16, "fp16x3").
 //
 // Kernel: persistent, warp-specialised, one CTA per SM.
 //   warp 0      TMA producer: cp.async.bulk.tensor loads of the A hi/lo [128 x 64] and
@@ -24,6 +24,7 @@
 #include <stdlib.h>
 
 #include "ntb_gemm_tc.cuh"
+#include "ntb_lstm_cell.cuh"
 #include "ntb_tc_ptx.cuh"
 
 namespace ntb {
@@ -43,7 +44,7 @@ struct TcParams {
     int n_tiles, BN, Np, N;
     int taps, k_blocks;    // k_blocks per tap = ceil(K / 64)
     int k16_last;          // k16 steps in the last k block of a tap
-    int passes;            // 3 = bf16x3, 1 = plain bf16 (ablation only)
+    int passes;            // 3 = fp16x3, 1 = plain bf16 (ablation only)
     int stages;
     int T, pad;            // pad = 1: plane rows are [window][T+2]
     int64_t out_rows;      // rows of `out`
@@ -52,6 +53,15 @@ struct TcParams {
     int ldo;
     int tma_store;         // plain row-major output through smem staging + cp.async.bulk.tensor stores
     int xproj_H;           // > 0: out is the recurrence's unit-major projected-gates layout (ntb_lstm_tc.cuh)
+    // LSTM timestep mode (lstm_H > 0): this GEMM is h_{t-1} . W_hh of ONE timestep for all windows and both
+    // directions (A rows = [dir][Mp windows], B rows = [dir][Np]); the epilogue adds the projected gates and runs
+    // the fused cell update (see gemm_tc_lstm_layer)
+    int lstm_H, lstm_s, lstm_mt_dir;   // hidden size, step index, M tiles per direction
+    int64_t lstm_n, lstm_Mp;           // windows, windows padded to the M-tile pair
+    const float *lstm_x; int lstm_ldx; // projected gates [n*T][ldx], column dir*4H + u*4 + g (bias folded, pre-scaled)
+    float *lstm_c;                     // cell state [2][n][H]
+    const int32_t *lstm_lens;
+    op16_t *lstm_hi, *lstm_lo;  // h_t operand planes of the NEXT step [2][Mp][H]
 };
 
 // CG = 1: one CTA per tile (M = 128).  CG = 2: CTA pair (cluster of 2, tcgen05 cta_group::2, M = 256): each CTA loads
@@ -109,9 +119,10 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
             for (int64_t tile = first_tile; tile < total_tiles; tile += tile_step) {
                 const int n_tile = (int)(tile % p.n_tiles);
                 const int64_t m_tile = (tile / p.n_tiles) * CG + rank;
+                const int dir_rows = (p.lstm_H > 0 && m_tile >= p.lstm_mt_dir) ? p.Np : 0;   // W_hh of the bw direction
                 for (int tap = 0; tap < p.taps; ++tap) {
                     const int row0 = (int)(m_tile * BM) + tap - left;
-                    const int brow0 = tap * p.Np + n_tile * p.BN + rank * (p.BN / CG);
+                    const int brow0 = tap * p.Np + n_tile * p.BN + rank * (p.BN / CG) + dir_rows;
                     for (int kb = 0; kb < p.k_blocks; ++kb) {
                         mbar_wait(&empty_bar[stage], phase ^ 1);
                         uint8_t *s = smem + (size_t)stage * stage_bytes;
@@ -141,7 +152,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         if (lane == 0 && rank == 0) {
-            const uint32_t idesc = idesc_bf16_f32(BM * CG, p.BN);
+            const uint32_t idesc = idesc_f16_f32(BM * CG, p.BN);
             int stage = 0; uint32_t phase = 0;
             int acc = 0; uint32_t acc_phase = 0;
             for (int64_t tile = first_tile; tile < total_tiles; tile += tile_step) {
@@ -240,6 +251,48 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                         tma_store_2d(&map_out, buf, nb, (int)(m_tile * BM) + q * 32);
                         bulk_commit_group();
                     }
+                } else if (p.lstm_H > 0) {
+                    // thread = one window of one direction; this chunk = 8 hidden units x (i, j, f, o)
+                    const int H = p.lstm_H, nb = n0 + c0;
+                    const int dir = m_tile >= p.lstm_mt_dir ? 1 : 0;
+                    const int64_t w = prow - dir * p.lstm_Mp;
+                    if (w < p.lstm_n && nb < p.N) {
+                        const int t = dir ? p.T - 1 - p.lstm_s : p.lstm_s;
+                        int len = p.lstm_lens[w];
+                        len = len > p.T ? p.T : len;
+                        const bool active = t < len;
+                        const int u0 = nb >> 2;
+                        const int nu = (p.N - nb >= 32 && c0 + 32 <= p.BN) ? 8 : 4;     // H % 4 == 0, BN % 16 == 0
+                        const float4 *xg = reinterpret_cast<const float4 *>(p.lstm_x + (w * p.T + t) * (int64_t)p.lstm_ldx + dir * 4 * H + nb);
+                        float *cg = p.lstm_c + ((int64_t)dir * p.lstm_n + w) * H + u0;
+                        float *og = p.out + (w * p.T + t) * (int64_t)p.ldo + dir * H + u0;
+                        float hv[8];
+#pragma unroll
+                        for (int half = 0; half < 2; ++half) {
+                            if (half * 4 < nu) {
+                                const float4 c4 = *reinterpret_cast<const float4 *>(cg + 4 * half);
+                                float cc[4] = {c4.x, c4.y, c4.z, c4.w};
+#pragma unroll
+                                for (int u = 0; u < 4; ++u) {
+                                    const int i = 16 * half + 4 * u;
+                                    const float4 xv = __ldg(xg + 4 * half + u);
+                                    float cn = cc[u], hh;
+                                    lstm_cell_update(__uint_as_float(r[i]) + xv.x, __uint_as_float(r[i + 1]) + xv.y,
+                                                     __uint_as_float(r[i + 2]) + xv.z, __uint_as_float(r[i + 3]) + xv.w, cn, hh);
+                                    cc[u] = active ? cn : cc[u];
+                                    hv[4 * half + u] = active ? hh : 0.0f;
+                                }
+                                if (active) *reinterpret_cast<float4 *>(cg + 4 * half) = make_float4(cc[0], cc[1], cc[2], cc[3]);
+                                *reinterpret_cast<float4 *>(og + 4 * half) = make_float4(hv[4 * half], hv[4 * half + 1], hv[4 * half + 2], hv[4 * half + 3]);
+                                uint32_t ph[2], pl[2];
+                                split_pack_op16x2(hv[4 * half], hv[4 * half + 1], ph[0], pl[0]);
+                                split_pack_op16x2(hv[4 * half + 2], hv[4 * half + 3], ph[1], pl[1]);
+                                const int64_t po = (dir * p.lstm_Mp + w) * (int64_t)H + u0 + 4 * half;
+                                *reinterpret_cast<uint2 *>(p.lstm_hi + po) = make_uint2(ph[0], ph[1]);
+                                *reinterpret_cast<uint2 *>(p.lstm_lo + po) = make_uint2(pl[0], pl[1]);
+                            }
+                        }
+                    }
                 } else if (p.xproj_H > 0 && m_tile < p.m_tiles) {
                     // xproj[dir][m_tile][unit][row] float4 (i,j,f,o): a warp's 32 rows are contiguous.
                     // One division per chunk; (dir, unit) then advance incrementally.
@@ -316,13 +369,13 @@ struct SplitParams {
     int K;                   // multiple of 8
     const float *aff_a, *aff_b; const int32_t *win_group;
     int T, relu, pad;
-    __nv_bfloat16 *hi, *lo;  // [plane_rows][K]
+    op16_t *hi, *lo;  // [plane_rows][K]
     int64_t plane_rows;
     int perm;                // 1: plane row (tile*T + t)*128 + wl <- source row (tile*128 + wl)*T + t
     int expand;              // 1: A is [rows] (a Cin = 1 conv folded into the affine): v[c] = A[r] * a[g][c] + b[g][c]
 };
 
-__global__ void __launch_bounds__(256) k_split_bf16(const SplitParams p) {
+__global__ void __launch_bounds__(256) k_split_op16(const SplitParams p) {
     const int K8 = p.K >> 3;
     const int64_t total = p.plane_rows * K8;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -365,9 +418,9 @@ __global__ void __launch_bounds__(256) k_split_bf16(const SplitParams p) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[j] = 0.0f;
         }
-        __align__(16) __nv_bfloat16 h[8], l[8];
+        __align__(16) op16_t h[8], l[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) ptx::split_bf16(v[j], h[j], l[j]);
+        for (int j = 0; j < 8; ++j) ptx::split_op16(v[j], h[j], l[j]);
         *reinterpret_cast<uint4 *>(p.hi + pr * p.K + c) = *reinterpret_cast<const uint4 *>(h);
         if (p.lo) *reinterpret_cast<uint4 *>(p.lo + pr * p.K + c) = *reinterpret_cast<const uint4 *>(l);
     }
@@ -376,7 +429,7 @@ __global__ void __launch_bounds__(256) k_split_bf16(const SplitParams p) {
 // Same transform with one CTA per window: the BN affine of the producer is constant over a window
 // (window -> group -> [a, b] per channel), so every thread keeps its 8 channels' a/b in registers
 // and walks the window's rows; no per-element index arithmetic.  Used for the conv operands.
-__global__ void __launch_bounds__(256) k_split_bf16_window(const SplitParams p) {
+__global__ void __launch_bounds__(256) k_split_window(const SplitParams p) {
     const int K8 = p.K >> 3;
     const int rows_per_it = blockDim.x / K8;
     const int cg = threadIdx.x % K8, rs = threadIdx.x / K8;
@@ -420,9 +473,9 @@ __global__ void __launch_bounds__(256) k_split_bf16_window(const SplitParams p) 
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[j] = 0.0f;
         }
-        __align__(16) __nv_bfloat16 h[8], l[8];
+        __align__(16) op16_t h[8], l[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) ptx::split_bf16(v[j], h[j], l[j]);
+        for (int j = 0; j < 8; ++j) ptx::split_op16(v[j], h[j], l[j]);
         *reinterpret_cast<uint4 *>(p.hi + (pr0 + i) * p.K + c) = *reinterpret_cast<const uint4 *>(h);
         if (p.lo) *reinterpret_cast<uint4 *>(p.lo + (pr0 + i) * p.K + c) = *reinterpret_cast<const uint4 *>(l);
     }
@@ -440,7 +493,7 @@ struct CombineParams {
     int T, C;
     int64_t rows;                    // source rows = n_windows * T
     float *out;                      // fp32 [rows][C] or null
-    __nv_bfloat16 *hi, *lo;          // planes or null
+    op16_t *hi, *lo;          // planes or null
     int64_t plane_rows;              // = rows unless perm (whole 128-window tiles)
     int perm;
 };
@@ -495,9 +548,9 @@ __global__ void __launch_bounds__(256) k_combine_split(const CombineParams p) {
             for (int j = 0; j < 8; ++j) v[j] = 0.0f;
         }
         if (p.hi) {
-            __align__(16) __nv_bfloat16 h[8], l[8];
+            __align__(16) op16_t h[8], l[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) ptx::split_bf16(v[j], h[j], l[j]);
+            for (int j = 0; j < 8; ++j) ptx::split_op16(v[j], h[j], l[j]);
             *reinterpret_cast<uint4 *>(p.hi + pr * p.C + c) = *reinterpret_cast<const uint4 *>(h);
             *reinterpret_cast<uint4 *>(p.lo + pr * p.C + c) = *reinterpret_cast<const uint4 *>(l);
         }
@@ -506,15 +559,15 @@ __global__ void __launch_bounds__(256) k_combine_split(const CombineParams p) {
 
 // TF weights [taps][K][N] fp32 -> K-major bf16 planes [taps][Np][Kp] (zero padded)
 __global__ void k_pack_weights(const float *__restrict__ w, int taps, int K, int N, int Kp, int Np,
-                               __nv_bfloat16 *__restrict__ hi, __nv_bfloat16 *__restrict__ lo) {
+                               op16_t *__restrict__ hi, op16_t *__restrict__ lo) {
     const int64_t total = (int64_t)taps * Np * Kp;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int k = (int)(i % Kp);
         const int n = (int)((i / Kp) % Np);
         const int tap = (int)(i / ((int64_t)Kp * Np));
         const float v = (k < K && n < N) ? w[((int64_t)tap * K + k) * N + n] : 0.0f;
-        __nv_bfloat16 h, l;
-        ptx::split_bf16(v, h, l);
+        op16_t h, l;
+        ptx::split_op16(v, h, l);
         hi[i] = h;
         lo[i] = l;
     }
@@ -543,7 +596,7 @@ int make_map(CUtensorMap *m, const void *base, int64_t rows, int K, int box_rows
     cuuint64_t strides[1] = {(cuuint64_t)K * 2};
     cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS)
@@ -591,7 +644,7 @@ int launch_split(cudaStream_t st, const SplitParams &sp, int64_t *launches) {
     const int K8 = sp.K >> 3;
     if (!sp.perm && sp.T > 1 && K8 <= 256 && sp.rows % sp.T == 0 && (sp.pad || sp.aff_a)) {
         const int threads = (256 / K8) * K8;
-        k_split_bf16_window<<<(unsigned)(sp.rows / sp.T), threads, 0, st>>>(sp);
+        k_split_window<<<(unsigned)(sp.rows / sp.T), threads, 0, st>>>(sp);
         if (launches) ++*launches;
         NTB_LAUNCH_CHECK();
         return NTB_OK;
@@ -601,7 +654,7 @@ int launch_split(cudaStream_t st, const SplitParams &sp, int64_t *launches) {
     const int64_t cap = (int64_t)sm_count() * 16;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    k_split_bf16<<<(unsigned)blocks, 256, 0, st>>>(sp);
+    k_split_op16<<<(unsigned)blocks, 256, 0, st>>>(sp);
     if (launches) ++*launches;
     NTB_LAUNCH_CHECK();
     return NTB_OK;
@@ -616,15 +669,9 @@ int gemm_cta_group() {
     return cg;
 }
 
-int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, int64_t plane_rows, int T, int pad,
-                int64_t out_rows, const float *bias, float *out, int ldo, int64_t *launches, int xproj_H = 0) {
+// tile / ring geometry of one GEMM launch (everything but the operands' addresses)
+int fill_params(TcParams &p, const GemmWeights &w, int64_t plane_rows) {
     const int cg = gemm_cta_group();
-    CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
-    NTB_TRY(make_map(&ma_hi, gs.a_hi, plane_rows, w.K, BM));
-    NTB_TRY(make_map(&ma_lo, gs.a_lo, plane_rows, w.K, BM));
-    NTB_TRY(make_map(&mb_hi, w.hi, (int64_t)w.taps * w.Np, w.Kp, w.BN / cg));
-    NTB_TRY(make_map(&mb_lo, w.lo, (int64_t)w.taps * w.Np, w.Kp, w.BN / cg));
-    TcParams p{};
     p.m_tiles = (plane_rows + BM - 1) / BM;
     p.BN = w.BN; p.Np = w.Np; p.N = w.N; p.n_tiles = w.Np / w.BN;
     p.taps = w.taps; p.k_blocks = (w.K + BK - 1) / BK;
@@ -634,13 +681,13 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     p.stages = SMEM_BUDGET / stage_bytes;
     if (p.stages > 8) p.stages = 8;
     if (p.stages < 2) return fail(NTB_EINVAL, "tcgen05 GEMM: tile does not fit shared memory%s", "");
-    p.T = T; p.pad = pad; p.out_rows = out_rows; p.bias = bias; p.out = out; p.ldo = ldo;
-    p.xproj_H = xproj_H;
-    // coalesced TMA-store epilogue for plain row-major outputs (N tiles of whole 32-column chunks)
-    p.tma_store = (!pad && xproj_H == 0 && w.BN % 32 == 0 && (ldo & 3) == 0 &&
-                   (reinterpret_cast<uintptr_t>(out) & 15) == 0) ? 1 : 0;
-    CUtensorMap mo = ma_hi;
-    if (p.tma_store) NTB_TRY(make_map_out(&mo, out, out_rows, w.N, ldo));
+    return NTB_OK;
+}
+
+int do_launch(cudaStream_t st, const CUtensorMap &ma_hi, const CUtensorMap &ma_lo, const CUtensorMap &mb_hi,
+              const CUtensorMap &mb_lo, const CUtensorMap &mo, const TcParams &p, int64_t *launches) {
+    const int cg = gemm_cta_group();
+    const int stage_bytes = (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + (p.BN / cg) * BK * 2);
     const size_t smem = (size_t)p.stages * stage_bytes + 1024 + EPI_STAGE_BYTES;
     static bool attr_set = false;
     if (!attr_set) {
@@ -669,6 +716,26 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     if (launches) ++*launches;
     NTB_LAUNCH_CHECK();
     return NTB_OK;
+}
+
+int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, int64_t plane_rows, int T, int pad,
+                int64_t out_rows, const float *bias, float *out, int ldo, int64_t *launches, int xproj_H = 0) {
+    const int cg = gemm_cta_group();
+    CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
+    NTB_TRY(make_map(&ma_hi, gs.a_hi, plane_rows, w.K, BM));
+    NTB_TRY(make_map(&ma_lo, gs.a_lo, plane_rows, w.K, BM));
+    NTB_TRY(make_map(&mb_hi, w.hi, (int64_t)w.taps * w.Np, w.Kp, w.BN / cg));
+    NTB_TRY(make_map(&mb_lo, w.lo, (int64_t)w.taps * w.Np, w.Kp, w.BN / cg));
+    TcParams p{};
+    NTB_TRY(fill_params(p, w, plane_rows));
+    p.T = T; p.pad = pad; p.out_rows = out_rows; p.bias = bias; p.out = out; p.ldo = ldo;
+    p.xproj_H = xproj_H;
+    // coalesced TMA-store epilogue for plain row-major outputs (N tiles of whole 32-column chunks)
+    p.tma_store = (!pad && xproj_H == 0 && w.BN % 32 == 0 && (ldo & 3) == 0 &&
+                   (reinterpret_cast<uintptr_t>(out) & 15) == 0) ? 1 : 0;
+    CUtensorMap mo = ma_hi;
+    if (p.tma_store) NTB_TRY(make_map_out(&mo, out, out_rows, w.N, ldo));
+    return do_launch(st, ma_hi, ma_lo, mb_hi, mb_lo, mo, p, launches);
 }
 
 }  // namespace
@@ -701,8 +768,8 @@ void gemm_tc_plan_weights(GemmWeights &w, int taps, int K, int N, Arena &ar) {
     w.BN = pick_bn(N);
     w.Np = (int)align_up(N, w.BN);
     const int64_t n = (int64_t)taps * w.Np * w.Kp;
-    w.hi = ar.take<__nv_bfloat16>(n);
-    w.lo = ar.take<__nv_bfloat16>(n);
+    w.hi = ar.take<op16_t>(n);
+    w.lo = ar.take<op16_t>(n);
     w.valid = true;
 }
 
@@ -726,8 +793,8 @@ void gemm_tc_plan_scratch(GemmScratch &gs, int64_t rows, int T, int maxk, Arena 
     if (cap < min_rows) cap = min_rows;
     gs.rows_cap = cap;
     gs.kp_cap = (int)align_up(maxk, 8);
-    gs.a_hi = ar.take<__nv_bfloat16>(cap * gs.kp_cap);
-    gs.a_lo = ar.take<__nv_bfloat16>(cap * gs.kp_cap);
+    gs.a_hi = ar.take<op16_t>(cap * gs.kp_cap);
+    gs.a_lo = ar.take<op16_t>(cap * gs.kp_cap);
     gs.valid = true;
 }
 
@@ -802,6 +869,81 @@ int gemm_tc_combine(cudaStream_t st, const float *y1, bool y1_scalar, const floa
     k_combine_split<<<(unsigned)blocks, 256, 0, st>>>(p);
     if (launches) ++*launches;
     NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// BLSTM recurrence for hidden sizes the persistent kernel cannot hold (4H + H/2 > 512 TMEM columns, W_hh
+// larger than one SM's shared memory): ONE tcgen05 GEMM launch per timestep,
+//   z_t = h_{t-1} . W_hh   for every window and both directions (M = 2 * windows, N = 4H, K = H, fp16x3),
+// whose epilogue adds the projected gates, applies the fused cell update and writes h_t three ways: fp32 layer
+// output, and the bf16 hi/lo operand planes of the next step (ping-pong buffers: other CTAs still read h_{t-1}).
+// W_hh hi/lo (1 MB at H = 256) stays L2-resident across the T launches; c lives in HBM as fp32.
+// ------------------------------------------------------------------------------------------
+__global__ void k_pack_whh_kn(const float *__restrict__ kernel_fw, const float *__restrict__ kernel_bw, int D, int H,
+                              float *__restrict__ out) {   // out [2][H][4H], column u*4 + g, pre-scaled
+    const int N = 4 * H;
+    const int64_t total = 2LL * H * N;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int n = (int)(i % N), k = (int)((i / N) % H), dir = (int)(i / ((int64_t)N * H));
+        const int u = n >> 2, g = n & 3;
+        const float *kern = dir ? kernel_bw : kernel_fw;
+        out[i] = (g == 1 ? LSTM_PRESCALE_J : LSTM_PRESCALE_IFO) * kern[(int64_t)(D + k) * N + g * H + u];
+    }
+}
+
+bool gemm_tc_lstm_supported(int H) { return H >= 64 && H % 8 == 0; }
+
+void gemm_tc_plan_whh(GemmWeights &w, int H, Arena &ar, float **staging) {
+    gemm_tc_plan_weights(w, 2, H, 4 * H, ar);        // "taps" = the two directions
+    *staging = w.valid ? ar.take<float>(2LL * H * 4 * H) : nullptr;
+}
+
+int gemm_tc_pack_whh(cudaStream_t st, const float *kernel_fw, const float *kernel_bw, int D, int H, float *staging,
+                     GemmWeights &w) {
+    if (!w.valid) return NTB_OK;
+    k_pack_whh_kn<<<512, 256, 0, st>>>(kernel_fw, kernel_bw, D, H, staging);
+    NTB_LAUNCH_CHECK();
+    return gemm_tc_pack_weights(st, staging, w);
+}
+
+int64_t gemm_tc_lstm_state_floats(int64_t n_windows, int H) { return 2 * n_windows * H; }
+
+int gemm_tc_lstm_layer(cudaStream_t st, const GemmWeights &whh, const float *xproj, int ldx, const int32_t *lens,
+                       int64_t n_windows, int T, int H, float *cstate, float *out, int ldo, const GemmScratch &gs,
+                       int64_t *launches) {
+    const int cg = gemm_cta_group();
+    const int64_t Mp = align_up(n_windows, 2 * BM);                 // a CTA pair never straddles the directions
+    const int64_t plane_elems = 2 * Mp * H;                          // one parity: [2 dirs][Mp][H]
+    if (!whh.valid || !gs.valid || whh.K != H || whh.N != 4 * H || whh.BN % 16 ||
+        2 * plane_elems > gs.rows_cap * (int64_t)gs.kp_cap || (ldx & 3) || (ldo & 3) || H % 8)
+        return fail(NTB_EINVAL, "tcgen05 LSTM step: operand not supported (windows %s%lld, H %lld)", "",
+                    (long long)n_windows, (long long)H);
+    // h_0 = 0 (both parities: pad rows are never written), c_0 = 0
+    NTB_CUDA(cudaMemsetAsync(gs.a_hi, 0, 2 * plane_elems * sizeof(op16_t), st));
+    NTB_CUDA(cudaMemsetAsync(gs.a_lo, 0, 2 * plane_elems * sizeof(op16_t), st));
+    NTB_CUDA(cudaMemsetAsync(cstate, 0, gemm_tc_lstm_state_floats(n_windows, H) * sizeof(float), st));
+    CUtensorMap ma_hi[2], ma_lo[2], mb_hi, mb_lo;
+    for (int par = 0; par < 2; ++par) {
+        NTB_TRY(make_map(&ma_hi[par], gs.a_hi + par * plane_elems, 2 * Mp, H, BM));
+        NTB_TRY(make_map(&ma_lo[par], gs.a_lo + par * plane_elems, 2 * Mp, H, BM));
+    }
+    NTB_TRY(make_map(&mb_hi, whh.hi, 2LL * whh.Np, whh.Kp, whh.BN / cg));
+    NTB_TRY(make_map(&mb_lo, whh.lo, 2LL * whh.Np, whh.Kp, whh.BN / cg));
+    GemmWeights w1 = whh;
+    w1.taps = 1;                                                     // the second "tap" is the bw direction's W_hh
+    TcParams p{};
+    NTB_TRY(fill_params(p, w1, 2 * Mp));
+    p.T = T; p.pad = 0; p.out_rows = n_windows * T; p.bias = nullptr; p.out = out; p.ldo = ldo;
+    p.lstm_H = H; p.lstm_mt_dir = (int)(Mp / BM); p.lstm_n = n_windows; p.lstm_Mp = Mp;
+    p.lstm_x = xproj; p.lstm_ldx = ldx; p.lstm_c = cstate; p.lstm_lens = lens;
+    for (int s = 0; s < T; ++s) {
+        const int rd = s & 1, wr = rd ^ 1;
+        p.lstm_s = s;
+        p.lstm_hi = gs.a_hi + wr * plane_elems;
+        p.lstm_lo = gs.a_lo + wr * plane_elems;
+        NTB_TRY(do_launch(st, ma_hi[rd], ma_lo[rd], mb_hi, mb_lo, ma_hi[rd], p, launches));
+    }
     return NTB_OK;
 }
 

@@ -1,4 +1,4 @@
-// tcgen05 / TMA / TMEM GEMM (bf16x3 split operands) -- interface; implementation in ntb_gemm_tc.cu.
+// tcgen05 / TMA / TMEM GEMM (fp16x3 split operands) -- interface; implementation in ntb_gemm_tc.cu.
 #pragma once
 #include "ntb_common.cuh"
 
@@ -9,14 +9,14 @@ struct GemmWeights {
     bool valid = false;
     bool single_pass = false;   // hi*hi only (plain bf16; measurement / ablation only)
     int taps = 1, K = 0, N = 0, Kp = 0, Np = 0, BN = 0;
-    __nv_bfloat16 *hi = nullptr, *lo = nullptr;   // [taps][Np][Kp], Kp = K rounded up to 64
+    op16_t *hi = nullptr, *lo = nullptr;   // [taps][Np][Kp], Kp = K rounded up to 64
 };
 // bf16 hi/lo planes of the A operand for one GEMM (rewritten by every call).
 struct GemmScratch {
     bool valid = false;
     int64_t rows_cap = 0;
     int kp_cap = 0;
-    __nv_bfloat16 *a_hi = nullptr, *a_lo = nullptr;   // [plane rows][K] of the GEMM in flight
+    op16_t *a_hi = nullptr, *a_lo = nullptr;   // [plane rows][K] of the GEMM in flight
 };
 
 void gemm_tc_plan_weights(GemmWeights &w, int taps, int K, int N, Arena &ar);
@@ -41,5 +41,17 @@ int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, co
 int gemm_tc_combine(cudaStream_t st, const float *y1, bool y1_scalar, const float *a1, const float *b1,
                     const float *y2, const float *a2, const float *b2, const int32_t *win_group, int T, int C,
                     int64_t rows, float *out, const GemmScratch *planes, int layout, int64_t *launches);
+
+// BLSTM recurrence as one tcgen05 GEMM launch per timestep (hidden sizes beyond the persistent kernel, e.g. H = 256):
+// see ntb_gemm_tc.cu.  whh = [2 dirs][4H][H] hi/lo planes (plan/pack below); xproj row-major [n*T][ldx] with column
+// dir*4H + u*4 + g, pre-scaled like whh (k_repack_lstm prescale = 1); cstate = gemm_tc_lstm_state_floats() floats.
+bool gemm_tc_lstm_supported(int H);
+void gemm_tc_plan_whh(GemmWeights &w, int H, Arena &ar, float **staging);
+int gemm_tc_pack_whh(cudaStream_t st, const float *kernel_fw, const float *kernel_bw, int D, int H, float *staging,
+                     GemmWeights &w);
+int64_t gemm_tc_lstm_state_floats(int64_t n_windows, int H);
+int gemm_tc_lstm_layer(cudaStream_t st, const GemmWeights &whh, const float *xproj, int ldx, const int32_t *lens,
+                       int64_t n_windows, int T, int H, float *cstate, float *out, int ldo, const GemmScratch &gs,
+                       int64_t *launches);
 
 }  // namespace ntb

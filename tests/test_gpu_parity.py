@@ -109,7 +109,8 @@ def test_conv_bn_matches_oracle(lib, Cin, Cout, k, relu, bn):
 
 # ------------------------------------------------------------------ BLSTM
 @pytest.mark.parametrize("D,H,T,n", [(12, 5, 30, 80), (256, 100, 100, 70), (200, 100, 100, 130), (7, 33, 17, 65),
-                                     (16, 128, 12, 9), (64, 64, 40, 300), (128, 68, 25, 129), (72, 96, 7, 3)])
+                                     (16, 128, 12, 9), (64, 64, 40, 300), (128, 68, 25, 129), (72, 96, 7, 3),
+                                     (512, 256, 100, 40), (12, 256, 30, 300), (96, 200, 9, 257)])
 def test_blstm_matches_oracle(lib, D, H, T, n):
     rng = np.random.default_rng(D * H + T)
     lim = np.sqrt(6.0 / (D + 5 * H))
@@ -132,8 +133,10 @@ def test_blstm_matches_oracle(lib, D, H, T, n):
     # H = 100 shapes run the tcgen05 projection + tensor-core recurrence (bf16x3 split operands,
     # ~2^-16 relative per product, 100 dependent steps): measured max error 8e-5; the fp32 SIMT
     # shapes hold 2e-5.  Both are far inside the 1e-3 logits budget checked on whole models below.
+    # H >= 64 beyond that kernel (128, 200, 256: BASELINE.json configs[4]) run one tcgen05 GEMM per timestep.
     tc_path = H % 4 == 0 and 16 <= H <= 100 and D % 8 == 0 and D >= 64
-    np.testing.assert_allclose(got, ref, atol=2e-4 if tc_path else 2e-5, rtol=0)
+    step_path = not tc_path and H >= 64 and H % 8 == 0
+    np.testing.assert_allclose(got, ref, atol=2e-4 if (tc_path or step_path) else 2e-5, rtol=0)
     mask = (np.arange(T)[None, :] >= lens[:, None]).reshape(-1)
     assert np.all(got[mask] == 0.0)                    # dynamic_rnn zeros beyond seq_len, exactly
 
@@ -235,6 +238,26 @@ def test_label_agreement_with_diverse_labels():
     report = near_tie_report(logits, ref, LOGIT_TOL * gain)
     assert 1.0 - len(report) / float(len(ref)) >= 0.999
     assert all(gap <= 2 * LOGIT_TOL * gain for _, gap in report), report[:10]
+
+
+def test_stress_blstm256_model_matches_oracle():
+    # BASELINE.json configs[4]: 5 x BLSTM(256), CrossEntropy over 1025 classes, len_x 12, T 100 (ragged lengths)
+    net, Cc, T = syn.NETWORKS["stress_blstm256"], 1025, 100
+    w = syn.random_weights(net, 12, Cc, seed=31, graph="CrossEntropy")
+    rng = np.random.default_rng(30)
+    n = 24
+    x = rng.standard_normal((n, T, 12)).astype(np.float32)
+    lens = rng.integers(1, T + 1, n).astype(np.int32)
+    lens[:2] = [T, 0]
+    m, labels, llen, logits = _run_model(net, w, "CrossEntropy", T, 12, Cc, x, lens, None)
+    ref, ref_labels = A.forward_batch(x, lens, net, w, "CrossEntropy")
+    ref = ref.reshape(-1, Cc)
+    err = float(np.abs(logits - ref).max())
+    assert err <= LOGIT_TOL, err
+    report = near_tie_report(logits, ref, LOGIT_TOL)
+    agree = 1.0 - len(report) / float(ref.shape[0])
+    assert agree >= 0.999 and all(gap <= 2 * LOGIT_TOL for _, gap in report), (agree, report[:10])
+    assert m.last_launches() >= 5 * T                       # one recurrence GEMM per timestep and layer
 
 
 def test_chunking_and_host_device_paths_are_bit_identical():
