@@ -45,6 +45,8 @@ def parse():
     ap.add_argument("--windows", type=int, default=1048576, help="windows per GPU per step")
     ap.add_argument("--cpu-windows", type=int, default=0,
                     help="windows in the CPU baseline sample (0 = auto-size to ~10-20 s)")
+    ap.add_argument("--chunk-windows", type=int, default=0,
+                    help="windows per forward call (0 = as many as the workspace budget allows)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end (host buffers) leg")
     return ap.parse_args()
@@ -249,7 +251,7 @@ def run_b200(args):
     x_pin = torch.from_numpy(x).pin_memory()
     lens_pin = torch.from_numpy(lens).pin_memory()
     x_d, lens_d = x_pin.to(dev), lens_pin.to(dev)
-    chunks = engine.plan_chunks(goff, m.max_chunk_windows())
+    chunks = engine.plan_chunks(goff, args.chunk_windows or m.max_chunk_windows(), m.chunk_align())
     chunk_goff = [torch.from_numpy(np.ascontiguousarray(goff[g:h + 1] - goff[g], dtype=np.int32)).to(dev)
                   for g, h in chunks]
     labels_d = torch.empty(n * T, dtype=torch.int32, device=dev)

@@ -337,6 +337,7 @@ struct Workspace {
     float *y1, *y2a, *y2b;
     float *aff[8];
     float *xproj;
+    float2 *bn_part;
     float *cstate;
     float *logits;
     GemmScratch gs;
@@ -361,6 +362,7 @@ static int64_t plan_workspace(const ntb_model *m, int64_t n, int64_t n_groups, b
     // the tensor-core recurrence works on whole 128-window tiles (time-major), tail tile padded
     const int64_t tile_rows = m->any_tc_rec ? align_up(n, LSTM_TC_ROWS) * m->T : 0;
     ws.xproj = m->max_proj_n ? ar.take<float>((tile_rows > rows ? tile_rows : rows) * m->max_proj_n) : nullptr;
+    ws.bn_part = nullptr;   // set below, once the operand planes are sized
     ws.cstate = m->max_step_h ? ar.take<float>(gemm_tc_lstm_state_floats(n, m->max_step_h)) : nullptr;
     const bool small_c = m->C <= 8;
     ws.logits = (!small_c && own_logits) ? ar.take<float>(rows * m->C) : nullptr;
@@ -373,6 +375,7 @@ static int64_t plan_workspace(const ntb_model *m, int64_t n, int64_t n_groups, b
     // the per-timestep recurrence keeps its h operand planes (2 parities x 2 dirs x padded windows x H) in the same scratch
     const int64_t step_rows = m->max_step_h ? cdiv(4 * align_up(n, 256) * m->max_step_h, align_up(maxk, 8)) : 0;
     gemm_tc_plan_scratch(ws.gs, rows, m->T, maxk, ar, tile_rows > step_rows ? tile_rows : step_rows);
+    if (m->has_res && ws.gs.valid && m->T >= 32) ws.bn_part = ar.take<float2>(gemm_tc_bn_part_elems(ws.gs, m->max_res_c));
     return ar.off;
 }
 }  // namespace ntb
@@ -418,8 +421,18 @@ static int residual_forward(Ctx &cx, ntb_model *m, const LayerDev &ld, const flo
             // conv1 and conv2a are both 1x1 convs of the layer input: one operand split serves both
             const bool reuse = (c == 1 && ld.convw[0].valid) || (c == 0 && in_planes);
             const bool expand = k1 && c == 2;
+            // BN statistics ride in the GEMM epilogue (partials) and are folded per group right after
+            float2 *part = ld.bn_scale[c] ? ws.bn_part : nullptr;
             NTB_TRY(gemm_tc_conv(cx.st, expand ? in : A, K, rows, T, fa, fb, ws.win_group, src_of[c] >= 0, ld.convw[c],
-                                 ys[c], C, ws.gs, &cx.launches, reuse, expand));
+                                 ys[c], C, ws.gs, &cx.launches, reuse, expand, part));
+            if (part) {
+                dim3 grid((unsigned)n_groups, cdiv(C, 256));
+                k_bn_finish<<<grid, 256, 0, cx.st>>>(part, C, T, taps[c] == 3 ? T + 2 : T, group_off, ld.bn_scale[c],
+                                                     ld.bn_offset[c], 1e-5f, aa[c], bb[c]);
+                cx.count();
+                NTB_LAUNCH_CHECK();
+                continue;
+            }
         } else {
             ConvGemmParams p{};
             p.A = A; p.lda = K; p.W = ld.conv[c]; p.bias = nullptr;

@@ -53,6 +53,10 @@ struct TcParams {
     int ldo;
     int tma_store;         // plain row-major output through smem staging + cp.async.bulk.tensor stores
     int xproj_H;           // > 0: out is the recurrence's unit-major projected-gates layout (ntb_lstm_tc.cuh)
+    // fused batch-norm statistics (bn_part != null): every epilogue warp reduces its 32 rows x 32 columns to per-column
+    // (sum, sum of squares), split at the window boundary inside the block (T >= 32: at most one), and
+    // writes bn_part[(block * 2 + seg) * N + n]; k_bn_finish folds the partials of each BN group (ntb_kernels.cuh)
+    float2 *bn_part;
     // LSTM timestep mode (lstm_H > 0): this GEMM is h_{t-1} . W_hh of ONE timestep for all windows and both
     // directions (A rows = [dir][Mp windows], B rows = [dir][Np]); the epilogue adds the projected gates and runs
     // the fused cell update (see gemm_tc_lstm_layer)
@@ -63,6 +67,34 @@ struct TcParams {
     const int32_t *lstm_lens;
     op16_t *lstm_hi, *lstm_lo;  // h_t operand planes of the NEXT step [2][Mp][H]
 };
+
+// Column statistics of one staged [32 rows][32 cols] fp32 tile (128-byte swizzled rows): lane = column; rows
+// [0, split) belong to the first window of the block (segment 0), [split, 32) to the next (segment 1); rows whose
+// bit in vmask is clear (padding rows of the 1x3 layout, rows past the end) are skipped.
+__device__ __forceinline__ void bn_partials(const uint8_t *buf, int lane, uint32_t vmask, int split, float2 *part,
+                                            int64_t rec0, int N, int n) {
+    // <= 32 values per record: fp32 with four interleaved chains per segment (row i -> chain i & 3), folded in a
+    // fixed order -> bit-stable; the records are combined in fp64 (k_bn_finish)
+    float s0[4] = {0, 0, 0, 0}, q0[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0}, q1[4] = {0, 0, 0, 0};
+    const int cj = lane >> 2, ci = (lane & 3) << 2;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+        const float f = *reinterpret_cast<const float *>(buf + i * 128 + ((cj ^ (i & 7)) << 4) + ci);
+        const float v = ((vmask >> i) & 1u) ? f : 0.0f;
+        if (i < split) {
+            s0[i & 3] += v;
+            q0[i & 3] = fmaf(v, v, q0[i & 3]);
+        } else {
+            s1[i & 3] += v;
+            q1[i & 3] = fmaf(v, v, q1[i & 3]);
+        }
+    }
+    if (n < N) {
+        part[rec0 * N + n] = make_float2((s0[0] + s0[1]) + (s0[2] + s0[3]), (q0[0] + q0[1]) + (q0[2] + q0[3]));
+        if (split < 32)
+            part[(rec0 + 1) * N + n] = make_float2((s1[0] + s1[1]) + (s1[2] + s1[3]), (q1[0] + q1[1]) + (q1[2] + q1[3]));
+    }
+}
 
 // CG = 1: one CTA per tile (M = 128).  CG = 2: CTA pair (cluster of 2, tcgen05 cta_group::2, M = 256): each CTA loads
 // its own 128 A rows and HALF of the B tile, the leader issues the MMAs for both SMs, so the B operand
@@ -215,6 +247,16 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
             row_ok = row_ok && orow < p.out_rows;
             float *orow_ptr = p.out + orow * (int64_t)p.ldo;
             const int n0 = n_tile * p.BN;
+            // fused BN statistics: which of this warp's 32 rows are real output rows, and where the window changes
+            uint32_t bn_vmask = 0;
+            int bn_split = 32;
+            if (p.bn_part) {
+                const int Tp = p.pad ? p.T + 2 : p.T;
+                const int64_t w_lane = prow / Tp, w_first = __shfl_sync(0xffffffffu, w_lane, 0);
+                bn_vmask = __ballot_sync(0xffffffffu, row_ok);
+                const uint32_t diff = __ballot_sync(0xffffffffu, w_lane != w_first);
+                bn_split = diff ? __ffs(diff) - 1 : 32;
+            }
             for (int c0 = 0; c0 < p.BN; c0 += 32) {
                 uint32_t r[32];
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256 + c0);
@@ -251,6 +293,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                         tma_store_2d(&map_out, buf, nb, (int)(m_tile * BM) + q * 32);
                         bulk_commit_group();
                     }
+                    if (p.bn_part) bn_partials(buf, lane, bn_vmask, bn_split, p.bn_part, (m_tile * 4 + q) * 2, p.N, nb + lane);
                 } else if (p.lstm_H > 0) {
                     // thread = one window of one direction; this chunk = 8 hidden units x (i, j, f, o)
                     const int H = p.lstm_H, nb = n0 + c0;
@@ -318,7 +361,21 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                         dst += BM;
                         if (++u == H) { u = 0; dst += dir_stride - (int64_t)H * BM; }
                     }
-                } else if (row_ok) {
+                } else {
+                  if (p.bn_part) {
+                    // statistics of the tile (direct-store path, e.g. the padded-row 1x3 conv): stage, reduce columns
+                    uint8_t *buf = stage_buf + (stage_it & 1) * 4096;
+                    ++stage_it;
+                    __syncwarp();
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        *reinterpret_cast<float4 *>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                            make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                        __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+                    __syncwarp();
+                    bn_partials(buf, lane, bn_vmask, bn_split, p.bn_part, (m_tile * 4 + q) * 2, p.N, n0 + c0 + lane);
+                  }
+                  if (row_ok) {
                     const int nb = n0 + c0;
                     if (vec_ok && nb + 32 <= p.N && c0 + 32 <= p.BN) {
 #pragma unroll
@@ -339,6 +396,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                                 orow_ptr[n] = __uint_as_float(r[i]) + (p.bias ? p.bias[n] : 0.0f);
                         }
                     }
+                  }
                 }
             }
             tc_fence_before();
@@ -719,7 +777,8 @@ int do_launch(cudaStream_t st, const CUtensorMap &ma_hi, const CUtensorMap &ma_l
 }
 
 int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, int64_t plane_rows, int T, int pad,
-                int64_t out_rows, const float *bias, float *out, int ldo, int64_t *launches, int xproj_H = 0) {
+                int64_t out_rows, const float *bias, float *out, int ldo, int64_t *launches, int xproj_H = 0,
+                float2 *bn_part = nullptr) {
     const int cg = gemm_cta_group();
     CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
     NTB_TRY(make_map(&ma_hi, gs.a_hi, plane_rows, w.K, BM));
@@ -730,6 +789,7 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     NTB_TRY(fill_params(p, w, plane_rows));
     p.T = T; p.pad = pad; p.out_rows = out_rows; p.bias = bias; p.out = out; p.ldo = ldo;
     p.xproj_H = xproj_H;
+    p.bn_part = bn_part;
     // coalesced TMA-store epilogue for plain row-major outputs (N tiles of whole 32-column chunks)
     p.tma_store = (!pad && xproj_H == 0 && w.BN % 32 == 0 && (ldo & 3) == 0 &&
                    (reinterpret_cast<uintptr_t>(out) & 15) == 0) ? 1 : 0;
@@ -830,7 +890,7 @@ int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_window
 
 int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, const float *aff_a,
                  const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
-                 int ldo, const GemmScratch &gs, int64_t *launches, bool reuse_planes, bool expand) {
+                 int ldo, const GemmScratch &gs, int64_t *launches, bool reuse_planes, bool expand, float2 *bn_part) {
     const int pad = w.taps == 3;
     const int64_t windows = rows / T;
     const int64_t plane_rows = pad ? windows * (T + 2) : rows;
@@ -843,7 +903,12 @@ int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, co
     if (expand) sp.lda = 1;
     sp.hi = gs.a_hi; sp.lo = w.single_pass ? nullptr : gs.a_lo; sp.plane_rows = plane_rows;
     if (!reuse_planes) NTB_TRY(launch_split(st, sp, launches));   // else: the previous conv split the same input
-    return launch_gemm(st, w, gs, plane_rows, T, pad, rows, nullptr, out, ldo, launches);
+    if (bn_part && T < 32) return fail(NTB_EINVAL, "tcgen05 conv: fused BN statistics need T >= 32%s", "");
+    return launch_gemm(st, w, gs, plane_rows, T, pad, rows, nullptr, out, ldo, launches, 0, bn_part);
+}
+
+int64_t gemm_tc_bn_part_elems(const GemmScratch &gs, int C) {
+    return gs.valid ? (gs.rows_cap / 32 + 1) * 2 * (int64_t)C : 0;   // double2 records
 }
 
 int gemm_tc_combine(cudaStream_t st, const float *y1, bool y1_scalar, const float *a1, const float *b1,

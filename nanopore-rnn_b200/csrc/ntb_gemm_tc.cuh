@@ -34,7 +34,12 @@ int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_window
 int make_map_xproj(void *map_out, const float *xproj, int64_t units_total);
 int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, const float *aff_a,
                  const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
-                 int ldo, const GemmScratch &gs, int64_t *launches, bool reuse_planes = false, bool expand = false);
+                 int ldo, const GemmScratch &gs, int64_t *launches, bool reuse_planes = false, bool expand = false,
+                 float2 *bn_part = nullptr);
+// bn_part (optional): the GEMM epilogue also emits per-(32-row block, window segment, channel) (sum, sum of
+// squares) partials of the conv output -- [(block * 2 + seg) * C + c], block = plane row / 32, plane rows per
+// window = T (1x1) or T + 2 (1x3) -- which k_bn_finish folds per BN group (no extra pass over the output).
+int64_t gemm_tc_bn_part_elems(const GemmScratch &gs, int C);
 // residual_layer tail relu(bn?(branch1) + bn(conv2c)) written as fp32 (`out`, may be null) and/or straight into the
 // operand planes of the next GEMM: layout 0 = none, 1 = plain rows (next 1x1 convs), 2 = time-major tiles (projection).
 // y1_scalar: branch1 is a Cin = 1 conv folded into (a1, b1): value = y1[r] * a1[g][c] + b1[g][c].

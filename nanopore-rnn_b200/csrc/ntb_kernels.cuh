@@ -240,6 +240,42 @@ __global__ void __launch_bounds__(BN_CH4 * BN_SLICES) k_bn_stats(const float *__
     }
 }
 
+// Same affine from the partial sums the tcgen05 conv epilogue emitted (ntb_gemm_tc.cu, bn_partials): record
+// (block, seg) holds the fp32 (sum, sum of squares) of the rows of plane-row block `block` (32 rows) that belong to
+// the block's first window (seg 0) or to the next one (seg 1); a window occupies Tp plane rows (T, or T + 2 in the
+// padded 1x3 layout whose padding rows were left out).  One thread per channel, records folded in fp64 in block order -> bit-stable.
+__global__ void __launch_bounds__(256) k_bn_finish(const float2 *__restrict__ part, int C, int T, int Tp,
+                                                   const int32_t *__restrict__ group_off,
+                                                   const float *__restrict__ scale, const float *__restrict__ offset,
+                                                   float eps, float *__restrict__ aff_a, float *__restrict__ aff_b) {
+    const int g = blockIdx.x;
+    const int ch = blockIdx.y * 256 + threadIdx.x;
+    if (ch >= C) return;
+    const int64_t wa = group_off[g], wb = group_off[g + 1];
+    const int64_t n = (wb - wa) * T;
+    double ss = 0.0, qq = 0.0;
+    if (wb > wa) {
+        const int64_t b0 = (wa * Tp) >> 5, b1 = (wb * Tp - 1) >> 5;
+        for (int64_t b = b0; b <= b1; ++b) {
+            const int64_t w_first = (b << 5) / Tp, w_last = ((b << 5) + 31) / Tp;
+            if (w_first >= wa && w_first < wb) {
+                const float2 v = part[(b * 2) * C + ch];
+                ss += v.x; qq += v.y;
+            }
+            if (w_last != w_first && w_last >= wa && w_last < wb) {
+                const float2 v = part[(b * 2 + 1) * C + ch];
+                ss += v.x; qq += v.y;
+            }
+        }
+    }
+    const double mean = n > 0 ? ss / (double)n : 0.0;
+    double var = n > 0 ? qq / (double)n - mean * mean : 0.0;
+    var = var < 0.0 ? 0.0 : var;
+    const float a = (1.0f / sqrtf((float)var + eps)) * scale[ch];
+    aff_a[(int64_t)g * C + ch] = a;
+    aff_b[(int64_t)g * C + ch] = offset[ch] - (float)mean * a;
+}
+
 // Cin = 1 convs (the first residual layer of the CtcLoss graphs, network.py:515-518 reshapes x to [B,T,1]):
 // a 1x1 conv of a single channel is the outer product y[r][n] = x[r] * w[n], so it is never materialised.
 // Its batch moments are those of x scaled: mean_y = w mean_x, var_y = w^2 var_x, and BN(y) = A x + B with

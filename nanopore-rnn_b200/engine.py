@@ -44,9 +44,14 @@ def group_offsets(read_window_counts, batch_size):
     return np.asarray(offs, dtype=np.int32)
 
 
-def plan_chunks(group_off, max_windows):
+def plan_chunks(group_off, max_windows, align=1):
     """Split [0, n_groups) into runs of whole groups with <= max_windows windows each, preferring
-    a multiple of one recurrence wave (64 windows x 74 tiles x 2 directions = 148 CTAs)."""
+    a multiple of one recurrence wave (64 windows x 74 tiles x 2 directions = 148 CTAs).
+
+    ``align`` (Model.chunk_align()): cuts are placed where the window count so far is a multiple of it whenever
+    such a group boundary exists inside the limit.  The conv epilogue sums the batch-norm statistics in 32-row
+    blocks counted from the start of a chunk; with aligned cuts those blocks -- hence every bit of the result --
+    are the same however the job is cut (unaligned cuts differ by fp32 rounding of the block sums, ~1e-7)."""
     group_off = np.asarray(group_off, dtype=np.int64)
     n_groups = len(group_off) - 1
     total = int(group_off[-1])
@@ -60,6 +65,10 @@ def plan_chunks(group_off, max_windows):
     while g < n_groups:
         limit = group_off[g] + target
         h = int(np.searchsorted(group_off, limit, side="right")) - 1
+        if align > 1 and h > g and h < n_groups:
+            ok = np.nonzero(group_off[g + 1:h + 1] % align == 0)[0]
+            if len(ok):
+                h = g + 1 + int(ok[-1])
         if h <= g:
             h = g + 1
             if group_off[h] - group_off[g] > max_windows:
@@ -157,6 +166,15 @@ class Model:
             self._ws = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
         return self._ws
 
+    def chunk_align(self):
+        """Window-count multiple at which chunk cuts keep the fused BN statistics bit-identical (plan_chunks)."""
+        if not any(l["type"] == "residual_layer" for l in self.network) or self.T < 32:
+            return 1
+        a = 1
+        for tp in (self.T, self.T + 2):          # plane rows per window: 1x1 convs, padded 1x3 conv
+            a = int(np.lcm(a, 32 // int(np.gcd(tp, 32))))
+        return a
+
     def max_chunk_windows(self, budget_bytes=None, groups_per_window=0.1):
         """Largest chunk whose workspace fits ``budget_bytes`` (default: 60 % of free HBM)."""
         if budget_bytes is None:
@@ -215,7 +233,7 @@ class Model:
         logits = _pinned((n * T, Cc), torch.float32) if want_logits else None
         if n == 0:
             return self._shape_labels(labels, n), llen, logits
-        chunks = plan_chunks(group_off, max_windows or self.max_chunk_windows())
+        chunks = plan_chunks(group_off, max_windows or self.max_chunk_windows(), self.chunk_align())
         stream = _stream_ptr(self.device)
         with torch.cuda.device(self.device):
             wmax = max(int(group_off[h] - group_off[g]) for g, h in chunks)

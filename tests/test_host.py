@@ -58,8 +58,18 @@ def test_plan_chunks_whole_groups():
     sizes = [int(goff[b] - goff[a]) for a, b in chunks]
     assert max(sizes) <= 9472 and sum(sizes) == 30007
     assert sizes[0] == 9470                       # largest multiple of the group size under 2 waves
+    # aligned cuts (Model.chunk_align(): the fused BN statistics stay bit-identical under re-chunking)
+    chunks = engine.plan_chunks(goff, 9472, align=16)
+    sizes = [int(goff[b] - goff[a]) for a, b in chunks]
+    assert sum(sizes) == 30007 and max(sizes) <= 9472
+    assert all(int(goff[b]) % 16 == 0 for a, b in chunks[:-1])
+    assert sizes[0] == 9440                       # largest multiple of lcm(10, 16) = 80 windows under the limit
+    # no aligned boundary available: falls back to plain group boundaries
+    odd = engine.group_offsets([25] * 8, 20)
+    chunks = engine.plan_chunks(odd, 64, align=16)
+    assert [int(odd[b] - odd[a]) for a, b in chunks] == [50, 50, 50, 50]
     with pytest.raises(ValueError):
-        engine.plan_chunks(np.array([0, 100]), 64) if False else engine.plan_chunks(np.array([0, 100, 200]), 64)
+        engine.plan_chunks(np.array([0, 100, 200]), 64)
 
 
 def test_signal_dataset_windows_and_job(tmp_path):
