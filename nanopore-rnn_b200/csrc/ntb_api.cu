@@ -423,11 +423,19 @@ static int residual_forward(Ctx &cx, ntb_model *m, const LayerDev &ld, const flo
             const bool expand = k1 && c == 2;
             // BN statistics ride in the GEMM epilogue (partials) and are folded per group right after
             float2 *part = ld.bn_scale[c] ? ws.bn_part : nullptr;
-            NTB_TRY(gemm_tc_conv(cx.st, expand ? in : A, K, rows, T, fa, fb, ws.win_group, src_of[c] >= 0, ld.convw[c],
-                                 ys[c], C, ws.gs, &cx.launches, reuse, expand, part));
+            // conv2b / conv2c: the producer's BN + ReLU + operand split run inside the GEMM (transform warps)
+            const bool fused = src_of[c] >= 0 && !expand && gemm_tc_conv_fused_supported(ld.convw[c], K, T, C);
+            int tp = taps[c] == 3 ? T + 2 : T;
+            if (fused) {
+                NTB_TRY(gemm_tc_conv_fused(cx.st, A, K, rows, T, fa, fb, ws.win_group, 1, ld.convw[c], ys[c], C, &cx.launches, part));
+                tp = T;
+            } else {
+                NTB_TRY(gemm_tc_conv(cx.st, expand ? in : A, K, rows, T, fa, fb, ws.win_group, src_of[c] >= 0, ld.convw[c],
+                                     ys[c], C, ws.gs, &cx.launches, reuse, expand, part));
+            }
             if (part) {
                 dim3 grid((unsigned)n_groups, cdiv(C, 256));
-                k_bn_finish<<<grid, 256, 0, cx.st>>>(part, C, T, taps[c] == 3 ? T + 2 : T, group_off, ld.bn_scale[c],
+                k_bn_finish<<<grid, 256, 0, cx.st>>>(part, C, T, tp, group_off, ld.bn_scale[c],
                                                      ld.bn_offset[c], 1e-5f, aa[c], bb[c]);
                 cx.count();
                 NTB_LAUNCH_CHECK();

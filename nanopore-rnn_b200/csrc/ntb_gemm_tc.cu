@@ -417,6 +417,251 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
 }
 
 // ------------------------------------------------------------------------------------------
+// K2b'  conv GEMM with the operand transform fused in (conv2b / conv2c of residual_layer, network.py:385-400):
+//   out = conv( relu( y * a[g] + b[g] ) )        y = the previous conv's raw fp32 output, (a, b) its BN affine
+// The standalone split pass (read y, write fp16 hi/lo planes, read them back) is gone: warp 0 TMA-loads raw fp32
+// tiles of y, eight TRANSFORM warps apply affine + ReLU, split to fp16 hi/lo and write the 128-byte-swizzled UMMA
+// operand tiles in shared memory, the MMA warp of the pair's leader consumes them.  A 1x3 conv loads ONE raw tile of
+// 130 rows per k-block (rows r0-1 .. r0+128) and produces its three taps from it (zero rows outside the window =
+// SAME padding), so the padded plane layout is not needed either and the output goes out through TMA stores with the
+// BN partials (bn_partials) like the 1x1 convs.
+// CTA pair (cta_group::2, M = 256): each CTA transforms its own 128 rows and loads half of the weight tile.
+// Shared memory: 2 raw stages (33 KB) + 2 operand stages (A hi/lo 32 KB + B hi/lo <= 32 KB) + 16 KB staging.
+// ------------------------------------------------------------------------------------------
+constexpr int CF_THREADS = 512;                 // warps: 0 TMA, 1 MMA, 2 TMEM, 3 idle, 4-7 epilogue, 8-15 transform
+constexpr int CF_TWARPS = 8;
+constexpr int CF_RAW_STAGE = 33792;             // 130 rows x 64 fp32 = 33280, rounded to 1 KB
+constexpr int CF_RAW_STAGES = 2, CF_OP_STAGES = 2;
+constexpr int CF_EPI_BYTES = 4 * 4096;
+
+struct ConvFusedParams {
+    int64_t m_tiles, rows;
+    int N, K, taps, T, k_blocks, relu;
+    const float *aff_a, *aff_b;
+    const int32_t *win_group;
+    float2 *bn_part;
+};
+
+__global__ void __launch_bounds__(CF_THREADS, 1)
+k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant__ CUtensorMap map_b_hi,
+             const __grid_constant__ CUtensorMap map_b_lo, const __grid_constant__ CUtensorMap map_out,
+             const ConvFusedParams p) {
+    using namespace ptx;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t raw_full[CF_RAW_STAGES], raw_empty[CF_RAW_STAGES], op_full[CF_OP_STAGES], op_empty[CF_OP_STAGES],
+        acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_base_smem;
+
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    uint8_t *smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+    const int b_tile_bytes = (p.N / 2) * BK * 2;                       // this CTA's half of one B plane tile
+    const int op_stage_bytes = 2 * A_TILE_BYTES + 2 * b_tile_bytes;    // A_hi | A_lo | B_hi | B_lo
+    uint8_t *op_base = smem;
+    uint8_t *raw_base = op_base + CF_OP_STAGES * op_stage_bytes;
+    uint8_t *epi_base = raw_base + CF_RAW_STAGES * CF_RAW_STAGE;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();
+    const int64_t pairs = (p.m_tiles + 1) / 2;
+    const int64_t first = blockIdx.x / 2, step = gridDim.x / 2;
+    const int left = (p.taps - 1) / 2;
+    const int raw_rows = p.taps == 3 ? BM + 2 : BM;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&map_raw); prefetch_tmap(&map_b_hi); prefetch_tmap(&map_b_lo); prefetch_tmap(&map_out);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < CF_RAW_STAGES; ++s) { mbar_init(&raw_full[s], 1); mbar_init(&raw_empty[s], CF_TWARPS); }
+        for (int s = 0; s < CF_OP_STAGES; ++s) { mbar_init(&op_full[s], 1 + 2 * CF_TWARPS); mbar_init(&op_empty[s], 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 8); }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc_pair(&tmem_base_smem, TMEM_COLS);
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_smem;
+
+    if (warp == 0) {
+        // ===================== TMA producer: raw fp32 activation tiles + weight tiles =====================
+        if (lane == 0) {
+            int rs = 0, os = 0; uint32_t rph = 0, oph = 0;
+            for (int64_t it = first; it < pairs; it += step) {
+                const int64_t m_tile = it * 2 + rank;
+                for (int kb = 0; kb < p.k_blocks; ++kb) {
+                    mbar_wait_backoff(&raw_empty[rs], rph ^ 1, 100);
+                    mbar_expect_tx(&raw_full[rs], (uint32_t)(raw_rows * BK * 4));
+                    tma_load_2d(raw_base + rs * CF_RAW_STAGE, &map_raw, &raw_full[rs], kb * BK, (int)(m_tile * BM) - left);
+                    if (++rs == CF_RAW_STAGES) { rs = 0; rph ^= 1; }
+                    for (int tap = 0; tap < p.taps; ++tap) {
+                        mbar_wait_backoff(&op_empty[os], oph ^ 1, 101);
+                        uint8_t *s = op_base + os * op_stage_bytes + 2 * A_TILE_BYTES;
+                        const int brow0 = tap * p.N + rank * (p.N / 2);
+                        if (rank == 0) mbar_expect_tx(&op_full[os], (uint32_t)(4 * b_tile_bytes));   // both CTAs, both planes
+                        tma_load_2d_pair(s, &map_b_hi, &op_full[os], kb * BK, brow0);
+                        tma_load_2d_pair(s + b_tile_bytes, &map_b_lo, &op_full[os], kb * BK, brow0);
+                        if (++os == CF_OP_STAGES) { os = 0; oph ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader CTA) =====================
+        if (lane == 0 && rank == 0) {
+            const uint32_t idesc = idesc_f16_f32(2 * BM, p.N);
+            int os = 0; uint32_t oph = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            for (int64_t it = first; it < pairs; it += step) {
+                mbar_wait_backoff(&acc_empty[acc], acc_phase ^ 1, 102);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
+                for (int kb = 0; kb < p.k_blocks * p.taps; ++kb) {
+                    mbar_wait_backoff(&op_full[os], oph, 103);
+                    tc_fence_after();
+                    const uint32_t s = smem_u32(op_base + os * op_stage_bytes);
+                    const uint64_t a_hi = smem_desc_sw128(s), a_lo = smem_desc_sw128(s + A_TILE_BYTES);
+                    const uint64_t b_hi = smem_desc_sw128(s + 2 * A_TILE_BYTES);
+                    const uint64_t b_lo = smem_desc_sw128(s + 2 * A_TILE_BYTES + b_tile_bytes);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {
+                        umma_f16_pair(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_hi, k), idesc, (kb | k) != 0);
+                        umma_f16_pair(d_tmem, desc_advance_k16(a_lo, k), desc_advance_k16(b_hi, k), idesc, 1);
+                        umma_f16_pair(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_lo, k), idesc, 1);
+                    }
+                    umma_commit_pair(&op_empty[os], 3);
+                    if (++os == CF_OP_STAGES) { os = 0; oph ^= 1; }
+                }
+                umma_commit_pair(&acc_full[acc], 3);
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp >= 8) {
+        // ===================== transform: raw fp32 -> affine + ReLU -> fp16 hi/lo swizzled operand tiles ==========
+        // thread = 8 channels (one 16-byte operand chunk, j) of rows tw*16 + rsub + 4 i, i = 0..3
+        constexpr int RPT = BM / (4 * CF_TWARPS);                 // rows per thread
+        const int tw = warp - 8, j = lane & 7, rsub = lane >> 3;
+        int rs = 0, os = 0; uint32_t rph = 0, oph = 0;
+        for (int64_t it = first; it < pairs; it += step) {
+            const int64_t m_tile = it * 2 + rank;
+            int tpos[RPT], grp[RPT];                              // t of the row inside its window (-1000: no such row), BN group
+#pragma unroll
+            for (int i = 0; i < RPT; ++i) {
+                const int64_t grow = m_tile * BM + tw * (4 * RPT) + rsub + 4 * i;
+                if (grow < p.rows) {
+                    const int64_t w = grow / p.T;
+                    tpos[i] = (int)(grow - w * p.T);
+                    grp[i] = p.aff_a ? __ldg(p.win_group + w) : 0;
+                } else {
+                    tpos[i] = -1000; grp[i] = 0;
+                }
+            }
+            for (int kb = 0; kb < p.k_blocks; ++kb) {
+                mbar_wait(&raw_full[rs], rph, 200);
+                const uint8_t *raw = raw_base + rs * CF_RAW_STAGE;
+                const int c = kb * BK + j * 8;                    // first of this thread's 8 channels
+                for (int tap = 0; tap < p.taps; ++tap) {
+                    mbar_wait(&op_empty[os], oph ^ 1, 201);
+                    uint8_t *a_hi = op_base + os * op_stage_bytes, *a_lo = a_hi + A_TILE_BYTES;
+                    int gcur = -1;
+                    float a[8], b[8];
+#pragma unroll
+                    for (int i = 0; i < RPT; ++i) {
+                        const int row = tw * (4 * RPT) + rsub + 4 * i;
+                        const int tt = tpos[i] + tap - left;
+                        float v[8];
+                        if (tt >= 0 && tt < p.T) {                // same window as the output row: SAME padding otherwise
+                            const float4 x0 = *reinterpret_cast<const float4 *>(raw + (row + tap) * (BK * 4) + j * 32);
+                            const float4 x1 = *reinterpret_cast<const float4 *>(raw + (row + tap) * (BK * 4) + j * 32 + 16);
+                            v[0] = x0.x; v[1] = x0.y; v[2] = x0.z; v[3] = x0.w; v[4] = x1.x; v[5] = x1.y; v[6] = x1.z; v[7] = x1.w;
+                            if (p.aff_a) {
+                                if (grp[i] != gcur) {
+                                    gcur = grp[i];
+                                    const float4 a0 = __ldg(reinterpret_cast<const float4 *>(p.aff_a + (int64_t)gcur * p.K + c));
+                                    const float4 a1 = __ldg(reinterpret_cast<const float4 *>(p.aff_a + (int64_t)gcur * p.K + c + 4));
+                                    const float4 b0 = __ldg(reinterpret_cast<const float4 *>(p.aff_b + (int64_t)gcur * p.K + c));
+                                    const float4 b1 = __ldg(reinterpret_cast<const float4 *>(p.aff_b + (int64_t)gcur * p.K + c + 4));
+                                    a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+                                    b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+                                }
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) v[q] = fmaf(v[q], a[q], b[q]);
+                            }
+                            if (p.relu) {
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) v[q] = fmaxf(v[q], 0.0f);
+                            }
+                        } else {
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) v[q] = 0.0f;
+                        }
+                        uint4 h, l;
+                        split_op16x8(v, h, l);
+                        const int off = row * 128 + ((j ^ (row & 7)) << 4);
+                        *reinterpret_cast<uint4 *>(a_hi + off) = h;
+                        *reinterpret_cast<uint4 *>(a_lo + off) = l;
+                    }
+                    fence_proxy_async_smem();                     // generic-proxy stores -> visible to tcgen05.mma
+                    __syncwarp();
+                    if (lane == 0) { if (rank == 0) mbar_arrive(&op_full[os]); else mbar_arrive_cluster(&op_full[os], 0); }
+                    if (++os == CF_OP_STAGES) { os = 0; oph ^= 1; }
+                }
+                __syncwarp();                                     // every lane is done reading the raw stage
+                if (lane == 0) mbar_arrive(&raw_empty[rs]);
+                if (++rs == CF_RAW_STAGES) { rs = 0; rph ^= 1; }
+            }
+        }
+    } else if (warp >= 4) {
+        // ===================== epilogue: TMEM -> swizzled staging -> TMA store, BN partials =====================
+        const int q = warp & 3;
+        int acc = 0; uint32_t acc_phase = 0;
+        uint8_t *buf = epi_base + q * 4096;
+        for (int64_t it = first; it < pairs; it += step) {
+            const int64_t m_tile = it * 2 + rank;
+            mbar_wait(&acc_full[acc], acc_phase, 300);
+            tc_fence_after();
+            const int64_t prow = m_tile * BM + q * 32 + lane;
+            uint32_t bn_vmask = 0;
+            int bn_split = 32;
+            if (p.bn_part) {
+                const int64_t w_lane = prow / p.T, w_first = __shfl_sync(0xffffffffu, w_lane, 0);
+                bn_vmask = __ballot_sync(0xffffffffu, prow < p.rows);
+                const uint32_t diff = __ballot_sync(0xffffffffu, w_lane != w_first);
+                bn_split = diff ? __ffs(diff) - 1 : 32;
+            }
+            for (int c0 = 0; c0 < p.N; c0 += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256 + c0), r);
+                tmem_ld_wait();
+                if (lane == 0) bulk_wait_group_read<0>();          // the previous store has read the staging tile
+                __syncwarp();
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    *reinterpret_cast<float4 *>(buf + lane * 128 + ((k ^ (lane & 7)) << 4)) =
+                        make_float4(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1]), __uint_as_float(r[4 * k + 2]),
+                                    __uint_as_float(r[4 * k + 3]));
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    tma_store_2d(&map_out, buf, c0, (int)(m_tile * BM) + q * 32);
+                    bulk_commit_group();
+                }
+                if (p.bn_part) bn_partials(buf, lane, bn_vmask, bn_split, p.bn_part, (m_tile * 4 + q) * 2, p.N, c0 + lane);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { if (rank == 0) mbar_arrive(&acc_empty[acc]); else mbar_arrive_cluster(&acc_empty[acc], 0); }
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+        if (lane == 0) bulk_wait_group<0>();
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, TMEM_COLS);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // fp32 -> bf16 hi/lo operand planes, with the producer's BN affine (+ReLU) applied on the way
 // (simple_global_bn + relu of the previous conv, network.py:330-349) and, for the 1x3 conv, the
 // per-window padded row layout.  8 channels per thread: two float4 loads, two 16-byte stores.
@@ -476,11 +721,10 @@ __global__ void __launch_bounds__(256) k_split_op16(const SplitParams p) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[j] = 0.0f;
         }
-        __align__(16) op16_t h[8], l[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) ptx::split_op16(v[j], h[j], l[j]);
-        *reinterpret_cast<uint4 *>(p.hi + pr * p.K + c) = *reinterpret_cast<const uint4 *>(h);
-        if (p.lo) *reinterpret_cast<uint4 *>(p.lo + pr * p.K + c) = *reinterpret_cast<const uint4 *>(l);
+        uint4 h, l;
+        ptx::split_op16x8(v, h, l);
+        *reinterpret_cast<uint4 *>(p.hi + pr * p.K + c) = h;
+        if (p.lo) *reinterpret_cast<uint4 *>(p.lo + pr * p.K + c) = l;
     }
 }
 
@@ -531,11 +775,10 @@ __global__ void __launch_bounds__(256) k_split_window(const SplitParams p) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[j] = 0.0f;
         }
-        __align__(16) op16_t h[8], l[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) ptx::split_op16(v[j], h[j], l[j]);
-        *reinterpret_cast<uint4 *>(p.hi + (pr0 + i) * p.K + c) = *reinterpret_cast<const uint4 *>(h);
-        if (p.lo) *reinterpret_cast<uint4 *>(p.lo + (pr0 + i) * p.K + c) = *reinterpret_cast<const uint4 *>(l);
+        uint4 h, l;
+        ptx::split_op16x8(v, h, l);
+        *reinterpret_cast<uint4 *>(p.hi + (pr0 + i) * p.K + c) = h;
+        if (p.lo) *reinterpret_cast<uint4 *>(p.lo + (pr0 + i) * p.K + c) = l;
     }
 }
 
@@ -576,7 +819,14 @@ __global__ void __launch_bounds__(256) k_combine_split(const CombineParams p) {
         float v[8];
         if (r < p.rows) {
             const int g = p.win_group[w];
-            const float *a2 = p.a2 + (int64_t)g * p.C + c, *b2 = p.b2 + (int64_t)g * p.C + c;
+            float a2[8], b2[8];
+            {
+                const float4 *pa = reinterpret_cast<const float4 *>(p.a2 + (int64_t)g * p.C + c);
+                const float4 *pb = reinterpret_cast<const float4 *>(p.b2 + (int64_t)g * p.C + c);
+                const float4 a0 = __ldg(pa), a1 = __ldg(pa + 1), b0 = __ldg(pb), b1 = __ldg(pb + 1);
+                a2[0] = a0.x; a2[1] = a0.y; a2[2] = a0.z; a2[3] = a0.w; a2[4] = a1.x; a2[5] = a1.y; a2[6] = a1.z; a2[7] = a1.w;
+                b2[0] = b0.x; b2[1] = b0.y; b2[2] = b0.z; b2[3] = b0.w; b2[4] = b1.x; b2[5] = b1.y; b2[6] = b1.z; b2[7] = b1.w;
+            }
             const float4 y0 = *reinterpret_cast<const float4 *>(p.y2 + r * p.C + c);
             const float4 y1 = *reinterpret_cast<const float4 *>(p.y2 + r * p.C + c + 4);
             const float yy[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
@@ -591,9 +841,13 @@ __global__ void __launch_bounds__(256) k_combine_split(const CombineParams p) {
                 u[0] = u0.x; u[1] = u0.y; u[2] = u0.z; u[3] = u0.w; u[4] = u1.x; u[5] = u1.y; u[6] = u1.z; u[7] = u1.w;
             }
             if (p.a1) {
-                const float *a1 = p.a1 + (int64_t)g * p.C + c, *b1 = p.b1 + (int64_t)g * p.C + c;
+                const float4 *pa = reinterpret_cast<const float4 *>(p.a1 + (int64_t)g * p.C + c);
+                const float4 *pb = reinterpret_cast<const float4 *>(p.b1 + (int64_t)g * p.C + c);
+                const float4 a0 = __ldg(pa), a1 = __ldg(pa + 1), b0 = __ldg(pb), b1 = __ldg(pb + 1);
+                const float aa[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-                for (int j = 0; j < 8; ++j) u[j] = u[j] * a1[j] + b1[j];
+                for (int j = 0; j < 8; ++j) u[j] = u[j] * aa[j] + bb[j];
             }
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[j] = fmaxf(u[j] + (yy[j] * a2[j] + b2[j]), 0.0f);
@@ -606,11 +860,10 @@ __global__ void __launch_bounds__(256) k_combine_split(const CombineParams p) {
             for (int j = 0; j < 8; ++j) v[j] = 0.0f;
         }
         if (p.hi) {
-            __align__(16) op16_t h[8], l[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) ptx::split_op16(v[j], h[j], l[j]);
-            *reinterpret_cast<uint4 *>(p.hi + pr * p.C + c) = *reinterpret_cast<const uint4 *>(h);
-            *reinterpret_cast<uint4 *>(p.lo + pr * p.C + c) = *reinterpret_cast<const uint4 *>(l);
+            uint4 h, l;
+            ptx::split_op16x8(v, h, l);
+            *reinterpret_cast<uint4 *>(p.hi + pr * p.C + c) = h;
+            *reinterpret_cast<uint4 *>(p.lo + pr * p.C + c) = l;
         }
     }
 }
@@ -675,6 +928,22 @@ int make_map_out(CUtensorMap *m, const float *base, int64_t rows, int N, int ldo
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS)
         return fail(NTB_ECUDA, "cuTensorMapEncodeTiled (output) failed (%s%lld) rows %lld", "", (long long)r, (long long)rows);
+    return NTB_OK;
+}
+
+// fp32 [rows][K] activation, box {64 floats, box_rows}, no swizzle (the transform warps read it with plain loads)
+int make_map_raw(CUtensorMap *m, const float *base, int64_t rows, int K, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return fail(NTB_ECUDA, "cuTensorMapEncodeTiled entry point not found%s", "");
+    cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)K * 4};
+    cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(NTB_ECUDA, "cuTensorMapEncodeTiled (raw activation) failed (%s%lld) rows %lld", "", (long long)r, (long long)rows);
     return NTB_OK;
 }
 
@@ -905,6 +1174,50 @@ int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, co
     if (!reuse_planes) NTB_TRY(launch_split(st, sp, launches));   // else: the previous conv split the same input
     if (bn_part && T < 32) return fail(NTB_EINVAL, "tcgen05 conv: fused BN statistics need T >= 32%s", "");
     return launch_gemm(st, w, gs, plane_rows, T, pad, rows, nullptr, out, ldo, launches, 0, bn_part);
+}
+
+bool gemm_tc_conv_fused_supported(const GemmWeights &w, int K, int T, int ldo) {
+    static const bool off = getenv("NTB_NO_FUSED_CONV") != nullptr;      // A/B measurement switch
+    return !off && w.valid && !w.single_pass && gemm_cta_group() == 2 && w.K == K && K % BK == 0 && w.Np == w.N &&
+           w.BN == w.N && w.N % 32 == 0 && w.N <= 256 && (w.taps == 1 || w.taps == 3) && T >= 32 && (ldo & 3) == 0;
+}
+
+int gemm_tc_conv_fused(cudaStream_t st, const float *y, int K, int64_t rows, int T, const float *aff_a,
+                       const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
+                       int ldo, int64_t *launches, float2 *bn_part) {
+    if (!gemm_tc_conv_fused_supported(w, K, T, ldo) || rows % T || (reinterpret_cast<uintptr_t>(y) & 15) ||
+        (reinterpret_cast<uintptr_t>(out) & 15) || (aff_a && !win_group))
+        return fail(NTB_EINVAL, "tcgen05 fused conv: operand not supported (rows %s%lld, K %lld)", "", (long long)rows,
+                    (long long)K);
+    CUtensorMap m_raw, mb_hi, mb_lo, mo;
+    NTB_TRY(make_map_raw(&m_raw, y, rows, K, w.taps == 3 ? BM + 2 : BM));
+    NTB_TRY(make_map(&mb_hi, w.hi, (int64_t)w.taps * w.Np, w.Kp, w.BN / 2));
+    NTB_TRY(make_map(&mb_lo, w.lo, (int64_t)w.taps * w.Np, w.Kp, w.BN / 2));
+    NTB_TRY(make_map_out(&mo, out, rows, w.N, ldo));
+    ConvFusedParams p{};
+    p.m_tiles = (rows + BM - 1) / BM; p.rows = rows; p.N = w.N; p.K = K; p.taps = w.taps; p.T = T;
+    p.k_blocks = K / BK; p.relu = relu_in; p.aff_a = aff_a; p.aff_b = aff_b; p.win_group = win_group; p.bn_part = bn_part;
+    const size_t smem = (size_t)CF_OP_STAGES * (2 * A_TILE_BYTES + 2 * (w.N / 2) * BK * 2) +
+                        (size_t)CF_RAW_STAGES * CF_RAW_STAGE + CF_EPI_BYTES + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        NTB_CUDA(cudaFuncSetAttribute(k_conv_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048));
+        attr_set = true;
+    }
+    const int64_t items = (p.m_tiles + 1) / 2, pairs_hw = sm_count() / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * (items < pairs_hw ? items : pairs_hw)));
+    cfg.blockDim = dim3(CF_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    NTB_CUDA(cudaLaunchKernelEx(&cfg, k_conv_fused, m_raw, mb_hi, mb_lo, mo, p));
+    if (launches) ++*launches;
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
 }
 
 int64_t gemm_tc_bn_part_elems(const GemmScratch &gs, int C) {

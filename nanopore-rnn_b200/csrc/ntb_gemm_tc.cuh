@@ -40,6 +40,12 @@ int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, co
 // squares) partials of the conv output -- [(block * 2 + seg) * C + c], block = plane row / 32, plane rows per
 // window = T (1x1) or T + 2 (1x3) -- which k_bn_finish folds per BN group (no extra pass over the output).
 int64_t gemm_tc_bn_part_elems(const GemmScratch &gs, int C);
+// Same conv with the operand transform (BN affine + ReLU + fp16 hi/lo split of the producer's raw fp32 output y)
+// done by transform warps inside the GEMM: no operand planes, no padded layout, output rows = input rows.
+bool gemm_tc_conv_fused_supported(const GemmWeights &w, int K, int T, int ldo);
+int gemm_tc_conv_fused(cudaStream_t st, const float *y, int K, int64_t rows, int T, const float *aff_a,
+                       const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
+                       int ldo, int64_t *launches, float2 *bn_part);
 // residual_layer tail relu(bn?(branch1) + bn(conv2c)) written as fp32 (`out`, may be null) and/or straight into the
 // operand planes of the next GEMM: layout 0 = none, 1 = plain rows (next 1x1 convs), 2 = time-major tiles (projection).
 // y1_scalar: branch1 is a Cin = 1 conv folded into (a1, b1): value = y1[r] * a1[g][c] + b1[g][c].

@@ -256,16 +256,22 @@ __global__ void __launch_bounds__(256) k_bn_finish(const float2 *__restrict__ pa
     double ss = 0.0, qq = 0.0;
     if (wb > wa) {
         const int64_t b0 = (wa * Tp) >> 5, b1 = (wb * Tp - 1) >> 5;
-        for (int64_t b = b0; b <= b1; ++b) {
-            const int64_t w_first = (b << 5) / Tp, w_last = ((b << 5) + 31) / Tp;
+        // first window of block b and the offset of the block's first row inside it, advanced without divisions
+        int64_t w_first = (b0 << 5) / Tp;
+        int rem = (int)((b0 << 5) - w_first * Tp);
+        const float2 *rec = part + (b0 * 2) * C + ch;
+        for (int64_t b = b0; b <= b1; ++b, rec += 2 * C) {
+            const bool two = rem + 31 >= Tp;                       // the window changes inside this block (Tp >= 32)
             if (w_first >= wa && w_first < wb) {
-                const float2 v = part[(b * 2) * C + ch];
-                ss += v.x; qq += v.y;
+                const float2 v = rec[0];
+                ss += (double)v.x; qq += (double)v.y;
             }
-            if (w_last != w_first && w_last >= wa && w_last < wb) {
-                const float2 v = part[(b * 2 + 1) * C + ch];
-                ss += v.x; qq += v.y;
+            if (two && w_first + 1 >= wa && w_first + 1 < wb) {
+                const float2 v = rec[C];
+                ss += (double)v.x; qq += (double)v.y;
             }
+            rem += 32;
+            if (rem >= Tp) { rem -= Tp; ++w_first; }
         }
     }
     const double mean = n > 0 ? ss / (double)n : 0.0;

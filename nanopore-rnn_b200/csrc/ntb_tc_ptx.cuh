@@ -324,5 +324,22 @@ __device__ __forceinline__ void split_op16(float x, op16_t &hi, op16_t &lo) {
     lo = __float2half_rn(fminf(fmaxf(x - __half2float(hi), -65504.0f), 65504.0f));
 }
 
+// Same split for 8 values at once with packed conversions (F2FP packs two floats per instruction): 16-byte hi and lo
+// chunks ready for a uint4 store.  hi saturates at the fp16 range (upper clamp only when the values are >= 0).
+__device__ __forceinline__ void split_op16x8(const float (&v)[8], uint4 &hi, uint4 &lo) {
+    uint32_t h[4], l[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float a = fminf(fmaxf(v[2 * i], -65504.0f), 65504.0f), b = fminf(fmaxf(v[2 * i + 1], -65504.0f), 65504.0f);
+        const __half2 hh = __floats2half2_rn(a, b);
+        const float2 hf = __half22float2(hh);
+        const __half2 ll = __floats2half2_rn(v[2 * i] - hf.x, v[2 * i + 1] - hf.y);
+        h[i] = *reinterpret_cast<const uint32_t *>(&hh);
+        l[i] = *reinterpret_cast<const uint32_t *>(&ll);
+    }
+    hi = make_uint4(h[0], h[1], h[2], h[3]);
+    lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
 }  // namespace ptx
 }  // namespace ntb
