@@ -53,6 +53,10 @@ struct TcParams {
     int ldo;
     int tma_store;         // plain row-major output through smem staging + cp.async.bulk.tensor stores
     int xproj_H;           // > 0: out is the recurrence's unit-major projected-gates layout (ntb_lstm_tc.cuh)
+    int epi_bytes;         // bytes reserved behind the operand ring (TMA-store staging, or just the bias vector)
+    int bstat;             // B-stationary schedule (CG = 2, several N tiles, small K): every CTA pair keeps ONE weight
+                           // tile (all k-blocks, hi + lo) resident in shared memory and streams M tiles through it;
+                           // only A moves through the ring -- the operand feed from L2 drops from ~46 to ~26 B/clk/SM
     // fused batch-norm statistics (bn_part != null): every epilogue warp reduces its 32 rows x 32 columns to per-column
     // (sum, sum of squares), split at the window boundary inside the block (T >= 32: at most one), and
     // writes bn_part[(block * 2 + seg) * N + n]; k_bn_finish folds the partials of each BN group (ntb_kernels.cuh)
@@ -112,13 +116,29 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t *smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);     // 1024 B: swizzle-128B atoms
     const int b_tile_bytes = (p.BN / CG) * BK * 2;               // this CTA's share of the B tile
-    const int stage_bytes = (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + b_tile_bytes);
+    const bool bstat = CG == 2 && p.bstat;
+    const int stage_bytes = bstat ? 2 * A_TILE_BYTES : (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + b_tile_bytes);
+    const int bres_bytes = bstat ? p.k_blocks * 2 * b_tile_bytes : 0;   // resident B: [k block][hi | lo]
+    uint8_t *stages_base = smem + bres_bytes;
+    __shared__ uint64_t b_full;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rank = CG == 2 ? (int)cluster_ctarank() : 0;      // 0 = leader of the pair
     const int64_t m_groups = (p.m_tiles + CG - 1) / CG;         // a work item = CG consecutive M tiles x one N tile
     const int64_t total_tiles = m_groups * p.n_tiles;
-    const int64_t first_tile = blockIdx.x / CG, tile_step = gridDim.x / CG;
+    const int64_t P = blockIdx.x / CG, NP = gridDim.x / CG;
     const int kb_total = p.taps * p.k_blocks;
+    // work item `it` of this CTA (pair) -> (M group, N tile).  B-stationary: the N tile is fixed, M groups are strided
+    auto item = [&](int64_t it, int64_t &mg, int &nt) -> bool {
+        if (bstat) {
+            nt = (int)(P % p.n_tiles);
+            mg = P / p.n_tiles + it * (NP / p.n_tiles);
+            return mg < m_groups;
+        }
+        const int64_t tile = P + it * NP;
+        nt = (int)(tile % p.n_tiles);
+        mg = tile / p.n_tiles;
+        return tile < total_tiles;
+    };
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&map_a_hi); prefetch_tmap(&map_a_lo); prefetch_tmap(&map_b_hi); prefetch_tmap(&map_b_lo);
@@ -127,6 +147,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
         for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4 * CG); }
+        mbar_init(&b_full, 1);
         fence_barrier_init();
     }
     if (warp == 2) {
@@ -134,8 +155,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
     }
     // xproj mode: the (unused) TMA-store staging area holds the bias vector, so the epilogue's bias reads
     // are shared-memory broadcasts instead of global loads queued behind its own stores
-    float *bias_s = reinterpret_cast<float *>(smem + (size_t)p.stages * stage_bytes);
-    const bool bias_in_smem = p.xproj_H > 0 && p.bias && p.Np * 4 <= EPI_STAGE_BYTES;
+    float *bias_s = reinterpret_cast<float *>(stages_base + (size_t)p.stages * stage_bytes);
+    const bool bias_in_smem = p.xproj_H > 0 && p.bias && p.Np * 4 <= p.epi_bytes;
     if (bias_in_smem)
         for (int i = threadIdx.x; i < p.Np; i += TC_THREADS) bias_s[i] = i < p.N ? p.bias[i] : 0.0f;
     tc_fence_before();
@@ -148,17 +169,30 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
             const int left = (p.taps - 1) / 2;
-            for (int64_t tile = first_tile; tile < total_tiles; tile += tile_step) {
-                const int n_tile = (int)(tile % p.n_tiles);
-                const int64_t m_tile = (tile / p.n_tiles) * CG + rank;
+            int64_t mg; int n_tile;
+            if (bstat && item(0, mg, n_tile)) {
+                // the resident weight tile of this pair: every k-block, hi and lo, each CTA its half of the rows
+                if (rank == 0) mbar_expect_tx(&b_full, (uint32_t)(2 * bres_bytes));
+                const int brow0 = n_tile * p.BN + rank * (p.BN / CG);
+                for (int kb = 0; kb < p.k_blocks; ++kb) {
+                    tma_load_2d_pair(smem + (size_t)(2 * kb) * b_tile_bytes, &map_b_hi, &b_full, kb * BK, brow0);
+                    tma_load_2d_pair(smem + (size_t)(2 * kb + 1) * b_tile_bytes, &map_b_lo, &b_full, kb * BK, brow0);
+                }
+            }
+            for (int64_t it = 0; item(it, mg, n_tile); ++it) {
+                const int64_t m_tile = mg * CG + rank;
                 const int dir_rows = (p.lstm_H > 0 && m_tile >= p.lstm_mt_dir) ? p.Np : 0;   // W_hh of the bw direction
                 for (int tap = 0; tap < p.taps; ++tap) {
                     const int row0 = (int)(m_tile * BM) + tap - left;
                     const int brow0 = tap * p.Np + n_tile * p.BN + rank * (p.BN / CG) + dir_rows;
                     for (int kb = 0; kb < p.k_blocks; ++kb) {
                         mbar_wait(&empty_bar[stage], phase ^ 1);
-                        uint8_t *s = smem + (size_t)stage * stage_bytes;
-                        if (CG == 1) {
+                        uint8_t *s = stages_base + (size_t)stage * stage_bytes;
+                        if (bstat) {
+                            if (rank == 0) mbar_expect_tx(&full_bar[stage], (uint32_t)(2 * stage_bytes));
+                            tma_load_2d_pair(s, &map_a_hi, &full_bar[stage], kb * BK, row0);
+                            tma_load_2d_pair(s + A_TILE_BYTES, &map_a_lo, &full_bar[stage], kb * BK, row0);
+                        } else if (CG == 1) {
                             mbar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
                             tma_load_2d(s, &map_a_hi, &full_bar[stage], kb * BK, row0);
                             tma_load_2d(s + A_TILE_BYTES, &map_b_hi, &full_bar[stage], kb * BK, brow0);
@@ -187,18 +221,24 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
             const uint32_t idesc = idesc_f16_f32(BM * CG, p.BN);
             int stage = 0; uint32_t phase = 0;
             int acc = 0; uint32_t acc_phase = 0;
-            for (int64_t tile = first_tile; tile < total_tiles; tile += tile_step) {
+            int64_t mg; int n_tile;
+            if (bstat && item(0, mg, n_tile)) {
+                mbar_wait(&b_full, 0);
+                tc_fence_after();
+            }
+            for (int64_t it = 0; item(it, mg, n_tile); ++it) {
                 mbar_wait(&acc_empty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
                 for (int kb = 0; kb < kb_total; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
-                    const uint32_t s = smem_u32(smem + (size_t)stage * stage_bytes);
+                    const uint32_t s = smem_u32(stages_base + (size_t)stage * stage_bytes);
+                    const uint32_t sb = smem_u32(smem + (size_t)(2 * kb) * b_tile_bytes);   // resident B (bstat)
                     const uint64_t a_hi = smem_desc_sw128(s);
-                    const uint64_t b_hi = smem_desc_sw128(s + A_TILE_BYTES);
-                    const uint64_t a_lo = smem_desc_sw128(s + A_TILE_BYTES + b_tile_bytes);
-                    const uint64_t b_lo = smem_desc_sw128(s + 2 * A_TILE_BYTES + b_tile_bytes);
+                    const uint64_t b_hi = smem_desc_sw128(bstat ? sb : s + A_TILE_BYTES);
+                    const uint64_t a_lo = smem_desc_sw128(bstat ? s + A_TILE_BYTES : s + A_TILE_BYTES + b_tile_bytes);
+                    const uint64_t b_lo = smem_desc_sw128(bstat ? sb + b_tile_bytes : s + 2 * A_TILE_BYTES + b_tile_bytes);
                     const int k16n = ((kb % p.k_blocks) == p.k_blocks - 1) ? p.k16_last : BK / 16;
                     for (int k = 0; k < k16n; ++k) {
                         if (CG == 1) {
@@ -228,11 +268,11 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
         const int q = warp & 3;                                // TMEM lane quarter this warp may access
         int acc = 0; uint32_t acc_phase = 0;
         const bool vec_ok = ((p.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
-        uint8_t *stage_buf = smem + (size_t)p.stages * stage_bytes + (size_t)q * 8192;   // 1024-B aligned
+        uint8_t *stage_buf = stages_base + (size_t)p.stages * stage_bytes + (size_t)q * 8192;   // 1024-B aligned
         int stage_it = 0;
-        for (int64_t tile = first_tile; tile < total_tiles; tile += tile_step) {
-            const int n_tile = (int)(tile % p.n_tiles);
-            const int64_t m_tile = (tile / p.n_tiles) * CG + rank;
+        int64_t mg; int n_tile;
+        for (int64_t it = 0; item(it, mg, n_tile); ++it) {
+            const int64_t m_tile = mg * CG + rank;
             mbar_wait(&acc_full[acc], acc_phase);
             tc_fence_after();
             const int64_t prow = m_tile * BM + q * 32 + lane;       // row in the A-plane layout
@@ -337,29 +377,40 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                         }
                     }
                 } else if (p.xproj_H > 0 && m_tile < p.m_tiles) {
-                    // xproj[dir][m_tile][unit][row] float4 (i,j,f,o): a warp's 32 rows are contiguous.
-                    // One division per chunk; (dir, unit) then advance incrementally.
+                    // xproj[dir][m_tile][unit][row] float4 (i,j,f,o): a warp's 32 rows are contiguous (512 B per unit).
                     float4 *out4 = reinterpret_cast<float4 *>(p.out);
                     const int nb = n0 + c0, H = p.xproj_H;
-                    int d = (nb >> 2) / H, u = (nb >> 2) - d * H;
+                    const int d = (nb >> 2) / H, u = (nb >> 2) - d * H;
                     const int64_t dir_stride = p.m_tiles * (int64_t)H * BM;
                     float4 *dst = out4 + d * dir_stride + (m_tile * H + u) * (int64_t)BM + (q * 32 + lane);
                     int lim = (p.N < n0 + p.BN ? p.N : n0 + p.BN) - nb;       // valid columns of this chunk
                     lim = lim > 32 ? 32 : lim;
+                    if (lim == 32 && u + 8 <= H && bias_in_smem) {
+                        // common case: 8 whole units of one direction -> straight-line code, constant store offsets
+                        const float4 *b4 = reinterpret_cast<const float4 *>(bias_s + nb);
 #pragma unroll
-                    for (int i = 0; i < 32; i += 4) {
-                        if (i < lim) {
-                            float4 v = make_float4(__uint_as_float(r[i]), __uint_as_float(r[i + 1]),
-                                                   __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
-                            if (p.bias) {
-                                const float4 b = bias_in_smem ? *reinterpret_cast<const float4 *>(bias_s + nb + i)
-                                                              : __ldg(reinterpret_cast<const float4 *>(p.bias + nb + i));
-                                v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
-                            }
-                            *dst = v;
+                        for (int k = 0; k < 8; ++k) {
+                            const float4 bb = b4[k];
+                            dst[k * BM] = make_float4(__uint_as_float(r[4 * k]) + bb.x, __uint_as_float(r[4 * k + 1]) + bb.y,
+                                                      __uint_as_float(r[4 * k + 2]) + bb.z, __uint_as_float(r[4 * k + 3]) + bb.w);
                         }
-                        dst += BM;
-                        if (++u == H) { u = 0; dst += dir_stride - (int64_t)H * BM; }
+                    } else {
+                        int uu = u;
+#pragma unroll
+                        for (int i = 0; i < 32; i += 4) {
+                            if (i < lim) {
+                                float4 v = make_float4(__uint_as_float(r[i]), __uint_as_float(r[i + 1]),
+                                                       __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+                                if (p.bias) {
+                                    const float4 bb = bias_in_smem ? *reinterpret_cast<const float4 *>(bias_s + nb + i)
+                                                                   : __ldg(reinterpret_cast<const float4 *>(p.bias + nb + i));
+                                    v.x += bb.x; v.y += bb.y; v.z += bb.z; v.w += bb.w;
+                                }
+                                *dst = v;
+                            }
+                            dst += BM;
+                            if (++uu == H) { uu = 0; dst += dir_stride - (int64_t)H * BM; }
+                        }
                     }
                 } else {
                   if (p.bn_part) {
@@ -488,12 +539,12 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
             for (int64_t it = first; it < pairs; it += step) {
                 const int64_t m_tile = it * 2 + rank;
                 for (int kb = 0; kb < p.k_blocks; ++kb) {
-                    mbar_wait_backoff(&raw_empty[rs], rph ^ 1, 100);
+                    mbar_wait_backoff<128>(&raw_empty[rs], rph ^ 1, 100);
                     mbar_expect_tx(&raw_full[rs], (uint32_t)(raw_rows * BK * 4));
                     tma_load_2d(raw_base + rs * CF_RAW_STAGE, &map_raw, &raw_full[rs], kb * BK, (int)(m_tile * BM) - left);
                     if (++rs == CF_RAW_STAGES) { rs = 0; rph ^= 1; }
                     for (int tap = 0; tap < p.taps; ++tap) {
-                        mbar_wait_backoff(&op_empty[os], oph ^ 1, 101);
+                        mbar_wait_backoff<128>(&op_empty[os], oph ^ 1, 101);
                         uint8_t *s = op_base + os * op_stage_bytes + 2 * A_TILE_BYTES;
                         const int brow0 = tap * p.N + rank * (p.N / 2);
                         if (rank == 0) mbar_expect_tx(&op_full[os], (uint32_t)(4 * b_tile_bytes));   // both CTAs, both planes
@@ -511,7 +562,7 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
             int os = 0; uint32_t oph = 0;
             int acc = 0; uint32_t acc_phase = 0;
             for (int64_t it = first; it < pairs; it += step) {
-                mbar_wait_backoff(&acc_empty[acc], acc_phase ^ 1, 102);
+                mbar_wait_backoff<64>(&acc_empty[acc], acc_phase ^ 1, 102);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
                 for (int kb = 0; kb < p.k_blocks * p.taps; ++kb) {
@@ -558,11 +609,11 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
                 mbar_wait(&raw_full[rs], rph, 200);
                 const uint8_t *raw = raw_base + rs * CF_RAW_STAGE;
                 const int c = kb * BK + j * 8;                    // first of this thread's 8 channels
+                int gcur = -1;                                    // (a, b) of group gcur for channels c..c+7 stay in registers
+                float a[8], b[8];                                 //  across the taps (and rows) of this k-block
                 for (int tap = 0; tap < p.taps; ++tap) {
                     mbar_wait(&op_empty[os], oph ^ 1, 201);
                     uint8_t *a_hi = op_base + os * op_stage_bytes, *a_lo = a_hi + A_TILE_BYTES;
-                    int gcur = -1;
-                    float a[8], b[8];
 #pragma unroll
                     for (int i = 0; i < RPT; ++i) {
                         const int row = tw * (4 * RPT) + rsub + 4 * i;
@@ -594,7 +645,7 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
                             for (int q = 0; q < 8; ++q) v[q] = 0.0f;
                         }
                         uint4 h, l;
-                        split_op16x8(v, h, l);
+                        if (p.relu) split_op16x8<true>(v, h, l); else split_op16x8<false>(v, h, l);
                         const int off = row * 128 + ((j ^ (row & 7)) << 4);
                         *reinterpret_cast<uint4 *>(a_hi + off) = h;
                         *reinterpret_cast<uint4 *>(a_lo + off) = l;
@@ -616,7 +667,7 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
         uint8_t *buf = epi_base + q * 4096;
         for (int64_t it = first; it < pairs; it += step) {
             const int64_t m_tile = it * 2 + rank;
-            mbar_wait(&acc_full[acc], acc_phase, 300);
+            mbar_wait_backoff<128>(&acc_full[acc], acc_phase, 300);   // long wait next to the transform warps: sleep
             tc_fence_after();
             const int64_t prow = m_tile * BM + q * 32 + lane;
             uint32_t bn_vmask = 0;
@@ -997,15 +1048,31 @@ int gemm_cta_group() {
 }
 
 // tile / ring geometry of one GEMM launch (everything but the operands' addresses)
-int fill_params(TcParams &p, const GemmWeights &w, int64_t plane_rows) {
+int fill_params(TcParams &p, const GemmWeights &w, int64_t plane_rows, bool allow_bstat = true, bool small_epi = false) {
     const int cg = gemm_cta_group();
     p.m_tiles = (plane_rows + BM - 1) / BM;
     p.BN = w.BN; p.Np = w.Np; p.N = w.N; p.n_tiles = w.Np / w.BN;
     p.taps = w.taps; p.k_blocks = (w.K + BK - 1) / BK;
     p.k16_last = ((w.K - (p.k_blocks - 1) * BK) + 15) / 16;
     p.passes = w.single_pass ? 1 : 3;
-    const int stage_bytes = (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + (w.BN / cg) * BK * 2);   // per CTA
-    p.stages = SMEM_BUDGET / stage_bytes;
+    const int b_tile_bytes = (w.BN / cg) * BK * 2;
+    int stage_bytes = (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + b_tile_bytes);   // per CTA
+    // B-stationary (opt-in, NTB_BSTAT=1): measured on the LSTM projections (K <= 256, N = 800) it ties with the
+    // streaming schedule (26.7 vs 27.0 ms per 65 536 windows) -- these GEMMs are bound by the 2.6 GB projected-gates
+    // write, not by the operand feed from L2 -- so streaming stays the default
+    static const bool no_bstat = getenv("NTB_BSTAT") == nullptr;
+    const int bres = p.k_blocks * 2 * b_tile_bytes;
+    // the projected-gates epilogue stores straight from registers: its staging area only holds the bias vector
+    p.epi_bytes = small_epi && w.Np * 4 <= 4096 ? 4096 : EPI_STAGE_BYTES;
+    const int budget = SMEM_BUDGET + EPI_STAGE_BYTES - p.epi_bytes;
+    p.bstat = (allow_bstat && small_epi && !no_bstat && cg == 2 && p.passes == 3 && p.taps == 1 && p.n_tiles > 1 && p.n_tiles <= sm_count() / 2 &&
+               bres + 3 * 2 * A_TILE_BYTES <= budget) ? 1 : 0;
+    if (p.bstat) {
+        stage_bytes = 2 * A_TILE_BYTES;
+        p.stages = (budget - bres) / stage_bytes;
+    } else {
+        p.stages = budget / stage_bytes;
+    }
     if (p.stages > 8) p.stages = 8;
     if (p.stages < 2) return fail(NTB_EINVAL, "tcgen05 GEMM: tile does not fit shared memory%s", "");
     return NTB_OK;
@@ -1014,8 +1081,9 @@ int fill_params(TcParams &p, const GemmWeights &w, int64_t plane_rows) {
 int do_launch(cudaStream_t st, const CUtensorMap &ma_hi, const CUtensorMap &ma_lo, const CUtensorMap &mb_hi,
               const CUtensorMap &mb_lo, const CUtensorMap &mo, const TcParams &p, int64_t *launches) {
     const int cg = gemm_cta_group();
-    const int stage_bytes = (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + (p.BN / cg) * BK * 2);
-    const size_t smem = (size_t)p.stages * stage_bytes + 1024 + EPI_STAGE_BYTES;
+    const int b_tile_bytes = (p.BN / cg) * BK * 2;
+    const int stage_bytes = p.bstat ? 2 * A_TILE_BYTES : (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + b_tile_bytes);
+    const size_t smem = (size_t)p.stages * stage_bytes + (p.bstat ? p.k_blocks * 2 * b_tile_bytes : 0) + 1024 + p.epi_bytes;
     static bool attr_set = false;
     if (!attr_set) {
         NTB_CUDA(cudaFuncSetAttribute(k_gemm_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET + 1024 + EPI_STAGE_BYTES));
@@ -1028,7 +1096,8 @@ int do_launch(cudaStream_t st, const CUtensorMap &ma_hi, const CUtensorMap &ma_l
         k_gemm_tc<1><<<grid, TC_THREADS, smem, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, mo, p);
     } else {
         const int64_t items = ((p.m_tiles + 1) / 2) * p.n_tiles;            // pairs of M tiles x N tiles
-        const int64_t pairs_hw = sm_count() / 2;
+        int64_t pairs_hw = sm_count() / 2;
+        if (p.bstat) pairs_hw = pairs_hw / p.n_tiles * p.n_tiles;          // every pair owns one N tile for the whole launch
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)(2 * (items < pairs_hw ? items : pairs_hw)));
         cfg.blockDim = dim3(TC_THREADS);
@@ -1055,7 +1124,7 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     NTB_TRY(make_map(&mb_hi, w.hi, (int64_t)w.taps * w.Np, w.Kp, w.BN / cg));
     NTB_TRY(make_map(&mb_lo, w.lo, (int64_t)w.taps * w.Np, w.Kp, w.BN / cg));
     TcParams p{};
-    NTB_TRY(fill_params(p, w, plane_rows));
+    NTB_TRY(fill_params(p, w, plane_rows, true, xproj_H > 0));
     p.T = T; p.pad = pad; p.out_rows = out_rows; p.bias = bias; p.out = out; p.ldo = ldo;
     p.xproj_H = xproj_H;
     p.bn_part = bn_part;
@@ -1311,7 +1380,7 @@ int gemm_tc_lstm_layer(cudaStream_t st, const GemmWeights &whh, const float *xpr
     GemmWeights w1 = whh;
     w1.taps = 1;                                                     // the second "tap" is the bw direction's W_hh
     TcParams p{};
-    NTB_TRY(fill_params(p, w1, 2 * Mp));
+    NTB_TRY(fill_params(p, w1, 2 * Mp, false));   // the weight tile depends on the direction of the M tile
     p.T = T; p.pad = 0; p.out_rows = n_windows * T; p.bias = nullptr; p.out = out; p.ldo = ldo;
     p.lstm_H = H; p.lstm_mt_dir = (int)(Mp / BM); p.lstm_n = n_windows; p.lstm_Mp = Mp;
     p.lstm_x = xproj; p.lstm_ldx = ldx; p.lstm_c = cstate; p.lstm_lens = lens;

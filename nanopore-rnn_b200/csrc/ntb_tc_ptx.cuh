@@ -60,11 +60,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity, int ta
 }
 // Same, for single-thread control roles (TMA producer, MMA issuer) that wait for a long time next to
 // working warps on the same scheduler: back off with nanosleep between polls.
+template <int NS = 32>
 __device__ __forceinline__ void mbar_wait_backoff(uint64_t *bar, uint32_t parity, int tag = 0) {
     if (mbar_try_wait(bar, parity)) return;
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        __nanosleep(32);
+        __nanosleep(NS);
         if (++spins > (1u << 24)) {
 #ifdef NTB_DEBUG_SYNC
             printf("mbar timeout tag %d block (%d,%d) thread %d parity %u\n", tag, blockIdx.x, blockIdx.y, threadIdx.x, parity);
@@ -87,6 +88,10 @@ __device__ __forceinline__ void tma_load_2d(void *dst, const void *tmap, uint64_
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(smem_u32(dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
+}
+// 2D tiled prefetch into L2 (no smem, no barrier): hides the HBM latency of a later tma_load_2d of the same box
+__device__ __forceinline__ void tma_prefetch_2d(const void *tmap, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(tmap), "r"(c0), "r"(c1) : "memory");
 }
 // 2D tiled store smem -> global (bulk async group); coordinates are {inner, outer}; out-of-bounds
 // parts of the box are clipped by the tensor map.
@@ -326,11 +331,13 @@ __device__ __forceinline__ void split_op16(float x, op16_t &hi, op16_t &lo) {
 
 // Same split for 8 values at once with packed conversions (F2FP packs two floats per instruction): 16-byte hi and lo
 // chunks ready for a uint4 store.  hi saturates at the fp16 range (upper clamp only when the values are >= 0).
+template <bool NONNEG = false>
 __device__ __forceinline__ void split_op16x8(const float (&v)[8], uint4 &hi, uint4 &lo) {
     uint32_t h[4], l[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const float a = fminf(fmaxf(v[2 * i], -65504.0f), 65504.0f), b = fminf(fmaxf(v[2 * i + 1], -65504.0f), 65504.0f);
+        float a = fminf(v[2 * i], 65504.0f), b = fminf(v[2 * i + 1], 65504.0f);
+        if (!NONNEG) { a = fmaxf(a, -65504.0f); b = fmaxf(b, -65504.0f); }
         const __half2 hh = __floats2half2_rn(a, b);
         const float2 hf = __half22float2(hh);
         const __half2 ll = __floats2half2_rn(v[2 * i] - hf.x, v[2 * i + 1] - hf.y);
