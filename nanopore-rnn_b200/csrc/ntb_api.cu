@@ -563,10 +563,16 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
         const int F = fused_fnn ? dim / 2 : dim;
         const size_t smem = sizeof(float) * ((size_t)F * m->C + (fused_fnn ? 3 * F : 0));
         if (smem > 200 * 1024) return fail(NTB_EINVAL, "readout: dense weights do not fit shared memory%s", "");
-        NTB_CUDA(cudaFuncSetAttribute(k_readout_small<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_readout_small<8><<<cdiv(n, 8), 256, smem, st>>>(cur, dim, fused_fnn ? fused_fnn->fnn_w : nullptr,
-                                                          fused_fnn ? fused_fnn->fnn_b : nullptr, m->out_w, m->out_b,
-                                                          lens, n, T, m->C, m->graph, logits_out, labels, label_len);
+        if (F <= 128) {
+            k_readout_small_pipe<8><<<cdiv(n, 8), 256, 0, st>>>(cur, dim, fused_fnn ? fused_fnn->fnn_w : nullptr,
+                                                               fused_fnn ? fused_fnn->fnn_b : nullptr, m->out_w, m->out_b,
+                                                               lens, n, T, m->C, m->graph, logits_out, labels, label_len);
+        } else {
+            NTB_CUDA(cudaFuncSetAttribute(k_readout_small<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_readout_small<8><<<cdiv(n, 8), 256, smem, st>>>(cur, dim, fused_fnn ? fused_fnn->fnn_w : nullptr,
+                                                              fused_fnn ? fused_fnn->fnn_b : nullptr, m->out_w, m->out_b,
+                                                              lens, n, T, m->C, m->graph, logits_out, labels, label_len);
+        }
         cx.count();
         NTB_LAUNCH_CHECK();
     } else {

@@ -81,16 +81,26 @@ __device__ __forceinline__ void bn_partials(const uint8_t *buf, int lane, uint32
     // fixed order -> bit-stable; the records are combined in fp64 (k_bn_finish)
     float s0[4] = {0, 0, 0, 0}, q0[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0}, q1[4] = {0, 0, 0, 0};
     const int cj = lane >> 2, ci = (lane & 3) << 2;
+    if (vmask == 0xffffffffu && split == 32) {
+        // common case (no window boundary, no padding row in the block): same chains, no per-row selects
 #pragma unroll
-    for (int i = 0; i < 32; ++i) {
-        const float f = *reinterpret_cast<const float *>(buf + i * 128 + ((cj ^ (i & 7)) << 4) + ci);
-        const float v = ((vmask >> i) & 1u) ? f : 0.0f;
-        if (i < split) {
+        for (int i = 0; i < 32; ++i) {
+            const float v = *reinterpret_cast<const float *>(buf + i * 128 + ((cj ^ (i & 7)) << 4) + ci);
             s0[i & 3] += v;
             q0[i & 3] = fmaf(v, v, q0[i & 3]);
-        } else {
-            s1[i & 3] += v;
-            q1[i & 3] = fmaf(v, v, q1[i & 3]);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            const float f = *reinterpret_cast<const float *>(buf + i * 128 + ((cj ^ (i & 7)) << 4) + ci);
+            const float v = ((vmask >> i) & 1u) ? f : 0.0f;
+            if (i < split) {
+                s0[i & 3] += v;
+                q0[i & 3] = fmaf(v, v, q0[i & 3]);
+            } else {
+                s1[i & 3] += v;
+                q1[i & 3] = fmaf(v, v, q1[i & 3]);
+            }
         }
     }
     if (n < N) {

@@ -472,6 +472,92 @@ __global__ void __launch_bounds__(256) k_readout_small(
     }
 }
 
+// Same readout for F <= 128 (the shipped CRNN configs: F = 100): every lane owns up to 4 features, keeps their
+// dense / chiron_fnn weights in registers and loads row t + 1 while it reduces row t (one warp walks its window's
+// T rows in order -- without the prefetch each row costs a full memory latency).
+template <int MAXC>
+__global__ void __launch_bounds__(256) k_readout_small_pipe(
+    const float *__restrict__ v, int F_in, const float *__restrict__ fnn_w, const float *__restrict__ fnn_b,
+    const float *__restrict__ out_w, const float *__restrict__ out_b, const int32_t *__restrict__ lens,
+    int64_t n_windows, int T, int C, int graph, float *__restrict__ logits, int32_t *__restrict__ labels,
+    int32_t *__restrict__ label_len) {
+    const int F = fnn_w ? F_in / 2 : F_in;
+    const int lane = threadIdx.x & 31;
+    const int64_t w = (int64_t)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+    if (w >= n_windows) return;
+    float wd[4][MAXC], fw0[4], fw1[4], fb[4], ob[MAXC];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int f = lane + 32 * k;
+        const bool ok = f < F;
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) wd[k][c] = (ok && c < C) ? out_w[f * C + c] : 0.0f;
+        fw0[k] = (ok && fnn_w) ? fnn_w[f] : 1.0f;
+        fw1[k] = (ok && fnn_w) ? fnn_w[F + f] : 0.0f;
+        fb[k] = (ok && fnn_w) ? fnn_b[f] : 0.0f;
+    }
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c) ob[c] = c < C ? out_b[c] : 0.0f;
+    const int len = lens[w];
+    const float *row = v + w * T * (int64_t)F_in;
+    float a[4], b[4], na[4], nb[4];
+    auto load = [&](const float *r, float (&x)[4], float (&y)[4]) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int f = lane + 32 * k;
+            x[k] = f < F ? __ldg(r + f) : 0.0f;
+            y[k] = (f < F && fnn_w) ? __ldg(r + F + f) : 0.0f;
+        }
+    };
+    load(row, a, b);
+    int prev = -1, cnt = 0;
+    for (int t = 0; t < T; ++t) {
+        if (t + 1 < T) load(row + (int64_t)(t + 1) * F_in, na, nb);
+        float part[MAXC];
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) part[c] = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            // same operation order as the generic kernel: (v0 w0 + v1 w1) + b, then the dense FMAs over f ascending
+            const float y = fnn_w ? a[k] * fw0[k] + b[k] * fw1[k] + fb[k] : a[k];
+#pragma unroll
+            for (int c = 0; c < MAXC; ++c) part[c] = fmaf(y, wd[k][c], part[c]);
+        }
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) part[c] += __shfl_xor_sync(0xffffffffu, part[c], o);
+        }
+        int best = 0;
+        float bv = 0.0f;
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) {
+            if (c < C) {
+                const float lg = part[c] + ob[c];
+                if (logits && lane == c % 32) logits[(w * T + t) * (int64_t)C + c] = lg;
+                if (c == 0 || lg > bv) { bv = lg; best = c; }   // strict > : first max wins
+            }
+        }
+        if (graph == NTB_GRAPH_CTC) {
+            if (t < len) {
+                if (best != C - 1 && best != prev) {
+                    if (lane == 0) labels[w * T + cnt] = best;
+                    ++cnt;
+                }
+                prev = best;
+            }
+        } else if (lane == 0) {
+            labels[w * T + t] = best;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { a[k] = na[k]; b[k] = nb[k]; }
+    }
+    if (graph == NTB_GRAPH_CTC) {
+        for (int i = cnt + lane; i < T; i += 32) labels[w * T + i] = -1;
+        if (lane == 0 && label_len) label_len[w] = cnt;
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // Decode for large C (event model, C = 1025): logits already materialised by the dense GEMM.
 // argmax: one warp per row; CTC: one warp per window walking t.
