@@ -302,23 +302,37 @@ def run_b200(args):
                "h2d_bytes_per_step": int(x.nbytes + lens.nbytes + goff.nbytes),
                "d2h_bytes_per_step": int(labels.nbytes + llen.nbytes), "ms_per_step": dt * 1e3}
 
-    # ---- roofline of the dominant stage (stage marks = CUDA events on the forward's stream)
+    # ---- roofline of the dominant kernel: k_gemm_tc<2>, the tcgen05 GEMM of the LSTM input projections (three
+    # launches per forward, the largest share of the launch list in profiles/).  Its launches are bracketed by CUDA
+    # events on the forward's stream (stage 4 of ntb_model_stage_ms); achieved = SURVEY.md 8(d)'s algorithmic projection
+    # FLOPs per window x windows / that time.  The per-stage table (same events) covers the rest of the step.
     pk = peaks()
+    proj_ms = stage.get("projection_gemm", 0.0)
+    stage4 = {"conv_bn": stage.get("conv_bn", 0.0),
+              "projection": stage.get("projection_split", 0.0) + proj_ms,
+              "recurrence": stage.get("recurrence", 0.0), "readout": stage.get("readout", 0.0)}
     flops = {"conv_bn": FLOPS_CONV, "projection": FLOPS_PROJ, "recurrence": FLOPS_REC, "readout": FLOPS_READOUT}
-    top = max(stage, key=lambda k: stage[k]) if stage else None
     roof = None
-    if top is not None and stage[top] > 0:
-        achieved = flops[top] * n * args.steps / (stage[top] * 1e-3) / 1e12
+    if proj_ms > 0:
+        n_launch_k = 3 * len(chunks) * args.steps
+        achieved = FLOPS_PROJ * n * args.steps / (proj_ms * 1e-3) / 1e12
         peak = pk["bf16_tflops_sustained"]
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
-            traffic = json.load(open(tp)).get(top)
-        roof = {"bound": "tensor", "kernel": top, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                "frac": achieved / peak, "traffic": traffic, "peak_source": pk["src"] + " (sustained bf16)",
-                "stage_ms_per_step": {k: v / max(args.steps, 1) for k, v in stage.items()},
+            per_window = json.load(open(tp)).get("k_gemm_tc_xproj_dram_bytes_per_window")
+            if per_window:
+                traffic = per_window * n / len(chunks)      # bytes per launch at this chunk size (ncu: --set full)
+        roof = {"bound": "tensor", "kernel": "k_gemm_tc<2> (LSTM input projection GEMM, tcgen05 fp16x3)",
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
+                "peak_source": pk["src"] + " (sustained bf16)",
+                "us_per_launch": proj_ms * 1e3 / n_launch_k, "launches": n_launch_k,
+                "algorithmic_flops_per_launch": FLOPS_PROJ * n / len(chunks) / 3,
+                "tensor_pipe_frac_with_3_passes": 3 * achieved / peak,
+                "stage_ms_per_step": {k: v / max(args.steps, 1) for k, v in stage4.items()},
                 "stage_tflops": {k: (flops[k] * n * args.steps / (v * 1e-3) / 1e12 if v > 0 else None)
-                                 for k, v in stage.items()}}
+                                 for k, v in stage4.items()},
+                "hbm_peak_gbs": pk["hbm_gbs"]}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

@@ -132,7 +132,9 @@ NTB_API int64_t ntb_model_workspace_bytes_host(const ntb_model *m, int64_t n_win
 NTB_API int64_t ntb_model_last_launches(const ntb_model *m);
 /* Per-stage device time (ms), summed over every forward issued since profiling was enabled with
  * ntb_model_set_profile(m, 1) (or since the previous ntb_model_stage_ms call): stages are
- * 0 conv/BN front-end, 1 LSTM input projections, 2 LSTM recurrences, 3 readout.  Stage marks are
+ * 0 conv/BN front-end, 1 LSTM input projections, 2 LSTM recurrences, 3 readout and -- only when
+ * max_stages >= 5 -- 4 = the projection GEMM kernel alone (stage 1 then holds just the operand
+ * split passes; with max_stages == 4 stage 1 is split + GEMM).  Stage marks are
  * CUDA events recorded on the forward's stream WITHOUT synchronising; this call waits for the
  * last one.  Returns the number of stages written. */
 NTB_API int ntb_model_set_profile(ntb_model *m, int enable);

@@ -59,7 +59,7 @@ struct ntb_model {
     bool has_res = false, any_tc_rec = false;
     int64_t launches = 0;
     int profile = 0;
-    float stage_ms[4] = {0, 0, 0, 0};
+    float stage_ms[5] = {0, 0, 0, 0, 0};
     // profile mode: (stage, event) marks of every forward since the last ntb_model_stage_ms();
     // recorded without synchronising so that profiling does not perturb the timed region
     std::vector<std::pair<int, cudaEvent_t>> marks;
@@ -476,7 +476,7 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
     const int T = m->T;
     const int64_t rows = n * T;
     if (n == 0) return NTB_OK;
-    int stage = -1;   // 0 conv, 1 projection, 2 recurrence, 3 readout
+    int stage = -1;   // 0 conv, 1 projection (operand split), 2 recurrence, 3 readout, 4 projection GEMM kernel
     auto &marks = m->marks;
     auto mark = [&](int s) -> int {
         if (!m->profile) return NTB_OK;
@@ -522,8 +522,9 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
             if (ld.tc_rec) {
                 // the packed projection weights are pre-scaled for this recurrence: no SIMT detour from here
                 if (!ws.gs.valid) return fail(NTB_EINVAL, "blstm: operand planes missing for the tensor-core path%s", "");
+                struct Hook { decltype(mark) *mk; static void call(void *a) { (*static_cast<Hook *>(a)->mk)(4); } } hook{&mark};
                 NTB_TRY(gemm_tc_run_xproj(cx.st, cur, dim, n, T, ld.wihw, ld.bias, ws.xproj, ld.size, ws.gs, &cx.launches,
-                                          planes == 2));
+                                          planes == 2, &Hook::call, &hook));
                 NTB_TRY(mark(2));
                 LstmTcParams p{};
                 p.xproj = (const float4 *)ws.xproj; p.whh_hi = ld.whh_hi; p.whh_lo = ld.whh_lo; p.lens = lens;
@@ -588,7 +589,7 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
         cudaEvent_t e;
         NTB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDefault));
         NTB_CUDA(cudaEventRecord(e, st));
-        marks.push_back({4, e});
+        marks.push_back({-1, e});
     }
     m->launches = cx.launches;
     return NTB_OK;
@@ -686,17 +687,18 @@ extern "C" int ntb_model_set_profile(ntb_model *m, int enable) {
 }
 extern "C" int ntb_model_stage_ms(ntb_model *m, float *ms_out, int max_stages) {
     if (!m || !ms_out) return 0;
-    float acc[4] = {0, 0, 0, 0};
+    float acc[5] = {0, 0, 0, 0, 0};
     auto &marks = m->marks;
     if (!marks.empty()) cudaEventSynchronize(marks.back().second);
     for (size_t i = 0; i + 1 < marks.size(); ++i) {
-        if (marks[i].first < 0 || marks[i].first > 3) continue;   // 4 = end of one forward
+        if (marks[i].first < 0 || marks[i].first > 4) continue;   // -1 = end of one forward
         float ms = 0;
         if (cudaEventElapsedTime(&ms, marks[i].second, marks[i + 1].second) == cudaSuccess) acc[marks[i].first] += ms;
     }
     drop_marks(m);
-    for (int i = 0; i < 4; ++i) m->stage_ms[i] = acc[i];
-    int k = max_stages < 4 ? max_stages : 4;
+    for (int i = 0; i < 5; ++i) m->stage_ms[i] = acc[i];
+    if (max_stages < 5) m->stage_ms[1] += acc[4];   // callers of the 4-stage form: projection = split + GEMM
+    int k = max_stages < 5 ? max_stages : 5;
     for (int i = 0; i < k; ++i) ms_out[i] = m->stage_ms[i];
     return k;
 }

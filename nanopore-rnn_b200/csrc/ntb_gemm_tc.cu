@@ -53,6 +53,7 @@ struct TcParams {
     int ldo;
     int tma_store;         // plain row-major output through smem staging + cp.async.bulk.tensor stores
     int xproj_H;           // > 0: out is the recurrence's unit-major projected-gates layout (ntb_lstm_tc.cuh)
+    int abl;               // timing ablation (NTB_XPROJ_ABL): 1 = projected-gates epilogue without its global stores
     int epi_bytes;         // bytes reserved behind the operand ring (TMA-store staging, or just the bias vector)
     int bstat;             // B-stationary schedule (CG = 2, several N tiles, small K): every CTA pair keeps ONE weight
                            // tile (all k-blocks, hi + lo) resident in shared memory and streams M tiles through it;
@@ -387,6 +388,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                         }
                     }
                 } else if (p.xproj_H > 0 && m_tile < p.m_tiles) {
+                    if (p.abl & 1) continue;
                     // xproj[dir][m_tile][unit][row] float4 (i,j,f,o): a warp's 32 rows are contiguous (512 B per unit).
                     float4 *out4 = reinterpret_cast<float4 *>(p.out);
                     const int nb = n0 + c0, H = p.xproj_H;
@@ -1138,6 +1140,8 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     p.T = T; p.pad = pad; p.out_rows = out_rows; p.bias = bias; p.out = out; p.ldo = ldo;
     p.xproj_H = xproj_H;
     p.bn_part = bn_part;
+    static const int abl = getenv("NTB_XPROJ_ABL") ? atoi(getenv("NTB_XPROJ_ABL")) : 0;
+    p.abl = abl;
     // coalesced TMA-store epilogue for plain row-major outputs (N tiles of whole 32-column chunks)
     p.tma_store = (!pad && xproj_H == 0 && w.BN % 32 == 0 && (ldo & 3) == 0 &&
                    (reinterpret_cast<uintptr_t>(out) & 15) == 0) ? 1 : 0;
@@ -1222,7 +1226,7 @@ int gemm_tc_run(cudaStream_t st, const float *A, int lda, int64_t rows, const Ge
 
 int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, const GemmWeights &w,
                       const float *bias, float *xproj, int H, const GemmScratch &gs, int64_t *launches,
-                      bool planes_ready) {
+                      bool planes_ready, void (*before_gemm)(void *), void *hook_arg) {
     const int64_t n_tiles = (n_windows + BM - 1) / BM;
     const int64_t plane_rows = n_tiles * BM * T;
     if (!w.valid || !gs.valid || plane_rows > gs.rows_cap || w.K > gs.kp_cap || (lda & 3) || w.taps != 1 ||
@@ -1233,6 +1237,7 @@ int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_window
     sp.A = A; sp.lda = lda; sp.rows = n_windows * T; sp.K = w.K; sp.T = T; sp.relu = 0; sp.pad = 0; sp.perm = 1;
     sp.hi = gs.a_hi; sp.lo = w.single_pass ? nullptr : gs.a_lo; sp.plane_rows = plane_rows;
     if (!planes_ready) NTB_TRY(launch_split(st, sp, launches));   // else: the producer wrote the planes itself
+    if (before_gemm) before_gemm(hook_arg);                       // profiling mark: the GEMM kernel alone
     return launch_gemm(st, w, gs, plane_rows, 1, 0, plane_rows, bias, xproj, 0, launches, H);
 }
 

@@ -29,7 +29,7 @@ int gemm_tc_run(cudaStream_t st, const float *A, int lda, int64_t rows, const Ge
 // (xproj must hold ceil(n_windows/128)*128*T*8H floats).
 int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, const GemmWeights &w,
                       const float *bias, float *xproj, int H, const GemmScratch &gs, int64_t *launches,
-                      bool planes_ready = false);
+                      bool planes_ready = false, void (*before_gemm)(void *) = nullptr, void *hook_arg = nullptr);
 // CUtensorMap (128 bytes, 64-byte aligned) over the projected-gates buffer for the recurrence's TMA ring.
 int make_map_xproj(void *map_out, const float *xproj, int64_t units_total);
 int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, const float *aff_a,

@@ -47,7 +47,7 @@ struct LstmTcParams {
     int64_t n_windows;
     int n_tiles;                      // ceil(n_windows / 128)
     int T, H, Hp;                     // Hp = H rounded up to 16
-    int flags;                        // debug/ablation: 2 = no slice overlap, 16 = L2 prefetch of the next step, 64 = hi.hi pass only, 128 = no MMA (timing only)
+    int flags;                        // debug/ablation: 2 = no slice overlap, 16 = L2 prefetch of the next step, 32 = warp-3 L2 prefetch two steps ahead, 64 = hi.hi pass only, 128 = no MMA (timing only), 256 = no projected-gates stream (timing only)
 };
 
 static inline bool lstm_tc_supported(int H) {
@@ -172,9 +172,21 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
                 }
             }
         }
+    } else if (warp == 3) {
+        // ===================== L2 prefetcher (flags & 32): projected gates of step s + 2 towards L2, paced by the MMAs
+        if (lane == 0 && (p.flags & 32)) {
+            const uint32_t bytes = (uint32_t)step_f4 * 16, piece = (bytes / 8) & ~15u;
+            for (int s = 0; s + 2 < T; ++s) {
+                if (s > 0) mbar_wait_backoff(&d_full[0], (uint32_t)((s - 1) & 1), 6000 + s);
+                const int tn = dir ? T - 3 - s : s + 2;
+                const char *g = reinterpret_cast<const char *>(xtile + (int64_t)tn * step_f4);
+                for (int q = 0; q < 8; ++q)
+                    bulk_prefetch_l2(g + (size_t)q * piece, q == 7 ? bytes - 7 * piece : piece);
+            }
+        }
     } else if (warp == 1) {
         // ===================== x producer: projected-gate chunks -> smem ring (TMA) ==========
-        if (lane == 0) {
+        if (lane == 0 && !(p.flags & 256)) {
             uint32_t slot = 0, ph = 0;
             for (int s = 0; s < T; ++s) {
                 const int t = dir ? T - 1 - s : s;
@@ -245,7 +257,7 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
                 }
                 if (c < n_chunks) {
                     const bool real = c * 8 + half * 4 < H;     // warp-uniform
-                    mbar_wait(&x_full[slot], xph, 5000 + s);
+                    if (!(p.flags & 256)) mbar_wait(&x_full[slot], xph, 5000 + s);
                     float4 xv[4];
                     uint32_t a[16];
                     if (real) {
@@ -287,7 +299,7 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
                     }
                     // every lane has consumed its x values (data dependence) -> the slot may be refilled
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&x_empty[slot]);
+                    if (lane == 0 && !(p.flags & 256)) mbar_arrive(&x_empty[slot]);
                     if (++slot == LSTM_TC_XSLOTS) { slot = 0; xph ^= 1; }
                 }
             }

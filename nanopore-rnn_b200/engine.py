@@ -265,9 +265,9 @@ class Model:
         self.lib.ntb_model_set_profile(self._h, int(bool(on)))
 
     def stage_ms(self):
-        buf = (C.c_float * 4)()
-        k = self.lib.ntb_model_stage_ms(self._h, buf, 4)
-        return dict(zip(["conv_bn", "projection", "recurrence", "readout"][:k], list(buf)[:k]))
+        buf = (C.c_float * 5)()
+        k = self.lib.ntb_model_stage_ms(self._h, buf, 5)
+        return dict(zip(["conv_bn", "projection_split", "recurrence", "readout", "projection_gemm"][:k], list(buf)[:k]))
 
 
 def _pinned(shape, dtype):
