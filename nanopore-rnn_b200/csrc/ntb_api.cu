@@ -530,7 +530,20 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
                 p.xproj = (const float4 *)ws.xproj; p.whh_hi = ld.whh_hi; p.whh_lo = ld.whh_lo; p.lens = lens;
                 p.out = out; p.ldo = 2 * ld.size; p.n_windows = n; p.n_tiles = cdiv(n, LSTM_TC_ROWS);
                 p.T = T; p.H = ld.size; p.Hp = (int)align_up(ld.size, 16);
+                // a following tensor-core BLSTM layer can take h straight as its projection operand planes.  Opt-in
+                // (NTB_REC_PLANES=1): the two 8-byte row-strided stores per chunk cost the recurrence more (24.3 -> 30.0 ms
+                // per 65 536 windows) than the saved split pass gives back (32.2 -> 23.8 ms incl. the TMA-store epilogue,
+                // 26.8 -> 23.8 without it): its scattered stores are the recurrence's L1 bottleneck
+                static const bool rec_planes = getenv("NTB_REC_PLANES") && getenv("NTB_REC_PLANES")[0] == '1';
+                const bool feed_next = rec_planes && li + 1 < nl && m->layers[li + 1].type == NTB_LAYER_BLSTM &&
+                                       m->layers[li + 1].tc_rec && 2 * ld.size <= ws.gs.kp_cap && (2 * ld.size) % 8 == 0;
+                if (feed_next) { p.next_hi = ws.gs.a_hi; p.next_lo = ws.gs.a_lo; p.next_K = 2 * ld.size; }
                 NTB_TRY(launch_lstm_tc(cx, p));
+                dim = 2 * ld.size;
+                planes = feed_next ? 2 : 0;
+                cur = out;
+                flip ^= 1;
+                continue;
             } else if (ld.step_rec) {
                 if (!ws.gs.valid) return fail(NTB_EINVAL, "blstm: operand planes missing for the tensor-core path%s", "");
                 NTB_TRY(dense(cx, cur, dim, rows, dim, N, ld.wih, &ld.wihw, ld.bias, ws.xproj, N, &ws.gs));
@@ -564,7 +577,16 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
         const int F = fused_fnn ? dim / 2 : dim;
         const size_t smem = sizeof(float) * ((size_t)F * m->C + (fused_fnn ? 3 * F : 0));
         if (smem > 200 * 1024) return fail(NTB_EINVAL, "readout: dense weights do not fit shared memory%s", "");
-        if (F <= 128) {
+        const bool vec = F <= 128 && F % 4 == 0 && (dim % 4) == 0 && (reinterpret_cast<uintptr_t>(cur) & 15) == 0;
+        if (vec && m->C <= 4) {
+            k_readout_small_vec<4><<<cdiv(n, 8), 256, 0, st>>>(cur, dim, fused_fnn ? fused_fnn->fnn_w : nullptr,
+                                                               fused_fnn ? fused_fnn->fnn_b : nullptr, m->out_w, m->out_b,
+                                                               lens, n, T, m->C, m->graph, logits_out, labels, label_len);
+        } else if (vec) {
+            k_readout_small_vec<8><<<cdiv(n, 8), 256, 0, st>>>(cur, dim, fused_fnn ? fused_fnn->fnn_w : nullptr,
+                                                               fused_fnn ? fused_fnn->fnn_b : nullptr, m->out_w, m->out_b,
+                                                               lens, n, T, m->C, m->graph, logits_out, labels, label_len);
+        } else if (F <= 128) {
             k_readout_small_pipe<8><<<cdiv(n, 8), 256, 0, st>>>(cur, dim, fused_fnn ? fused_fnn->fnn_w : nullptr,
                                                                fused_fnn ? fused_fnn->fnn_b : nullptr, m->out_w, m->out_b,
                                                                lens, n, T, m->C, m->graph, logits_out, labels, label_len);

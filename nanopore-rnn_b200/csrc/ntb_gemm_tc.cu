@@ -53,6 +53,7 @@ struct TcParams {
     int ldo;
     int tma_store;         // plain row-major output through smem staging + cp.async.bulk.tensor stores
     int xproj_H;           // > 0: out is the recurrence's unit-major projected-gates layout (ntb_lstm_tc.cuh)
+    int xproj_tma;         // projected-gates epilogue through smem staging + 3-D TMA stores (map_out = store map)
     int abl;               // timing ablation (NTB_XPROJ_ABL): 1 = projected-gates epilogue without its global stores
     int epi_bytes;         // bytes reserved behind the operand ring (TMA-store staging, or just the bias vector)
     int bstat;             // B-stationary schedule (CG = 2, several N tiles, small K): every CTA pair keeps ONE weight
@@ -153,7 +154,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&map_a_hi); prefetch_tmap(&map_a_lo); prefetch_tmap(&map_b_hi); prefetch_tmap(&map_b_lo);
-        if (p.tma_store) prefetch_tmap(&map_out);
+        if (p.tma_store || p.xproj_tma) prefetch_tmap(&map_out);
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
@@ -166,8 +167,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
     }
     // xproj mode: the (unused) TMA-store staging area holds the bias vector, so the epilogue's bias reads
     // are shared-memory broadcasts instead of global loads queued behind its own stores
-    float *bias_s = reinterpret_cast<float *>(stages_base + (size_t)p.stages * stage_bytes);
-    const bool bias_in_smem = p.xproj_H > 0 && p.bias && p.Np * 4 <= p.epi_bytes;
+    float *bias_s = reinterpret_cast<float *>(stages_base + (size_t)p.stages * stage_bytes + (p.xproj_tma ? EPI_STAGE_BYTES : 0));
+    const bool bias_in_smem = p.xproj_H > 0 && p.bias && p.Np * 4 <= p.epi_bytes - (p.xproj_tma ? EPI_STAGE_BYTES : 0);
     if (bias_in_smem)
         for (int i = threadIdx.x; i < p.Np; i += TC_THREADS) bias_s[i] = i < p.N ? p.bias[i] : 0.0f;
     tc_fence_before();
@@ -397,7 +398,28 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                     float4 *dst = out4 + d * dir_stride + (m_tile * H + u) * (int64_t)BM + (q * 32 + lane);
                     int lim = (p.N < n0 + p.BN ? p.N : n0 + p.BN) - nb;       // valid columns of this chunk
                     lim = lim > 32 ? 32 : lim;
-                    if (lim == 32 && u + 8 <= H && bias_in_smem) {
+                    if (lim == 32 && u + 8 <= H && bias_in_smem && p.xproj_tma) {
+                        // common case, TMA form: [8 units][32 rows] float4 staging tile (4 KB, conflict-free) -> ONE
+                        // 3-D tensor store {128 floats, 1, 8 units} per warp and chunk
+                        uint8_t *buf = stage_buf + (stage_it & 1) * 4096;
+                        ++stage_it;
+                        if (lane == 0) bulk_wait_group_read<1>();
+                        __syncwarp();
+                        const float4 *b4 = reinterpret_cast<const float4 *>(bias_s + nb);
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) {
+                            const float4 bb = b4[k];
+                            *reinterpret_cast<float4 *>(buf + k * 512 + lane * 16) =
+                                make_float4(__uint_as_float(r[4 * k]) + bb.x, __uint_as_float(r[4 * k + 1]) + bb.y,
+                                            __uint_as_float(r[4 * k + 2]) + bb.z, __uint_as_float(r[4 * k + 3]) + bb.w);
+                        }
+                        fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0) {
+                            tma_store_3d(&map_out, buf, (q & 1) * 128, q >> 1, (int)((d * p.m_tiles + m_tile) * H + u));
+                            bulk_commit_group();
+                        }
+                    } else if (lim == 32 && u + 8 <= H && bias_in_smem) {
                         // common case: 8 whole units of one direction -> straight-line code, constant store offsets
                         const float4 *b4 = reinterpret_cast<const float4 *>(bias_s + nb);
 #pragma unroll
@@ -469,7 +491,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
             }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
-        if (p.tma_store && lane == 0) bulk_wait_group<0>();   // stores complete before smem goes away
+        if ((p.tma_store || p.xproj_tma) && lane == 0) bulk_wait_group<0>();   // stores complete before smem goes away
     }
     tc_fence_before();
     if (CG == 2) cluster_sync_all(); else __syncthreads();
@@ -1060,7 +1082,8 @@ int gemm_cta_group() {
 }
 
 // tile / ring geometry of one GEMM launch (everything but the operands' addresses)
-int fill_params(TcParams &p, const GemmWeights &w, int64_t plane_rows, bool allow_bstat = true, bool small_epi = false) {
+int fill_params(TcParams &p, const GemmWeights &w, int64_t plane_rows, bool allow_bstat = true, bool small_epi = false,
+                bool xproj_tma = false) {
     const int cg = gemm_cta_group();
     p.m_tiles = (plane_rows + BM - 1) / BM;
     p.BN = w.BN; p.Np = w.Np; p.N = w.N; p.n_tiles = w.Np / w.BN;
@@ -1076,6 +1099,7 @@ int fill_params(TcParams &p, const GemmWeights &w, int64_t plane_rows, bool allo
     const int bres = p.k_blocks * 2 * b_tile_bytes;
     // the projected-gates epilogue stores straight from registers: its staging area only holds the bias vector
     p.epi_bytes = small_epi && w.Np * 4 <= 4096 ? 4096 : EPI_STAGE_BYTES;
+    if (xproj_tma && w.Np * 4 <= 4096) p.epi_bytes = EPI_STAGE_BYTES + 4096;     // store staging + bias vector
     const int budget = SMEM_BUDGET + EPI_STAGE_BYTES - p.epi_bytes;
     p.bstat = (allow_bstat && small_epi && !no_bstat && cg == 2 && p.passes == 3 && p.taps == 1 && p.n_tiles > 1 && p.n_tiles <= sm_count() / 2 &&
                bres + 3 * 2 * A_TILE_BYTES <= budget) ? 1 : 0;
@@ -1126,6 +1150,22 @@ int do_launch(cudaStream_t st, const CUtensorMap &ma_hi, const CUtensorMap &ma_l
     return NTB_OK;
 }
 
+// store view of the projected-gates buffer (layout: make_map_xproj below): one warp's [8 units][32 rows] float4 tile
+int make_map_xproj_store(CUtensorMap *m, const float *xproj, int64_t units_total) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return fail(NTB_ECUDA, "cuTensorMapEncodeTiled entry point not found%s", "");
+    cuuint64_t dims[3] = {256, 2, (cuuint64_t)units_total};
+    cuuint64_t strides[2] = {1024, 2048};
+    cuuint32_t box[3] = {128, 1, 8};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float *>(xproj), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(NTB_ECUDA, "cuTensorMapEncodeTiled (xproj store) failed (%s%lld) units %lld", "", (long long)r, (long long)units_total);
+    return NTB_OK;
+}
+
 int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, int64_t plane_rows, int T, int pad,
                 int64_t out_rows, const float *bias, float *out, int ldo, int64_t *launches, int xproj_H = 0,
                 float2 *bn_part = nullptr) {
@@ -1136,7 +1176,12 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     NTB_TRY(make_map(&mb_hi, w.hi, (int64_t)w.taps * w.Np, w.Kp, w.BN / cg));
     NTB_TRY(make_map(&mb_lo, w.lo, (int64_t)w.taps * w.Np, w.Kp, w.BN / cg));
     TcParams p{};
-    NTB_TRY(fill_params(p, w, plane_rows, true, xproj_H > 0));
+    // opt-in (NTB_XPROJ_TMA=1): measured SLOWER than the register-direct stores (projection 28.4 vs 23.8 ms per 65 536
+    // windows, profiles/r01_final_ablations.txt) -- the staging round trip costs more than the store path saves
+    static const bool xtma_on = getenv("NTB_XPROJ_TMA") && getenv("NTB_XPROJ_TMA")[0] == '1';
+    const bool xtma = xproj_H > 0 && xtma_on && w.Np * 4 <= 4096 && bias;
+    NTB_TRY(fill_params(p, w, plane_rows, true, xproj_H > 0, xtma));
+    p.xproj_tma = xtma ? 1 : 0;
     p.T = T; p.pad = pad; p.out_rows = out_rows; p.bias = bias; p.out = out; p.ldo = ldo;
     p.xproj_H = xproj_H;
     p.bn_part = bn_part;
@@ -1147,6 +1192,7 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
                    (reinterpret_cast<uintptr_t>(out) & 15) == 0) ? 1 : 0;
     CUtensorMap mo = ma_hi;
     if (p.tma_store) NTB_TRY(make_map_out(&mo, out, out_rows, w.N, ldo));
+    if (p.xproj_tma) NTB_TRY(make_map_xproj_store(&mo, out, 2 * p.m_tiles * (int64_t)xproj_H));
     return do_launch(st, ma_hi, ma_lo, mb_hi, mb_lo, mo, p, launches);
 }
 

@@ -558,6 +558,123 @@ __global__ void __launch_bounds__(256) k_readout_small_pipe(
     }
 }
 
+// Vectorised form for F % 4 == 0, F <= 128 (F = 100 in the shipped CRNN configs): lane l owns features 4l .. 4l+3
+// (one 16-byte load per direction and row, row t + 1 in flight under the reduction of row t), and the C class sums
+// are reduced across the warp TRANSPOSED -- every butterfly step halves the number of classes a lane carries
+// (MAXC/2 + MAXC/4 + ... shuffles instead of 5 per class) -- then gathered for the first-max argmax.
+template <int MAXC>
+__global__ void __launch_bounds__(256) k_readout_small_vec(
+    const float *__restrict__ v, int F_in, const float *__restrict__ fnn_w, const float *__restrict__ fnn_b,
+    const float *__restrict__ out_w, const float *__restrict__ out_b, const int32_t *__restrict__ lens,
+    int64_t n_windows, int T, int C, int graph, float *__restrict__ logits, int32_t *__restrict__ labels,
+    int32_t *__restrict__ label_len) {
+    static_assert(MAXC == 4 || MAXC == 8, "class tile");
+    const int F = fnn_w ? F_in / 2 : F_in;
+    const int lane = threadIdx.x & 31;
+    const int64_t w = (int64_t)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+    if (w >= n_windows) return;
+    const bool own = 4 * lane < F;
+    float wd[4][MAXC], fw0[4], fw1[4], fb[4], ob[MAXC];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int f = 4 * lane + k;
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) wd[k][c] = (own && c < C) ? out_w[f * C + c] : 0.0f;
+        fw0[k] = (own && fnn_w) ? fnn_w[f] : 1.0f;
+        fw1[k] = (own && fnn_w) ? fnn_w[F + f] : 0.0f;
+        fb[k] = (own && fnn_w) ? fnn_b[f] : 0.0f;
+    }
+#pragma unroll
+    for (int c = 0; c < MAXC; ++c) ob[c] = c < C ? out_b[c] : 0.0f;
+    const int len = lens[w];
+    const float *row = v + w * T * (int64_t)F_in + 4 * lane;
+    const float4 z4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    float4 a = own ? __ldg(reinterpret_cast<const float4 *>(row)) : z4;
+    float4 b = (own && fnn_w) ? __ldg(reinterpret_cast<const float4 *>(row + F)) : z4;
+    // lane that ends up holding class c after the transposed reduction (bits 4, 3[, 2] of the lane select the class)
+    int prev = -1, cnt = 0;
+    for (int t = 0; t < T; ++t) {
+        float4 na = z4, nb = z4;
+        if (t + 1 < T && own) {
+            na = __ldg(reinterpret_cast<const float4 *>(row + (int64_t)(t + 1) * F_in));
+            if (fnn_w) nb = __ldg(reinterpret_cast<const float4 *>(row + (int64_t)(t + 1) * F_in + F));
+        }
+        const float av[4] = {a.x, a.y, a.z, a.w}, bv4[4] = {b.x, b.y, b.z, b.w};
+        float part[MAXC];
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) part[c] = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float y = fnn_w ? av[k] * fw0[k] + bv4[k] * fw1[k] + fb[k] : av[k];
+#pragma unroll
+            for (int c = 0; c < MAXC; ++c) part[c] = fmaf(y, wd[k][c], part[c]);
+        }
+        // transposed butterfly: after the step with offset o a lane carries half as many classes
+        float r4[4];
+        if (MAXC == 8) {
+            const bool up = lane & 16;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float send = up ? part[i] : part[i + 4];
+                const float keep = up ? part[i + 4] : part[i];
+                r4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) r4[i] = part[i];
+        }
+        float r2[2], r1;
+        {
+            const int o = MAXC == 8 ? 8 : 16;
+            const bool up = lane & o;
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const float send = up ? r4[i] : r4[i + 2];
+                const float keep = up ? r4[i + 2] : r4[i];
+                r2[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+            }
+        }
+        {
+            const int o = MAXC == 8 ? 4 : 8;
+            const bool up = lane & o;
+            const float send = up ? r2[0] : r2[1];
+            const float keep = up ? r2[1] : r2[0];
+            r1 = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+#pragma unroll
+        for (int o = (MAXC == 8 ? 2 : 4); o > 0; o >>= 1) r1 += __shfl_xor_sync(0xffffffffu, r1, o);
+        // class c lives in the lanes whose top bits spell c (MAXC = 8: bits 4,3,2; MAXC = 4: bits 4,3)
+        int best = 0;
+        float bvv = 0.0f;
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) {
+            if (c < C) {
+                const int src = MAXC == 8 ? (((c >> 2) & 1) << 4) | (((c >> 1) & 1) << 3) | ((c & 1) << 2)
+                                          : (((c >> 1) & 1) << 4) | ((c & 1) << 3);
+                const float lg = __shfl_sync(0xffffffffu, r1, src) + ob[c];
+                if (logits && lane == c) logits[(w * T + t) * (int64_t)C + c] = lg;
+                if (c == 0 || lg > bvv) { bvv = lg; best = c; }   // strict > : first max wins
+            }
+        }
+        if (graph == NTB_GRAPH_CTC) {
+            if (t < len) {
+                if (best != C - 1 && best != prev) {
+                    if (lane == 0) labels[w * T + cnt] = best;
+                    ++cnt;
+                }
+                prev = best;
+            }
+        } else if (lane == 0) {
+            labels[w * T + t] = best;
+        }
+        a = na; b = nb;
+    }
+    if (graph == NTB_GRAPH_CTC) {
+        for (int i = cnt + lane; i < T; i += 32) labels[w * T + i] = -1;
+        if (lane == 0 && label_len) label_len[w] = cnt;
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // Decode for large C (event model, C = 1025): logits already materialised by the dense GEMM.
 // argmax: one warp per row; CTC: one warp per window walking t.

@@ -47,7 +47,11 @@ struct LstmTcParams {
     int64_t n_windows;
     int n_tiles;                      // ceil(n_windows / 128)
     int T, H, Hp;                     // Hp = H rounded up to 16
-    int flags;                        // debug/ablation: 2 = no slice overlap, 16 = L2 prefetch of the next step, 32 = warp-3 L2 prefetch two steps ahead, 64 = hi.hi pass only, 128 = no MMA (timing only), 256 = no projected-gates stream (timing only)
+    // next_hi/next_lo != null: h_t is emitted as the NEXT layer's projection operand (fp16 hi/lo planes, time-major
+    // 128-window tiles: plane row (tile*T + t)*128 + window, next_K columns) instead of the fp32 `out`
+    op16_t *next_hi, *next_lo;
+    int next_K;
+    int flags;                        // debug/ablation: 2 = no slice overlap, 16 = L2 prefetch of the next step, 32 = warp-3 L2 prefetch two steps ahead, 64 = hi.hi pass only, 128 = no MMA (timing only), 256 = no projected-gates stream (timing only), 512 = no output stores (timing only)
 };
 
 static inline bool lstm_tc_supported(int H) {
@@ -233,7 +237,10 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
         uint32_t slot = 0, xph = 0;                              // ring position
         float *orow = p.out + (w * T + (dir ? T - 1 : 0)) * (int64_t)p.ldo + dir * H + half * 4;
         const int64_t ostep = dir ? -(int64_t)p.ldo : (int64_t)p.ldo;
-        for (int s = 0; s < T; ++s, orow += ostep) {
+        const bool planes = p.next_hi != nullptr;
+        int64_t poff = (((int64_t)tile * T + (dir ? T - 1 : 0)) * LSTM_TC_ROWS + r) * p.next_K + dir * H + half * 4;
+        const int64_t pstep = (dir ? -1 : 1) * (int64_t)LSTM_TC_ROWS * p.next_K;
+        for (int s = 0; s < T; ++s, orow += ostep, poff += pstep) {
             const int t = dir ? T - 1 - s : s;
             const bool active = t < len;
             uint32_t dh[8][2], dl[8][2];                         // h of the slice-0 chunks, written once slice 1 is done
@@ -295,7 +302,12 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
                             tmem_st_32x2(ah_col + (uint32_t)(4 * c), ph2[0], ph2[1]);
                             tmem_st_32x2(al_col + (uint32_t)(4 * c), pl2[0], pl2[1]);
                         }
-                        if (exists) *reinterpret_cast<float4 *>(orow + 8 * c) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+                        if (planes) {       // rows of windows past the end are written too (zeros: len = 0)
+                            *reinterpret_cast<uint2 *>(p.next_hi + poff + 8 * c) = make_uint2(ph2[0], ph2[1]);
+                            *reinterpret_cast<uint2 *>(p.next_lo + poff + 8 * c) = make_uint2(pl2[0], pl2[1]);
+                        } else if (exists && !(p.flags & 512)) {
+                            *reinterpret_cast<float4 *>(orow + 8 * c) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+                        }
                     }
                     // every lane has consumed its x values (data dependence) -> the slot may be refilled
                     __syncwarp();
