@@ -12,7 +12,7 @@ every rank processes its own ``--windows`` windows (reads shard across GPUs, no 
 the data path); ``value`` = valid samples of all ranks / max-over-ranks device time.
 
 One JSON line is printed by rank 0 (keys: see DESIGN.md "Measurement").  ``--impl reference``
-times the CPU restatement of the reference's TensorFlow forward (oracle/oracle_torch.py, all host
+times the CPU restatement of the reference's TensorFlow forward (oracle/oracle_cpu.cpp, C++/OpenMP, all host
 threads) on a bounded sample of the same workload: TensorFlow 1.4 itself is unavailable on the
 box.
 """
@@ -127,33 +127,51 @@ class ClockSampler(threading.Thread):
 
 
 # ---------------------------------------------------------------------------- CPU baseline
-def cpu_baseline(n_windows, seed=1234):
-    """Times oracle/oracle_torch.forward_job (the CPU restatement of the reference's TF forward,
-    all host threads, best-case large batch with per-batch BN kept) on a bounded sample."""
+def _cpu_forward():
+    """The CPU arm: oracle/oracle_cpu.cpp (C++/OpenMP restatement of the reference's TF forward, all host threads)
+    -- the faster of the two CPU restatements; oracle/oracle_torch.py if the library has not been built."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import torch
-    import oracle_np as A
-    import oracle_torch as B
     net, w = network_and_weights()
     cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
+    try:
+        import oracle_cpu as Cc
+        Cc.load()
 
-    def run(nw):
-        x, lens, _ = make_workload(nw, seed)
-        t0 = time.perf_counter()
-        logits = B.forward_job(x, lens, net, w, "CtcLoss", BATCH)
-        A.ctc_greedy(logits, lens)                       # the label output is part of the path
-        return time.perf_counter() - t0, int(lens.sum())
+        def run(x, lens, goff):
+            Cc.forward(x, lens, net, w, "CtcLoss", group_off=goff, n_threads=cores)   # logits + CTC-greedy labels
+        return run, cores, "C++/OpenMP restatement (oracle/oracle_cpu.cpp)"
+    except Exception:
+        import torch
+        import oracle_np as A
+        import oracle_torch as B
+        torch.set_num_threads(cores)
 
-    run(BATCH * 8)                                       # warm the thread pool / allocators
+        def run(x, lens, goff):
+            A.ctc_greedy(B.forward_job(x, lens, net, w, "CtcLoss", BATCH), lens)
+        return run, cores, "torch-CPU restatement (oracle/oracle_torch.py)"
+
+
+def _cpu_sample_size(run, target_s, cap):
+    x, lens, goff = make_workload(BATCH * 64, 1234)
+    run(x[:BATCH * 8], lens[:BATCH * 8], goff[:9])           # warm the thread pool / allocators
+    t0 = time.perf_counter()
+    run(x, lens, goff)
+    dt = time.perf_counter() - t0
+    return int(max(BATCH * 64, min(cap, (target_s / dt) * BATCH * 64)) // BATCH * BATCH)
+
+
+def cpu_baseline(n_windows):
+    """Times the CPU restatement of the reference's forward (per-batch BN kept, BN groups of 10) on a bounded sample."""
+    run, cores, what = _cpu_forward()
     if n_windows <= 0:
-        dt, _ = run(BATCH * 64)
-        n_windows = int(max(BATCH * 64, min(65536, (12.0 / dt) * BATCH * 64)) // BATCH * BATCH)
-    dt, samples = run(n_windows)
-    return {"value": samples / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "%d windows (T=%d, BN groups of %d) of the same workload, %.1f s; torch-CPU restatement "
-                      "(oracle/oracle_torch.py), %d threads; TensorFlow 1.4 reference unavailable on this box"
-                      % (n_windows, T, BATCH, dt, cores)}
+        n_windows = _cpu_sample_size(run, 12.0, 65536)
+    x, lens, goff = make_workload(n_windows, 1234)
+    t0 = time.perf_counter()
+    run(x, lens, goff)
+    dt = time.perf_counter() - t0
+    return {"value": int(lens.sum()) / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d windows (T=%d, BN groups of %d) of the same workload, %.1f s; %s, %d threads; "
+                      "TensorFlow 1.4 reference unavailable on this box" % (n_windows, T, BATCH, dt, what, cores)}
 
 
 # ---------------------------------------------------------------------------- reference arm
@@ -163,37 +181,22 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return 0
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import torch
-    import oracle_np as A
-    import oracle_torch as B
-    net, w = network_and_weights()
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
+    os.environ.pop("OMP_NUM_THREADS", None)       # torchrun pins it to 1; the arm uses every host thread explicitly
+    run, cores, what = _cpu_forward()
     nw = args.cpu_windows
     if nw <= 0:
-        x, lens, _ = make_workload(BATCH * 64, 1234)
-        B.forward_job(x[:BATCH * 8], lens[:BATCH * 8], net, w, "CtcLoss", BATCH)
-        t0 = time.perf_counter()
-        B.forward_job(x, lens, net, w, "CtcLoss", BATCH)
-        dt = time.perf_counter() - t0
-        nw = int(max(BATCH * 64, min(32768, (5.0 / dt) * BATCH * 64)) // BATCH * BATCH)
-    x, lens, _ = make_workload(nw, 1234)
+        nw = _cpu_sample_size(run, 5.0, 32768)
+    x, lens, goff = make_workload(nw, 1234)
     samples = int(lens.sum())
-
-    def step():
-        logits = B.forward_job(x, lens, net, w, "CtcLoss", BATCH)
-        A.ctc_greedy(logits, lens)
-
     for _ in range(args.warmup):
-        step()
+        run(x, lens, goff)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        step()
+        run(x, lens, goff)
     dt = (time.perf_counter() - t0) / max(args.steps, 1)
     value = samples / dt
-    sample = ("%d windows per step (T=%d, BN groups of %d), torch-CPU restatement of the TF forward "
-              "(oracle/oracle_torch.py), %d threads; TensorFlow 1.4 unavailable on this box" % (nw, T, BATCH, cores))
+    sample = ("%d windows per step (T=%d, BN groups of %d), %s, %d threads; TensorFlow 1.4 unavailable on this box"
+              % (nw, T, BATCH, what, cores))
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",

@@ -260,6 +260,8 @@ __global__ void __launch_bounds__(256) k_bn_finish(const float2 *__restrict__ pa
         int64_t w_first = (b0 << 5) / Tp;
         int rem = (int)((b0 << 5) - w_first * Tp);
         const float2 *rec = part + (b0 * 2) * C + ch;
+        // unrolled: the (predicated) record loads of 8 blocks are in flight together; the fp64 fold order is unchanged
+#pragma unroll 8
         for (int64_t b = b0; b <= b1; ++b, rec += 2 * C) {
             const bool two = rem + 31 >= Tp;                       // the window changes inside this block (Tp >= 32)
             if (w_first >= wa && w_first < wb) {

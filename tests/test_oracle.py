@@ -170,3 +170,54 @@ def test_process_output_assembly():
     np.testing.assert_array_equal(simple_assembly(["ACGT"]), A.simple_assembly(["ACGT"]))
     np.testing.assert_array_equal(simple_assembly(["ACGTAC", "TTACGTAC", "GTACC"]),
                                   A.simple_assembly(["ACGTAC", "TTACGTAC", "GTACC"]))
+
+
+# ---------------------------------------------------------------- the C++/OpenMP restatement (oracle/oracle_cpu.cpp)
+def _cpu():
+    import subprocess
+    import oracle_cpu as Cc
+    if not os.path.exists(Cc.LIB_PATH):
+        subprocess.check_call(["bash", os.path.join(os.path.dirname(Cc.LIB_PATH), "build.sh")])
+    return Cc
+
+
+def test_cpp_oracle_event_fixture_matches_golden(golden_dir):
+    Cc = _cpu()
+    g, net, w = _event(golden_dir)
+    logits, labels, _ = Cc.forward(g["x"], g["lens"], net, w, "CrossEntropy", batch_size=16)
+    np.testing.assert_allclose(logits[:240], g["logits_head"], atol=2e-5)
+    np.testing.assert_allclose(logits.max(1), g["logits_rowmax"], atol=2e-5)
+    assert float((labels == g["labels"]).mean()) >= 0.999
+
+
+@pytest.mark.parametrize("name,key", [("crnn_signal", "signal_CRNN"), ("crnn_run_nanotensor", "run_nanotensor")])
+def test_cpp_oracle_crnn_matches_golden(golden_dir, name, key):
+    Cc = _cpu()
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    net = syn.NETWORKS[key]
+    C = int(g["n_classes"])
+    w = syn.random_weights(net, 1, C, seed=int(g["seed"]) + 2)
+    logits, labels, llen = Cc.forward(g["x"], g["lens"], net, w, "CtcLoss", group_off=g["group_off"])
+    np.testing.assert_allclose(logits, g["logits"].reshape(-1, C), atol=1e-4)
+    # integer outputs from the GOLDEN logits are bit-exact; from its own logits they may differ only at near ties
+    agree = float((labels == g["labels"]).mean())
+    assert agree >= 0.999, agree
+
+
+def test_cpp_oracle_ragged_blstm_and_ctc_rules():
+    Cc = _cpu()
+    rng = np.random.default_rng(9)
+    net = [{"type": "blstm", "name": "l1", "size": 8, "bias": 5.0, "concat": True},
+           {"type": "blstm", "name": "l2", "size": 8, "bias": 1.0, "concat": True}]
+    w = syn.random_weights(net, 3, 5, seed=4, graph="CtcLoss", readout_gain=4.0)
+    x = rng.standard_normal((9, 11, 3)).astype(np.float32)
+    lens = np.array([11, 0, 1, 5, 11, 7, 2, 30, 10], dtype=np.int32)     # 0, 1, > T
+    lg, labels, llen = Cc.forward(x, lens, net, w, "CtcLoss", batch_size=4)
+    # the logits do not depend on the graph kind (oracle_np's CtcLoss graph insists on len_x = 1, network.py:515-518)
+    ref, _ = A.forward_batch(x, np.minimum(lens, 11), net, w, "CrossEntropy")
+    np.testing.assert_allclose(lg, ref.reshape(-1, 5), atol=2e-5)
+    rl, _ = A.ctc_greedy(lg.reshape(9, 11, 5), np.minimum(lens, 11))
+    dense = np.full((9, 11), -1)
+    dense[:, :rl.shape[1]] = rl
+    assert np.array_equal(labels, dense)
+    assert np.array_equal(llen, (dense >= 0).sum(1))
