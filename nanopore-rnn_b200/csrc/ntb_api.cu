@@ -204,6 +204,7 @@ static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &a
         return dst;
     };
     int dim = d->len_x;
+    bool m_prev_tc = false;      // the previous layer is a BLSTM on the tensor-core recurrence
     for (int i = 0; i < d->n_layers; ++i) {
         const ntb_layer &l = d->layers[i];
         LayerDev ld;
@@ -233,9 +234,17 @@ static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &a
             ld.wih = ar.take<float>((int64_t)D * 8 * Hp);
             ld.bias = ar.take<float>(8 * Hp);
             ld.whh = ar.take<float>(2LL * H * Hp * 4);
-            gemm_tc_plan_weights(ld.wihw, 1, D, 8 * Hp, ar);
+            // a BLSTM layer fed by a tensor-core BLSTM layer can take its input as the interleaved hi/lo plane the previous
+            // recurrence writes (no operand-split pass, no fp32 hand-over).  Opt-in (NTB_ILV=1): it removes k_split_op16 but
+            // the projection GEMM then runs 2 passes over 2K columns (7 instead of 4 k-blocks at K = 200) and loses exactly
+            // what the split cost (projection stage 26.8 vs 26.5 ms per 65 536 windows, profiles/r01_final_ablations.txt)
+            static const bool no_ilv = !(getenv("NTB_ILV") && getenv("NTB_ILV")[0] == '1');
+            const bool prev_tc = i > 0 && d->layers[i - 1].type == NTB_LAYER_BLSTM && m_prev_tc;
+            const bool can_tc = Hp == H && lstm_tc_supported(H) && D % 8 == 0 && D >= 64;
+            gemm_tc_plan_weights(ld.wihw, 1, D, 8 * Hp, ar, prev_tc && can_tc && !no_ilv);
             ld.kernel_fw = kf; ld.kernel_bw = kb;
             ld.tc_rec = ld.wihw.valid && Hp == H && lstm_tc_supported(H);
+            m_prev_tc = ld.tc_rec;
             if (ld.tc_rec) {
                 ld.whh_hi = ar.take<op16_t>(lstm_tc_whh_elems(H));
                 ld.whh_lo = ar.take<op16_t>(lstm_tc_whh_elems(H));
@@ -538,9 +547,17 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
                 const bool feed_next = rec_planes && li + 1 < nl && m->layers[li + 1].type == NTB_LAYER_BLSTM &&
                                        m->layers[li + 1].tc_rec && 2 * ld.size <= ws.gs.kp_cap && (2 * ld.size) % 8 == 0;
                 if (feed_next) { p.next_hi = ws.gs.a_hi; p.next_lo = ws.gs.a_lo; p.next_K = 2 * ld.size; }
+                const bool feed_ilv = li + 1 < nl && m->layers[li + 1].type == NTB_LAYER_BLSTM && m->layers[li + 1].wihw.ilv;
+                if (feed_ilv) {
+                    if (!ws.gs.contiguous() ||
+                        (int64_t)p.n_tiles * LSTM_TC_ROWS * T * 4 * ld.size > 2 * ws.gs.rows_cap * (int64_t)ws.gs.kp_cap)
+                        return fail(NTB_EINVAL, "blstm: operand scratch too small for the interleaved hand-over%s", "");
+                    p.next_hi = p.next_lo = nullptr;
+                    p.next_ilv = ws.gs.a_hi; p.next_K = 2 * ld.size;
+                }
                 NTB_TRY(launch_lstm_tc(cx, p));
                 dim = 2 * ld.size;
-                planes = feed_next ? 2 : 0;
+                planes = (feed_next || feed_ilv) ? 2 : 0;
                 cur = out;
                 flip ^= 1;
                 continue;

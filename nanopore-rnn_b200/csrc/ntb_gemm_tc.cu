@@ -44,7 +44,7 @@ struct TcParams {
     int n_tiles, BN, Np, N;
     int taps, k_blocks;    // k_blocks per tap = ceil(K / 64)
     int k16_last;          // k16 steps in the last k block of a tap
-    int passes;            // 3 = fp16x3, 1 = plain bf16 (ablation only)
+    int passes;            // 3 = fp16x3, 2 = interleaved-A form (one A plane, B' and B''), 1 = plain bf16 (ablation only)
     int stages;
     int T, pad;            // pad = 1: plane rows are [window][T+2]
     int64_t out_rows;      // rows of `out`
@@ -54,6 +54,7 @@ struct TcParams {
     int tma_store;         // plain row-major output through smem staging + cp.async.bulk.tensor stores
     int xproj_H;           // > 0: out is the recurrence's unit-major projected-gates layout (ntb_lstm_tc.cuh)
     int xproj_tma;         // projected-gates epilogue through smem staging + 3-D TMA stores (map_out = store map)
+    int l2pf;              // opt-in experiment: the producer prefetches the NEXT work item's A tiles into L2 (measured slower)
     int abl;               // timing ablation (NTB_XPROJ_ABL): 1 = projected-gates epilogue without its global stores
     int epi_bytes;         // bytes reserved behind the operand ring (TMA-store staging, or just the bias vector)
     int bstat;             // B-stationary schedule (CG = 2, several N tiles, small K): every CTA pair keeps ONE weight
@@ -129,7 +130,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
     uint8_t *smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);     // 1024 B: swizzle-128B atoms
     const int b_tile_bytes = (p.BN / CG) * BK * 2;               // this CTA's share of the B tile
     const bool bstat = CG == 2 && p.bstat;
-    const int stage_bytes = bstat ? 2 * A_TILE_BYTES : (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + b_tile_bytes);
+    const int stage_bytes = bstat ? 2 * A_TILE_BYTES
+                          : p.passes == 2 ? A_TILE_BYTES + 2 * b_tile_bytes : (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + b_tile_bytes);
     const int bres_bytes = bstat ? p.k_blocks * 2 * b_tile_bytes : 0;   // resident B: [k block][hi | lo]
     uint8_t *stages_base = smem + bres_bytes;
     __shared__ uint64_t b_full;
@@ -194,6 +196,16 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
             for (int64_t it = 0; item(it, mg, n_tile); ++it) {
                 const int64_t m_tile = mg * CG + rank;
                 const int dir_rows = (p.lstm_H > 0 && m_tile >= p.lstm_mt_dir) ? p.Np : 0;   // W_hh of the bw direction
+                if (p.l2pf) {
+                    int64_t mg2; int nt2;
+                    if (item(it + 1, mg2, nt2) && mg2 != mg) {
+                        const int r2 = (int)((mg2 * CG + rank) * BM) - left;
+                        for (int kb = 0; kb < p.k_blocks; ++kb) {
+                            tma_prefetch_2d(&map_a_hi, kb * BK, r2);
+                            if (p.passes == 3) tma_prefetch_2d(&map_a_lo, kb * BK, r2);
+                        }
+                    }
+                }
                 for (int tap = 0; tap < p.taps; ++tap) {
                     const int row0 = (int)(m_tile * BM) + tap - left;
                     const int brow0 = tap * p.Np + n_tile * p.BN + rank * (p.BN / CG) + dir_rows;
@@ -211,6 +223,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                             if (p.passes == 3) {
                                 tma_load_2d(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], kb * BK, row0);
                                 tma_load_2d(s + 2 * A_TILE_BYTES + b_tile_bytes, &map_b_lo, &full_bar[stage], kb * BK, brow0);
+                            } else if (p.passes == 2) {
+                                tma_load_2d(s + A_TILE_BYTES + b_tile_bytes, &map_b_lo, &full_bar[stage], kb * BK, brow0);
                             }
                         } else {
                             // both CTAs' bytes are credited to the LEADER's full barrier
@@ -220,6 +234,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                             if (p.passes == 3) {
                                 tma_load_2d_pair(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], kb * BK, row0);
                                 tma_load_2d_pair(s + 2 * A_TILE_BYTES + b_tile_bytes, &map_b_lo, &full_bar[stage], kb * BK, brow0);
+                            } else if (p.passes == 2) {
+                                tma_load_2d_pair(s + A_TILE_BYTES + b_tile_bytes, &map_b_lo, &full_bar[stage], kb * BK, brow0);
                             }
                         }
                         if (++stage == p.stages) { stage = 0; phase ^= 1; }
@@ -258,12 +274,16 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                             if (p.passes == 3) {
                                 umma_f16(d_tmem, desc_advance_k16(a_lo, k), desc_advance_k16(b_hi, k), idesc, 1);
                                 umma_f16(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_lo, k), idesc, 1);
+                            } else if (p.passes == 2) {     // a_lo's slot holds B'' here
+                                umma_f16(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(a_lo, k), idesc, 1);
                             }
                         } else {
                             umma_f16_pair(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_hi, k), idesc, (kb | k) != 0);
                             if (p.passes == 3) {
                                 umma_f16_pair(d_tmem, desc_advance_k16(a_lo, k), desc_advance_k16(b_hi, k), idesc, 1);
                                 umma_f16_pair(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_lo, k), idesc, 1);
+                            } else if (p.passes == 2) {     // a_lo's slot holds B'' here
+                                umma_f16_pair(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(a_lo, k), idesc, 1);
                             }
                         }
                     }
@@ -969,6 +989,24 @@ __global__ void k_pack_weights(const float *__restrict__ w, int taps, int K, int
     }
 }
 
+// Interleaved-A form of the same weights (GemmWeights::ilv): operand column k' = 8 * (k / 4) + 4 * slot + k % 4 of the
+// A plane is the hi (slot 0) or lo (slot 1) part of source column k, so B'[n][k'] = hi(W[k][n]) and B''[n][k'] = lo(W[k][n])
+// in BOTH slots.
+__global__ void k_pack_weights_ilv(const float *__restrict__ w, int Ksrc, int N, int Kp, int Np,
+                                   op16_t *__restrict__ hi, op16_t *__restrict__ lo) {
+    const int64_t total = (int64_t)Np * Kp;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int kk = (int)(i % Kp);
+        const int n = (int)(i / Kp);
+        const int k = 4 * (kk >> 3) + (kk & 3);
+        const float v = (k < Ksrc && n < N) ? w[(int64_t)k * N + n] : 0.0f;
+        op16_t h, l;
+        ptx::split_op16(v, h, l);
+        hi[i] = h;
+        lo[i] = l;
+    }
+}
+
 // ------------------------------------------------------------------------------------------ host
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
@@ -1089,9 +1127,9 @@ int fill_params(TcParams &p, const GemmWeights &w, int64_t plane_rows, bool allo
     p.BN = w.BN; p.Np = w.Np; p.N = w.N; p.n_tiles = w.Np / w.BN;
     p.taps = w.taps; p.k_blocks = (w.K + BK - 1) / BK;
     p.k16_last = ((w.K - (p.k_blocks - 1) * BK) + 15) / 16;
-    p.passes = w.single_pass ? 1 : 3;
+    p.passes = w.single_pass ? 1 : (w.ilv ? 2 : 3);
     const int b_tile_bytes = (w.BN / cg) * BK * 2;
-    int stage_bytes = (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + b_tile_bytes);   // per CTA
+    int stage_bytes = p.passes == 2 ? A_TILE_BYTES + 2 * b_tile_bytes : (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + b_tile_bytes);   // per CTA
     // B-stationary (opt-in, NTB_BSTAT=1): measured on the LSTM projections (K <= 256, N = 800) it ties with the
     // streaming schedule (26.7 vs 27.0 ms per 65 536 windows) -- these GEMMs are bound by the 2.6 GB projected-gates
     // write, not by the operand feed from L2 -- so streaming stays the default
@@ -1118,7 +1156,8 @@ int do_launch(cudaStream_t st, const CUtensorMap &ma_hi, const CUtensorMap &ma_l
               const CUtensorMap &mb_lo, const CUtensorMap &mo, const TcParams &p, int64_t *launches) {
     const int cg = gemm_cta_group();
     const int b_tile_bytes = (p.BN / cg) * BK * 2;
-    const int stage_bytes = p.bstat ? 2 * A_TILE_BYTES : (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + b_tile_bytes);
+    const int stage_bytes = p.bstat ? 2 * A_TILE_BYTES
+                          : p.passes == 2 ? A_TILE_BYTES + 2 * b_tile_bytes : (p.passes == 3 ? 2 : 1) * (A_TILE_BYTES + b_tile_bytes);
     const size_t smem = (size_t)p.stages * stage_bytes + (p.bstat ? p.k_blocks * 2 * b_tile_bytes : 0) + 1024 + p.epi_bytes;
     static bool attr_set = false;
     if (!attr_set) {
@@ -1172,7 +1211,8 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     const int cg = gemm_cta_group();
     CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
     NTB_TRY(make_map(&ma_hi, gs.a_hi, plane_rows, w.K, BM));
-    NTB_TRY(make_map(&ma_lo, gs.a_lo, plane_rows, w.K, BM));
+    if (w.ilv) ma_lo = ma_hi;      // one interleaved plane [rows][2 Ksrc] spanning both scratch planes
+    else NTB_TRY(make_map(&ma_lo, gs.a_lo, plane_rows, w.K, BM));
     NTB_TRY(make_map(&mb_hi, w.hi, (int64_t)w.taps * w.Np, w.Kp, w.BN / cg));
     NTB_TRY(make_map(&mb_lo, w.lo, (int64_t)w.taps * w.Np, w.Kp, w.BN / cg));
     TcParams p{};
@@ -1187,6 +1227,9 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     p.bn_part = bn_part;
     static const int abl = getenv("NTB_XPROJ_ABL") ? atoi(getenv("NTB_XPROJ_ABL")) : 0;
     p.abl = abl;
+    // opt-in (NTB_GEMM_L2PF=1): measured slower (projection GEMM 7.49 -> 8.93 ms per 65 536 windows, conv stage +2 ms)
+    static const int l2pf = getenv("NTB_GEMM_L2PF") ? atoi(getenv("NTB_GEMM_L2PF")) : 0;
+    p.l2pf = l2pf;
     // coalesced TMA-store epilogue for plain row-major outputs (N tiles of whole 32-column chunks)
     p.tma_store = (!pad && xproj_H == 0 && w.BN % 32 == 0 && (ldo & 3) == 0 &&
                    (reinterpret_cast<uintptr_t>(out) & 15) == 0) ? 1 : 0;
@@ -1216,9 +1259,10 @@ int make_map_xproj(void *map_out, const float *xproj, int64_t units_total) {
     return NTB_OK;
 }
 
-void gemm_tc_plan_weights(GemmWeights &w, int taps, int K, int N, Arena &ar) {
+void gemm_tc_plan_weights(GemmWeights &w, int taps, int K, int N, Arena &ar, bool ilv) {
     w = GemmWeights();
     w.taps = taps; w.K = K; w.N = N;
+    if (ilv && taps == 1 && K % 4 == 0) { w.ilv = true; w.Ksrc = K; w.K = 2 * K; K = 2 * K; }
     // the tensor-core path needs 16-byte rows in the A planes (K % 8) and a worthwhile shape;
     // Cin = 1 convs, len_x = 12 / H = 5 event shapes and the tiny CTC readout stay on the SIMT path
     if (K % 8 != 0 || K < 64 || N < 32) return;
@@ -1236,7 +1280,8 @@ int gemm_tc_pack_weights(cudaStream_t st, const float *w_kn, GemmWeights &w) {
     const int64_t total = (int64_t)w.taps * w.Np * w.Kp;
     int blocks = (int)((total + 255) / 256);
     if (blocks > 1024) blocks = 1024;
-    k_pack_weights<<<blocks, 256, 0, st>>>(w_kn, w.taps, w.K, w.N, w.Kp, w.Np, w.hi, w.lo);
+    if (w.ilv) k_pack_weights_ilv<<<blocks, 256, 0, st>>>(w_kn, w.Ksrc, w.N, w.Kp, w.Np, w.hi, w.lo);
+    else k_pack_weights<<<blocks, 256, 0, st>>>(w_kn, w.taps, w.K, w.N, w.Kp, w.Np, w.hi, w.lo);
     NTB_LAUNCH_CHECK();
     return NTB_OK;
 }
@@ -1275,6 +1320,15 @@ int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_window
                       bool planes_ready, void (*before_gemm)(void *), void *hook_arg) {
     const int64_t n_tiles = (n_windows + BM - 1) / BM;
     const int64_t plane_rows = n_tiles * BM * T;
+    if (w.ilv) {
+        // the previous recurrence wrote the interleaved plane into the scratch region (both planes, contiguous)
+        if (!w.valid || !gs.valid || !planes_ready || !gs.contiguous() || w.N != 8 * H ||
+            plane_rows * (int64_t)w.K > 2 * gs.rows_cap * (int64_t)gs.kp_cap)
+            return fail(NTB_EINVAL, "tcgen05 projection: interleaved operand not available (windows %s%lld, K %lld)", "",
+                        (long long)n_windows, (long long)w.K);
+        if (before_gemm) before_gemm(hook_arg);
+        return launch_gemm(st, w, gs, plane_rows, 1, 0, plane_rows, bias, xproj, 0, launches, H);
+    }
     if (!w.valid || !gs.valid || plane_rows > gs.rows_cap || w.K > gs.kp_cap || (lda & 3) || w.taps != 1 ||
         w.N != 8 * H || (reinterpret_cast<uintptr_t>(A) & 15))
         return fail(NTB_EINVAL, "tcgen05 projection: operand not supported (windows %s%lld, K %lld)", "",

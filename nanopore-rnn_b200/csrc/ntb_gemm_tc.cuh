@@ -8,6 +8,12 @@ namespace ntb {
 struct GemmWeights {
     bool valid = false;
     bool single_pass = false;   // hi*hi only (plain bf16; measurement / ablation only)
+    // Interleaved-A form (LSTM projections fed straight by the previous recurrence, ntb_lstm_tc.cuh): the A operand is ONE
+    // plane [rows][2*Ksrc] whose 8-element groups are (4 x hi, 4 x lo) of 4 consecutive source columns; K = 2*Ksrc here,
+    // plane `hi` holds W_hi in both slots and plane `lo` holds W_lo in both slots, so two passes A'.B' + A'.B'' give
+    // a_hi.W_hi + a_lo.W_hi + a_hi.W_lo (+ a_lo.W_lo) -- the fp16x3 product without a separate operand-split pass.
+    bool ilv = false;
+    int Ksrc = 0;
     int taps = 1, K = 0, N = 0, Kp = 0, Np = 0, BN = 0;
     op16_t *hi = nullptr, *lo = nullptr;   // [taps][Np][Kp], Kp = K rounded up to 64
 };
@@ -17,9 +23,11 @@ struct GemmScratch {
     int64_t rows_cap = 0;
     int kp_cap = 0;
     op16_t *a_hi = nullptr, *a_lo = nullptr;   // [plane rows][K] of the GEMM in flight
+    // the two planes are adjacent in the workspace: an interleaved-A operand [rows][2K] uses them as one region
+    bool contiguous() const { return a_lo == a_hi + rows_cap * (int64_t)kp_cap; }
 };
 
-void gemm_tc_plan_weights(GemmWeights &w, int taps, int K, int N, Arena &ar);
+void gemm_tc_plan_weights(GemmWeights &w, int taps, int K, int N, Arena &ar, bool ilv = false);
 int gemm_tc_pack_weights(cudaStream_t st, const float *w_kn, GemmWeights &w);
 void gemm_tc_plan_scratch(GemmScratch &gs, int64_t rows, int T, int maxk, Arena &ar, int64_t min_rows = 0);
 int gemm_tc_run(cudaStream_t st, const float *A, int lda, int64_t rows, const GemmWeights &w, const float *bias,

@@ -51,6 +51,10 @@ struct LstmTcParams {
     // 128-window tiles: plane row (tile*T + t)*128 + window, next_K columns) instead of the fp32 `out`
     op16_t *next_hi, *next_lo;
     int next_K;
+    // next_ilv != null (default between tensor-core BLSTM layers): same rows, ONE plane of 2 * next_K columns whose
+    // 8-element groups are (4 x hi, 4 x lo) of 4 consecutive units -- a thread's 4 units are one 16-byte store, the
+    // same store count as the fp32 output, and the next projection consumes the plane directly (GemmWeights::ilv)
+    op16_t *next_ilv;
     int flags;                        // debug/ablation: 2 = no slice overlap, 16 = L2 prefetch of the next step, 32 = warp-3 L2 prefetch two steps ahead, 64 = hi.hi pass only, 128 = no MMA (timing only), 256 = no projected-gates stream (timing only), 512 = no output stores (timing only)
 };
 
@@ -237,7 +241,7 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
         uint32_t slot = 0, xph = 0;                              // ring position
         float *orow = p.out + (w * T + (dir ? T - 1 : 0)) * (int64_t)p.ldo + dir * H + half * 4;
         const int64_t ostep = dir ? -(int64_t)p.ldo : (int64_t)p.ldo;
-        const bool planes = p.next_hi != nullptr;
+        const bool planes = p.next_hi != nullptr, ilv = p.next_ilv != nullptr;
         int64_t poff = (((int64_t)tile * T + (dir ? T - 1 : 0)) * LSTM_TC_ROWS + r) * p.next_K + dir * H + half * 4;
         const int64_t pstep = (dir ? -1 : 1) * (int64_t)LSTM_TC_ROWS * p.next_K;
         for (int s = 0; s < T; ++s, orow += ostep, poff += pstep) {
@@ -302,7 +306,10 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
                             tmem_st_32x2(ah_col + (uint32_t)(4 * c), ph2[0], ph2[1]);
                             tmem_st_32x2(al_col + (uint32_t)(4 * c), pl2[0], pl2[1]);
                         }
-                        if (planes) {       // rows of windows past the end are written too (zeros: len = 0)
+                        if (ilv) {          // rows of windows past the end are written too (zeros: len = 0)
+                            // interleaved plane: twice the columns, same rows
+                            *reinterpret_cast<uint4 *>(p.next_ilv + 2 * poff + 16 * c) = make_uint4(ph2[0], ph2[1], pl2[0], pl2[1]);
+                        } else if (planes) {
                             *reinterpret_cast<uint2 *>(p.next_hi + poff + 8 * c) = make_uint2(ph2[0], ph2[1]);
                             *reinterpret_cast<uint2 *>(p.next_lo + poff + 8 * c) = make_uint2(pl2[0], pl2[1]);
                         } else if (exists && !(p.flags & 512)) {

@@ -6,7 +6,7 @@ import sys,json
 for l in sys.stdin:
     l=l.strip()
     if l.startswith('{'):
-        d=json.loads(l); print(round(d['value']/1e6,2),'M/s', {k:round(v,2) for k,v in d['roofline']['stage_ms_per_step'].items()}, d['clocks']['sm_mhz'])
+        d=json.loads(l); print(round(d['value']/1e6,2),'M/s', {k:round(v,2) for k,v in d['roofline']['stage_ms_per_step'].items()}, d['clocks']['sm_mhz'], 'launches', d['gpu_launches'], 'proj_gemm_us', round(d['roofline']['us_per_launch'],1))
     elif l: print(l[:300])
 "; }
 for cfg in "$@"; do run $cfg; done
