@@ -34,6 +34,8 @@ struct LayerDev {
     const float *bn_scale[4] = {nullptr, nullptr, nullptr, nullptr};
     const float *bn_offset[4] = {nullptr, nullptr, nullptr, nullptr};
     GemmWeights convw[4];   // tensor-core tiles (bf16 hi/lo, K-major) where the shape allows
+    GemmWeights conv12w;    // [conv1 | conv2a] along N: both 1x1 convs of the layer input as one dual-output launch
+    float *conv12_stage = nullptr;   // [Cin][2C] fp32 staging the tiles are packed from
     // blstm
     int Hp = 0;
     float *wih = nullptr, *bias = nullptr, *whh = nullptr;
@@ -223,6 +225,11 @@ static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &a
                 }
                 gemm_tc_plan_weights(ld.convw[c], taps[c], kin[c], C, ar);
             }
+            if (ld.convw[0].valid && ld.convw[1].valid && C % 32 == 0 && !getenv("NTB_NO_DUAL_CONV")) {
+                gemm_tc_plan_weights(ld.conv12w, 1, Cin, 2 * C, ar);
+                if (ld.conv12w.valid && ld.conv12w.BN <= C && C % ld.conv12w.BN == 0) ld.conv12_stage = ar.take<float>((int64_t)Cin * 2 * C);
+                else ld.conv12w = GemmWeights();
+            }
             dim = C;
         } else if (l.type == NTB_LAYER_BLSTM) {
             const int H = l.size, D = dim, Hp = pad_hidden(H);
@@ -304,6 +311,12 @@ extern "C" int ntb_model_create(const ntb_model_desc *desc, void *weights_dev, i
         if (ld.type == NTB_LAYER_RESIDUAL) {
             for (int c = 0; c < 4; ++c)
                 if (ld.convw[c].valid) gemm_tc_pack_weights(st, ld.conv[c], ld.convw[c]);
+            if (ld.conv12w.valid) {
+                const size_t cb = (size_t)ld.size * sizeof(float);
+                cudaMemcpy2DAsync(ld.conv12_stage, 2 * cb, ld.conv[0], cb, cb, ld.in_dim, cudaMemcpyDeviceToDevice, st);
+                cudaMemcpy2DAsync(ld.conv12_stage + ld.size, 2 * cb, ld.conv[1], cb, cb, ld.in_dim, cudaMemcpyDeviceToDevice, st);
+                gemm_tc_pack_weights(st, ld.conv12_stage, ld.conv12w);
+            }
             m->has_res = true;
             if (ld.size > m->max_res_c) m->max_res_c = ld.size;
             if (ld.size > m->max_act_c) m->max_act_c = ld.size;
@@ -346,7 +359,7 @@ struct Workspace {
     float *y1, *y2a, *y2b;
     float *aff[8];
     float *xproj;
-    float2 *bn_part;
+    float2 *bn_part, *bn_part2;
     float *cstate;
     float *logits;
     GemmScratch gs;
@@ -384,7 +397,11 @@ static int64_t plan_workspace(const ntb_model *m, int64_t n, int64_t n_groups, b
     // the per-timestep recurrence keeps its h operand planes (2 parities x 2 dirs x padded windows x H) in the same scratch
     const int64_t step_rows = m->max_step_h ? cdiv(4 * align_up(n, 256) * m->max_step_h, align_up(maxk, 8)) : 0;
     gemm_tc_plan_scratch(ws.gs, rows, m->T, maxk, ar, tile_rows > step_rows ? tile_rows : step_rows);
-    if (m->has_res && ws.gs.valid && m->T >= 32) ws.bn_part = ar.take<float2>(gemm_tc_bn_part_elems(ws.gs, m->max_res_c));
+    ws.bn_part2 = nullptr;
+    if (m->has_res && ws.gs.valid && m->T >= 32) {
+        ws.bn_part = ar.take<float2>(gemm_tc_bn_part_elems(ws.gs, m->max_res_c));
+        ws.bn_part2 = ar.take<float2>(gemm_tc_bn_part_elems(ws.gs, m->max_res_c));
+    }
     return ar.off;
 }
 }  // namespace ntb
@@ -420,7 +437,23 @@ static int residual_forward(Ctx &cx, ntb_model *m, const LayerDev &ld, const flo
         cx.count();
         NTB_LAUNCH_CHECK();
     }
-    for (int c = k1 ? 2 : 0; c < 4; ++c) {
+    int c_first = k1 ? 2 : 0;
+    if (!k1 && ld.conv12w.valid && ws.gs.valid && ws.bn_part && ws.bn_part2 && ld.bn_scale[1]) {
+        // conv1 | conv2a: one dual-output launch over the shared operand planes, then the two BN folds
+        float2 *p1 = ld.bn_scale[0] ? ws.bn_part : nullptr;
+        NTB_TRY(gemm_tc_conv_dual(cx.st, in, Cin, rows, T, ld.conv12w, ys[0], ys[1], C, ws.gs, &cx.launches, in_planes, p1,
+                                  ws.bn_part2));
+        for (int c = 0; c < 2; ++c) {
+            if (!ld.bn_scale[c]) continue;
+            dim3 grid((unsigned)n_groups, cdiv(C, 256));
+            k_bn_finish<<<grid, 256, 0, cx.st>>>(c ? ws.bn_part2 : ws.bn_part, C, T, T, group_off, ld.bn_scale[c],
+                                                 ld.bn_offset[c], 1e-5f, aa[c], bb[c]);
+            cx.count();
+            NTB_LAUNCH_CHECK();
+        }
+        c_first = 2;
+    }
+    for (int c = c_first; c < 4; ++c) {
         if (c == 3) { aa[3] = ws.aff[2]; bb[3] = ws.aff[3]; }   // conv2a's affine is dead by now
         const float *A = src_of[c] < 0 ? in : ys[src_of[c]];
         const int K = src_of[c] < 0 ? Cin : C;

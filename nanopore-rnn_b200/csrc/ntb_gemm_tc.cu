@@ -64,6 +64,11 @@ struct TcParams {
     // (sum, sum of squares), split at the window boundary inside the block (T >= 32: at most one), and
     // writes bn_part[(block * 2 + seg) * N + n]; k_bn_finish folds the partials of each BN group (ntb_kernels.cuh)
     float2 *bn_part;
+    // dual output (n_split > 0): two GEMMs of the SAME A operand in one launch (conv1 | conv2a of residual_layer, weights
+    // concatenated along N): N tiles >= n_split go to map_out2 / bn_part2 with column origin n_split * BN, and the BN
+    // partial records of both halves are indexed with N = n_half channels.  A is read from DRAM once instead of twice.
+    int n_split, n_half;
+    float2 *bn_part2;
     // LSTM timestep mode (lstm_H > 0): this GEMM is h_{t-1} . W_hh of ONE timestep for all windows and both
     // directions (A rows = [dir][Mp windows], B rows = [dir][Np]); the epilogue adds the projected gates and runs
     // the fused cell update (see gemm_tc_lstm_layer)
@@ -120,7 +125,7 @@ template <int CG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
           const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
-          const __grid_constant__ CUtensorMap map_out, const TcParams p) {
+          const __grid_constant__ CUtensorMap map_out, const __grid_constant__ CUtensorMap map_out2, const TcParams p) {
     using namespace ptx;
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint64_t full_bar[8], empty_bar[8], acc_full[2], acc_empty[2];
@@ -157,6 +162,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&map_a_hi); prefetch_tmap(&map_a_lo); prefetch_tmap(&map_b_hi); prefetch_tmap(&map_b_lo);
         if (p.tma_store || p.xproj_tma) prefetch_tmap(&map_out);
+        if (p.n_split > 0) prefetch_tmap(&map_out2);
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
@@ -322,7 +328,11 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
             // fused BN statistics: which of this warp's 32 rows are real output rows, and where the window changes
             uint32_t bn_vmask = 0;
             int bn_split = 32;
-            if (p.bn_part) {
+            const bool second = p.n_split > 0 && n_tile >= p.n_split;          // dual output: the second GEMM's tiles
+            float2 *bn_dst = second ? p.bn_part2 : p.bn_part;
+            const int bn_N = p.n_split > 0 ? p.n_half : p.N;
+            const int n_org = second ? p.n_split * p.BN : 0;
+            if (bn_dst) {
                 const int Tp = p.pad ? p.T + 2 : p.T;
                 const int64_t w_lane = prow / Tp, w_first = __shfl_sync(0xffffffffu, w_lane, 0);
                 bn_vmask = __ballot_sync(0xffffffffu, row_ok);
@@ -362,10 +372,10 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                     fence_proxy_async_smem();
                     __syncwarp();
                     if (lane == 0) {
-                        tma_store_2d(&map_out, buf, nb, (int)(m_tile * BM) + q * 32);
+                        tma_store_2d(second ? &map_out2 : &map_out, buf, nb - n_org, (int)(m_tile * BM) + q * 32);
                         bulk_commit_group();
                     }
-                    if (p.bn_part) bn_partials(buf, lane, bn_vmask, bn_split, p.bn_part, (m_tile * 4 + q) * 2, p.N, nb + lane);
+                    if (bn_dst) bn_partials(buf, lane, bn_vmask, bn_split, bn_dst, (m_tile * 4 + q) * 2, bn_N, nb - n_org + lane);
                 } else if (p.lstm_H > 0) {
                     // thread = one window of one direction; this chunk = 8 hidden units x (i, j, f, o)
                     const int H = p.lstm_H, nb = n0 + c0;
@@ -1153,7 +1163,8 @@ int fill_params(TcParams &p, const GemmWeights &w, int64_t plane_rows, bool allo
 }
 
 int do_launch(cudaStream_t st, const CUtensorMap &ma_hi, const CUtensorMap &ma_lo, const CUtensorMap &mb_hi,
-              const CUtensorMap &mb_lo, const CUtensorMap &mo, const TcParams &p, int64_t *launches) {
+              const CUtensorMap &mb_lo, const CUtensorMap &mo, const TcParams &p, int64_t *launches,
+              const CUtensorMap *mo2 = nullptr) {
     const int cg = gemm_cta_group();
     const int b_tile_bytes = (p.BN / cg) * BK * 2;
     const int stage_bytes = p.bstat ? 2 * A_TILE_BYTES
@@ -1168,7 +1179,7 @@ int do_launch(cudaStream_t st, const CUtensorMap &ma_hi, const CUtensorMap &ma_l
     if (cg == 1) {
         const int64_t tiles = p.m_tiles * p.n_tiles;
         const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-        k_gemm_tc<1><<<grid, TC_THREADS, smem, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, mo, p);
+        k_gemm_tc<1><<<grid, TC_THREADS, smem, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, mo, mo2 ? *mo2 : mo, p);
     } else {
         const int64_t items = ((p.m_tiles + 1) / 2) * p.n_tiles;            // pairs of M tiles x N tiles
         int64_t pairs_hw = sm_count() / 2;
@@ -1182,7 +1193,7 @@ int do_launch(cudaStream_t st, const CUtensorMap &ma_hi, const CUtensorMap &ma_l
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr; cfg.numAttrs = 1;
-        NTB_CUDA(cudaLaunchKernelEx(&cfg, k_gemm_tc<2>, ma_hi, ma_lo, mb_hi, mb_lo, mo, p));
+        NTB_CUDA(cudaLaunchKernelEx(&cfg, k_gemm_tc<2>, ma_hi, ma_lo, mb_hi, mb_lo, mo, mo2 ? *mo2 : mo, p));
     }
     if (launches) ++*launches;
     NTB_LAUNCH_CHECK();
@@ -1207,7 +1218,7 @@ int make_map_xproj_store(CUtensorMap *m, const float *xproj, int64_t units_total
 
 int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, int64_t plane_rows, int T, int pad,
                 int64_t out_rows, const float *bias, float *out, int ldo, int64_t *launches, int xproj_H = 0,
-                float2 *bn_part = nullptr) {
+                float2 *bn_part = nullptr, float *out2 = nullptr, float2 *bn_part2 = nullptr) {
     const int cg = gemm_cta_group();
     CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
     NTB_TRY(make_map(&ma_hi, gs.a_hi, plane_rows, w.K, BM));
@@ -1236,6 +1247,16 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     CUtensorMap mo = ma_hi;
     if (p.tma_store) NTB_TRY(make_map_out(&mo, out, out_rows, w.N, ldo));
     if (p.xproj_tma) NTB_TRY(make_map_xproj_store(&mo, out, 2 * p.m_tiles * (int64_t)xproj_H));
+    if (out2) {
+        // dual output: w holds [W1 | W2] along N (N = 2 * n_half, whole N tiles per half), both outputs [rows][n_half]
+        if (!p.tma_store || p.n_tiles % 2 || w.N % 2 || (w.N / 2) % w.BN)
+            return fail(NTB_EINVAL, "tcgen05 dual GEMM: unsupported tiling (N %s%lld)", "", (long long)w.N);
+        CUtensorMap mo2;
+        p.n_split = p.n_tiles / 2; p.n_half = w.N / 2; p.bn_part2 = bn_part2;
+        NTB_TRY(make_map_out(&mo, out, out_rows, w.N / 2, ldo));
+        NTB_TRY(make_map_out(&mo2, out2, out_rows, w.N / 2, ldo));
+        return do_launch(st, ma_hi, ma_lo, mb_hi, mb_lo, mo, p, launches, &mo2);
+    }
     return do_launch(st, ma_hi, ma_lo, mb_hi, mb_lo, mo, p, launches);
 }
 
@@ -1358,6 +1379,20 @@ int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, co
     if (!reuse_planes) NTB_TRY(launch_split(st, sp, launches));   // else: the previous conv split the same input
     if (bn_part && T < 32) return fail(NTB_EINVAL, "tcgen05 conv: fused BN statistics need T >= 32%s", "");
     return launch_gemm(st, w, gs, plane_rows, T, pad, rows, nullptr, out, ldo, launches, 0, bn_part);
+}
+
+int gemm_tc_conv_dual(cudaStream_t st, const float *A, int K, int64_t rows, int T, const GemmWeights &w12, float *out1,
+                      float *out2, int C, const GemmScratch &gs, int64_t *launches, bool reuse_planes, float2 *part1,
+                      float2 *part2) {
+    if (!w12.valid || !gs.valid || w12.taps != 1 || w12.N != 2 * C || rows > gs.rows_cap || K != w12.K || K > gs.kp_cap)
+        return fail(NTB_EINVAL, "tcgen05 dual conv: operand not supported (rows %s%lld, K %lld)", "", (long long)rows,
+                    (long long)K);
+    SplitParams sp{};
+    sp.A = A; sp.lda = K; sp.rows = rows; sp.K = K; sp.T = T; sp.relu = 0; sp.pad = 0;
+    sp.hi = gs.a_hi; sp.lo = gs.a_lo; sp.plane_rows = rows;
+    if (!reuse_planes) NTB_TRY(launch_split(st, sp, launches));
+    if ((part1 || part2) && T < 32) return fail(NTB_EINVAL, "tcgen05 conv: fused BN statistics need T >= 32%s", "");
+    return launch_gemm(st, w12, gs, rows, T, 0, rows, nullptr, out1, C, launches, 0, part1, out2, part2);
 }
 
 bool gemm_tc_conv_fused_supported(const GemmWeights &w, int K, int T, int ldo) {

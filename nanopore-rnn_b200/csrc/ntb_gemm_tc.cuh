@@ -44,6 +44,12 @@ int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, co
                  const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
                  int ldo, const GemmScratch &gs, int64_t *launches, bool reuse_planes = false, bool expand = false,
                  float2 *bn_part = nullptr);
+// conv1 and conv2a of a residual layer (two 1x1 convs of the same input) as ONE launch: w12 = [W1 | W2] along N
+// (gemm_tc_plan_weights with N = 2C, packed from a [K][2C] staging matrix), outputs out1 / out2 [rows][C], BN partials
+// part1 (may be null: branch1 without BN) / part2.  The A planes are streamed from DRAM once instead of twice.
+int gemm_tc_conv_dual(cudaStream_t st, const float *A, int K, int64_t rows, int T, const GemmWeights &w12, float *out1,
+                      float *out2, int C, const GemmScratch &gs, int64_t *launches, bool reuse_planes, float2 *part1,
+                      float2 *part2);
 // bn_part (optional): the GEMM epilogue also emits per-(32-row block, window segment, channel) (sum, sum of
 // squares) partials of the conv output -- [(block * 2 + seg) * C + c], block = plane row / 32, plane rows per
 // window = T (1x1) or T + 2 (1x3) -- which k_bn_finish folds per BN group (no extra pass over the output).
