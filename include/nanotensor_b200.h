@@ -16,7 +16,7 @@
  *    ntb_last_error() returns a thread-local message.  There is no CPU fallback: without an
  *    sm_100 device every compute entry point returns NTB_ENODEVICE.
  *  - all arithmetic is float32 in / float32 accumulate; the dense contractions on the tensor
- *    cores use bf16x3 split operands (hi*hi + lo*hi + hi*lo), see DESIGN.md.
+ *    cores use fp16x3 split operands (hi*hi + lo*hi + hi*lo), see DESIGN.md.
  *  - activations are row-major [window][t][channel]; "row" = window * seq_len + t.
  */
 #ifndef NANOTENSOR_B200_H
@@ -92,7 +92,7 @@ NTB_API int ntb_device_ok(void);
 /* Device bytes needed for the repacked, GPU-resident weight tiles of `desc`. */
 NTB_API int64_t ntb_model_weight_bytes(const ntb_model_desc *desc);
 /* Uploads the TF-layout host tensors and repacks them on the device into `weights_dev`
- * (gate-interleaved fp32 recurrence tiles, K-major bf16 hi/lo GEMM tiles).  The buffer must
+ * (gate-interleaved fp32 recurrence tiles, K-major fp16 hi/lo GEMM tiles).  The buffer must
  * stay alive until ntb_model_destroy. */
 NTB_API int ntb_model_create(const ntb_model_desc *desc, void *weights_dev, int64_t weights_bytes,
                      void *stream, ntb_model **out);
@@ -182,7 +182,7 @@ NTB_API int ntb_decode(const float *logits_dev, const int32_t *len_dev, int64_t 
 
 /* Dense GEMM used by the conv / projection stages, exposed for roofline measurement and
  * parity tests: out[M,N] = A[M,K] @ B[K,N] (+ bias[N]), float32 in/out.
- * impl 0 = fp32 SIMT, 1 = tcgen05 bf16x3 (TMA + TMEM), 2 = tcgen05 single-pass bf16. */
+ * impl 0 = fp32 SIMT, 1 = tcgen05 fp16x3 (TMA + TMEM), 2 = tcgen05 single-pass fp16. */
 NTB_API int ntb_gemm(const float *a_dev, const float *b_dev, const float *bias_dev, int64_t M, int32_t N,
              int32_t K, int32_t impl, void *workspace_dev, int64_t workspace_bytes,
              float *out_dev, void *stream);

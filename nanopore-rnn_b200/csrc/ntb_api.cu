@@ -33,7 +33,7 @@ struct LayerDev {
     const float *conv[4] = {nullptr, nullptr, nullptr, nullptr};      // conv1, conv2a, conv2b, conv2c
     const float *bn_scale[4] = {nullptr, nullptr, nullptr, nullptr};
     const float *bn_offset[4] = {nullptr, nullptr, nullptr, nullptr};
-    GemmWeights convw[4];   // tensor-core tiles (bf16 hi/lo, K-major) where the shape allows
+    GemmWeights convw[4];   // tensor-core tiles (fp16 hi/lo, K-major) where the shape allows
     GemmWeights conv12w;    // [conv1 | conv2a] along N: both 1x1 convs of the layer input as one dual-output launch
     float *conv12_stage = nullptr;   // [Cin][2C] fp32 staging the tiles are packed from
     // blstm
@@ -306,7 +306,7 @@ extern "C" int ntb_model_create(const ntb_model_desc *desc, void *weights_dev, i
         return fail(NTB_ENOMEM, "weights buffer too small: need %s%lld bytes, have %lld", "", (long long)ar.off,
                     (long long)weights_bytes);
     }
-    // tensor-core tiles: split the fp32 TF tensors into K-major bf16 hi/lo planes
+    // tensor-core tiles: split the fp32 TF tensors into K-major fp16 hi/lo planes
     for (auto &ld : m->layers) {
         if (ld.type == NTB_LAYER_RESIDUAL) {
             for (int c = 0; c < 4; ++c)

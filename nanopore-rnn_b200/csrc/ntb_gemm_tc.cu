@@ -3,9 +3,9 @@
 //   the LSTM input projection x_t . kernel[0:D, :] (network.py:275-282) and fulconn_layer
 //   (network.py:291-309) when the class count is large.
 //
-// The reference computes these in float32.  bf16 tensor-core operands alone miss the 1e-3 logits
+// The reference computes these in float32.  single 16-bit tensor-core operands alone miss the 1e-3 logits
 // budget by two orders of magnitude (precision table), so every fp32 operand is split
-// into bf16 hi + bf16 lo planes and the product is accumulated in fp32 TMEM as
+// into fp16 hi + fp16 lo planes and the product is accumulated in fp32 TMEM as
 //   A.B ~= Ahi.Bhi + Alo.Bhi + Ahi.Blo            (relative error ~2^-16, "fp16x3").
 //
 // Kernel: persistent, warp-specialised, one CTA per SM.
@@ -32,7 +32,7 @@ namespace ntb {
 namespace {
 
 constexpr int BM = 128;        // rows per tile (TMEM lanes)
-constexpr int BK = 64;         // bf16 per smem row = one 128-byte swizzle span
+constexpr int BK = 64;         // fp16 per smem row = one 128-byte swizzle span
 constexpr int TC_THREADS = 256;
 constexpr int TMEM_COLS = 512;
 constexpr int A_TILE_BYTES = BM * BK * 2;     // 16 KB
@@ -44,7 +44,7 @@ struct TcParams {
     int n_tiles, BN, Np, N;
     int taps, k_blocks;    // k_blocks per tap = ceil(K / 64)
     int k16_last;          // k16 steps in the last k block of a tap
-    int passes;            // 3 = fp16x3, 2 = interleaved-A form (one A plane, B' and B''), 1 = plain bf16 (ablation only)
+    int passes;            // 3 = fp16x3, 2 = interleaved-A form (one A plane, B' and B''), 1 = single pass (ablation only)
     int stages;
     int T, pad;            // pad = 1: plane rows are [window][T+2]
     int64_t out_rows;      // rows of `out`
@@ -555,6 +555,9 @@ struct ConvFusedParams {
     const float *aff_a, *aff_b;
     const int32_t *win_group;
     float2 *bn_part;
+    int abl;       // timing ablations (NTB_CF_ABL): 1 = no BN partials, 2 = no output store, 4 = transform warps skip their work
+    int l2pf;      // the producer pulls the NEXT tile's raw rows into L2 while this tile runs: only one or two 33 KB raw
+                   // stages are in flight per SM, so every k-block otherwise waits a full DRAM latency
 };
 
 __global__ void __launch_bounds__(CF_THREADS, 1)
@@ -602,6 +605,10 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
             int rs = 0, os = 0; uint32_t rph = 0, oph = 0;
             for (int64_t it = first; it < pairs; it += step) {
                 const int64_t m_tile = it * 2 + rank;
+                if (p.l2pf && it + step < pairs) {
+                    const int r2 = (int)(((it + step) * 2 + rank) * BM) - left;
+                    for (int kb = 0; kb < p.k_blocks; ++kb) tma_prefetch_2d(&map_raw, kb * BK, r2);
+                }
                 for (int kb = 0; kb < p.k_blocks; ++kb) {
                     mbar_wait_backoff<128>(&raw_empty[rs], rph ^ 1, 100);
                     mbar_expect_tx(&raw_full[rs], (uint32_t)(raw_rows * BK * 4));
@@ -651,16 +658,20 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
         }
     } else if (warp >= 8) {
         // ===================== transform: raw fp32 -> affine + ReLU -> fp16 hi/lo swizzled operand tiles ==========
-        // thread = 8 channels (one 16-byte operand chunk, j) of rows tw*16 + rsub + 4 i, i = 0..3
+        // thread = channels 4j .. 4j+3 and 32+4j .. 32+4j+3 of the k-block for 4 rows of its warp's 16: the eight lanes of a
+        // quarter warp read 128 CONTIGUOUS bytes of one raw row per 16-byte load (the row pitch is 256 B: a 32-byte lane
+        // stride would put lanes j and j+4 on the same banks), and a half warp writes rows r and r+4, whose swizzle keys
+        // differ in bit 2, so its sixteen 8-byte operand stores fall on 128 distinct bytes of the banks.
         constexpr int RPT = BM / (4 * CF_TWARPS);                 // rows per thread
-        const int tw = warp - 8, j = lane & 7, rsub = lane >> 3;
+        const int tw = warp - 8, j = lane & 7, rsel = lane >> 3;
+        const int rlane = (rsel & 1) * 4 + (rsel >> 1);           // row offsets {0, 4, 1, 5}
         int rs = 0, os = 0; uint32_t rph = 0, oph = 0;
         for (int64_t it = first; it < pairs; it += step) {
             const int64_t m_tile = it * 2 + rank;
             int tpos[RPT], grp[RPT];                              // t of the row inside its window (-1000: no such row), BN group
 #pragma unroll
             for (int i = 0; i < RPT; ++i) {
-                const int64_t grow = m_tile * BM + tw * (4 * RPT) + rsub + 4 * i;
+                const int64_t grow = m_tile * BM + tw * (4 * RPT) + (i >> 1) * 8 + (i & 1) * 2 + rlane;
                 if (grow < p.rows) {
                     const int64_t w = grow / p.T;
                     tpos[i] = (int)(grow - w * p.T);
@@ -672,28 +683,29 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
             for (int kb = 0; kb < p.k_blocks; ++kb) {
                 mbar_wait(&raw_full[rs], rph, 200);
                 const uint8_t *raw = raw_base + rs * CF_RAW_STAGE;
-                const int c = kb * BK + j * 8;                    // first of this thread's 8 channels
-                int gcur = -1;                                    // (a, b) of group gcur for channels c..c+7 stay in registers
+                const int c = kb * BK + j * 4;                    // first of this thread's channels (second group: c + 32)
+                int gcur = -1;                                    // (a, b) of group gcur for the 8 channels stay in registers
                 float a[8], b[8];                                 //  across the taps (and rows) of this k-block
                 for (int tap = 0; tap < p.taps; ++tap) {
                     mbar_wait(&op_empty[os], oph ^ 1, 201);
                     uint8_t *a_hi = op_base + os * op_stage_bytes, *a_lo = a_hi + A_TILE_BYTES;
 #pragma unroll
                     for (int i = 0; i < RPT; ++i) {
-                        const int row = tw * (4 * RPT) + rsub + 4 * i;
+                        if (p.abl & 4) break;
+                        const int row = tw * (4 * RPT) + (i >> 1) * 8 + (i & 1) * 2 + rlane;
                         const int tt = tpos[i] + tap - left;
                         float v[8];
                         if (tt >= 0 && tt < p.T) {                // same window as the output row: SAME padding otherwise
-                            const float4 x0 = *reinterpret_cast<const float4 *>(raw + (row + tap) * (BK * 4) + j * 32);
-                            const float4 x1 = *reinterpret_cast<const float4 *>(raw + (row + tap) * (BK * 4) + j * 32 + 16);
+                            const float4 x0 = *reinterpret_cast<const float4 *>(raw + (row + tap) * (BK * 4) + j * 16);
+                            const float4 x1 = *reinterpret_cast<const float4 *>(raw + (row + tap) * (BK * 4) + 128 + j * 16);
                             v[0] = x0.x; v[1] = x0.y; v[2] = x0.z; v[3] = x0.w; v[4] = x1.x; v[5] = x1.y; v[6] = x1.z; v[7] = x1.w;
                             if (p.aff_a) {
                                 if (grp[i] != gcur) {
                                     gcur = grp[i];
                                     const float4 a0 = __ldg(reinterpret_cast<const float4 *>(p.aff_a + (int64_t)gcur * p.K + c));
-                                    const float4 a1 = __ldg(reinterpret_cast<const float4 *>(p.aff_a + (int64_t)gcur * p.K + c + 4));
+                                    const float4 a1 = __ldg(reinterpret_cast<const float4 *>(p.aff_a + (int64_t)gcur * p.K + c + 32));
                                     const float4 b0 = __ldg(reinterpret_cast<const float4 *>(p.aff_b + (int64_t)gcur * p.K + c));
-                                    const float4 b1 = __ldg(reinterpret_cast<const float4 *>(p.aff_b + (int64_t)gcur * p.K + c + 4));
+                                    const float4 b1 = __ldg(reinterpret_cast<const float4 *>(p.aff_b + (int64_t)gcur * p.K + c + 32));
                                     a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
                                     b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
                                 }
@@ -710,9 +722,13 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
                         }
                         uint4 h, l;
                         if (p.relu) split_op16x8<true>(v, h, l); else split_op16x8<false>(v, h, l);
-                        const int off = row * 128 + ((j ^ (row & 7)) << 4);
-                        *reinterpret_cast<uint4 *>(a_hi + off) = h;
-                        *reinterpret_cast<uint4 *>(a_lo + off) = l;
+                        // channels 4j..4j+3 -> half (j & 1) of 16-byte chunk j >> 1; channels 32+4j.. -> chunk 4 + (j >> 1)
+                        const int off0 = row * 128 + (((j >> 1) ^ (row & 7)) << 4) + (j & 1) * 8;
+                        const int off1 = row * 128 + (((4 + (j >> 1)) ^ (row & 7)) << 4) + (j & 1) * 8;
+                        *reinterpret_cast<uint2 *>(a_hi + off0) = make_uint2(h.x, h.y);
+                        *reinterpret_cast<uint2 *>(a_hi + off1) = make_uint2(h.z, h.w);
+                        *reinterpret_cast<uint2 *>(a_lo + off0) = make_uint2(l.x, l.y);
+                        *reinterpret_cast<uint2 *>(a_lo + off1) = make_uint2(l.z, l.w);
                     }
                     fence_proxy_async_smem();                     // generic-proxy stores -> visible to tcgen05.mma
                     __syncwarp();
@@ -755,11 +771,11 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
                                     __uint_as_float(r[4 * k + 3]));
                 fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0) {
+                if (lane == 0 && !(p.abl & 2)) {
                     tma_store_2d(&map_out, buf, c0, (int)(m_tile * BM) + q * 32);
                     bulk_commit_group();
                 }
-                if (p.bn_part) bn_partials(buf, lane, bn_vmask, bn_split, p.bn_part, (m_tile * 4 + q) * 2, p.N, c0 + lane);
+                if (p.bn_part && !(p.abl & 1)) bn_partials(buf, lane, bn_vmask, bn_split, p.bn_part, (m_tile * 4 + q) * 2, p.N, c0 + lane);
             }
             tc_fence_before();
             __syncwarp();
@@ -777,7 +793,7 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
 }
 
 // ------------------------------------------------------------------------------------------
-// fp32 -> bf16 hi/lo operand planes, with the producer's BN affine (+ReLU) applied on the way
+// fp32 -> fp16 hi/lo operand planes, with the producer's BN affine (+ReLU) applied on the way
 // (simple_global_bn + relu of the previous conv, network.py:330-349) and, for the 1x3 conv, the
 // per-window padded row layout.  8 channels per thread: two float4 loads, two 16-byte stores.
 // ------------------------------------------------------------------------------------------
@@ -898,7 +914,7 @@ __global__ void __launch_bounds__(256) k_split_window(const SplitParams p) {
 }
 
 // residual_layer tail (network.py:398-399)  out = relu( bn?(branch1) + bn(conv2c) )  emitted directly as
-// the NEXT GEMM's bf16 hi/lo operand planes (plain rows for the next residual layer's 1x1 convs, time-major
+// the NEXT GEMM's fp16 hi/lo operand planes (plain rows for the next residual layer's 1x1 convs, time-major
 // 128-window tiles for the LSTM projection) and/or as fp32.  8 channels per thread, one plane row per
 // K/8 threads.  y1_scalar: branch1 is a Cin = 1 conv folded into its affine (y1[r] * a1[g][c] + b1[g][c]).
 struct CombineParams {
@@ -983,7 +999,7 @@ __global__ void __launch_bounds__(256) k_combine_split(const CombineParams p) {
     }
 }
 
-// TF weights [taps][K][N] fp32 -> K-major bf16 planes [taps][Np][Kp] (zero padded)
+// TF weights [taps][K][N] fp32 -> K-major fp16 planes [taps][Np][Kp] (zero padded)
 __global__ void k_pack_weights(const float *__restrict__ w, int taps, int K, int N, int Kp, int Np,
                                op16_t *__restrict__ hi, op16_t *__restrict__ lo) {
     const int64_t total = (int64_t)taps * Np * Kp;
@@ -1032,7 +1048,7 @@ EncodeTiledFn encode_fn() {
     return fn;
 }
 
-// bf16 [rows][K] row-major plane, box {64, box_rows}, 128-byte swizzle, zero fill out of bounds
+// fp16 [rows][K] row-major plane, box {64, box_rows}, 128-byte swizzle, zero fill out of bounds
 int make_map(CUtensorMap *m, const void *base, int64_t rows, int K, int box_rows) {
     EncodeTiledFn fn = encode_fn();
     if (!fn) return fail(NTB_ECUDA, "cuTensorMapEncodeTiled entry point not found%s", "");
@@ -1416,6 +1432,11 @@ int gemm_tc_conv_fused(cudaStream_t st, const float *y, int K, int64_t rows, int
     ConvFusedParams p{};
     p.m_tiles = (rows + BM - 1) / BM; p.rows = rows; p.N = w.N; p.K = K; p.taps = w.taps; p.T = T;
     p.k_blocks = K / BK; p.relu = relu_in; p.aff_a = aff_a; p.aff_b = aff_b; p.win_group = win_group; p.bn_part = bn_part;
+    // opt-in: measured neutral to slightly slower (conv stage 56.5 vs 55.8 ms per 65 536 windows)
+    static const int cf_l2pf = getenv("NTB_CF_L2PF") ? atoi(getenv("NTB_CF_L2PF")) : 0;
+    p.l2pf = cf_l2pf;
+    static const int cf_abl = getenv("NTB_CF_ABL") ? atoi(getenv("NTB_CF_ABL")) : 0;
+    p.abl = cf_abl;
     const size_t smem = (size_t)CF_OP_STAGES * (2 * A_TILE_BYTES + 2 * (w.N / 2) * BK * 2) +
                         (size_t)CF_RAW_STAGES * CF_RAW_STAGE + CF_EPI_BYTES + 1024;
     static bool attr_set = false;
@@ -1474,7 +1495,7 @@ int gemm_tc_combine(cudaStream_t st, const float *y1, bool y1_scalar, const floa
 // larger than one SM's shared memory): ONE tcgen05 GEMM launch per timestep,
 //   z_t = h_{t-1} . W_hh   for every window and both directions (M = 2 * windows, N = 4H, K = H, fp16x3),
 // whose epilogue adds the projected gates, applies the fused cell update and writes h_t three ways: fp32 layer
-// output, and the bf16 hi/lo operand planes of the next step (ping-pong buffers: other CTAs still read h_{t-1}).
+// output, and the fp16 hi/lo operand planes of the next step (ping-pong buffers: other CTAs still read h_{t-1}).
 // W_hh hi/lo (1 MB at H = 256) stays L2-resident across the T launches; c lives in HBM as fp32.
 // ------------------------------------------------------------------------------------------
 __global__ void k_pack_whh_kn(const float *__restrict__ kernel_fw, const float *__restrict__ kernel_bw, int D, int H,

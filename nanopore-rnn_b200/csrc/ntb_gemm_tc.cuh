@@ -4,10 +4,10 @@
 
 namespace ntb {
 
-// K-major bf16 hi/lo planes of a [taps][K][N] fp32 weight tensor, padded for the MMA tiles.
+// K-major fp16 hi/lo planes of a [taps][K][N] fp32 weight tensor, padded for the MMA tiles.
 struct GemmWeights {
     bool valid = false;
-    bool single_pass = false;   // hi*hi only (plain bf16; measurement / ablation only)
+    bool single_pass = false;   // hi*hi only (single 16-bit pass; measurement / ablation only)
     // Interleaved-A form (LSTM projections fed straight by the previous recurrence, ntb_lstm_tc.cuh): the A operand is ONE
     // plane [rows][2*Ksrc] whose 8-element groups are (4 x hi, 4 x lo) of 4 consecutive source columns; K = 2*Ksrc here,
     // plane `hi` holds W_hi in both slots and plane `lo` holds W_lo in both slots, so two passes A'.B' + A'.B'' give
@@ -17,7 +17,7 @@ struct GemmWeights {
     int taps = 1, K = 0, N = 0, Kp = 0, Np = 0, BN = 0;
     op16_t *hi = nullptr, *lo = nullptr;   // [taps][Np][Kp], Kp = K rounded up to 64
 };
-// bf16 hi/lo planes of the A operand for one GEMM (rewritten by every call).
+// fp16 hi/lo planes of the A operand for one GEMM (rewritten by every call).
 struct GemmScratch {
     bool valid = false;
     int64_t rows_cap = 0;

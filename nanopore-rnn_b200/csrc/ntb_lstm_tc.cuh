@@ -4,9 +4,9 @@
 //
 // One persistent CTA per (tile of 128 windows, direction); forward and backward tiles are CTAs
 // of one launch.  Per timestep the recurrent term is a [128 x Hp] x [Hp x 4H] GEMM:
-//   * B = W_hh^T, bf16 hi + lo planes, resident in shared memory for all T steps in the
+//   * B = W_hh^T, fp16 hi + lo planes, resident in shared memory for all T steps in the
 //     non-swizzled K-major core-matrix layout (2 * 4H * Hp * 2 bytes = 175 KB at H = 100);
-//   * A = h_{t-1}, bf16 hi + lo, lives in TENSOR MEMORY next to the accumulator ("TS" MMA):
+//   * A = h_{t-1}, fp16 hi + lo, lives in TENSOR MEMORY next to the accumulator ("TS" MMA):
 //     TMEM columns [0,4H) gate pre-activations (fp32), [4H, 4H+Hp/2) h hi, [.., 4H+Hp) h lo;
 //     the epilogue writes h_t straight back with tcgen05.st, so h never touches shared memory;
 //   * fp16x3: D = hhi.Whi + hlo.Whi + hhi.Wlo accumulated in fp32 (relative error ~2^-16; the
@@ -71,7 +71,7 @@ static inline int64_t lstm_tc_smem_bytes(int H) {
 }
 static inline int64_t lstm_tc_whh_elems(int H) { return 2LL * align_up(H, 16) * 4 * H; }   // per plane, both dirs
 
-// TF LSTMCell kernel rows D..D+H-1 (the h part), gate column blocks i|j|f|o  ->  bf16 hi/lo
+// TF LSTMCell kernel rows D..D+H-1 (the h part), gate column blocks i|j|f|o  ->  fp16 hi/lo
 // planes [dir][k/8][n = u*4+g][k%8], zero for k >= H.
 __global__ void k_pack_whh_tc(const float *__restrict__ kernel_fw, const float *__restrict__ kernel_bw, int D, int H,
                               int Hp, op16_t *__restrict__ hi, op16_t *__restrict__ lo) {
@@ -97,7 +97,7 @@ __global__ void k_pack_whh_tc(const float *__restrict__ kernel_fw, const float *
 __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const __grid_constant__ CUtensorMap map_x,
                                                                                const LstmTcParams p) {
     using namespace ptx;
-    extern __shared__ __align__(128) uint8_t smem_w[];          // [2 planes][Hp/8][4H][8] bf16, then the x ring
+    extern __shared__ __align__(128) uint8_t smem_w[];          // [2 planes][Hp/8][4H][8] fp16, then the x ring
     __shared__ uint64_t d_full[2], h_ready, x_full[LSTM_TC_XSLOTS], x_empty[LSTM_TC_XSLOTS];
     __shared__ uint32_t tmem_base_smem;
 
