@@ -124,6 +124,15 @@ NTB_API int ntb_model_forward_host(ntb_model *m, const float *x_host, const int3
                            const int32_t *group_off_host, int64_t n_windows, int64_t n_groups,
                            void *workspace_dev, int64_t workspace_bytes, float *logits_host,
                            int32_t *labels_host, int32_t *label_len_host, void *stream);
+/* Same, WITHOUT the final synchronisation: copies and kernels are only enqueued on `stream`.  The host buffers must be
+ * page-locked, and they, the workspace and the inputs must stay untouched until the caller has synchronised the
+ * stream.  Alternating two streams and two workspaces over the chunks of a job overlaps the host<->device copies of
+ * one chunk with the kernels of the other (what engine.Model.forward_host does; the reference's counterpart is the
+ * tf.data prefetch in front of sess.run, dataset.py:357-380). */
+NTB_API int ntb_model_forward_host_async(ntb_model *m, const float *x_host, const int32_t *len_host,
+                                 const int32_t *group_off_host, int64_t n_windows, int64_t n_groups,
+                                 void *workspace_dev, int64_t workspace_bytes, float *logits_host,
+                                 int32_t *labels_host, int32_t *label_len_host, void *stream);
 /* Workspace bytes for ntb_model_forward_host (forward scratch + staged inputs/outputs). */
 NTB_API int64_t ntb_model_workspace_bytes_host(const ntb_model *m, int64_t n_windows, int64_t n_groups,
                                        int want_logits);

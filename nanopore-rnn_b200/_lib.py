@@ -40,6 +40,7 @@ SIGNATURES = {
     "ntb_model_workspace_bytes": (_I64, [_P, _I64, _I64]),
     "ntb_model_forward": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _P, _I64, _P, _P, _P, _P]),
     "ntb_model_forward_host": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _P, _I64, _P, _P, _P, _P]),
+    "ntb_model_forward_host_async": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _P, _I64, _P, _P, _P, _P]),
     "ntb_model_workspace_bytes_host": (_I64, [_P, _I64, _I64, C.c_int]),
     "ntb_model_last_launches": (_I64, [_P]),
     "ntb_model_set_profile": (C.c_int, [_P, C.c_int]),

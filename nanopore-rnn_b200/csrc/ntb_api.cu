@@ -713,10 +713,10 @@ extern "C" int64_t ntb_model_workspace_bytes_host(const ntb_model *m, int64_t n_
     return plan_workspace(m, n_windows, n_groups, !want_logits, ar, ws);
 }
 
-extern "C" int ntb_model_forward_host(ntb_model *m, const float *x_host, const int32_t *len_host,
-                                      const int32_t *group_off_host, int64_t n_windows, int64_t n_groups,
-                                      void *workspace_dev, int64_t workspace_bytes, float *logits_host,
-                                      int32_t *labels_host, int32_t *label_len_host, void *stream) {
+static int forward_host_impl(ntb_model *m, const float *x_host, const int32_t *len_host,
+                             const int32_t *group_off_host, int64_t n_windows, int64_t n_groups,
+                             void *workspace_dev, int64_t workspace_bytes, float *logits_host,
+                             int32_t *labels_host, int32_t *label_len_host, void *stream, bool sync) {
     if (!m || !x_host || !len_host || !labels_host || n_windows < 0)
         return fail(NTB_EINVAL, "ntb_model_forward_host: NULL argument%s", "");
     NTB_TRY(check_device());
@@ -742,8 +742,24 @@ extern "C" int ntb_model_forward_host(ntb_model *m, const float *x_host, const i
         NTB_CUDA(cudaMemcpyAsync(label_len_host, hs.label_len, n_windows * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     if (logits_host)
         NTB_CUDA(cudaMemcpyAsync(logits_host, hs.logits, rows * m->C * sizeof(float), cudaMemcpyDeviceToHost, st));
-    NTB_CUDA(cudaStreamSynchronize(st));
+    if (sync) NTB_CUDA(cudaStreamSynchronize(st));
     return NTB_OK;
+}
+
+extern "C" int ntb_model_forward_host(ntb_model *m, const float *x_host, const int32_t *len_host,
+                                      const int32_t *group_off_host, int64_t n_windows, int64_t n_groups,
+                                      void *workspace_dev, int64_t workspace_bytes, float *logits_host,
+                                      int32_t *labels_host, int32_t *label_len_host, void *stream) {
+    return forward_host_impl(m, x_host, len_host, group_off_host, n_windows, n_groups, workspace_dev, workspace_bytes,
+                             logits_host, labels_host, label_len_host, stream, true);
+}
+
+extern "C" int ntb_model_forward_host_async(ntb_model *m, const float *x_host, const int32_t *len_host,
+                                            const int32_t *group_off_host, int64_t n_windows, int64_t n_groups,
+                                            void *workspace_dev, int64_t workspace_bytes, float *logits_host,
+                                            int32_t *labels_host, int32_t *label_len_host, void *stream) {
+    return forward_host_impl(m, x_host, len_host, group_off_host, n_windows, n_groups, workspace_dev, workspace_bytes,
+                             logits_host, labels_host, label_len_host, stream, false);
 }
 
 extern "C" int64_t ntb_model_last_launches(const ntb_model *m) { return m ? m->launches : 0; }

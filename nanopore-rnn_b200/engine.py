@@ -3,6 +3,7 @@ BN-group-aligned chunks of windows and drives ``ntb_model_forward`` / ``_forward
 
 torch is used for device memory, streams and pinned host buffers only."""
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -12,8 +13,8 @@ from ._lib import (NTB_GRAPH_CROSS_ENTROPY, NTB_GRAPH_CTC, NTB_LAYER_BLSTM, NTB_
                    NTB_LAYER_RESIDUAL, NtbLayer, NtbModelDesc)
 
 GRAPHS = {"CrossEntropy": NTB_GRAPH_CROSS_ENTROPY, "CtcLoss": NTB_GRAPH_CTC}
-# recurrence tile = 64 windows x 2 directions; 74 tiles x 2 = one wave of 148 SMs
-_WAVE_WINDOWS = 64 * 74
+# recurrence tile = 128 windows x 2 directions; 74 tiles x 2 = one wave of 148 SMs
+_WAVE_WINDOWS = 128 * 74
 
 
 def _fp(a):
@@ -46,7 +47,7 @@ def group_offsets(read_window_counts, batch_size):
 
 def plan_chunks(group_off, max_windows, align=1):
     """Split [0, n_groups) into runs of whole groups with <= max_windows windows each, preferring
-    a multiple of one recurrence wave (64 windows x 74 tiles x 2 directions = 148 CTAs).
+    a multiple of one recurrence wave (128 windows x 74 tiles x 2 directions = 148 CTAs).
 
     ``align`` (Model.chunk_align()): cuts are placed where the window count so far is a multiple of it whenever
     such a group boundary exists inside the limit.  The conv epilogue sums the batch-norm statistics in 32-row
@@ -145,12 +146,15 @@ class Model:
                                                  _stream_ptr(self.device), C.byref(handle)))
         self._h = handle
         self._ws = None
+        self._ws2 = None          # two-chunk workspace of the pipelined host path
+        self._streams = None
         del keep
 
     def close(self):
         if getattr(self, "_h", None):
             self.lib.ntb_model_destroy(self._h)
             self._h = None
+            self._ws = self._ws2 = None
 
     __del__ = close
 
@@ -233,25 +237,66 @@ class Model:
         logits = _pinned((n * T, Cc), torch.float32) if want_logits else None
         if n == 0:
             return self._shape_labels(labels, n), llen, logits
-        chunks = plan_chunks(group_off, max_windows or self.max_chunk_windows(), self.chunk_align())
-        stream = _stream_ptr(self.device)
         with torch.cuda.device(self.device):
+            # Opt-in (NTB_HOST_PIPELINE=1): alternate two streams and two workspaces over the chunks, so that the
+            # host<->device copies of one chunk run under the kernels of the other (ntb_model_forward_host_async;
+            # pageable inputs are staged through pinned memory first).  Measured on 1 x B200 at 1 048 576 windows it is
+            # slightly SLOWER than the synchronous form (57.8 vs 58.6 M samples/s end to end): the copies are only ~2 % of a
+            # step, and two half-size chunks whose persistent kernels interleave cost more than that.
+            pipeline = os.environ.get("NTB_HOST_PIPELINE", "0") == "1"
+            limit = max_windows or self.max_chunk_windows()
+            chunks = plan_chunks(group_off, limit, self.chunk_align())
+            if pipeline and max_windows is None and len(chunks) >= 1 and n > 2 * _WAVE_WINDOWS:
+                half = self.max_chunk_windows(budget_bytes=int(torch.cuda.mem_get_info(self.device)[0] * 0.3))
+                if self._ws is not None:          # the cached one-chunk workspace would not leave room for two
+                    half = min(half, max(64, limit // 2))
+                chunks = plan_chunks(group_off, half, self.chunk_align())
+            pipeline = pipeline and len(chunks) >= 2
             wmax = max(int(group_off[h] - group_off[g]) for g, h in chunks)
             gmax = max(h - g for g, h in chunks)
-            ws = self._workspace(self.workspace_bytes(wmax, gmax, host=True, want_logits=want_logits))
-            for g, h in chunks:
+            nbytes = (self.workspace_bytes(wmax, gmax, host=True, want_logits=want_logits) + 1023) // 1024 * 1024
+            if pipeline:
+                x, lens = _pin(x), _pin(lens)
+                if self._ws is not None and self._ws.numel() >= 2 * nbytes:
+                    wss = [self._ws[:nbytes], self._ws[nbytes:2 * nbytes]]
+                else:
+                    if self._ws2 is None or self._ws2.numel() < 2 * nbytes:
+                        self._ws2 = None
+                        self._ws2 = torch.empty(int(2 * nbytes), dtype=torch.uint8, device=self.device)
+                    wss = [self._ws2[:nbytes], self._ws2[nbytes:2 * nbytes]]
+                if self._streams is None:
+                    self._streams = [torch.cuda.Stream(self.device), torch.cuda.Stream(self.device)]
+                cur = torch.cuda.current_stream(self.device)
+                for st in self._streams:
+                    st.wait_stream(cur)
+                call = self.lib.ntb_model_forward_host_async
+                goffs = []                                     # pinned per-chunk group offsets stay alive until the sync
+            else:
+                wss = [self._workspace(nbytes)]
+                call = self.lib.ntb_model_forward_host
+            for i, (g, h) in enumerate(chunks):
                 w0, w1 = int(group_off[g]), int(group_off[h])
                 nw = w1 - w0
                 goff = np.ascontiguousarray(group_off[g:h + 1] - group_off[g], dtype=np.int32)
+                if pipeline:
+                    goff = _pin(goff)
+                    goffs.append(goff)
+                    stream = C.c_void_p(self._streams[i & 1].cuda_stream)
+                else:
+                    stream = _stream_ptr(self.device)
+                ws = wss[i & 1] if pipeline else wss[0]
                 xs = x[w0:w1]
                 ls = lens[w0:w1]
-                _lib.check(self.lib.ntb_model_forward_host(
+                _lib.check(call(
                     self._h, C.c_void_p(xs.ctypes.data), C.c_void_p(ls.ctypes.data),
                     C.c_void_p(goff.ctypes.data) if pass_groups else C.c_void_p(0), nw,
                     (h - g) if pass_groups else 0, _ptr(ws), ws.numel(),
                     C.c_void_p(logits[w0 * T:].ctypes.data) if want_logits else C.c_void_p(0),
                     C.c_void_p(labels[w0 * T:].ctypes.data),
                     C.c_void_p(llen[w0:].ctypes.data) if llen is not None else C.c_void_p(0), stream))
+            if pipeline:
+                for st in self._streams:
+                    st.synchronize()
         return self._shape_labels(labels, n), llen, logits
 
     def _shape_labels(self, labels, n):
@@ -268,6 +313,14 @@ class Model:
         buf = (C.c_float * 5)()
         k = self.lib.ntb_model_stage_ms(self._h, buf, 5)
         return dict(zip(["conv_bn", "projection_split", "recurrence", "readout", "projection_gemm"][:k], list(buf)[:k]))
+
+
+def _pin(a):
+    """numpy array -> the same data in page-locked memory (no copy if torch says it already is pinned)."""
+    t = torch.from_numpy(a)
+    if t.numel() == 0 or t.is_pinned():
+        return a
+    return t.pin_memory().numpy()
 
 
 def _pinned(shape, dtype):

@@ -400,3 +400,19 @@ def test_read_order_does_not_change_per_read_labels():
             assert top[1] - top[0] <= 2e-4
         if len(diff) == 0:
             assert np.array_equal(a[i][0], b[i][0])
+
+
+def test_pipelined_host_path_is_bit_identical(monkeypatch):
+    """engine.Model.forward_host with NTB_HOST_PIPELINE=1 (two streams, two workspaces, ntb_model_forward_host_async)
+    returns exactly what the synchronous path returns."""
+    net, Cc = syn.NETWORKS["signal_CRNN"], 6
+    w = syn.random_weights(net, 1, Cc, seed=5)
+    m = engine.Model(net, w, "CtcLoss", 100, 1, Cc, device=DEV)
+    x, lens, _ = syn.synthetic_reads(10, 32, 100, seed=16)
+    goff = engine.group_offsets([32] * 10, 16)
+    monkeypatch.setenv("NTB_HOST_PIPELINE", "0")
+    l1, k1, g1 = m.forward_host(x, lens, goff, want_logits=True, max_windows=64)
+    monkeypatch.setenv("NTB_HOST_PIPELINE", "1")
+    l2, k2, g2 = m.forward_host(x, lens, goff, want_logits=True, max_windows=64)      # 5 chunks, pageable inputs
+    assert m._streams is not None
+    assert np.array_equal(g1, g2) and np.array_equal(l1, l2) and np.array_equal(k1, k2)
