@@ -4,6 +4,7 @@ BN-group-aligned chunks of windows and drives ``ntb_model_forward`` / ``_forward
 torch is used for device memory, streams and pinned host buffers only."""
 import ctypes as C
 import os
+import weakref
 
 import numpy as np
 import torch
@@ -146,7 +147,8 @@ class Model:
                                                  _stream_ptr(self.device), C.byref(handle)))
         self._h = handle
         self._ws = None
-        self._ws2 = None          # two-chunk workspace of the pipelined host path
+        self._chunk_cap = None    # max_chunk_windows() with the default budget, computed once
+        self._stage = None        # (key, two sets of device staging buffers) of the overlapped host path
         self._streams = None
         del keep
 
@@ -154,7 +156,7 @@ class Model:
         if getattr(self, "_h", None):
             self.lib.ntb_model_destroy(self._h)
             self._h = None
-            self._ws = self._ws2 = None
+            self._ws = self._stage = None
 
     __del__ = close
 
@@ -181,12 +183,19 @@ class Model:
 
     def max_chunk_windows(self, budget_bytes=None, groups_per_window=0.1):
         """Largest chunk whose workspace fits ``budget_bytes`` (default: 60 % of free HBM)."""
-        if budget_bytes is None:
+        default = budget_bytes is None
+        if default:
+            # cudaMemGetInfo costs ~9 ms: ask once while no workspace is cached (a cached one already fits its chunk)
+            if self._chunk_cap is not None:
+                return self._chunk_cap
             free, _ = torch.cuda.mem_get_info(self.device)
             budget_bytes = int(free * 0.6)
         per = self.workspace_bytes(4096, int(4096 * groups_per_window) + 1, host=True) / 4096.0
         n = int(budget_bytes / per)
-        return max(64, min(n, 16 * _WAVE_WINDOWS))
+        n = max(64, min(n, 16 * _WAVE_WINDOWS))
+        if default:
+            self._chunk_cap = n
+        return n
 
     # ------------------------------------------------------------------ forward, device-resident inputs
     def forward_device(self, x, lens, group_off=None, want_logits=False, labels_out=None, label_len_out=None):
@@ -237,67 +246,104 @@ class Model:
         logits = _pinned((n * T, Cc), torch.float32) if want_logits else None
         if n == 0:
             return self._shape_labels(labels, n), llen, logits
+        chunks = plan_chunks(group_off, max_windows or self.max_chunk_windows(), self.chunk_align())
+        if len(chunks) >= 2 and os.environ.get("NTB_HOST_PIPELINE", "1") != "0":
+            self._forward_host_overlapped(x, lens, group_off, pass_groups, chunks, labels, llen, logits)
+            return self._shape_labels(labels, n), llen, logits
+        stream = _stream_ptr(self.device)
         with torch.cuda.device(self.device):
-            # Opt-in (NTB_HOST_PIPELINE=1): alternate two streams and two workspaces over the chunks, so that the
-            # host<->device copies of one chunk run under the kernels of the other (ntb_model_forward_host_async;
-            # pageable inputs are staged through pinned memory first).  Measured on 1 x B200 at 1 048 576 windows it is
-            # slightly SLOWER than the synchronous form (57.8 vs 58.6 M samples/s end to end): the copies are only ~2 % of a
-            # step, and two half-size chunks whose persistent kernels interleave cost more than that.
-            pipeline = os.environ.get("NTB_HOST_PIPELINE", "0") == "1"
-            limit = max_windows or self.max_chunk_windows()
-            chunks = plan_chunks(group_off, limit, self.chunk_align())
-            if pipeline and max_windows is None and len(chunks) >= 1 and n > 2 * _WAVE_WINDOWS:
-                half = self.max_chunk_windows(budget_bytes=int(torch.cuda.mem_get_info(self.device)[0] * 0.3))
-                if self._ws is not None:          # the cached one-chunk workspace would not leave room for two
-                    half = min(half, max(64, limit // 2))
-                chunks = plan_chunks(group_off, half, self.chunk_align())
-            pipeline = pipeline and len(chunks) >= 2
             wmax = max(int(group_off[h] - group_off[g]) for g, h in chunks)
             gmax = max(h - g for g, h in chunks)
-            nbytes = (self.workspace_bytes(wmax, gmax, host=True, want_logits=want_logits) + 1023) // 1024 * 1024
-            if pipeline:
-                x, lens = _pin(x), _pin(lens)
-                if self._ws is not None and self._ws.numel() >= 2 * nbytes:
-                    wss = [self._ws[:nbytes], self._ws[nbytes:2 * nbytes]]
-                else:
-                    if self._ws2 is None or self._ws2.numel() < 2 * nbytes:
-                        self._ws2 = None
-                        self._ws2 = torch.empty(int(2 * nbytes), dtype=torch.uint8, device=self.device)
-                    wss = [self._ws2[:nbytes], self._ws2[nbytes:2 * nbytes]]
-                if self._streams is None:
-                    self._streams = [torch.cuda.Stream(self.device), torch.cuda.Stream(self.device)]
-                cur = torch.cuda.current_stream(self.device)
-                for st in self._streams:
-                    st.wait_stream(cur)
-                call = self.lib.ntb_model_forward_host_async
-                goffs = []                                     # pinned per-chunk group offsets stay alive until the sync
-            else:
-                wss = [self._workspace(nbytes)]
-                call = self.lib.ntb_model_forward_host
-            for i, (g, h) in enumerate(chunks):
+            ws = self._workspace(self.workspace_bytes(wmax, gmax, host=True, want_logits=want_logits))
+            for g, h in chunks:
                 w0, w1 = int(group_off[g]), int(group_off[h])
                 nw = w1 - w0
                 goff = np.ascontiguousarray(group_off[g:h + 1] - group_off[g], dtype=np.int32)
-                if pipeline:
-                    goff = _pin(goff)
-                    goffs.append(goff)
-                    stream = C.c_void_p(self._streams[i & 1].cuda_stream)
-                else:
-                    stream = _stream_ptr(self.device)
-                ws = wss[i & 1] if pipeline else wss[0]
                 xs = x[w0:w1]
                 ls = lens[w0:w1]
-                _lib.check(call(
+                _lib.check(self.lib.ntb_model_forward_host(
                     self._h, C.c_void_p(xs.ctypes.data), C.c_void_p(ls.ctypes.data),
                     C.c_void_p(goff.ctypes.data) if pass_groups else C.c_void_p(0), nw,
                     (h - g) if pass_groups else 0, _ptr(ws), ws.numel(),
                     C.c_void_p(logits[w0 * T:].ctypes.data) if want_logits else C.c_void_p(0),
                     C.c_void_p(labels[w0 * T:].ctypes.data),
                     C.c_void_p(llen[w0:].ctypes.data) if llen is not None else C.c_void_p(0), stream))
-            if pipeline:
-                for st in self._streams:
-                    st.synchronize()
         return self._shape_labels(labels, n), llen, logits
+
+    def _forward_host_overlapped(self, x, lens, group_off, pass_groups, chunks, labels, llen, logits):
+        """Several chunks: the kernels of all chunks run back to back on the caller's stream through
+        ``ntb_model_forward`` with ONE workspace, while a second stream carries the host->device copy of chunk i+1 and
+        the device->host read of chunk i-1 through two sets of staging buffers.  Results are bit-identical to the
+        synchronous per-chunk ``ntb_model_forward_host`` calls (same chunks, same kernels)."""
+        T, Cc, dev = self.T, self.C, self.device
+        want_logits = logits is not None
+        wmax = max(int(group_off[h] - group_off[g]) for g, h in chunks)
+        gmax = max(h - g for g, h in chunks)
+        xt, lt = torch.from_numpy(_pin(x)), torch.from_numpy(_pin(lens))
+        lab_t = torch.from_numpy(labels)
+        llen_t = torch.from_numpy(llen) if llen is not None else None
+        log_t = torch.from_numpy(logits) if want_logits else None
+        with torch.cuda.device(dev):
+            ws = self._workspace(self.workspace_bytes(wmax, gmax))
+            key = (wmax, gmax, want_logits, tuple(x.shape[1:]))
+            if self._stage is None or self._stage[0] != key:
+                def bufs():
+                    return {"x": torch.empty((wmax,) + tuple(x.shape[1:]), dtype=torch.float32, device=dev),
+                            "len": torch.empty(wmax, dtype=torch.int32, device=dev),
+                            "goff": torch.empty(gmax + 1, dtype=torch.int32, device=dev),
+                            "lab": torch.empty(wmax * T, dtype=torch.int32, device=dev),
+                            "llen": torch.empty(wmax, dtype=torch.int32, device=dev),
+                            "log": torch.empty((wmax * T, Cc), dtype=torch.float32, device=dev) if want_logits else None}
+                self._stage = (key, [bufs(), bufs()])
+            stage = self._stage[1]
+            if self._streams is None:
+                self._streams = [torch.cuda.Stream(dev)]
+            copy = self._streams[0]
+            main = torch.cuda.current_stream(dev)
+            copy.wait_stream(main)
+            goffs = [_pin(np.ascontiguousarray(group_off[g:h + 1] - group_off[g], dtype=np.int32)) for g, h in chunks]
+            in_ready = [torch.cuda.Event() for _ in chunks]
+            out_ready = [torch.cuda.Event() for _ in chunks]
+            drained = [torch.cuda.Event() for _ in chunks]        # staging set free again (its D2H has finished)
+
+            def upload(i):
+                g, h = chunks[i]
+                w0, w1 = int(group_off[g]), int(group_off[h])
+                b = stage[i & 1]
+                with torch.cuda.stream(copy):
+                    if i >= 2:
+                        copy.wait_event(out_ready[i - 2])          # chunk i-2 no longer reads / writes this set
+                    b["x"][:w1 - w0].copy_(xt[w0:w1], non_blocking=True)
+                    b["len"][:w1 - w0].copy_(lt[w0:w1], non_blocking=True)
+                    if pass_groups:
+                        b["goff"][:h - g + 1].copy_(torch.from_numpy(goffs[i]), non_blocking=True)
+                    in_ready[i].record(copy)
+
+            upload(0)
+            for i, (g, h) in enumerate(chunks):
+                w0, w1 = int(group_off[g]), int(group_off[h])
+                nw = w1 - w0
+                b = stage[i & 1]
+                if i + 1 < len(chunks):
+                    upload(i + 1)
+                main.wait_event(in_ready[i])
+                if i >= 2:
+                    main.wait_event(drained[i - 2])                # the labels of chunk i-2 have left this set
+                _lib.check(self.lib.ntb_model_forward(
+                    self._h, _ptr(b["x"]), _ptr(b["len"]), _ptr(b["goff"]) if pass_groups else C.c_void_p(0), nw,
+                    (h - g) if pass_groups else 0, _ptr(ws), ws.numel(), _ptr(b["log"]), _ptr(b["lab"]), _ptr(b["llen"]),
+                    C.c_void_p(main.cuda_stream)))
+                out_ready[i].record(main)
+                with torch.cuda.stream(copy):
+                    copy.wait_event(out_ready[i])
+                    lab_t[w0 * T:w1 * T].copy_(b["lab"][:nw * T], non_blocking=True)
+                    if llen_t is not None:
+                        llen_t[w0:w1].copy_(b["llen"][:nw], non_blocking=True)
+                    if want_logits:
+                        log_t[w0 * T:w1 * T].copy_(b["log"][:nw * T], non_blocking=True)
+                    drained[i].record(copy)
+            copy.synchronize()
+            main.synchronize()
 
     def _shape_labels(self, labels, n):
         return labels.reshape(n, self.T) if self.graph == "CtcLoss" else labels
@@ -323,10 +369,27 @@ def _pin(a):
     return t.pin_memory().numpy()
 
 
+_PIN_POOL = []      # [pinned torch tensor, weakref to the numpy array handed out]: page-locking 100 MB costs ~9 ms
+
+
 def _pinned(shape, dtype):
-    if int(np.prod(shape)) == 0:
+    """Page-locked numpy array for results.  Blocks are recycled once the caller has dropped the array (and every
+    view of it) that was handed out before: a weak reference to that array tells."""
+    count = int(np.prod(shape))
+    if count == 0:
         return np.empty(shape, dtype=torch.empty(0, dtype=dtype).numpy().dtype)
-    return torch.empty(shape, dtype=dtype, pin_memory=True).numpy()
+    for entry in _PIN_POOL:
+        t, ref = entry
+        if ref() is None and t.dtype == dtype and t.numel() == count:
+            a = t.numpy().reshape(shape)
+            entry[1] = weakref.ref(a.base if a.base is not None else a)
+            return a
+    if len(_PIN_POOL) >= 8:                       # drop the idle blocks before growing without bound
+        _PIN_POOL[:] = [e for e in _PIN_POOL if e[1]() is not None]
+    t = torch.empty(count, dtype=dtype, pin_memory=True)
+    base = t.numpy()
+    _PIN_POOL.append([t, weakref.ref(base)])
+    return base.reshape(shape)
 
 
 def _as_np(a, dtype):

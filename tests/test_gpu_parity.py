@@ -402,9 +402,10 @@ def test_read_order_does_not_change_per_read_labels():
             assert np.array_equal(a[i][0], b[i][0])
 
 
-def test_pipelined_host_path_is_bit_identical(monkeypatch):
-    """engine.Model.forward_host with NTB_HOST_PIPELINE=1 (two streams, two workspaces, ntb_model_forward_host_async)
-    returns exactly what the synchronous path returns."""
+def test_pipelined_host_path_is_bit_identical(monkeypatch, lib):
+    """engine.Model.forward_host over several chunks overlaps the copies of one chunk with the kernels of another
+    (default; NTB_HOST_PIPELINE=0 = one synchronous ntb_model_forward_host call per chunk): same bits either way, and
+    the same again through ntb_model_forward_host_async called directly."""
     net, Cc = syn.NETWORKS["signal_CRNN"], 6
     w = syn.random_weights(net, 1, Cc, seed=5)
     m = engine.Model(net, w, "CtcLoss", 100, 1, Cc, device=DEV)
@@ -412,7 +413,23 @@ def test_pipelined_host_path_is_bit_identical(monkeypatch):
     goff = engine.group_offsets([32] * 10, 16)
     monkeypatch.setenv("NTB_HOST_PIPELINE", "0")
     l1, k1, g1 = m.forward_host(x, lens, goff, want_logits=True, max_windows=64)
+    assert m._streams is None
     monkeypatch.setenv("NTB_HOST_PIPELINE", "1")
     l2, k2, g2 = m.forward_host(x, lens, goff, want_logits=True, max_windows=64)      # 5 chunks, pageable inputs
     assert m._streams is not None
     assert np.array_equal(g1, g2) and np.array_equal(l1, l2) and np.array_equal(k1, k2)
+    # the C entry without the final synchronisation, on a side stream
+    n, T = len(x), 100
+    xp, lp, gp = (torch.from_numpy(a).pin_memory() for a in (x, lens, goff.astype(np.int32)))
+    lab = torch.empty(n * T, dtype=torch.int32).pin_memory()
+    ll = torch.empty(n, dtype=torch.int32).pin_memory()
+    buf = ws(lib.ntb_model_workspace_bytes_host(m._h, n, len(goff) - 1, 0))
+    side = torch.cuda.Stream(DEV)
+    rc = lib.ntb_model_forward_host_async(m._h, C.c_void_p(xp.data_ptr()), C.c_void_p(lp.data_ptr()),
+                                          C.c_void_p(gp.data_ptr()), n, len(goff) - 1, P(buf), buf.numel(), None,
+                                          C.c_void_p(lab.data_ptr()), C.c_void_p(ll.data_ptr()),
+                                          C.c_void_p(side.cuda_stream))
+    assert rc == 0, lib.ntb_last_error()
+    side.synchronize()
+    whole_l, whole_k, _ = m.forward_host(x, lens, goff)
+    assert np.array_equal(lab.numpy().reshape(n, T), whole_l) and np.array_equal(ll.numpy(), whole_k)
