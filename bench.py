@@ -303,8 +303,8 @@ def run_b200(args):
         torch.cuda.synchronize()
         dt = max_over_ranks(time.perf_counter() - t0) / max(args.steps, 1)
         e2e = {"value": total_samples / dt, "unit": UNIT,
-               "h2d_bytes_per_step": int(x.nbytes + lens.nbytes + goff.nbytes),
-               "d2h_bytes_per_step": int(labels.nbytes + llen.nbytes), "ms_per_step": dt * 1e3}
+               "h2d_bytes_per_step": int(sum_over_ranks(x.nbytes + lens.nbytes + goff.nbytes)),
+               "d2h_bytes_per_step": int(sum_over_ranks(labels.nbytes + llen.nbytes)), "ms_per_step": dt * 1e3}
 
     # ---- roofline of the dominant kernel: k_gemm_tc<2>, the tcgen05 GEMM of the LSTM input projections (three
     # launches per forward, the largest share of the launch list in profiles/).  Its launches are bracketed by CUDA
