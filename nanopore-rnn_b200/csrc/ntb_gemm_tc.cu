@@ -153,6 +153,13 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
             mg = P / p.n_tiles + it * (NP / p.n_tiles);
             return mg < m_groups;
         }
+        if (p.n_split > 0) {
+            // dual output: one pair takes BOTH halves of an M group back to back, so the second pass over the A tiles is an
+            // L2 hit (with the N tiles spread over neighbouring pairs ncu showed the A planes read from DRAM 1.84 times)
+            nt = (int)(it % p.n_tiles);
+            mg = P + (it / p.n_tiles) * NP;
+            return mg < m_groups;
+        }
         const int64_t tile = P + it * NP;
         nt = (int)(tile % p.n_tiles);
         mg = tile / p.n_tiles;
