@@ -163,6 +163,26 @@ NTB_API int ntb_pack_windows(const int16_t *raw_dev, const int64_t *read_off_dev
                      int32_t seq_len, int32_t step, int32_t start_index, float *x_dev,
                      int32_t *len_dev, void *stream);
 
+/* events_to_features (nanonet/nanonet/features.py:61-75) with SquiggleFeatureGenerator.__init__
+ * (features.py:266-293, sloika_model=False), scale_array (features.py:32-58) and padded_offset_array
+ * (features.py:14-29), window [-1, 0, 1]: the feature front end of the event (CrossEntropy) model
+ * (nanonetcall.py:204 feeds features.astype(nn.dtype) to the network).  Per read: mean / stdv / length
+ * standardised over the read, delta = diff of the standardised mean / its population std; per event the
+ * 12 columns [mean, stdv, length, delta] x (left neighbour, self, right neighbour), zeros past the ends.
+ * float64 arithmetic in NumPy's own operation and pairwise-summation order: with out_f64 = 1 the result is
+ * bit-identical to the reference's; out_f64 = 0 rounds once to float32 (the .astype at the call site).
+ * mean/stdv/length [total_events] float64, reads concatenated; read_off_host [n_reads+1] int64 is a HOST
+ * pointer (event offsets, 0 .. total_events); out [total_events, 12] float64 or float32.
+ * NTB_EINVAL for a read too long for the per-read leaf table in shared memory (> ~500k events; the
+ * reference's own callers drop reads above max_len = 9000 events, features.py:78).
+ * _host: all buffers on the host; copies in, runs, copies out and synchronises `stream`. */
+NTB_API int ntb_event_features(const double *mean_dev, const double *stdv_dev, const double *length_dev,
+                       const int64_t *read_off_host, int64_t n_reads, int64_t total_events,
+                       int32_t out_f64, void *out_dev, void *stream);
+NTB_API int ntb_event_features_host(const double *mean_host, const double *stdv_host,
+                            const double *length_host, const int64_t *read_off_host, int64_t n_reads,
+                            int64_t total_events, int32_t out_f64, void *out_host, void *stream);
+
 /* conv_layer + simple_global_bn (+ReLU) (network.py:312-349): y = conv(in) (k = 1 or 3, SAME,
  * no bias), then per-group batch moments and normalisation.  in_dev [n_windows*T, Cin],
  * filt_dev = TF filter [1,k,Cin,Cout] on the device; scale/offset NULL = no BN.

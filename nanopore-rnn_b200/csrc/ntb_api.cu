@@ -5,6 +5,7 @@
 #include <vector>
 
 #include "ntb_common.cuh"
+#include "ntb_events.cuh"
 #include "ntb_gemm_tc.cuh"
 #include "ntb_kernels.cuh"
 #include "ntb_lstm.cuh"
@@ -811,6 +812,96 @@ extern "C" int ntb_pack_windows(const int16_t *raw_dev, const int64_t *read_off_
     cudaFreeAsync(ms, st);
     if (e != cudaSuccess) return fail(NTB_ECUDA, "ntb_pack_windows: %s", cudaGetErrorString(e));
     return NTB_OK;
+}
+
+// ---- event features (nanonet/nanonet/features.py:61-75; kernels in ntb_events.cuh) ----
+namespace ntb {
+// validates the read table, returns the leaf-table size the longest read needs (or a negative error code)
+static int64_t event_tree_size(const int64_t *read_off, int64_t n_reads, int64_t total_events) {
+    int64_t longest = 0;
+    if (read_off[0] != 0 || read_off[n_reads] != total_events)
+        return fail(NTB_EINVAL, "ntb_event_features: read_off must run from 0 to total_events%s", "");
+    for (int64_t r = 0; r < n_reads; ++r) {
+        const int64_t n = read_off[r + 1] - read_off[r];
+        if (n < 0) return fail(NTB_EINVAL, "ntb_event_features: read_off not monotonic at read %s%lld", "", (long long)r);
+        longest = n > longest ? n : longest;
+    }
+    const int64_t l_max = longest / EV_MIN_LEAF + 1;
+    if (ev_smem_bytes((int)l_max) > 227 * 1024 || longest > (1 << 30))
+        return fail(NTB_EINVAL, "ntb_event_features: read of %s%lld events exceeds the per-read limit", "", (long long)longest);
+    return l_max;
+}
+
+static int launch_event_features(const double *mean, const double *stdv, const double *length, const int64_t *read_off_dev,
+                                 int64_t n_reads, int l_max, int out_f64, void *out, cudaStream_t st) {
+    const size_t smem = ev_smem_bytes(l_max);
+    if (out_f64) {
+        if (smem > 48 * 1024)
+            NTB_CUDA(cudaFuncSetAttribute(k_event_features<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_event_features<double><<<(unsigned)n_reads, EV_THREADS, smem, st>>>(mean, stdv, length, read_off_dev, (double *)out, l_max);
+    } else {
+        if (smem > 48 * 1024)
+            NTB_CUDA(cudaFuncSetAttribute(k_event_features<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_event_features<float><<<(unsigned)n_reads, EV_THREADS, smem, st>>>(mean, stdv, length, read_off_dev, (float *)out, l_max);
+    }
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+}  // namespace ntb
+
+extern "C" int ntb_event_features(const double *mean_dev, const double *stdv_dev, const double *length_dev,
+                                  const int64_t *read_off_host, int64_t n_reads, int64_t total_events, int32_t out_f64,
+                                  void *out_dev, void *stream) {
+    if (!read_off_host || n_reads < 0 || total_events < 0)
+        return fail(NTB_EINVAL, "ntb_event_features: bad argument%s", "");
+    if (total_events > 0 && (!mean_dev || !stdv_dev || !length_dev || !out_dev))
+        return fail(NTB_EINVAL, "ntb_event_features: null buffer%s", "");
+    const int64_t l_max = event_tree_size(read_off_host, n_reads, total_events);
+    if (l_max < 0) return (int)l_max;
+    NTB_TRY(check_device());
+    if (n_reads == 0 || total_events == 0) return NTB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    int64_t *off = nullptr;
+    NTB_CUDA(cudaMallocAsync((void **)&off, sizeof(int64_t) * (n_reads + 1), st));
+    cudaError_t e = cudaMemcpyAsync(off, read_off_host, sizeof(int64_t) * (n_reads + 1), cudaMemcpyHostToDevice, st);
+    int rc = e == cudaSuccess ? launch_event_features(mean_dev, stdv_dev, length_dev, off, n_reads, (int)l_max, out_f64, out_dev, st)
+                              : fail(NTB_ECUDA, "ntb_event_features: %s", cudaGetErrorString(e));
+    cudaFreeAsync(off, st);
+    return rc;
+}
+
+extern "C" int ntb_event_features_host(const double *mean_host, const double *stdv_host, const double *length_host,
+                                       const int64_t *read_off_host, int64_t n_reads, int64_t total_events,
+                                       int32_t out_f64, void *out_host, void *stream) {
+    if (!read_off_host || n_reads < 0 || total_events < 0)
+        return fail(NTB_EINVAL, "ntb_event_features_host: bad argument%s", "");
+    if (total_events > 0 && (!mean_host || !stdv_host || !length_host || !out_host))
+        return fail(NTB_EINVAL, "ntb_event_features_host: null buffer%s", "");
+    const int64_t l_max = event_tree_size(read_off_host, n_reads, total_events);
+    if (l_max < 0) return (int)l_max;
+    NTB_TRY(check_device());
+    if (n_reads == 0 || total_events == 0) return NTB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t in_b = sizeof(double) * (size_t)total_events, out_b = (out_f64 ? 8 : 4) * 12 * (size_t)total_events;
+    const size_t off_b = sizeof(int64_t) * (size_t)(n_reads + 1);
+    unsigned char *buf = nullptr;
+    NTB_CUDA(cudaMallocAsync((void **)&buf, 3 * in_b + out_b + off_b, st));
+    double *m = (double *)buf, *s = m + total_events, *l = s + total_events;
+    unsigned char *o = buf + 3 * in_b;
+    int64_t *off = (int64_t *)(o + out_b);
+    cudaError_t e = cudaMemcpyAsync(m, mean_host, in_b, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(s, stdv_host, in_b, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(l, length_host, in_b, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(off, read_off_host, off_b, cudaMemcpyHostToDevice, st);
+    int rc = e == cudaSuccess ? launch_event_features(m, s, l, off, n_reads, (int)l_max, out_f64, o, st)
+                              : fail(NTB_ECUDA, "ntb_event_features_host: %s", cudaGetErrorString(e));
+    if (rc == NTB_OK) {
+        e = cudaMemcpyAsync(out_host, o, out_b, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) rc = fail(NTB_ECUDA, "ntb_event_features_host: %s", cudaGetErrorString(e));
+    }
+    cudaFreeAsync(buf, st);
+    return rc;
 }
 
 extern "C" int64_t ntb_conv_bn_workspace_bytes(int64_t n_windows, int64_t n_groups, int32_t T, int32_t Cin,

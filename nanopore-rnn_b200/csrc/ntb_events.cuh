@@ -1,0 +1,212 @@
+// Event-feature front end of the event (CrossEntropy) BLSTM model -- SURVEY.md section 8(f) rank 4.
+//
+// Replaces nanonet/nanonet/features.py::events_to_features (features.py:61-75) with
+// SquiggleFeatureGenerator.__init__ (features.py:266-293, sloika_model=False), scale_array (features.py:32-58) and
+// padded_offset_array (features.py:14-29): per read, the event fields mean / stdv / length are standardised over the
+// read, delta = first difference of the standardised mean divided by its population std, and every event gets
+// [mean, stdv, length, delta] of its left neighbour, itself and its right neighbour (zeros past the read ends).
+//
+// The result is BIT-IDENTICAL to the reference (float64 output), not merely close: every float64 operation is the
+// IEEE round-to-nearest one NumPy performs (no FMA contraction: explicit __dadd_rn / __dmul_rn / __ddiv_rn), and the
+// reductions follow NumPy's pairwise-summation tree (loops_utils.h.src @TYPE@_pairwise_sum: blocks of <= 128 values,
+// eight interleaved running sums folded ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)), halves split at n/2 rounded down to a
+// multiple of 8).  The tree maps onto the GPU naturally: a leaf is eight independent running sums = eight lanes, a
+// warp takes four leaves at a time, the fold is three xor-shuffles, and one lane per field adds the leaf sums in the
+// tree's post-order.
+//
+// One CTA per read; nothing is staged: each of the 7 dependent reductions re-derives its operand from the raw fields
+// (L1/L2 resident after the first pass) with the scalars found so far, so the only HBM traffic is 24 B in and
+// 12 x sizeof(out) B out per event.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace ntb {
+
+constexpr int EV_THREADS = 256;
+constexpr int EV_PW_BLOCK = 128;          // numpy PW_BLOCKSIZE
+constexpr int EV_MIN_LEAF = 64;           // a split node has n > 128, so both halves hold >= 64 values
+constexpr double EV_ATOL = 1.0e-8;        // np.allclose(m, 0.0)
+
+struct EvScale {                          // scalars of scale_array for one field, in the order they are found
+    double mean0, m1, sm, s, m2;
+    int c1, c2;                           // the two "re-centre" branches taken?
+};
+
+// value of a field entry after `stage` steps of scale_array: 0 raw, 1 centred, 2 re-centred, 3 squared deviation
+// (np.std's operand), 4 divided by the std, 5 final
+__device__ __forceinline__ double ev_stage(double x, const EvScale &p, int stage) {
+    if (stage == 0) return x;
+    double v = __dsub_rn(x, p.mean0);
+    if (stage == 1) return v;
+    if (p.c1) v = __dsub_rn(v, p.m1);
+    if (stage == 2) return v;
+    if (stage == 3) {
+        const double d = __dsub_rn(v, p.sm);
+        return __dmul_rn(d, d);
+    }
+    v = __ddiv_rn(v, p.s);
+    if (stage == 4) return v;
+    if (p.c2) v = __dsub_rn(v, p.m2);
+    return v;
+}
+
+// The pairwise tree of n values as a leaf table: leaf k covers [leaf_off[k], leaf_off[k+1]); after pushing leaf k's sum
+// the evaluator performs merges[k] additions of the two topmost partial sums (post-order).  Returns the leaf count.
+__device__ inline int ev_build_tree(int n, int *leaf_off, uint8_t *merges) {
+    struct Node { int off, n; };
+    Node st[64];
+    int sp = 0, L = 0;
+    st[sp++] = Node{0, n};
+    while (sp) {
+        const Node e = st[--sp];
+        if (e.n < 0) {                    // merge marker: both children of a node are done
+            ++merges[L - 1];
+            continue;
+        }
+        if (e.n <= EV_PW_BLOCK) {
+            leaf_off[L] = e.off;
+            merges[L] = 0;
+            ++L;
+            continue;
+        }
+        int n2 = e.n / 2;
+        n2 -= n2 % 8;
+        st[sp++] = Node{0, -1};
+        st[sp++] = Node{e.off + n2, e.n - n2};
+        st[sp++] = Node{e.off, n2};
+    }
+    leaf_off[L] = n;
+    return L;
+}
+
+// result[f] = 0.0 + pairwise_sum_i val(f, i) for f < n_fields, in NumPy's order.  All threads of the CTA call this.
+template <class F>
+__device__ __forceinline__ void ev_reduce(int n_fields, const int *leaf_off, const uint8_t *merges, int L, double *sums,
+                                          int l_stride, double *result, F val) {
+    const int grp = threadIdx.x >> 3, j = threadIdx.x & 7;
+    const int items = L * n_fields;
+    for (int base = 0; base < items; base += EV_THREADS / 8) {
+        const int it = base + grp;
+        const bool on = it < items;
+        const int f = on ? it / L : 0, k = on ? it - f * L : 0;
+        const int a = leaf_off[k], len = on ? leaf_off[k + 1] - a : 0;
+        const int full = len & ~7;
+        double r = 0.0;
+        if (len >= 8) {
+            r = val(f, a + j);
+            for (int i = 8 + j; i < full; i += 8) r = __dadd_rn(r, val(f, a + i));
+        }
+        r = __dadd_rn(r, __shfl_xor_sync(0xffffffffu, r, 1));
+        r = __dadd_rn(r, __shfl_xor_sync(0xffffffffu, r, 2));
+        r = __dadd_rn(r, __shfl_xor_sync(0xffffffffu, r, 4));
+        if (on && j == 0) {
+            if (len < 8) {
+                r = 0.0;
+                for (int i = 0; i < len; ++i) r = __dadd_rn(r, val(f, a + i));
+            } else {
+                for (int i = full; i < len; ++i) r = __dadd_rn(r, val(f, a + i));
+            }
+            sums[f * l_stride + k] = r;
+        }
+    }
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0 && (threadIdx.x >> 5) < n_fields) {
+        const int f = threadIdx.x >> 5;
+        double st[40];
+        int sp = 0;
+        for (int k = 0; k < L; ++k) {
+            st[sp++] = sums[f * l_stride + k];
+            for (int m = merges[k]; m; --m) {
+                --sp;
+                st[sp - 1] = __dadd_rn(st[sp - 1], st[sp]);
+            }
+        }
+        result[f] = __dadd_rn(0.0, st[0]);
+    }
+    __syncthreads();
+}
+
+// out [total_events, 12]; l_max >= max over reads of n / 64 + 1 sizes the dynamic shared memory
+template <typename OutT>
+__global__ void __launch_bounds__(EV_THREADS) k_event_features(const double *__restrict__ mean,
+                                                               const double *__restrict__ stdv,
+                                                               const double *__restrict__ length,
+                                                               const int64_t *__restrict__ read_off, OutT *out,
+                                                               int l_max) {
+    extern __shared__ __align__(16) unsigned char ev_smem[];
+    double *sums = reinterpret_cast<double *>(ev_smem);                   // [3][l_max]
+    int *leaf_off = reinterpret_cast<int *>(sums + 3 * (size_t)l_max);    // [l_max + 1]
+    uint8_t *merges = reinterpret_cast<uint8_t *>(leaf_off + l_max + 1);  // [l_max]
+    __shared__ double red[3];
+    __shared__ EvScale sc[3];
+    __shared__ double d_sm, d_s;
+    __shared__ int s_L;
+
+    const int64_t a0 = read_off[blockIdx.x];
+    const int n = (int)(read_off[blockIdx.x + 1] - a0);
+    if (n <= 0) return;
+    const double *xm = mean + a0, *xs = stdv + a0, *xl = length + a0;
+    if (threadIdx.x == 0) s_L = ev_build_tree(n, leaf_off, merges);
+    __syncthreads();
+    const int L = s_L;
+    const double dn = (double)n;
+
+    // scale_array on the three fields at once: five dependent reductions
+    for (int stage = 0; stage <= 4; ++stage) {
+        ev_reduce(3, leaf_off, merges, L, sums, l_max, red, [&](int f, int i) {
+            const double *x = f == 0 ? xm : (f == 1 ? xs : xl);
+            return ev_stage(x[i], sc[f], stage);
+        });
+        if (threadIdx.x < 3) {
+            EvScale &p = sc[threadIdx.x];
+            const double m = __ddiv_rn(red[threadIdx.x], dn);
+            if (stage == 0) p.mean0 = m;
+            else if (stage == 1) { p.m1 = m; p.c1 = !(fabs(m) <= EV_ATOL); }
+            else if (stage == 2) p.sm = m;
+            else if (stage == 3) { const double s = __dsqrt_rn(m); p.s = (s == 0.0) ? 1.0 : s; }
+            else { p.m2 = m; p.c2 = !(fabs(m) <= EV_ATOL); }
+        }
+        __syncthreads();
+    }
+
+    // delta = ediff1d(scaled mean, to_begin=0) / np.std(delta): two more reductions
+    auto diff = [&](int i) {
+        return i == 0 ? 0.0 : __dsub_rn(ev_stage(xm[i], sc[0], 5), ev_stage(xm[i - 1], sc[0], 5));
+    };
+    ev_reduce(1, leaf_off, merges, L, sums, l_max, red, [&](int, int i) { return diff(i); });
+    if (threadIdx.x == 0) d_sm = __ddiv_rn(red[0], dn);
+    __syncthreads();
+    ev_reduce(1, leaf_off, merges, L, sums, l_max, red, [&](int, int i) {
+        const double d = __dsub_rn(diff(i), d_sm);
+        return __dmul_rn(d, d);
+    });
+    if (threadIdx.x == 0) {
+        const double s = __dsqrt_rn(__ddiv_rn(red[0], dn));
+        d_s = (s == 0.0) ? 1.0 : s;
+    }
+    __syncthreads();
+
+    // centre columns 4..7 of every row, then the neighbours' copies (columns 0..3 from row i-1, 8..11 from row i+1)
+    OutT *o = out + a0 * 12;
+    for (int i = threadIdx.x; i < n; i += EV_THREADS) {
+        OutT *row = o + (int64_t)i * 12 + 4;
+        row[0] = (OutT)ev_stage(xm[i], sc[0], 5);
+        row[1] = (OutT)ev_stage(xs[i], sc[1], 5);
+        row[2] = (OutT)ev_stage(xl[i], sc[2], 5);
+        row[3] = (OutT)__ddiv_rn(diff(i), d_s);
+    }
+    __syncthreads();
+    for (int64_t e = threadIdx.x; e < (int64_t)n * 8; e += EV_THREADS) {
+        const int i = (int)(e >> 3), c = (int)(e & 7);                    // c < 4: pos -1, else pos +1
+        const int src = c < 4 ? i - 1 : i + 1;
+        const OutT v = (src >= 0 && src < n) ? o[(int64_t)src * 12 + 4 + (c & 3)] : (OutT)0;
+        o[(int64_t)i * 12 + (c < 4 ? c : c + 4)] = v;
+    }
+}
+
+inline size_t ev_smem_bytes(int l_max) {
+    return 3 * sizeof(double) * (size_t)l_max + sizeof(int) * ((size_t)l_max + 1) + (size_t)l_max + 16;
+}
+
+}  // namespace ntb
