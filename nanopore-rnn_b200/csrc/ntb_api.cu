@@ -816,36 +816,64 @@ extern "C" int ntb_pack_windows(const int16_t *raw_dev, const int64_t *read_off_
 
 // ---- event features (nanonet/nanonet/features.py:61-75; kernels in ntb_events.cuh) ----
 namespace ntb {
-// validates the read table, returns the leaf-table size the longest read needs (or a negative error code)
-static int64_t event_tree_size(const int64_t *read_off, int64_t n_reads, int64_t total_events) {
-    int64_t longest = 0;
+// Which kernels a read table needs: reads up to `small` events run k_event_features_smem at two CTAs per SM, up to `mid`
+// at one CTA per SM, longer ones the any-length kernel.
+struct EventPlan {
+    int small = 0, mid = 0, lng = 0;   // longest read of each class (0 = class empty)
+};
+
+static int ev_cap(size_t budget) {     // largest n whose field + tree fit `budget` bytes of shared memory
+    int lo = 0, hi = 1 << 16;
+    while (lo < hi) {
+        const int m = (lo + hi + 1) / 2;
+        if (ev_smem_bytes_sm(m, m / EV_MIN_LEAF + 1) <= budget) lo = m; else hi = m - 1;
+    }
+    return lo;
+}
+
+static int plan_events(const int64_t *read_off, int64_t n_reads, int64_t total_events, EventPlan &pl) {
+    static const int cap2 = ev_cap((228 * 1024) / 2 - 1024 - 128), cap1 = ev_cap(227 * 1024 - 128);
     if (read_off[0] != 0 || read_off[n_reads] != total_events)
         return fail(NTB_EINVAL, "ntb_event_features: read_off must run from 0 to total_events%s", "");
     for (int64_t r = 0; r < n_reads; ++r) {
         const int64_t n = read_off[r + 1] - read_off[r];
         if (n < 0) return fail(NTB_EINVAL, "ntb_event_features: read_off not monotonic at read %s%lld", "", (long long)r);
-        longest = n > longest ? n : longest;
+        if (n > (1 << 30) || ev_smem_bytes((int)(n / EV_MIN_LEAF + 1)) > 227 * 1024)
+            return fail(NTB_EINVAL, "ntb_event_features: read of %s%lld events exceeds the per-read limit", "", (long long)n);
+        int &slot = n <= cap2 ? pl.small : (n <= cap1 ? pl.mid : pl.lng);
+        slot = (int)n > slot ? (int)n : slot;
     }
-    const int64_t l_max = longest / EV_MIN_LEAF + 1;
-    if (ev_smem_bytes((int)l_max) > 227 * 1024 || longest > (1 << 30))
-        return fail(NTB_EINVAL, "ntb_event_features: read of %s%lld events exceeds the per-read limit", "", (long long)longest);
-    return l_max;
+    return NTB_OK;
 }
 
-static int launch_event_features(const double *mean, const double *stdv, const double *length, const int64_t *read_off_dev,
-                                 int64_t n_reads, int l_max, int out_f64, void *out, cudaStream_t st) {
-    const size_t smem = ev_smem_bytes(l_max);
-    if (out_f64) {
-        if (smem > 48 * 1024)
-            NTB_CUDA(cudaFuncSetAttribute(k_event_features<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_event_features<double><<<(unsigned)n_reads, EV_THREADS, smem, st>>>(mean, stdv, length, read_off_dev, (double *)out, l_max);
-    } else {
-        if (smem > 48 * 1024)
-            NTB_CUDA(cudaFuncSetAttribute(k_event_features<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_event_features<float><<<(unsigned)n_reads, EV_THREADS, smem, st>>>(mean, stdv, length, read_off_dev, (float *)out, l_max);
+template <typename OutT>
+static int launch_event_features_t(const double *mean, const double *stdv, const double *length, const int64_t *read_off_dev,
+                                   int64_t n_reads, const EventPlan &pl, OutT *out, cudaStream_t st) {
+    int n_lo = 1;
+    for (int cls = 0; cls < 2; ++cls) {
+        const int longest = cls == 0 ? pl.small : pl.mid;
+        if (!longest) continue;
+        const int n_cap = (longest + 7) & ~7, l_max = n_cap / EV_MIN_LEAF + 1;
+        const size_t smem = ev_smem_bytes_sm(n_cap, l_max);
+        NTB_CUDA(cudaFuncSetAttribute(k_event_features_smem<OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_event_features_smem<OutT><<<(unsigned)n_reads, EV_SM_THREADS, smem, st>>>(mean, stdv, length, read_off_dev, out,
+                                                                                   l_max, n_lo, n_cap);
+        n_lo = n_cap + 1;
+    }
+    if (pl.lng) {
+        const int l_max = pl.lng / EV_MIN_LEAF + 1;
+        const size_t smem = ev_smem_bytes(l_max);
+        NTB_CUDA(cudaFuncSetAttribute(k_event_features<OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_event_features<OutT><<<(unsigned)n_reads, EV_THREADS, smem, st>>>(mean, stdv, length, read_off_dev, out, l_max, n_lo);
     }
     NTB_LAUNCH_CHECK();
     return NTB_OK;
+}
+
+static int launch_event_features(const double *mean, const double *stdv, const double *length, const int64_t *read_off_dev,
+                                 int64_t n_reads, const EventPlan &pl, int out_f64, void *out, cudaStream_t st) {
+    return out_f64 ? launch_event_features_t<double>(mean, stdv, length, read_off_dev, n_reads, pl, (double *)out, st)
+                   : launch_event_features_t<float>(mean, stdv, length, read_off_dev, n_reads, pl, (float *)out, st);
 }
 }  // namespace ntb
 
@@ -856,15 +884,15 @@ extern "C" int ntb_event_features(const double *mean_dev, const double *stdv_dev
         return fail(NTB_EINVAL, "ntb_event_features: bad argument%s", "");
     if (total_events > 0 && (!mean_dev || !stdv_dev || !length_dev || !out_dev))
         return fail(NTB_EINVAL, "ntb_event_features: null buffer%s", "");
-    const int64_t l_max = event_tree_size(read_off_host, n_reads, total_events);
-    if (l_max < 0) return (int)l_max;
+    EventPlan pl;
+    NTB_TRY(plan_events(read_off_host, n_reads, total_events, pl));
     NTB_TRY(check_device());
     if (n_reads == 0 || total_events == 0) return NTB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     int64_t *off = nullptr;
     NTB_CUDA(cudaMallocAsync((void **)&off, sizeof(int64_t) * (n_reads + 1), st));
     cudaError_t e = cudaMemcpyAsync(off, read_off_host, sizeof(int64_t) * (n_reads + 1), cudaMemcpyHostToDevice, st);
-    int rc = e == cudaSuccess ? launch_event_features(mean_dev, stdv_dev, length_dev, off, n_reads, (int)l_max, out_f64, out_dev, st)
+    int rc = e == cudaSuccess ? launch_event_features(mean_dev, stdv_dev, length_dev, off, n_reads, pl, out_f64, out_dev, st)
                               : fail(NTB_ECUDA, "ntb_event_features: %s", cudaGetErrorString(e));
     cudaFreeAsync(off, st);
     return rc;
@@ -877,8 +905,8 @@ extern "C" int ntb_event_features_host(const double *mean_host, const double *st
         return fail(NTB_EINVAL, "ntb_event_features_host: bad argument%s", "");
     if (total_events > 0 && (!mean_host || !stdv_host || !length_host || !out_host))
         return fail(NTB_EINVAL, "ntb_event_features_host: null buffer%s", "");
-    const int64_t l_max = event_tree_size(read_off_host, n_reads, total_events);
-    if (l_max < 0) return (int)l_max;
+    EventPlan pl;
+    NTB_TRY(plan_events(read_off_host, n_reads, total_events, pl));
     NTB_TRY(check_device());
     if (n_reads == 0 || total_events == 0) return NTB_OK;
     cudaStream_t st = (cudaStream_t)stream;
@@ -893,7 +921,7 @@ extern "C" int ntb_event_features_host(const double *mean_host, const double *st
     if (e == cudaSuccess) e = cudaMemcpyAsync(s, stdv_host, in_b, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(l, length_host, in_b, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(off, read_off_host, off_b, cudaMemcpyHostToDevice, st);
-    int rc = e == cudaSuccess ? launch_event_features(m, s, l, off, n_reads, (int)l_max, out_f64, o, st)
+    int rc = e == cudaSuccess ? launch_event_features(m, s, l, off, n_reads, pl, out_f64, o, st)
                               : fail(NTB_ECUDA, "ntb_event_features_host: %s", cudaGetErrorString(e));
     if (rc == NTB_OK) {
         e = cudaMemcpyAsync(out_host, o, out_b, cudaMemcpyDeviceToHost, st);

@@ -14,9 +14,9 @@
 // warp takes four leaves at a time, the fold is three xor-shuffles, and one lane per field adds the leaf sums in the
 // tree's post-order.
 //
-// One CTA per read; nothing is staged: each of the 7 dependent reductions re-derives its operand from the raw fields
-// (L1/L2 resident after the first pass) with the scalars found so far, so the only HBM traffic is 24 B in and
-// 12 x sizeof(out) B out per event.
+// One CTA per read.  Two kernels: k_event_features_smem keeps the field being standardised in shared memory and updates
+// it in place (reads up to ~27.9k events; the only HBM traffic is 24 B in and 12 x sizeof(out) B out per event);
+// k_event_features is the any-length path that re-derives each reduction's operand from the raw fields in global memory.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -127,13 +127,14 @@ __device__ __forceinline__ void ev_reduce(int n_fields, const int *leaf_off, con
     __syncthreads();
 }
 
+// GENERIC path (reads too long to hold one field in shared memory; any length up to the leaf-table limit).
 // out [total_events, 12]; l_max >= max over reads of n / 64 + 1 sizes the dynamic shared memory
 template <typename OutT>
 __global__ void __launch_bounds__(EV_THREADS) k_event_features(const double *__restrict__ mean,
                                                                const double *__restrict__ stdv,
                                                                const double *__restrict__ length,
                                                                const int64_t *__restrict__ read_off, OutT *out,
-                                                               int l_max) {
+                                                               int l_max, int n_lo) {
     extern __shared__ __align__(16) unsigned char ev_smem[];
     double *sums = reinterpret_cast<double *>(ev_smem);                   // [3][l_max]
     int *leaf_off = reinterpret_cast<int *>(sums + 3 * (size_t)l_max);    // [l_max + 1]
@@ -145,7 +146,7 @@ __global__ void __launch_bounds__(EV_THREADS) k_event_features(const double *__r
 
     const int64_t a0 = read_off[blockIdx.x];
     const int n = (int)(read_off[blockIdx.x + 1] - a0);
-    if (n <= 0) return;
+    if (n <= 0 || n < n_lo) return;       // shorter reads belong to k_event_features_smem
     const double *xm = mean + a0, *xs = stdv + a0, *xl = length + a0;
     if (threadIdx.x == 0) s_L = ev_build_tree(n, leaf_off, merges);
     __syncthreads();
@@ -203,6 +204,179 @@ __global__ void __launch_bounds__(EV_THREADS) k_event_features(const double *__r
         const OutT v = (src >= 0 && src < n) ? o[(int64_t)src * 12 + 4 + (c & 3)] : (OutT)0;
         o[(int64_t)i * 12 + (c < 4 ? c : c + 4)] = v;
     }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// FAST path: reads short enough for one field to live in shared memory (n <= ~13.9k events at two CTAs per SM, ~27.9k
+// at one; the reference's own callers cap reads at 9000 events).  The field is loaded once and updated IN PLACE the way
+// scale_array updates its array (x -= mean, x /= std ...), so every value is read from HBM once, divided once, and
+// written once; the leaf sums are combined level by level of the pairwise tree by the whole CTA instead of one lane.
+constexpr int EV_SM_THREADS = 512;
+
+struct EvTreeSm {            // the pairwise tree with explicit children; value slots: leaf k -> k, inner id -> l_max + id
+    double *vals;            // [2 * l_max]
+    int *leaf_off;           // [l_max + 1]
+    uint16_t *lch, *rch;     // [l_max] children (value-slot indices) of inner node id
+    uint8_t *hgt;            // [l_max] height of inner node id (leaves are 0)
+    int L, n_inner, H, root;
+};
+
+__device__ inline void ev_build_tree_sm(int n, int l_max, EvTreeSm &t, int *hdr) {
+    struct Fr { int off, n, left, lh, state; };
+    Fr st[36];
+    int sp = 0, L = 0, ni = 0, ret = 0, ret_h = 0;
+    st[sp++] = Fr{0, n, 0, 0, 0};
+    while (sp) {
+        Fr &f = st[sp - 1];
+        int n2 = f.n / 2;
+        n2 -= n2 % 8;
+        if (f.state == 0) {
+            if (f.n <= EV_PW_BLOCK) {
+                t.leaf_off[L] = f.off;
+                ret = L++;
+                ret_h = 0;
+                --sp;
+            } else {
+                f.state = 1;
+                st[sp++] = Fr{f.off, n2, 0, 0, 0};
+            }
+        } else if (f.state == 1) {
+            f.left = ret;
+            f.lh = ret_h;
+            f.state = 2;
+            st[sp++] = Fr{f.off + n2, f.n - n2, 0, 0, 0};
+        } else {
+            t.lch[ni] = (uint16_t)f.left;
+            t.rch[ni] = (uint16_t)ret;
+            ret_h = (f.lh > ret_h ? f.lh : ret_h) + 1;
+            t.hgt[ni] = (uint8_t)ret_h;
+            ret = l_max + ni++;
+            --sp;
+        }
+    }
+    t.leaf_off[L] = n;
+    hdr[0] = L; hdr[1] = ni; hdr[2] = ret_h; hdr[3] = ret;
+}
+
+// One reduction pass over the shared-memory field: every element takes v = get(i) (which may store the updated value),
+// contributes term(v); returns 0.0 + the pairwise sum to every thread.
+template <class G, class T>
+__device__ __forceinline__ double ev_pass_sm(const EvTreeSm &t, int l_max, G get, T term) {
+    const int grp = threadIdx.x >> 3, j = threadIdx.x & 7;
+    for (int base = 0; base < t.L; base += EV_SM_THREADS / 8) {
+        const int k = base + grp;
+        const bool on = k < t.L;
+        const int a = on ? t.leaf_off[k] : 0, len = on ? t.leaf_off[k + 1] - a : 0;
+        const int full = len & ~7;
+        double r = 0.0;
+        if (len >= 8) {
+            r = term(get(a + j));
+#pragma unroll 4
+            for (int i = 8 + j; i < full; i += 8) r = __dadd_rn(r, term(get(a + i)));
+        }
+        r = __dadd_rn(r, __shfl_xor_sync(0xffffffffu, r, 1));
+        r = __dadd_rn(r, __shfl_xor_sync(0xffffffffu, r, 2));
+        r = __dadd_rn(r, __shfl_xor_sync(0xffffffffu, r, 4));
+        if (on && j == 0) {
+            if (len < 8) {
+                r = 0.0;
+                for (int i = 0; i < len; ++i) r = __dadd_rn(r, term(get(a + i)));
+            } else {
+                for (int i = full; i < len; ++i) r = __dadd_rn(r, term(get(a + i)));
+            }
+            t.vals[k] = r;
+        }
+    }
+    __syncthreads();
+    for (int h = 1; h <= t.H; ++h) {
+        for (int id = threadIdx.x; id < t.n_inner; id += EV_SM_THREADS)
+            if (t.hgt[id] == h) t.vals[l_max + id] = __dadd_rn(t.vals[t.lch[id]], t.vals[t.rch[id]]);
+        __syncthreads();
+    }
+    const double tot = __dadd_rn(0.0, t.vals[t.root]);
+    __syncthreads();            // the next pass overwrites vals
+    return tot;
+}
+
+// scale_array(with_mean=True) of one field: g (global) -> x (shared, final values); returns nothing, x holds the result
+__device__ __forceinline__ void ev_scale_field_sm(const double *__restrict__ g, double *x, int n, const EvTreeSm &t,
+                                                  int l_max) {
+    const double dn = (double)n;
+    auto id = [](double v) { return v; };
+    const double mean0 = __ddiv_rn(ev_pass_sm(t, l_max, [&](int i) { const double v = g[i]; x[i] = v; return v; }, id), dn);
+    const double m1 = __ddiv_rn(ev_pass_sm(t, l_max, [&](int i) { const double v = __dsub_rn(x[i], mean0); x[i] = v; return v; }, id), dn);
+    const bool c1 = !(fabs(m1) <= EV_ATOL);
+    const double sm = __ddiv_rn(ev_pass_sm(t, l_max, [&](int i) {
+        double v = x[i];
+        if (c1) { v = __dsub_rn(v, m1); x[i] = v; }
+        return v; }, id), dn);
+    const double var = __ddiv_rn(ev_pass_sm(t, l_max, [&](int i) { return x[i]; },
+                                            [&](double v) { const double d = __dsub_rn(v, sm); return __dmul_rn(d, d); }), dn);
+    double s = __dsqrt_rn(var);
+    if (s == 0.0) s = 1.0;
+    const double m2 = __ddiv_rn(ev_pass_sm(t, l_max, [&](int i) { const double v = __ddiv_rn(x[i], s); x[i] = v; return v; }, id), dn);
+    if (!(fabs(m2) <= EV_ATOL)) {
+        for (int i = threadIdx.x; i < n; i += EV_SM_THREADS) x[i] = __dsub_rn(x[i], m2);
+    }
+    __syncthreads();
+}
+
+// handles the reads with n_lo <= n <= n_cap; x holds n_cap doubles
+template <typename OutT>
+__global__ void __launch_bounds__(EV_SM_THREADS) k_event_features_smem(const double *__restrict__ mean,
+                                                                       const double *__restrict__ stdv,
+                                                                       const double *__restrict__ length,
+                                                                       const int64_t *__restrict__ read_off, OutT *out,
+                                                                       int l_max, int n_lo, int n_cap) {
+    extern __shared__ __align__(16) unsigned char ev_smem[];
+    __shared__ int hdr[4];
+    const int64_t a0 = read_off[blockIdx.x];
+    const int n = (int)(read_off[blockIdx.x + 1] - a0);
+    if (n <= 0 || n < n_lo || n > n_cap) return;
+    double *x = reinterpret_cast<double *>(ev_smem);                      // [n_cap]
+    EvTreeSm t;
+    t.vals = x + n_cap;
+    t.leaf_off = reinterpret_cast<int *>(t.vals + 2 * (size_t)l_max);
+    t.lch = reinterpret_cast<uint16_t *>(t.leaf_off + l_max + 1);
+    t.rch = t.lch + l_max;
+    t.hgt = reinterpret_cast<uint8_t *>(t.rch + l_max);
+    if (threadIdx.x == 0) ev_build_tree_sm(n, l_max, t, hdr);
+    __syncthreads();
+    t.L = hdr[0]; t.n_inner = hdr[1]; t.H = hdr[2]; t.root = hdr[3];
+    const double dn = (double)n;
+    OutT *o = out + a0 * 12 + 4;                                          // centre columns 4..7
+
+    // mean, then delta from the standardised mean still in shared memory
+    ev_scale_field_sm(mean + a0, x, n, t, l_max);
+    for (int i = threadIdx.x; i < n; i += EV_SM_THREADS) o[(int64_t)i * 12] = (OutT)x[i];
+    auto diff = [&](int i) { return i == 0 ? 0.0 : __dsub_rn(x[i], x[i - 1]); };
+    auto idn = [](double v) { return v; };
+    const double d_sm = __ddiv_rn(ev_pass_sm(t, l_max, diff, idn), dn);
+    const double d_var = __ddiv_rn(ev_pass_sm(t, l_max, diff, [&](double v) { const double d = __dsub_rn(v, d_sm); return __dmul_rn(d, d); }), dn);
+    double d_s = __dsqrt_rn(d_var);
+    if (d_s == 0.0) d_s = 1.0;
+    for (int i = threadIdx.x; i < n; i += EV_SM_THREADS) o[(int64_t)i * 12 + 3] = (OutT)__ddiv_rn(diff(i), d_s);
+    __syncthreads();
+    ev_scale_field_sm(stdv + a0, x, n, t, l_max);
+    for (int i = threadIdx.x; i < n; i += EV_SM_THREADS) o[(int64_t)i * 12 + 1] = (OutT)x[i];
+    __syncthreads();
+    ev_scale_field_sm(length + a0, x, n, t, l_max);
+    for (int i = threadIdx.x; i < n; i += EV_SM_THREADS) o[(int64_t)i * 12 + 2] = (OutT)x[i];
+    __syncthreads();
+
+    // the neighbours' copies: columns 0..3 from row i-1, 8..11 from row i+1
+    o -= 4;
+    for (int64_t e = threadIdx.x; e < (int64_t)n * 8; e += EV_SM_THREADS) {
+        const int i = (int)(e >> 3), c = (int)(e & 7);
+        const int src = c < 4 ? i - 1 : i + 1;
+        const OutT v = (src >= 0 && src < n) ? o[(int64_t)src * 12 + 4 + (c & 3)] : (OutT)0;
+        o[(int64_t)i * 12 + (c < 4 ? c : c + 4)] = v;
+    }
+}
+
+inline size_t ev_smem_bytes_sm(int n_cap, int l_max) {
+    return sizeof(double) * ((size_t)n_cap + 2 * (size_t)l_max) + sizeof(int) * ((size_t)l_max + 1) +
+           2 * sizeof(uint16_t) * (size_t)l_max + (size_t)l_max + 16;
 }
 
 inline size_t ev_smem_bytes(int l_max) {

@@ -116,10 +116,11 @@ def test_kernel_every_read_length_up_to_300(lib):
 
 @pytest.mark.gpu
 def test_kernel_long_and_ragged_reads(lib, monkeypatch):
-    """Reads of 9000 events (the reference's max_len) up to 300 000, empty reads in between, an offset of 1e6 pA
-    that makes both re-centring branches fire; NumPy's own reductions are the checker at these sizes."""
+    """Reads of 9000 events (the reference's max_len) up to 300 000 -- all three kernel classes in one call (field in
+    shared memory at two CTAs / one CTA per SM, any-length path) -- empty reads in between, an offset of 1e6 pA that
+    makes the re-centring branches fire; NumPy's own reductions are the checker at these sizes."""
     monkeypatch.setattr(OE, "_SUM", np.add.reduce)
-    lens = [9000, 0, 65537, 1, 300000, 0, 12345, 8999]
+    lens = [9000, 0, 65537, 1, 300000, 0, 12345, 8999, 20000, 27001, 14000, 13000, 28500]
     reads = [synthetic_read(n, 7 + i, offset=1.0e6 if i % 2 else 0.0) for i, n in enumerate(lens)]
     off = np.concatenate([[0], np.cumsum(lens)])
     cat = {k: np.concatenate([r[k] for r in reads]) for k in ("mean", "stdv", "length")}
