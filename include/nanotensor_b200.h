@@ -175,10 +175,14 @@ NTB_API int ntb_pack_windows(const int16_t *raw_dev, const int64_t *read_off_dev
  * pointer (event offsets, 0 .. total_events); out [total_events, 12] float64 or float32.
  * NTB_EINVAL for a read too long for the per-read leaf table in shared memory (> ~500k events; the
  * reference's own callers drop reads above max_len = 9000 events, features.py:78).
- * _host: all buffers on the host; copies in, runs, copies out and synchronises `stream`. */
+ * workspace_dev: ntb_event_features_workspace_bytes() bytes on the device (the read table and the
+ * standardised stdv / length columns between the kernel's passes); nothing is allocated by the call.
+ * _host: all buffers on the host; allocates, copies in, runs, copies out and synchronises `stream`. */
+NTB_API int64_t ntb_event_features_workspace_bytes(int64_t n_reads, int64_t total_events);
 NTB_API int ntb_event_features(const double *mean_dev, const double *stdv_dev, const double *length_dev,
                        const int64_t *read_off_host, int64_t n_reads, int64_t total_events,
-                       int32_t out_f64, void *out_dev, void *stream);
+                       int32_t out_f64, void *workspace_dev, int64_t workspace_bytes, void *out_dev,
+                       void *stream);
 NTB_API int ntb_event_features_host(const double *mean_host, const double *stdv_host,
                             const double *length_host, const int64_t *read_off_host, int64_t n_reads,
                             int64_t total_events, int32_t out_f64, void *out_host, void *stream);

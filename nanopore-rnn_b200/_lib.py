@@ -46,7 +46,8 @@ SIGNATURES = {
     "ntb_model_set_profile": (C.c_int, [_P, C.c_int]),
     "ntb_model_stage_ms": (C.c_int, [_P, _FP, C.c_int]),
     "ntb_pack_windows": (C.c_int, [_P, _P, _P, _I64, _I64, _I32, _I32, _I32, _P, _P, _P]),
-    "ntb_event_features": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I32, _P, _P]),
+    "ntb_event_features_workspace_bytes": (_I64, [_I64, _I64]),
+    "ntb_event_features": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I32, _P, _I64, _P, _P]),
     "ntb_event_features_host": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _I32, _P, _P]),
     "ntb_conv_bn": (C.c_int, [_P, _P, _P, _P, _P, _I64, _I64, _I32, _I32, _I32, _I32, _I32, _P, _I64, _P, _P]),
     "ntb_conv_bn_workspace_bytes": (_I64, [_I64, _I64, _I32, _I32, _I32, _I32]),

@@ -848,38 +848,48 @@ static int plan_events(const int64_t *read_off, int64_t n_reads, int64_t total_e
 
 template <typename OutT>
 static int launch_event_features_t(const double *mean, const double *stdv, const double *length, const int64_t *read_off_dev,
-                                   int64_t n_reads, const EventPlan &pl, OutT *out, cudaStream_t st) {
+                                   int64_t n_reads, int64_t total_events, const EventPlan &pl, double *scratch, OutT *out,
+                                   cudaStream_t st) {
     int n_lo = 1;
     for (int cls = 0; cls < 2; ++cls) {
         const int longest = cls == 0 ? pl.small : pl.mid;
         if (!longest) continue;
         const int n_cap = (longest + 7) & ~7, l_max = n_cap / EV_MIN_LEAF + 1;
         const size_t smem = ev_smem_bytes_sm(n_cap, l_max);
-        NTB_CUDA(cudaFuncSetAttribute(k_event_features_smem<OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cudaFuncSetAttribute(k_event_features_smem<OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         k_event_features_smem<OutT><<<(unsigned)n_reads, EV_SM_THREADS, smem, st>>>(mean, stdv, length, read_off_dev, out,
-                                                                                   l_max, n_lo, n_cap);
+                                                                                   scratch, total_events, l_max,
+                                                                                   (2 << ev_tree_depth(n_cap)) - 1, n_lo, n_cap);
         n_lo = n_cap + 1;
     }
     if (pl.lng) {
         const int l_max = pl.lng / EV_MIN_LEAF + 1;
         const size_t smem = ev_smem_bytes(l_max);
-        NTB_CUDA(cudaFuncSetAttribute(k_event_features<OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cudaFuncSetAttribute(k_event_features<OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         k_event_features<OutT><<<(unsigned)n_reads, EV_THREADS, smem, st>>>(mean, stdv, length, read_off_dev, out, l_max, n_lo);
     }
-    NTB_LAUNCH_CHECK();
+    const cudaError_t e = cudaGetLastError();      // also reports a failed cudaFuncSetAttribute above
+    if (e != cudaSuccess) return fail(NTB_ECUDA, "ntb_event_features: %s", cudaGetErrorString(e));
     return NTB_OK;
 }
 
 static int launch_event_features(const double *mean, const double *stdv, const double *length, const int64_t *read_off_dev,
-                                 int64_t n_reads, const EventPlan &pl, int out_f64, void *out, cudaStream_t st) {
-    return out_f64 ? launch_event_features_t<double>(mean, stdv, length, read_off_dev, n_reads, pl, (double *)out, st)
-                   : launch_event_features_t<float>(mean, stdv, length, read_off_dev, n_reads, pl, (float *)out, st);
+                                 int64_t n_reads, int64_t total_events, const EventPlan &pl, double *scratch, int out_f64,
+                                 void *out, cudaStream_t st) {
+    return out_f64 ? launch_event_features_t<double>(mean, stdv, length, read_off_dev, n_reads, total_events, pl, scratch, (double *)out, st)
+                   : launch_event_features_t<float>(mean, stdv, length, read_off_dev, n_reads, total_events, pl, scratch, (float *)out, st);
 }
 }  // namespace ntb
 
+// workspace: [read_off: n_reads + 1 int64][scratch: 2 * total_events doubles]
+extern "C" int64_t ntb_event_features_workspace_bytes(int64_t n_reads, int64_t total_events) {
+    if (n_reads < 0 || total_events < 0) return 0;
+    return align_up((int64_t)sizeof(int64_t) * (n_reads + 1), 256) + (int64_t)sizeof(double) * 2 * total_events;
+}
+
 extern "C" int ntb_event_features(const double *mean_dev, const double *stdv_dev, const double *length_dev,
                                   const int64_t *read_off_host, int64_t n_reads, int64_t total_events, int32_t out_f64,
-                                  void *out_dev, void *stream) {
+                                  void *workspace_dev, int64_t workspace_bytes, void *out_dev, void *stream) {
     if (!read_off_host || n_reads < 0 || total_events < 0)
         return fail(NTB_EINVAL, "ntb_event_features: bad argument%s", "");
     if (total_events > 0 && (!mean_dev || !stdv_dev || !length_dev || !out_dev))
@@ -888,14 +898,14 @@ extern "C" int ntb_event_features(const double *mean_dev, const double *stdv_dev
     NTB_TRY(plan_events(read_off_host, n_reads, total_events, pl));
     NTB_TRY(check_device());
     if (n_reads == 0 || total_events == 0) return NTB_OK;
+    const int64_t need = ntb_event_features_workspace_bytes(n_reads, total_events);
+    if (!workspace_dev || workspace_bytes < need)
+        return fail(NTB_ENOMEM, "ntb_event_features: workspace too small (need %s%lld)", "", (long long)need);
     cudaStream_t st = (cudaStream_t)stream;
-    int64_t *off = nullptr;
-    NTB_CUDA(cudaMallocAsync((void **)&off, sizeof(int64_t) * (n_reads + 1), st));
-    cudaError_t e = cudaMemcpyAsync(off, read_off_host, sizeof(int64_t) * (n_reads + 1), cudaMemcpyHostToDevice, st);
-    int rc = e == cudaSuccess ? launch_event_features(mean_dev, stdv_dev, length_dev, off, n_reads, pl, out_f64, out_dev, st)
-                              : fail(NTB_ECUDA, "ntb_event_features: %s", cudaGetErrorString(e));
-    cudaFreeAsync(off, st);
-    return rc;
+    int64_t *off = (int64_t *)workspace_dev;
+    double *scratch = (double *)((char *)workspace_dev + align_up((int64_t)sizeof(int64_t) * (n_reads + 1), 256));
+    NTB_CUDA(cudaMemcpyAsync(off, read_off_host, sizeof(int64_t) * (n_reads + 1), cudaMemcpyHostToDevice, st));
+    return launch_event_features(mean_dev, stdv_dev, length_dev, off, n_reads, total_events, pl, scratch, out_f64, out_dev, st);
 }
 
 extern "C" int ntb_event_features_host(const double *mean_host, const double *stdv_host, const double *length_host,
@@ -913,15 +923,15 @@ extern "C" int ntb_event_features_host(const double *mean_host, const double *st
     const size_t in_b = sizeof(double) * (size_t)total_events, out_b = (out_f64 ? 8 : 4) * 12 * (size_t)total_events;
     const size_t off_b = sizeof(int64_t) * (size_t)(n_reads + 1);
     unsigned char *buf = nullptr;
-    NTB_CUDA(cudaMallocAsync((void **)&buf, 3 * in_b + out_b + off_b, st));
-    double *m = (double *)buf, *s = m + total_events, *l = s + total_events;
-    unsigned char *o = buf + 3 * in_b;
+    NTB_CUDA(cudaMallocAsync((void **)&buf, 5 * in_b + out_b + off_b, st));
+    double *m = (double *)buf, *s = m + total_events, *l = s + total_events, *scratch = l + total_events;
+    unsigned char *o = buf + 5 * in_b;
     int64_t *off = (int64_t *)(o + out_b);
     cudaError_t e = cudaMemcpyAsync(m, mean_host, in_b, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(s, stdv_host, in_b, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(l, length_host, in_b, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(off, read_off_host, off_b, cudaMemcpyHostToDevice, st);
-    int rc = e == cudaSuccess ? launch_event_features(m, s, l, off, n_reads, pl, out_f64, o, st)
+    int rc = e == cudaSuccess ? launch_event_features(m, s, l, off, n_reads, total_events, pl, scratch, out_f64, o, st)
                               : fail(NTB_ECUDA, "ntb_event_features_host: %s", cudaGetErrorString(e));
     if (rc == NTB_OK) {
         e = cudaMemcpyAsync(out_host, o, out_b, cudaMemcpyDeviceToHost, st);

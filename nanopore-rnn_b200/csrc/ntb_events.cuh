@@ -210,63 +210,66 @@ __global__ void __launch_bounds__(EV_THREADS) k_event_features(const double *__r
 // FAST path: reads short enough for one field to live in shared memory (n <= ~13.9k events at two CTAs per SM, ~27.9k
 // at one; the reference's own callers cap reads at 9000 events).  The field is loaded once and updated IN PLACE the way
 // scale_array updates its array (x -= mean, x /= std ...), so every value is read from HBM once, divided once, and
-// written once; the leaf sums are combined level by level of the pairwise tree by the whole CTA instead of one lane.
+// written once.  The pairwise tree is held in HEAP form (children of slot q are 2q+1 and 2q+2): every thread derives
+// the span of its own slot from n alone, so the tree is built by the whole CTA in a few integer steps, the leaf sums land
+// in their slots in any order, and one warp folds the levels bottom-up between two block barriers.
 constexpr int EV_SM_THREADS = 512;
 
-struct EvTreeSm {            // the pairwise tree with explicit children; value slots: leaf k -> k, inner id -> l_max + id
-    double *vals;            // [2 * l_max]
-    int *leaf_off;           // [l_max + 1]
-    uint16_t *lch, *rch;     // [l_max] children (value-slot indices) of inner node id
-    uint8_t *hgt;            // [l_max] height of inner node id (leaves are 0)
-    int L, n_inner, H, root;
+__host__ __device__ inline int ev_tree_depth(int n) {     // depth of the deepest leaf (the right child is never smaller)
+    int d = 0;
+    while (n > EV_PW_BLOCK) {
+        int n2 = n / 2;
+        n2 -= n2 % 8;
+        n -= n2;
+        ++d;
+    }
+    return d;
+}
+
+struct EvTreeSm {
+    double *vals;            // [heap] partial sums, slot q
+    int2 *leaf;              // [l_max] {offset << 8 | length, slot} of every leaf, in no particular order
+    uint8_t *inner;          // [heap] 1 = slot q is a split node
+    double *tot;             // [2] totals of the last two passes (double-buffered: no barrier between read and reuse)
+    int *n_leaf;             // leaf counter
+    int L, D, pass;
 };
 
-__device__ inline void ev_build_tree_sm(int n, int l_max, EvTreeSm &t, int *hdr) {
-    struct Fr { int off, n, left, lh, state; };
-    Fr st[36];
-    int sp = 0, L = 0, ni = 0, ret = 0, ret_h = 0;
-    st[sp++] = Fr{0, n, 0, 0, 0};
-    while (sp) {
-        Fr &f = st[sp - 1];
-        int n2 = f.n / 2;
-        n2 -= n2 % 8;
-        if (f.state == 0) {
-            if (f.n <= EV_PW_BLOCK) {
-                t.leaf_off[L] = f.off;
-                ret = L++;
-                ret_h = 0;
-                --sp;
-            } else {
-                f.state = 1;
-                st[sp++] = Fr{f.off, n2, 0, 0, 0};
-            }
-        } else if (f.state == 1) {
-            f.left = ret;
-            f.lh = ret_h;
-            f.state = 2;
-            st[sp++] = Fr{f.off + n2, f.n - n2, 0, 0, 0};
-        } else {
-            t.lch[ni] = (uint16_t)f.left;
-            t.rch[ni] = (uint16_t)ret;
-            ret_h = (f.lh > ret_h ? f.lh : ret_h) + 1;
-            t.hgt[ni] = (uint8_t)ret_h;
-            ret = l_max + ni++;
-            --sp;
+// all threads; heap = 2^(D+1) - 1 slots
+__device__ __forceinline__ void ev_build_tree_sm(int n, EvTreeSm &t) {
+    t.D = ev_tree_depth(n);
+    t.pass = 0;
+    if (threadIdx.x == 0) *t.n_leaf = 0;
+    __syncthreads();
+    const int heap = (2 << t.D) - 1;
+    for (int q = threadIdx.x; q < heap; q += EV_SM_THREADS) {
+        const int d = 31 - __clz(q + 1);
+        int off = 0, m = n;
+        bool exists = true;
+        for (int s = d - 1; s >= 0; --s) {                // walk down from the root along the bits of q + 1
+            if (m <= EV_PW_BLOCK) { exists = false; break; }
+            int n2 = m / 2;
+            n2 -= n2 % 8;
+            if (((q + 1) >> s) & 1) { off += n2; m -= n2; } else m = n2;
         }
+        const bool split = exists && m > EV_PW_BLOCK;
+        t.inner[q] = split ? 1 : 0;
+        if (exists && !split) t.leaf[atomicAdd(t.n_leaf, 1)] = make_int2((off << 8) | m, q);
     }
-    t.leaf_off[L] = n;
-    hdr[0] = L; hdr[1] = ni; hdr[2] = ret_h; hdr[3] = ret;
+    __syncthreads();
+    t.L = *t.n_leaf;
 }
 
 // One reduction pass over the shared-memory field: every element takes v = get(i) (which may store the updated value),
 // contributes term(v); returns 0.0 + the pairwise sum to every thread.
 template <class G, class T>
-__device__ __forceinline__ double ev_pass_sm(const EvTreeSm &t, int l_max, G get, T term) {
+__device__ __forceinline__ double ev_pass_sm(EvTreeSm &t, G get, T term) {
     const int grp = threadIdx.x >> 3, j = threadIdx.x & 7;
     for (int base = 0; base < t.L; base += EV_SM_THREADS / 8) {
         const int k = base + grp;
         const bool on = k < t.L;
-        const int a = on ? t.leaf_off[k] : 0, len = on ? t.leaf_off[k + 1] - a : 0;
+        const int2 lf = on ? t.leaf[k] : make_int2(0, 0);
+        const int a = lf.x >> 8, len = lf.x & 255;
         const int full = len & ~7;
         double r = 0.0;
         if (len >= 8) {
@@ -284,99 +287,119 @@ __device__ __forceinline__ double ev_pass_sm(const EvTreeSm &t, int l_max, G get
             } else {
                 for (int i = full; i < len; ++i) r = __dadd_rn(r, term(get(a + i)));
             }
-            t.vals[k] = r;
+            t.vals[lf.y] = r;
         }
     }
     __syncthreads();
-    for (int h = 1; h <= t.H; ++h) {
-        for (int id = threadIdx.x; id < t.n_inner; id += EV_SM_THREADS)
-            if (t.hgt[id] == h) t.vals[l_max + id] = __dadd_rn(t.vals[t.lch[id]], t.vals[t.rch[id]]);
-        __syncthreads();
+    const int par = t.pass++ & 1;
+    if (threadIdx.x < 32) {
+        for (int d = t.D - 1; d >= 0; --d) {
+            const int first = (1 << d) - 1;
+            for (int q = first + (int)threadIdx.x; q < 2 * first + 1; q += 32)
+                if (t.inner[q]) t.vals[q] = __dadd_rn(t.vals[2 * q + 1], t.vals[2 * q + 2]);
+            __syncwarp();
+        }
+        if (threadIdx.x == 0) t.tot[par] = __dadd_rn(0.0, t.vals[0]);
     }
-    const double tot = __dadd_rn(0.0, t.vals[t.root]);
-    __syncthreads();            // the next pass overwrites vals
-    return tot;
+    __syncthreads();
+    return t.tot[par];
 }
 
-// scale_array(with_mean=True) of one field: g (global) -> x (shared, final values); returns nothing, x holds the result
-__device__ __forceinline__ void ev_scale_field_sm(const double *__restrict__ g, double *x, int n, const EvTreeSm &t,
-                                                  int l_max) {
+// scale_array(with_mean=True) of one field: g (global) -> x (shared) holding the final values
+__device__ __forceinline__ void ev_scale_field_sm(const double *__restrict__ g, double *x, int n, EvTreeSm &t) {
     const double dn = (double)n;
     auto id = [](double v) { return v; };
-    const double mean0 = __ddiv_rn(ev_pass_sm(t, l_max, [&](int i) { const double v = g[i]; x[i] = v; return v; }, id), dn);
-    const double m1 = __ddiv_rn(ev_pass_sm(t, l_max, [&](int i) { const double v = __dsub_rn(x[i], mean0); x[i] = v; return v; }, id), dn);
+    const double mean0 = __ddiv_rn(ev_pass_sm(t, [&](int i) { const double v = g[i]; x[i] = v; return v; }, id), dn);
+    const double m1 = __ddiv_rn(ev_pass_sm(t, [&](int i) { const double v = __dsub_rn(x[i], mean0); x[i] = v; return v; }, id), dn);
     const bool c1 = !(fabs(m1) <= EV_ATOL);
-    const double sm = __ddiv_rn(ev_pass_sm(t, l_max, [&](int i) {
+    const double sm = __ddiv_rn(ev_pass_sm(t, [&](int i) {
         double v = x[i];
         if (c1) { v = __dsub_rn(v, m1); x[i] = v; }
         return v; }, id), dn);
-    const double var = __ddiv_rn(ev_pass_sm(t, l_max, [&](int i) { return x[i]; },
+    const double var = __ddiv_rn(ev_pass_sm(t, [&](int i) { return x[i]; },
                                             [&](double v) { const double d = __dsub_rn(v, sm); return __dmul_rn(d, d); }), dn);
     double s = __dsqrt_rn(var);
     if (s == 0.0) s = 1.0;
-    const double m2 = __ddiv_rn(ev_pass_sm(t, l_max, [&](int i) { const double v = __ddiv_rn(x[i], s); x[i] = v; return v; }, id), dn);
+    const double m2 = __ddiv_rn(ev_pass_sm(t, [&](int i) { const double v = __ddiv_rn(x[i], s); x[i] = v; return v; }, id), dn);
     if (!(fabs(m2) <= EV_ATOL)) {
         for (int i = threadIdx.x; i < n; i += EV_SM_THREADS) x[i] = __dsub_rn(x[i], m2);
     }
     __syncthreads();
 }
 
-// handles the reads with n_lo <= n <= n_cap; x holds n_cap doubles
+__device__ __forceinline__ void ev_prefetch_l2(const double *g, int n) {
+    const char *p = reinterpret_cast<const char *>(g);
+    for (int b = threadIdx.x * 128; b < n * 8; b += EV_SM_THREADS * 128)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(p + b));
+}
+
+// handles the reads with n_lo <= n <= n_cap; x holds n_cap doubles, the heap 2^(depth(n_cap)+1) slots; scratch
+// [2][total_events] doubles (field-major standardised stdv and length -- coalesced, L2-resident between its write and
+// its read a few microseconds later)
 template <typename OutT>
 __global__ void __launch_bounds__(EV_SM_THREADS) k_event_features_smem(const double *__restrict__ mean,
                                                                        const double *__restrict__ stdv,
                                                                        const double *__restrict__ length,
                                                                        const int64_t *__restrict__ read_off, OutT *out,
-                                                                       int l_max, int n_lo, int n_cap) {
+                                                                       double *scratch, int64_t total_events, int l_max,
+                                                                       int heap, int n_lo, int n_cap) {
     extern __shared__ __align__(16) unsigned char ev_smem[];
-    __shared__ int hdr[4];
+    __shared__ double tot[2];
+    __shared__ int n_leaf;
     const int64_t a0 = read_off[blockIdx.x];
     const int n = (int)(read_off[blockIdx.x + 1] - a0);
     if (n <= 0 || n < n_lo || n > n_cap) return;
+    ev_prefetch_l2(stdv + a0, n);
+    ev_prefetch_l2(length + a0, n);
+    ev_prefetch_l2(mean + a0, n);
     double *x = reinterpret_cast<double *>(ev_smem);                      // [n_cap]
     EvTreeSm t;
     t.vals = x + n_cap;
-    t.leaf_off = reinterpret_cast<int *>(t.vals + 2 * (size_t)l_max);
-    t.lch = reinterpret_cast<uint16_t *>(t.leaf_off + l_max + 1);
-    t.rch = t.lch + l_max;
-    t.hgt = reinterpret_cast<uint8_t *>(t.rch + l_max);
-    if (threadIdx.x == 0) ev_build_tree_sm(n, l_max, t, hdr);
-    __syncthreads();
-    t.L = hdr[0]; t.n_inner = hdr[1]; t.H = hdr[2]; t.root = hdr[3];
+    t.leaf = reinterpret_cast<int2 *>(t.vals + heap);
+    t.inner = reinterpret_cast<uint8_t *>(t.leaf + l_max);
+    t.tot = tot;
+    t.n_leaf = &n_leaf;
+    ev_build_tree_sm(n, t);
     const double dn = (double)n;
-    OutT *o = out + a0 * 12 + 4;                                          // centre columns 4..7
+    double *f_sd = scratch + a0, *f_len = scratch + total_events + a0;
 
-    // mean, then delta from the standardised mean still in shared memory
-    ev_scale_field_sm(mean + a0, x, n, t, l_max);
-    for (int i = threadIdx.x; i < n; i += EV_SM_THREADS) o[(int64_t)i * 12] = (OutT)x[i];
+    ev_scale_field_sm(stdv + a0, x, n, t);
+    for (int i = threadIdx.x; i < n; i += EV_SM_THREADS) f_sd[i] = x[i];
+    __syncthreads();
+    ev_scale_field_sm(length + a0, x, n, t);
+    for (int i = threadIdx.x; i < n; i += EV_SM_THREADS) f_len[i] = x[i];
+    __syncthreads();
+    // mean last: it stays in shared memory for delta and for the output pass
+    ev_scale_field_sm(mean + a0, x, n, t);
     auto diff = [&](int i) { return i == 0 ? 0.0 : __dsub_rn(x[i], x[i - 1]); };
     auto idn = [](double v) { return v; };
-    const double d_sm = __ddiv_rn(ev_pass_sm(t, l_max, diff, idn), dn);
-    const double d_var = __ddiv_rn(ev_pass_sm(t, l_max, diff, [&](double v) { const double d = __dsub_rn(v, d_sm); return __dmul_rn(d, d); }), dn);
+    const double d_sm = __ddiv_rn(ev_pass_sm(t, diff, idn), dn);
+    const double d_var = __ddiv_rn(ev_pass_sm(t, diff, [&](double v) { const double d = __dsub_rn(v, d_sm); return __dmul_rn(d, d); }), dn);
     double d_s = __dsqrt_rn(d_var);
     if (d_s == 0.0) d_s = 1.0;
-    for (int i = threadIdx.x; i < n; i += EV_SM_THREADS) o[(int64_t)i * 12 + 3] = (OutT)__ddiv_rn(diff(i), d_s);
-    __syncthreads();
-    ev_scale_field_sm(stdv + a0, x, n, t, l_max);
-    for (int i = threadIdx.x; i < n; i += EV_SM_THREADS) o[(int64_t)i * 12 + 1] = (OutT)x[i];
-    __syncthreads();
-    ev_scale_field_sm(length + a0, x, n, t, l_max);
-    for (int i = threadIdx.x; i < n; i += EV_SM_THREADS) o[(int64_t)i * 12 + 2] = (OutT)x[i];
-    __syncthreads();
 
-    // the neighbours' copies: columns 0..3 from row i-1, 8..11 from row i+1
-    o -= 4;
-    for (int64_t e = threadIdx.x; e < (int64_t)n * 8; e += EV_SM_THREADS) {
-        const int i = (int)(e >> 3), c = (int)(e & 7);
-        const int src = c < 4 ? i - 1 : i + 1;
-        const OutT v = (src >= 0 && src < n) ? o[(int64_t)src * 12 + 4 + (c & 3)] : (OutT)0;
-        o[(int64_t)i * 12 + (c < 4 ? c : c + 4)] = v;
+    // thread (i, k) holds feature k of event i and stores it where the three rows want it: columns 4+k of row i, k of
+    // row i+1, 8+k of row i-1; four neighbouring threads write one aligned group of four values each time
+    OutT *o = out + a0 * 12;
+#pragma unroll 2
+    for (int e = threadIdx.x; e < 4 * n; e += EV_SM_THREADS) {
+        const int i = e >> 2, k = e & 3;
+        double v;
+        if (k == 0) v = x[i];
+        else if (k == 1) v = f_sd[i];
+        else if (k == 2) v = f_len[i];
+        else v = __ddiv_rn(diff(i), d_s);
+        const OutT w = (OutT)v;
+        OutT *row = o + (int64_t)i * 12 + k;
+        row[4] = w;
+        if (i + 1 < n) row[12] = w; else row[8] = (OutT)0;
+        if (i > 0) row[-4] = w; else row[0] = (OutT)0;
     }
 }
 
 inline size_t ev_smem_bytes_sm(int n_cap, int l_max) {
-    return sizeof(double) * ((size_t)n_cap + 2 * (size_t)l_max) + sizeof(int) * ((size_t)l_max + 1) +
-           2 * sizeof(uint16_t) * (size_t)l_max + (size_t)l_max + 16;
+    const size_t heap = ((size_t)2 << ev_tree_depth(n_cap)) - 1;
+    return sizeof(double) * ((size_t)n_cap + heap) + sizeof(int2) * (size_t)l_max + heap + 16;
 }
 
 inline size_t ev_smem_bytes(int l_max) {

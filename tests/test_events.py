@@ -80,8 +80,10 @@ def _run(lib, mean, stdv, length, read_off, f64=True, host=False):
     d = [torch.as_tensor(np.ascontiguousarray(v, dtype=np.float64)).to("cuda:0") for v in (mean, stdv, length)]
     out = torch.full((total, 12), float("nan"), dtype=torch.float64 if f64 else torch.float32, device="cuda:0")
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    wb = lib.ntb_event_features_workspace_bytes(len(off) - 1, total)
+    ws = torch.empty(max(int(wb), 256), dtype=torch.uint8, device="cuda:0")
     _lib.check(lib.ntb_event_features(d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), off.ctypes.data,
-                                      len(off) - 1, total, int(f64), out.data_ptr(), st))
+                                      len(off) - 1, total, int(f64), ws.data_ptr(), wb, out.data_ptr(), st))
     torch.cuda.synchronize()
     return out.cpu().numpy()
 
@@ -155,6 +157,10 @@ def test_bad_read_tables_are_rejected(lib):
     for off in ([0, 8, 4, 16], [1, 16], [0, 8]):
         o = np.asarray(off, dtype=np.int64)
         rc = lib.ntb_event_features(z.data_ptr(), z.data_ptr(), z.data_ptr(), o.ctypes.data, len(o) - 1, 16, 1,
-                                    out.data_ptr(), None)
+                                    out.data_ptr(), out.numel() * 8, out.data_ptr(), None)
         assert rc == -1, (off, rc)
+    o = np.asarray([0, 16], dtype=np.int64)                            # a workspace that is too small: NTB_ENOMEM
+    rc = lib.ntb_event_features(z.data_ptr(), z.data_ptr(), z.data_ptr(), o.ctypes.data, 1, 16, 1, z.data_ptr(), 64,
+                                out.data_ptr(), None)
+    assert rc == -4 and b"workspace" in lib.ntb_last_error()
     assert features.events_to_features_batch([])[0].shape == (0, 12)

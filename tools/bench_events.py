@@ -53,9 +53,11 @@ def main():
     st = torch.cuda.current_stream()
     for f64 in (1, 0):
         out = torch.empty((total, 12), dtype=torch.float64 if f64 else torch.float32, device="cuda")
+        wb = lib.ntb_event_features_workspace_bytes(a.reads, total)
+        ws = torch.empty(wb, dtype=torch.uint8, device="cuda")
         call = lambda: _lib.check(lib.ntb_event_features(d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(),  # noqa: E731
-                                                         off.ctypes.data, a.reads, total, f64, out.data_ptr(),
-                                                         C.c_void_p(st.cuda_stream)))
+                                                         off.ctypes.data, a.reads, total, f64, ws.data_ptr(), wb,
+                                                         out.data_ptr(), C.c_void_p(st.cuda_stream)))
         for _ in range(3):
             call()
         torch.cuda.synchronize()
