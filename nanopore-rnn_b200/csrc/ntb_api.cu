@@ -816,10 +816,11 @@ extern "C" int ntb_pack_windows(const int16_t *raw_dev, const int64_t *read_off_
 
 // ---- event features (nanonet/nanonet/features.py:61-75; kernels in ntb_events.cuh) ----
 namespace ntb {
-// Which kernels a read table needs: reads up to `small` events run k_event_features_smem at two CTAs per SM, up to `mid`
-// at one CTA per SM, longer ones the any-length kernel.
+// Which kernels a read table needs: k_event_features_smem at three, two or one CTA per SM by read length, the any-length
+// kernel beyond that.
 struct EventPlan {
-    int small = 0, mid = 0, lng = 0;   // longest read of each class (0 = class empty)
+    int sm[3] = {0, 0, 0};             // longest read of each shared-memory class (0 = class empty)
+    int lng = 0;                       // longest read of the any-length class
 };
 
 static int ev_cap(size_t budget) {     // largest n whose field + tree fit `budget` bytes of shared memory
@@ -832,7 +833,8 @@ static int ev_cap(size_t budget) {     // largest n whose field + tree fit `budg
 }
 
 static int plan_events(const int64_t *read_off, int64_t n_reads, int64_t total_events, EventPlan &pl) {
-    static const int cap2 = ev_cap((228 * 1024) / 2 - 1024 - 128), cap1 = ev_cap(227 * 1024 - 128);
+    static const int cap[3] = {ev_cap((228 * 1024) / 3 - 1024 - 128), ev_cap((228 * 1024) / 2 - 1024 - 128),
+                               ev_cap(227 * 1024 - 128)};
     if (read_off[0] != 0 || read_off[n_reads] != total_events)
         return fail(NTB_EINVAL, "ntb_event_features: read_off must run from 0 to total_events%s", "");
     for (int64_t r = 0; r < n_reads; ++r) {
@@ -840,7 +842,7 @@ static int plan_events(const int64_t *read_off, int64_t n_reads, int64_t total_e
         if (n < 0) return fail(NTB_EINVAL, "ntb_event_features: read_off not monotonic at read %s%lld", "", (long long)r);
         if (n > (1 << 30) || ev_smem_bytes((int)(n / EV_MIN_LEAF + 1)) > 227 * 1024)
             return fail(NTB_EINVAL, "ntb_event_features: read of %s%lld events exceeds the per-read limit", "", (long long)n);
-        int &slot = n <= cap2 ? pl.small : (n <= cap1 ? pl.mid : pl.lng);
+        int &slot = n <= cap[0] ? pl.sm[0] : (n <= cap[1] ? pl.sm[1] : (n <= cap[2] ? pl.sm[2] : pl.lng));
         slot = (int)n > slot ? (int)n : slot;
     }
     return NTB_OK;
@@ -851,8 +853,8 @@ static int launch_event_features_t(const double *mean, const double *stdv, const
                                    int64_t n_reads, int64_t total_events, const EventPlan &pl, double *scratch, OutT *out,
                                    cudaStream_t st) {
     int n_lo = 1;
-    for (int cls = 0; cls < 2; ++cls) {
-        const int longest = cls == 0 ? pl.small : pl.mid;
+    for (int cls = 0; cls < 3; ++cls) {
+        const int longest = pl.sm[cls];
         if (!longest) continue;
         const int n_cap = (longest + 7) & ~7, l_max = n_cap / EV_MIN_LEAF + 1;
         const size_t smem = ev_smem_bytes_sm(n_cap, l_max);

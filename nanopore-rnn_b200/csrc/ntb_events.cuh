@@ -207,13 +207,13 @@ __global__ void __launch_bounds__(EV_THREADS) k_event_features(const double *__r
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// FAST path: reads short enough for one field to live in shared memory (n <= ~13.9k events at two CTAs per SM, ~27.9k
-// at one; the reference's own callers cap reads at 9000 events).  The field is loaded once and updated IN PLACE the way
+// FAST path: reads short enough for one field to live in shared memory (n <= ~9.1k events at three CTAs per SM, ~13.9k
+// at two, ~27.9k at one; the reference's own callers cap reads at 9000 events).  The field is loaded once and updated IN PLACE the way
 // scale_array updates its array (x -= mean, x /= std ...), so every value is read from HBM once, divided once, and
 // written once.  The pairwise tree is held in HEAP form (children of slot q are 2q+1 and 2q+2): every thread derives
 // the span of its own slot from n alone, so the tree is built by the whole CTA in a few integer steps, the leaf sums land
 // in their slots in any order, and one warp folds the levels bottom-up between two block barriers.
-constexpr int EV_SM_THREADS = 512;
+constexpr int EV_SM_THREADS = 384;
 
 __host__ __device__ inline int ev_tree_depth(int n) {     // depth of the deepest leaf (the right child is never smaller)
     int d = 0;
@@ -260,32 +260,49 @@ __device__ __forceinline__ void ev_build_tree_sm(int n, EvTreeSm &t) {
     t.L = *t.n_leaf;
 }
 
-// One reduction pass over the shared-memory field: every element takes v = get(i) (which may store the updated value),
-// contributes term(v); returns 0.0 + the pairwise sum to every thread.
-template <class G, class T>
-__device__ __forceinline__ double ev_pass_sm(EvTreeSm &t, G get, T term) {
+// One reduction pass over the field: every element takes v = f(src + i, i), is stored to dst[i] when WRITE, and
+// contributes term(v); returns 0.0 + the pairwise sum to every thread.  A lane walks its column of the leaf (elements
+// j, j + 8, ...) through a pointer, four rows per trip, so that the address arithmetic stays off the dependent DADD chain.
+template <bool WRITE, class F, class T>
+__device__ __forceinline__ double ev_pass_sm(EvTreeSm &t, const double *src, double *dst, F f, T term) {
     const int grp = threadIdx.x >> 3, j = threadIdx.x & 7;
     for (int base = 0; base < t.L; base += EV_SM_THREADS / 8) {
         const int k = base + grp;
         const bool on = k < t.L;
         const int2 lf = on ? t.leaf[k] : make_int2(0, 0);
         const int a = lf.x >> 8, len = lf.x & 255;
-        const int full = len & ~7;
+        const int cnt = len >> 3;                       // full rows of eight
         double r = 0.0;
-        if (len >= 8) {
-            r = term(get(a + j));
-#pragma unroll 4
-            for (int i = 8 + j; i < full; i += 8) r = __dadd_rn(r, term(get(a + i)));
+        if (cnt) {
+            int i = a + j;
+            const double *ps = src + i;
+            double *pd = dst + i;
+            auto one = [&](int o) {
+                const double v = f(ps + o, i + o);
+                if (WRITE) pd[o] = v;
+                return term(v);
+            };
+            r = one(0);
+            int c = 1;
+            for (; c + 4 <= cnt; c += 4) {
+                const double v0 = one(8), v1 = one(16), v2 = one(24), v3 = one(32);
+                r = __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(r, v0), v1), v2), v3);
+                ps += 32; pd += 32; i += 32;
+            }
+            for (; c < cnt; ++c) {
+                r = __dadd_rn(r, one(8));
+                ps += 8; pd += 8; i += 8;
+            }
         }
         r = __dadd_rn(r, __shfl_xor_sync(0xffffffffu, r, 1));
         r = __dadd_rn(r, __shfl_xor_sync(0xffffffffu, r, 2));
         r = __dadd_rn(r, __shfl_xor_sync(0xffffffffu, r, 4));
         if (on && j == 0) {
-            if (len < 8) {
-                r = 0.0;
-                for (int i = 0; i < len; ++i) r = __dadd_rn(r, term(get(a + i)));
-            } else {
-                for (int i = full; i < len; ++i) r = __dadd_rn(r, term(get(a + i)));
+            if (len < 8) r = 0.0;
+            for (int i = a + (cnt << 3); i < a + len; ++i) {          // the n % 8 tail (all of a leaf shorter than 8)
+                const double v = f(src + i, i);
+                if (WRITE) dst[i] = v;
+                r = __dadd_rn(r, term(v));
             }
             t.vals[lf.y] = r;
         }
@@ -309,18 +326,17 @@ __device__ __forceinline__ double ev_pass_sm(EvTreeSm &t, G get, T term) {
 __device__ __forceinline__ void ev_scale_field_sm(const double *__restrict__ g, double *x, int n, EvTreeSm &t) {
     const double dn = (double)n;
     auto id = [](double v) { return v; };
-    const double mean0 = __ddiv_rn(ev_pass_sm(t, [&](int i) { const double v = g[i]; x[i] = v; return v; }, id), dn);
-    const double m1 = __ddiv_rn(ev_pass_sm(t, [&](int i) { const double v = __dsub_rn(x[i], mean0); x[i] = v; return v; }, id), dn);
+    const double mean0 = __ddiv_rn(ev_pass_sm<true>(t, g, x, [](const double *p, int) { return *p; }, id), dn);
+    const double m1 = __ddiv_rn(ev_pass_sm<true>(t, x, x, [&](const double *p, int) { return __dsub_rn(*p, mean0); }, id), dn);
     const bool c1 = !(fabs(m1) <= EV_ATOL);
-    const double sm = __ddiv_rn(ev_pass_sm(t, [&](int i) {
-        double v = x[i];
-        if (c1) { v = __dsub_rn(v, m1); x[i] = v; }
-        return v; }, id), dn);
-    const double var = __ddiv_rn(ev_pass_sm(t, [&](int i) { return x[i]; },
-                                            [&](double v) { const double d = __dsub_rn(v, sm); return __dmul_rn(d, d); }), dn);
+    // np.std's own mean of the array: without the re-centring the array, the order and hence the sum are those of
+    // the previous pass, bit for bit
+    const double sm = !c1 ? m1 : __ddiv_rn(ev_pass_sm<true>(t, x, x, [&](const double *p, int) { return __dsub_rn(*p, m1); }, id), dn);
+    const double var = __ddiv_rn(ev_pass_sm<false>(t, x, x, [](const double *p, int) { return *p; },
+                                                   [&](double v) { const double d = __dsub_rn(v, sm); return __dmul_rn(d, d); }), dn);
     double s = __dsqrt_rn(var);
     if (s == 0.0) s = 1.0;
-    const double m2 = __ddiv_rn(ev_pass_sm(t, [&](int i) { const double v = __ddiv_rn(x[i], s); x[i] = v; return v; }, id), dn);
+    const double m2 = __ddiv_rn(ev_pass_sm<true>(t, x, x, [&](const double *p, int) { return __ddiv_rn(*p, s); }, id), dn);
     if (!(fabs(m2) <= EV_ATOL)) {
         for (int i = threadIdx.x; i < n; i += EV_SM_THREADS) x[i] = __dsub_rn(x[i], m2);
     }
@@ -371,29 +387,42 @@ __global__ void __launch_bounds__(EV_SM_THREADS) k_event_features_smem(const dou
     __syncthreads();
     // mean last: it stays in shared memory for delta and for the output pass
     ev_scale_field_sm(mean + a0, x, n, t);
-    auto diff = [&](int i) { return i == 0 ? 0.0 : __dsub_rn(x[i], x[i - 1]); };
+    auto diff = [](const double *p, int i) { return i == 0 ? 0.0 : __dsub_rn(p[0], p[-1]); };
     auto idn = [](double v) { return v; };
-    const double d_sm = __ddiv_rn(ev_pass_sm(t, diff, idn), dn);
-    const double d_var = __ddiv_rn(ev_pass_sm(t, diff, [&](double v) { const double d = __dsub_rn(v, d_sm); return __dmul_rn(d, d); }), dn);
+    const double d_sm = __ddiv_rn(ev_pass_sm<false>(t, x, x, diff, idn), dn);
+    const double d_var = __ddiv_rn(ev_pass_sm<false>(t, x, x, diff, [&](double v) { const double d = __dsub_rn(v, d_sm); return __dmul_rn(d, d); }), dn);
     double d_s = __dsqrt_rn(d_var);
     if (d_s == 0.0) d_s = 1.0;
 
     // thread (i, k) holds feature k of event i and stores it where the three rows want it: columns 4+k of row i, k of
     // row i+1, 8+k of row i-1; four neighbouring threads write one aligned group of four values each time
     OutT *o = out + a0 * 12;
-#pragma unroll 2
-    for (int e = threadIdx.x; e < 4 * n; e += EV_SM_THREADS) {
-        const int i = e >> 2, k = e & 3;
-        double v;
-        if (k == 0) v = x[i];
-        else if (k == 1) v = f_sd[i];
-        else if (k == 2) v = f_len[i];
-        else v = __ddiv_rn(diff(i), d_s);
-        const OutT w = (OutT)v;
-        OutT *row = o + (int64_t)i * 12 + k;
-        row[4] = w;
-        if (i + 1 < n) row[12] = w; else row[8] = (OutT)0;
-        if (i > 0) row[-4] = w; else row[0] = (OutT)0;
+    constexpr int UB = 4;                                 // values in flight per thread: the scratch reads are L2 / HBM latency
+    const int k = threadIdx.x & 3;                        // EV_SM_THREADS % 4 == 0: a thread keeps its feature
+    for (int e0 = threadIdx.x; e0 < 4 * n; e0 += EV_SM_THREADS * UB) {
+        double v[UB];
+#pragma unroll
+        for (int u = 0; u < UB; ++u) {
+            const int e = e0 + u * EV_SM_THREADS, i = e >> 2;
+            v[u] = 0.0;
+            if (e < 4 * n) {
+                if (k == 0) v[u] = x[i];
+                else if (k == 1) v[u] = __ldcg(f_sd + i);
+                else if (k == 2) v[u] = __ldcg(f_len + i);
+                else v[u] = __ddiv_rn(diff(x + i, i), d_s);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < UB; ++u) {
+            const int e = e0 + u * EV_SM_THREADS, i = e >> 2;
+            if (e < 4 * n) {
+                const OutT w = (OutT)v[u];
+                OutT *row = o + (3 * e - 2 * k);          // row i, column k: 12 i + k with e = 4 i + k
+                __stcs(row + 4, w);                       // streaming stores: the output must not push the scratch out of L2
+                if (i + 1 < n) __stcs(row + 12, w); else __stcs(row + 8, (OutT)0);
+                if (i > 0) __stcs(row - 4, w); else __stcs(row, (OutT)0);
+            }
+        }
     }
 }
 
