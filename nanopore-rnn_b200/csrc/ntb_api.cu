@@ -896,6 +896,8 @@ extern "C" int ntb_event_features(const double *mean_dev, const double *stdv_dev
         return fail(NTB_EINVAL, "ntb_event_features: bad argument%s", "");
     if (total_events > 0 && (!mean_dev || !stdv_dev || !length_dev || !out_dev))
         return fail(NTB_EINVAL, "ntb_event_features: null buffer%s", "");
+    if (((uintptr_t)out_dev & 15) || ((uintptr_t)workspace_dev & 15))
+        return fail(NTB_EINVAL, "ntb_event_features: out_dev and workspace_dev must be 16-byte aligned%s", "");
     EventPlan pl;
     NTB_TRY(plan_events(read_off_host, n_reads, total_events, pl));
     NTB_TRY(check_device());
@@ -922,21 +924,23 @@ extern "C" int ntb_event_features_host(const double *mean_host, const double *st
     NTB_TRY(check_device());
     if (n_reads == 0 || total_events == 0) return NTB_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    const size_t in_b = sizeof(double) * (size_t)total_events, out_b = (out_f64 ? 8 : 4) * 12 * (size_t)total_events;
+    const size_t in_b = (size_t)align_up((int64_t)sizeof(double) * total_events, 256);   // keeps every sub-buffer aligned
+    const size_t out_b = (size_t)align_up((int64_t)(out_f64 ? 8 : 4) * 12 * total_events, 256);
     const size_t off_b = sizeof(int64_t) * (size_t)(n_reads + 1);
     unsigned char *buf = nullptr;
     NTB_CUDA(cudaMallocAsync((void **)&buf, 5 * in_b + out_b + off_b, st));
-    double *m = (double *)buf, *s = m + total_events, *l = s + total_events, *scratch = l + total_events;
+    double *m = (double *)buf, *s = (double *)(buf + in_b), *l = (double *)(buf + 2 * in_b), *scratch = (double *)(buf + 3 * in_b);
     unsigned char *o = buf + 5 * in_b;
     int64_t *off = (int64_t *)(o + out_b);
-    cudaError_t e = cudaMemcpyAsync(m, mean_host, in_b, cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(s, stdv_host, in_b, cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(l, length_host, in_b, cudaMemcpyHostToDevice, st);
+    const size_t in_n = sizeof(double) * (size_t)total_events, out_n = (out_f64 ? 8 : 4) * 12 * (size_t)total_events;
+    cudaError_t e = cudaMemcpyAsync(m, mean_host, in_n, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(s, stdv_host, in_n, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(l, length_host, in_n, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(off, read_off_host, off_b, cudaMemcpyHostToDevice, st);
     int rc = e == cudaSuccess ? launch_event_features(m, s, l, off, n_reads, total_events, pl, scratch, out_f64, o, st)
                               : fail(NTB_ECUDA, "ntb_event_features_host: %s", cudaGetErrorString(e));
     if (rc == NTB_OK) {
-        e = cudaMemcpyAsync(out_host, o, out_b, cudaMemcpyDeviceToHost, st);
+        e = cudaMemcpyAsync(out_host, o, out_n, cudaMemcpyDeviceToHost, st);
         if (e == cudaSuccess) e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) rc = fail(NTB_ECUDA, "ntb_event_features_host: %s", cudaGetErrorString(e));
     }

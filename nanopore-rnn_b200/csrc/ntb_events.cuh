@@ -343,6 +343,23 @@ __device__ __forceinline__ void ev_scale_field_sm(const double *__restrict__ g, 
     __syncthreads();
 }
 
+// one thread's share of an output group as a streaming 16-byte store (the output must not push the scratch out of
+// L2); p is 16-byte aligned: out is, and every group starts at a multiple of four values
+__device__ __forceinline__ void ev_store_group(double *p, const double (&v)[2]) {
+    __stcs(reinterpret_cast<double2 *>(p), make_double2(v[0], v[1]));
+}
+__device__ __forceinline__ void ev_store_group(float *p, const double (&v)[4]) {
+    __stcs(reinterpret_cast<float4 *>(p), make_float4((float)v[0], (float)v[1], (float)v[2], (float)v[3]));
+}
+template <int N>
+__device__ __forceinline__ void ev_store_zero(double *p) {
+    __stcs(reinterpret_cast<double2 *>(p), make_double2(0.0, 0.0));
+}
+template <int N>
+__device__ __forceinline__ void ev_store_zero(float *p) {
+    __stcs(reinterpret_cast<float4 *>(p), make_float4(0.f, 0.f, 0.f, 0.f));
+}
+
 __device__ __forceinline__ void ev_prefetch_l2(const double *g, int n) {
     const char *p = reinterpret_cast<const char *>(g);
     for (int b = threadIdx.x * 128; b < n * 8; b += EV_SM_THREADS * 128)
@@ -394,33 +411,41 @@ __global__ void __launch_bounds__(EV_SM_THREADS) k_event_features_smem(const dou
     double d_s = __dsqrt_rn(d_var);
     if (d_s == 0.0) d_s = 1.0;
 
-    // thread (i, k) holds feature k of event i and stores it where the three rows want it: columns 4+k of row i, k of
-    // row i+1, 8+k of row i-1; four neighbouring threads write one aligned group of four values each time
+    // Output: the features of event i go, as one aligned group of four, to columns 4..7 of row i, 0..3 of row i+1 and
+    // 8..11 of row i-1 (zeros past the read ends).  float32: one thread per event, one 16-byte store per group;
+    // float64: two threads per event (features 0-1 / 2-3), so that a lane pair fills one 32-byte sector.
     OutT *o = out + a0 * 12;
-    constexpr int UB = 4;                                 // values in flight per thread: the scratch reads are L2 / HBM latency
-    const int k = threadIdx.x & 3;                        // EV_SM_THREADS % 4 == 0: a thread keeps its feature
-    for (int e0 = threadIdx.x; e0 < 4 * n; e0 += EV_SM_THREADS * UB) {
-        double v[UB];
+    constexpr int TPE = sizeof(OutT) == 8 ? 2 : 1, FPT = 4 / TPE;   // threads per event, features per thread
+    constexpr int UB = 2;                                 // groups in flight per thread: the scratch reads are L2 / HBM latency
+    const int h = TPE == 2 ? (threadIdx.x & 1) : 0;       // EV_SM_THREADS is even: a thread keeps its half
+    for (int e0 = threadIdx.x; e0 < n * TPE; e0 += EV_SM_THREADS * UB) {
+        double v[UB][FPT];
 #pragma unroll
         for (int u = 0; u < UB; ++u) {
-            const int e = e0 + u * EV_SM_THREADS, i = e >> 2;
-            v[u] = 0.0;
-            if (e < 4 * n) {
-                if (k == 0) v[u] = x[i];
-                else if (k == 1) v[u] = __ldcg(f_sd + i);
-                else if (k == 2) v[u] = __ldcg(f_len + i);
-                else v[u] = __ddiv_rn(diff(x + i, i), d_s);
+            const int e = e0 + u * EV_SM_THREADS, i = e / TPE;
+            if (e < n * TPE) {
+                if (TPE == 1) {
+                    v[u][0] = x[i];
+                    v[u][1] = __ldcg(f_sd + i);
+                    v[u][FPT - 2] = __ldcg(f_len + i);
+                    v[u][FPT - 1] = __ddiv_rn(diff(x + i, i), d_s);
+                } else if (h == 0) {
+                    v[u][0] = x[i];
+                    v[u][1] = __ldcg(f_sd + i);
+                } else {
+                    v[u][0] = __ldcg(f_len + i);
+                    v[u][1] = __ddiv_rn(diff(x + i, i), d_s);
+                }
             }
         }
 #pragma unroll
         for (int u = 0; u < UB; ++u) {
-            const int e = e0 + u * EV_SM_THREADS, i = e >> 2;
-            if (e < 4 * n) {
-                const OutT w = (OutT)v[u];
-                OutT *row = o + (3 * e - 2 * k);          // row i, column k: 12 i + k with e = 4 i + k
-                __stcs(row + 4, w);                       // streaming stores: the output must not push the scratch out of L2
-                if (i + 1 < n) __stcs(row + 12, w); else __stcs(row + 8, (OutT)0);
-                if (i > 0) __stcs(row - 4, w); else __stcs(row, (OutT)0);
+            const int e = e0 + u * EV_SM_THREADS, i = e / TPE;
+            if (e < n * TPE) {
+                OutT *row = o + i * 12 + h * FPT;
+                ev_store_group(row + 4, v[u]);
+                if (i + 1 < n) ev_store_group(row + 12, v[u]); else ev_store_zero<FPT>(row + 8);
+                if (i > 0) ev_store_group(row - 4, v[u]); else ev_store_zero<FPT>(row);
             }
         }
     }
