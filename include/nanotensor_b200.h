@@ -10,8 +10,8 @@
  *  - plain pointers and sizes only; no torch / TF types.  `stream` is a cudaStream_t passed as
  *    void* (NULL = legacy default stream).  Pointers suffixed _dev are device pointers on the
  *    current CUDA device, _host are host pointers.
- *  - the library never allocates device memory: callers size buffers with the *_bytes()
- *    queries and pass them in (the Python host side uses torch's caching allocator).
+ *  - the device-pointer entry points never allocate device memory: callers size buffers with the
+ *    *_bytes() queries and pass them in (the Python host side uses torch's caching allocator).
  *  - every function returns 0 on success, a negative NTB_E* code otherwise;
  *    ntb_last_error() returns a thread-local message.  There is no CPU fallback: without an
  *    sm_100 device every compute entry point returns NTB_ENODEVICE.
@@ -177,6 +177,7 @@ NTB_API int ntb_pack_windows(const int16_t *raw_dev, const int64_t *read_off_dev
  * reference's own callers drop reads above max_len = 9000 events, features.py:78).
  * workspace_dev: ntb_event_features_workspace_bytes() bytes on the device (the read table and the
  * standardised stdv / length columns between the kernel's passes); nothing is allocated by the call.
+ * out_dev and workspace_dev must be 16-byte aligned (vector stores).
  * _host: all buffers on the host; allocates, copies in, runs, copies out and synchronises `stream`. */
 NTB_API int64_t ntb_event_features_workspace_bytes(int64_t n_reads, int64_t total_events);
 NTB_API int ntb_event_features(const double *mean_dev, const double *stdv_dev, const double *length_dev,
