@@ -188,6 +188,28 @@ NTB_API int ntb_event_features_host(const double *mean_host, const double *stdv_
                             const double *length_host, const int64_t *read_off_host, int64_t n_reads,
                             int64_t total_events, int32_t out_f64, void *out_host, void *stream);
 
+/* process_output (nanotensor/dataset.py:421-432): SignalLabel.index2base per window
+ * (nanotensor/trim_signal.py:116-122), simple_assembly + add_count
+ * (chiron/chiron/utils/easy_assembler.py:11-37), np.argmax, index2base -- the consensus call of every read
+ * from the label rows the CTC readout produced.  labels [n_windows, T] int32, -1 padded (ntb_model_forward's
+ * labels_dev); read_off_host [n_reads+1] int64 window offsets (HOST pointer).  Each window is placed against
+ * its predecessor by the offset of their longest common block (difflib's choice and tie-break for windows
+ * under 200 called bases; a longer window sets status 2 and is rejected), bases vote per position, the
+ * consensus is the first-max vote.  Integer work: identical to the reference, vote matrix included.
+ * cons_dev [capacity] uint8 ASCII "ACGTE", reads back to back; cons_off_dev [n_reads+1] int64;
+ * counts_dev optional [5, capacity] int32 vote matrix (row stride = capacity); capacity >= the number of
+ * label entries that are not -1 (n_windows * T always suffices; status 1 otherwise);
+ * status_dev int32: 0 ok.  _host: host buffers, allocates, synchronises, returns the status as an error;
+ * counts_host optional [5, cons_off[n_reads]] compact. */
+NTB_API int64_t ntb_assemble_workspace_bytes(int64_t n_windows, int64_t n_reads, int32_t T, int64_t capacity);
+NTB_API int ntb_assemble_reads(const int32_t *labels_dev, const int64_t *read_off_host, int64_t n_reads,
+                       int64_t n_windows, int32_t T, int64_t capacity, void *workspace_dev,
+                       int64_t workspace_bytes, uint8_t *cons_dev, int64_t *cons_off_dev, int32_t *counts_dev,
+                       int32_t *status_dev, void *stream);
+NTB_API int ntb_assemble_reads_host(const int32_t *labels_host, const int64_t *read_off_host, int64_t n_reads,
+                            int64_t n_windows, int32_t T, int64_t capacity, uint8_t *cons_host,
+                            int64_t *cons_off_host, int32_t *counts_host, void *stream);
+
 /* conv_layer + simple_global_bn (+ReLU) (network.py:312-349): y = conv(in) (k = 1 or 3, SAME,
  * no bias), then per-group batch moments and normalisation.  in_dev [n_windows*T, Cin],
  * filt_dev = TF filter [1,k,Cin,Cout] on the device; scale/offset NULL = no BN.

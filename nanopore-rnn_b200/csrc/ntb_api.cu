@@ -5,6 +5,7 @@
 #include <vector>
 
 #include "ntb_common.cuh"
+#include "ntb_assembly.cuh"
 #include "ntb_events.cuh"
 #include "ntb_gemm_tc.cuh"
 #include "ntb_kernels.cuh"
@@ -946,6 +947,134 @@ extern "C" int ntb_event_features_host(const double *mean_host, const double *st
     }
     cudaFreeAsync(buf, st);
     return rc;
+}
+
+// ---- consensus assembly (nanotensor/dataset.py:421-432; kernels in ntb_assembly.cuh) ----
+namespace ntb {
+struct AsmBufs {
+    int64_t *read_off, *bound, *len, *bound_off;
+    uint8_t *bases;
+    int32_t *blen, *disp, *start, *win_read, *votes, *status;
+};
+static AsmBufs asm_carve(Arena &ar, int64_t n_windows, int64_t n_reads, int32_t T, int64_t capacity) {
+    AsmBufs b;
+    b.read_off = ar.take<int64_t>(n_reads + 1);
+    b.bound = ar.take<int64_t>(n_reads);
+    b.len = ar.take<int64_t>(n_reads);
+    b.bound_off = ar.take<int64_t>(n_reads + 1);
+    b.bases = ar.take<uint8_t>(n_windows * T);
+    b.blen = ar.take<int32_t>(n_windows);
+    b.disp = ar.take<int32_t>(n_windows);
+    b.start = ar.take<int32_t>(n_windows);
+    b.win_read = ar.take<int32_t>(n_windows);
+    b.votes = ar.take<int32_t>(5 * capacity);
+    b.status = ar.take<int32_t>(1);
+    return b;
+}
+static int asm_check_table(const int64_t *read_off, int64_t n_reads, int64_t n_windows) {
+    if (read_off[0] != 0 || read_off[n_reads] != n_windows)
+        return fail(NTB_EINVAL, "ntb_assemble_reads: read_off must run from 0 to n_windows%s", "");
+    for (int64_t r = 0; r < n_reads; ++r)
+        if (read_off[r + 1] < read_off[r])
+            return fail(NTB_EINVAL, "ntb_assemble_reads: read_off not monotonic at read %s%lld", "", (long long)r);
+    return NTB_OK;
+}
+}  // namespace ntb
+
+extern "C" int64_t ntb_assemble_workspace_bytes(int64_t n_windows, int64_t n_reads, int32_t T, int64_t capacity) {
+    if (n_windows < 0 || n_reads < 0 || T <= 0 || capacity < 0) return 0;
+    Arena ar(nullptr, 0);
+    asm_carve(ar, n_windows, n_reads, T, capacity);
+    return ar.off;
+}
+
+extern "C" int ntb_assemble_reads(const int32_t *labels_dev, const int64_t *read_off_host, int64_t n_reads,
+                                  int64_t n_windows, int32_t T, int64_t capacity, void *workspace_dev,
+                                  int64_t workspace_bytes, uint8_t *cons_dev, int64_t *cons_off_dev, int32_t *counts_dev,
+                                  int32_t *status_dev, void *stream) {
+    if (!read_off_host || !cons_off_dev || !status_dev || n_reads < 0 || n_windows < 0 || T <= 0 || capacity < 0 ||
+        (n_windows > 0 && !labels_dev) || (capacity > 0 && !cons_dev))
+        return fail(NTB_EINVAL, "ntb_assemble_reads: bad argument%s", "");
+    NTB_TRY(asm_check_table(read_off_host, n_reads, n_windows));
+    NTB_TRY(check_device());
+    Arena ar(workspace_dev, workspace_bytes);
+    AsmBufs b = asm_carve(ar, n_windows, n_reads, T, capacity);
+    if (!workspace_dev || !ar.ok())
+        return fail(NTB_ENOMEM, "ntb_assemble_reads: workspace too small (need %s%lld)", "", (long long)ar.off);
+    cudaStream_t st = (cudaStream_t)stream;
+    NTB_CUDA(cudaMemsetAsync(status_dev, 0, sizeof(int32_t), st));
+    NTB_CUDA(cudaMemsetAsync(cons_off_dev, 0, sizeof(int64_t) * (n_reads + 1), st));
+    if (n_reads == 0) return NTB_OK;
+    NTB_CUDA(cudaMemcpyAsync(b.read_off, read_off_host, sizeof(int64_t) * (n_reads + 1), cudaMemcpyHostToDevice, st));
+    NTB_CUDA(cudaMemsetAsync(b.votes, 0, sizeof(int32_t) * 5 * capacity, st));
+    if (n_windows > 0) {
+        const unsigned wgrid = (unsigned)cdiv(n_windows, 4);
+        k_asm_compact<<<wgrid, 128, 0, st>>>(labels_dev, n_windows, T, b.bases, b.blen, status_dev);
+        k_asm_window_reads<<<(unsigned)n_reads, 128, 0, st>>>(b.read_off, b.win_read);
+        const size_t smem = asm_disp_smem(T);
+        if (smem > 48 * 1024) cudaFuncSetAttribute(k_asm_disp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_asm_disp<<<(unsigned)cdiv(n_windows, ASM_WARPS), ASM_WARPS * 32, smem, st>>>(b.bases, b.blen, b.win_read, b.read_off,
+                                                                                      n_windows, T, b.disp);
+    }
+    k_asm_scan<<<(unsigned)n_reads, 256, 0, st>>>(b.disp, b.blen, b.read_off, b.start, b.bound, b.len);
+    k_asm_read_offsets<<<1, 1024, 0, st>>>(b.bound, b.len, n_reads, capacity, b.bound_off, cons_off_dev, status_dev);
+    if (n_windows > 0)
+        k_asm_vote<<<(unsigned)cdiv(n_windows, 4), 128, 0, st>>>(b.bases, b.blen, b.start, b.win_read, b.bound_off, b.len,
+                                                                 n_windows, T, capacity, b.votes);
+    k_asm_consensus<<<(unsigned)n_reads, 256, 0, st>>>(b.votes, b.bound_off, cons_off_dev, capacity, cons_dev, counts_dev, capacity);
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+extern "C" int ntb_assemble_reads_host(const int32_t *labels_host, const int64_t *read_off_host, int64_t n_reads,
+                                       int64_t n_windows, int32_t T, int64_t capacity, uint8_t *cons_host,
+                                       int64_t *cons_off_host, int32_t *counts_host, void *stream) {
+    if (!read_off_host || !cons_off_host || n_reads < 0 || n_windows < 0 || T <= 0 || capacity < 0 ||
+        (n_windows > 0 && !labels_host) || (capacity > 0 && !cons_host))
+        return fail(NTB_EINVAL, "ntb_assemble_reads_host: bad argument%s", "");
+    NTB_TRY(asm_check_table(read_off_host, n_reads, n_windows));
+    NTB_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t ws_b = ntb_assemble_workspace_bytes(n_windows, n_reads, T, capacity);
+    const int64_t lab_b = align_up((int64_t)sizeof(int32_t) * n_windows * T, 256), cons_b = align_up(capacity, 256);
+    const int64_t off_b = align_up((int64_t)sizeof(int64_t) * (n_reads + 1), 256);
+    const int64_t cnt_b = counts_host ? align_up((int64_t)sizeof(int32_t) * 5 * capacity, 256) : 0;
+    char *buf = nullptr;
+    NTB_CUDA(cudaMallocAsync((void **)&buf, ws_b + lab_b + cons_b + off_b + cnt_b + 256, st));
+    int32_t *labels = (int32_t *)(buf + ws_b);
+    uint8_t *cons = (uint8_t *)(buf + ws_b + lab_b);
+    int64_t *cons_off = (int64_t *)(buf + ws_b + lab_b + cons_b);
+    int32_t *counts = (int32_t *)(buf + ws_b + lab_b + cons_b + off_b);
+    int32_t *status = (int32_t *)(buf + ws_b + lab_b + cons_b + off_b + cnt_b);
+    auto at = [](void *p) { return p; };   // (device pointers inside buf)
+    int rc = NTB_OK;
+    cudaError_t e = cudaMemcpyAsync(at(labels), labels_host, sizeof(int32_t) * n_windows * T, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess)
+        rc = ntb_assemble_reads((const int32_t *)at(labels), read_off_host, n_reads, n_windows, T, capacity, buf, ws_b,
+                                (uint8_t *)at(cons), (int64_t *)at(cons_off), counts_host ? (int32_t *)at(counts) : nullptr,
+                                (int32_t *)at(status), st);
+    int32_t status_h = 0;
+    if (e == cudaSuccess && rc == NTB_OK) {
+        e = cudaMemcpyAsync(cons_off_host, at(cons_off), sizeof(int64_t) * (n_reads + 1), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&status_h, at(status), sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e == cudaSuccess && status_h == 0) {
+            const int64_t total = cons_off_host[n_reads];
+            e = cudaMemcpyAsync(cons_host, at(cons), (size_t)total, cudaMemcpyDeviceToHost, st);
+            for (int c = 0; counts_host && c < 5 && e == cudaSuccess; ++c)     // compact [5, total] like the reference's matrix
+                e = cudaMemcpyAsync(counts_host + c * total, (int32_t *)at(counts) + c * capacity, sizeof(int32_t) * total,
+                                    cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        }
+    }
+    cudaFreeAsync(buf, st);
+    if (e != cudaSuccess) return fail(NTB_ECUDA, "ntb_assemble_reads_host: %s", cudaGetErrorString(e));
+    if (rc != NTB_OK) return rc;
+    if (status_h == ASM_STATUS_LONG_WINDOW)
+        return fail(NTB_EINVAL, "ntb_assemble_reads: a window has >= 200 called bases (difflib autojunk regime, not built)%s", "");
+    if (status_h == ASM_STATUS_CAPACITY)
+        return fail(NTB_ENOMEM, "ntb_assemble_reads: capacity smaller than the number of called bases%s", "");
+    return NTB_OK;
 }
 
 extern "C" int64_t ntb_conv_bn_workspace_bytes(int64_t n_windows, int64_t n_groups, int32_t T, int32_t Cin,
