@@ -160,10 +160,20 @@ class RunTensorflow(object):
             x, lens, goff, read_off = self.inference.inference_job(files)
             preds, _ = self.inference_model.run_job(x, lens, goff)
             group_read = np.searchsorted(read_off, goff[:-1], side="right") - 1
-            for r, file_path in enumerate(files):
-                mine = [preds[g] for g in np.nonzero(group_read == r)[0]]
-                outputs.append(self.inference.process_output(mine, file_path))
-                log.info(file_path)
+            if type(self.inference) is FullSignalSequence and preds and np.ndim(preds[0]) == 2:
+                # all reads of the job in one launch chain: index2base + simple_assembly + argmax on the GPU
+                # (assembly.py; same FASTA as process_output, dataset.py:421-432)
+                from . import assembly
+                names = [os.path.splitext(os.path.basename(f))[0] for f in files]
+                outputs.extend(assembly.write_fastas(names, np.concatenate(preds), read_off,
+                                                     self.inference.inference_output_dir))
+                for file_path in files:
+                    log.info(file_path)
+            else:
+                for r, file_path in enumerate(files):
+                    mine = [preds[g] for g in np.nonzero(group_read == r)[0]]
+                    outputs.append(self.inference.process_output(mine, file_path))
+                    log.info(file_path)
         print("Finished Inference", file=sys.stderr)
         return outputs
 
