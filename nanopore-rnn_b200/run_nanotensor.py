@@ -165,8 +165,13 @@ class RunTensorflow(object):
                 # (assembly.py; same FASTA as process_output, dataset.py:421-432)
                 from . import assembly
                 names = [os.path.splitext(os.path.basename(f))[0] for f in files]
-                outputs.extend(assembly.write_fastas(names, np.concatenate(preds), read_off,
-                                                     self.inference.inference_output_dir))
+                width = max(p.shape[1] for p in preds)        # each batch is dense to its own longest call
+                rows = np.full((int(read_off[-1]), max(width, 1)), -1, dtype=np.int32)
+                at = 0
+                for p in preds:
+                    rows[at:at + len(p), :p.shape[1]] = p
+                    at += len(p)
+                outputs.extend(assembly.write_fastas(names, rows, read_off, self.inference.inference_output_dir))
                 for file_path in files:
                     log.info(file_path)
             else:
