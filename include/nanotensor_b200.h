@@ -210,6 +210,27 @@ NTB_API int ntb_assemble_reads_host(const int32_t *labels_host, const int64_t *r
                             int64_t n_windows, int32_t T, int64_t capacity, uint8_t *cons_host,
                             int64_t *cons_off_host, int32_t *counts_host, void *stream);
 
+/* minknow_event_detect (nanonet/nanonet/eventdetection/filters.py:299-322): compute_sum_sumsq
+ * (filters.c:57-72), compute_tstat for the two windows (filters.c:130-195), short_long_peak_detector
+ * (filters.c:235-300) and _construct_events (filters.py:146-204): raw current samples -> events, the table
+ * ntb_event_features standardises.  raw [total_samples] float64, reads concatenated; read_off_host
+ * [n_reads+1] int64 sample offsets (HOST pointer); window_lengths[2] / thresholds[2] HOST arrays in the
+ * reference's argument order (the shorter window dominates, as in the reference); events [capacity, 4]
+ * float64 = start, length (both / sample_rate), mean, stdv, reads back to back; event_off [n_reads+1].
+ * Same float64 operations in the same order as the reference's C (sequential cumulative sums included):
+ * start / length / mean bit-identical, stdv within 1 ulp-of-variance (the reference squares the mean with
+ * libm pow).  capacity >= number of events (total_samples always suffices); status_dev: 0 ok, 1 capacity. */
+NTB_API int64_t ntb_event_detect_workspace_bytes(int64_t n_reads, int64_t total_samples);
+NTB_API int ntb_event_detect(const double *raw_dev, const int64_t *read_off_host, int64_t n_reads,
+                     int64_t total_samples, double sample_rate, const int32_t *window_lengths,
+                     const double *thresholds, double peak_height, void *workspace_dev,
+                     int64_t workspace_bytes, int64_t capacity, double *events_dev, int64_t *event_off_dev,
+                     int32_t *status_dev, void *stream);
+NTB_API int ntb_event_detect_host(const double *raw_host, const int64_t *read_off_host, int64_t n_reads,
+                          int64_t total_samples, double sample_rate, const int32_t *window_lengths,
+                          const double *thresholds, double peak_height, int64_t capacity,
+                          double *events_host, int64_t *event_off_host, void *stream);
+
 /* conv_layer + simple_global_bn (+ReLU) (network.py:312-349): y = conv(in) (k = 1 or 3, SAME,
  * no bias), then per-group batch moments and normalisation.  in_dev [n_windows*T, Cin],
  * filt_dev = TF filter [1,k,Cin,Cout] on the device; scale/offset NULL = no BN.

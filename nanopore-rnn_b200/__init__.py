@@ -12,6 +12,6 @@ __version__ = "0.1.0"
 def __getattr__(name):
     # torch-dependent modules load lazily so that config / checkpoint tooling imports fast
     import importlib
-    if name in ("engine", "network", "dataset", "run_nanotensor", "shard", "features", "assembly", "_lib"):
+    if name in ("engine", "network", "dataset", "run_nanotensor", "shard", "features", "assembly", "eventdetection", "_lib"):
         return importlib.import_module("." + name, __name__)
     raise AttributeError(name)

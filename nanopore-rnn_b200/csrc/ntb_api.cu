@@ -1,11 +1,13 @@
 // C ABI of nanotensor_b200 (include/nanotensor_b200.h): model life cycle, the chunk forward and
 // the op-level entry points.  Host-side orchestration only; the kernels live in the .cuh files.
+#include <algorithm>
 #include <new>
 #include <stdlib.h>
 #include <vector>
 
 #include "ntb_common.cuh"
 #include "ntb_assembly.cuh"
+#include "ntb_eventdetect.cuh"
 #include "ntb_events.cuh"
 #include "ntb_gemm_tc.cuh"
 #include "ntb_kernels.cuh"
@@ -1074,6 +1076,119 @@ extern "C" int ntb_assemble_reads_host(const int32_t *labels_host, const int64_t
         return fail(NTB_EINVAL, "ntb_assemble_reads: a window has >= 200 called bases (difflib autojunk regime, not built)%s", "");
     if (status_h == ASM_STATUS_CAPACITY)
         return fail(NTB_ENOMEM, "ntb_assemble_reads: capacity smaller than the number of called bases%s", "");
+    return NTB_OK;
+}
+
+// ---- event detection (nanonet/nanonet/eventdetection/filters.py:299-322; kernels in ntb_eventdetect.cuh) ----
+namespace ntb {
+struct EdBufs {
+    int64_t *read_off, *n_events, *tmp_off;
+    double *sums, *sumsqs, *t_short, *t_long;
+    int32_t *peaks;
+};
+static EdBufs ed_carve(Arena &ar, int64_t n_reads, int64_t total) {
+    EdBufs b;
+    b.read_off = ar.take<int64_t>(n_reads + 1);
+    b.n_events = ar.take<int64_t>(n_reads);
+    b.tmp_off = ar.take<int64_t>(n_reads + 1);
+    b.sums = ar.take<double>(total);
+    b.sumsqs = ar.take<double>(total);
+    b.t_short = ar.take<double>(total);
+    b.t_long = ar.take<double>(total);
+    b.peaks = ar.take<int32_t>(total);
+    return b;
+}
+static int ed_check(const int64_t *read_off, int64_t n_reads, int64_t total, const int32_t *w, const char *who) {
+    if (read_off[0] != 0 || read_off[n_reads] != total) return fail(NTB_EINVAL, "%s: read_off must run from 0 to total_samples", who);
+    for (int64_t r = 0; r < n_reads; ++r) {
+        if (read_off[r + 1] < read_off[r]) return fail(NTB_EINVAL, "%s: read_off not monotonic", who);
+        if (read_off[r + 1] - read_off[r] > 0x7fffffff) return fail(NTB_EINVAL, "%s: read longer than 2^31 samples", who);
+    }
+    if (w[0] < 1 || w[1] < 1) return fail(NTB_EINVAL, "%s: window lengths must be positive", who);
+    return NTB_OK;
+}
+}  // namespace ntb
+
+extern "C" int64_t ntb_event_detect_workspace_bytes(int64_t n_reads, int64_t total_samples) {
+    if (n_reads < 0 || total_samples < 0) return 0;
+    Arena ar(nullptr, 0);
+    ed_carve(ar, n_reads, total_samples);
+    return ar.off;
+}
+
+extern "C" int ntb_event_detect(const double *raw_dev, const int64_t *read_off_host, int64_t n_reads, int64_t total_samples,
+                                double sample_rate, const int32_t *window_lengths, const double *thresholds,
+                                double peak_height, void *workspace_dev, int64_t workspace_bytes, int64_t capacity,
+                                double *events_dev, int64_t *event_off_dev, int32_t *status_dev, void *stream) {
+    if (!read_off_host || !window_lengths || !thresholds || !event_off_dev || !status_dev || n_reads < 0 ||
+        total_samples < 0 || capacity < 0 || (total_samples > 0 && !raw_dev) || (capacity > 0 && !events_dev))
+        return fail(NTB_EINVAL, "ntb_event_detect: bad argument%s", "");
+    NTB_TRY(ed_check(read_off_host, n_reads, total_samples, window_lengths, "ntb_event_detect"));
+    NTB_TRY(check_device());
+    Arena ar(workspace_dev, workspace_bytes);
+    EdBufs b = ed_carve(ar, n_reads, total_samples);
+    if (!workspace_dev || !ar.ok())
+        return fail(NTB_ENOMEM, "ntb_event_detect: workspace too small (need %s%lld)", "", (long long)ar.off);
+    cudaStream_t st = (cudaStream_t)stream;
+    NTB_CUDA(cudaMemsetAsync(status_dev, 0, sizeof(int32_t), st));
+    NTB_CUDA(cudaMemsetAsync(event_off_dev, 0, sizeof(int64_t) * (n_reads + 1), st));
+    if (n_reads == 0) return NTB_OK;
+    // the shorter window is the dominant detector, whatever the order given (filters.py:232-233)
+    const int z = window_lengths[0] > window_lengths[1] ? 1 : 0;
+    const int w_short = window_lengths[z], w_long = window_lengths[1 - z];
+    const double th_short = thresholds[z], th_long = thresholds[1 - z];
+    NTB_CUDA(cudaMemcpyAsync(b.read_off, read_off_host, sizeof(int64_t) * (n_reads + 1), cudaMemcpyHostToDevice, st));
+    const unsigned wgrid = (unsigned)cdiv(n_reads, 4);
+    k_ed_prefix<<<wgrid, 128, 0, st>>>(raw_dev, b.read_off, n_reads, b.sums, b.sumsqs);
+    const int64_t per_read = total_samples / n_reads + 1;
+    const unsigned ychunks = (unsigned)std::min<int64_t>(std::max<int64_t>(per_read / 4096, 1), 64);
+    k_ed_tstat<<<dim3((unsigned)n_reads, ychunks), 256, 0, st>>>(b.sums, b.sumsqs, b.read_off, w_short, w_long, b.t_short, b.t_long);
+    k_ed_peaks<<<wgrid, 128, 0, st>>>(b.t_short, b.t_long, b.read_off, n_reads, w_short, w_long, th_short, th_long,
+                                      peak_height, b.peaks, b.n_events);
+    k_asm_read_offsets<<<1, 1024, 0, st>>>(b.n_events, b.n_events, n_reads, capacity, b.tmp_off, event_off_dev, status_dev);
+    k_ed_events<<<(unsigned)n_reads, 256, 0, st>>>(b.sums, b.sumsqs, b.peaks, b.read_off, event_off_dev, sample_rate, capacity,
+                                                   events_dev);
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+extern "C" int ntb_event_detect_host(const double *raw_host, const int64_t *read_off_host, int64_t n_reads,
+                                     int64_t total_samples, double sample_rate, const int32_t *window_lengths,
+                                     const double *thresholds, double peak_height, int64_t capacity, double *events_host,
+                                     int64_t *event_off_host, void *stream) {
+    if (!read_off_host || !window_lengths || !thresholds || !event_off_host || n_reads < 0 || total_samples < 0 ||
+        capacity < 0 || (total_samples > 0 && !raw_host) || (capacity > 0 && !events_host))
+        return fail(NTB_EINVAL, "ntb_event_detect_host: bad argument%s", "");
+    NTB_TRY(ed_check(read_off_host, n_reads, total_samples, window_lengths, "ntb_event_detect_host"));
+    NTB_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t ws_b = ntb_event_detect_workspace_bytes(n_reads, total_samples);
+    const int64_t raw_b = align_up((int64_t)sizeof(double) * total_samples, 256), ev_b = align_up((int64_t)sizeof(double) * 4 * capacity, 256);
+    const int64_t off_b = align_up((int64_t)sizeof(int64_t) * (n_reads + 1), 256);
+    char *buf = nullptr;
+    NTB_CUDA(cudaMallocAsync((void **)&buf, ws_b + raw_b + ev_b + off_b + 256, st));
+    double *raw = (double *)(buf + ws_b), *ev = (double *)(buf + ws_b + raw_b);
+    int64_t *ev_off = (int64_t *)(buf + ws_b + raw_b + ev_b);
+    int32_t *status = (int32_t *)(buf + ws_b + raw_b + ev_b + off_b);
+    int rc = NTB_OK;
+    int32_t status_h = 0;
+    cudaError_t e = cudaMemcpyAsync(raw, raw_host, sizeof(double) * total_samples, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess)
+        rc = ntb_event_detect(raw, read_off_host, n_reads, total_samples, sample_rate, window_lengths, thresholds, peak_height,
+                              buf, ws_b, capacity, ev, ev_off, status, st);
+    if (e == cudaSuccess && rc == NTB_OK) {
+        e = cudaMemcpyAsync(event_off_host, ev_off, sizeof(int64_t) * (n_reads + 1), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&status_h, status, sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e == cudaSuccess && status_h == 0) {
+            e = cudaMemcpyAsync(events_host, ev, sizeof(double) * 4 * event_off_host[n_reads], cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        }
+    }
+    cudaFreeAsync(buf, st);
+    if (e != cudaSuccess) return fail(NTB_ECUDA, "ntb_event_detect_host: %s", cudaGetErrorString(e));
+    if (rc != NTB_OK) return rc;
+    if (status_h) return fail(NTB_ENOMEM, "ntb_event_detect: capacity smaller than the number of events%s", "");
     return NTB_OK;
 }
 

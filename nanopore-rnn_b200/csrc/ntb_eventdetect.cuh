@@ -1,0 +1,159 @@
+// MinKNOW-style event detection -- SURVEY.md section 8(f) rank 4, second half: raw current samples -> events
+// (start, length, mean, stdv), the table events_to_features (ntb_events.cuh) standardises for the event model.
+//
+// Replaces minknow_event_detect (nanonet/nanonet/eventdetection/filters.py:299-322): compute_sum_sumsq (filters.c:57-72),
+// compute_tstat for two window lengths (filters.c:130-195), short_long_peak_detector (filters.c:235-300, Detector state
+// of filters.py:116-143) and _construct_events (filters.py:146-204).
+//
+// Bit-exact against the reference's own compiled C (oracle/_ref): the cumulative sums are the same SEQUENTIAL float64
+// additions (a parallel scan would round differently), the t-statistic is the same un-fused expression, the peak
+// detector is the same two-detector state machine.  The sequential stages run one WARP per read: the lanes load 32
+// consecutive samples with one coalesced access and then step through them together via shuffles, every lane carrying
+// the same state (lane k keeps the value of step k, so the store is coalesced too); throughput comes from thousands of
+// reads in flight, the parallel stages (t-statistics, events) from one CTA per read.  Float64 IEEE operations only.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace ntb {
+
+__device__ __forceinline__ double ed_bcast(double v, int k) { return __shfl_sync(0xffffffffu, v, k); }
+
+// K1: sum[i] = sum[i-1] + x[i], sumsq[i] = sumsq[i-1] + x[i]*x[i], in order (filters.c:57-72); one warp per read
+__global__ void __launch_bounds__(128) k_ed_prefix(const double *__restrict__ raw, const int64_t *__restrict__ read_off,
+                                                   int64_t n_reads, double *__restrict__ sums, double *__restrict__ sumsqs) {
+    const int64_t r = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (r >= n_reads) return;
+    const int64_t a = read_off[r], b = read_off[r + 1];
+    double s = 0.0, q = 0.0;
+    for (int64_t base = a; base < b; base += 32) {
+        const int64_t i = base + lane;
+        const double x = i < b ? raw[i] : 0.0;
+        const double xx = __dmul_rn(x, x);
+        const int m = (int)min((int64_t)32, b - base);
+        double my_s = 0.0, my_q = 0.0;
+        for (int k = 0; k < m; ++k) {
+            const double v = ed_bcast(x, k), vv = ed_bcast(xx, k);
+            if (base == a && k == 0) { s = v; q = vv; }        // sum[0] = data[0]: no 0.0 + x (keeps -0.0)
+            else { s = __dadd_rn(s, v); q = __dadd_rn(q, vv); }
+            if (k == lane) { my_s = s; my_q = q; }
+        }
+        if (i < b) { sums[i] = my_s; sumsqs[i] = my_q; }
+    }
+}
+
+// K2: windowed t-statistic of the two windows (filters.c:130-195, pooled = false); one CTA per read
+__device__ __forceinline__ double ed_tstat_at(const double *__restrict__ sum, const double *__restrict__ sumsq, int64_t n,
+                                              int64_t i, int w) {
+    if (n < 2 * (int64_t)w || w < 2 || i < w || i > n - w) return 0.0;
+    const double dw = (double)w;
+    double sum1 = sum[i - 1], sumsq1 = sumsq[i - 1];
+    if (i > w) {
+        sum1 = __dsub_rn(sum1, sum[i - w - 1]);
+        sumsq1 = __dsub_rn(sumsq1, sumsq[i - w - 1]);
+    }
+    const double sum2 = __dsub_rn(sum[i + w - 1], sum[i - 1]), sumsq2 = __dsub_rn(sumsq[i + w - 1], sumsq[i - 1]);
+    const double mean1 = __ddiv_rn(sum1, dw), mean2 = __ddiv_rn(sum2, dw);
+    double var1 = __dsub_rn(__ddiv_rn(sumsq1, dw), __dmul_rn(mean1, mean1));
+    double var2 = __dsub_rn(__ddiv_rn(sumsq2, dw), __dmul_rn(mean2, mean2));
+    var1 = fmax(var1, 1e-100);
+    var2 = fmax(var2, 1e-100);
+    const double delta = __dsub_rn(mean2, mean1);
+    const double totvar = __dadd_rn(__ddiv_rn(var1, dw), __ddiv_rn(var2, dw));
+    return fabs(__ddiv_rn(delta, __dsqrt_rn(totvar)));
+}
+
+__global__ void __launch_bounds__(256) k_ed_tstat(const double *__restrict__ sums, const double *__restrict__ sumsqs,
+                                                  const int64_t *__restrict__ read_off, int w_short, int w_long,
+                                                  double *__restrict__ t_short, double *__restrict__ t_long) {
+    const int64_t a = read_off[blockIdx.x], n = read_off[blockIdx.x + 1] - a;
+    for (int64_t i = threadIdx.x + (int64_t)blockIdx.y * 256; i < n; i += 256 * (int64_t)gridDim.y) {
+        t_short[a + i] = ed_tstat_at(sums + a, sumsqs + a, n, i, w_short);
+        t_long[a + i] = ed_tstat_at(sums + a, sumsqs + a, n, i, w_long);
+    }
+}
+
+// K3: the two-detector peak state machine (filters.c:235-300); one warp per read, all lanes in lock step
+struct EdDet {
+    double threshold, peak_value;
+    long long masked_to;
+    int window, peak_pos;
+    bool valid;
+};
+
+__global__ void __launch_bounds__(128) k_ed_peaks(const double *__restrict__ t_short, const double *__restrict__ t_long,
+                                                  const int64_t *__restrict__ read_off, int64_t n_reads, int w_short,
+                                                  int w_long, double th_short, double th_long, double peak_height,
+                                                  int32_t *__restrict__ peaks, int64_t *__restrict__ n_events) {
+    const int64_t r = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (r >= n_reads) return;
+    const int64_t a = read_off[r], b = read_off[r + 1];
+    EdDet d[2];
+    d[0] = EdDet{th_short, 1e100, 0, w_short, -1, false};
+    d[1] = EdDet{th_long, 1e100, 0, w_long, -1, false};
+    int32_t *out = peaks + a;
+    int count = 0;
+    for (int64_t base = a; base < b; base += 32) {
+        const double xs = base + lane < b ? t_short[base + lane] : 0.0, xl = base + lane < b ? t_long[base + lane] : 0.0;
+        const int m = (int)min((int64_t)32, b - base);
+        for (int k = 0; k < m; ++k) {
+            const long long i = base - a + k;
+            const double cur2[2] = {ed_bcast(xs, k), ed_bcast(xl, k)};
+#pragma unroll
+            for (int z = 0; z < 2; ++z) {
+                EdDet &t = d[z];
+                if (t.masked_to >= i) continue;
+                const double cur = cur2[z];
+                if (t.peak_pos == -1) {
+                    if (cur < t.peak_value) t.peak_value = cur;
+                    else if (__dsub_rn(cur, t.peak_value) > peak_height) { t.peak_value = cur; t.peak_pos = (int)i; }
+                } else {
+                    if (cur > t.peak_value) { t.peak_value = cur; t.peak_pos = (int)i; }
+                    if (z == 0 && t.peak_value > t.threshold) {
+                        d[1].masked_to = (long long)t.peak_pos + t.window;
+                        d[1].peak_pos = -1;
+                        d[1].peak_value = 1e100;
+                        d[1].valid = false;
+                    }
+                    if (__dsub_rn(t.peak_value, cur) > peak_height && t.peak_value > t.threshold) t.valid = true;
+                    if (t.valid && (i - t.peak_pos) > t.window / 2) {
+                        if (lane == 0) out[count] = t.peak_pos;
+                        ++count;
+                        t.peak_pos = -1;
+                        t.peak_value = cur;
+                        t.valid = false;
+                    }
+                }
+            }
+        }
+    }
+    if (lane == 0) n_events[r] = b > a ? count + 1 : 0;      // _construct_events: the edges plus the end of the read
+}
+
+// K4: events from the edges (filters.py:180-204); one CTA per read; events [*, 4] = start, length, mean, stdv
+__global__ void __launch_bounds__(256) k_ed_events(const double *__restrict__ sums, const double *__restrict__ sumsqs,
+                                                   const int32_t *__restrict__ peaks, const int64_t *__restrict__ read_off,
+                                                   const int64_t *__restrict__ event_off, double sample_rate,
+                                                   int64_t capacity, double *__restrict__ events) {
+    const int64_t a = read_off[blockIdx.x], n = read_off[blockIdx.x + 1] - a;
+    const int64_t e0 = event_off[blockIdx.x], ne = event_off[blockIdx.x + 1] - e0;
+    const double *sum = sums + a, *sumsq = sumsqs + a;
+    const int32_t *pk = peaks + a;
+    for (int64_t k = threadIdx.x; k < ne; k += 256) {
+        if (e0 + k >= capacity) break;
+        const int64_t e = k < ne - 1 ? pk[k] : n, s = k ? pk[k - 1] : 0;
+        const double ln = (double)(e - s);
+        const double sm = k ? sum[s - 1] : 0.0, smsq = k ? sumsq[s - 1] : 0.0;
+        const double mean = __ddiv_rn(k ? __dsub_rn(sum[e - 1], sm) : sum[e - 1], ln);
+        const double v = __dsub_rn(__ddiv_rn(k ? __dsub_rn(sumsq[e - 1], smsq) : sumsq[e - 1], ln), __dmul_rn(mean, mean));
+        double *ev = events + (e0 + k) * 4;
+        ev[0] = __ddiv_rn((double)s, sample_rate);
+        ev[1] = __ddiv_rn(ln, sample_rate);
+        ev[2] = mean;
+        ev[3] = __dsqrt_rn(v > 0.0 ? v : 0.0);
+    }
+}
+
+}  // namespace ntb
