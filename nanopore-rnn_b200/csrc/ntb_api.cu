@@ -1139,12 +1139,23 @@ extern "C" int ntb_event_detect(const double *raw_dev, const int64_t *read_off_h
     const double th_short = thresholds[z], th_long = thresholds[1 - z];
     NTB_CUDA(cudaMemcpyAsync(b.read_off, read_off_host, sizeof(int64_t) * (n_reads + 1), cudaMemcpyHostToDevice, st));
     const unsigned wgrid = (unsigned)cdiv(n_reads, 4);
-    k_ed_prefix<<<wgrid, 128, 0, st>>>(raw_dev, b.read_off, n_reads, b.sums, b.sumsqs);
+    // sequential stages: a lane per read once there are enough reads to fill the machine that way (32 reads per warp:
+    // measured 26 ms vs 39 ms at 32 768 reads, but 78 ms vs 41 ms at 8192), else a warp per read
+    // (NTB_ED_LANES=0/1 forces one form: A/B and tests)
+    static const char *ed_env = getenv("NTB_ED_LANES");
+    const bool lanes = ed_env ? ed_env[0] == '1' : n_reads >= 20000;
+    const unsigned lgrid = (unsigned)cdiv(n_reads, 64);
+    if (lanes) k_ed_prefix_t<<<lgrid, 64, 0, st>>>(raw_dev, b.read_off, n_reads, b.sums, b.sumsqs);
+    else k_ed_prefix<<<wgrid, 128, 0, st>>>(raw_dev, b.read_off, n_reads, b.sums, b.sumsqs);
     const int64_t per_read = total_samples / n_reads + 1;
     const unsigned ychunks = (unsigned)std::min<int64_t>(std::max<int64_t>(per_read / 4096, 1), 64);
     k_ed_tstat<<<dim3((unsigned)n_reads, ychunks), 256, 0, st>>>(b.sums, b.sumsqs, b.read_off, w_short, w_long, b.t_short, b.t_long);
-    k_ed_peaks<<<wgrid, 128, 0, st>>>(b.t_short, b.t_long, b.read_off, n_reads, w_short, w_long, th_short, th_long,
-                                      peak_height, b.peaks, b.n_events);
+    if (lanes)
+        k_ed_peaks_t<<<lgrid, 64, 0, st>>>(b.t_short, b.t_long, b.read_off, n_reads, w_short, w_long, th_short, th_long,
+                                            peak_height, b.peaks, b.n_events);
+    else
+        k_ed_peaks<<<wgrid, 128, 0, st>>>(b.t_short, b.t_long, b.read_off, n_reads, w_short, w_long, th_short, th_long,
+                                          peak_height, b.peaks, b.n_events);
     k_asm_read_offsets<<<1, 1024, 0, st>>>(b.n_events, b.n_events, n_reads, capacity, b.tmp_off, event_off_dev, status_dev);
     k_ed_events<<<(unsigned)n_reads, 256, 0, st>>>(b.sums, b.sumsqs, b.peaks, b.read_off, event_off_dev, sample_rate, capacity,
                                                    events_dev);

@@ -132,6 +132,115 @@ __global__ void __launch_bounds__(128) k_ed_peaks(const double *__restrict__ t_s
     if (lane == 0) n_events[r] = b > a ? count + 1 : 0;      // _construct_events: the edges plus the end of the read
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// LANE-PER-READ forms of the two sequential stages.  One warp-instruction then advances 32 reads instead of one, which
+// is what the sequential float64 chains need: the warp-per-read forms above spend ~60 issue slots per sample on a
+// single read.  A warp owns 32 consecutive reads; for every chunk of 32 samples it loads each read's chunk with one
+// coalesced access into a padded shared-memory tile, and each lane then walks its own read's row.
+constexpr int ED_TILE = 33;     // row pitch in doubles: lane r reading column k hits bank (33 r + k) % 32, conflict-free
+
+__global__ void __launch_bounds__(64) k_ed_prefix_t(const double *__restrict__ raw, const int64_t *__restrict__ read_off,
+                                                     int64_t n_reads, double *__restrict__ sums, double *__restrict__ sumsqs) {
+    __shared__ double tile[2][2][32 * ED_TILE];
+    const int wi = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t r0 = ((int64_t)blockIdx.x * 2 + wi) * 32;
+    if (r0 >= n_reads) return;
+    double *tx = tile[wi][0], *tq = tile[wi][1];
+    const int64_t my_r = min(r0 + lane, n_reads - 1);
+    const int64_t my_a = read_off[my_r], my_n = r0 + lane < n_reads ? read_off[my_r + 1] - my_a : 0;
+    int64_t longest = my_n;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) longest = max(longest, __shfl_xor_sync(0xffffffffu, longest, o));
+    double s = 0.0, q = 0.0;
+    for (int64_t base = 0; base < longest; base += 32) {
+        for (int rr = 0; rr < 32; ++rr) {                       // coalesced loads, one read at a time
+            const int64_t a = __shfl_sync(0xffffffffu, my_a, rr), n = __shfl_sync(0xffffffffu, my_n, rr);
+            if (base + lane < n) tx[rr * ED_TILE + lane] = raw[a + base + lane];
+        }
+        __syncwarp();
+        const int m = (int)max((int64_t)0, min((int64_t)32, my_n - base));
+        for (int k = 0; k < m; ++k) {
+            const double v = tx[lane * ED_TILE + k], vv = __dmul_rn(v, v);
+            if (base == 0 && k == 0) { s = v; q = vv; }
+            else { s = __dadd_rn(s, v); q = __dadd_rn(q, vv); }
+            tx[lane * ED_TILE + k] = s;
+            tq[lane * ED_TILE + k] = q;
+        }
+        __syncwarp();
+        for (int rr = 0; rr < 32; ++rr) {                       // coalesced stores
+            const int64_t a = __shfl_sync(0xffffffffu, my_a, rr), n = __shfl_sync(0xffffffffu, my_n, rr);
+            if (base + lane < n) {
+                sums[a + base + lane] = tx[rr * ED_TILE + lane];
+                sumsqs[a + base + lane] = tq[rr * ED_TILE + lane];
+            }
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(64) k_ed_peaks_t(const double *__restrict__ t_short, const double *__restrict__ t_long,
+                                                    const int64_t *__restrict__ read_off, int64_t n_reads, int w_short,
+                                                    int w_long, double th_short, double th_long, double peak_height,
+                                                    int32_t *__restrict__ peaks, int64_t *__restrict__ n_events) {
+    __shared__ double tile[2][2][32 * ED_TILE];
+    const int wi = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t r0 = ((int64_t)blockIdx.x * 2 + wi) * 32;
+    if (r0 >= n_reads) return;
+    double *ts = tile[wi][0], *tl = tile[wi][1];
+    const int64_t my_r = min(r0 + lane, n_reads - 1);
+    const int64_t my_a = read_off[my_r], my_n = r0 + lane < n_reads ? read_off[my_r + 1] - my_a : 0;
+    int64_t longest = my_n;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) longest = max(longest, __shfl_xor_sync(0xffffffffu, longest, o));
+    EdDet d[2];
+    d[0] = EdDet{th_short, 1e100, 0, w_short, -1, false};
+    d[1] = EdDet{th_long, 1e100, 0, w_long, -1, false};
+    int32_t *out = peaks + my_a;
+    int count = 0;
+    for (int64_t base = 0; base < longest; base += 32) {
+        for (int rr = 0; rr < 32; ++rr) {
+            const int64_t a = __shfl_sync(0xffffffffu, my_a, rr), n = __shfl_sync(0xffffffffu, my_n, rr);
+            if (base + lane < n) {
+                ts[rr * ED_TILE + lane] = t_short[a + base + lane];
+                tl[rr * ED_TILE + lane] = t_long[a + base + lane];
+            }
+        }
+        __syncwarp();
+        const int m = (int)max((int64_t)0, min((int64_t)32, my_n - base));
+        for (int k = 0; k < m; ++k) {
+            const long long i = base + k;
+            const double cur2[2] = {ts[lane * ED_TILE + k], tl[lane * ED_TILE + k]};
+#pragma unroll
+            for (int z = 0; z < 2; ++z) {
+                EdDet &t = d[z];
+                if (t.masked_to >= i) continue;
+                const double cur = cur2[z];
+                if (t.peak_pos == -1) {
+                    if (cur < t.peak_value) t.peak_value = cur;
+                    else if (__dsub_rn(cur, t.peak_value) > peak_height) { t.peak_value = cur; t.peak_pos = (int)i; }
+                } else {
+                    if (cur > t.peak_value) { t.peak_value = cur; t.peak_pos = (int)i; }
+                    if (z == 0 && t.peak_value > t.threshold) {
+                        d[1].masked_to = (long long)t.peak_pos + t.window;
+                        d[1].peak_pos = -1;
+                        d[1].peak_value = 1e100;
+                        d[1].valid = false;
+                    }
+                    if (__dsub_rn(t.peak_value, cur) > peak_height && t.peak_value > t.threshold) t.valid = true;
+                    if (t.valid && (i - t.peak_pos) > t.window / 2) {
+                        out[count++] = t.peak_pos;
+                        t.peak_pos = -1;
+                        t.peak_value = cur;
+                        t.valid = false;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    }
+    if (r0 + lane < n_reads) n_events[r0 + lane] = my_n > 0 ? count + 1 : 0;
+}
+
 // K4: events from the edges (filters.py:180-204); one CTA per read; events [*, 4] = start, length, mean, stdv
 __global__ void __launch_bounds__(256) k_ed_events(const double *__restrict__ sums, const double *__restrict__ sumsqs,
                                                    const int32_t *__restrict__ peaks, const int64_t *__restrict__ read_off,

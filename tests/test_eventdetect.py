@@ -113,6 +113,24 @@ def test_gpu_matches_reference_golden(lib, golden, p):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("lanes", ["0", "1"])
+def test_both_kernel_forms_agree_with_the_golden(golden, lanes):
+    """The warp-per-read and lane-per-read forms of the sequential stages (the library picks by read count; the switch is
+    read once per process, hence the subprocess)."""
+    import subprocess
+    import sys
+    code = ("import sys, numpy as np; sys.path[:0] = [%r, %r]; import nanopore_rnn_b200; "
+            "from nanopore_rnn_b200 import eventdetection as E; g = np.load(%r); o = g['read_off']; eo = g['event_off_0']; "
+            "ev = E.minknow_event_detect_batch([g['raw'][a:b] for a, b in zip(o[:-1], o[1:])], 4000.0, [3, 6], [1.4, 1.1], 0.2); "
+            "m = np.concatenate([e['mean'] for e in ev]); s = np.concatenate([e['start'] for e in ev]); "
+            "assert np.array_equal(m, g['events_0'][:, 2]) and np.array_equal(s, g['events_0'][:, 0]); print('ok')"
+            % (ROOT, os.path.join(ROOT, "oracle"), os.path.join(GOLDEN, "event_detect.npz")))
+    out = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, NTB_ED_LANES=lanes), capture_output=True,
+                         text=True, timeout=300)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
+
+
+@pytest.mark.gpu
 def test_gpu_matches_oracle_on_many_ragged_reads(lib):
     rng = np.random.default_rng(9)
     raws = [squiggle(rng, int(n)) for n in rng.integers(1, 6000, 300)] + [squiggle(rng, 150000, dwell=12.0)]
