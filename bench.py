@@ -14,7 +14,8 @@ the data path); ``value`` = valid samples of all ranks / max-over-ranks device t
 One JSON line is printed by rank 0 (keys: see DESIGN.md "Measurement").  ``--impl reference``
 times the CPU restatement of the reference's TensorFlow forward (oracle/oracle_cpu.cpp, C++/OpenMP, all host
 threads) on a bounded sample of the same workload: TensorFlow 1.4 itself is unavailable on the
-box.
+box.  ``--row event_features|assembly|event_detect`` measures one of the rows the path was
+widened into with that row's own metric instead (tools/bench_*.py).
 """
 import argparse
 import json
@@ -28,6 +29,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+ROWS = {"event_features": "bench_events.py", "assembly": "bench_assembly.py", "event_detect": "bench_eventdetect.py"}
 METRIC = "signal samples/sec basecalled (BLSTM fwd)"
 UNIT = "samples/s"
 WORKLOAD = "run_nanotensor.config.json network, synthetic windows"
@@ -49,7 +51,12 @@ def parse():
                     help="windows per forward call (0 = as many as the workspace budget allows)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end (host buffers) leg")
-    return ap.parse_args()
+    ap.add_argument("--row", default="forward", choices=["forward"] + sorted(ROWS),
+                    help="which SURVEY section-8 row to measure: the BLSTM forward (default, the contract's line) or one "
+                         "of the widened rows (f): their own metric, roofline and cpu_baseline, one GPU")
+    args, rest = ap.parse_known_args()
+    args.rest = rest
+    return args
 
 
 def peaks():
@@ -358,8 +365,21 @@ def run_b200(args):
     return 0
 
 
+def run_row(args):
+    """The rows SURVEY section 8(f) widened into (event detection, event features, consensus assembly): each has its own
+    bench under tools/ -- metric, HBM roofline on its algorithmic bytes, and a cpu_baseline leg (the only place they
+    touch oracle/) -- run here so that bench.py stays the one measurement entry point.  Extra flags go through
+    (e.g. ``python bench.py --row event_features --reads 2048 --events 9000``)."""
+    import runpy
+    sys.argv = [os.path.join(ROOT, "tools", ROWS[args.row])] + args.rest
+    runpy.run_path(sys.argv[0], run_name="__main__")
+    return 0
+
+
 def main():
     args = parse()
+    if args.row != "forward":
+        return run_row(args)
     if args.impl == "reference":
         return run_reference(args)
     return run_b200(args)

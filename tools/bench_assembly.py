@@ -4,6 +4,9 @@ GPU: windows/s with the label rows resident in HBM (CUDA events around the five 
 the HBM roofline fraction of its algorithmic bytes (4 T bytes of labels in per window + 1 byte per consensus base out),
 and the difflib host mirror (the calls the reference makes) on one core beside it.  Prints one JSON line.
 
+This is the body of ``python bench.py --row assembly``; the oracle import below is that bench's cpu_baseline leg (the checker
+and the timed CPU arm), never part of the measured path.
+
     python tools/bench_assembly.py [--reads 1024] [--windows 1024] [--iters 10]
 """
 import argparse

@@ -4,6 +4,9 @@ signal resident in HBM (CUDA events around the five launches), through the host 
 of its algorithmic bytes (8 B of raw signal in per sample + 32 B per event out), and the reference's own compiled C
 (oracle/_ref, driven by the NumPy restatement's Python for the peak detector and event table) on one core beside it.
 
+This is the body of ``python bench.py --row event_detect``; the oracle import below is that bench's cpu_baseline leg (the checker
+and the timed CPU arm), never part of the measured path.
+
     python tools/bench_eventdetect.py [--reads 8192] [--samples 50000] [--iters 5]
 """
 import argparse

@@ -4,6 +4,9 @@ events/s device-resident and through the host entry point, the HBM roofline frac
 (24 B in + 12 x sizeof(out) B out per event), and the NumPy restatement (NumPy's own reductions = what the reference
 executes) timed on one host core beside it.  Prints one JSON line per output type.
 
+This is the body of ``python bench.py --row event_features``; the oracle import below is that bench's cpu_baseline leg (the checker
+and the timed CPU arm), never part of the measured path.
+
     python tools/bench_events.py [--reads 2048] [--events 9000] [--iters 10]
 """
 import argparse
