@@ -231,6 +231,21 @@ NTB_API int ntb_event_detect_host(const double *raw_host, const int64_t *read_of
                           const double *thresholds, double peak_height, int64_t capacity,
                           double *events_host, int64_t *event_off_host, void *stream);
 
+/* The text parse of read_signal (chiron/chiron/chiron_input.py:220-226): `.signal` files hold whitespace
+ * separated integers; signal += [int(x) for x in line.split()].  text [total_bytes] = the bytes of n_files
+ * files back to back, file_off_host [n_files+1] byte offsets (HOST pointer; a token never spans two files);
+ * samples [capacity] int16 and read_off [n_files+1] int64 (samples per file, cumulative) are exactly the raw_dev /
+ * read_off_dev inputs of ntb_pack_windows, which does the z-score and the windows.  capacity >= number of
+ * samples (total_bytes / 2 + n_files always suffices).  status_dev: 0 ok, 1 capacity, 2 a token that is not
+ * [+-]?[0-9]{1,6}, 3 a value outside int16.  Synchronises the stream once (chunk table upload). */
+NTB_API int64_t ntb_parse_signal_workspace_bytes(int64_t total_bytes, int64_t n_files);
+NTB_API int ntb_parse_signal(const uint8_t *text_dev, const int64_t *file_off_host, int64_t n_files,
+                     int64_t total_bytes, void *workspace_dev, int64_t workspace_bytes, int64_t capacity,
+                     int16_t *samples_dev, int64_t *read_off_dev, int32_t *status_dev, void *stream);
+NTB_API int ntb_parse_signal_host(const uint8_t *text_host, const int64_t *file_off_host, int64_t n_files,
+                          int64_t total_bytes, int64_t capacity, int16_t *samples_host,
+                          int64_t *read_off_host, void *stream);
+
 /* conv_layer + simple_global_bn (+ReLU) (network.py:312-349): y = conv(in) (k = 1 or 3, SAME,
  * no bias), then per-group batch moments and normalisation.  in_dev [n_windows*T, Cin],
  * filt_dev = TF filter [1,k,Cin,Cout] on the device; scale/offset NULL = no BN.

@@ -55,6 +55,9 @@ SIGNATURES = {
     "ntb_event_detect_workspace_bytes": (_I64, [_I64, _I64]),
     "ntb_event_detect": (C.c_int, [_P, _P, _I64, _I64, C.c_double, _P, _P, C.c_double, _P, _I64, _I64, _P, _P, _P, _P]),
     "ntb_event_detect_host": (C.c_int, [_P, _P, _I64, _I64, C.c_double, _P, _P, C.c_double, _I64, _P, _P, _P]),
+    "ntb_parse_signal_workspace_bytes": (_I64, [_I64, _I64]),
+    "ntb_parse_signal": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _I64, _P, _P, _P, _P]),
+    "ntb_parse_signal_host": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P, _P]),
     "ntb_conv_bn": (C.c_int, [_P, _P, _P, _P, _P, _I64, _I64, _I32, _I32, _I32, _I32, _I32, _P, _I64, _P, _P]),
     "ntb_conv_bn_workspace_bytes": (_I64, [_I64, _I64, _I32, _I32, _I32, _I32]),
     "ntb_blstm": (C.c_int, [_P, _P, _P, _P, _P, _P, _F, _I64, _I32, _I32, _I32, _P, _I64, _P, _P]),

@@ -8,6 +8,7 @@
 #include "ntb_common.cuh"
 #include "ntb_assembly.cuh"
 #include "ntb_eventdetect.cuh"
+#include "ntb_parse.cuh"
 #include "ntb_events.cuh"
 #include "ntb_gemm_tc.cuh"
 #include "ntb_kernels.cuh"
@@ -1200,6 +1201,118 @@ extern "C" int ntb_event_detect_host(const double *raw_host, const int64_t *read
     if (e != cudaSuccess) return fail(NTB_ECUDA, "ntb_event_detect_host: %s", cudaGetErrorString(e));
     if (rc != NTB_OK) return rc;
     if (status_h) return fail(NTB_ENOMEM, "ntb_event_detect: capacity smaller than the number of events%s", "");
+    return NTB_OK;
+}
+
+// ---- .signal text parse (chiron/chiron/chiron_input.py:220-226; kernels in ntb_parse.cuh) ----
+namespace ntb {
+struct ParseBufs {
+    int64_t *file_off, *first_chunk, *chunk_lo, *counts, *chunk_out, *tmp;
+    int32_t *chunk_file;
+};
+static ParseBufs parse_carve(Arena &ar, int64_t n_files, int64_t max_chunks) {
+    ParseBufs b;
+    b.file_off = ar.take<int64_t>(n_files + 1);
+    b.first_chunk = ar.take<int64_t>(n_files + 1);
+    b.chunk_lo = ar.take<int64_t>(max_chunks);
+    b.counts = ar.take<int64_t>(max_chunks);
+    b.chunk_out = ar.take<int64_t>(max_chunks + 1);
+    b.tmp = ar.take<int64_t>(max_chunks + 1);
+    b.chunk_file = ar.take<int32_t>(max_chunks);
+    return b;
+}
+static int64_t parse_max_chunks(int64_t total_bytes, int64_t n_files) { return total_bytes / PARSE_CHUNK + n_files + 1; }
+}  // namespace ntb
+
+extern "C" int64_t ntb_parse_signal_workspace_bytes(int64_t total_bytes, int64_t n_files) {
+    if (total_bytes < 0 || n_files < 0) return 0;
+    Arena ar(nullptr, 0);
+    parse_carve(ar, n_files, parse_max_chunks(total_bytes, n_files));
+    return ar.off;
+}
+
+extern "C" int ntb_parse_signal(const uint8_t *text_dev, const int64_t *file_off_host, int64_t n_files, int64_t total_bytes,
+                                void *workspace_dev, int64_t workspace_bytes, int64_t capacity, int16_t *samples_dev,
+                                int64_t *read_off_dev, int32_t *status_dev, void *stream) {
+    if (!file_off_host || !read_off_dev || !status_dev || n_files < 0 || total_bytes < 0 || capacity < 0 ||
+        (total_bytes > 0 && !text_dev) || (capacity > 0 && !samples_dev))
+        return fail(NTB_EINVAL, "ntb_parse_signal: bad argument%s", "");
+    if (file_off_host[0] != 0 || file_off_host[n_files] != total_bytes)
+        return fail(NTB_EINVAL, "ntb_parse_signal: file_off must run from 0 to total_bytes%s", "");
+    std::vector<int64_t> chunk_lo, first_chunk((size_t)n_files + 1);
+    std::vector<int32_t> chunk_file;
+    for (int64_t f = 0; f < n_files; ++f) {
+        if (file_off_host[f + 1] < file_off_host[f])
+            return fail(NTB_EINVAL, "ntb_parse_signal: file_off not monotonic at file %s%lld", "", (long long)f);
+        first_chunk[f] = (int64_t)chunk_lo.size();
+        for (int64_t b = file_off_host[f]; b < file_off_host[f + 1]; b += PARSE_CHUNK) {
+            chunk_lo.push_back(b);
+            chunk_file.push_back((int32_t)f);
+        }
+    }
+    const int64_t n_chunks = (int64_t)chunk_lo.size();
+    first_chunk[n_files] = n_chunks;
+    NTB_TRY(check_device());
+    Arena ar(workspace_dev, workspace_bytes);
+    ParseBufs b = parse_carve(ar, n_files, parse_max_chunks(total_bytes, n_files));
+    if (!workspace_dev || !ar.ok())
+        return fail(NTB_ENOMEM, "ntb_parse_signal: workspace too small (need %s%lld)", "", (long long)ar.off);
+    cudaStream_t st = (cudaStream_t)stream;
+    NTB_CUDA(cudaMemsetAsync(status_dev, 0, sizeof(int32_t), st));
+    NTB_CUDA(cudaMemsetAsync(read_off_dev, 0, sizeof(int64_t) * (n_files + 1), st));
+    if (n_chunks == 0) return NTB_OK;
+    // the tables are small (16 + 4 bytes per 4 KiB of text); pageable copies complete before the vectors go away
+    NTB_CUDA(cudaMemcpyAsync(b.file_off, file_off_host, sizeof(int64_t) * (n_files + 1), cudaMemcpyHostToDevice, st));
+    NTB_CUDA(cudaMemcpyAsync(b.first_chunk, first_chunk.data(), sizeof(int64_t) * (n_files + 1), cudaMemcpyHostToDevice, st));
+    NTB_CUDA(cudaMemcpyAsync(b.chunk_lo, chunk_lo.data(), sizeof(int64_t) * n_chunks, cudaMemcpyHostToDevice, st));
+    NTB_CUDA(cudaMemcpyAsync(b.chunk_file, chunk_file.data(), sizeof(int32_t) * n_chunks, cudaMemcpyHostToDevice, st));
+    NTB_CUDA(cudaStreamSynchronize(st));
+    k_parse_count<<<(unsigned)n_chunks, PARSE_THREADS, 0, st>>>(text_dev, b.chunk_lo, b.chunk_file, b.file_off, b.counts);
+    k_asm_read_offsets<<<1, 1024, 0, st>>>(b.counts, b.counts, n_chunks, capacity, b.tmp, b.chunk_out, status_dev);
+    k_parse_emit<<<(unsigned)n_chunks, PARSE_THREADS, 0, st>>>(text_dev, b.chunk_lo, b.chunk_file, b.file_off, b.chunk_out,
+                                                               capacity, samples_dev, status_dev);
+    k_parse_read_off<<<(unsigned)cdiv(n_files + 1, 256), 256, 0, st>>>(b.chunk_out, b.first_chunk, n_files, read_off_dev);
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+extern "C" int ntb_parse_signal_host(const uint8_t *text_host, const int64_t *file_off_host, int64_t n_files,
+                                     int64_t total_bytes, int64_t capacity, int16_t *samples_host, int64_t *read_off_host,
+                                     void *stream) {
+    if (!file_off_host || !read_off_host || n_files < 0 || total_bytes < 0 || capacity < 0 || (total_bytes > 0 && !text_host) ||
+        (capacity > 0 && !samples_host))
+        return fail(NTB_EINVAL, "ntb_parse_signal_host: bad argument%s", "");
+    NTB_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t ws_b = ntb_parse_signal_workspace_bytes(total_bytes, n_files);
+    const int64_t txt_b = align_up(total_bytes, 256), smp_b = align_up((int64_t)sizeof(int16_t) * capacity, 256);
+    const int64_t off_b = align_up((int64_t)sizeof(int64_t) * (n_files + 1), 256);
+    char *buf = nullptr;
+    NTB_CUDA(cudaMallocAsync((void **)&buf, ws_b + txt_b + smp_b + off_b + 256, st));
+    uint8_t *text = (uint8_t *)(buf + ws_b);
+    int16_t *samples = (int16_t *)(buf + ws_b + txt_b);
+    int64_t *read_off = (int64_t *)(buf + ws_b + txt_b + smp_b);
+    int32_t *status = (int32_t *)(buf + ws_b + txt_b + smp_b + off_b);
+    int rc = NTB_OK;
+    int32_t status_h = 0;
+    cudaError_t e = cudaMemcpyAsync(text, text_host, (size_t)total_bytes, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess)
+        rc = ntb_parse_signal(text, file_off_host, n_files, total_bytes, buf, ws_b, capacity, samples, read_off, status, st);
+    if (e == cudaSuccess && rc == NTB_OK) {
+        e = cudaMemcpyAsync(read_off_host, read_off, sizeof(int64_t) * (n_files + 1), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&status_h, status, sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e == cudaSuccess && status_h == 0) {
+            e = cudaMemcpyAsync(samples_host, samples, sizeof(int16_t) * read_off_host[n_files], cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        }
+    }
+    cudaFreeAsync(buf, st);
+    if (e != cudaSuccess) return fail(NTB_ECUDA, "ntb_parse_signal_host: %s", cudaGetErrorString(e));
+    if (rc != NTB_OK) return rc;
+    if (status_h == PARSE_STATUS_CAPACITY) return fail(NTB_ENOMEM, "ntb_parse_signal: capacity smaller than the number of samples%s", "");
+    if (status_h == PARSE_STATUS_BADCHAR) return fail(NTB_EINVAL, "ntb_parse_signal: a token is not [+-]?[0-9]{1,6}%s", "");
+    if (status_h == PARSE_STATUS_RANGE) return fail(NTB_EINVAL, "ntb_parse_signal: a sample does not fit int16%s", "");
     return NTB_OK;
 }
 

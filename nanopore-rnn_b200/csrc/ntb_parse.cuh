@@ -1,0 +1,117 @@
+// `.signal` text -> int16 samples on the device -- SURVEY.md section 8(f) rank 2 (read ingestion).
+//
+// Replaces the parse in read_signal (chiron/chiron/chiron_input.py:220-226): for every line, int(x) for x in
+// line.split().  The bytes of many files are concatenated; every file is cut into fixed chunks (table built on the
+// host), a CTA owns one chunk: pass 1 counts the tokens that START in the chunk, a scan turns the counts into output
+// offsets, pass 2 re-finds the starts, ranks them with a block scan and parses each token (a token may run past its
+// chunk, never past its file).  Byte work, HBM-bound: the text is read twice, two bytes per sample are written.
+// Accepted tokens: [+-]?[0-9]{1,6} (what a .signal file holds); anything else int() would also take (underscores,
+// other Unicode digits) or reject raises status 2; a value outside int16 raises status 3.  Output feeds
+// ntb_pack_windows directly (samples + per-read offsets).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace ntb {
+
+constexpr int PARSE_CHUNK = 4096, PARSE_THREADS = 256, PARSE_PER_THREAD = PARSE_CHUNK / PARSE_THREADS;
+constexpr int PARSE_STATUS_CAPACITY = 1, PARSE_STATUS_BADCHAR = 2, PARSE_STATUS_RANGE = 3;
+
+__device__ __forceinline__ bool parse_is_ws(uint8_t c) {       // str.split() whitespace in ASCII
+    return c == ' ' || (c >= 9 && c <= 13) || (c >= 28 && c <= 31);
+}
+
+// token starts among this thread's bytes [p, p + PARSE_PER_THREAD) of a chunk [lo, hi) of a file that begins at f_lo
+__device__ __forceinline__ int parse_count_starts(const uint8_t *__restrict__ text, int64_t p, int64_t hi, int64_t f_lo,
+                                                  unsigned *mask) {
+    unsigned m = 0;
+    uint8_t prev = p > f_lo ? text[p - 1] : (uint8_t)' ';
+#pragma unroll
+    for (int k = 0; k < PARSE_PER_THREAD; ++k) {
+        const uint8_t c = p + k < hi ? text[p + k] : (uint8_t)' ';
+        if (!parse_is_ws(c) && parse_is_ws(prev)) m |= 1u << k;
+        prev = c;
+    }
+    *mask = m;
+    return __popc(m);
+}
+
+// chunk table: chunk c covers bytes [chunk_lo[c], chunk_lo[c] + PARSE_CHUNK) clipped to its file [file_lo, file_hi)
+__global__ void __launch_bounds__(PARSE_THREADS) k_parse_count(const uint8_t *__restrict__ text,
+                                                               const int64_t *__restrict__ chunk_lo,
+                                                               const int32_t *__restrict__ chunk_file,
+                                                               const int64_t *__restrict__ file_off,
+                                                               int64_t *__restrict__ counts) {
+    __shared__ int warp_n[PARSE_THREADS / 32];
+    const int c = blockIdx.x, f = chunk_file[c];
+    const int64_t lo = chunk_lo[c], hi = min(lo + PARSE_CHUNK, file_off[f + 1]);
+    unsigned mask;
+    int n = parse_count_starts(text, lo + (int64_t)threadIdx.x * PARSE_PER_THREAD, hi, file_off[f], &mask);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+    if ((threadIdx.x & 31) == 0) warp_n[threadIdx.x >> 5] = n;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int q = 0; q < PARSE_THREADS / 32; ++q) t += warp_n[q];
+        counts[c] = t;
+    }
+}
+
+__global__ void __launch_bounds__(PARSE_THREADS) k_parse_emit(const uint8_t *__restrict__ text,
+                                                              const int64_t *__restrict__ chunk_lo,
+                                                              const int32_t *__restrict__ chunk_file,
+                                                              const int64_t *__restrict__ file_off,
+                                                              const int64_t *__restrict__ chunk_out, int64_t capacity,
+                                                              int16_t *__restrict__ samples, int32_t *status) {
+    __shared__ int warp_n[PARSE_THREADS / 32];
+    const int c = blockIdx.x, f = chunk_file[c], lane = threadIdx.x & 31, wi = threadIdx.x >> 5;
+    const int64_t f_hi = file_off[f + 1];
+    const int64_t lo = chunk_lo[c], hi = min(lo + PARSE_CHUNK, f_hi);
+    const int64_t p = lo + (int64_t)threadIdx.x * PARSE_PER_THREAD;
+    unsigned mask;
+    const int n = parse_count_starts(text, p, hi, file_off[f], &mask);
+    int incl = n;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += up;
+    }
+    if (lane == 31) warp_n[wi] = incl;
+    __syncthreads();
+    int before = incl - n;
+    for (int q = 0; q < wi; ++q) before += warp_n[q];
+    int64_t out = chunk_out[c] + before;
+    while (mask) {
+        const int k = __ffs(mask) - 1;
+        mask &= mask - 1;
+        int64_t i = p + k;
+        uint8_t ch = text[i];
+        const bool neg = ch == '-';
+        if (ch == '-' || ch == '+') ch = ++i < f_hi ? text[i] : (uint8_t)' ';
+        int v = 0, digits = 0;
+        bool bad = false;
+        while (!parse_is_ws(ch)) {
+            if (ch < '0' || ch > '9' || digits >= 6) { bad = true; break; }
+            v = v * 10 + (ch - '0');
+            ++digits;
+            ch = ++i < f_hi ? text[i] : (uint8_t)' ';
+        }
+        if (bad || digits == 0) atomicMax(status, PARSE_STATUS_BADCHAR);
+        else {
+            v = neg ? -v : v;
+            if (v < -32768 || v > 32767) atomicMax(status, PARSE_STATUS_RANGE);
+            else if (out < capacity) samples[out] = (int16_t)v;
+        }
+        ++out;
+    }
+}
+
+// samples per file from the scanned chunk offsets: read_off[f] = chunk_out[first chunk of f]
+__global__ void k_parse_read_off(const int64_t *__restrict__ chunk_out, const int64_t *__restrict__ first_chunk,
+                                 int64_t n_files, int64_t *__restrict__ read_off) {
+    const int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (f <= n_files) read_off[f] = chunk_out[first_chunk[f]];
+}
+
+}  // namespace ntb
