@@ -14,7 +14,7 @@ the data path); ``value`` = valid samples of all ranks / max-over-ranks device t
 One JSON line is printed by rank 0 (keys: see DESIGN.md "Measurement").  ``--impl reference``
 times the CPU restatement of the reference's TensorFlow forward (oracle/oracle_cpu.cpp, C++/OpenMP, all host
 threads) on a bounded sample of the same workload: TensorFlow 1.4 itself is unavailable on the
-box.  ``--row event_features|assembly|event_detect`` measures one of the rows the path was
+box.  ``--row event_features|assembly|event_detect|signal_parse`` measures one of the rows the path was
 widened into with that row's own metric instead (tools/bench_*.py).
 """
 import argparse
@@ -29,7 +29,8 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-ROWS = {"event_features": "bench_events.py", "assembly": "bench_assembly.py", "event_detect": "bench_eventdetect.py"}
+ROWS = {"event_features": "bench_events.py", "assembly": "bench_assembly.py", "event_detect": "bench_eventdetect.py",
+        "signal_parse": "bench_parse.py"}
 METRIC = "signal samples/sec basecalled (BLSTM fwd)"
 UNIT = "samples/s"
 WORKLOAD = "run_nanotensor.config.json network, synthetic windows"

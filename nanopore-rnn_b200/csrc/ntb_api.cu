@@ -1239,6 +1239,7 @@ extern "C" int ntb_parse_signal(const uint8_t *text_dev, const int64_t *file_off
         return fail(NTB_EINVAL, "ntb_parse_signal: bad argument%s", "");
     if (file_off_host[0] != 0 || file_off_host[n_files] != total_bytes)
         return fail(NTB_EINVAL, "ntb_parse_signal: file_off must run from 0 to total_bytes%s", "");
+    if ((uintptr_t)text_dev & 15) return fail(NTB_EINVAL, "ntb_parse_signal: text_dev must be 16-byte aligned%s", "");
     std::vector<int64_t> chunk_lo, first_chunk((size_t)n_files + 1);
     std::vector<int32_t> chunk_file;
     for (int64_t f = 0; f < n_files; ++f) {
@@ -1267,9 +1268,9 @@ extern "C" int ntb_parse_signal(const uint8_t *text_dev, const int64_t *file_off
     NTB_CUDA(cudaMemcpyAsync(b.chunk_lo, chunk_lo.data(), sizeof(int64_t) * n_chunks, cudaMemcpyHostToDevice, st));
     NTB_CUDA(cudaMemcpyAsync(b.chunk_file, chunk_file.data(), sizeof(int32_t) * n_chunks, cudaMemcpyHostToDevice, st));
     NTB_CUDA(cudaStreamSynchronize(st));
-    k_parse_count<<<(unsigned)n_chunks, PARSE_THREADS, 0, st>>>(text_dev, b.chunk_lo, b.chunk_file, b.file_off, b.counts);
+    k_parse_count<<<(unsigned)n_chunks, PARSE_THREADS, 0, st>>>(text_dev, b.chunk_lo, b.chunk_file, b.file_off, total_bytes, b.counts);
     k_asm_read_offsets<<<1, 1024, 0, st>>>(b.counts, b.counts, n_chunks, capacity, b.tmp, b.chunk_out, status_dev);
-    k_parse_emit<<<(unsigned)n_chunks, PARSE_THREADS, 0, st>>>(text_dev, b.chunk_lo, b.chunk_file, b.file_off, b.chunk_out,
+    k_parse_emit<<<(unsigned)n_chunks, PARSE_THREADS, 0, st>>>(text_dev, b.chunk_lo, b.chunk_file, b.file_off, total_bytes, b.chunk_out,
                                                                capacity, samples_dev, status_dev);
     k_parse_read_off<<<(unsigned)cdiv(n_files + 1, 256), 256, 0, st>>>(b.chunk_out, b.first_chunk, n_files, read_off_dev);
     NTB_LAUNCH_CHECK();

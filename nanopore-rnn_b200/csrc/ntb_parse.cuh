@@ -21,16 +21,30 @@ __device__ __forceinline__ bool parse_is_ws(uint8_t c) {       // str.split() wh
     return c == ' ' || (c >= 9 && c <= 13) || (c >= 28 && c <= 31);
 }
 
-// token starts among this thread's bytes [p, p + PARSE_PER_THREAD) of a chunk [lo, hi) of a file that begins at f_lo
-__device__ __forceinline__ int parse_count_starts(const uint8_t *__restrict__ text, int64_t p, int64_t hi, int64_t f_lo,
-                                                  unsigned *mask) {
+// Stage the chunk [lo, hi) plus the byte before it into shared memory with 16-byte loads: sh[1 + k] = text[lo + k],
+// sh[0] = the byte before the chunk (a space at the start of the file).  text is 16-byte aligned (checked by the API).
+__device__ __forceinline__ void parse_stage(const uint8_t *__restrict__ text, int64_t total, int64_t lo, int64_t hi,
+                                            int64_t f_lo, uint8_t *sh /* [16 + PARSE_CHUNK + 16] */) {
+    const int64_t a_lo = lo & ~(int64_t)15;                    // aligned start, <= lo
+    const int shift = (int)(lo - a_lo);                        // sh_raw[shift + k] = text[lo + k]
+    uint8_t *raw = sh + 16;                                    // raw[j] = text[a_lo + j]; 16 bytes of headroom in front
+    for (int64_t j = (int64_t)threadIdx.x * 16; a_lo + j < hi; j += (int64_t)PARSE_THREADS * 16) {
+        if (a_lo + j + 16 <= total) *reinterpret_cast<uint4 *>(raw + j) = *reinterpret_cast<const uint4 *>(text + a_lo + j);
+        else for (int q = 0; q < 16 && a_lo + j + q < total; ++q) raw[j + q] = text[a_lo + j + q];
+    }
+    if (threadIdx.x == 0) raw[shift - 1] = lo > f_lo ? text[lo - 1] : (uint8_t)' ';
+    __syncthreads();
+}
+
+// token starts among this thread's bytes [k0, k0 + PARSE_PER_THREAD) of the staged chunk of n bytes; c[-1] is valid
+__device__ __forceinline__ int parse_count_starts(const uint8_t *c, int k0, int n, unsigned *mask) {
     unsigned m = 0;
-    uint8_t prev = p > f_lo ? text[p - 1] : (uint8_t)' ';
+    uint8_t prev = c[k0 - 1];
 #pragma unroll
     for (int k = 0; k < PARSE_PER_THREAD; ++k) {
-        const uint8_t c = p + k < hi ? text[p + k] : (uint8_t)' ';
-        if (!parse_is_ws(c) && parse_is_ws(prev)) m |= 1u << k;
-        prev = c;
+        const uint8_t ch = k0 + k < n ? c[k0 + k] : (uint8_t)' ';
+        if (!parse_is_ws(ch) && parse_is_ws(prev)) m |= 1u << k;
+        prev = ch;
     }
     *mask = m;
     return __popc(m);
@@ -40,13 +54,15 @@ __device__ __forceinline__ int parse_count_starts(const uint8_t *__restrict__ te
 __global__ void __launch_bounds__(PARSE_THREADS) k_parse_count(const uint8_t *__restrict__ text,
                                                                const int64_t *__restrict__ chunk_lo,
                                                                const int32_t *__restrict__ chunk_file,
-                                                               const int64_t *__restrict__ file_off,
+                                                               const int64_t *__restrict__ file_off, int64_t total,
                                                                int64_t *__restrict__ counts) {
     __shared__ int warp_n[PARSE_THREADS / 32];
+    __shared__ __align__(16) uint8_t sh[16 + PARSE_CHUNK + 32];
     const int c = blockIdx.x, f = chunk_file[c];
     const int64_t lo = chunk_lo[c], hi = min(lo + PARSE_CHUNK, file_off[f + 1]);
+    parse_stage(text, total, lo, hi, file_off[f], sh);
     unsigned mask;
-    int n = parse_count_starts(text, lo + (int64_t)threadIdx.x * PARSE_PER_THREAD, hi, file_off[f], &mask);
+    int n = parse_count_starts(sh + 16 + (int)(lo & 15), threadIdx.x * PARSE_PER_THREAD, (int)(hi - lo), &mask);
 #pragma unroll
     for (int o = 16; o; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
     if ((threadIdx.x & 31) == 0) warp_n[threadIdx.x >> 5] = n;
@@ -61,16 +77,19 @@ __global__ void __launch_bounds__(PARSE_THREADS) k_parse_count(const uint8_t *__
 __global__ void __launch_bounds__(PARSE_THREADS) k_parse_emit(const uint8_t *__restrict__ text,
                                                               const int64_t *__restrict__ chunk_lo,
                                                               const int32_t *__restrict__ chunk_file,
-                                                              const int64_t *__restrict__ file_off,
+                                                              const int64_t *__restrict__ file_off, int64_t total,
                                                               const int64_t *__restrict__ chunk_out, int64_t capacity,
                                                               int16_t *__restrict__ samples, int32_t *status) {
     __shared__ int warp_n[PARSE_THREADS / 32];
+    __shared__ __align__(16) uint8_t sh[16 + PARSE_CHUNK + 32];
     const int c = blockIdx.x, f = chunk_file[c], lane = threadIdx.x & 31, wi = threadIdx.x >> 5;
     const int64_t f_hi = file_off[f + 1];
     const int64_t lo = chunk_lo[c], hi = min(lo + PARSE_CHUNK, f_hi);
     const int64_t p = lo + (int64_t)threadIdx.x * PARSE_PER_THREAD;
+    parse_stage(text, total, lo, hi, file_off[f], sh);
+    const uint8_t *cs = sh + 16 + (int)(lo & 15);              // cs[k] = text[lo + k] for k < hi - lo
     unsigned mask;
-    const int n = parse_count_starts(text, p, hi, file_off[f], &mask);
+    const int n = parse_count_starts(cs, threadIdx.x * PARSE_PER_THREAD, (int)(hi - lo), &mask);
     int incl = n;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -86,16 +105,17 @@ __global__ void __launch_bounds__(PARSE_THREADS) k_parse_emit(const uint8_t *__r
         const int k = __ffs(mask) - 1;
         mask &= mask - 1;
         int64_t i = p + k;
-        uint8_t ch = text[i];
+        auto at = [&](int64_t q) -> uint8_t { return q < hi ? cs[q - lo] : (q < f_hi ? text[q] : (uint8_t)' '); };
+        uint8_t ch = at(i);
         const bool neg = ch == '-';
-        if (ch == '-' || ch == '+') ch = ++i < f_hi ? text[i] : (uint8_t)' ';
+        if (ch == '-' || ch == '+') ch = at(++i);
         int v = 0, digits = 0;
         bool bad = false;
         while (!parse_is_ws(ch)) {
             if (ch < '0' || ch > '9' || digits >= 6) { bad = true; break; }
             v = v * 10 + (ch - '0');
             ++digits;
-            ch = ++i < f_hi ? text[i] : (uint8_t)' ';
+            ch = at(++i);
         }
         if (bad || digits == 0) atomicMax(status, PARSE_STATUS_BADCHAR);
         else {
