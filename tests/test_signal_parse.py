@@ -89,3 +89,45 @@ def test_gpu_rejects_what_the_grammar_excludes(lib):
     assert rc == 0 and len(samples) == 0
     rc, samples, off = _parse(lib, b"7 8", [0, 1, 1, 3])          # a token never spans two files: "7", "", "8"
     assert rc == 0 and list(samples) == [7, 8] and list(off) == [0, 1, 1, 2]
+
+
+@pytest.mark.gpu
+def test_file_bytes_to_model_input_on_the_device(lib, tmp_path):
+    """Rank 2 chained into row a9 without leaving the GPU: file bytes -> ntb_parse_signal -> ntb_pack_windows (z-score +
+    windows) against the host route FullSignalSequence.load_file_windows (read_signal + windows): window lengths
+    identical, samples within the float32 z-score tolerance of the packer's own parity test (2e-6)."""
+    import torch
+    rng = np.random.default_rng(12)
+    T, step = 100, 100
+    paths, blobs = [], []
+    for f in range(5):
+        vals = rng.integers(350, 800, int(rng.integers(150, 4000)))
+        p = tmp_path / ("r%d.signal" % f)
+        p.write_text(" ".join(map(str, vals)) + "\n")
+        paths.append(str(p))
+        blobs.append(p.read_bytes())
+    file_off = np.concatenate([[0], np.cumsum([len(b) for b in blobs])]).astype(np.int64)
+    total = int(file_off[-1])
+    text = torch.as_tensor(np.frombuffer(b"".join(blobs), dtype=np.uint8).copy()).cuda()
+    cap = total // 2 + len(paths) + 1
+    ws = torch.empty(lib.ntb_parse_signal_workspace_bytes(total, len(paths)), dtype=torch.uint8, device="cuda")
+    samples = torch.empty(cap, dtype=torch.int16, device="cuda")
+    read_off = torch.empty(len(paths) + 1, dtype=torch.int64, device="cuda")
+    status = torch.zeros(1, dtype=torch.int32, device="cuda")
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _lib.check(lib.ntb_parse_signal(text.data_ptr(), file_off.ctypes.data, len(paths), total, ws.data_ptr(), ws.numel(), cap,
+                                    samples.data_ptr(), read_off.data_ptr(), status.data_ptr(), st))
+    ro = read_off.cpu().numpy()                                   # the host sizes the window table (as for any job)
+    assert int(status[0]) == 0
+    counts = [-(-int(n) // step) for n in np.diff(ro)]
+    win_off = torch.as_tensor(np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)).cuda()
+    n_win = int(sum(counts))
+    x = torch.empty((n_win, T), dtype=torch.float32, device="cuda")
+    ln = torch.empty(n_win, dtype=torch.int32, device="cuda")
+    _lib.check(lib.ntb_pack_windows(samples.data_ptr(), read_off.data_ptr(), win_off.data_ptr(), len(paths), n_win, T, step, 0,
+                                    x.data_ptr(), ln.data_ptr(), st))
+    torch.cuda.synchronize()
+    ds = dataset.FullSignalSequence(paths, mode=2, batch_size=10, seq_len=T, step=step, verbose=False)
+    xs, ls = zip(*(ds.load_file_windows(p) for p in paths))
+    assert np.array_equal(ln.cpu().numpy(), np.concatenate(ls))
+    np.testing.assert_allclose(x.cpu().numpy(), np.concatenate(xs), atol=2e-6, rtol=0)
