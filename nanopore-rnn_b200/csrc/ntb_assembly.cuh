@@ -153,32 +153,46 @@ __global__ void __launch_bounds__(256) k_asm_scan(const int32_t *__restrict__ di
     }
 }
 
-// exclusive prefix sums over the reads (one CTA): bound -> bound_off, len -> cons_off; flags a capacity overflow
+// exclusive prefix sums over the reads (one CTA): bound -> bound_off, len -> cons_off; flags a capacity overflow.
+// Each thread scans SCAN_PER consecutive entries serially, the per-thread totals are scanned across the block
+// (warp shuffles + one shared-memory hop), 8192 entries per trip.  Also used by the event-detection and parse rows.
+constexpr int SCAN_PER = 8;
 __global__ void __launch_bounds__(1024) k_asm_read_offsets(const int64_t *__restrict__ bound, const int64_t *__restrict__ len,
                                                            int64_t n_reads, int64_t capacity, int64_t *__restrict__ bound_off,
                                                            int64_t *__restrict__ cons_off, int32_t *status) {
-    __shared__ long long sb[1024], sl[1024];
+    __shared__ long long wb[32], wl[32];
     __shared__ long long cb, cl;
+    const int lane = threadIdx.x & 31, wi = threadIdx.x >> 5;
     if (threadIdx.x == 0) { cb = 0; cl = 0; }
     __syncthreads();
-    for (int64_t base = 0; base < n_reads; base += 1024) {
-        const int64_t r = base + threadIdx.x;
-        sb[threadIdx.x] = r < n_reads ? bound[r] : 0;
-        sl[threadIdx.x] = r < n_reads ? len[r] : 0;
-        __syncthreads();
-        for (int o = 1; o < 1024; o <<= 1) {
-            const long long ub = threadIdx.x >= o ? sb[threadIdx.x - o] : 0, ul = threadIdx.x >= o ? sl[threadIdx.x - o] : 0;
-            __syncthreads();
-            sb[threadIdx.x] += ub;
-            sl[threadIdx.x] += ul;
-            __syncthreads();
+    for (int64_t base = 0; base < n_reads; base += 1024 * SCAN_PER) {
+        const int64_t r0 = base + (int64_t)threadIdx.x * SCAN_PER;
+        long long vb[SCAN_PER], vl[SCAN_PER], tb = 0, tl = 0;
+#pragma unroll
+        for (int k = 0; k < SCAN_PER; ++k) {
+            vb[k] = r0 + k < n_reads ? bound[r0 + k] : 0;
+            vl[k] = r0 + k < n_reads ? len[r0 + k] : 0;
+            tb += vb[k];
+            tl += vl[k];
         }
-        if (r < n_reads) {
-            bound_off[r] = cb + sb[threadIdx.x] - bound[r];
-            cons_off[r] = cl + sl[threadIdx.x] - len[r];
+        long long ib = tb, il = tl;                       // inclusive scan of the per-thread totals
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const long long ub = __shfl_up_sync(0xffffffffu, ib, o), ul = __shfl_up_sync(0xffffffffu, il, o);
+            if (lane >= o) { ib += ub; il += ul; }
+        }
+        if (lane == 31) { wb[wi] = ib; wl[wi] = il; }
+        __syncthreads();
+        long long pb = cb + ib - tb, pl = cl + il - tl;   // exclusive prefix of this thread's first entry
+        for (int q = 0; q < wi; ++q) { pb += wb[q]; pl += wl[q]; }
+#pragma unroll
+        for (int k = 0; k < SCAN_PER; ++k) {
+            if (r0 + k < n_reads) { bound_off[r0 + k] = pb; cons_off[r0 + k] = pl; }
+            pb += vb[k];
+            pl += vl[k];
         }
         __syncthreads();
-        if (threadIdx.x == 1023) { cb += sb[1023]; cl += sl[1023]; }
+        if (threadIdx.x == 1023) { cb = pb; cl = pl; }
         __syncthreads();
     }
     if (threadIdx.x == 0) {

@@ -110,6 +110,6 @@ def events_to_features(mean, stdv, length, window=(-1, 0, 1)):
 
 def events_to_features_reads(mean, stdv, length, read_off, window=(-1, 0, 1)):
     """Concatenated reads (the C ABI's layout): read r is events read_off[r]:read_off[r+1]."""
-    outs = [events_to_features(mean[a:b], stdv[a:b], length[a:b], window)
-            for a, b in zip(read_off[:-1], read_off[1:])]
+    outs = [events_to_features(mean[a:b], stdv[a:b], length[a:b], window) if b > a else np.zeros((0, 4 * len(window)))
+            for a, b in zip(read_off[:-1], read_off[1:])]      # (the reference divides by zero on an empty table)
     return np.concatenate(outs) if outs else np.zeros((0, 4 * len(window)))
