@@ -1049,23 +1049,21 @@ extern "C" int ntb_assemble_reads_host(const int32_t *labels_host, const int64_t
     int64_t *cons_off = (int64_t *)(buf + ws_b + lab_b + cons_b);
     int32_t *counts = (int32_t *)(buf + ws_b + lab_b + cons_b + off_b);
     int32_t *status = (int32_t *)(buf + ws_b + lab_b + cons_b + off_b + cnt_b);
-    auto at = [](void *p) { return p; };   // (device pointers inside buf)
     int rc = NTB_OK;
-    cudaError_t e = cudaMemcpyAsync(at(labels), labels_host, sizeof(int32_t) * n_windows * T, cudaMemcpyHostToDevice, st);
+    cudaError_t e = cudaMemcpyAsync(labels, labels_host, sizeof(int32_t) * n_windows * T, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess)
-        rc = ntb_assemble_reads((const int32_t *)at(labels), read_off_host, n_reads, n_windows, T, capacity, buf, ws_b,
-                                (uint8_t *)at(cons), (int64_t *)at(cons_off), counts_host ? (int32_t *)at(counts) : nullptr,
-                                (int32_t *)at(status), st);
+        rc = ntb_assemble_reads(labels, read_off_host, n_reads, n_windows, T, capacity, buf, ws_b, cons, cons_off,
+                                counts_host ? counts : nullptr, status, st);
     int32_t status_h = 0;
     if (e == cudaSuccess && rc == NTB_OK) {
-        e = cudaMemcpyAsync(cons_off_host, at(cons_off), sizeof(int64_t) * (n_reads + 1), cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(&status_h, at(status), sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+        e = cudaMemcpyAsync(cons_off_host, cons_off, sizeof(int64_t) * (n_reads + 1), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&status_h, status, sizeof(int32_t), cudaMemcpyDeviceToHost, st);
         if (e == cudaSuccess) e = cudaStreamSynchronize(st);
         if (e == cudaSuccess && status_h == 0) {
             const int64_t total = cons_off_host[n_reads];
-            e = cudaMemcpyAsync(cons_host, at(cons), (size_t)total, cudaMemcpyDeviceToHost, st);
+            e = cudaMemcpyAsync(cons_host, cons, (size_t)total, cudaMemcpyDeviceToHost, st);
             for (int c = 0; counts_host && c < 5 && e == cudaSuccess; ++c)     // compact [5, total] like the reference's matrix
-                e = cudaMemcpyAsync(counts_host + c * total, (int32_t *)at(counts) + c * capacity, sizeof(int32_t) * total,
+                e = cudaMemcpyAsync(counts_host + c * total, counts + c * capacity, sizeof(int32_t) * total,
                                     cudaMemcpyDeviceToHost, st);
             if (e == cudaSuccess) e = cudaStreamSynchronize(st);
         }
