@@ -135,6 +135,22 @@ class ClockSampler(threading.Thread):
 
 
 # ---------------------------------------------------------------------------- CPU baseline
+def tf_probe():
+    """Run-time probe for the real reference arithmetic (oracle/tf_probe.py): `import tensorflow` is TRIED on the box
+    this runs on and the outcome recorded in the JSON line; if it ever imports, the goldens are re-derived with TF ops
+    and the distance to the committed goldens is reported too (that would pin the CPU restatements)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import tf_probe as tp
+    out = tp.probe()
+    out["observed"] = tp.describe()
+    if out["importable"]:
+        try:
+            out["golden_max_abs_err"] = tp.pin_against_goldens(os.path.join(ROOT, "tests", "golden"))
+        except Exception as e:
+            out["golden_error"] = repr(e)[:200]
+    return out
+
+
 def _cpu_forward():
     """The CPU arm: oracle/oracle_cpu.cpp (C++/OpenMP restatement of the reference's TF forward, all host threads)
     -- the faster of the two CPU restatements; oracle/oracle_torch.py if the library has not been built."""
@@ -177,9 +193,10 @@ def cpu_baseline(n_windows):
     t0 = time.perf_counter()
     run(x, lens, goff)
     dt = time.perf_counter() - t0
-    return {"value": int(lens.sum()) / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "%d windows (T=%d, BN groups of %d) of the same workload, %.1f s; %s, %d threads; "
-                      "TensorFlow 1.4 reference unavailable on this box" % (n_windows, T, BATCH, dt, what, cores)}
+    tfp = tf_probe()
+    return {"value": int(lens.sum()) / dt, "unit": UNIT, "cores": cores, "kind": "port", "tf_probe": tfp,
+            "sample": "%d windows (T=%d, BN groups of %d) of the same workload, %.1f s; %s, %d threads; %s"
+                      % (n_windows, T, BATCH, dt, what, cores, tfp["observed"])}
 
 
 # ---------------------------------------------------------------------------- reference arm
@@ -203,14 +220,16 @@ def run_reference(args):
         run(x, lens, goff)
     dt = (time.perf_counter() - t0) / max(args.steps, 1)
     value = samples / dt
-    sample = ("%d windows per step (T=%d, BN groups of %d), %s, %d threads; TensorFlow 1.4 unavailable on this box"
-              % (nw, T, BATCH, what, cores))
+    tfp = tf_probe()
+    sample = ("%d windows per step (T=%d, BN groups of %d), %s, %d threads; %s"
+              % (nw, T, BATCH, what, cores, tfp["observed"]))
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "windows_per_step": nw, "seq_len": T, "bn_group": BATCH,
                        "n_classes": NCLASS},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                             "tf_probe": tfp},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))

@@ -110,8 +110,8 @@ static int launch_lstm(Ctx &cx, const LstmParams &p, int sm_count) {
     (void)sm_count;
     const int UG = p.Hp / LSTM_UPT;
     if (UG * LSTM_WG > 256)
-        return fail(NTB_EINVAL, "blstm: hidden size %s%lld needs the cluster recurrence (H <= 128 supported)", "",
-                    (long long)p.H);
+        return fail(NTB_EINVAL, "blstm: hidden size %s%lld is outside the SIMT recurrence (H <= 128); larger H must be a "
+                    "multiple of 8 to take the per-timestep tcgen05 path", "", (long long)p.H);
     const bool w_smem = lstm_smem_bytes(p.H, p.Hp, true) <= 227 * 1024;
     const int64_t smem = lstm_smem_bytes(p.H, p.Hp, w_smem);
     dim3 grid(cdiv(p.n_windows, LSTM_BT), 2);
@@ -137,7 +137,7 @@ static int launch_lstm_tc(Ctx &cx, const LstmTcParams &p) {
     }
     dim3 grid((unsigned)p.n_tiles, 2);
     LstmTcParams pp = p;
-    if (const char *e = getenv("NTB_LSTM_FLAGS")) pp.flags = atoi(e);   // ablation switches (ntb_lstm_tc.cuh)
+    if (const char *e = ntb_env("NTB_LSTM_FLAGS")) pp.flags = atoi(e);   // ablation switches (ntb_lstm_tc.cuh)
     alignas(64) CUtensorMap map_x;
     NTB_TRY(make_map_xproj(&map_x, reinterpret_cast<const float *>(p.xproj), 2LL * p.n_tiles * p.T * p.H));
     k_lstm_recurrence_tc<<<grid, LSTM_TC_THREADS, smem, cx.st>>>(map_x, pp);
@@ -230,7 +230,7 @@ static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &a
                 }
                 gemm_tc_plan_weights(ld.convw[c], taps[c], kin[c], C, ar);
             }
-            if (ld.convw[0].valid && ld.convw[1].valid && C % 32 == 0 && !getenv("NTB_NO_DUAL_CONV")) {
+            if (ld.convw[0].valid && ld.convw[1].valid && C % 32 == 0 && !ntb_env("NTB_NO_DUAL_CONV")) {
                 gemm_tc_plan_weights(ld.conv12w, 1, Cin, 2 * C, ar);
                 if (ld.conv12w.valid && ld.conv12w.BN <= C && C % ld.conv12w.BN == 0) ld.conv12_stage = ar.take<float>((int64_t)Cin * 2 * C);
                 else ld.conv12w = GemmWeights();
@@ -250,7 +250,7 @@ static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &a
             // recurrence writes (no operand-split pass, no fp32 hand-over).  Opt-in (NTB_ILV=1): it removes k_split_op16 but
             // the projection GEMM then runs 2 passes over 2K columns (7 instead of 4 k-blocks at K = 200) and loses exactly
             // what the split cost (projection stage 26.8 vs 26.5 ms per 65 536 windows, profiles/r01_final_ablations.txt)
-            static const bool no_ilv = !(getenv("NTB_ILV") && getenv("NTB_ILV")[0] == '1');
+            static const bool no_ilv = !(ntb_env("NTB_ILV") && ntb_env("NTB_ILV")[0] == '1');
             const bool prev_tc = i > 0 && d->layers[i - 1].type == NTB_LAYER_BLSTM && m_prev_tc;
             const bool can_tc = Hp == H && lstm_tc_supported(H) && D % 8 == 0 && D >= 64;
             gemm_tc_plan_weights(ld.wihw, 1, D, 8 * Hp, ar, prev_tc && can_tc && !no_ilv);
@@ -537,7 +537,8 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
     };
     if (m->has_res) {
         if (!group_off || n_groups <= 0) return fail(NTB_EINVAL, "forward: residual layers need group_off (BN groups)%s", "");
-        k_window_groups<<<(unsigned)n_groups, 128, 0, st>>>(group_off, (int)n_groups, ws.win_group);
+        NTB_CUDA(cudaMemsetAsync(ws.win_group, 0, sizeof(int32_t) * (size_t)n, st));
+        k_window_groups<<<(unsigned)n_groups, 128, 0, st>>>(group_off, (int)n_groups, n, ws.win_group);
         cx.count();
         NTB_LAUNCH_CHECK();
     }
@@ -581,7 +582,7 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
                 // (NTB_REC_PLANES=1): the two 8-byte row-strided stores per chunk cost the recurrence more (24.3 -> 30.0 ms
                 // per 65 536 windows) than the saved split pass gives back (32.2 -> 23.8 ms incl. the TMA-store epilogue,
                 // 26.8 -> 23.8 without it): its scattered stores are the recurrence's L1 bottleneck
-                static const bool rec_planes = getenv("NTB_REC_PLANES") && getenv("NTB_REC_PLANES")[0] == '1';
+                static const bool rec_planes = ntb_env("NTB_REC_PLANES") && ntb_env("NTB_REC_PLANES")[0] == '1';
                 const bool feed_next = rec_planes && li + 1 < nl && m->layers[li + 1].type == NTB_LAYER_BLSTM &&
                                        m->layers[li + 1].tc_rec && 2 * ld.size <= ws.gs.kp_cap && (2 * ld.size) % 8 == 0;
                 if (feed_next) { p.next_hi = ws.gs.a_hi; p.next_lo = ws.gs.a_lo; p.next_K = 2 * ld.size; }
@@ -736,6 +737,17 @@ static int forward_host_impl(ntb_model *m, const float *x_host, const int32_t *l
                     (long long)workspace_bytes);
     const int64_t rows = n_windows * m->T;
     if (n_windows == 0) return NTB_OK;
+    if (group_off_host && n_groups > 0) {   // the BN group table must tile [0, n_windows) exactly (header contract)
+        bool ok = group_off_host[0] == 0 && group_off_host[n_groups] == n_windows;
+        for (int64_t g = 0; ok && g < n_groups; ++g) ok = group_off_host[g] <= group_off_host[g + 1];
+        if (!ok)
+            return fail(NTB_EINVAL, "ntb_model_forward_host: group_off must ascend from 0 to n_windows (%s%lld)", "",
+                        (long long)n_windows);
+    }
+    for (int64_t w = 0; w < n_windows; ++w)
+        if (len_host[w] < 0 || len_host[w] > m->T)
+            return fail(NTB_EINVAL, "ntb_model_forward_host: len[%s%lld] = %lld outside [0, seq_len]", "", (long long)w,
+                        (long long)len_host[w]);
     NTB_CUDA(cudaMemcpyAsync(hs.x, x_host, rows * m->len_x * sizeof(float), cudaMemcpyHostToDevice, st));
     NTB_CUDA(cudaMemcpyAsync(hs.len, len_host, n_windows * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     if (group_off_host && n_groups > 0)
@@ -1350,7 +1362,8 @@ extern "C" int ntb_conv_bn(const float *in_dev, const float *filt_dev, const flo
     p.rows = rows; p.K = Cin; p.N = Cout; p.taps = ksize; p.T = T;
     NTB_TRY(launch_conv_gemm(cx, p));
     if (scale_dev) {
-        k_window_groups<<<(unsigned)n_groups, 128, 0, cx.st>>>(group_off_dev, (int)n_groups, win_group);
+        NTB_CUDA(cudaMemsetAsync(win_group, 0, sizeof(int32_t) * (size_t)n_windows, cx.st));
+        k_window_groups<<<(unsigned)n_groups, 128, 0, cx.st>>>(group_off_dev, (int)n_groups, n_windows, win_group);
         NTB_TRY(launch_bn_stats(cx, y, Cout, T, group_off_dev, n_groups, scale_dev, offset_dev, a, b));
         k_bn_apply<<<elementwise_grid(rows * Cout, 148), 256, 0, cx.st>>>(y, a, b, win_group, T, Cout, rows * Cout, relu, out_dev);
     } else if (relu) {

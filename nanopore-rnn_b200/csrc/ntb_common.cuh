@@ -4,6 +4,7 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/nanotensor_b200.h"
@@ -44,6 +45,19 @@ inline int fail(int code, const char *fmt, const char *a = "", long long b = 0, 
         int _rc = (expr);            \
         if (_rc != NTB_OK) return _rc; \
     } while (0)
+
+// Ablation / A-B switches (NTB_LSTM_FLAGS, NTB_XPROJ_ABL, NTB_CF_ABL, ... -- several of them change RESULTS: they skip
+// barrier waits, stores or whole stages to time what is left).  The production build never reads them: ntb_env()
+// returns NULL unless the library was built with -DNTB_ABLATION (csrc/build.sh: NTB_ABLATION=1), so a stray
+// environment variable cannot produce silently wrong labels with rc 0.
+static inline const char *ntb_env(const char *name) {
+#ifdef NTB_ABLATION
+    return getenv(name);
+#else
+    (void)name;
+    return nullptr;
+#endif
+}
 
 static inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }

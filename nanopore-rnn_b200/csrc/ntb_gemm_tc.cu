@@ -391,7 +391,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                     if (w < p.lstm_n && nb < p.N) {
                         const int t = dir ? p.T - 1 - p.lstm_s : p.lstm_s;
                         int len = p.lstm_lens[w];
-                        len = len > p.T ? p.T : len;
+                        len = len > p.T ? p.T : (len < 0 ? 0 : len);
                         const bool active = t < len;
                         const int u0 = nb >> 2;
                         const int nu = (p.N - nb >= 32 && c0 + 32 <= p.BN) ? 8 : 4;     // H % 4 == 0, BN % 16 == 0
@@ -1146,7 +1146,7 @@ int launch_split(cudaStream_t st, const SplitParams &sp, int64_t *launches) {
 int gemm_cta_group() {
     // NTB_GEMM_CG=1 selects the single-CTA kernel (A/B measurement); default is the CTA-pair kernel
     static int cg = [] {
-        const char *e = getenv("NTB_GEMM_CG");
+        const char *e = ntb_env("NTB_GEMM_CG");
         return (e && e[0] == '1') ? 1 : 2;
     }();
     return cg;
@@ -1166,7 +1166,7 @@ int fill_params(TcParams &p, const GemmWeights &w, int64_t plane_rows, bool allo
     // B-stationary (opt-in, NTB_BSTAT=1): measured on the LSTM projections (K <= 256, N = 800) it ties with the
     // streaming schedule (26.7 vs 27.0 ms per 65 536 windows) -- these GEMMs are bound by the 2.6 GB projected-gates
     // write, not by the operand feed from L2 -- so streaming stays the default
-    static const bool no_bstat = getenv("NTB_BSTAT") == nullptr;
+    static const bool no_bstat = ntb_env("NTB_BSTAT") == nullptr;
     const int bres = p.k_blocks * 2 * b_tile_bytes;
     // the projected-gates epilogue stores straight from registers: its staging area only holds the bias vector
     p.epi_bytes = small_epi && w.Np * 4 <= 4096 ? 4096 : EPI_STAGE_BYTES;
@@ -1252,17 +1252,17 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     TcParams p{};
     // opt-in (NTB_XPROJ_TMA=1): measured SLOWER than the register-direct stores (projection 28.4 vs 23.8 ms per 65 536
     // windows, profiles/r01_final_ablations.txt) -- the staging round trip costs more than the store path saves
-    static const bool xtma_on = getenv("NTB_XPROJ_TMA") && getenv("NTB_XPROJ_TMA")[0] == '1';
+    static const bool xtma_on = ntb_env("NTB_XPROJ_TMA") && ntb_env("NTB_XPROJ_TMA")[0] == '1';
     const bool xtma = xproj_H > 0 && xtma_on && w.Np * 4 <= 4096 && bias;
     NTB_TRY(fill_params(p, w, plane_rows, true, xproj_H > 0, xtma));
     p.xproj_tma = xtma ? 1 : 0;
     p.T = T; p.pad = pad; p.out_rows = out_rows; p.bias = bias; p.out = out; p.ldo = ldo;
     p.xproj_H = xproj_H;
     p.bn_part = bn_part;
-    static const int abl = getenv("NTB_XPROJ_ABL") ? atoi(getenv("NTB_XPROJ_ABL")) : 0;
+    static const int abl = ntb_env("NTB_XPROJ_ABL") ? atoi(ntb_env("NTB_XPROJ_ABL")) : 0;
     p.abl = abl;
     // opt-in (NTB_GEMM_L2PF=1): measured slower (projection GEMM 7.49 -> 8.93 ms per 65 536 windows, conv stage +2 ms)
-    static const int l2pf = getenv("NTB_GEMM_L2PF") ? atoi(getenv("NTB_GEMM_L2PF")) : 0;
+    static const int l2pf = ntb_env("NTB_GEMM_L2PF") ? atoi(ntb_env("NTB_GEMM_L2PF")) : 0;
     p.l2pf = l2pf;
     // coalesced TMA-store epilogue for plain row-major outputs (N tiles of whole 32-column chunks)
     p.tma_store = (!pad && xproj_H == 0 && w.BN % 32 == 0 && (ldo & 3) == 0 &&
@@ -1419,7 +1419,7 @@ int gemm_tc_conv_dual(cudaStream_t st, const float *A, int K, int64_t rows, int 
 }
 
 bool gemm_tc_conv_fused_supported(const GemmWeights &w, int K, int T, int ldo) {
-    static const bool off = getenv("NTB_NO_FUSED_CONV") != nullptr;      // A/B measurement switch
+    static const bool off = ntb_env("NTB_NO_FUSED_CONV") != nullptr;      // A/B measurement switch
     return !off && w.valid && !w.single_pass && gemm_cta_group() == 2 && w.K == K && K % BK == 0 && w.Np == w.N &&
            w.BN == w.N && w.N % 32 == 0 && w.N <= 256 && (w.taps == 1 || w.taps == 3) && T >= 32 && (ldo & 3) == 0;
 }
@@ -1440,9 +1440,9 @@ int gemm_tc_conv_fused(cudaStream_t st, const float *y, int K, int64_t rows, int
     p.m_tiles = (rows + BM - 1) / BM; p.rows = rows; p.N = w.N; p.K = K; p.taps = w.taps; p.T = T;
     p.k_blocks = K / BK; p.relu = relu_in; p.aff_a = aff_a; p.aff_b = aff_b; p.win_group = win_group; p.bn_part = bn_part;
     // opt-in: measured neutral to slightly slower (conv stage 56.5 vs 55.8 ms per 65 536 windows)
-    static const int cf_l2pf = getenv("NTB_CF_L2PF") ? atoi(getenv("NTB_CF_L2PF")) : 0;
+    static const int cf_l2pf = ntb_env("NTB_CF_L2PF") ? atoi(ntb_env("NTB_CF_L2PF")) : 0;
     p.l2pf = cf_l2pf;
-    static const int cf_abl = getenv("NTB_CF_ABL") ? atoi(getenv("NTB_CF_ABL")) : 0;
+    static const int cf_abl = ntb_env("NTB_CF_ABL") ? atoi(ntb_env("NTB_CF_ABL")) : 0;
     p.abl = cf_abl;
     const size_t smem = (size_t)CF_OP_STAGES * (2 * A_TILE_BYTES + 2 * (w.N / 2) * BK * 2) +
                         (size_t)CF_RAW_STAGES * CF_RAW_STAGE + CF_EPI_BYTES + 1024;

@@ -9,12 +9,17 @@ namespace ntb {
 // ------------------------------------------------------------------------------------------
 // window -> BN group id   (group = one reference batch: network.py:339-349 takes moments over it)
 // ------------------------------------------------------------------------------------------
-__global__ void k_window_groups(const int32_t *__restrict__ group_off, int n_groups,
+// group_off comes from the caller's device memory on the device-pointer entry (the host entries validate it on the
+// CPU first): offsets are clamped to [0, n_windows] and win_group is zero-filled beforehand, so a malformed table can
+// give wrong BN statistics but never an out-of-bounds index into the [n_groups][C] affine arrays.
+__global__ void k_window_groups(const int32_t *__restrict__ group_off, int n_groups, int64_t n_windows,
                                 int32_t *__restrict__ win_group) {
     int g = blockIdx.x;
     if (g >= n_groups) return;
-    int w0 = group_off[g], w1 = group_off[g + 1];
-    for (int w = w0 + threadIdx.x; w < w1; w += blockDim.x) win_group[w] = g;
+    int64_t w0 = group_off[g], w1 = group_off[g + 1];
+    w0 = w0 < 0 ? 0 : w0;
+    w1 = w1 > n_windows ? n_windows : w1;
+    for (int64_t w = w0 + threadIdx.x; w < w1; w += blockDim.x) win_group[w] = g;
 }
 
 // ------------------------------------------------------------------------------------------

@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(256, 1) k_lstm_recurrence(LstmParams p) {
 #pragma unroll
     for (int i = 0; i < LSTM_WPT; ++i) {
         const int64_t w = w_tile + wl0 + i;
-        len[i] = (worker && w < p.n_windows) ? p.lens[w] : -1;   // -1: window does not exist
+        len[i] = (worker && w < p.n_windows) ? max(p.lens[w], 0) : -1;   // -1: window does not exist
         if (len[i] > T) len[i] = T;
 #pragma unroll
         for (int q = 0; q < LSTM_UPT; ++q) c[i][q] = 0.0f;

@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(LSTM_TC_THREADS, 1) k_lstm_recurrence_tc(const
         const int64_t w = (int64_t)tile * LSTM_TC_ROWS + r;
         const bool exists = w < p.n_windows;
         int len = exists ? p.lens[w] : 0;
-        len = len > T ? T : len;
+        len = len > T ? T : (len < 0 ? 0 : len);    // dynamic_rnn's sequence_length, clamped to [0, T]
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
         const uint32_t d_col = lane_base + (uint32_t)(16 * half);
         const uint32_t ah_col = lane_base + a_hi_col + (uint32_t)(2 * half), al_col = lane_base + a_lo_col + (uint32_t)(2 * half);

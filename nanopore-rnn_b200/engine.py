@@ -239,6 +239,10 @@ class Model:
         else:
             group_off = _as_np(group_off, np.int32)
             pass_groups = True
+            if len(group_off) < 1 or group_off[0] != 0 or group_off[-1] != n or np.any(np.diff(group_off) < 0):
+                raise ValueError("group_off must ascend from 0 to the number of windows (%d)" % n)
+        if len(lens) != n or (n and (lens.min() < 0 or lens.max() > self.T)):
+            raise ValueError("lens must hold one value in [0, seq_len] per window")
         T, Cc = self.T, self.C
         # results land in pinned host memory (torch's caching host allocator recycles the blocks)
         labels = _pinned((n * T,), torch.int32)

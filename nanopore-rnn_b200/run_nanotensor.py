@@ -223,4 +223,5 @@ def main(in_args=None):
 
 
 if __name__ == "__main__":
-    sys.exit(main() if isinstance(main(), int) else 0)
+    _rc = main()                      # ONCE: the job must not run a second time for the exit code
+    sys.exit(_rc if isinstance(_rc, int) else 0)

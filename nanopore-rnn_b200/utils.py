@@ -34,12 +34,14 @@ def save_json(obj, path):
 
 
 def list_dir(path, ext=""):
-    """Sorted absolute paths of the files in ``path`` ending with ``ext``."""
-    if ext:
-        names = [f for f in os.listdir(path) if f.endswith(ext)]
-    else:
-        names = [f for f in os.listdir(path) if os.path.isfile(os.path.join(path, f))]
-    return sorted(os.path.join(os.path.abspath(path), f) for f in names)
+    """Absolute paths of the regular files in ``path`` whose last dot-separated component equals ``ext`` (all regular
+    files when ``ext`` is empty): the reference's predicate, nanotensor/utils.py:71-82 (``isfile`` and
+    ``f.split(".")[-1] == ext``).  Deliberate deviation: the result is sorted (the reference returns ``os.listdir``
+    order, which is filesystem dependent) so that jobs, BN groups over concatenated files and shards are reproducible."""
+    root = os.path.abspath(path)
+    names = [f for f in os.listdir(path) if os.path.isfile(os.path.join(root, f))
+             and (ext == "" or f.split(".")[-1] == ext)]
+    return sorted(os.path.join(root, f) for f in names)
 
 
 def merge_two_dicts(a, b):

@@ -71,7 +71,24 @@ def test_run_tensorflow_inference_and_test_routes(golden_dir, tmp_path):
     x, lens, goff, _ = ds.inference_job()
     batches = [A.forward_batch(x[a:b], lens[a:b], net, w, "CtcLoss")[1] for a, b in zip(goff[:-1], goff[1:])]
     fasta = open(outs[0]).read().split("\n")[1]
-    assert fasta == A.process_output(batches) or len(fasta) > 0
+    # exact comparison against the oracle route: the FASTA must equal the oracle's consensus whenever every argmax
+    # agrees; positions that flip must be near ties in the oracle (readout gain 8 scales the 1e-3 logits budget), and
+    # then the FASTA must still equal the oracle's assembly of the GPU's own decoded labels
+    from nanopore_rnn_b200 import engine
+    labels, llen, logits = runner.inference_model.model.forward_host(x, lens, goff, want_logits=True)
+    ref_logits = np.concatenate([A.forward_batch(x[a:b], lens[a:b], net, w, "CtcLoss")[0]
+                                 for a, b in zip(goff[:-1], goff[1:])]).reshape(-1, 6)
+    assert np.abs(logits - ref_logits).max() <= 8e-3
+    flips = np.argwhere(logits.argmax(1) != ref_logits.argmax(1)).reshape(-1)
+    for r in flips:
+        top = np.sort(ref_logits[r])[-2:]
+        assert top[1] - top[0] <= 2 * 8e-3, (int(r), float(top[1] - top[0]))
+    assert len(flips) <= 1e-3 * len(ref_logits)
+    gpu_batches = [engine.ctc_dense(labels[a:b], llen[a:b]) for a, b in zip(goff[:-1], goff[1:])]
+    assert fasta == A.process_output(gpu_batches)
+    if len(flips) == 0:
+        assert fasta == A.process_output(batches)
+    assert len(fasta) > 20                                   # and the case is not degenerate
 
     # test route: CrossEntropy accuracy on the shipped event checkpoint
     arr_dir = tmp_path / "npy"

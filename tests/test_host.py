@@ -177,3 +177,27 @@ dist.destroy_process_group()
                          capture_output=True, text=True, timeout=240)
     assert out.returncode == 0, out.stderr[-2000:]
     assert "OK 7" in out.stdout
+
+
+def test_list_dir_uses_the_reference_predicate(tmp_path):
+    """nanotensor/utils.py:71-82: regular files whose LAST dot component equals ext (not endswith)."""
+    from nanopore_rnn_b200.utils import list_dir
+    for name in ("a.signal", "b.fullsignal", "notasignal", "c.signal.bak", "d.txt"):
+        (tmp_path / name).write_text("1 2 3")
+    (tmp_path / "dir.signal").mkdir()
+    got = [os.path.basename(p) for p in list_dir(str(tmp_path), ext="signal")]
+    assert got == ["a.signal"]
+    assert len(list_dir(str(tmp_path))) == 5                      # ext "": every regular file, no directories
+
+
+def test_module_main_runs_the_job_once(tmp_path):
+    """`python -m nanopore_rnn_b200.run_nanotensor -c cfg` must call main() exactly once (round-1 bug: twice) and
+    return the Usage exit code 2 of THAT run."""
+    cfg = tmp_path / "bad.json"
+    cfg.write_text(json.dumps({"train": False, "inference": False, "test": False, "network": [],
+                               "CreateDataset": {"dataset": "FullSignalSequence"}}))
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    p = subprocess.run([sys.executable, "-m", "nanopore_rnn_b200.run_nanotensor", "-c", str(cfg)],
+                       capture_output=True, text=True, cwd=ROOT, env=env, timeout=300)
+    assert p.returncode == 2, (p.returncode, p.stderr[-500:])
+    assert p.stderr.count("Need to specify exactly one of") == 1, p.stderr

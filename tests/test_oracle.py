@@ -221,3 +221,17 @@ def test_cpp_oracle_ragged_blstm_and_ctc_rules():
     dense[:, :rl.shape[1]] = rl
     assert np.array_equal(labels, dense)
     assert np.array_equal(llen, (dense >= 0).sum(1))
+
+
+def test_tensorflow_probe_reports_what_it_observes(golden_dir):
+    """BASELINE.md section 2 / SURVEY.md section 7: the TF probe runs where the tests run.  Absent (expected): the
+    outcome names the import error.  Present: the committed goldens must be reproduced by TF's own ops -- that pins
+    every restatement under oracle/."""
+    import tf_probe
+    p = tf_probe.probe()
+    assert set(p) == {"importable", "version", "error"}
+    if not p["importable"]:
+        assert p["error"] and "tensorflow" in tf_probe.describe().lower()
+        return
+    errs = tf_probe.pin_against_goldens(golden_dir)
+    assert all(e <= 1e-4 for e in errs.values()), errs
