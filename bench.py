@@ -33,10 +33,51 @@ ROWS = {"event_features": "bench_events.py", "assembly": "bench_assembly.py", "e
         "signal_parse": "bench_parse.py"}
 METRIC = "signal samples/sec basecalled (BLSTM fwd)"
 UNIT = "samples/s"
-WORKLOAD = "run_nanotensor.config.json network, synthetic windows"
-T, BATCH, NCLASS, WIN_PER_READ = 100, 10, 4, 1000
-# algorithmic FLOPs per window (multiply-add = 2)
-FLOPS_CONV, FLOPS_PROJ, FLOPS_REC, FLOPS_READOUT = 209.8e6, 105.0e6, 48.0e6, 0.12e6
+WIN_PER_READ = 1000
+# --network: the three networks BASELINE.json's configs name.  The contract line (no flag) is configs[1]; the others
+# are extra throughput + roofline lines (profiles/), each parity-tested in tests/test_gpu_parity.py.
+WORKLOADS = {
+    "run_nanotensor": {"graph": "CtcLoss", "T": 100, "batch": 10, "n_classes": 4, "len_x": 1, "windows": 1048576,
+                       "weights_seed": 2, "what": "BASELINE configs[1]: run_nanotensor.config.json network "
+                                                  "(3 residual(256) + 3 BLSTM(100) + chiron_fnn, CTC C=4), synthetic windows"},
+    "signal_CRNN": {"graph": "CtcLoss", "T": 100, "batch": 20, "n_classes": 6, "len_x": 1, "windows": 1048576,
+                    "weights_seed": 12, "what": "BASELINE configs[2]: signal_CRNN.config.json network as shipped "
+                                                "(2 residual(256) + 1 BLSTM(100) + chiron_fnn, CTC C=6), synthetic windows"},
+    "stress_blstm256": {"graph": "CrossEntropy", "T": 100, "batch": 0, "n_classes": 1025, "len_x": 12, "windows": 262144,
+                        "weights_seed": 32, "what": "BASELINE configs[4]: 5 x BLSTM(256), CrossEntropy C=1025, len_x 12, "
+                                                    "synthetic N(0,1) windows"},
+}
+WL = dict(WORKLOADS["run_nanotensor"], name="run_nanotensor")
+T, BATCH, NCLASS = WL["T"], WL["batch"], WL["n_classes"]
+WORKLOAD = WL["what"]
+
+
+def select_workload(name):
+    global WL, T, BATCH, NCLASS, WORKLOAD
+    WL = dict(WORKLOADS[name], name=name)
+    T, BATCH, NCLASS, WORKLOAD = WL["T"], WL["batch"], WL["n_classes"], WL["what"]
+
+
+def flops_per_window(net, T, len_x, n_classes):
+    """Algorithmic FLOPs per window by stage (multiply-add = 2): residual layer
+    2T(2 Cin Cout + 3 Cout^2 + Cout^2); blstm projection 16 T D H, recurrence 16 T H^2; fnn 2T 2H; dense 2T F C."""
+    f = {"conv_bn": 0.0, "projection": 0.0, "recurrence": 0.0, "readout": 0.0}
+    d = len_x
+    for l in net:
+        if l["type"] == "residual_layer":
+            c = l["out_channel"]
+            f["conv_bn"] += 2.0 * T * (2 * d * c + 4 * c * c)
+            d = c
+        elif l["type"] == "blstm":
+            h = l["size"]
+            f["projection"] += 16.0 * T * d * h
+            f["recurrence"] += 16.0 * T * h * h
+            d = 2 * h
+        elif l["type"] == "chiron_fnn":
+            f["readout"] += 2.0 * T * d
+            d //= 2
+    f["readout"] += 2.0 * T * d * n_classes
+    return f
 
 
 def parse():
@@ -45,7 +86,9 @@ def parse():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--windows", type=int, default=1048576, help="windows per GPU per step")
+    ap.add_argument("--network", default="run_nanotensor", choices=sorted(WORKLOADS),
+                    help="which BASELINE.json network to time (default: configs[1], the contract's line)")
+    ap.add_argument("--windows", type=int, default=0, help="windows per GPU per step (0 = the workload's own size)")
     ap.add_argument("--cpu-windows", type=int, default=0,
                     help="windows in the CPU baseline sample (0 = auto-size to ~10-20 s)")
     ap.add_argument("--chunk-windows", type=int, default=0,
@@ -57,6 +100,9 @@ def parse():
                          "of the widened rows (f): their own metric, roofline and cpu_baseline, one GPU")
     args, rest = ap.parse_known_args()
     args.rest = rest
+    select_workload(args.network)
+    if args.windows <= 0:
+        args.windows = WL["windows"]
     return args
 
 
@@ -71,8 +117,16 @@ def peaks():
 
 # ---------------------------------------------------------------------------- workload
 def make_workload(n_windows, seed):
-    """Windows of synthetic z-scored reads + BN group offsets."""
+    """Windows of synthetic z-scored reads (SURVEY.md 8d config 2) + BN group offsets (networks with residual layers;
+    the pure-BLSTM stress network has no cross-window coupling: ragged N(0,1) windows, group table = None)."""
     from nanopore_rnn_b200 import engine, synthetic as syn
+    if WL["batch"] == 0:
+        rng = np.random.default_rng(seed)
+        x = rng.standard_normal((n_windows, T, WL["len_x"]), dtype=np.float32)
+        lens = np.full(n_windows, T, dtype=np.int32)
+        lens[WIN_PER_READ - 1::WIN_PER_READ] = rng.integers(1, T + 1, size=len(lens[WIN_PER_READ - 1::WIN_PER_READ]))
+        x *= (np.arange(T)[None, :] < lens[:, None])[:, :, None]
+        return x, lens, None
     n_reads = max(1, -(-n_windows // WIN_PER_READ))
     wpr = WIN_PER_READ if n_windows >= WIN_PER_READ else n_windows
     x, lens, _ = syn.synthetic_reads(n_reads, wpr, T, seed=seed)
@@ -85,8 +139,8 @@ def make_workload(n_windows, seed):
 
 def network_and_weights():
     from nanopore_rnn_b200 import synthetic as syn
-    net = syn.NETWORKS["run_nanotensor"]
-    return net, syn.random_weights(net, 1, NCLASS, seed=2)
+    net = syn.NETWORKS[WL["name"]]
+    return net, syn.random_weights(net, WL["len_x"], NCLASS, seed=WL["weights_seed"], graph=WL["graph"])
 
 
 # ---------------------------------------------------------------------------- clocks
@@ -162,7 +216,7 @@ def _cpu_forward():
         Cc.load()
 
         def run(x, lens, goff):
-            Cc.forward(x, lens, net, w, "CtcLoss", group_off=goff, n_threads=cores)   # logits + CTC-greedy labels
+            Cc.forward(x, lens, net, w, WL["graph"], group_off=goff, n_threads=cores)   # logits + CTC-greedy labels
         return run, cores, "C++/OpenMP restatement (oracle/oracle_cpu.cpp)"
     except Exception:
         import torch
@@ -171,17 +225,19 @@ def _cpu_forward():
         torch.set_num_threads(cores)
 
         def run(x, lens, goff):
-            A.ctc_greedy(B.forward_job(x, lens, net, w, "CtcLoss", BATCH), lens)
+            lg = B.forward_job(x, lens, net, w, WL["graph"], BATCH or len(x))
+            A.ctc_greedy(lg, lens) if WL["graph"] == "CtcLoss" else A.argmax_first(lg.reshape(-1, NCLASS))
         return run, cores, "torch-CPU restatement (oracle/oracle_torch.py)"
 
 
 def _cpu_sample_size(run, target_s, cap):
-    x, lens, goff = make_workload(BATCH * 64, 1234)
-    run(x[:BATCH * 8], lens[:BATCH * 8], goff[:9])           # warm the thread pool / allocators
+    b = BATCH or 16
+    x, lens, goff = make_workload(b * 64, 1234)
+    run(x[:b * 8], lens[:b * 8], goff[:9] if goff is not None else None)     # warm the thread pool / allocators
     t0 = time.perf_counter()
     run(x, lens, goff)
     dt = time.perf_counter() - t0
-    return int(max(BATCH * 64, min(cap, (target_s / dt) * BATCH * 64)) // BATCH * BATCH)
+    return int(max(b * 64, min(cap, (target_s / dt) * b * 64)) // b * b)
 
 
 def cpu_baseline(n_windows):
@@ -275,24 +331,32 @@ def run_b200(args):
     n = len(x)
     samples = int(lens.sum())
     net, w = network_and_weights()
-    m = engine.Model(net, w, "CtcLoss", T, 1, NCLASS, device=str(dev))
+    m = engine.Model(net, w, WL["graph"], T, WL["len_x"], NCLASS, device=str(dev))
+    ctc = WL["graph"] == "CtcLoss"
 
     # ---- device-resident job: inputs already in HBM when the timed region starts
     x_pin = torch.from_numpy(x).pin_memory()
     lens_pin = torch.from_numpy(lens).pin_memory()
     x_d, lens_d = x_pin.to(dev), lens_pin.to(dev)
-    chunks = engine.plan_chunks(goff, args.chunk_windows or m.max_chunk_windows(), m.chunk_align())
-    chunk_goff = [torch.from_numpy(np.ascontiguousarray(goff[g:h + 1] - goff[g], dtype=np.int32)).to(dev)
-                  for g, h in chunks]
+    cap = args.chunk_windows or m.max_chunk_windows()
+    if goff is None:        # no BN groups (pure BLSTM network): any cut is legal -> equal chunks under the cap
+        cuts = np.unique(np.linspace(0, n, -(-n // cap) + 1).astype(np.int64))
+        plan_off, chunks = cuts, [(i, i + 1) for i in range(len(cuts) - 1)]
+        chunk_goff = [None] * len(chunks)
+    else:
+        plan_off = goff
+        chunks = engine.plan_chunks(goff, cap, m.chunk_align())
+        chunk_goff = [torch.from_numpy(np.ascontiguousarray(goff[g:h + 1] - goff[g], dtype=np.int32)).to(dev)
+                      for g, h in chunks]
     labels_d = torch.empty(n * T, dtype=torch.int32, device=dev)
-    llen_d = torch.empty(n, dtype=torch.int32, device=dev)
+    llen_d = torch.empty(n, dtype=torch.int32, device=dev) if ctc else None
     launches = [0]
 
     def step():
         for (g, h), go in zip(chunks, chunk_goff):
-            w0, w1 = int(goff[g]), int(goff[h])
+            w0, w1 = int(plan_off[g]), int(plan_off[h])
             m.forward_device(x_d[w0:w1], lens_d[w0:w1], go, labels_out=labels_d[w0 * T:w1 * T],
-                             label_len_out=llen_d[w0:w1])
+                             label_len_out=llen_d[w0:w1] if ctc else None)
             launches[0] += m.last_launches()
 
     for _ in range(args.warmup):
@@ -330,39 +394,62 @@ def run_b200(args):
         torch.cuda.synchronize()
         dt = max_over_ranks(time.perf_counter() - t0) / max(args.steps, 1)
         e2e = {"value": total_samples / dt, "unit": UNIT,
-               "h2d_bytes_per_step": int(sum_over_ranks(x.nbytes + lens.nbytes + goff.nbytes)),
-               "d2h_bytes_per_step": int(sum_over_ranks(labels.nbytes + llen.nbytes)), "ms_per_step": dt * 1e3}
+               "h2d_bytes_per_step": int(sum_over_ranks(x.nbytes + lens.nbytes + (goff.nbytes if goff is not None else 0))),
+               "d2h_bytes_per_step": int(sum_over_ranks(labels.nbytes + (llen.nbytes if llen is not None else 0))),
+               "ms_per_step": dt * 1e3}
 
-    # ---- roofline of the dominant kernel: k_gemm_tc<2>, the tcgen05 GEMM of the LSTM input projections (three
-    # launches per forward, the largest share of the launch list in profiles/).  Its launches are bracketed by CUDA
-    # events on the forward's stream (stage 4 of ntb_model_stage_ms); achieved = SURVEY.md 8(d)'s algorithmic projection
-    # FLOPs per window x windows / that time.  The per-stage table (same events) covers the rest of the step.
+    # ---- roofline.  Dominant kernel: k_gemm_tc<2>, the persistent tcgen05 GEMM -- in the CRNN networks its largest
+    # role is the LSTM input projection (one launch per BLSTM layer and chunk), bracketed by its own CUDA events on the
+    # forward's stream (stage 4 of ntb_model_stage_ms); in the pure-BLSTM stress network it runs once per timestep and
+    # direction pair inside the recurrence stage, so the stage marks are the kernel's.  achieved = SURVEY.md 8(d)'s
+    # algorithmic FLOPs per window x windows / that time.  roofline_stages: the same for every stage of the step.
     pk = peaks()
     proj_ms = stage.get("projection_gemm", 0.0)
     stage4 = {"conv_bn": stage.get("conv_bn", 0.0),
               "projection": stage.get("projection_split", 0.0) + proj_ms,
               "recurrence": stage.get("recurrence", 0.0), "readout": stage.get("readout", 0.0)}
-    flops = {"conv_bn": FLOPS_CONV, "projection": FLOPS_PROJ, "recurrence": FLOPS_REC, "readout": FLOPS_READOUT}
+    flops = flops_per_window(net, T, WL["len_x"], NCLASS)
+    peak = pk["bf16_tflops_sustained"]
+    n_blstm = sum(1 for l in net if l["type"] == "blstm")
+    steps = max(args.steps, 1)
+    stages = {}
+    for k, v in stage4.items():
+        tf_s = flops[k] * n * steps / (v * 1e-3) / 1e12 if v > 0 else None
+        stages[k] = {"ms_per_step": v / steps, "algorithmic_mflop_per_window": flops[k] / 1e6, "achieved_tflops": tf_s,
+                     "frac": (tf_s / peak if tf_s else None),
+                     "tensor_pipe_frac_with_3_passes": (3 * tf_s / peak if tf_s else None)}
+    stages["readout"]["bound"] = "hbm"          # reads the last layer's activations once; FLOPs are negligible
     roof = None
     if proj_ms > 0:
-        n_launch_k = 3 * len(chunks) * args.steps
-        achieved = FLOPS_PROJ * n * args.steps / (proj_ms * 1e-3) / 1e12
-        peak = pk["bf16_tflops_sustained"]
+        kname, k_ms, k_flops = "k_gemm_tc<2> (LSTM input projection GEMM, tcgen05 fp16x3)", proj_ms, flops["projection"]
+        n_launch_k = n_blstm * len(chunks) * steps
+        tkey = "k_gemm_tc_xproj_dram_bytes_per_window"
+    elif stage4["recurrence"] > 0:
+        kname = "k_gemm_tc<2> (per-timestep recurrence GEMM h.W_hh with fused cell epilogue, tcgen05 fp16x3)"
+        k_ms, k_flops = stage4["recurrence"], flops["recurrence"]
+        n_launch_k = n_blstm * T * len(chunks) * steps
+        tkey = "k_gemm_tc_step_dram_bytes_per_window"
+    else:
+        kname = None
+    if kname:
+        achieved = k_flops * n * steps / (k_ms * 1e-3) / 1e12
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
-            per_window = json.load(open(tp)).get("k_gemm_tc_xproj_dram_bytes_per_window")
-            if per_window:
-                traffic = per_window * n / len(chunks)      # bytes per launch at this chunk size (ncu: --set full)
-        roof = {"bound": "tensor", "kernel": "k_gemm_tc<2> (LSTM input projection GEMM, tcgen05 fp16x3)",
+        if os.path.exists(tp) and WL["name"] != "signal_CRNN":
+            per_window = json.load(open(tp)).get(tkey)
+            if per_window:     # bytes per launch at this chunk size (ncu --set full, per window, profiles/)
+                traffic = per_window * n / len(chunks) * (1.0 if proj_ms > 0 else 1.0 / (n_blstm * T))
+        roof = {"bound": "tensor", "kernel": kname,
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
                 "peak_source": pk["src"] + " (sustained bf16)",
-                "us_per_launch": proj_ms * 1e3 / n_launch_k, "launches": n_launch_k,
-                "algorithmic_flops_per_launch": FLOPS_PROJ * n / len(chunks) / 3,
+                "us_per_launch": k_ms * 1e3 / n_launch_k, "launches": n_launch_k,
+                "algorithmic_flops_per_launch": k_flops * n * steps / n_launch_k,
                 "tensor_pipe_frac_with_3_passes": 3 * achieved / peak,
-                "stage_ms_per_step": {k: v / max(args.steps, 1) for k, v in stage4.items()},
-                "stage_tflops": {k: (flops[k] * n * args.steps / (v * 1e-3) / 1e12 if v > 0 else None)
-                                 for k, v in stage4.items()},
+                "stage_ms_per_step": {k: v / steps for k, v in stage4.items()},
+                "stage_tflops": {k: stages[k]["achieved_tflops"] for k in stage4},
+                "whole_step": {"algorithmic_mflop_per_window": sum(flops.values()) / 1e6,
+                               "achieved_tflops": sum(flops.values()) * n / (ms_step * 1e-3) / 1e12,
+                               "frac": sum(flops.values()) * n / (ms_step * 1e-3) / 1e12 / peak},
                 "hbm_peak_gbs": pk["hbm_gbs"]}
 
     cpu = None
@@ -377,7 +464,7 @@ def run_b200(args):
                            "l2": "inputs (%.0f MB) and activations larger than L2" % (x.nbytes / 1e6),
                            "parallelism": "reads sharded over %d GPU(s), no collective" % world},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(n_launch), "roofline": roof,
-                "cpu_baseline": cpu}
+                "roofline_stages": stages, "cpu_baseline": cpu}
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()
