@@ -93,6 +93,13 @@ def parse():
                     help="windows in the CPU baseline sample (0 = auto-size to ~10-20 s)")
     ap.add_argument("--chunk-windows", type=int, default=0,
                     help="windows per forward call (0 = as many as the workspace budget allows)")
+    ap.add_argument("--workload", default="reads", choices=["reads", "windows"],
+                    help="reads (default): ONE variable-length read set of --windows windows in total, LPT-sharded over "
+                         "the ranks (strong scaling; raw int16 samples -> called reads, gather to rank 0 in e2e); "
+                         "windows: every rank its own pre-windowed uniform windows (weak scaling, round 1's line)")
+    ap.add_argument("--step", type=int, default=100,
+                    help="window step of the reads workload (100 = dense; 300 = the reference's default, dataset.py:337)")
+    ap.add_argument("--no-replica", action="store_true", help="reads workload: skip the replica_weak second key")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end (host buffers) leg")
     ap.add_argument("--row", default="forward", choices=["forward"] + sorted(ROWS),
@@ -293,45 +300,130 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------- B200 arm
-def run_b200(args):
+class Ctx(object):
+    """Per-process plumbing: device, NCCL group (torch.distributed), the model, rank-reduction helpers."""
+
+    def __init__(self):
+        import torch
+        import nanopore_rnn_b200  # noqa: F401
+        from nanopore_rnn_b200 import engine
+        self.torch = torch
+        self.rank = int(os.environ.get("RANK", 0))
+        self.world = int(os.environ.get("WORLD_SIZE", 1))
+        self.local = int(os.environ.get("LOCAL_RANK", 0))
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            self.dist = dist
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.net, self.w = network_and_weights()
+        self.m = engine.Model(self.net, self.w, WL["graph"], T, WL["len_x"], NCLASS, device=str(self.dev))
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def _reduce(self, v, op):
+        if self.dist is None:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    def max_over_ranks(self, v):
+        return self._reduce(v, self.dist.ReduceOp.MAX if self.dist else None)
+
+    def sum_over_ranks(self, v):
+        return self._reduce(v, self.dist.ReduceOp.SUM if self.dist else None)
+
+    def all_values(self, v):
+        if self.dist is None:
+            return [v]
+        t = self.torch.zeros(self.world, dtype=self.torch.float64, device=self.dev)
+        t[self.rank] = v
+        self.dist.all_reduce(t)
+        return [float(a) for a in t.tolist()]
+
+    def close(self):
+        if self.dist is not None:
+            self.dist.barrier()
+            self.dist.destroy_process_group()
+
+
+def roofline_of(cx, stage, n, n_chunks, steps, ms_step):
+    """roofline / roofline_stages from the stage marks of ``steps`` forwards over ``n`` windows in ``n_chunks`` chunks.
+    Dominant kernel: k_gemm_tc<2>, the persistent tcgen05 GEMM -- in the CRNN networks its largest role is the LSTM
+    input projection (one launch per BLSTM layer and chunk), bracketed by its own CUDA events on the forward's stream
+    (stage 4 of ntb_model_stage_ms); in the pure-BLSTM stress network it runs once per timestep and direction pair
+    inside the recurrence stage, so the stage marks are the kernel's.  achieved = SURVEY.md 8(d)'s algorithmic FLOPs
+    per window x windows / that time."""
+    net = cx.net
+    pk = peaks()
+    proj_ms = stage.get("projection_gemm", 0.0)
+    stage4 = {"conv_bn": stage.get("conv_bn", 0.0),
+              "projection": stage.get("projection_split", 0.0) + proj_ms,
+              "recurrence": stage.get("recurrence", 0.0), "readout": stage.get("readout", 0.0)}
+    flops = flops_per_window(net, T, WL["len_x"], NCLASS)
+    peak = pk["bf16_tflops_sustained"]
+    n_blstm = sum(1 for l in net if l["type"] == "blstm")
+    stages = {}
+    for k, v in stage4.items():
+        tf_s = flops[k] * n * steps / (v * 1e-3) / 1e12 if v > 0 else None
+        stages[k] = {"ms_per_step": v / steps, "algorithmic_mflop_per_window": flops[k] / 1e6, "achieved_tflops": tf_s,
+                     "frac": (tf_s / peak if tf_s else None),
+                     "tensor_pipe_frac_with_3_passes": (3 * tf_s / peak if tf_s else None)}
+    stages["readout"]["bound"] = "hbm"          # reads the last layer's activations once; FLOPs are negligible
+    roof = None
+    if proj_ms > 0:
+        kname, k_ms, k_flops = "k_gemm_tc<2> (LSTM input projection GEMM, tcgen05 fp16x3)", proj_ms, flops["projection"]
+        n_launch_k = n_blstm * n_chunks * steps
+        tkey = "k_gemm_tc_xproj_dram_bytes_per_window"
+    elif stage4["recurrence"] > 0:
+        kname = "k_gemm_tc<2> (per-timestep recurrence GEMM h.W_hh with fused cell epilogue, tcgen05 fp16x3)"
+        k_ms, k_flops = stage4["recurrence"], flops["recurrence"]
+        n_launch_k = n_blstm * T * n_chunks * steps
+        tkey = "k_gemm_tc_step_dram_bytes_per_window"
+    else:
+        kname = None
+    if kname:
+        achieved = k_flops * n * steps / (k_ms * 1e-3) / 1e12
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp) and WL["name"] != "signal_CRNN":
+            per_window = json.load(open(tp)).get(tkey)
+            if per_window:     # bytes per launch at this chunk size (ncu --set full, per window, profiles/)
+                traffic = per_window * n / n_chunks * (1.0 if proj_ms > 0 else 1.0 / (n_blstm * T))
+        roof = {"bound": "tensor", "kernel": kname,
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
+                "peak_source": pk["src"] + " (sustained bf16)",
+                "us_per_launch": k_ms * 1e3 / n_launch_k, "launches": n_launch_k,
+                "algorithmic_flops_per_launch": k_flops * n * steps / n_launch_k,
+                "tensor_pipe_frac_with_3_passes": 3 * achieved / peak,
+                "stage_ms_per_step": {k: v / steps for k, v in stage4.items()},
+                "stage_tflops": {k: stages[k]["achieved_tflops"] for k in stage4},
+                "whole_step": {"algorithmic_mflop_per_window": sum(flops.values()) / 1e6,
+                               "achieved_tflops": sum(flops.values()) * n / (ms_step * 1e-3) / 1e12,
+                               "frac": sum(flops.values()) * n / (ms_step * 1e-3) / 1e12 / peak},
+                "hbm_peak_gbs": pk["hbm_gbs"]}
+    return roof, stages
+
+
+def bench_windows(cx, args, steps, warmup, with_e2e=True, with_cpu=True):
+    """Weak-scaling replica line: every rank runs its own ``--windows`` pre-windowed synthetic windows (uniform
+    1000-window reads); no data crosses ranks."""
     import torch
-    import nanopore_rnn_b200  # noqa: F401
     from nanopore_rnn_b200 import engine
-    rank = int(os.environ.get("RANK", 0))
-    world = int(os.environ.get("WORLD_SIZE", 1))
-    local = int(os.environ.get("LOCAL_RANK", 0))
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(v):
-        if dist is None:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(v):
-        if dist is None:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    rank, world, local, dev, dist, m, net = cx.rank, cx.world, cx.local, cx.dev, cx.dist, cx.m, cx.net
+    barrier, max_over_ranks, sum_over_ranks = cx.barrier, cx.max_over_ranks, cx.sum_over_ranks
+    args = argparse.Namespace(**dict(vars(args), steps=steps, warmup=warmup, no_e2e=not with_e2e, no_cpu=not with_cpu))
 
     # each rank owns its own reads (weak scaling): no collective on the data path
     x, lens, goff = make_workload(args.windows, seed=100 + rank)
     n = len(x)
     samples = int(lens.sum())
-    net, w = network_and_weights()
-    m = engine.Model(net, w, WL["graph"], T, WL["len_x"], NCLASS, device=str(dev))
     ctc = WL["graph"] == "CtcLoss"
 
     # ---- device-resident job: inputs already in HBM when the timed region starts
@@ -398,77 +490,183 @@ def run_b200(args):
                "d2h_bytes_per_step": int(sum_over_ranks(labels.nbytes + (llen.nbytes if llen is not None else 0))),
                "ms_per_step": dt * 1e3}
 
-    # ---- roofline.  Dominant kernel: k_gemm_tc<2>, the persistent tcgen05 GEMM -- in the CRNN networks its largest
-    # role is the LSTM input projection (one launch per BLSTM layer and chunk), bracketed by its own CUDA events on the
-    # forward's stream (stage 4 of ntb_model_stage_ms); in the pure-BLSTM stress network it runs once per timestep and
-    # direction pair inside the recurrence stage, so the stage marks are the kernel's.  achieved = SURVEY.md 8(d)'s
-    # algorithmic FLOPs per window x windows / that time.  roofline_stages: the same for every stage of the step.
-    pk = peaks()
-    proj_ms = stage.get("projection_gemm", 0.0)
-    stage4 = {"conv_bn": stage.get("conv_bn", 0.0),
-              "projection": stage.get("projection_split", 0.0) + proj_ms,
-              "recurrence": stage.get("recurrence", 0.0), "readout": stage.get("readout", 0.0)}
-    flops = flops_per_window(net, T, WL["len_x"], NCLASS)
-    peak = pk["bf16_tflops_sustained"]
-    n_blstm = sum(1 for l in net if l["type"] == "blstm")
-    steps = max(args.steps, 1)
-    stages = {}
-    for k, v in stage4.items():
-        tf_s = flops[k] * n * steps / (v * 1e-3) / 1e12 if v > 0 else None
-        stages[k] = {"ms_per_step": v / steps, "algorithmic_mflop_per_window": flops[k] / 1e6, "achieved_tflops": tf_s,
-                     "frac": (tf_s / peak if tf_s else None),
-                     "tensor_pipe_frac_with_3_passes": (3 * tf_s / peak if tf_s else None)}
-    stages["readout"]["bound"] = "hbm"          # reads the last layer's activations once; FLOPs are negligible
-    roof = None
-    if proj_ms > 0:
-        kname, k_ms, k_flops = "k_gemm_tc<2> (LSTM input projection GEMM, tcgen05 fp16x3)", proj_ms, flops["projection"]
-        n_launch_k = n_blstm * len(chunks) * steps
-        tkey = "k_gemm_tc_xproj_dram_bytes_per_window"
-    elif stage4["recurrence"] > 0:
-        kname = "k_gemm_tc<2> (per-timestep recurrence GEMM h.W_hh with fused cell epilogue, tcgen05 fp16x3)"
-        k_ms, k_flops = stage4["recurrence"], flops["recurrence"]
-        n_launch_k = n_blstm * T * len(chunks) * steps
-        tkey = "k_gemm_tc_step_dram_bytes_per_window"
-    else:
-        kname = None
-    if kname:
-        achieved = k_flops * n * steps / (k_ms * 1e-3) / 1e12
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp) and WL["name"] != "signal_CRNN":
-            per_window = json.load(open(tp)).get(tkey)
-            if per_window:     # bytes per launch at this chunk size (ncu --set full, per window, profiles/)
-                traffic = per_window * n / len(chunks) * (1.0 if proj_ms > 0 else 1.0 / (n_blstm * T))
-        roof = {"bound": "tensor", "kernel": kname,
-                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
-                "peak_source": pk["src"] + " (sustained bf16)",
-                "us_per_launch": k_ms * 1e3 / n_launch_k, "launches": n_launch_k,
-                "algorithmic_flops_per_launch": k_flops * n * steps / n_launch_k,
-                "tensor_pipe_frac_with_3_passes": 3 * achieved / peak,
-                "stage_ms_per_step": {k: v / steps for k, v in stage4.items()},
-                "stage_tflops": {k: stages[k]["achieved_tflops"] for k in stage4},
-                "whole_step": {"algorithmic_mflop_per_window": sum(flops.values()) / 1e6,
-                               "achieved_tflops": sum(flops.values()) * n / (ms_step * 1e-3) / 1e12,
-                               "frac": sum(flops.values()) * n / (ms_step * 1e-3) / 1e12 / peak},
-                "hbm_peak_gbs": pk["hbm_gbs"]}
+    roof, stages = roofline_of(cx, stage, n, len(chunks), max(args.steps, 1), ms_step)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_baseline(args.cpu_windows)
-    if rank == 0:
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "windows_per_gpu": n, "seq_len": T, "bn_group": BATCH,
-                           "n_classes": NCLASS, "chunks_per_step": len(chunks),
-                           "l2": "inputs (%.0f MB) and activations larger than L2" % (x.nbytes / 1e6),
-                           "parallelism": "reads sharded over %d GPU(s), no collective" % world},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": int(n_launch), "roofline": roof,
-                "roofline_stages": stages, "cpu_baseline": cpu}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "windows_per_gpu": n, "seq_len": T, "bn_group": BATCH,
+                       "n_classes": NCLASS, "chunks_per_step": len(chunks),
+                       "l2": "inputs (%.0f MB) and activations larger than L2" % (x.nbytes / 1e6),
+                       "parallelism": "independent replicas: every rank runs its own windows on %d GPU(s), no collective" % world},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(n_launch), "roofline": roof,
+            "roofline_stages": stages, "cpu_baseline": cpu}
+    del x_d, lens_d, labels_d, llen_d
+    return line
+
+
+# ---------------------------------------------------------------------------- the sharded read set (configs[1] + [3])
+READSET = {"n_reads": 65536, "seed": 20, "mu_samples": 40000.0, "sigma": 0.8, "clip": (2000, 400000)}
+
+
+def make_read_set(total_windows, step):
+    """65 536 read lengths ~ LogNormal(ln 40 000, 0.8) clipped to [2 000, 400 000] samples
+    (seed 20).  One bench step can not take all of them (36 M windows at step 100 = a minute per step on one GPU), so
+    the job is the first reads of that set whose windows add up to ``total_windows`` (the last one cut to fit):
+    the 1 048 576-window job of configs[1], made of config 4's variable-length reads."""
+    from nanopore_rnn_b200 import synthetic as syn
+    from nanopore_rnn_b200.job import window_counts
+    lengths = syn.lognormal_read_lengths(READSET["n_reads"], READSET["seed"], np.log(READSET["mu_samples"]),
+                                         READSET["sigma"], *READSET["clip"])
+    cum = np.cumsum(window_counts(lengths, step))
+    k = int(np.searchsorted(cum, total_windows, side="left")) + 1
+    lengths = lengths[:k].copy()
+    over = int(cum[k - 1] - total_windows) if k <= len(cum) else 0
+    if over > 0:
+        lengths[-1] -= over * step
+    return lengths
+
+
+def synth_read(read_id, length):
+    """int16 current samples of one synthetic read: N(500, 60) around a slow drift; seeded by the read id alone, so a
+    read's samples do not depend on how the set is sharded."""
+    rng = np.random.default_rng([7, int(read_id)])
+    v = rng.standard_normal(int(length), dtype=np.float32) * 60.0 + 500.0 + 20.0 * np.sin(np.arange(int(length)) * 1e-3)
+    return np.rint(v).astype(np.int16)
+
+
+def bench_reads(cx, args):
+    """Strong scaling: ONE read set, reads assigned to ranks by LPT on window counts (shard.assign_reads), each rank
+    packs its share length-sorted and runs the device-resident chain (job.ReadJob); the end-to-end leg gathers the
+    called reads to rank 0 in original read order inside the timed region (job.gather_consensus)."""
+    import torch
+    from nanopore_rnn_b200 import shard
+    from nanopore_rnn_b200.job import ReadJob, gather_consensus, window_counts
+    rank, world, dev, m = cx.rank, cx.world, cx.dev, cx.m
+    lengths = make_read_set(args.windows, args.step)
+    counts = window_counts(lengths, args.step)
+    assignment = shard.assign_reads(counts, world)
+    mine = np.asarray(assignment[rank], dtype=np.int64)
+    job = ReadJob(m, step=args.step, start_index=0, batch_size=BATCH, chunk_windows=args.chunk_windows or None)
+    plan, host = job.stage_raw([synth_read(r, lengths[r]) for r in mine])
+    read_ids = mine[plan.order]                                  # packed position -> original read index
+    samples = plan.valid_samples
+    total_samples = cx.sum_over_ranks(samples)
+    raw_d = torch.from_numpy(host).to(dev)
+    steps = max(args.steps, 1)
+
+    # ---- device-resident: samples already in HBM; pack -> forward -> assemble, CUDA events on the chain's stream
+    for _ in range(args.warmup):
+        job.run_device(raw_d, plan)
+    cx.barrier()
+    sampler = ClockSampler(cx.local)
+    sampler.start()
+    m.set_profile(True)
+    n_launch = 0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(steps):
+        job.run_device(raw_d, plan)
+        n_launch += job.last["launches"]
+    ev1.record()
+    cx.barrier()
+    clocks = sampler.finish()
+    my_ms = ev0.elapsed_time(ev1) / steps
+    ms_step = cx.max_over_ranks(my_ms)
+    per_rank_ms = cx.all_values(my_ms)
+    stage = m.stage_ms()
+    m.set_profile(False)
+    value = total_samples / (ms_step * 1e-3)
+
+    # ---- end to end: pinned host int16 samples in, called reads (FASTA bodies) of ALL ranks out on rank 0
+    e2e = None
+    if not args.no_e2e:
+        raw_e = torch.empty_like(raw_d)
+        host_t = torch.from_numpy(host)
+        gather_s = [0.0]
+        called = [None]
+
+        def e2e_step(timed):
+            raw_e.copy_(host_t, non_blocking=True)
+            cons, cons_off, status = job.run_device(raw_e, plan)
+            if timed:
+                torch.cuda.current_stream(dev).synchronize()
+                t = time.perf_counter()
+            called[0] = gather_consensus(cons, cons_off, plan.n_reads, read_ids, len(lengths), rank, world, dev)
+            if timed:
+                gather_s[0] += time.perf_counter() - t
+
+        for _ in range(2):
+            e2e_step(False)
+        cx.barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            e2e_step(True)
+        torch.cuda.synchronize()
+        cx.barrier()
+        dt = cx.max_over_ranks(time.perf_counter() - t0) / steps
+        d2h = sum(len(c) for c in called[0]) + 16 * len(lengths) + 8 if rank == 0 else 0
+        e2e = {"value": total_samples / dt, "unit": UNIT, "ms_per_step": dt * 1e3,
+               "h2d_bytes_per_step": int(cx.sum_over_ranks(host.nbytes + 16 * (plan.n_reads + 1) + 4 * len(plan.group_off))),
+               "d2h_bytes_per_step": int(cx.sum_over_ranks(d2h)),
+               "gather_ms_per_step": cx.max_over_ranks(gather_s[0]) / steps * 1e3,
+               "called_bases_per_step": int(sum(len(c) for c in called[0])) if rank == 0 else None,
+               "what": "pinned int16 samples -> H2D -> z-score/windows -> forward -> consensus assembly -> NCCL gather "
+                       "of the called reads to rank 0 -> one D2H -> original read order"}
+        if rank == 0:
+            assert all(c is not None for c in called[0]), "a read is missing from the gather"
+
+    roof, stages = roofline_of(cx, stage, plan.n_windows, len(plan.chunks), steps, my_ms)
+    win_rank = [int(v) for v in cx.all_values(float(plan.n_windows))]
+    reads_rank = [int(v) for v in cx.all_values(float(plan.n_reads))]
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu = cpu_baseline(args.cpu_windows)
+        cpu["sample"] += "; forward only (the CPU leg does not pay for z-score/windowing or the consensus assembly)"
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "%s, as ONE read set of BASELINE configs[3]: first %d reads of the 65 536-read "
+                                   "LogNormal(ln 40000, 0.8) set (SURVEY 8d config 4), %d windows in total, window step %d, "
+                                   "reads LPT-sharded over %d GPU(s), length-sorted packing"
+                                   % (WORKLOAD, len(lengths), int(counts.sum()), args.step, world),
+                       "reads": len(lengths), "total_windows": int(counts.sum()), "total_samples": int(lengths.sum()),
+                       "seq_len": T, "step": args.step, "bn_group": BATCH, "n_classes": NCLASS,
+                       "windows_per_rank": win_rank, "reads_per_rank": reads_rank,
+                       "imbalance_max_over_mean": max(win_rank) / (sum(win_rank) / len(win_rank)),
+                       "device_ms_per_rank": per_rank_ms, "chunks_per_step": len(plan.chunks),
+                       "l2": "inputs (%.0f MB int16, %.0f MB of windows) and activations larger than L2"
+                             % (host.nbytes / 1e6, plan.n_windows * T * 4 / 1e6),
+                       "parallelism": "reads sharded over %d GPU(s) by LPT on window counts; no collective on the compute "
+                                      "path, one NCCL gather of the called reads (e2e)" % world},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(n_launch), "roofline": roof,
+            "roofline_stages": stages, "cpu_baseline": cpu}
+    del raw_d
+    job._bufs.clear()
+    return line
+
+
+def run_b200(args):
+    cx = Ctx()
+    reads_ok = WL["graph"] == "CtcLoss" and WL["len_x"] == 1
+    if args.workload == "reads" and reads_ok:
+        line = bench_reads(cx, args)
+        if not args.no_replica:
+            # second key: the weak-scaling replica line of round 1 (uniform pre-windowed windows, every rank its own),
+            # device-resident only, over min(steps, 3) steps after 1 warm-up -- context for the strong-scaling value
+            cx.torch.cuda.empty_cache()
+            rl = bench_windows(cx, args, steps=min(max(args.steps, 1), 3), warmup=1, with_e2e=False, with_cpu=False)
+            line["replica_weak"] = {"value": rl["value"], "unit": UNIT, "ms_per_step": rl["ms_per_step"], "scaling": "weak",
+                                    "steps": rl["steps"], "warmup": rl["warmup"], "windows_per_gpu": rl["config"]["windows_per_gpu"],
+                                    "what": rl["config"]["parallelism"]}
+    else:
+        line = bench_windows(cx, args, args.steps, args.warmup, with_e2e=not args.no_e2e, with_cpu=not args.no_cpu)
+    if cx.rank == 0:
         print(json.dumps(line))
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+    cx.close()
     return 0
 
 

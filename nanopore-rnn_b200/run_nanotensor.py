@@ -156,29 +156,28 @@ class RunTensorflow(object):
                 except OutOfRangeError:
                     outputs.append(self.inference.process_output(prediction_list, file_path))
                     log.info(file_path)
+        elif type(self.inference) is FullSignalSequence and self.inference_model.graph_name == "CtcLoss":
+            # the device-resident chain (job.ReadJob): file bytes -> ntb_parse_signal -> ntb_pack_windows ->
+            # ntb_model_forward -> ntb_assemble_reads; the text crosses PCIe once, the called reads come back
+            # (same FASTA as dataset.process_output, dataset.py:421-432)
+            from .job import ReadJob
+            job = ReadJob(self.inference_model.model, step=self.inference.step, start_index=self.inference.start_index,
+                          batch_size=self.inference.batch_size)
+            for file_path, seq in zip(files, job.run_signal_files(files) if files else []):
+                name = os.path.splitext(os.path.basename(file_path))[0]
+                path = os.path.join(self.inference.inference_output_dir, name + ".fasta")
+                with open(path, "w+") as fasta_f:
+                    fasta_f.write(">{}\n{}\n".format(name, seq))
+                outputs.append(path)
+                log.info(file_path)
         else:
             x, lens, goff, read_off = self.inference.inference_job(files)
             preds, _ = self.inference_model.run_job(x, lens, goff)
             group_read = np.searchsorted(read_off, goff[:-1], side="right") - 1
-            if type(self.inference) is FullSignalSequence and preds and np.ndim(preds[0]) == 2:
-                # all reads of the job in one launch chain: index2base + simple_assembly + argmax on the GPU
-                # (assembly.py; same FASTA as process_output, dataset.py:421-432)
-                from . import assembly
-                names = [os.path.splitext(os.path.basename(f))[0] for f in files]
-                width = max(p.shape[1] for p in preds)        # each batch is dense to its own longest call
-                rows = np.full((int(read_off[-1]), max(width, 1)), -1, dtype=np.int32)
-                at = 0
-                for p in preds:
-                    rows[at:at + len(p), :p.shape[1]] = p
-                    at += len(p)
-                outputs.extend(assembly.write_fastas(names, rows, read_off, self.inference.inference_output_dir))
-                for file_path in files:
-                    log.info(file_path)
-            else:
-                for r, file_path in enumerate(files):
-                    mine = [preds[g] for g in np.nonzero(group_read == r)[0]]
-                    outputs.append(self.inference.process_output(mine, file_path))
-                    log.info(file_path)
+            for r, file_path in enumerate(files):
+                mine = [preds[g] for g in np.nonzero(group_read == r)[0]]
+                outputs.append(self.inference.process_output(mine, file_path))
+                log.info(file_path)
         print("Finished Inference", file=sys.stderr)
         return outputs
 

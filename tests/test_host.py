@@ -179,6 +179,72 @@ dist.destroy_process_group()
     assert "OK 7" in out.stdout
 
 
+def test_job_plan_tables_match_the_per_read_definitions():
+    """job.JobPlan: window counts / BN groups / valid samples against the plain per-read definitions
+    (dataset.py:435-445 windows, :374-377 batches), packing order = descending window count."""
+    from nanopore_rnn_b200 import engine, job
+    rng = np.random.default_rng(3)
+    lengths = np.concatenate([rng.integers(1, 5000, 40), [100, 101, 99, 300, 301, 1]])
+    for step, seq, start in ((100, 100, 0), (300, 100, 0), (30, 100, 0), (100, 100, 7)):
+        counts = job.window_counts(lengths, step, start)
+        brute_valid = 0
+        for n, c in zip(lengths, counts):
+            _, lens = dataset.windows_from_signal(np.zeros(n), seq, step, start)
+            assert len(lens) == c
+            brute_valid += int(lens.sum())
+        plan = job.JobPlan(lengths, seq, step, start, 10, 1 << 30, 1)
+        assert plan.valid_samples == brute_valid and plan.n_windows == counts.sum()
+        assert np.all(np.diff(plan.counts) <= 0) and sorted(plan.order) == list(range(len(lengths)))
+        assert np.array_equal(plan.group_off, engine.group_offsets(plan.counts, 10))
+        assert np.array_equal(np.diff(plan.read_off), lengths[plan.order])
+    assert np.array_equal(job.group_offsets_vec([0, 5, 0, 23], 10), engine.group_offsets([0, 5, 0, 23], 10))
+
+
+def test_bench_read_set_is_exact_and_sharding_independent():
+    sys.path.insert(0, ROOT)
+    import bench
+    from nanopore_rnn_b200 import job
+    for step in (100, 300):
+        lengths = bench.make_read_set(20000, step)
+        assert job.window_counts(lengths, step).sum() == 20000 and lengths.min() >= 1
+    assert np.array_equal(bench.synth_read(5, 1000), bench.synth_read(5, 1000))
+    assert not np.array_equal(bench.synth_read(5, 1000), bench.synth_read(6, 1000))
+
+
+def test_world_size_2_gloo_gather_consensus(tmp_path):
+    """job.gather_consensus over gloo with CPU tensors: the N>1 gather path of the reads workload (bench.py, e2e)."""
+    script = tmp_path / "g.py"
+    script.write_text("""
+import sys
+sys.path.insert(0, %r)
+import numpy as np, torch, torch.distributed as dist
+import nanopore_rnn_b200
+from nanopore_rnn_b200 import shard, job
+dist.init_process_group("gloo")
+r, w = dist.get_rank(), dist.get_world_size()
+counts = [5, 3, 9, 1, 1, 7, 2, 4]
+mine = shard.assign_reads(counts, w)[r]
+seqs = [("ACGT"[i %% 4] * (i + 1) + str(i)).encode() for i in mine]          # read i -> its own byte string
+order = list(reversed(range(len(mine))))                                        # any packing order
+cons = torch.from_numpy(np.frombuffer(b"".join(seqs[k] for k in order), dtype=np.uint8).copy())
+off = torch.from_numpy(np.concatenate([[0], np.cumsum([len(seqs[k]) for k in order])]).astype(np.int64))
+ids = np.asarray([mine[k] for k in order])
+out = job.gather_consensus(cons, off, len(mine), ids, len(counts), r, w, "cpu")
+if r == 0:
+    assert out == [("ACGT"[i %% 4] * (i + 1) + str(i)).encode() for i in range(len(counts))], out
+    print("OK", len(out))
+else:
+    assert out is None
+dist.barrier()
+dist.destroy_process_group()
+""" % ROOT)
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29619", str(script)],
+                         capture_output=True, text=True, timeout=240)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "OK 8" in out.stdout
+
+
 def test_list_dir_uses_the_reference_predicate(tmp_path):
     """nanotensor/utils.py:71-82: regular files whose LAST dot component equals ext (not endswith)."""
     from nanopore_rnn_b200.utils import list_dir
