@@ -381,6 +381,17 @@ def roofline_of(cx, stage, n, n_chunks, steps, ms_step):
         kname, k_ms, k_flops = "k_gemm_tc<2> (LSTM input projection GEMM, tcgen05 fp16x3)", proj_ms, flops["projection"]
         n_launch_k = n_blstm * n_chunks * steps
         tkey = "k_gemm_tc_xproj_dram_bytes_per_window"
+    elif stage4["recurrence"] > 0 and all(l["size"] <= 100 for l in net if l["type"] == "blstm"):
+        # the fused BLSTM kernel: input projection AND recurrence of a layer in one persistent CTA-pair launch, so the
+        # "recurrence" stage marks bracket exactly its launches and its FLOPs are projection + recurrence
+        kname = "k_blstm_fused (x_t.W_ih + h_{t-1}.W_hh + cell update per timestep, tcgen05 cta_group::2 fp16x3)"
+        k_ms, k_flops = stage4["recurrence"], flops["projection"] + flops["recurrence"]
+        n_launch_k = n_blstm * n_chunks * steps
+        tkey = "k_blstm_fused_dram_bytes_per_window"
+        fused_tf = k_flops * n * steps / (k_ms * 1e-3) / 1e12
+        stages["recurrence"].update({"includes": "projection (fused kernel)", "algorithmic_mflop_per_window": k_flops / 1e6,
+                                     "achieved_tflops": fused_tf, "frac": fused_tf / peak,
+                                     "tensor_pipe_frac_with_3_passes": 3 * fused_tf / peak})
     elif stage4["recurrence"] > 0:
         kname = "k_gemm_tc<2> (per-timestep recurrence GEMM h.W_hh with fused cell epilogue, tcgen05 fp16x3)"
         k_ms, k_flops = stage4["recurrence"], flops["recurrence"]
@@ -395,7 +406,7 @@ def roofline_of(cx, stage, n, n_chunks, steps, ms_step):
         if os.path.exists(tp) and WL["name"] != "signal_CRNN":
             per_window = json.load(open(tp)).get(tkey)
             if per_window:     # bytes per launch at this chunk size (ncu --set full, per window, profiles/)
-                traffic = per_window * n / n_chunks * (1.0 if proj_ms > 0 else 1.0 / (n_blstm * T))
+                traffic = per_window * n / n_chunks * (1.0 if (proj_ms > 0 or "fused" in tkey) else 1.0 / (n_blstm * T))
         roof = {"bound": "tensor", "kernel": kname,
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
                 "peak_source": pk["src"] + " (sustained bf16)",
@@ -589,10 +600,14 @@ def bench_reads(cx, args):
         gather_s = [0.0]
         called = [None]
 
+        enq_s = [0.0]
+
         def e2e_step(timed):
+            t_a = time.perf_counter()
             raw_e.copy_(host_t, non_blocking=True)
             cons, cons_off, status = job.run_device(raw_e, plan)
             if timed:
+                enq_s[0] += time.perf_counter() - t_a          # host time to enqueue the chain (the assembly's table upload waits for the forward)
                 torch.cuda.current_stream(dev).synchronize()
                 t = time.perf_counter()
             called[0] = gather_consensus(cons, cons_off, plan.n_reads, read_ids, len(lengths), rank, world, dev)
@@ -613,6 +628,7 @@ def bench_reads(cx, args):
                "h2d_bytes_per_step": int(cx.sum_over_ranks(host.nbytes + 16 * (plan.n_reads + 1) + 4 * len(plan.group_off))),
                "d2h_bytes_per_step": int(cx.sum_over_ranks(d2h)),
                "gather_ms_per_step": cx.max_over_ranks(gather_s[0]) / steps * 1e3,
+               "enqueue_ms_per_step": cx.max_over_ranks(enq_s[0]) / steps * 1e3,
                "called_bases_per_step": int(sum(len(c) for c in called[0])) if rank == 0 else None,
                "what": "pinned int16 samples -> H2D -> z-score/windows -> forward -> consensus assembly -> NCCL gather "
                        "of the called reads to rank 0 -> one D2H -> original read order"}

@@ -14,6 +14,7 @@
 #include "ntb_kernels.cuh"
 #include "ntb_lstm.cuh"
 #include "ntb_lstm_tc.cuh"
+#include "ntb_blstm_fused.cuh"
 
 namespace ntb {
 
@@ -47,6 +48,10 @@ struct LayerDev {
     GemmWeights wihw;
     const float *kernel_fw = nullptr, *kernel_bw = nullptr;   // raw TF kernels on the device
     op16_t *whh_hi = nullptr, *whh_lo = nullptr;       // tensor-core recurrence planes (ntb_lstm_tc.cuh)
+    bool fused = false;       // projection + recurrence in ONE persistent CTA-pair kernel (ntb_blstm_fused.cuh; H <= 100)
+    BlstmGeom fg;
+    op16_t *f_wih = nullptr, *f_whh = nullptr;   // its operand images
+    float *f_bias = nullptr;
     bool tc_rec = false;      // persistent tensor-core recurrence (H <= 100)
     bool step_rec = false;    // one tcgen05 GEMM per timestep (larger H; ntb_gemm_tc.cu)
     GemmWeights whhw;         // [2 dirs][4H][H] planes for step_rec
@@ -63,6 +68,7 @@ struct ntb_model {
     const float *out_w = nullptr, *out_b = nullptr;
     ntb::GemmWeights outw;
     int max_res_c = 0, max_act_c = 0, max_proj_n = 0, max_step_h = 0;
+    int fused_maxk = 0, fused_next_k = 0;   // widest input of a fused BLSTM layer / widest hand-over between two of them (16-padded)
     bool has_res = false, any_tc_rec = false;
     int64_t launches = 0;
     int profile = 0;
@@ -141,6 +147,36 @@ static int launch_lstm_tc(Ctx &cx, const LstmTcParams &p) {
     alignas(64) CUtensorMap map_x;
     NTB_TRY(make_map_xproj(&map_x, reinterpret_cast<const float *>(p.xproj), 2LL * p.n_tiles * p.T * p.H));
     k_lstm_recurrence_tc<<<grid, LSTM_TC_THREADS, smem, cx.st>>>(map_x, pp);
+    cx.count();
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+// One fused BLSTM layer: x planes (k-group-major, fp16 hi/lo) -> h as fp32 rows (`out`) or as the next layer's planes.
+static int launch_blstm_fused(Ctx &cx, const BlstmGeom &g, const op16_t *x_hi, const op16_t *x_lo, const op16_t *wih_img,
+                              const op16_t *whh_img, const float *bias, const int32_t *lens, int64_t n, int T, float *out,
+                              int ldo, op16_t *next_hi, op16_t *next_lo, int sm_count) {
+    BlstmFusedParams p{};
+    p.whh_img = whh_img; p.bias = bias; p.lens = lens; p.out = out; p.ldo = ldo;
+    p.next_hi = next_hi; p.next_lo = next_lo; p.next_K8 = 2 * ((2 * g.H + 15) / 16);
+    p.n_windows = n; p.n_pairs = cdiv(n, 256); p.T = T; p.g = g;
+    alignas(64) CUtensorMap mx_hi, mx_lo, mw_a, mw_b;
+    const int64_t xrows = (int64_t)p.n_pairs * 2 * T * g.K8 * 16;           // 128-byte rows of one x plane
+    const int64_t wrows = 2LL * 2 * g.KC * 2 * ((g.RA + g.RB) / 4);
+    NTB_TRY(make_map_rows128(&mx_hi, x_hi, xrows, 32));
+    NTB_TRY(make_map_rows128(&mx_lo, x_lo, xrows, 32));
+    NTB_TRY(make_map_rows128(&mw_a, wih_img, wrows, g.RA / 4));
+    NTB_TRY(make_map_rows128(&mw_b, wih_img, wrows, g.RB / 4));
+    static bool attr_set = false;
+    if (!attr_set) {
+        NTB_CUDA(cudaFuncSetAttribute(k_blstm_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, BF_SMEM_MAX - 1024));
+        attr_set = true;
+    }
+    const int items = 2 * p.n_pairs;                  // even; with <= sm_count/2 (even) CTA pairs a pair keeps ONE direction
+    int pairs_hw = (sm_count / 2) & ~1;
+    if (pairs_hw < 2) pairs_hw = 2;
+    const int cpairs = items < pairs_hw ? items : pairs_hw;
+    k_blstm_fused<<<2 * cpairs, BF_THREADS, (size_t)g.smem, cx.st>>>(mx_hi, mx_lo, mw_a, mw_b, p);
     cx.count();
     NTB_LAUNCH_CHECK();
     return NTB_OK;
@@ -256,6 +292,14 @@ static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &a
             gemm_tc_plan_weights(ld.wihw, 1, D, 8 * Hp, ar, prev_tc && can_tc && !no_ilv);
             ld.kernel_fw = kf; ld.kernel_bw = kb;
             ld.tc_rec = ld.wihw.valid && Hp == H && lstm_tc_supported(H);
+            // default for these shapes: projection and recurrence fused (NTB_NO_FUSED_BLSTM=1 in an ablation build
+            // selects the round-1 pair of kernels for A/B runs)
+            ld.fused = ld.tc_rec && !ntb_env("NTB_NO_FUSED_BLSTM") && blstm_fused_geom(H, D, ld.fg);
+            if (ld.fused) {
+                ld.f_wih = ar.take<op16_t>(blstm_wih_img_elems(ld.fg));
+                ld.f_whh = ar.take<op16_t>(blstm_whh_img_elems(ld.fg));
+                ld.f_bias = ar.take<float>(8 * H);
+            }
             m_prev_tc = ld.tc_rec;
             if (ld.tc_rec) {
                 ld.whh_hi = ar.take<op16_t>(lstm_tc_whh_elems(H));
@@ -270,6 +314,8 @@ static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &a
                 if (ld.tc_rec)
                     k_pack_whh_tc<<<256, 256, 0, st>>>(kf, kb, D, H, (int)align_up(H, 16), ld.whh_hi, ld.whh_lo);
                 if (ld.step_rec) gemm_tc_pack_whh(st, kf, kb, D, H, ld.whh_stage, ld.whhw);
+                if (ld.fused)
+                    k_pack_blstm_fused<<<512, 256, 0, st>>>(kf, bf, kb, bb, l.forget_bias, ld.fg, ld.f_wih, ld.f_whh, ld.f_bias);
             }
             dim = 2 * H;
         } else {
@@ -328,8 +374,17 @@ extern "C" int ntb_model_create(const ntb_model_desc *desc, void *weights_dev, i
         } else if (ld.type == NTB_LAYER_BLSTM) {
             if (ld.wihw.valid) gemm_tc_pack_weights(st, ld.wih, ld.wihw);
             if (2 * ld.size > m->max_act_c) m->max_act_c = 2 * ld.size;
-            if (8 * ld.Hp > m->max_proj_n) m->max_proj_n = 8 * ld.Hp;
-            if (ld.tc_rec) m->any_tc_rec = true;
+            if (!ld.fused && 8 * ld.Hp > m->max_proj_n) m->max_proj_n = 8 * ld.Hp;
+            if (ld.tc_rec && !ld.fused) m->any_tc_rec = true;
+            if (ld.fused) {
+                const int kin = (int)align_up(ld.in_dim, 16);
+                if (kin > m->fused_maxk) m->fused_maxk = kin;
+                const size_t at = &ld - &m->layers[0];
+                if (at + 1 < m->layers.size() && m->layers[at + 1].type == NTB_LAYER_BLSTM && m->layers[at + 1].fused) {
+                    const int kn = (int)align_up(2 * ld.size, 16);
+                    if (kn > m->fused_next_k) m->fused_next_k = kn;
+                }
+            }
             if (ld.step_rec && ld.size > m->max_step_h) m->max_step_h = ld.size;
         } else {
             if (ld.in_dim / 2 > m->max_act_c) m->max_act_c = ld.in_dim / 2;
@@ -368,6 +423,7 @@ struct Workspace {
     float *cstate;
     float *logits;
     GemmScratch gs;
+    op16_t *fx_hi = nullptr, *fx_lo = nullptr;   // second set of x planes of the fused BLSTM layers (the first is gs.a_hi / a_lo)
 };
 
 static int64_t plan_workspace(const ntb_model *m, int64_t n, int64_t n_groups, bool own_logits, Arena &ar,
@@ -401,7 +457,16 @@ static int64_t plan_workspace(const ntb_model *m, int64_t n, int64_t n_groups, b
     if (m->F_final > maxk) maxk = m->F_final;
     // the per-timestep recurrence keeps its h operand planes (2 parities x 2 dirs x padded windows x H) in the same scratch
     const int64_t step_rows = m->max_step_h ? cdiv(4 * align_up(n, 256) * m->max_step_h, align_up(maxk, 8)) : 0;
-    gemm_tc_plan_scratch(ws.gs, rows, m->T, maxk, ar, tile_rows > step_rows ? tile_rows : step_rows);
+    if (m->fused_maxk > maxk) maxk = m->fused_maxk;
+    // fused BLSTM layers read their input as k-group-major planes of whole 256-window tile pairs
+    const int64_t fused_rows = m->fused_maxk ? cdiv(blstm_plane_elems(n, m->T, m->fused_maxk), align_up(maxk, 8)) : 0;
+    int64_t min_rows = tile_rows > step_rows ? tile_rows : step_rows;
+    if (fused_rows > min_rows) min_rows = fused_rows;
+    gemm_tc_plan_scratch(ws.gs, rows, m->T, maxk, ar, min_rows);
+    if (m->fused_next_k) {
+        ws.fx_hi = ar.take<op16_t>(blstm_plane_elems(n, m->T, m->fused_next_k));
+        ws.fx_lo = ar.take<op16_t>(blstm_plane_elems(n, m->T, m->fused_next_k));
+    }
     ws.bn_part2 = nullptr;
     if (m->has_res && ws.gs.valid && m->T >= 32) {
         ws.bn_part = ar.take<float2>(gemm_tc_bn_part_elems(ws.gs, m->max_res_c));
@@ -504,7 +569,8 @@ static int residual_forward(Ctx &cx, ntb_model *m, const LayerDev &ld, const flo
         const bool bn1 = k1 || ld.bn_scale[0];
         *got_layout = want_layout;
         return gemm_tc_combine(cx.st, k1 ? in : ws.y1, k1, bn1 ? aa[0] : nullptr, bn1 ? bb[0] : nullptr, ys[3], aa[3], bb[3],
-                               ws.win_group, T, C, rows, want_layout ? nullptr : out, &ws.gs, want_layout, &cx.launches);
+                               ws.win_group, T, C, rows, want_layout ? nullptr : out, &ws.gs, want_layout, &cx.launches,
+                               ws.gs.a_hi, ws.gs.a_lo);
     }
     const int64_t total4 = rows * C / 4;
     k_residual_combine<<<elementwise_grid(total4, m->sm_count), 256, 0, cx.st>>>(
@@ -548,7 +614,8 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
     const size_t nl = m->layers.size();
     const bool small_c = m->C <= 8;
     const LayerDev *fused_fnn = nullptr;
-    int planes = 0;   // the GEMM operand planes hold the current activation: 1 plain rows, 2 time-major tiles
+    int planes = 0;   // the GEMM operand planes hold the current activation: 1 plain rows, 2 time-major tiles,
+                      // 3 k-group-major tiles in the scratch planes, 4 the same in the fx planes (fused BLSTM layers)
     for (size_t li = 0; li < nl; ++li) {
         const LayerDev &ld = m->layers[li];
         float *out = ws.act[flip];
@@ -558,6 +625,7 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
             if (li + 1 < nl && ws.gs.valid) {
                 const LayerDev &nx = m->layers[li + 1];
                 if (nx.type == NTB_LAYER_RESIDUAL && nx.convw[0].valid && nx.convw[1].valid) want = 1;
+                else if (nx.type == NTB_LAYER_BLSTM && nx.fused) want = 3;
                 else if (nx.type == NTB_LAYER_BLSTM && nx.tc_rec) want = 2;
             }
             int got = 0;
@@ -567,6 +635,24 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
         } else if (ld.type == NTB_LAYER_BLSTM) {
             NTB_TRY(mark(1));
             const int N = 8 * ld.Hp;
+            if (ld.fused) {
+                if (!ws.gs.valid) return fail(NTB_EINVAL, "blstm: operand planes missing for the fused tensor-core path%s", "");
+                // x planes: set 0 = the GEMM scratch planes, set 1 = fx; a layer reads one set and hands h to the other
+                op16_t *xin_hi = ws.gs.a_hi, *xin_lo = ws.gs.a_lo;
+                if (planes == 4) { xin_hi = ws.fx_hi; xin_lo = ws.fx_lo; }
+                else if (planes != 3) NTB_TRY(gemm_tc_split_kmajor(cx.st, cur, dim, n, T, dim, xin_hi, xin_lo, &cx.launches));
+                NTB_TRY(mark(2));
+                const bool feed = li + 1 < nl && m->layers[li + 1].type == NTB_LAYER_BLSTM && m->layers[li + 1].fused;
+                op16_t *nx_hi = nullptr, *nx_lo = nullptr;
+                if (feed) { nx_hi = planes == 4 ? ws.gs.a_hi : ws.fx_hi; nx_lo = planes == 4 ? ws.gs.a_lo : ws.fx_lo; }
+                NTB_TRY(launch_blstm_fused(cx, ld.fg, xin_hi, xin_lo, ld.f_wih, ld.f_whh, ld.f_bias, lens, n, T,
+                                           feed ? nullptr : out, 2 * ld.size, nx_hi, nx_lo, m->sm_count));
+                dim = 2 * ld.size;
+                planes = feed ? (planes == 4 ? 3 : 4) : 0;
+                cur = out;
+                flip ^= 1;
+                continue;
+            }
             if (ld.tc_rec) {
                 // the packed projection weights are pre-scaled for this recurrence: no SIMT detour from here
                 if (!ws.gs.valid) return fail(NTB_EINVAL, "blstm: operand planes missing for the tensor-core path%s", "");
@@ -1383,9 +1469,23 @@ struct BlstmOpBufs {
     GemmWeights wihw;
     GemmScratch gs;
     op16_t *whh_hi, *whh_lo;
+    bool fused = false;           // the model's default for these shapes: ONE fused kernel (ntb_blstm_fused.cuh)
+    BlstmGeom fg;
+    op16_t *f_wih = nullptr, *f_whh = nullptr, *fx_hi = nullptr, *fx_lo = nullptr;
+    float *f_bias = nullptr;
 };
 static int64_t plan_blstm_op(Arena &ar, int64_t n, int T, int D, int H, BlstmOpBufs &b) {
     const int Hp = pad_hidden(H);
+    b.fused = Hp == H && lstm_tc_supported(H) && D % 8 == 0 && D >= 64 && !ntb_env("NTB_NO_FUSED_BLSTM") &&
+              blstm_fused_geom(H, D, b.fg);
+    if (b.fused) {
+        b.f_wih = ar.take<op16_t>(blstm_wih_img_elems(b.fg));
+        b.f_whh = ar.take<op16_t>(blstm_whh_img_elems(b.fg));
+        b.f_bias = ar.take<float>(8 * H);
+        b.fx_hi = ar.take<op16_t>(blstm_plane_elems(n, T, D));
+        b.fx_lo = ar.take<op16_t>(blstm_plane_elems(n, T, D));
+        return ar.off;
+    }
     b.wih = ar.take<float>((int64_t)D * 8 * Hp);
     b.bias = ar.take<float>(8 * Hp);
     b.whh = ar.take<float>(2LL * H * Hp * 4);
@@ -1431,6 +1531,16 @@ extern "C" int ntb_blstm(const float *in_dev, const int32_t *len_dev, const floa
     plan_blstm_op(ar, n_windows, T, D, H, b);
     if (!workspace_dev || !ar.ok()) return fail(NTB_ENOMEM, "ntb_blstm: workspace too small (need %s%lld)", "", (long long)ar.off);
     if (n_windows == 0) return NTB_OK;
+    if (b.fused) {
+        k_pack_blstm_fused<<<512, 256, 0, cx.st>>>(kernel_fw_dev, bias_fw_dev, kernel_bw_dev, bias_bw_dev, forget_bias, b.fg,
+                                                   b.f_wih, b.f_whh, b.f_bias);
+        NTB_LAUNCH_CHECK();
+        NTB_TRY(gemm_tc_split_kmajor(cx.st, in_dev, D, n_windows, T, D, b.fx_hi, b.fx_lo, &cx.launches));
+        int sms = 148;
+        { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+        return launch_blstm_fused(cx, b.fg, b.fx_hi, b.fx_lo, b.f_wih, b.f_whh, b.f_bias, len_dev, n_windows, T, out_dev,
+                                  2 * H, nullptr, nullptr, sms);
+    }
     k_repack_lstm<<<256, 256, 0, cx.st>>>(kernel_fw_dev, bias_fw_dev, kernel_bw_dev, bias_bw_dev, forget_bias, D, H, Hp,
                                           b.wih, b.bias, b.whh, ((b.tc && b.gs.valid) || b.step) ? 1 : 0);
     NTB_LAUNCH_CHECK();

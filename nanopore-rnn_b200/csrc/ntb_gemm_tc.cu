@@ -813,6 +813,8 @@ struct SplitParams {
     op16_t *hi, *lo;  // [plane_rows][K]
     int64_t plane_rows;
     int perm;                // 1: plane row (tile*T + t)*128 + wl <- source row (tile*128 + wl)*T + t
+                             // 2: same rows, k-group-major tiles [tile][t][K8p][128][8] (fused BLSTM kernel, ntb_blstm_fused.cuh)
+    int K8p;                 // perm 2: 8-channel groups per (tile, t) = 2 * ceil(K / 16); groups >= K / 8 are zero
     int expand;              // 1: A is [rows] (a Cin = 1 conv folded into the affine): v[c] = A[r] * a[g][c] + b[g][c]
 };
 
@@ -861,6 +863,18 @@ __global__ void __launch_bounds__(256) k_split_op16(const SplitParams p) {
         }
         uint4 h, l;
         ptx::split_op16x8(v, h, l);
+        if (p.perm == 2) {
+            const int64_t o = (((pr >> 7) * p.K8p + (c >> 3)) * 128 + (pr & 127)) * 8;
+            *reinterpret_cast<uint4 *>(p.hi + o) = h;
+            *reinterpret_cast<uint4 *>(p.lo + o) = l;
+            if (c + 8 == p.K)
+                for (int g = K8; g < p.K8p; ++g) {
+                    const int64_t oz = (((pr >> 7) * p.K8p + g) * 128 + (pr & 127)) * 8;
+                    *reinterpret_cast<uint4 *>(p.hi + oz) = make_uint4(0, 0, 0, 0);
+                    *reinterpret_cast<uint4 *>(p.lo + oz) = make_uint4(0, 0, 0, 0);
+                }
+            continue;
+        }
         *reinterpret_cast<uint4 *>(p.hi + pr * p.K + c) = h;
         if (p.lo) *reinterpret_cast<uint4 *>(p.lo + pr * p.K + c) = l;
     }
@@ -934,8 +948,50 @@ struct CombineParams {
     float *out;                      // fp32 [rows][C] or null
     op16_t *hi, *lo;          // planes or null
     int64_t plane_rows;              // = rows unless perm (whole 128-window tiles)
-    int perm;
+    int perm;                        // 1: time-major tiles, 2: k-group-major tiles (SplitParams::perm)
+    int K8p;
 };
+
+// relu( bn?(branch1) + bn(conv2c) ) of 8 channels c..c+7 of source row r (window w)
+__device__ __forceinline__ void combine_values(const CombineParams &p, int64_t r, int64_t w, int c, float (&v)[8]) {
+    const int g = p.win_group[w];
+    float a2[8], b2[8];
+    {
+        const float4 *pa = reinterpret_cast<const float4 *>(p.a2 + (int64_t)g * p.C + c);
+        const float4 *pb = reinterpret_cast<const float4 *>(p.b2 + (int64_t)g * p.C + c);
+        const float4 a0 = __ldg(pa), a1 = __ldg(pa + 1), b0 = __ldg(pb), b1 = __ldg(pb + 1);
+        a2[0] = a0.x; a2[1] = a0.y; a2[2] = a0.z; a2[3] = a0.w; a2[4] = a1.x; a2[5] = a1.y; a2[6] = a1.z; a2[7] = a1.w;
+        b2[0] = b0.x; b2[1] = b0.y; b2[2] = b0.z; b2[3] = b0.w; b2[4] = b1.x; b2[5] = b1.y; b2[6] = b1.z; b2[7] = b1.w;
+    }
+    const float4 y0 = *reinterpret_cast<const float4 *>(p.y2 + r * p.C + c);
+    const float4 y1 = *reinterpret_cast<const float4 *>(p.y2 + r * p.C + c + 4);
+    const float yy[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+    float u[8];
+    if (p.y1_scalar) {
+        const float xv = __ldg(p.y1 + r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) u[j] = xv;
+    } else {
+        const float4 u0 = *reinterpret_cast<const float4 *>(p.y1 + r * p.C + c);
+        const float4 u1 = *reinterpret_cast<const float4 *>(p.y1 + r * p.C + c + 4);
+        u[0] = u0.x; u[1] = u0.y; u[2] = u0.z; u[3] = u0.w; u[4] = u1.x; u[5] = u1.y; u[6] = u1.z; u[7] = u1.w;
+    }
+    if (p.a1) {
+        const float4 *pa = reinterpret_cast<const float4 *>(p.a1 + (int64_t)g * p.C + c);
+        const float4 *pb = reinterpret_cast<const float4 *>(p.b1 + (int64_t)g * p.C + c);
+        const float4 a0 = __ldg(pa), a1 = __ldg(pa + 1), b0 = __ldg(pb), b1 = __ldg(pb + 1);
+        const float aa[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) u[j] = u[j] * aa[j] + bb[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = fmaxf(u[j] + (yy[j] * a2[j] + b2[j]), 0.0f);
+    if (p.out) {
+        *reinterpret_cast<float4 *>(p.out + r * p.C + c) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4 *>(p.out + r * p.C + c + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    }
+}
 
 __global__ void __launch_bounds__(256) k_combine_split(const CombineParams p) {
     const int K8 = p.C >> 3;
@@ -956,43 +1012,7 @@ __global__ void __launch_bounds__(256) k_combine_split(const CombineParams p) {
         }
         float v[8];
         if (r < p.rows) {
-            const int g = p.win_group[w];
-            float a2[8], b2[8];
-            {
-                const float4 *pa = reinterpret_cast<const float4 *>(p.a2 + (int64_t)g * p.C + c);
-                const float4 *pb = reinterpret_cast<const float4 *>(p.b2 + (int64_t)g * p.C + c);
-                const float4 a0 = __ldg(pa), a1 = __ldg(pa + 1), b0 = __ldg(pb), b1 = __ldg(pb + 1);
-                a2[0] = a0.x; a2[1] = a0.y; a2[2] = a0.z; a2[3] = a0.w; a2[4] = a1.x; a2[5] = a1.y; a2[6] = a1.z; a2[7] = a1.w;
-                b2[0] = b0.x; b2[1] = b0.y; b2[2] = b0.z; b2[3] = b0.w; b2[4] = b1.x; b2[5] = b1.y; b2[6] = b1.z; b2[7] = b1.w;
-            }
-            const float4 y0 = *reinterpret_cast<const float4 *>(p.y2 + r * p.C + c);
-            const float4 y1 = *reinterpret_cast<const float4 *>(p.y2 + r * p.C + c + 4);
-            const float yy[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
-            float u[8];
-            if (p.y1_scalar) {
-                const float xv = __ldg(p.y1 + r);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) u[j] = xv;
-            } else {
-                const float4 u0 = *reinterpret_cast<const float4 *>(p.y1 + r * p.C + c);
-                const float4 u1 = *reinterpret_cast<const float4 *>(p.y1 + r * p.C + c + 4);
-                u[0] = u0.x; u[1] = u0.y; u[2] = u0.z; u[3] = u0.w; u[4] = u1.x; u[5] = u1.y; u[6] = u1.z; u[7] = u1.w;
-            }
-            if (p.a1) {
-                const float4 *pa = reinterpret_cast<const float4 *>(p.a1 + (int64_t)g * p.C + c);
-                const float4 *pb = reinterpret_cast<const float4 *>(p.b1 + (int64_t)g * p.C + c);
-                const float4 a0 = __ldg(pa), a1 = __ldg(pa + 1), b0 = __ldg(pb), b1 = __ldg(pb + 1);
-                const float aa[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-#pragma unroll
-                for (int j = 0; j < 8; ++j) u[j] = u[j] * aa[j] + bb[j];
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = fmaxf(u[j] + (yy[j] * a2[j] + b2[j]), 0.0f);
-            if (p.out) {
-                *reinterpret_cast<float4 *>(p.out + r * p.C + c) = make_float4(v[0], v[1], v[2], v[3]);
-                *reinterpret_cast<float4 *>(p.out + r * p.C + c + 4) = make_float4(v[4], v[5], v[6], v[7]);
-            }
+            combine_values(p, r, w, c, v);
         } else {
 #pragma unroll
             for (int j = 0; j < 8; ++j) v[j] = 0.0f;
@@ -1000,9 +1020,60 @@ __global__ void __launch_bounds__(256) k_combine_split(const CombineParams p) {
         if (p.hi) {
             uint4 h, l;
             ptx::split_op16x8(v, h, l);
-            *reinterpret_cast<uint4 *>(p.hi + pr * p.C + c) = h;
-            *reinterpret_cast<uint4 *>(p.lo + pr * p.C + c) = l;
+            if (p.perm == 2) {
+                const int64_t o = (((pr >> 7) * p.K8p + (c >> 3)) * 128 + (pr & 127)) * 8;
+                *reinterpret_cast<uint4 *>(p.hi + o) = h;
+                *reinterpret_cast<uint4 *>(p.lo + o) = l;
+                if (c + 8 == p.C)
+                    for (int g = K8; g < p.K8p; ++g) {
+                        const int64_t oz = (((pr >> 7) * p.K8p + g) * 128 + (pr & 127)) * 8;
+                        *reinterpret_cast<uint4 *>(p.hi + oz) = make_uint4(0, 0, 0, 0);
+                        *reinterpret_cast<uint4 *>(p.lo + oz) = make_uint4(0, 0, 0, 0);
+                    }
+            } else {
+                *reinterpret_cast<uint4 *>(p.hi + pr * p.C + c) = h;
+                *reinterpret_cast<uint4 *>(p.lo + pr * p.C + c) = l;
+            }
         }
+    }
+}
+
+// Same tail written as the fused BLSTM kernel's k-group-major planes [tile][t][K8p][128 windows][8] (C <= 256), through a
+// shared-memory transpose: a work unit = (tile, t, slab of 32 windows); reads run along the channels of a source row
+// (lane = 8-channel group, 1 KB contiguous per row), stores along the windows of a plane row group (lane = window,
+// 512 B contiguous).  Without it every 16-byte store of a warp lands 2 KB from the next one.
+__global__ void __launch_bounds__(256) k_combine_kmajor(const CombineParams p) {
+    __shared__ uint4 s_hi[32][33], s_lo[32][33];           // [channel group][window of the slab], padded: conflict-free both ways
+    const int K8 = p.C >> 3;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t n_tiles = p.plane_rows / ((int64_t)128 * p.T);
+    const int64_t units = n_tiles * p.T * 4;
+    for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
+        const int64_t tile = u / (p.T * 4);
+        const int rem = (int)(u - tile * (p.T * 4));
+        const int t = rem >> 2, wl0 = (rem & 3) * 32;
+        for (int jj = 0; jj < 4; ++jj) {
+            const int j = 4 * warp + jj;
+            const int64_t w = tile * 128 + wl0 + j, r = w * p.T + t;
+            if (lane < K8) {
+                float v[8];
+                if (r < p.rows) {
+                    combine_values(p, r, w, lane << 3, v);
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) v[k] = 0.0f;
+                }
+                ptx::split_op16x8(v, s_hi[lane][j], s_lo[lane][j]);
+            }
+        }
+        __syncthreads();
+        const int64_t base = ((tile * p.T + t) * p.K8p) * 128 + wl0 + lane;
+        for (int cg = warp; cg < p.K8p; cg += 8) {
+            const uint4 z = make_uint4(0, 0, 0, 0);
+            *reinterpret_cast<uint4 *>(p.hi + (base + (int64_t)cg * 128) * 8) = cg < K8 ? s_hi[cg][lane] : z;
+            *reinterpret_cast<uint4 *>(p.lo + (base + (int64_t)cg * 128) * 8) = cg < K8 ? s_lo[cg][lane] : z;
+        }
+        __syncthreads();
     }
 }
 
@@ -1303,6 +1374,32 @@ int make_map_xproj(void *map_out, const float *xproj, int64_t units_total) {
     return NTB_OK;
 }
 
+int make_map_rows128(void *map_out, const void *base, int64_t rows, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return fail(NTB_ECUDA, "cuTensorMapEncodeTiled entry point not found%s", "");
+    cuuint64_t dims[2] = {128, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {128};
+    cuuint32_t box[2] = {128, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn((CUtensorMap *)map_out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), dims, strides, box,
+                    estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(NTB_ECUDA, "cuTensorMapEncodeTiled (128-byte rows) failed (%s%lld) rows %lld", "", (long long)r, (long long)rows);
+    return NTB_OK;
+}
+
+int gemm_tc_split_kmajor(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, int K, op16_t *hi, op16_t *lo,
+                         int64_t *launches) {
+    if (K % 8 || (lda & 3) || (reinterpret_cast<uintptr_t>(A) & 15) || !hi || !lo)
+        return fail(NTB_EINVAL, "k-group-major split: operand not supported (K %s%lld)", "", (long long)K);
+    SplitParams sp{};
+    sp.A = A; sp.lda = lda; sp.rows = n_windows * T; sp.K = K; sp.T = T; sp.relu = 0; sp.pad = 0; sp.perm = 2;
+    sp.K8p = 2 * ((K + 15) / 16);
+    sp.hi = hi; sp.lo = lo; sp.plane_rows = align_up(n_windows, 2 * BM) * T;
+    return launch_split(st, sp, launches);
+}
+
 void gemm_tc_plan_weights(GemmWeights &w, int taps, int K, int N, Arena &ar, bool ilv) {
     w = GemmWeights();
     w.taps = taps; w.K = K; w.N = N;
@@ -1473,13 +1570,19 @@ int64_t gemm_tc_bn_part_elems(const GemmScratch &gs, int C) {
 
 int gemm_tc_combine(cudaStream_t st, const float *y1, bool y1_scalar, const float *a1, const float *b1,
                     const float *y2, const float *a2, const float *b2, const int32_t *win_group, int T, int C,
-                    int64_t rows, float *out, const GemmScratch *planes, int layout, int64_t *launches) {
+                    int64_t rows, float *out, const GemmScratch *planes, int layout, int64_t *launches,
+                    op16_t *kmajor_hi, op16_t *kmajor_lo) {
     if (C % 8 || rows % T) return fail(NTB_EINVAL, "combine: C %% 8 and whole windows required%s", "");
     CombineParams p{};
     p.y1 = y1; p.y1_scalar = y1_scalar ? 1 : 0; p.a1 = a1; p.b1 = b1; p.y2 = y2; p.a2 = a2; p.b2 = b2;
     p.win_group = win_group; p.T = T; p.C = C; p.rows = rows; p.out = out;
     p.plane_rows = rows;
-    if (planes && layout) {
+    if (layout == 3) {
+        if (!kmajor_hi || !kmajor_lo) return fail(NTB_EINVAL, "combine: k-group-major planes missing%s", "");
+        p.perm = 2; p.K8p = 2 * ((C + 15) / 16);
+        p.plane_rows = align_up(rows / T, 2 * BM) * T;
+        p.hi = kmajor_hi; p.lo = kmajor_lo;
+    } else if (planes && layout) {
         p.perm = layout == 2;
         if (p.perm) p.plane_rows = align_up(rows / T, BM) * T;
         if (!planes->valid || p.plane_rows > planes->rows_cap || C > planes->kp_cap)
@@ -1491,6 +1594,11 @@ int gemm_tc_combine(cudaStream_t st, const float *y1, bool y1_scalar, const floa
     const int64_t cap = (int64_t)sm_count() * 16;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
+    if (p.perm == 2 && C <= 256) {
+        int64_t units = p.plane_rows / 128 * 4;
+        const int64_t ucap = (int64_t)sm_count() * 8;
+        k_combine_kmajor<<<(unsigned)(units < ucap ? (units > 0 ? units : 1) : ucap), 256, 0, st>>>(p);
+    } else
     k_combine_split<<<(unsigned)blocks, 256, 0, st>>>(p);
     if (launches) ++*launches;
     NTB_LAUNCH_CHECK();

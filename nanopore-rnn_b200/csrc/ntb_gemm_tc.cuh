@@ -40,6 +40,17 @@ int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_window
                       bool planes_ready = false, void (*before_gemm)(void *) = nullptr, void *hook_arg = nullptr);
 // CUtensorMap (128 bytes, 64-byte aligned) over the projected-gates buffer for the recurrence's TMA ring.
 int make_map_xproj(void *map_out, const float *xproj, int64_t units_total);
+// CUtensorMap over a byte region seen as [rows][128 bytes] (no swizzle), box = {128 B, box_rows}: the contiguous operand
+// images of the fused BLSTM kernel (ntb_blstm_fused.cuh) are loaded as runs of whole 128-byte rows.
+int make_map_rows128(void *map_out, const void *base, int64_t rows, int box_rows);
+// fp32 activation [n_windows*T][lda] -> the fused BLSTM kernel's operand planes (fp16 hi / lo):
+// [tile of 128 windows][t][K8 groups of 8 channels][128 windows][8], K8 = 2*ceil(K/16) (pad groups zero), whole tile
+// PAIRS (windows padded to 256 with zeros).  Plane capacity: blstm_plane_elems().
+int gemm_tc_split_kmajor(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, int K, op16_t *hi, op16_t *lo,
+                         int64_t *launches);
+static inline int64_t blstm_plane_elems(int64_t n_windows, int T, int K) {
+    return align_up(n_windows, 256) * T * align_up(K, 16);
+}
 int gemm_tc_conv(cudaStream_t st, const float *A, int K, int64_t rows, int T, const float *aff_a,
                  const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
                  int ldo, const GemmScratch &gs, int64_t *launches, bool reuse_planes = false, bool expand = false,
@@ -61,11 +72,13 @@ int gemm_tc_conv_fused(cudaStream_t st, const float *y, int K, int64_t rows, int
                        const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
                        int ldo, int64_t *launches, float2 *bn_part);
 // residual_layer tail relu(bn?(branch1) + bn(conv2c)) written as fp32 (`out`, may be null) and/or straight into the
-// operand planes of the next GEMM: layout 0 = none, 1 = plain rows (next 1x1 convs), 2 = time-major tiles (projection).
+// operand planes of the next GEMM: layout 0 = none, 1 = plain rows (next 1x1 convs), 2 = time-major tiles (projection),
+// 3 = the fused BLSTM kernel's k-group-major tiles (gemm_tc_split_kmajor's layout; `kmajor_hi/lo` name the planes).
 // y1_scalar: branch1 is a Cin = 1 conv folded into (a1, b1): value = y1[r] * a1[g][c] + b1[g][c].
 int gemm_tc_combine(cudaStream_t st, const float *y1, bool y1_scalar, const float *a1, const float *b1,
                     const float *y2, const float *a2, const float *b2, const int32_t *win_group, int T, int C,
-                    int64_t rows, float *out, const GemmScratch *planes, int layout, int64_t *launches);
+                    int64_t rows, float *out, const GemmScratch *planes, int layout, int64_t *launches,
+                    op16_t *kmajor_hi = nullptr, op16_t *kmajor_lo = nullptr);
 
 // BLSTM recurrence as one tcgen05 GEMM launch per timestep (hidden sizes beyond the persistent kernel, e.g. H = 256):
 // see ntb_gemm_tc.cu.  whh = [2 dirs][4H][H] hi/lo planes (plan/pack below); xproj row-major [n*T][ldx] with column

@@ -255,6 +255,19 @@ __device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t adesc, u
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// Same with the A operand in tensor memory ("TS"): every CTA of the pair reads ITS 128 A rows from its own TMEM at
+// column `tmem_a` (16-bit elements, two per 32-bit column, K = 16 -> 8 columns).
+__device__ __forceinline__ void umma_f16_ts_pair(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                                 uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // commit: arrives on the barrier at this smem offset in every CTA of `mask` when the pair's MMAs retire
 __device__ __forceinline__ void umma_commit_pair(uint64_t *bar, uint32_t mask) {
     asm volatile(

@@ -152,9 +152,11 @@ class ReadJob(object):
                     where.append(at)
                     at += b - a + 1
                 g[:at].copy_(torch.from_numpy(np.concatenate(rel).astype(np.int32)), non_blocking=True)
+                # ONE workspace sized for the largest chunk (growing it chunk by chunk would keep two alive at once)
+                ws = m._workspace(max(m.workspace_bytes(int(plan.group_off[b] - plan.group_off[a]), b - a)
+                                      for a, b in plan.chunks))
                 for (a, b), o in zip(plan.chunks, where):
                     w0, w1 = int(plan.group_off[a]), int(plan.group_off[b])
-                    ws = m._workspace(m.workspace_bytes(w1 - w0, b - a))
                     _lib.check(self.lib.ntb_model_forward(
                         m._h, C.c_void_p(x.data_ptr() + 4 * w0 * T), C.c_void_p(lens.data_ptr() + 4 * w0),
                         C.c_void_p(g.data_ptr() + 4 * o), w1 - w0, b - a, _ptr(ws), ws.numel(), C.c_void_p(0),
