@@ -272,6 +272,30 @@ NTB_API int ntb_decode(const float *logits_dev, const int32_t *len_dev, int64_t 
                int32_t C, int32_t graph, int32_t *labels_dev, int32_t *label_len_dev,
                void *stream);
 
+/* tf.nn.ctc_greedy_decoder(logits, sequence_length, merge_repeated) with BOTH outputs (nanotensor/network.py:528-533 keeps
+ * decoded[0] and drops neg_sum_logits; chiron/chiron/chiron_rcnn_train.py:68).  logits [n_windows, T, C] float32 (the
+ * "output_layer" of the CTC graphs; blank = class C-1); labels [n_windows, T] int32 padded with -1; label_len [n_windows]
+ * (may be NULL); neg_sum_logits [n_windows] float32 = -(sum over t < len of max_c logits), accumulated in frame order in
+ * float32 as TF's CTCGreedyDecoder does (may be NULL).  Integer outputs identical to ntb_decode(graph = CTC) when
+ * merge_repeated = 1. */
+NTB_API int ntb_ctc_greedy(const float *logits_dev, const int32_t *len_dev, int64_t n_windows, int32_t T, int32_t C,
+                   int32_t merge_repeated, int32_t *labels_dev, int32_t *label_len_dev, float *neg_sum_logits_dev,
+                   void *stream);
+
+/* tf.nn.ctc_beam_search_decoder(logits, sequence_length, beam_width, top_paths, merge_repeated)
+ * (chiron/chiron/chiron_rcnn_train.py:66-67: merge_repeated=False, top_paths=k; chiron_cnn_train.py:32, train_test.py:43,83;
+ * beam_width = TF's default 100): TensorFlow 1.4's CTCBeamSearchDecoder::Step / TopPaths restated (prefix tree of beam
+ * entries that keep their identity when they leave and re-enter the beam; per frame logits - max are used AS
+ * log-probabilities, which is what TF 1.4 does; log_softmax = 1 normalises them first, the later TF behaviour).
+ * 2 <= C <= 8, beam_width <= 128, T <= 512, top_paths <= beam_width.  paths [n_windows, top_paths, T] int32 padded with
+ * -1, path_len [n_windows, top_paths], log_prob [n_windows, top_paths] float32 (-inf for a missing path).
+ * workspace: ntb_ctc_beam_workspace_bytes() bytes on the device (the prefix trees of the sequences in flight). */
+NTB_API int64_t ntb_ctc_beam_workspace_bytes(int64_t n_windows, int32_t T, int32_t beam_width);
+NTB_API int ntb_ctc_beam_search(const float *logits_dev, const int32_t *len_dev, int64_t n_windows, int32_t T, int32_t C,
+                        int32_t beam_width, int32_t top_paths, int32_t merge_repeated, int32_t log_softmax,
+                        void *workspace_dev, int64_t workspace_bytes, int32_t *paths_dev, int32_t *path_len_dev,
+                        float *log_prob_dev, void *stream);
+
 /* Dense GEMM used by the conv / projection stages, exposed for roofline measurement and
  * parity tests: out[M,N] = A[M,K] @ B[K,N] (+ bias[N]), float32 in/out.
  * impl 0 = fp32 SIMT, 1 = tcgen05 fp16x3 (TMA + TMEM), 2 = tcgen05 single-pass fp16. */

@@ -63,6 +63,9 @@ SIGNATURES = {
     "ntb_blstm": (C.c_int, [_P, _P, _P, _P, _P, _P, _F, _I64, _I32, _I32, _I32, _P, _I64, _P, _P]),
     "ntb_blstm_workspace_bytes": (_I64, [_I64, _I32, _I32, _I32]),
     "ntb_decode": (C.c_int, [_P, _P, _I64, _I32, _I32, _I32, _P, _P, _P]),
+    "ntb_ctc_greedy": (C.c_int, [_P, _P, _I64, _I32, _I32, _I32, _P, _P, _P, _P]),
+    "ntb_ctc_beam_workspace_bytes": (_I64, [_I64, _I32, _I32]),
+    "ntb_ctc_beam_search": (C.c_int, [_P, _P, _I64, _I32, _I32, _I32, _I32, _I32, _I32, _P, _I64, _P, _P, _P, _P]),
     "ntb_gemm": (C.c_int, [_P, _P, _P, _I64, _I32, _I32, _I32, _P, _I64, _P, _P]),
     "ntb_gemm_workspace_bytes": (_I64, [_I64, _I32, _I32, _I32]),
 }

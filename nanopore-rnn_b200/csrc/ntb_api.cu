@@ -15,6 +15,7 @@
 #include "ntb_lstm.cuh"
 #include "ntb_lstm_tc.cuh"
 #include "ntb_blstm_fused.cuh"
+#include "ntb_ctc.cuh"
 
 namespace ntb {
 
@@ -1579,6 +1580,60 @@ extern "C" int ntb_decode(const float *logits_dev, const int32_t *len_dev, int64
     if (n_windows == 0) return NTB_OK;
     const int64_t warps = graph == NTB_GRAPH_CROSS_ENTROPY ? n_windows * T : n_windows;
     k_decode<<<cdiv(warps, 8), 256, 0, (cudaStream_t)stream>>>(logits_dev, len_dev, n_windows, T, C, graph, labels_dev, label_len_dev);
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+// ---- CTC decoders (kernels in ntb_ctc.cuh) ----
+extern "C" int ntb_ctc_greedy(const float *logits_dev, const int32_t *len_dev, int64_t n_windows, int32_t T, int32_t C,
+                              int32_t merge_repeated, int32_t *labels_dev, int32_t *label_len_dev,
+                              float *neg_sum_logits_dev, void *stream) {
+    if (!logits_dev || !len_dev || !labels_dev || n_windows < 0 || T <= 0 || C < 2)
+        return fail(NTB_EINVAL, "ntb_ctc_greedy: bad argument%s", "");
+    NTB_TRY(check_device());
+    if (n_windows == 0) return NTB_OK;
+    k_ctc_greedy<<<cdiv(n_windows, 8), 256, 0, (cudaStream_t)stream>>>(logits_dev, len_dev, n_windows, T, C,
+                                                                      merge_repeated ? 1 : 0, labels_dev, label_len_dev,
+                                                                      neg_sum_logits_dev);
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
+static int ctc_beam_blocks(int64_t n) {
+    int sms = 148, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int64_t want = (n + CTC_WARPS - 1) / CTC_WARPS, cap = (int64_t)sms * 3;
+    return (int)(want < cap ? (want > 0 ? want : 1) : cap);
+}
+
+extern "C" int64_t ntb_ctc_beam_workspace_bytes(int64_t n_windows, int32_t T, int32_t beam_width) {
+    if (n_windows < 0 || T <= 0 || beam_width <= 0) return 0;
+    if (check_device() != NTB_OK) return 0;
+    return (int64_t)ctc_beam_blocks(n_windows) * CTC_WARPS * CTC_NODE_I32 * ((int64_t)T * beam_width + 1) * (int64_t)sizeof(int32_t);
+}
+
+extern "C" int ntb_ctc_beam_search(const float *logits_dev, const int32_t *len_dev, int64_t n_windows, int32_t T, int32_t C,
+                                   int32_t beam_width, int32_t top_paths, int32_t merge_repeated, int32_t log_softmax,
+                                   void *workspace_dev, int64_t workspace_bytes, int32_t *paths_dev,
+                                   int32_t *path_len_dev, float *log_prob_dev, void *stream) {
+    if (!logits_dev || !len_dev || !paths_dev || !path_len_dev || !log_prob_dev || n_windows < 0 || T <= 0 || T > 512 ||
+        C < 2 || C > CTC_MAXC || beam_width < 1 || beam_width > CTC_MAXW || top_paths < 1 || top_paths > beam_width)
+        return fail(NTB_EINVAL, "ntb_ctc_beam_search: bad argument (2 <= C <= 8, beam_width <= 128, T <= 512, top_paths <= beam_width)%s", "");
+    NTB_TRY(check_device());
+    if (n_windows == 0) return NTB_OK;
+    const int64_t need = ntb_ctc_beam_workspace_bytes(n_windows, T, beam_width);
+    if (!workspace_dev || workspace_bytes < need)
+        return fail(NTB_ENOMEM, "ntb_ctc_beam_search: workspace too small (need %s%lld)", "", (long long)need);
+    const size_t smem = sizeof(CtcBeamSmem) * CTC_WARPS;
+    static bool attr_set = false;
+    if (!attr_set) {
+        NTB_CUDA(cudaFuncSetAttribute(k_ctc_beam_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    k_ctc_beam_search<<<ctc_beam_blocks(n_windows), CTC_WARPS * 32, smem, (cudaStream_t)stream>>>(
+        logits_dev, len_dev, n_windows, T, C, beam_width, top_paths, merge_repeated ? 1 : 0, log_softmax ? 1 : 0,
+        (int32_t *)workspace_dev, paths_dev, path_len_dev, log_prob_dev);
     NTB_LAUNCH_CHECK();
     return NTB_OK;
 }

@@ -149,7 +149,7 @@ k_blstm_fused(const __grid_constant__ CUtensorMap map_x_hi, const __grid_constan
 
     const BlstmGeom &g = p.g;
     const int H = g.H, Hp = g.Hp, T = p.T, N = g.N, NA = g.NA;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int rank = (int)cluster_ctarank();
     const int pair = blockIdx.x >> 1, n_cpairs = gridDim.x >> 1;
     const int n_items = 2 * p.n_pairs;                         // (tile pair, direction); this CTA pair takes item, item + n_cpairs, ..
@@ -182,42 +182,51 @@ k_blstm_fused(const __grid_constant__ CUtensorMap map_x_hi, const __grid_constan
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_smem;
 
+    // shared-window addresses of the barriers and the stage ring, computed once (uniform registers in the loops below)
+    const uint32_t full_u = smem_u32(&full_bar[0]), empty_u = smem_u32(&empty_bar[0]), dfull_u = smem_u32(&d_full[0]);
+    const uint32_t drain_u = smem_u32(&drain_a), hready_u = smem_u32(&h_ready), stage_u = smem_u32(stage0);
+
     if (warp == 0) {
         // ===================== TMA producer (both CTAs: own x rows, own half of the weight rows) =====================
-        if (lane == 0) {
-            int st = 0; uint32_t ph = 0;
-            const int RS4 = (g.RA + g.RB) / 4;                 // 128-byte rows of one plane of a W_ih chunk
-            for (int item = pair; item < n_items; item += n_cpairs) {
-                const int tile = 2 * (item >> 1) + rank;
-                const int64_t wrow0 = (int64_t)(dir * 2 + rank) * g.KC * 2 * RS4;
-                for (int s = 0; s < T; ++s) {
-                    const int t = dir ? T - 1 - s : s;
-                    const int64_t xrow0 = ((int64_t)tile * T + t) * g.K8 * 16;
-                    for (int half = 0; half < 2; ++half) {
-                        const uint32_t wb = (uint32_t)(half ? g.RB : g.RA) * 32;       // bytes per plane of this half's chunk
-                        for (int kc = 0; kc < g.KC; ++kc) {
-                            mbar_wait_backoff(&empty_bar[st], ph ^ 1, 100 + st);
-                            uint8_t *sp = stage0 + (size_t)st * g.stage_bytes;
-                            if (rank == 0) mbar_expect_tx(&full_bar[st], 2u * (2u * BF_XBYTES + 2u * wb));
-                            tma_load_2d_pair(sp, &map_x_hi, &full_bar[st], 0, (int)(xrow0 + kc * 32));
-                            tma_load_2d_pair(sp + BF_XBYTES, &map_x_lo, &full_bar[st], 0, (int)(xrow0 + kc * 32));
-                            const int wr = (int)(wrow0 + (int64_t)kc * 2 * RS4) + (half ? g.RA / 4 : 0);
-                            const CUtensorMap *mw = half ? &map_w_b : &map_w_a;
-                            tma_load_2d_pair(sp + 2 * BF_XBYTES, mw, &full_bar[st], 0, wr);
-                            tma_load_2d_pair(sp + 2 * BF_XBYTES + g.wst_bytes / 2, mw, &full_bar[st], 0, wr + RS4);
-                            if (++st == g.stages) { st = 0; ph ^= 1; }
+        // the whole warp walks the loop (warp-uniform counters), one elected lane issues
+        int st = 0; uint32_t ph = 0;
+        const int RS4 = (g.RA + g.RB) / 4;                     // 128-byte rows of one plane of a W_ih chunk
+        const int wrow_base = (dir * 2 + rank) * g.KC * 2 * RS4;
+        const uint32_t wlo_off = 2u * BF_XBYTES + (uint32_t)g.wst_bytes / 2;
+        for (int item = pair; item < n_items; item += n_cpairs) {
+            const int tile = 2 * (item >> 1) + rank;
+            for (int s = 0; s < T; ++s) {
+                const int t = dir ? T - 1 - s : s;
+                const int xrow0 = (tile * T + t) * g.K8 * 16;
+                for (int half = 0; half < 2; ++half) {
+                    const uint32_t wb = (uint32_t)(half ? g.RB : g.RA) * 32;           // bytes per plane of this half's chunk
+                    const CUtensorMap *mw = half ? &map_w_b : &map_w_a;
+                    int wr = wrow_base + (half ? g.RA / 4 : 0);
+                    for (int kc = 0; kc < g.KC; ++kc, wr += 2 * RS4) {
+                        mbar_wait_u32(empty_u + 8u * st, ph ^ 1);
+                        if (elect_one()) {
+                            const uint32_t sp = stage_u + (uint32_t)st * g.stage_bytes, fb = full_u + 8u * st;
+                            if (rank == 0) mbar_expect_tx_u32(fb, 2u * (2u * BF_XBYTES + 2u * wb));
+                            tma_load_2d_pair_u32(sp, &map_x_hi, fb, 0, xrow0 + kc * 32);
+                            tma_load_2d_pair_u32(sp + BF_XBYTES, &map_x_lo, fb, 0, xrow0 + kc * 32);
+                            tma_load_2d_pair_u32(sp + 2 * BF_XBYTES, mw, fb, 0, wr);
+                            tma_load_2d_pair_u32(sp + wlo_off, mw, fb, 0, wr + RS4);
                         }
+                        __syncwarp();
+                        if (++st == g.stages) { st = 0; ph ^= 1; }
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer (leader CTA, one thread) =====================
-        if (lane == 0 && rank == 0) {
+        // ===================== MMA issuer (leader CTA; warp-uniform loop, one elected lane issues) =====================
+        if (rank == 0) {
             const uint32_t idA = idesc_f16_f32(256, g.NA), idB = idesc_f16_f32(256, g.NB);
             const uint32_t whh_u = smem_u32(whh_s);
             const uint32_t plane_b = (uint32_t)(g.RA + g.RB) * Hp * 2;                  // bytes of one W_hh plane
             const int k16n = Hp / 16;
+            const uint32_t xlbo = 2048u << 12;                                         // (LBO >> 4) << 16
+            const uint32_t stage16 = (uint32_t)g.stage_bytes >> 4;
             int st = 0; uint32_t ph = 0, ph_drain = 0, ph_h = 0;
             for (int item = pair; item < n_items; item += n_cpairs) {
                 for (int s = 0; s < T; ++s) {
@@ -225,45 +234,52 @@ k_blstm_fused(const __grid_constant__ CUtensorMap map_x_hi, const __grid_constan
                         const uint32_t R = (uint32_t)(half ? g.RB : g.RA);
                         const uint32_t d = tmem_base + (uint32_t)(half ? NA : 0);
                         const uint32_t idesc = half ? idB : idA;
+                        const uint32_t wlbo = R << 16;                                  // LBO = R * 16 bytes
                         if (half == 0) {
                             // the epilogue of the previous step has read the A half out of TMEM
-                            mbar_wait_backoff(&drain_a, ph_drain, 200);
+                            mbar_wait_u32(drain_u, ph_drain);
                             ph_drain ^= 1;
                             tc_fence_after();
                         }
                         // ---- projection: D = x_t . W_ih[:, half]
                         for (int kc = 0; kc < g.KC; ++kc) {
-                            mbar_wait(&full_bar[st], ph, 300 + st);
+                            mbar_wait_u32(full_u + 8u * st, ph);
                             tc_fence_after();
-                            const uint32_t sp = smem_u32(stage0 + (size_t)st * g.stage_bytes);
-                            const uint64_t xh = smem_desc_nosw(sp, 2048, 128), xl = smem_desc_nosw(sp + BF_XBYTES, 2048, 128);
-                            const uint64_t wh = smem_desc_nosw(sp + 2 * BF_XBYTES, R * 16, 128);
-                            const uint64_t wl = smem_desc_nosw(sp + 2 * BF_XBYTES + g.wst_bytes / 2, R * 16, 128);
-                            umma_f16_pair(d, xh, wh, idesc, kc != 0);
-                            umma_f16_pair(d, xl, wh, idesc, 1);
-                            umma_f16_pair(d, xh, wl, idesc, 1);
-                            umma_commit_pair(&empty_bar[st], 3);       // stage free in both CTAs once these retire
+                            if (elect_one()) {
+                                const uint32_t sp16 = ((stage_u & 0x3FFFFu) >> 4) + (uint32_t)st * stage16;
+                                const uint32_t xh = sp16 | xlbo, xl = (sp16 + (BF_XBYTES >> 4)) | xlbo;
+                                const uint32_t wh = (sp16 + (2 * BF_XBYTES >> 4)) | wlbo;
+                                const uint32_t wl = (sp16 + (2 * BF_XBYTES >> 4) + ((uint32_t)g.wst_bytes >> 5)) | wlbo;
+                                umma_f16_pair_w(d, xh, wh, DESC_NOSW_HI_SBO128, idesc, kc != 0);
+                                umma_f16_pair_w(d, xl, wh, DESC_NOSW_HI_SBO128, idesc, 1);
+                                umma_f16_pair_w(d, xh, wl, DESC_NOSW_HI_SBO128, idesc, 1);
+                                umma_commit_pair_u32(empty_u + 8u * st, 3);   // stage free in both CTAs once these retire
+                            }
+                            __syncwarp();
                             if (++st == g.stages) { st = 0; ph ^= 1; }
                         }
                         if (half == 0) {
                             // h_{s-1} is complete in both CTAs' TMEM (and the B half has been read out)
-                            mbar_wait_backoff(&h_ready, ph_h, 400);
+                            mbar_wait_u32(hready_u, ph_h);
                             ph_h ^= 1;
                             tc_fence_after();
                         }
                         // ---- recurrent term: D += h_{s-1} . W_hh[:, half]
-                        const uint32_t wbase = whh_u + (half ? (uint32_t)g.RA * Hp * 2 : 0u);
-                        for (int j = 0; j < k16n; ++j) {
-                            const uint32_t off = (uint32_t)j * 2 * R * 16;
-                            const uint64_t bh = smem_desc_nosw(wbase + off, R * 16, 128);
-                            const uint64_t bl = smem_desc_nosw(wbase + plane_b + off, R * 16, 128);
-                            const uint32_t ah = tmem_base + a_hi_col + (uint32_t)(8 * j);
-                            const uint32_t al = tmem_base + a_lo_col + (uint32_t)(8 * j);
-                            umma_f16_ts_pair(d, ah, bh, idesc, 1);
-                            umma_f16_ts_pair(d, al, bh, idesc, 1);
-                            umma_f16_ts_pair(d, ah, bl, idesc, 1);
+                        if (elect_one()) {
+                            const uint32_t wb16 = ((whh_u & 0x3FFFFu) + (half ? (uint32_t)g.RA * Hp * 2 : 0u)) >> 4;
+                            const uint32_t pl16 = plane_b >> 4, step16 = 2 * R;       // one k16 chunk = 2 K groups of R x 16 B
+                            for (int j = 0; j < k16n; ++j) {
+                                const uint32_t bh = (wb16 + (uint32_t)j * step16) | wlbo;
+                                const uint32_t bl = (wb16 + pl16 + (uint32_t)j * step16) | wlbo;
+                                const uint32_t ah = tmem_base + a_hi_col + (uint32_t)(8 * j);
+                                const uint32_t al = tmem_base + a_lo_col + (uint32_t)(8 * j);
+                                umma_f16_ts_pair_w(d, ah, bh, DESC_NOSW_HI_SBO128, idesc);
+                                umma_f16_ts_pair_w(d, al, bh, DESC_NOSW_HI_SBO128, idesc);
+                                umma_f16_ts_pair_w(d, ah, bl, DESC_NOSW_HI_SBO128, idesc);
+                            }
+                            umma_commit_pair_u32(dfull_u + 8u * half, 3);
                         }
-                        umma_commit_pair(&d_full[half], 3);
+                        __syncwarp();
                     }
                 }
             }

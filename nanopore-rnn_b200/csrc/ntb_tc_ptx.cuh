@@ -313,6 +313,97 @@ __device__ __forceinline__ void tmem_ld_wait_dep(uint32_t (&r)[16]) {
                  : "memory");
 }
 
+// ------------------------------------------------------------------ single-thread issue inside warp-uniform control flow
+// One lane of a fully converged warp (the same lane for the same mask every time): TMA / tcgen05.mma / tcgen05.commit
+// are issued under this predicate while the loop around them stays warp-uniform, so its counters and addresses live in
+// uniform registers -- issuing from inside `if (lane == 0)` makes the compiler re-broadcast every operand (ELECT + R2UR
+// sequences per instruction), which made the MMA issue thread of the fused BLSTM kernel the critical path.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
+// mbarrier helpers on precomputed 32-bit shared addresses (no generic -> shared conversion per call)
+__device__ __forceinline__ uint32_t mbar_try_wait_u32(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity), "r"(1000u)
+        : "memory");
+    return ok;
+}
+__device__ __forceinline__ void mbar_wait_u32(uint32_t bar, uint32_t parity) {
+    if (mbar_try_wait_u32(bar, parity)) return;
+    uint32_t spins = 0;
+    while (!mbar_try_wait_u32(bar, parity)) {
+        if (++spins > (1u << 24)) __trap();
+    }
+}
+__device__ __forceinline__ void mbar_expect_tx_u32(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair_u32(uint32_t dst, const void *tmap, uint32_t bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(tmap), "r"(bar & 0xFEFFFFFFu), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair_u32(uint32_t bar, uint32_t mask) {
+    asm volatile(
+        "{\n"
+        ".reg .b16 m;\n"
+        "cvt.u16.u32 m, %1;\n"
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], m;\n"
+        "}\n" ::"r"(bar),
+        "r"(mask)
+        : "memory");
+}
+// cta_group::2 MMAs taking the two 32-bit halves of the shared-memory descriptors (the high half of a no-swizzle
+// K-major descriptor is a constant: SBO and the version bit)
+__device__ __forceinline__ void umma_f16_pair_w(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                                uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b64 da, db;\n"
+        "mov.b64 da, {%1, %3};\n"
+        "mov.b64 db, {%2, %3};\n"
+        "setp.ne.b32 p, %5, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_f16_ts_pair_w(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_lo, uint32_t desc_hi,
+                                                   uint32_t idesc) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b64 db;\n"
+        "mov.b64 db, {%2, %3};\n"
+        "setp.ne.b32 p, 1, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], db, %4, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "r"(tmem_a), "r"(b_lo), "r"(desc_hi), "r"(idesc)
+        : "memory");
+}
+// low half of a no-swizzle K-major descriptor: (address >> 4) | (LBO >> 4) << 16; high half: SBO = 128 B, version 1
+__device__ __forceinline__ uint32_t desc_nosw_lo(uint32_t smem_addr, uint32_t lbo) {
+    return ((smem_addr & 0x3FFFF) >> 4) | (((lbo >> 4) & 0x3FFF) << 16);
+}
+constexpr uint32_t DESC_NOSW_HI_SBO128 = (128u >> 4) | (1u << 14);
+
 // ------------------------------------------------------------------ descriptors
 // K-major operand tile stored as [rows][64 fp16] (128 B per row) with the 128-byte swizzle
 // (8-row x 128 B atoms of 1024 B; 16-byte chunk c of row r lives at chunk c ^ (r & 7)), exactly
