@@ -13,8 +13,13 @@
 //   every leaf: label' = LSE(label, parent active ? (same label ? parent.blank : parent.total) : -inf) + input[label],
 //               blank' = total + input[blank], total' = LSE(blank', label');
 //   every inactive child c of a leaf b: total' = label' = input[c] + (c == b.label ? b.blank : b.total), blank' = -inf;
-//   the new beam = the beam_width best totals of both kinds (> -inf).  TF reaches the same set by pushing the leaves and
-//   then letting children evict the current bottom one at a time; only exact ties can order differently.
+//   the leaves are pushed back first (there are at most beam_width of them); then, leaf by leaf in descending OLD total,
+//   a leaf proposes its children -- only while its old total still beats the current bottom of a full beam -- and a
+//   child enters iff its total beats the current bottom, which it evicts (an evicted leaf loses its probabilities).
+//   This is TF's order-dependent procedure, kept as it is: a leaf evicted before its parent's turn is proposed again as a
+//   fresh child, loses, has its OLD probabilities reset too and therefore does not expand in this frame -- the result is
+//   not always the beam_width best totals.  The warp walks the leaves sequentially; the (<= 7) children of a leaf are
+//   evaluated by lanes, the current bottom is a warp arg-min over the live slots.
 // TopPaths: the top_paths best leaves by total, log_probability = total; merge_repeated collapses the OUTPUT labels.
 #pragma once
 #include "ntb_common.cuh"
@@ -81,9 +86,11 @@ struct CtcBeamSmem {
     int16_t parent[CTC_MAXW];                                    // entry slot of the parent if it is in the beam, else -1
     int16_t plabel[CTC_MAXW];                                    // the parent's label
     float tb[CTC_MAXW], tl[CTC_MAXW];                            // updated blank / label of the leaves
-    float cand[CTC_MAXW * CTC_MAXC];                             // totals: slot j = leaf j, slot n + b (C-1) + c = child c of b
-    int32_t cnode[CTC_MAXW * (CTC_MAXC - 1)];                    // existing (inactive) node id of a child candidate, or -1
-    int16_t rank[CTC_MAXW * CTC_MAXC];                           // new entry slot of a selected candidate, or -1
+    float tt[CTC_MAXW];                                          // updated total of the leaves
+    float lt[CTC_MAXW];                                          // live slots of the new beam: total
+    int32_t lsrc[CTC_MAXW];                                      // .. source: leaf slot j >= 0, or -(1 + b * 8 + c) for child c of leaf b
+    int16_t ord[CTC_MAXW];                                       // leaves in descending old total
+    uint8_t evicted[CTC_MAXW], disabled[CTC_MAXW];               // leaf left the beam in this frame / may not expand in this frame
     float inp[CTC_MAXC];
     uint8_t path[512];
 };
@@ -144,96 +151,109 @@ __global__ void __launch_bounds__(CTC_WARPS * 32) k_ctc_beam_search(
                 }
                 const float nbv = S.nt[cur][j] + in_blank;
                 S.tb[j] = nbv; S.tl[j] = nlv;
-                S.cand[j] = ctc_lse(nbv, nlv);
-            }
-            // ---- children that are not in the beam
-            for (int i = lane; i < n_ent * NC; i += 32) {
-                const int b = i / NC, c = i - b * NC;
-                const int32_t cn = tree[(int64_t)S.node[cur][b] * CTC_NODE_I32 + 4 + c];
-                bool active = false;
-                if (cn >= 0) active = tree[(int64_t)cn * CTC_NODE_I32 + 2] >= 0;
-                S.cnode[i] = cn;
-                S.cand[n_ent + i] = active ? -INFINITY : S.inp[c] + (c == S.label[cur][b] ? S.nb[cur][b] : S.nt[cur][b]);
+                S.tt[j] = ctc_lse(nbv, nlv);
             }
             __syncwarp();
-            // ---- the W best totals among the n_ent * C candidates
-            const int M = n_ent * C;
-            int valid = 0;
-            for (int i = lane; i < M; i += 32) valid += S.cand[i] > -INFINITY;
-            for (int o = 16; o > 0; o >>= 1) valid += __shfl_xor_sync(0xffffffffu, valid, o);
-            uint32_t thr = ctc_key(-INFINITY) + 1;        // keys >= thr are selected (all valid candidates)
-            int quota_eq = 0;                             // candidates with key == thr - 1 ... (ties): none by default
-            if (valid > W) {
-                // largest key k with count(key >= k) >= W, by bisection on the bits
-                uint32_t lo = 0, hi = 0xFFFFFFFFu;
-                while (lo < hi) {
-                    const uint32_t mid = lo + ((hi - lo) >> 1) + 1;
-                    int cnt = 0;
-                    for (int i = lane; i < M; i += 32) cnt += ctc_key(S.cand[i]) >= mid;
-                    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-                    if (cnt >= W) lo = mid; else hi = mid - 1;
-                }
-                int above = 0;
-                for (int i = lane; i < M; i += 32) above += ctc_key(S.cand[i]) > lo;
-                for (int o = 16; o > 0; o >>= 1) above += __shfl_xor_sync(0xffffffffu, above, o);
-                thr = lo + 1;
-                quota_eq = W - above;                     // ties at the threshold: the first quota_eq in slot order
-                if (lo == 0xFFFFFFFFu) { thr = lo; quota_eq = 0; }
-            }
-            // ---- ranks of the selected candidates in slot order (warp scan over chunks of 32 slots)
-            int n_new = 0, eq_seen = 0;
-            const uint32_t eq_key = thr - 1;
-            for (int i0 = 0; i0 < M; i0 += 32) {
-                const int i = i0 + lane;
-                uint32_t k = 0;
-                bool v = false;
-                if (i < M) { k = ctc_key(S.cand[i]); v = S.cand[i] > -INFINITY; }
-                const bool gt = v && k >= thr;
-                const bool eq = v && quota_eq > 0 && k == eq_key;
-                const uint32_t meq = __ballot_sync(0xffffffffu, eq);
-                const bool eq_in = eq && (eq_seen + __popc(meq & ((1u << lane) - 1))) < quota_eq;
-                eq_seen += __popc(meq);
-                const bool sel = gt || eq_in;
-                const uint32_t ms = __ballot_sync(0xffffffffu, sel);
-                if (i < M) S.rank[i] = sel ? (int16_t)(n_new + __popc(ms & ((1u << lane) - 1))) : (int16_t)-1;
-                n_new += __popc(ms);
-            }
-            __syncwarp();
-            // ---- leaves that stay / leave: entry slots in the tree
-            const int nxt = cur ^ 1;
+            // ---- the leaves go back into the (new) beam first; order of expansion: descending old total (ties: slot)
             for (int j = lane; j < n_ent; j += 32) {
-                const int r = S.rank[j];
-                tree[(int64_t)S.node[cur][j] * CTC_NODE_I32 + 2] = r;          // -1: left the beam (probabilities are dropped)
-                if (r >= 0) {
-                    S.nb[nxt][r] = S.tb[j]; S.nl[nxt][r] = S.tl[j]; S.nt[nxt][r] = S.cand[j];
-                    S.node[nxt][r] = S.node[cur][j]; S.label[nxt][r] = S.label[cur][j];
+                S.lt[j] = S.tt[j]; S.lsrc[j] = j; S.evicted[j] = 0; S.disabled[j] = 0;
+                const float me = S.nt[cur][j];
+                int r = 0;
+                for (int i = 0; i < n_ent; ++i) { const float o = S.nt[cur][i]; r += (o > me) || (o == me && i < j); }
+                S.ord[r] = (int16_t)j;
+            }
+            __syncwarp();
+            int n_live = n_ent;
+            float bmin = INFINITY;
+            int bslot = -1;
+            auto find_bottom = [&]() {          // arg-min of the live totals (ties: the highest slot), whole warp
+                float m = INFINITY; int ms = -1;
+                for (int q = lane; q < n_live; q += 32) { const float v = S.lt[q]; if (v < m || (v == m && q > ms)) { m = v; ms = q; } }
+                for (int o = 16; o > 0; o >>= 1) {
+                    const float om = __shfl_xor_sync(0xffffffffu, m, o);
+                    const int os = __shfl_xor_sync(0xffffffffu, ms, o);
+                    if (os >= 0 && (ms < 0 || om < m || (om == m && os > ms))) { m = om; ms = os; }
+                }
+                bmin = m; bslot = ms;
+            };
+            if (n_live == W) find_bottom();
+            for (int r = 0; r < n_ent; ++r) {
+                const int b = S.ord[r];
+                const float ot = S.nt[cur][b];
+                if (S.disabled[b] || !(ot > -INFINITY) || (n_live == W && !(ot > bmin))) continue;    // is_candidate(b->oldp)
+                // the children of b, one per lane
+                float tot = -INFINITY;
+                int eslot = -1;                        // slot the child's node held at the start of the frame (-1: not a leaf)
+                if (lane < NC) {
+                    const int32_t cn = tree[(int64_t)S.node[cur][b] * CTC_NODE_I32 + 4 + lane];
+                    if (cn >= 0) eslot = tree[(int64_t)cn * CTC_NODE_I32 + 2];
+                    tot = S.inp[lane] + (lane == S.label[cur][b] ? S.nb[cur][b] : S.nt[cur][b]);
+                }
+                for (int c = 0; c < NC; ++c) {
+                    const float tc = __shfl_sync(0xffffffffu, tot, c);
+                    const int es = __shfl_sync(0xffffffffu, eslot, c);
+                    // active NOW: a leaf of this frame that has not been evicted so far (an earlier child of this very
+                    // leaf may just have evicted it)
+                    const bool ac = es >= 0 && !S.evicted[es];
+                    const int rl = (es >= 0 && !ac) ? es : -1;     // a leaf that left the beam in this frame, proposed again
+                    if (ac) continue;
+                    if (tc > -INFINITY && (n_live < W || tc > bmin)) {
+                        int slot;
+                        if (n_live == W) {
+                            slot = bslot;
+                            const int src = S.lsrc[slot];
+                            if (src >= 0 && lane == 0) S.evicted[src] = 1;          // the bottom leaves the beam
+                        } else {
+                            slot = n_live++;
+                        }
+                        if (lane == 0) { S.lt[slot] = tc; S.lsrc[slot] = -(1 + b * 8 + c); }
+                        __syncwarp();
+                        if (n_live == W) find_bottom();
+                    } else if (rl >= 0) {
+                        if (lane == 0) S.disabled[rl] = 1;                          // c.oldp.Reset(): no expansion in this frame
+                        __syncwarp();
+                    }
                 }
             }
             __syncwarp();
-            // ---- children that enter: reuse the node if the tree has it, else append one
+            // ---- the new beam = the live slots
+            const int nxt = cur ^ 1;
+            for (int j = lane; j < n_ent; j += 32)
+                if (S.evicted[j]) tree[(int64_t)S.node[cur][j] * CTC_NODE_I32 + 2] = -1;   // probabilities are dropped
             int n_created = 0;
-            for (int i0 = 0; i0 < n_ent * NC; i0 += 32) {
-                const int i = i0 + lane;
-                int r = -1;
+            for (int s0 = 0; s0 < n_live; s0 += 32) {
+                const int q = s0 + lane;
+                int src = 0, bb = 0, cc = 0;
                 int32_t cn = -1;
-                if (i < n_ent * NC) { r = S.rank[n_ent + i]; cn = S.cnode[i]; }
-                const bool need = r >= 0 && cn < 0;
+                bool child = false;
+                if (q < n_live) {
+                    src = S.lsrc[q];
+                    child = src < 0;
+                    if (child) { const int code = -src - 1; bb = code >> 3; cc = code & 7; cn = tree[(int64_t)S.node[cur][bb] * CTC_NODE_I32 + 4 + cc]; }
+                }
+                const bool need = child && cn < 0;
                 const uint32_t mn = __ballot_sync(0xffffffffu, need);
-                if (r >= 0) {
-                    const int b = i / NC, c = i - b * NC;
-                    if (need) {
-                        cn = n_nodes + n_created + __popc(mn & ((1u << lane) - 1));
-                        int32_t *nd = tree + (int64_t)cn * CTC_NODE_I32;
-                        nd[0] = S.node[cur][b]; nd[1] = c;
-                        for (int q = 0; q < 8; ++q) nd[4 + q] = -1;
-                        tree[(int64_t)S.node[cur][b] * CTC_NODE_I32 + 4 + c] = cn;
+                if (q < n_live) {
+                    if (!child) {
+                        S.nb[nxt][q] = S.tb[src]; S.nl[nxt][q] = S.tl[src]; S.nt[nxt][q] = S.lt[q];
+                        S.node[nxt][q] = S.node[cur][src]; S.label[nxt][q] = S.label[cur][src];
+                        tree[(int64_t)S.node[cur][src] * CTC_NODE_I32 + 2] = q;
+                    } else {
+                        if (need) {
+                            cn = n_nodes + n_created + __popc(mn & ((1u << lane) - 1));
+                            int32_t *nd = tree + (int64_t)cn * CTC_NODE_I32;
+                            nd[0] = S.node[cur][bb]; nd[1] = cc;
+                            for (int z = 0; z < 8; ++z) nd[4 + z] = -1;
+                            tree[(int64_t)S.node[cur][bb] * CTC_NODE_I32 + 4 + cc] = cn;
+                        }
+                        tree[(int64_t)cn * CTC_NODE_I32 + 2] = q;
+                        S.nb[nxt][q] = -INFINITY; S.nl[nxt][q] = S.lt[q]; S.nt[nxt][q] = S.lt[q];
+                        S.node[nxt][q] = cn; S.label[nxt][q] = (int8_t)cc;
                     }
-                    tree[(int64_t)cn * CTC_NODE_I32 + 2] = r;
-                    S.nb[nxt][r] = -INFINITY; S.nl[nxt][r] = S.cand[n_ent + i]; S.nt[nxt][r] = S.cand[n_ent + i];
-                    S.node[nxt][r] = cn; S.label[nxt][r] = (int8_t)c;
                 }
                 n_created += __popc(mn);
             }
+            const int n_new = n_live;
             n_nodes += n_created;
             n_ent = n_new;
             cur = nxt;
