@@ -120,7 +120,7 @@ class BuildGraph(object):
         flat = []
         for f in flist:      # the driver passes [self.inference_opts] (a nested list)
             flat.extend(f if isinstance(f, (list, tuple)) else [f])
-        want_logits = any(f.name == "output_layer" for f in flat)
+        want_logits = any(f.name in ("output_layer", "neg_sum_logits", "beam_prediction") for f in flat)
         x = np.ascontiguousarray(x, dtype=np.float32)
         seq_len = np.ascontiguousarray(seq_len, dtype=np.int32)
         n = len(x)
@@ -219,9 +219,25 @@ class CtcLoss(BuildGraph):
             learning_rate=learning_rate, seq_len=seq_len, forget_bias=forget_bias, reuse=reuse, mode=mode,
             y_shape=y_shape, x_shape=x_shape, seq_shape=seq_shape, len_x=len_x, len_y=len_y,
             summary_name=summary_name, dataset=dataset, **kw)
+        self.neg_sum_logits = Fetch(self, "neg_sum_logits")
+        self.beam_prediction = Fetch(self, "beam_prediction")       # (decoded list, log_probabilities)
+        self.beam_width, self.top_paths = 100, 1
 
     def _prediction(self, labels, llen, a, b):
         return ctc_dense(labels[a:b], llen[a:b])
+
+    def _value(self, name, x, seq_len, labels, llen, logits, y):
+        """Two more fetches next to the reference's ``prediction``: the decoder's second output, which the reference
+        drops (``tf.nn.ctc_greedy_decoder(...)[1]``, network.py:531), and Chiron's beam-search prediction
+        (``tf.nn.ctc_beam_search_decoder(merge_repeated=False, top_paths=self.top_paths)``, chiron_rcnn_train.py:66-67)."""
+        if name in ("neg_sum_logits", "beam_prediction"):
+            from . import ctc
+            lg = logits.reshape(len(x), self.seq_len, self.len_y)
+            if name == "neg_sum_logits":
+                return ctc.ctc_greedy_decoder(lg, seq_len, merge_repeated=True, time_major=False, device=str(self.model.device))[1]
+            return ctc.ctc_beam_search_decoder(lg, seq_len, beam_width=self.beam_width, top_paths=self.top_paths,
+                                               merge_repeated=False, time_major=False, device=str(self.model.device))
+        return super(CtcLoss, self)._value(name, x, seq_len, labels, llen, logits, y)
 
     def _shape_logits(self, logits, n):
         return logits.reshape(n, self.seq_len, self.len_y)

@@ -42,6 +42,15 @@ def test_ctc_graph_prediction_shape_conventions():
     assert np.abs(out - ref_logits).max() <= 8e-3
     if np.array_equal(out.argmax(2), ref_logits.argmax(2)):
         assert pred.shape == ref_pred.shape and np.array_equal(pred, ref_pred)   # [B, max_decoded], pad -1
+    # the decoder's second output (dropped by the reference, network.py:531) and Chiron's beam-search prediction
+    import oracle_ctc as O
+    neg, (dec, logp) = graph.run_batch(x, lens, fetches=[graph.neg_sum_logits, graph.beam_prediction])
+    _, _, rneg = O.ctc_greedy(out, lens)
+    assert neg.shape == (20, 1) and np.array_equal(neg[:, 0], rneg)
+    rp, rl, rlp = O.ctc_beam_search(out[:4], lens[:4], 100, 1, False)
+    assert np.allclose(logp[:4], rlp, atol=1e-3)
+    for b in range(4):
+        assert [int(v) for v in dec[0][b] if v >= 0] == [int(v) for v in rp[b, 0, :rl[b, 0]]]
 
 
 def test_run_tensorflow_inference_and_test_routes(golden_dir, tmp_path):
