@@ -117,7 +117,10 @@ __global__ void k_pack_blstm_fused(const float *__restrict__ kernel_fw, const fl
         const float *kern = dir ? kernel_bw : kernel_fw;
         const float sc = gt == 1 ? LSTM_PRESCALE_J : LSTM_PRESCALE_IFO;
         const int Kreal = ih ? g.D : H;
-        const float v = k < Kreal ? sc * kern[(int64_t)((ih ? 0 : g.D) + k) * N + gt * H + u] : 0.0f;
+        float v = k < Kreal ? sc * kern[(int64_t)((ih ? 0 : g.D) + k) * N + gt * H + u] : 0.0f;
+        // the recurrent operand has spare K rows when H is not a multiple of 16: row H carries the bias (forget_bias
+        // folded), multiplied by a constant 1 the kernel keeps in the A operand's column of "unit H"
+        if (!ih && k == H && g.Hp > H) v = sc * ((dir ? bias_bw : bias_fw)[gt * H + u] + (gt == 2 ? forget_bias : 0.0f));
         op16_t hv, lv;
         ptx::split_op16(v, hv, lv);
         const int RS = g.RA + g.RB;
@@ -292,6 +295,29 @@ k_blstm_fused(const __grid_constant__ CUtensorMap map_x_hi, const __grid_constan
         const int n_mine = (n_hc - sub + 1) / 2;                // this warp takes hc = 2 i + sub
         const int n_def = (hc_a - sub + 1) / 2;                 // .. of which the first n_def lie in half A
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+        const uint32_t hi_w = lane_base + a_hi_col + (uint32_t)(2 * sub), lo_w = lane_base + a_lo_col + (uint32_t)(2 * sub);
+        const bool bias_mma = Hp > H;                           // the bias rides in the recurrent MMA (see k_pack_blstm_fused)
+        const uint32_t ready_u32 = smem_u32(&h_ready), drain_u32 = smem_u32(&drain_a);
+        auto arrive = [&](uint64_t *bar) { if (rank == 0) mbar_arrive(bar); else mbar_arrive_cluster(bar, 0); };
+        (void)ready_u32; (void)drain_u32;
+        // store bases: a thread's 4 units of half-chunk hc = 2 i + sub sit at column dir H + 4 hc of the layer output;
+        // in the next layer's planes that is group (dir H + 4 hc) / 8, element (dir H + 4 hc) % 8 -- with
+        // m = sub + (dir H % 8) / 4 the offset is poff0 + i * 1024 elements: constant per warp, immediate per half-chunk
+        const int cb = (dir * H) & 7, m = sub + (cb >> 2);
+        const int64_t poff0 = ((int64_t)(((dir * H) >> 3) + (m >> 1))) * 1024 + (m & 1) * 4;
+        // one-time: A-operand columns of the pad units (>= H) are zero for good, except unit H, a constant 1 whose W_hh
+        // row holds the bias
+        if (sub == 0) {
+            for (int c4 = 0; c4 < Hp; c4 += 4) tmem_st_32x4(lane_base + a_hi_col + (uint32_t)c4, 0u, 0u, 0u, 0u);
+            if (bias_mma) {
+                const uint32_t one = (H & 1) ? 0x3C000000u : 0x00003C00u;       // fp16 1.0 in unit H's half of the column
+                tmem_st_32x2(lane_base + a_hi_col + (uint32_t)(H >> 1), one, 0u);
+            }
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        asm volatile("bar.sync 1, 256;" ::: "memory");          // the 8 epilogue warps: sub 1 starts after sub 0's clears
+        tc_fence_after();
         uint32_t ph_d = 0;
         bool first = true;
         for (int item = pair; item < n_items; item += n_cpairs) {
@@ -305,28 +331,30 @@ k_blstm_fused(const __grid_constant__ CUtensorMap map_x_hi, const __grid_constan
             for (int i = 0; i < BF_MAXI; ++i)
 #pragma unroll
                 for (int u = 0; u < 4; ++u) cst[i][u] = 0.0f;
-            if (first) {
-                // h_0 = 0 (pad units stay zero for good); nothing to drain yet
-                if (sub == 0)
-                    for (int c4 = 0; c4 < Hp; c4 += 4) tmem_st_32x4(lane_base + a_hi_col + (uint32_t)c4, 0u, 0u, 0u, 0u);
-                tmem_st_wait();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) {
-                    if (rank == 0) { mbar_arrive(&drain_a); mbar_arrive(&h_ready); }
-                    else { mbar_arrive_cluster(&drain_a, 0); mbar_arrive_cluster(&h_ready, 0); }
-                }
-                first = false;
+            // h_0 = 0: every warp clears the columns it writes (the previous item's last R_B has retired: its d_full was
+            // waited for), then tells the issuer that h is ready; at kernel start there is nothing to drain either
+#pragma unroll
+            for (int i = 0; i < BF_MAXI; ++i)
+                if (i < n_mine) { tmem_st_32x2(hi_w + (uint32_t)(4 * i), 0u, 0u); tmem_st_32x2(lo_w + (uint32_t)(4 * i), 0u, 0u); }
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (first) arrive(&drain_a);
+                arrive(&h_ready);
             }
-            float *orow = p.out ? p.out + (w * T + (dir ? T - 1 : 0)) * (int64_t)p.ldo + dir * H : nullptr;
+            first = false;
+            float *orow = (p.out && exists) ? p.out + (w * T + (dir ? T - 1 : 0)) * (int64_t)p.ldo + dir * H + 4 * sub : nullptr;
             const int64_t ostep = dir ? -(int64_t)p.ldo : (int64_t)p.ldo;
             // next layer's planes: element offset of (tile, t, group, r, e) = (((tile T + t) K8n + group) 128 + r) 8 + e
-            int64_t pbase = (((int64_t)tile * T + (dir ? T - 1 : 0)) * p.next_K8 * 128 + r) * 8;
+            const int64_t pbase0 = (((int64_t)tile * T + (dir ? T - 1 : 0)) * p.next_K8 * 128 + r) * 8;
             const int64_t pstep = (dir ? -1 : 1) * (int64_t)p.next_K8 * 1024;
-            for (int s = 0; s < T; ++s, pbase += pstep) {
+            op16_t *nh = p.next_hi ? p.next_hi + pbase0 + poff0 : nullptr;
+            op16_t *nl = p.next_hi ? p.next_lo + pbase0 + poff0 : nullptr;
+            const bool pad_writer = p.next_hi && dir == 1 && sub == ((n_hc - 1) & 1) && p.next_K8 > ((2 * H) >> 3);
+            for (int s = 0; s < T; ++s) {
                 const int t = dir ? T - 1 - s : s;
                 const bool active = t < len;
-                const bool last = s == T - 1;                    // the A operand is reset to h_0 = 0 for the next item
                 uint32_t dh[BF_MAXDEF][2], dl[BF_MAXDEF][2];
                 mbar_wait(&d_full[0], ph_d, 500 + s);
                 tc_fence_after();
@@ -335,7 +363,6 @@ k_blstm_fused(const __grid_constant__ CUtensorMap map_x_hi, const __grid_constan
 #pragma unroll
                 for (int i = 0; i < BF_MAXI; ++i) {
                     if (i < n_mine) {
-                        const int hc = 2 * i + sub;
                         uint32_t a[16];
                         tmem_ld_wait_dep(acc);
 #pragma unroll
@@ -344,60 +371,60 @@ k_blstm_fused(const __grid_constant__ CUtensorMap map_x_hi, const __grid_constan
                             // this was the last read of the A half: the next step's projection may overwrite it
                             tc_fence_before();
                             __syncwarp();
-                            if (lane == 0) { if (rank == 0) mbar_arrive(&drain_a); else mbar_arrive_cluster(&drain_a, 0); }
+                            if (lane == 0) arrive(&drain_a);
                         }
                         if (i + 1 < n_mine) {
                             if (i + 1 == n_def) {                // the next half-chunk is the first of the B half
                                 mbar_wait(&d_full[1], ph_d, 600 + s);
                                 tc_fence_after();
                             }
-                            tmem_ld_32x16(lane_base + (uint32_t)(16 * (hc + 2)), acc);
+                            tmem_ld_32x16(lane_base + (uint32_t)(16 * sub + 32 * (i + 1)), acc);
                         }
                         if (i == n_def) {
                             // R_B(s) has retired: no MMA reads h_{s-1} any more -> the deferred h_s of the A half goes in
 #pragma unroll
                             for (int k = 0; k < BF_MAXDEF; ++k)
                                 if (k < n_def) {
-                                    const uint32_t c2 = (uint32_t)(2 * (2 * k + sub));
-                                    tmem_st_32x2(lane_base + a_hi_col + c2, dh[k][0], dh[k][1]);
-                                    tmem_st_32x2(lane_base + a_lo_col + c2, dl[k][0], dl[k][1]);
+                                    tmem_st_32x2(hi_w + (uint32_t)(4 * k), dh[k][0], dh[k][1]);
+                                    tmem_st_32x2(lo_w + (uint32_t)(4 * k), dl[k][0], dl[k][1]);
                                 }
                         }
-                        const float4 *b4 = reinterpret_cast<const float4 *>(bias_s + 16 * hc);
                         float hv[4];
+                        if (bias_mma) {
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            const float4 bb = b4[u];
-                            float cc = cst[i][u], hh;
-                            lstm_cell_update(__uint_as_float(a[4 * u + 0]) + bb.x, __uint_as_float(a[4 * u + 1]) + bb.y,
-                                             __uint_as_float(a[4 * u + 2]) + bb.z, __uint_as_float(a[4 * u + 3]) + bb.w, cc, hh);
-                            cst[i][u] = active ? cc : cst[i][u];
-                            hv[u] = active ? hh : 0.0f;
+                            for (int u = 0; u < 4; ++u) {
+                                float cc = cst[i][u], hh;
+                                lstm_cell_update(__uint_as_float(a[4 * u + 0]), __uint_as_float(a[4 * u + 1]),
+                                                 __uint_as_float(a[4 * u + 2]), __uint_as_float(a[4 * u + 3]), cc, hh);
+                                cst[i][u] = active ? cc : cst[i][u];
+                                hv[u] = active ? hh : 0.0f;
+                            }
+                        } else {
+                            const float4 *b4 = reinterpret_cast<const float4 *>(bias_s + 16 * (2 * i + sub));
+#pragma unroll
+                            for (int u = 0; u < 4; ++u) {
+                                const float4 bb = b4[u];
+                                float cc = cst[i][u], hh;
+                                lstm_cell_update(__uint_as_float(a[4 * u + 0]) + bb.x, __uint_as_float(a[4 * u + 1]) + bb.y,
+                                                 __uint_as_float(a[4 * u + 2]) + bb.z, __uint_as_float(a[4 * u + 3]) + bb.w, cc, hh);
+                                cst[i][u] = active ? cc : cst[i][u];
+                                hv[u] = active ? hh : 0.0f;
+                            }
                         }
                         uint32_t ph2[2], pl2[2];
                         split_pack_op16x2(hv[0], hv[1], ph2[0], pl2[0]);
                         split_pack_op16x2(hv[2], hv[3], ph2[1], pl2[1]);
-                        const uint32_t t0 = last ? 0u : ph2[0], t1 = last ? 0u : ph2[1];
-                        const uint32_t t2 = last ? 0u : pl2[0], t3 = last ? 0u : pl2[1];
                         if (i < BF_MAXDEF && i < n_def) {
-                            dh[i][0] = t0; dh[i][1] = t1; dl[i][0] = t2; dl[i][1] = t3;
+                            dh[i][0] = ph2[0]; dh[i][1] = ph2[1]; dl[i][0] = pl2[0]; dl[i][1] = pl2[1];
                         } else {
-                            tmem_st_32x2(lane_base + a_hi_col + (uint32_t)(2 * hc), t0, t1);
-                            tmem_st_32x2(lane_base + a_lo_col + (uint32_t)(2 * hc), t2, t3);
+                            tmem_st_32x2(hi_w + (uint32_t)(4 * i), ph2[0], ph2[1]);
+                            tmem_st_32x2(lo_w + (uint32_t)(4 * i), pl2[0], pl2[1]);
                         }
-                        if (p.next_hi) {         // rows of windows past the end are written too (zeros: len = 0)
-                            const int c0 = dir * H + 4 * hc;
-                            const int64_t o = pbase + (int64_t)(c0 >> 3) * 1024 + (c0 & 7);
-                            *reinterpret_cast<uint2 *>(p.next_hi + o) = make_uint2(ph2[0], ph2[1]);
-                            *reinterpret_cast<uint2 *>(p.next_lo + o) = make_uint2(pl2[0], pl2[1]);
-                            if (dir == 1 && hc == n_hc - 1)      // zero the K pad groups of the next layer's operand
-                                for (int gz = (2 * H) >> 3; gz < p.next_K8; ++gz) {
-                                    *reinterpret_cast<uint4 *>(p.next_hi + pbase + (int64_t)gz * 1024) = make_uint4(0, 0, 0, 0);
-                                    *reinterpret_cast<uint4 *>(p.next_lo + pbase + (int64_t)gz * 1024) = make_uint4(0, 0, 0, 0);
-                                }
+                        if (nh) {                // rows of windows past the end are written too (zeros: len = 0)
+                            *reinterpret_cast<uint2 *>(nh + i * 1024) = make_uint2(ph2[0], ph2[1]);
+                            *reinterpret_cast<uint2 *>(nl + i * 1024) = make_uint2(pl2[0], pl2[1]);
                         }
-                        if (orow && exists)
-                            *reinterpret_cast<float4 *>(orow + 4 * hc) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+                        if (orow) *reinterpret_cast<float4 *>(orow + 8 * i) = make_float4(hv[0], hv[1], hv[2], hv[3]);
                     }
                 }
                 if (n_mine == n_def) {
@@ -407,17 +434,26 @@ k_blstm_fused(const __grid_constant__ CUtensorMap map_x_hi, const __grid_constan
 #pragma unroll
                     for (int k = 0; k < BF_MAXDEF; ++k)
                         if (k < n_def) {
-                            const uint32_t c2 = (uint32_t)(2 * (2 * k + sub));
-                            tmem_st_32x2(lane_base + a_hi_col + c2, dh[k][0], dh[k][1]);
-                            tmem_st_32x2(lane_base + a_lo_col + c2, dl[k][0], dl[k][1]);
+                            tmem_st_32x2(hi_w + (uint32_t)(4 * k), dh[k][0], dh[k][1]);
+                            tmem_st_32x2(lo_w + (uint32_t)(4 * k), dl[k][0], dl[k][1]);
                         }
+                }
+                if (pad_writer) {                // zero the K pad groups of the next layer's operand (once per row and step)
+                    op16_t *zh = nh - poff0, *zl = nl - poff0;
+                    for (int gz = (2 * H) >> 3; gz < p.next_K8; ++gz) {
+                        *reinterpret_cast<uint4 *>(zh + (int64_t)gz * 1024) = make_uint4(0, 0, 0, 0);
+                        *reinterpret_cast<uint4 *>(zl + (int64_t)gz * 1024) = make_uint4(0, 0, 0, 0);
+                    }
                 }
                 ph_d ^= 1;
                 if (orow) orow += ostep;
-                tmem_st_wait();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) { if (rank == 0) mbar_arrive(&h_ready); else mbar_arrive_cluster(&h_ready, 0); }
+                if (nh) { nh += pstep; nl += pstep; }
+                if (s + 1 < T) {                 // after the last step the next item's reset (above) signals instead
+                    tmem_st_wait();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) arrive(&h_ready);
+                }
             }
         }
     }
