@@ -185,6 +185,19 @@ static int launch_blstm_fused(Ctx &cx, const BlstmGeom &g, const op16_t *x_hi, c
 
 static inline int pad_hidden(int H) { return (int)align_up(H, LSTM_UPT); }
 
+// Input projection of a BLSTM layer on the per-timestep recurrence (H > 100), in the unit-major layout its epilogue reads:
+// the tcgen05 GEMM with the projected-gates epilogue when the input width allows, an FMA kernel otherwise (len_x = 12).
+static int step_rec_projection(Ctx &cx, const float *in, int D, int64_t n, int T, int H, const float *wih, const float *bias,
+                               const GemmWeights &wihw, float *xproj, const GemmScratch &gs) {
+    if (wihw.valid && gs.valid)
+        return gemm_tc_run_xproj(cx.st, in, D, n, T, wihw, bias, xproj, H, gs, &cx.launches, false);
+    dim3 grid((unsigned)(align_up(n, 128) / 128 * T), 2, (unsigned)cdiv(H, 32));
+    k_xproj_unit_major<<<grid, 128, 0, cx.st>>>(in, wih, bias, n, T, D, H, reinterpret_cast<float4 *>(xproj));
+    cx.count();
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
 // Dense [rows,K] x [K,N] (+bias): tensor-core path when the packed tiles exist, SIMT otherwise.
 static int dense(Ctx &cx, const float *A, int lda, int64_t rows, int K, int N, const float *W_kn,
                  const GemmWeights *tc, const float *bias, float *out, int ldo, GemmScratch *scratch) {
@@ -444,7 +457,7 @@ static int64_t plan_workspace(const ntb_model *m, int64_t n, int64_t n_groups, b
         for (auto &a : ws.aff) a = nullptr;
     }
     // the tensor-core recurrence works on whole 128-window tiles (time-major), tail tile padded
-    const int64_t tile_rows = m->any_tc_rec ? align_up(n, LSTM_TC_ROWS) * m->T : 0;
+    const int64_t tile_rows = (m->any_tc_rec || m->max_step_h) ? align_up(n, LSTM_TC_ROWS) * m->T : 0;
     ws.xproj = m->max_proj_n ? ar.take<float>((tile_rows > rows ? tile_rows : rows) * m->max_proj_n) : nullptr;
     ws.bn_part = nullptr;   // set below, once the operand planes are sized
     ws.cstate = m->max_step_h ? ar.take<float>(gemm_tc_lstm_state_floats(n, m->max_step_h)) : nullptr;
@@ -689,7 +702,7 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
                 continue;
             } else if (ld.step_rec) {
                 if (!ws.gs.valid) return fail(NTB_EINVAL, "blstm: operand planes missing for the tensor-core path%s", "");
-                NTB_TRY(dense(cx, cur, dim, rows, dim, N, ld.wih, &ld.wihw, ld.bias, ws.xproj, N, &ws.gs));
+                NTB_TRY(step_rec_projection(cx, cur, dim, n, T, ld.size, ld.wih, ld.bias, ld.wihw, ws.xproj, ws.gs));
                 NTB_TRY(mark(2));
                 NTB_TRY(gemm_tc_lstm_layer(cx.st, ld.whhw, ws.xproj, N, lens, n, T, ld.size, ws.cstate, out, 2 * ld.size,
                                            ws.gs, &cx.launches));
@@ -1492,7 +1505,7 @@ static int64_t plan_blstm_op(Arena &ar, int64_t n, int T, int D, int H, BlstmOpB
     b.whh = ar.take<float>(2LL * H * Hp * 4);
     gemm_tc_plan_weights(b.wihw, 1, D, 8 * Hp, ar);
     b.tc = b.wihw.valid && Hp == H && lstm_tc_supported(H);
-    const int64_t rows = n * T, tile_rows = b.tc ? align_up(n, LSTM_TC_ROWS) * T : 0;
+    const int64_t rows = n * T, tile_rows = align_up(n, LSTM_TC_ROWS) * T;
     b.xproj = ar.take<float>((tile_rows > rows ? tile_rows : rows) * 8LL * Hp);
     b.whh_hi = b.whh_lo = nullptr;
     b.gs = GemmScratch();
@@ -1504,7 +1517,8 @@ static int64_t plan_blstm_op(Arena &ar, int64_t n, int T, int D, int H, BlstmOpB
         gemm_tc_plan_whh(b.whhw, H, ar, &b.whh_stage);
         b.cstate = ar.take<float>(gemm_tc_lstm_state_floats(n, H));
         const int kcap = D > H ? D : H;
-        gemm_tc_plan_scratch(b.gs, rows, T, kcap, ar, cdiv(4 * align_up(n, 256) * H, align_up(kcap, 8)));
+        const int64_t step_rows = cdiv(4 * align_up(n, 256) * H, align_up(kcap, 8));
+        gemm_tc_plan_scratch(b.gs, rows, T, kcap, ar, step_rows > tile_rows ? step_rows : tile_rows);
         b.step = b.whhw.valid && b.gs.valid;
     }
     return ar.off;
@@ -1561,7 +1575,7 @@ extern "C" int ntb_blstm(const float *in_dev, const int32_t *len_dev, const floa
         // H beyond the persistent kernel: one tcgen05 GEMM per timestep (same path the model takes)
         if (b.wihw.valid) NTB_TRY(gemm_tc_pack_weights(cx.st, b.wih, b.wihw));
         NTB_TRY(gemm_tc_pack_whh(cx.st, kernel_fw_dev, kernel_bw_dev, D, H, b.whh_stage, b.whhw));
-        NTB_TRY(dense(cx, in_dev, D, n_windows * T, D, 8 * Hp, b.wih, &b.wihw, b.bias, b.xproj, 8 * Hp, &b.gs));
+        NTB_TRY(step_rec_projection(cx, in_dev, D, n_windows, T, H, b.wih, b.bias, b.wihw, b.xproj, b.gs));
         return gemm_tc_lstm_layer(cx.st, b.whhw, b.xproj, 8 * Hp, len_dev, n_windows, T, H, b.cstate, out_dev, 2 * H, b.gs,
                                   &cx.launches);
     }

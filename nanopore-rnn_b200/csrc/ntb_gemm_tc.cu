@@ -75,9 +75,12 @@ struct TcParams {
     int lstm_H, lstm_s, lstm_mt_dir;   // hidden size, step index, M tiles per direction
     int64_t lstm_n, lstm_Mp;           // windows, windows padded to the M-tile pair
     const float *lstm_x; int lstm_ldx; // projected gates [n*T][ldx], column dir*4H + u*4 + g (bias folded, pre-scaled)
-    float *lstm_c;                     // cell state [2][n][H]
+    float *lstm_c;                     // cell state [2 dirs][128-window tile][H/4][128][4]: a warp's float4 accesses are contiguous
     const int32_t *lstm_lens;
-    op16_t *lstm_hi, *lstm_lo;  // h_t operand planes of the NEXT step [2][Mp][H]
+    op16_t *lstm_hi, *lstm_lo;         // h_t operand planes of the NEXT step, k-group-major [H/8][2 Mp rows][8] (a_kmajor)
+    int64_t lstm_xmt;                  // M tiles per direction of the projected-gates buffer = 128-window tiles x T
+    int a_kmajor;                      // the A planes are [K/8][rows][8] (no swizzle; 3-D TMA box {8, 128, 8}) instead of
+                                       // row-major rows with the 128-byte swizzle: the LSTM epilogue's h stores coalesce
 };
 
 // Column statistics of one staged [32 rows][32 cols] fp32 tile (128-byte swizzled rows): lane = column; rows
@@ -242,9 +245,12 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                         } else {
                             // both CTAs' bytes are credited to the LEADER's full barrier
                             if (rank == 0) mbar_expect_tx(&full_bar[stage], (uint32_t)(2 * stage_bytes));
-                            tma_load_2d_pair(s, &map_a_hi, &full_bar[stage], kb * BK, row0);
+                            if (p.a_kmajor) tma_load_3d_pair(s, &map_a_hi, &full_bar[stage], 0, row0, kb * (BK / 8));
+                            else tma_load_2d_pair(s, &map_a_hi, &full_bar[stage], kb * BK, row0);
                             tma_load_2d_pair(s + A_TILE_BYTES, &map_b_hi, &full_bar[stage], kb * BK, brow0);
                             if (p.passes == 3) {
+                                if (p.a_kmajor) tma_load_3d_pair(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], 0, row0, kb * (BK / 8));
+                                else
                                 tma_load_2d_pair(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], kb * BK, row0);
                                 tma_load_2d_pair(s + 2 * A_TILE_BYTES + b_tile_bytes, &map_b_lo, &full_bar[stage], kb * BK, brow0);
                             } else if (p.passes == 2) {
@@ -290,6 +296,13 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                             } else if (p.passes == 2) {     // a_lo's slot holds B'' here
                                 umma_f16(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(a_lo, k), idesc, 1);
                             }
+                        } else if (p.a_kmajor) {
+                            // A tile = [8 K groups][128 rows][8]: k16 step k starts at group 2k; LBO = one group (2 KB), SBO = 128 B
+                            const uint64_t ah = smem_desc_nosw(s + (uint32_t)k * 4096u, 2048, 128);
+                            const uint64_t al = smem_desc_nosw(s + A_TILE_BYTES + b_tile_bytes + (uint32_t)k * 4096u, 2048, 128);
+                            umma_f16_pair(d_tmem, ah, desc_advance_k16(b_hi, k), idesc, (kb | k) != 0);
+                            umma_f16_pair(d_tmem, al, desc_advance_k16(b_hi, k), idesc, 1);
+                            umma_f16_pair(d_tmem, ah, desc_advance_k16(b_lo, k), idesc, 1);
                         } else {
                             umma_f16_pair(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(b_hi, k), idesc, (kb | k) != 0);
                             if (p.passes == 3) {
@@ -384,44 +397,66 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                     }
                     if (bn_dst) bn_partials(buf, lane, bn_vmask, bn_split, bn_dst, (m_tile * 4 + q) * 2, bn_N, nb - n_org + lane);
                 } else if (p.lstm_H > 0) {
-                    // thread = one window of one direction; this chunk = 8 hidden units x (i, j, f, o)
+                    // thread = one window of one direction; this chunk = 8 hidden units x (i, j, f, o).  Every global access
+                    // of a warp is contiguous: projected gates unit-major ([..][unit][128 windows] float4, the layout the
+                    // projection's epilogue writes), cell state [..][unit / 4][128][4], h planes k-group-major -- with
+                    // row-major buffers each warp-wide 16-byte access touched 32 lines and the L1 wavefronts (576 per chunk
+                    // and warp) took three times as long as the tile's MMAs
                     const int H = p.lstm_H, nb = n0 + c0;
                     const int dir = m_tile >= p.lstm_mt_dir ? 1 : 0;
                     const int64_t w = prow - dir * p.lstm_Mp;
-                    if (w < p.lstm_n && nb < p.N) {
+                    if (w < p.lstm_n && nb < p.N) {       // pad rows of the h planes stay at their initial zero
                         const int t = dir ? p.T - 1 - p.lstm_s : p.lstm_s;
                         int len = p.lstm_lens[w];
                         len = len > p.T ? p.T : (len < 0 ? 0 : len);
                         const bool active = t < len;
-                        const int u0 = nb >> 2;
-                        const int nu = (p.N - nb >= 32 && c0 + 32 <= p.BN) ? 8 : 4;     // H % 4 == 0, BN % 16 == 0
-                        const float4 *xg = reinterpret_cast<const float4 *>(p.lstm_x + (w * p.T + t) * (int64_t)p.lstm_ldx + dir * 4 * H + nb);
-                        float *cg = p.lstm_c + ((int64_t)dir * p.lstm_n + w) * H + u0;
-                        float *og = p.out + (w * p.T + t) * (int64_t)p.ldo + dir * H + u0;
+                        const int u0 = nb >> 2;                               // 8 units (4 in the 16-column tail chunk of a tile when BN % 32 == 16)
+                        const int nu = (p.N - nb >= 32 && c0 + 32 <= p.BN) ? 8 : 4;
+                        const int64_t tile = w >> 7;
+                        const int wl = (int)(w & 127);
+                        const int64_t n_tiles = p.lstm_xmt / p.T;          // 128-window tiles of the job (not of the padded M)
+                        const float4 *xg = reinterpret_cast<const float4 *>(p.lstm_x) +
+                                           ((dir * p.lstm_xmt + tile * p.T + t) * H + u0) * (int64_t)BM + wl;
+                        float4 *cg = reinterpret_cast<float4 *>(p.lstm_c) + ((dir * n_tiles + tile) * (H >> 2) + (u0 >> 2)) * (int64_t)BM + wl;
                         float hv[8];
 #pragma unroll
                         for (int half = 0; half < 2; ++half) {
-                            if (half * 4 < nu) {
-                                const float4 c4 = *reinterpret_cast<const float4 *>(cg + 4 * half);
-                                float cc[4] = {c4.x, c4.y, c4.z, c4.w};
+                            if (half * 4 >= nu) { hv[4] = hv[5] = hv[6] = hv[7] = 0.0f; break; }
+                            const float4 c4 = cg[half * BM];
+                            float cc[4] = {c4.x, c4.y, c4.z, c4.w};
 #pragma unroll
-                                for (int u = 0; u < 4; ++u) {
-                                    const int i = 16 * half + 4 * u;
-                                    const float4 xv = __ldg(xg + 4 * half + u);
-                                    float cn = cc[u], hh;
-                                    lstm_cell_update(__uint_as_float(r[i]) + xv.x, __uint_as_float(r[i + 1]) + xv.y,
-                                                     __uint_as_float(r[i + 2]) + xv.z, __uint_as_float(r[i + 3]) + xv.w, cn, hh);
-                                    cc[u] = active ? cn : cc[u];
-                                    hv[4 * half + u] = active ? hh : 0.0f;
-                                }
-                                if (active) *reinterpret_cast<float4 *>(cg + 4 * half) = make_float4(cc[0], cc[1], cc[2], cc[3]);
-                                *reinterpret_cast<float4 *>(og + 4 * half) = make_float4(hv[4 * half], hv[4 * half + 1], hv[4 * half + 2], hv[4 * half + 3]);
-                                uint32_t ph[2], pl[2];
-                                split_pack_op16x2(hv[4 * half], hv[4 * half + 1], ph[0], pl[0]);
-                                split_pack_op16x2(hv[4 * half + 2], hv[4 * half + 3], ph[1], pl[1]);
-                                const int64_t po = (dir * p.lstm_Mp + w) * (int64_t)H + u0 + 4 * half;
-                                *reinterpret_cast<uint2 *>(p.lstm_hi + po) = make_uint2(ph[0], ph[1]);
-                                *reinterpret_cast<uint2 *>(p.lstm_lo + po) = make_uint2(pl[0], pl[1]);
+                            for (int u = 0; u < 4; ++u) {
+                                const int i = 16 * half + 4 * u;
+                                const float4 xv = __ldg(xg + (4 * half + u) * BM);
+                                float cn = cc[u], hh;
+                                lstm_cell_update(__uint_as_float(r[i]) + xv.x, __uint_as_float(r[i + 1]) + xv.y,
+                                                 __uint_as_float(r[i + 2]) + xv.z, __uint_as_float(r[i + 3]) + xv.w, cn, hh);
+                                cc[u] = active ? cn : cc[u];
+                                hv[4 * half + u] = active ? hh : 0.0f;
+                            }
+                            if (active) cg[half * BM] = make_float4(cc[0], cc[1], cc[2], cc[3]);
+                        }
+                        float *og = p.out + (w * p.T + t) * (int64_t)p.ldo + dir * H + u0;
+                        *reinterpret_cast<float4 *>(og) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+                        if (nu == 8) *reinterpret_cast<float4 *>(og + 4) = make_float4(hv[4], hv[5], hv[6], hv[7]);
+                        uint4 ph, pl;
+                        split_pack_op16x2(hv[0], hv[1], ph.x, pl.x);
+                        split_pack_op16x2(hv[2], hv[3], ph.y, pl.y);
+                        split_pack_op16x2(hv[4], hv[5], ph.z, pl.z);
+                        split_pack_op16x2(hv[6], hv[7], ph.w, pl.w);
+                        if (nu == 8 && (u0 & 7) == 0) {                      // one whole K group: 16 bytes per plane
+                            const int64_t po = ((int64_t)(u0 >> 3) * (2 * p.lstm_Mp) + prow) * 8;
+                            *reinterpret_cast<uint4 *>(p.lstm_hi + po) = ph;
+                            *reinterpret_cast<uint4 *>(p.lstm_lo + po) = pl;
+                        } else {                                             // N tiles of 208 columns: chunks start mid-group
+                            const int64_t p0 = ((int64_t)(u0 >> 3) * (2 * p.lstm_Mp) + prow) * 8 + (u0 & 7);
+                            *reinterpret_cast<uint2 *>(p.lstm_hi + p0) = make_uint2(ph.x, ph.y);
+                            *reinterpret_cast<uint2 *>(p.lstm_lo + p0) = make_uint2(pl.x, pl.y);
+                            if (nu == 8) {
+                                const int u1 = u0 + 4;
+                                const int64_t p1 = ((int64_t)(u1 >> 3) * (2 * p.lstm_Mp) + prow) * 8 + (u1 & 7);
+                                *reinterpret_cast<uint2 *>(p.lstm_hi + p1) = make_uint2(ph.z, ph.w);
+                                *reinterpret_cast<uint2 *>(p.lstm_lo + p1) = make_uint2(pl.z, pl.w);
                             }
                         }
                     }
@@ -1640,16 +1675,33 @@ int gemm_tc_pack_whh(cudaStream_t st, const float *kernel_fw, const float *kerne
     return gemm_tc_pack_weights(st, staging, w);
 }
 
-int64_t gemm_tc_lstm_state_floats(int64_t n_windows, int H) { return 2 * n_windows * H; }
+int64_t gemm_tc_lstm_state_floats(int64_t n_windows, int H) { return 2 * align_up(n_windows, BM) * H; }
 
+// 3-D view of a k-group-major operand plane [K/8][rows][8] fp16: box {8, 128 rows, 8 groups} = one [128 x 64] A tile
+static int make_map_kmajor(CUtensorMap *m, const void *base, int64_t rows, int K) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return fail(NTB_ECUDA, "cuTensorMapEncodeTiled entry point not found%s", "");
+    cuuint64_t dims[3] = {8, (cuuint64_t)rows, (cuuint64_t)(K / 8)};
+    cuuint64_t strides[2] = {16, (cuuint64_t)rows * 16};
+    cuuint32_t box[3] = {8, (cuuint32_t)BM, (cuuint32_t)(BK / 8)};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void *>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(NTB_ECUDA, "cuTensorMapEncodeTiled (k-group-major plane) failed (%s%lld) rows %lld", "", (long long)r, (long long)rows);
+    return NTB_OK;
+}
+
+// xproj: the unit-major projected-gates buffer gemm_tc_run_xproj writes ([dir][128-window tile x T + t][unit][128] float4)
 int gemm_tc_lstm_layer(cudaStream_t st, const GemmWeights &whh, const float *xproj, int ldx, const int32_t *lens,
                        int64_t n_windows, int T, int H, float *cstate, float *out, int ldo, const GemmScratch &gs,
                        int64_t *launches) {
     const int cg = gemm_cta_group();
     const int64_t Mp = align_up(n_windows, 2 * BM);                 // a CTA pair never straddles the directions
     const int64_t plane_elems = 2 * Mp * H;                          // one parity: [2 dirs][Mp][H]
-    if (!whh.valid || !gs.valid || whh.K != H || whh.N != 4 * H || whh.BN % 16 ||
-        2 * plane_elems > gs.rows_cap * (int64_t)gs.kp_cap || (ldx & 3) || (ldo & 3) || H % 8)
+    if (!whh.valid || !gs.valid || whh.K != H || whh.N != 4 * H || whh.BN % 16 || cg != 2 ||
+        2 * plane_elems > gs.rows_cap * (int64_t)gs.kp_cap || (ldo & 3) || H % 8)
         return fail(NTB_EINVAL, "tcgen05 LSTM step: operand not supported (windows %s%lld, H %lld)", "",
                     (long long)n_windows, (long long)H);
     // h_0 = 0 (both parities: pad rows are never written), c_0 = 0
@@ -1658,8 +1710,8 @@ int gemm_tc_lstm_layer(cudaStream_t st, const GemmWeights &whh, const float *xpr
     NTB_CUDA(cudaMemsetAsync(cstate, 0, gemm_tc_lstm_state_floats(n_windows, H) * sizeof(float), st));
     CUtensorMap ma_hi[2], ma_lo[2], mb_hi, mb_lo;
     for (int par = 0; par < 2; ++par) {
-        NTB_TRY(make_map(&ma_hi[par], gs.a_hi + par * plane_elems, 2 * Mp, H, BM));
-        NTB_TRY(make_map(&ma_lo[par], gs.a_lo + par * plane_elems, 2 * Mp, H, BM));
+        NTB_TRY(make_map_kmajor(&ma_hi[par], gs.a_hi + par * plane_elems, 2 * Mp, H));
+        NTB_TRY(make_map_kmajor(&ma_lo[par], gs.a_lo + par * plane_elems, 2 * Mp, H));
     }
     NTB_TRY(make_map(&mb_hi, whh.hi, 2LL * whh.Np, whh.Kp, whh.BN / cg));
     NTB_TRY(make_map(&mb_lo, whh.lo, 2LL * whh.Np, whh.Kp, whh.BN / cg));
@@ -1670,6 +1722,7 @@ int gemm_tc_lstm_layer(cudaStream_t st, const GemmWeights &whh, const float *xpr
     p.T = T; p.pad = 0; p.out_rows = n_windows * T; p.bias = nullptr; p.out = out; p.ldo = ldo;
     p.lstm_H = H; p.lstm_mt_dir = (int)(Mp / BM); p.lstm_n = n_windows; p.lstm_Mp = Mp;
     p.lstm_x = xproj; p.lstm_ldx = ldx; p.lstm_c = cstate; p.lstm_lens = lens;
+    p.lstm_xmt = (align_up(n_windows, BM) / BM) * T; p.a_kmajor = 1;
     for (int s = 0; s < T; ++s) {
         const int rd = s & 1, wr = rd ^ 1;
         p.lstm_s = s;

@@ -730,6 +730,44 @@ __global__ void __launch_bounds__(256) k_decode(const float *__restrict__ logits
 }
 
 // ------------------------------------------------------------------------------------------
+// LSTM input projection for inputs the tensor-core GEMM does not take (len_x = 12: K % 8 != 0 or K < 64), written
+// straight in the unit-major projected-gates layout the per-timestep recurrence reads:
+//   xproj[dir][tile * T + t][unit][128 windows] float4 (i, j, f, o) = bias + x[w, t, :] . W[:, dir 4H + 4 unit + g]
+// thread = window of the tile; a block walks 32 units: stores are 2 KB contiguous per unit, the weights are warp
+// broadcasts.  FMA-bound on paper, store-bound in practice (K is tiny).  wih [K][8H], bias [8H] as k_repack_lstm packs them.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_xproj_unit_major(const float *__restrict__ x, const float *__restrict__ wih,
+                                                          const float *__restrict__ bias, int64_t n_windows, int T, int K,
+                                                          int H, float4 *__restrict__ xproj) {
+    const int64_t mt = blockIdx.x;                    // tile * T + t
+    const int dir = blockIdx.y, u0 = blockIdx.z * 32;
+    const int64_t tile = mt / T;
+    const int t = (int)(mt - tile * T);
+    const int64_t w = tile * 128 + threadIdx.x;
+    const int64_t xmt = (int64_t)gridDim.x;
+    float xv[16];
+    const bool exists = w < n_windows;
+    for (int k0 = 0; k0 < K; k0 += 16) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) xv[k] = (exists && k0 + k < K) ? x[(w * T + t) * (int64_t)K + k0 + k] : 0.0f;
+        for (int u = u0; u < u0 + 32 && u < H; ++u) {
+            const int col = dir * 4 * H + 4 * u;
+            float4 *dst = xproj + ((dir * xmt + mt) * H + u) * 128 + threadIdx.x;
+            float4 acc = k0 == 0 ? __ldg(reinterpret_cast<const float4 *>(bias + col)) : *dst;
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                if (k0 + k < K) {
+                    const float4 wv = __ldg(reinterpret_cast<const float4 *>(wih + (int64_t)(k0 + k) * 8 * H + col));
+                    acc.x = fmaf(xv[k], wv.x, acc.x); acc.y = fmaf(xv[k], wv.y, acc.y);
+                    acc.z = fmaf(xv[k], wv.z, acc.z); acc.w = fmaf(xv[k], wv.w, acc.w);
+                }
+            }
+            *dst = acc;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // Weight repack (device side, once per model): TF LSTMCell kernel [D+H, 4H] with gate column
 // blocks i|j|f|o (network.py:275-282; rnn_cell_impl.LSTMCell) ->
 //   wih  [D, 2*4*Hp]  projection B operand, column = dir*4Hp + u*4 + g  (gate-interleaved)
