@@ -331,9 +331,45 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
         int64_t mg; int n_tile;
         for (int64_t it = 0; item(it, mg, n_tile); ++it) {
             const int64_t m_tile = mg * CG + rank;
+            const int64_t prow = m_tile * BM + q * 32 + lane;       // row in the A-plane layout
+            // LSTM timestep mode: what does not depend on the column chunk, and the first chunk's projected gates / cell
+            // state requested BEFORE the wait for the accumulator (four epilogue warps have nothing else to hide a DRAM
+            // latency behind; every later chunk is requested one chunk ahead, see below)
+            int l_dir = 0, l_t = 0, l_wl = 0;
+            int64_t l_w = 0, l_tile = 0;
+            bool l_live = false, l_active = false;
+            float4 xpre[8], cpre[2];
+            const float4 *l_x = nullptr;
+            float4 *l_c = nullptr;
+            auto lstm_fetch = [&](int c0f) {       // projected gates + cell state of the chunk at column c0f of this N tile
+                const int nbf = n_tile * p.BN + c0f;
+                if (!l_live || nbf >= p.N) return;
+                const int nuf = (p.N - nbf >= 32 && c0f + 32 <= p.BN) ? 8 : 4, u0f = nbf >> 2;
+                const float4 *xg = l_x + (int64_t)u0f * BM;
+                const float4 *cgp = l_c + (int64_t)(u0f >> 2) * BM;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) if (k < nuf) xpre[k] = __ldg(xg + k * BM);
+                cpre[0] = cgp[0];
+                if (nuf == 8) cpre[1] = cgp[BM];
+            };
+            if (p.lstm_H > 0) {
+                l_dir = m_tile >= p.lstm_mt_dir ? 1 : 0;
+                l_w = prow - l_dir * p.lstm_Mp;
+                l_live = l_w < p.lstm_n;
+                if (l_live) {
+                    l_t = l_dir ? p.T - 1 - p.lstm_s : p.lstm_s;
+                    int len = p.lstm_lens[l_w];
+                    len = len > p.T ? p.T : (len < 0 ? 0 : len);
+                    l_active = l_t < len;
+                    l_tile = l_w >> 7; l_wl = (int)(l_w & 127);
+                    const int64_t n_tiles = p.lstm_xmt / p.T;          // 128-window tiles of the job (not of the padded M)
+                    l_x = reinterpret_cast<const float4 *>(p.lstm_x) + ((l_dir * p.lstm_xmt + l_tile * p.T + l_t) * p.lstm_H) * (int64_t)BM + l_wl;
+                    l_c = reinterpret_cast<float4 *>(p.lstm_c) + ((l_dir * n_tiles + l_tile) * (p.lstm_H >> 2)) * (int64_t)BM + l_wl;
+                }
+                lstm_fetch(0);
+            }
             mbar_wait(&acc_full[acc], acc_phase);
             tc_fence_after();
-            const int64_t prow = m_tile * BM + q * 32 + lane;       // row in the A-plane layout
             int64_t orow = prow;
             bool row_ok = true;
             if (p.pad) {
@@ -403,40 +439,33 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                     // row-major buffers each warp-wide 16-byte access touched 32 lines and the L1 wavefronts (576 per chunk
                     // and warp) took three times as long as the tile's MMAs
                     const int H = p.lstm_H, nb = n0 + c0;
-                    const int dir = m_tile >= p.lstm_mt_dir ? 1 : 0;
-                    const int64_t w = prow - dir * p.lstm_Mp;
-                    if (w < p.lstm_n && nb < p.N) {       // pad rows of the h planes stay at their initial zero
-                        const int t = dir ? p.T - 1 - p.lstm_s : p.lstm_s;
-                        int len = p.lstm_lens[w];
-                        len = len > p.T ? p.T : (len < 0 ? 0 : len);
-                        const bool active = t < len;
+                    if (l_live && nb < p.N) {             // pad rows of the h planes stay at their initial zero
                         const int u0 = nb >> 2;                               // 8 units (4 in the 16-column tail chunk of a tile when BN % 32 == 16)
                         const int nu = (p.N - nb >= 32 && c0 + 32 <= p.BN) ? 8 : 4;
-                        const int64_t tile = w >> 7;
-                        const int wl = (int)(w & 127);
-                        const int64_t n_tiles = p.lstm_xmt / p.T;          // 128-window tiles of the job (not of the padded M)
-                        const float4 *xg = reinterpret_cast<const float4 *>(p.lstm_x) +
-                                           ((dir * p.lstm_xmt + tile * p.T + t) * H + u0) * (int64_t)BM + wl;
-                        float4 *cg = reinterpret_cast<float4 *>(p.lstm_c) + ((dir * n_tiles + tile) * (H >> 2) + (u0 >> 2)) * (int64_t)BM + wl;
+                        float4 xcur[8], ccur[2];
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) xcur[k] = xpre[k];
+                        ccur[0] = cpre[0]; ccur[1] = cpre[1];
+                        float4 *cg = l_c + (int64_t)(u0 >> 2) * BM;
+                        lstm_fetch(c0 + 32);              // the next chunk's operands fly during this chunk's cell updates
                         float hv[8];
 #pragma unroll
                         for (int half = 0; half < 2; ++half) {
                             if (half * 4 >= nu) { hv[4] = hv[5] = hv[6] = hv[7] = 0.0f; break; }
-                            const float4 c4 = cg[half * BM];
-                            float cc[4] = {c4.x, c4.y, c4.z, c4.w};
+                            float cc[4] = {ccur[half].x, ccur[half].y, ccur[half].z, ccur[half].w};
 #pragma unroll
                             for (int u = 0; u < 4; ++u) {
                                 const int i = 16 * half + 4 * u;
-                                const float4 xv = __ldg(xg + (4 * half + u) * BM);
+                                const float4 xv = xcur[4 * half + u];
                                 float cn = cc[u], hh;
                                 lstm_cell_update(__uint_as_float(r[i]) + xv.x, __uint_as_float(r[i + 1]) + xv.y,
                                                  __uint_as_float(r[i + 2]) + xv.z, __uint_as_float(r[i + 3]) + xv.w, cn, hh);
-                                cc[u] = active ? cn : cc[u];
-                                hv[4 * half + u] = active ? hh : 0.0f;
+                                cc[u] = l_active ? cn : cc[u];
+                                hv[4 * half + u] = l_active ? hh : 0.0f;
                             }
-                            if (active) cg[half * BM] = make_float4(cc[0], cc[1], cc[2], cc[3]);
+                            if (l_active) cg[half * BM] = make_float4(cc[0], cc[1], cc[2], cc[3]);
                         }
-                        float *og = p.out + (w * p.T + t) * (int64_t)p.ldo + dir * H + u0;
+                        float *og = p.out + (l_w * p.T + l_t) * (int64_t)p.ldo + l_dir * H + u0;
                         *reinterpret_cast<float4 *>(og) = make_float4(hv[0], hv[1], hv[2], hv[3]);
                         if (nu == 8) *reinterpret_cast<float4 *>(og + 4) = make_float4(hv[4], hv[5], hv[6], hv[7]);
                         uint4 ph, pl;
