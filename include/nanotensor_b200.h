@@ -193,8 +193,9 @@ NTB_API int ntb_event_features_host(const double *mean_host, const double *stdv_
  * (chiron/chiron/utils/easy_assembler.py:11-37), np.argmax, index2base -- the consensus call of every read
  * from the label rows the CTC readout produced.  labels [n_windows, T] int32, -1 padded (ntb_model_forward's
  * labels_dev); read_off_host [n_reads+1] int64 window offsets (HOST pointer).  Each window is placed against
- * its predecessor by the offset of their longest common block (difflib's choice and tie-break for windows
- * under 200 called bases; a longer window sets status 2 and is rejected), bases vote per position, the
+ * its predecessor by the offset of the block the reference takes, max(SequenceMatcher.get_matching_blocks(), key=size):
+ * the longest common block with difflib's tie-break for windows under 200 called bases, difflib's whole "autojunk"
+ * procedure (popular symbols out of the match index, extension, recursion, merge) from 200 on, bases vote per position, the
  * consensus is the first-max vote.  Integer work: identical to the reference, vote matrix included.
  * cons_dev [capacity] uint8 ASCII "ACGTE", reads back to back; cons_off_dev [n_reads+1] int64;
  * counts_dev optional [5, capacity] int32 vote matrix (row stride = capacity); capacity >= the number of

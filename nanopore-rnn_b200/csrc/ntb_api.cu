@@ -1130,6 +1130,15 @@ extern "C" int ntb_assemble_reads(const int32_t *labels_dev, const int64_t *read
         if (smem > 48 * 1024) cudaFuncSetAttribute(k_asm_disp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         k_asm_disp<<<(unsigned)cdiv(n_windows, ASM_WARPS), ASM_WARPS * 32, smem, st>>>(b.bases, b.blen, b.win_read, b.read_off,
                                                                                       n_windows, T, b.disp);
+        if (T >= ASM_AUTOJUNK) {
+            // windows with 200 and more called bases exist only from T = 200 on: difflib's autojunk regime, restated in full
+            const size_t lsmem = asm_long_smem_per_warp(T) * ASM_WARPS;
+            if (lsmem > 200 * 1024) return fail(NTB_EINVAL, "ntb_assemble_reads: T too large for the long-window kernel%s", "");
+            if (lsmem > 48 * 1024) cudaFuncSetAttribute(k_asm_disp_long, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lsmem);
+            const int64_t want = cdiv(n_windows, ASM_WARPS);
+            k_asm_disp_long<<<(unsigned)(want < 148 * 8 ? want : 148 * 8), ASM_WARPS * 32, lsmem, st>>>(
+                b.bases, b.blen, b.win_read, b.read_off, n_windows, T, b.disp);
+        }
     }
     k_asm_scan<<<(unsigned)n_reads, 256, 0, st>>>(b.disp, b.blen, b.read_off, b.start, b.bound, b.len);
     k_asm_read_offsets<<<1, 1024, 0, st>>>(b.bound, b.len, n_reads, capacity, b.bound_off, cons_off_dev, status_dev);

@@ -4,7 +4,8 @@
 // simple_assembly + add_count (chiron/chiron/utils/easy_assembler.py:11-37), np.argmax, index2base.  Every window is
 // placed against its predecessor by the offset of their longest common block (the reference asks difflib for
 // max(get_matching_blocks(), key=size); for windows under 200 bases that is the longest common substring, ties broken by
-// the scan order of difflib's dynamic programme: end in the previous window ascending, then end in this window), the
+// the scan order of difflib's dynamic programme: end in the previous window ascending, then end in this window; from 200
+// bases on difflib's "autojunk" regime applies and k_asm_disp_long restates the whole procedure), the
 // offsets accumulate along the read, every base votes for its position, and the consensus is the first-max vote.
 // All integer work: results are identical to the reference's, vote matrix included.
 //
@@ -17,7 +18,7 @@
 
 namespace ntb {
 
-constexpr int ASM_AUTOJUNK = 200;          // difflib drops "popular" elements from 200 on: not restated, rejected
+constexpr int ASM_AUTOJUNK = 200;          // difflib drops "popular" elements from the match index from 200 on (k_asm_disp_long)
 constexpr int ASM_WARPS = 4;               // warps (window pairs) per CTA in the pair kernel
 constexpr int ASM_STATUS_LONG_WINDOW = 2, ASM_STATUS_CAPACITY = 1;
 
@@ -38,10 +39,8 @@ __global__ void __launch_bounds__(128) k_asm_compact(const int32_t *__restrict__
         if (v != -1) dst[n + __popc(keep & ((1u << lane) - 1))] = (uint8_t)v;
         n += __popc(keep);
     }
-    if (lane == 0) {
-        blen[w] = n;
-        if (n >= ASM_AUTOJUNK) atomicMax(status, ASM_STATUS_LONG_WINDOW);
-    }
+    if (lane == 0) blen[w] = n;
+    (void)status;
 }
 
 // window -> read id (one CTA per read)
@@ -65,7 +64,8 @@ __global__ void __launch_bounds__(ASM_WARPS * 32) k_asm_disp(const uint8_t *__re
         return;
     }
     const int la = blen[w - 1], lb = blen[w];
-    if (la == 0 || lb == 0 || la >= ASM_AUTOJUNK || lb >= ASM_AUTOJUNK) {   // no block: the sentinel (la, lb, 0)
+    if (lb >= ASM_AUTOJUNK) return;                             // autojunk regime: k_asm_disp_long writes disp[w]
+    if (la == 0 || lb == 0) {                                   // no block: the sentinel (la, lb, 0)
         if (lane == 0) disp[w] = la - lb;
         return;
     }
@@ -98,6 +98,127 @@ __global__ void __launch_bounds__(ASM_WARPS * 32) k_asm_disp(const uint8_t *__re
     if (lane == 0) {
         const int k = (int)(key >> 40), i = 0xFFFFF - (int)((key >> 20) & 0xFFFFF), j = 0xFFFFF - (int)(key & 0xFFFFF);
         disp[w] = k ? i - j : la - lb;
+    }
+}
+
+// K2': the windows k_asm_disp left out -- 200 and more called bases in the SECOND window of a pair, where
+// difflib.SequenceMatcher switches "autojunk" on (__chain_b): every symbol occurring more than lb / 100 + 1 times in b is
+// POPULAR and leaves the match index (with four bases that is normally every base).  The whole procedure is restated:
+// find_longest_match = longest run of matches made of non-popular symbols (difflib's scan order: end in a ascending, then
+// end in b, strict improvement), extended at both ends over equal symbols, popular ones included; get_matching_blocks
+// recurses left and right of every block (a stack, as difflib pops its queue from the end), sorts the blocks, merges
+// adjacent ones, and the reference takes the FIRST block of maximal size (the sentinel (la, lb, 0) when there is none).
+// One warp per pair: the dynamic programme runs with lanes across b, lane 0 keeps the stack and the block list.
+// Shared memory per warp: a[T], b[T], two rows of T + 2 run lengths (16 bit), stack 4 x T, blocks 3 x (T + 1) (16 bit).
+__host__ __device__ inline size_t asm_long_smem_per_warp(int T) { return ((size_t)20 * T + 64 + 15) & ~(size_t)15; }
+
+__global__ void __launch_bounds__(ASM_WARPS * 32) k_asm_disp_long(const uint8_t *__restrict__ bases,
+                                                                  const int32_t *__restrict__ blen,
+                                                                  const int32_t *__restrict__ win_read,
+                                                                  const int64_t *__restrict__ read_off, int64_t n_windows,
+                                                                  int T, int32_t *__restrict__ disp) {
+    extern __shared__ __align__(16) uint8_t asm_long_smem[];
+    const int wi = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint8_t *base = asm_long_smem + (size_t)wi * asm_long_smem_per_warp(T);
+    uint8_t *a = base, *b = a + T;
+    uint16_t *row0 = reinterpret_cast<uint16_t *>(base + ((2 * (size_t)T + 15) & ~(size_t)15));
+    uint16_t *row1 = row0 + T + 2;
+    int16_t *stk = reinterpret_cast<int16_t *>(row1 + T + 2);          // [T + 2][4]
+    int16_t *blk = stk + 4 * (T + 2);                                   // [T + 1][3]
+    for (int64_t w = (int64_t)blockIdx.x * ASM_WARPS + wi; w < n_windows; w += (int64_t)gridDim.x * ASM_WARPS) {
+        const int lb = blen[w];
+        if (lb < ASM_AUTOJUNK || w == read_off[win_read[w]]) continue;
+        const int la = blen[w - 1];
+        if (la == 0) { if (lane == 0) disp[w] = la - lb; continue; }
+        __syncwarp();
+        for (int t = lane; t < la; t += 32) a[t] = bases[(w - 1) * T + t];
+        for (int t = lane; t < lb; t += 32) b[t] = bases[w * T + t];
+        __syncwarp();
+        // popular symbols of b
+        uint32_t popular = 0;
+        for (int sym = 0; sym < 5; ++sym) {
+            int c = 0;
+            for (int j0 = 0; j0 < lb; j0 += 32) c += __popc(__ballot_sync(0xffffffffu, j0 + lane < lb && b[j0 + lane] == sym));
+            if (c > lb / 100 + 1) popular |= 1u << sym;
+        }
+        int n_stk = 1, n_blk = 0;
+        if (lane == 0) { stk[0] = 0; stk[1] = (int16_t)la; stk[2] = 0; stk[3] = (int16_t)lb; }
+        __syncwarp();
+        while (n_stk > 0) {
+            --n_stk;
+            const int alo = stk[4 * n_stk], ahi = stk[4 * n_stk + 1], blo = stk[4 * n_stk + 2], bhi = stk[4 * n_stk + 3];
+            __syncwarp();
+            uint16_t *prev = row0, *cur = row1;                  // index j + 1 = run ending at b[j]; index blo = "before blo"
+            for (int j = blo + lane; j <= bhi; j += 32) prev[j] = 0;
+            __syncwarp();
+            int best_k = 0, best_i = 0, best_j = 0;
+            for (int i = alo; i < ahi; ++i) {
+                const uint8_t ai = a[i];
+                const bool pop = (popular >> ai) & 1u;
+                for (int j = blo + lane; j < bhi; j += 32) {
+                    const int k = (!pop && b[j] == ai) ? prev[j] + 1 : 0;
+                    cur[j + 1] = (uint16_t)k;
+                    if (k > best_k) { best_k = k; best_i = i; best_j = j; }
+                }
+                if (lane == 0) cur[blo] = 0;
+                __syncwarp();
+                uint16_t *tmp = prev; prev = cur; cur = tmp;
+            }
+            unsigned long long key = ((unsigned long long)best_k << 40) | ((unsigned long long)(0xFFFFF - best_i) << 20) |
+                                     (unsigned long long)(0xFFFFF - best_j);
+#pragma unroll
+            for (int o = 16; o; o >>= 1) {
+                const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+                key = other > key ? other : key;
+            }
+            int push = 0;
+            if (lane == 0) {
+                int k = (int)(key >> 40), bi = alo, bj = blo;
+                if (k) { bi = 0xFFFFF - (int)((key >> 20) & 0xFFFFF) - k + 1; bj = 0xFFFFF - (int)(key & 0xFFFFF) - k + 1; }
+                while (bi > alo && bj > blo && a[bi - 1] == b[bj - 1]) { --bi; --bj; ++k; }
+                while (bi + k < ahi && bj + k < bhi && a[bi + k] == b[bj + k]) ++k;
+                if (k) {
+                    blk[3 * n_blk] = (int16_t)bi; blk[3 * n_blk + 1] = (int16_t)bj; blk[3 * n_blk + 2] = (int16_t)k;
+                    push |= 4;
+                    if (alo < bi && blo < bj) {
+                        stk[4 * n_stk] = (int16_t)alo; stk[4 * n_stk + 1] = (int16_t)bi; stk[4 * n_stk + 2] = (int16_t)blo; stk[4 * n_stk + 3] = (int16_t)bj;
+                        push |= 1;
+                    }
+                    if (bi + k < ahi && bj + k < bhi) {
+                        const int at = n_stk + (push & 1);
+                        stk[4 * at] = (int16_t)(bi + k); stk[4 * at + 1] = (int16_t)ahi; stk[4 * at + 2] = (int16_t)(bj + k); stk[4 * at + 3] = (int16_t)bhi;
+                        push |= 2;
+                    }
+                }
+            }
+            push = __shfl_sync(0xffffffffu, push, 0);
+            n_blk += (push >> 2) & 1;
+            n_stk += (push & 1) + ((push >> 1) & 1);
+            __syncwarp();
+        }
+        if (lane == 0) {
+            // blocks sorted by (i, j), adjacent ones merged, first of maximal size; the sentinel (la, lb, 0) if none
+            for (int x = 1; x < n_blk; ++x) {
+                const int16_t bi = blk[3 * x], bj = blk[3 * x + 1], bk = blk[3 * x + 2];
+                int y = x - 1;
+                while (y >= 0 && (blk[3 * y] > bi || (blk[3 * y] == bi && blk[3 * y + 1] > bj))) {
+                    blk[3 * y + 3] = blk[3 * y]; blk[3 * y + 4] = blk[3 * y + 1]; blk[3 * y + 5] = blk[3 * y + 2];
+                    --y;
+                }
+                blk[3 * y + 3] = bi; blk[3 * y + 4] = bj; blk[3 * y + 5] = bk;
+            }
+            int best_i = la, best_j = lb, best_k = 0;
+            int i1 = 0, j1 = 0, k1 = 0;
+            for (int x = 0; x <= n_blk; ++x) {
+                const bool end = x == n_blk;
+                const int i2 = end ? -1 : blk[3 * x], j2 = end ? -1 : blk[3 * x + 1], k2 = end ? 0 : blk[3 * x + 2];
+                if (!end && i1 + k1 == i2 && j1 + k1 == j2) { k1 += k2; continue; }
+                if (k1 > best_k) { best_k = k1; best_i = i1; best_j = j1; }
+                i1 = i2; j1 = j2; k1 = k2;
+            }
+            disp[w] = best_i - best_j;
+        }
+        __syncwarp();
     }
 }
 

@@ -14,8 +14,16 @@ the longest common substring found by the top-level ``find_longest_match``: ever
 of the full range, so none found later can be as long and start earlier.  Its tie-break is the scan order of the
 dynamic programme -- end position in ``a`` ascending, then in ``b`` ascending, strict improvement only -- restated in
 ``longest_block`` below without difflib (checked against difflib on random strings in the tests).  With no common
-element the only block is the sentinel ``(len(a), len(b), 0)``.  Windows with 200 or more called bases are outside
-this statement (difflib then drops "popular" elements first) and are rejected by the oracle and the kernel alike.
+element the only block is the sentinel ``(len(a), len(b), 0)``.
+
+A second sequence of 200 or more elements switches difflib's "autojunk" on (``SequenceMatcher.__chain_b``): every
+element occurring more than ``len(b) // 100 + 1`` times in ``b`` is POPULAR and leaves the match index -- with four bases
+that is normally every base.  ``find_longest_match`` then finds the longest run of matches made of non-popular elements
+only (same scan order), extends it at both ends over equal elements (popular ones included), ``get_matching_blocks``
+recurses to the left and to the right of each block, sorts the blocks, merges adjacent ones, appends the sentinel, and the
+reference takes the first block of maximal size.  ``longest_block_autojunk`` restates exactly that; it is pinned by
+tests/golden/assembly_long.npz (the reference's functions run on T = 300 windows of 200-300 bases) and checked against
+difflib itself on random strings.
 """
 import numpy as np
 
@@ -32,7 +40,7 @@ def longest_block(a, b):
     """(i, j, k): a[i:i+k] == b[j:j+k] with k maximal; among those the one ending first in a, then first in b;
     (len(a), len(b), 0) when nothing matches."""
     if len(b) >= AUTOJUNK_LEN:
-        raise ValueError("window with >= 200 bases: difflib's autojunk regime is not restated")
+        return longest_block_autojunk(a, b)
     best = (len(a), len(b), 0)
     prev = np.zeros(len(b) + 1, dtype=np.int32)
     for i in range(len(a)):
@@ -44,6 +52,60 @@ def longest_block(a, b):
             j = int(np.argmax(cur)) - 1                    # first j reaching k in this row
             best = (i - k + 1, j - k + 1, k)
         prev = cur
+    return best
+
+
+def _find_longest(a, b, popular, alo, ahi, blo, bhi):
+    """difflib.SequenceMatcher.find_longest_match with the popular elements out of the index and no junk."""
+    besti, bestj, bestsize = alo, blo, 0
+    j2len = {}
+    for i in range(alo, ahi):
+        new = {}
+        if not popular[int(a[i])]:
+            for j in range(blo, bhi):                      # b2j[a[i]] in ascending order, clipped to [blo, bhi)
+                if b[j] == a[i]:
+                    k = new[j] = j2len.get(j - 1, 0) + 1
+                    if k > bestsize:
+                        besti, bestj, bestsize = i - k + 1, j - k + 1, k
+        j2len = new
+    while besti > alo and bestj > blo and a[besti - 1] == b[bestj - 1]:
+        besti, bestj, bestsize = besti - 1, bestj - 1, bestsize + 1
+    while besti + bestsize < ahi and bestj + bestsize < bhi and a[besti + bestsize] == b[bestj + bestsize]:
+        bestsize += 1
+    return besti, bestj, bestsize
+
+
+def longest_block_autojunk(a, b):
+    """max(SequenceMatcher(None, a, b).get_matching_blocks(), key=size) for len(b) >= 200 (5 symbols)."""
+    n = len(b)
+    counts = np.bincount(np.asarray(b, dtype=np.int64), minlength=8)
+    popular = counts > n // 100 + 1
+    queue, blocks = [(0, len(a), 0, n)], []
+    while queue:
+        alo, ahi, blo, bhi = queue.pop()
+        i, j, k = _find_longest(a, b, popular, alo, ahi, blo, bhi)
+        if k:
+            blocks.append((i, j, k))
+            if alo < i and blo < j:
+                queue.append((alo, i, blo, j))
+            if i + k < ahi and j + k < bhi:
+                queue.append((i + k, ahi, j + k, bhi))
+    blocks.sort()
+    merged, (i1, j1, k1) = [], (0, 0, 0)
+    for i2, j2, k2 in blocks:
+        if i1 + k1 == i2 and j1 + k1 == j2:
+            k1 += k2
+        else:
+            if k1:
+                merged.append((i1, j1, k1))
+            i1, j1, k1 = i2, j2, k2
+    if k1:
+        merged.append((i1, j1, k1))
+    merged.append((len(a), n, 0))
+    best = merged[0]
+    for blk in merged[1:]:
+        if blk[2] > best[2]:
+            best = blk
     return best
 
 

@@ -50,6 +50,55 @@ def sliding_read(rng, n_windows, step=8, width=26, err=0.06, T=T):
     return rows
 
 
+def write_long(ns):
+    """assembly_long.npz: T = 300 label rows with 200 and more called bases per window -- difflib's "autojunk" regime
+    (len(b) >= 200: every element occurring more than len(b) // 100 + 1 times is dropped from the match index; with four
+    bases that is every base, unless one is rare in the window).  Same reference functions, same layout as assembly.npz."""
+    T2 = 300
+    rng = np.random.default_rng(20171105)
+    reads = []
+    # (1) sliding windows of ~230 bases over one sequence: all four bases popular -> no anchors at all -> sentinel blocks
+    reads.append(sliding_read(rng, 8, step=40, width=228, err=0.03, T=T2))
+    # (2) the same with a RARE fifth symbol ('E' = 4) sprinkled in: the few E's are the only anchors, matches grow from them
+    r = sliding_read(rng, 10, step=35, width=215, err=0.0, T=T2)
+    truth_e = rng.integers(0, 4, 35 * 10 + 215 + 8)
+    truth_e[rng.choice(len(truth_e), 9, replace=False)] = 4
+    r = [truth_e[w * 35: w * 35 + 215 + int(rng.integers(0, 20))].copy() for w in range(10)]
+    reads.append(r)
+    # (3) long and short windows alternating (autojunk depends on the SECOND sequence's length only), a rare base in some
+    r = []
+    for w in range(12):
+        n = int(rng.integers(200, 300)) if w % 2 else int(rng.integers(20, 199))
+        seg = rng.integers(0, 3, n)                       # A, C, G popular
+        pos = rng.choice(n, int(rng.integers(0, 4)), replace=False)
+        seg[pos] = 3                                      # at most 3 T's: never popular in a long window
+        r.append(seg)
+    reads.append(r)
+    # (4) exactly 199 / 200 / 201 bases around the threshold, related windows
+    base = rng.integers(0, 4, 260)
+    reads.append([base[:199].copy(), base[5:205].copy(), base[3:204].copy(), base[10:209].copy(), base[0:300].copy(), base[40:250].copy()])
+    labels, lens, off, cons_txt, counts, cons_off = [], [], [0], [], [], [0]
+    for rows in reads:
+        block = np.full((len(rows), T2), -1, dtype=np.int32)
+        for i, seg in enumerate(rows):
+            block[i, :len(seg)] = seg
+        all_reads = [ns["index2base"](row) for row in block]
+        cons = ns["simple_assembly"](all_reads)
+        txt = ns["index2base"](np.argmax(cons, axis=0)) if cons.shape[1] else ""
+        labels.append(block)
+        lens.extend(len(sg) for sg in rows)
+        off.append(off[-1] + len(rows))
+        cons_txt.append(txt)
+        counts.append(cons.astype(np.int32))
+        cons_off.append(cons_off[-1] + cons.shape[1])
+    np.savez_compressed(os.path.join(HERE, "assembly_long.npz"), labels=np.concatenate(labels),
+                        label_len=np.asarray(lens, dtype=np.int32), read_off=np.asarray(off, dtype=np.int64),
+                        consensus=np.frombuffer("".join(cons_txt).encode(), dtype=np.uint8),
+                        counts=np.concatenate(counts, axis=1), cons_off=np.asarray(cons_off, dtype=np.int64))
+    print("wrote assembly_long.npz: %d reads, %d windows (%d with >= 200 bases), consensus lengths %s"
+          % (len(reads), off[-1], sum(l >= 200 for l in lens), np.diff(cons_off)))
+
+
 def main():
     ns = reference_namespace()
     rng = np.random.default_rng(20171104)
@@ -80,6 +129,7 @@ def main():
         cons_txt.append(txt)
         counts.append(cons.astype(np.int32))
         cons_off.append(cons_off[-1] + cons.shape[1])
+    write_long(ns)
     np.savez_compressed(os.path.join(HERE, "assembly.npz"), labels=np.concatenate(labels),
                         label_len=np.asarray(lens, dtype=np.int32), read_off=np.asarray(off, dtype=np.int64),
                         consensus=np.frombuffer("".join(cons_txt).encode(), dtype=np.uint8),
