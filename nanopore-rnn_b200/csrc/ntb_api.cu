@@ -462,7 +462,7 @@ static int64_t plan_workspace(const ntb_model *m, int64_t n, int64_t n_groups, b
     ws.bn_part = nullptr;   // set below, once the operand planes are sized
     ws.cstate = m->max_step_h ? ar.take<float>(gemm_tc_lstm_state_floats(n, m->max_step_h)) : nullptr;
     const bool small_c = m->C <= 8;
-    ws.logits = (!small_c && own_logits) ? ar.take<float>(rows * m->C) : nullptr;
+    ws.logits = (!small_c && own_logits) ? ar.take<float>(rows * align_up(m->C, 4)) : nullptr;   // row stride padded to 16 bytes
     int maxk = m->len_x > m->max_step_h ? m->len_x : m->max_step_h;
     for (auto &ld : m->layers) {
         if (ld.in_dim > maxk) maxk = ld.in_dim;
@@ -757,9 +757,12 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
     } else {
         float *lg = logits_out ? logits_out : ws.logits;
         if (!lg) return fail(NTB_ENOMEM, "forward: no logits buffer for a large-C readout%s", "");
-        NTB_TRY(dense(cx, cur, dim, rows, dim, m->C, m->out_w, &m->outw, m->out_b, lg, m->C, &ws.gs));
+        // the caller's logits are dense [rows][C]; the internal scratch (labels only) pads the row stride to a multiple of 4
+        // floats: with C = 1025 the dense layer's epilogue otherwise falls back to scalar stores
+        const int ldl = logits_out ? m->C : (int)align_up(m->C, 4);
+        NTB_TRY(dense(cx, cur, dim, rows, dim, m->C, m->out_w, &m->outw, m->out_b, lg, ldl, &ws.gs));
         const int64_t warps = m->graph == NTB_GRAPH_CROSS_ENTROPY ? rows : n;
-        k_decode<<<cdiv(warps, 8), 256, 0, st>>>(lg, lens, n, T, m->C, m->graph, labels, label_len);
+        k_decode<<<cdiv(warps, 8), 256, 0, st>>>(lg, lens, n, T, m->C, m->graph, labels, label_len, ldl);
         cx.count();
         NTB_LAUNCH_CHECK();
     }
@@ -1602,7 +1605,7 @@ extern "C" int ntb_decode(const float *logits_dev, const int32_t *len_dev, int64
     NTB_TRY(check_device());
     if (n_windows == 0) return NTB_OK;
     const int64_t warps = graph == NTB_GRAPH_CROSS_ENTROPY ? n_windows * T : n_windows;
-    k_decode<<<cdiv(warps, 8), 256, 0, (cudaStream_t)stream>>>(logits_dev, len_dev, n_windows, T, C, graph, labels_dev, label_len_dev);
+    k_decode<<<cdiv(warps, 8), 256, 0, (cudaStream_t)stream>>>(logits_dev, len_dev, n_windows, T, C, graph, labels_dev, label_len_dev, C);
     NTB_LAUNCH_CHECK();
     return NTB_OK;
 }

@@ -702,15 +702,17 @@ __device__ __forceinline__ int warp_argmax_first(const float *row, int C, int la
     return bi == 0x7fffffff ? 0 : bi;   // all-NaN row -> 0 like a first-max scan
 }
 
+// ld = floats between consecutive logits rows (C for the caller's dense [rows][C]; the model's own scratch pads it to a
+// multiple of 4 so that the dense layer's epilogue stores 16 bytes at a time)
 __global__ void __launch_bounds__(256) k_decode(const float *__restrict__ logits,
                                                 const int32_t *__restrict__ lens, int64_t n_windows,
                                                 int T, int C, int graph, int32_t *__restrict__ labels,
-                                                int32_t *__restrict__ label_len) {
+                                                int32_t *__restrict__ label_len, int ld) {
     const int lane = threadIdx.x & 31;
     const int64_t gw = (int64_t)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
     if (graph == NTB_GRAPH_CROSS_ENTROPY) {
         if (gw >= n_windows * T) return;
-        const int best = warp_argmax_first(logits + gw * C, C, lane);
+        const int best = warp_argmax_first(logits + gw * (int64_t)ld, C, lane);
         if (lane == 0) labels[gw] = best;
         return;
     }
@@ -718,7 +720,7 @@ __global__ void __launch_bounds__(256) k_decode(const float *__restrict__ logits
     const int len = lens[gw];
     int prev = -1, cnt = 0;
     for (int t = 0; t < len && t < T; ++t) {
-        const int best = warp_argmax_first(logits + (gw * T + t) * (int64_t)C, C, lane);
+        const int best = warp_argmax_first(logits + (gw * T + t) * (int64_t)ld, C, lane);
         if (best != C - 1 && best != prev) {
             if (lane == 0) labels[gw * T + cnt] = best;
             ++cnt;
