@@ -376,6 +376,14 @@ def roofline_of(cx, stage, n, n_chunks, steps, ms_step):
                      "frac": (tf_s / peak if tf_s else None),
                      "tensor_pipe_frac_with_3_passes": (3 * tf_s / peak if tf_s else None)}
     stages["readout"]["bound"] = "hbm"          # reads the last layer's activations once; FLOPs are negligible
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath) and WL["name"] == "run_nanotensor" and stage4["conv_bn"] > 0:
+        # the conv/BN stage is co-limited: its kernels move 2.9 MB of DRAM traffic per window (ncu, profiles/) next to the
+        # three-pass tensor work -- both fractions are reported, they add up rather than overlap
+        bpw = json.load(open(tpath)).get("conv_bn_stage_dram_bytes_per_window")
+        if bpw:
+            gbs = bpw * n * steps / (stage4["conv_bn"] * 1e-3) / 1e9
+            stages["conv_bn"].update({"dram_mb_per_window": bpw / 1e6, "achieved_gbs": gbs, "hbm_frac": gbs / pk["hbm_gbs"]})
     roof = None
     if proj_ms > 0:
         kname, k_ms, k_flops = "k_gemm_tc<2> (LSTM input projection GEMM, tcgen05 fp16x3)", proj_ms, flops["projection"]
