@@ -288,9 +288,12 @@ def run_reference(args):
               % (nw, T, BATCH, what, cores, tfp["observed"]))
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "windows_per_step": nw, "seq_len": T, "bn_group": BATCH,
-                       "n_classes": NCLASS},
+            # same key as the B200 arm's default line (one read set over N GPUs); the CPU arm itself always runs on rank 0
+            "scaling": "strong" if (args.workload == "reads" and WL["graph"] == "CtcLoss" and WL["len_x"] == 1) else "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD + "; CPU arm: a bounded sample of windows of the same network per step, forward "
+                                   "only (the B200 arm's job adds z-score / windowing and the consensus assembly)",
+                       "windows_per_step": nw, "seq_len": T, "bn_group": BATCH, "n_classes": NCLASS},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
                              "tf_probe": tfp},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
