@@ -57,6 +57,9 @@ struct LayerDev {
     bool step_rec = false;    // one tcgen05 GEMM per timestep (larger H; ntb_gemm_tc.cu)
     GemmWeights whhw;         // [2 dirs][4H][H] planes for step_rec
     float *whh_stage = nullptr;
+    bool step_fused = false;  // step_rec with the input projection inside the per-timestep GEMM ([W_ih ; W_hh], D % 64 == 0)
+    GemmWeights wcatw;        // [2 dirs][4H][D + H] planes
+    float *wcat_stage = nullptr;
     // chiron_fnn
     const float *fnn_w = nullptr, *fnn_b = nullptr;
 };
@@ -321,6 +324,10 @@ static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &a
             } else if (Hp == H && gemm_tc_lstm_supported(H)) {
                 gemm_tc_plan_whh(ld.whhw, H, ar, &ld.whh_stage);
                 ld.step_rec = ld.whhw.valid;
+                if (ld.step_rec && ld.wihw.valid && gemm_tc_lstm_fused_supported(H, D) && !ntb_env("NTB_NO_FUSED_STEP")) {
+                    gemm_tc_plan_wcat(ld.wcatw, H, D, ar, &ld.wcat_stage);
+                    ld.step_fused = ld.wcatw.valid;
+                }
             }
             if (upload && ar.ok()) {
                 k_repack_lstm<<<256, 256, 0, st>>>(kf, bf, kb, bb, l.forget_bias, D, H, Hp, ld.wih, ld.bias, ld.whh,
@@ -328,6 +335,7 @@ static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &a
                 if (ld.tc_rec)
                     k_pack_whh_tc<<<256, 256, 0, st>>>(kf, kb, D, H, (int)align_up(H, 16), ld.whh_hi, ld.whh_lo);
                 if (ld.step_rec) gemm_tc_pack_whh(st, kf, kb, D, H, ld.whh_stage, ld.whhw);
+                if (ld.step_fused) gemm_tc_pack_wcat(st, ld.wih, kf, kb, D, H, ld.wcat_stage, ld.wcatw);
                 if (ld.fused)
                     k_pack_blstm_fused<<<512, 256, 0, st>>>(kf, bf, kb, bb, l.forget_bias, ld.fg, ld.f_wih, ld.f_whh, ld.f_bias);
             }
@@ -702,10 +710,21 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
                 continue;
             } else if (ld.step_rec) {
                 if (!ws.gs.valid) return fail(NTB_EINVAL, "blstm: operand planes missing for the tensor-core path%s", "");
+                if (ld.step_fused) {
+                    // the projection rides in the per-timestep GEMM: the layer input goes to time-major operand planes (they
+                    // live where the projected gates would have been) and no projected gates exist
+                    op16_t *x_hi = reinterpret_cast<op16_t *>(ws.xproj);
+                    op16_t *x_lo = x_hi + align_up(n, LSTM_TC_ROWS) * T * (int64_t)dim;
+                    NTB_TRY(gemm_tc_split_timemajor(cx.st, cur, dim, n, T, dim, x_hi, x_lo, &cx.launches));
+                    NTB_TRY(mark(2));
+                    NTB_TRY(gemm_tc_lstm_layer(cx.st, ld.wcatw, nullptr, N, lens, n, T, ld.size, ws.cstate, out, 2 * ld.size,
+                                               ws.gs, &cx.launches, dim, x_hi, x_lo, ld.bias));
+                } else {
                 NTB_TRY(step_rec_projection(cx, cur, dim, n, T, ld.size, ld.wih, ld.bias, ld.wihw, ws.xproj, ws.gs));
                 NTB_TRY(mark(2));
                 NTB_TRY(gemm_tc_lstm_layer(cx.st, ld.whhw, ws.xproj, N, lens, n, T, ld.size, ws.cstate, out, 2 * ld.size,
                                            ws.gs, &cx.launches));
+                }
             } else {
                 NTB_TRY(dense(cx, cur, dim, rows, dim, N, ld.wih, &ld.wihw, ld.bias, ws.xproj, N, &ws.gs));
                 NTB_TRY(mark(2));
@@ -1493,6 +1512,9 @@ struct BlstmOpBufs {
     GemmWeights whhw;
     float *whh_stage = nullptr, *cstate = nullptr;
     GemmWeights wihw;
+    bool step_fused = false;
+    GemmWeights wcatw;
+    float *wcat_stage = nullptr;
     GemmScratch gs;
     op16_t *whh_hi, *whh_lo;
     bool fused = false;           // the model's default for these shapes: ONE fused kernel (ntb_blstm_fused.cuh)
@@ -1532,6 +1554,10 @@ static int64_t plan_blstm_op(Arena &ar, int64_t n, int T, int D, int H, BlstmOpB
         const int64_t step_rows = cdiv(4 * align_up(n, 256) * H, align_up(kcap, 8));
         gemm_tc_plan_scratch(b.gs, rows, T, kcap, ar, step_rows > tile_rows ? step_rows : tile_rows);
         b.step = b.whhw.valid && b.gs.valid;
+        if (b.step && b.wihw.valid && gemm_tc_lstm_fused_supported(H, D) && !ntb_env("NTB_NO_FUSED_STEP")) {
+            gemm_tc_plan_wcat(b.wcatw, H, D, ar, &b.wcat_stage);
+            b.step_fused = b.wcatw.valid;
+        }
     }
     return ar.off;
 }
@@ -1587,6 +1613,14 @@ extern "C" int ntb_blstm(const float *in_dev, const int32_t *len_dev, const floa
         // H beyond the persistent kernel: one tcgen05 GEMM per timestep (same path the model takes)
         if (b.wihw.valid) NTB_TRY(gemm_tc_pack_weights(cx.st, b.wih, b.wihw));
         NTB_TRY(gemm_tc_pack_whh(cx.st, kernel_fw_dev, kernel_bw_dev, D, H, b.whh_stage, b.whhw));
+        if (b.step_fused) {
+            NTB_TRY(gemm_tc_pack_wcat(cx.st, b.wih, kernel_fw_dev, kernel_bw_dev, D, H, b.wcat_stage, b.wcatw));
+            op16_t *x_hi = reinterpret_cast<op16_t *>(b.xproj);
+            op16_t *x_lo = x_hi + align_up(n_windows, LSTM_TC_ROWS) * T * (int64_t)D;
+            NTB_TRY(gemm_tc_split_timemajor(cx.st, in_dev, D, n_windows, T, D, x_hi, x_lo, &cx.launches));
+            return gemm_tc_lstm_layer(cx.st, b.wcatw, nullptr, 8 * Hp, len_dev, n_windows, T, H, b.cstate, out_dev, 2 * H, b.gs,
+                                      &cx.launches, D, x_hi, x_lo, b.bias);
+        }
         NTB_TRY(step_rec_projection(cx, in_dev, D, n_windows, T, H, b.wih, b.bias, b.wihw, b.xproj, b.gs));
         return gemm_tc_lstm_layer(cx.st, b.whhw, b.xproj, 8 * Hp, len_dev, n_windows, T, H, b.cstate, out_dev, 2 * H, b.gs,
                                   &cx.launches);

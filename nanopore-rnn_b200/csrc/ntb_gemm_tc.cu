@@ -79,6 +79,12 @@ struct TcParams {
     const int32_t *lstm_lens;
     op16_t *lstm_hi, *lstm_lo;         // h_t operand planes of the NEXT step, k-group-major [H/8][2 Mp rows][8] (a_kmajor)
     int64_t lstm_xmt;                  // M tiles per direction of the projected-gates buffer = 128-window tiles x T
+    // lstm_kbx > 0: the input projection rides in the SAME GEMM -- the first lstm_kbx k-blocks of every timestep's
+    // contraction are x_t . W_ih (A = the layer input's time-major operand planes through map_out / map_out2, one
+    // [128 windows x 64] box per tile and k-block at row (tile T + t) 128), the rest h_{t-1} . W_hh; B = [W_ih ; W_hh]
+    // along K.  No projected gates exist then (lstm_x == null): the epilogue adds lstm_bias [2][4H] instead.
+    int lstm_kbx;
+    const float *lstm_bias;
     int a_kmajor;                      // the A planes are [K/8][rows][8] (no swizzle; 3-D TMA box {8, 128, 8}) instead of
                                        // row-major rows with the 128-byte swizzle: the LSTM epilogue's h stores coalesce
 };
@@ -171,8 +177,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&map_a_hi); prefetch_tmap(&map_a_lo); prefetch_tmap(&map_b_hi); prefetch_tmap(&map_b_lo);
-        if (p.tma_store || p.xproj_tma) prefetch_tmap(&map_out);
-        if (p.n_split > 0) prefetch_tmap(&map_out2);
+        if (p.tma_store || p.xproj_tma || p.lstm_kbx) prefetch_tmap(&map_out);
+        if (p.n_split > 0 || p.lstm_kbx) prefetch_tmap(&map_out2);
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
@@ -245,11 +251,20 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                         } else {
                             // both CTAs' bytes are credited to the LEADER's full barrier
                             if (rank == 0) mbar_expect_tx(&full_bar[stage], (uint32_t)(2 * stage_bytes));
-                            if (p.a_kmajor) tma_load_3d_pair(s, &map_a_hi, &full_bar[stage], 0, row0, kb * (BK / 8));
+                            const bool xk = p.lstm_kbx > 0 && kb < p.lstm_kbx;      // an x_t k-block of the fused step GEMM
+                            int xrow = 0;
+                            if (xk) {
+                                const int dirx = m_tile >= p.lstm_mt_dir ? 1 : 0;
+                                const int64_t tl = m_tile - (int64_t)dirx * p.lstm_mt_dir;
+                                xrow = (int)((tl * p.T + (dirx ? p.T - 1 - p.lstm_s : p.lstm_s)) * BM);
+                            }
+                            if (xk) tma_load_2d_pair(s, &map_out, &full_bar[stage], kb * BK, xrow);
+                            else if (p.a_kmajor) tma_load_3d_pair(s, &map_a_hi, &full_bar[stage], 0, row0, (kb - p.lstm_kbx) * (BK / 8));
                             else tma_load_2d_pair(s, &map_a_hi, &full_bar[stage], kb * BK, row0);
                             tma_load_2d_pair(s + A_TILE_BYTES, &map_b_hi, &full_bar[stage], kb * BK, brow0);
                             if (p.passes == 3) {
-                                if (p.a_kmajor) tma_load_3d_pair(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], 0, row0, kb * (BK / 8));
+                                if (xk) tma_load_2d_pair(s + A_TILE_BYTES + b_tile_bytes, &map_out2, &full_bar[stage], kb * BK, xrow);
+                                else if (p.a_kmajor) tma_load_3d_pair(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], 0, row0, (kb - p.lstm_kbx) * (BK / 8));
                                 else
                                 tma_load_2d_pair(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], kb * BK, row0);
                                 tma_load_2d_pair(s + 2 * A_TILE_BYTES + b_tile_bytes, &map_b_lo, &full_bar[stage], kb * BK, brow0);
@@ -296,7 +311,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                             } else if (p.passes == 2) {     // a_lo's slot holds B'' here
                                 umma_f16(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(a_lo, k), idesc, 1);
                             }
-                        } else if (p.a_kmajor) {
+                        } else if (p.a_kmajor && kb >= p.lstm_kbx) {
                             // A tile = [8 K groups][128 rows][8]: k16 step k starts at group 2k; LBO = one group (2 KB), SBO = 128 B
                             const uint64_t ah = smem_desc_nosw(s + (uint32_t)k * 4096u, 2048, 128);
                             const uint64_t al = smem_desc_nosw(s + A_TILE_BYTES + b_tile_bytes + (uint32_t)k * 4096u, 2048, 128);
@@ -345,10 +360,16 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                 const int nbf = n_tile * p.BN + c0f;
                 if (!l_live || nbf >= p.N) return;
                 const int nuf = (p.N - nbf >= 32 && c0f + 32 <= p.BN) ? 8 : 4, u0f = nbf >> 2;
-                const float4 *xg = l_x + (int64_t)u0f * BM;
                 const float4 *cgp = l_c + (int64_t)(u0f >> 2) * BM;
+                if (p.lstm_x) {
+                    const float4 *xg = l_x + (int64_t)u0f * BM;
 #pragma unroll
-                for (int k = 0; k < 8; ++k) if (k < nuf) xpre[k] = __ldg(xg + k * BM);
+                    for (int k = 0; k < 8; ++k) if (k < nuf) xpre[k] = __ldg(xg + k * BM);
+                } else {                           // projection inside the GEMM: only the bias is left to add
+                    const float4 *bg = reinterpret_cast<const float4 *>(p.lstm_bias) + ((l_dir * p.N) >> 2) + u0f;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) if (k < nuf) xpre[k] = __ldg(bg + k);
+                }
                 cpre[0] = cgp[0];
                 if (nuf == 8) cpre[1] = cgp[BM];
             };
@@ -363,7 +384,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                     l_active = l_t < len;
                     l_tile = l_w >> 7; l_wl = (int)(l_w & 127);
                     const int64_t n_tiles = p.lstm_xmt / p.T;          // 128-window tiles of the job (not of the padded M)
-                    l_x = reinterpret_cast<const float4 *>(p.lstm_x) + ((l_dir * p.lstm_xmt + l_tile * p.T + l_t) * p.lstm_H) * (int64_t)BM + l_wl;
+                    if (p.lstm_x)
+                        l_x = reinterpret_cast<const float4 *>(p.lstm_x) + ((l_dir * p.lstm_xmt + l_tile * p.T + l_t) * p.lstm_H) * (int64_t)BM + l_wl;
                     l_c = reinterpret_cast<float4 *>(p.lstm_c) + ((l_dir * n_tiles + l_tile) * (p.lstm_H >> 2)) * (int64_t)BM + l_wl;
                 }
                 lstm_fetch(0);
@@ -1706,6 +1728,46 @@ int gemm_tc_pack_whh(cudaStream_t st, const float *kernel_fw, const float *kerne
 
 int64_t gemm_tc_lstm_state_floats(int64_t n_windows, int H) { return 2 * align_up(n_windows, BM) * H; }
 
+// [W_ih ; W_hh] along K for the step GEMM that carries the input projection: out [2 dirs][D + H][4H], column u*4 + g,
+// pre-scaled; wih is k_repack_lstm's [D][8H] (prescale = 1), rows D.. come from the TF kernels like k_pack_whh_kn
+__global__ void k_pack_wcat_kn(const float *__restrict__ wih, const float *__restrict__ kernel_fw,
+                               const float *__restrict__ kernel_bw, int D, int H, float *__restrict__ out) {
+    const int N = 4 * H, K = D + H;
+    const int64_t total = 2LL * K * N;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int n = (int)(i % N), k = (int)((i / N) % K), dir = (int)(i / ((int64_t)N * K));
+        if (k < D) { out[i] = wih[(int64_t)k * 2 * N + dir * N + n]; continue; }
+        const int u = n >> 2, g = n & 3;
+        const float *kern = dir ? kernel_bw : kernel_fw;
+        out[i] = (g == 1 ? LSTM_PRESCALE_J : LSTM_PRESCALE_IFO) * kern[(int64_t)k * N + g * H + u];
+    }
+}
+
+bool gemm_tc_lstm_fused_supported(int H, int D) { return gemm_tc_lstm_supported(H) && D % BK == 0 && D >= BK && H % BK == 0; }
+
+void gemm_tc_plan_wcat(GemmWeights &w, int H, int D, Arena &ar, float **staging) {
+    gemm_tc_plan_weights(w, 2, D + H, 4 * H, ar);
+    *staging = w.valid ? ar.take<float>(2LL * (D + H) * 4 * H) : nullptr;
+}
+
+int gemm_tc_pack_wcat(cudaStream_t st, const float *wih, const float *kernel_fw, const float *kernel_bw, int D, int H,
+                      float *staging, GemmWeights &w) {
+    if (!w.valid) return NTB_OK;
+    k_pack_wcat_kn<<<1024, 256, 0, st>>>(wih, kernel_fw, kernel_bw, D, H, staging);
+    NTB_LAUNCH_CHECK();
+    return gemm_tc_pack_weights(st, staging, w);
+}
+
+int gemm_tc_split_timemajor(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, int K, op16_t *hi, op16_t *lo,
+                            int64_t *launches) {
+    if (K % 8 || (lda & 3) || (reinterpret_cast<uintptr_t>(A) & 15) || !hi || !lo)
+        return fail(NTB_EINVAL, "time-major split: operand not supported (K %s%lld)", "", (long long)K);
+    SplitParams sp{};
+    sp.A = A; sp.lda = lda; sp.rows = n_windows * T; sp.K = K; sp.T = T; sp.relu = 0; sp.pad = 0; sp.perm = 1;
+    sp.hi = hi; sp.lo = lo; sp.plane_rows = align_up(n_windows, BM) * T;
+    return launch_split(st, sp, launches);
+}
+
 // 3-D view of a k-group-major operand plane [K/8][rows][8] fp16: box {8, 128 rows, 8 groups} = one [128 x 64] A tile
 static int make_map_kmajor(CUtensorMap *m, const void *base, int64_t rows, int K) {
     EncodeTiledFn fn = encode_fn();
@@ -1725,11 +1787,14 @@ static int make_map_kmajor(CUtensorMap *m, const void *base, int64_t rows, int K
 // xproj: the unit-major projected-gates buffer gemm_tc_run_xproj writes ([dir][128-window tile x T + t][unit][128] float4)
 int gemm_tc_lstm_layer(cudaStream_t st, const GemmWeights &whh, const float *xproj, int ldx, const int32_t *lens,
                        int64_t n_windows, int T, int H, float *cstate, float *out, int ldo, const GemmScratch &gs,
-                       int64_t *launches) {
+                       int64_t *launches, int D_fused, const op16_t *x_hi, const op16_t *x_lo, const float *bias) {
     const int cg = gemm_cta_group();
+    const int Kw = H + D_fused;                                      // K of the weight planes: [W_ih ;] W_hh
+    if (D_fused && (!x_hi || !x_lo || !bias || D_fused % BK || H % BK))
+        return fail(NTB_EINVAL, "tcgen05 LSTM step with the projection inside: operand not supported (D %s%lld)", "", (long long)D_fused);
     const int64_t Mp = align_up(n_windows, 2 * BM);                 // a CTA pair never straddles the directions
     const int64_t plane_elems = 2 * Mp * H;                          // one parity: [2 dirs][Mp][H]
-    if (!whh.valid || !gs.valid || whh.K != H || whh.N != 4 * H || whh.BN % 16 || cg != 2 ||
+    if (!whh.valid || !gs.valid || whh.K != Kw || whh.N != 4 * H || whh.BN % 16 || cg != 2 ||
         2 * plane_elems > gs.rows_cap * (int64_t)gs.kp_cap || (ldo & 3) || H % 8)
         return fail(NTB_EINVAL, "tcgen05 LSTM step: operand not supported (windows %s%lld, H %lld)", "",
                     (long long)n_windows, (long long)H);
@@ -1752,12 +1817,19 @@ int gemm_tc_lstm_layer(cudaStream_t st, const GemmWeights &whh, const float *xpr
     p.lstm_H = H; p.lstm_mt_dir = (int)(Mp / BM); p.lstm_n = n_windows; p.lstm_Mp = Mp;
     p.lstm_x = xproj; p.lstm_ldx = ldx; p.lstm_c = cstate; p.lstm_lens = lens;
     p.lstm_xmt = (align_up(n_windows, BM) / BM) * T; p.a_kmajor = 1;
+    CUtensorMap mx_hi = ma_hi[0], mx_lo = ma_lo[0];
+    if (D_fused) {
+        const int64_t xrows = align_up(n_windows, BM) * T;           // time-major planes: row (tile T + t) 128 + window
+        NTB_TRY(make_map(&mx_hi, x_hi, xrows, D_fused, BM));
+        NTB_TRY(make_map(&mx_lo, x_lo, xrows, D_fused, BM));
+        p.lstm_kbx = D_fused / BK; p.lstm_bias = bias; p.lstm_x = nullptr;
+    }
     for (int s = 0; s < T; ++s) {
         const int rd = s & 1, wr = rd ^ 1;
         p.lstm_s = s;
         p.lstm_hi = gs.a_hi + wr * plane_elems;
         p.lstm_lo = gs.a_lo + wr * plane_elems;
-        NTB_TRY(do_launch(st, ma_hi[rd], ma_lo[rd], mb_hi, mb_lo, ma_hi[rd], p, launches));
+        NTB_TRY(do_launch(st, ma_hi[rd], ma_lo[rd], mb_hi, mb_lo, mx_hi, p, launches, &mx_lo));
     }
     return NTB_OK;
 }

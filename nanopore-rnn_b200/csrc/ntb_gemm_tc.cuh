@@ -88,8 +88,19 @@ void gemm_tc_plan_whh(GemmWeights &w, int H, Arena &ar, float **staging);
 int gemm_tc_pack_whh(cudaStream_t st, const float *kernel_fw, const float *kernel_bw, int D, int H, float *staging,
                      GemmWeights &w);
 int64_t gemm_tc_lstm_state_floats(int64_t n_windows, int H);
+// D_fused > 0: the input projection rides in the same GEMM (whh = [W_ih ; W_hh] planes from gemm_tc_plan_wcat /
+// gemm_tc_pack_wcat, x_hi / x_lo = the layer input as time-major operand planes from gemm_tc_split_timemajor, bias
+// [2][4H] pre-scaled with the forget bias folded); xproj is then unused.
 int gemm_tc_lstm_layer(cudaStream_t st, const GemmWeights &whh, const float *xproj, int ldx, const int32_t *lens,
                        int64_t n_windows, int T, int H, float *cstate, float *out, int ldo, const GemmScratch &gs,
-                       int64_t *launches);
+                       int64_t *launches, int D_fused = 0, const op16_t *x_hi = nullptr, const op16_t *x_lo = nullptr,
+                       const float *bias = nullptr);
+bool gemm_tc_lstm_fused_supported(int H, int D);
+void gemm_tc_plan_wcat(GemmWeights &w, int H, int D, Arena &ar, float **staging);
+int gemm_tc_pack_wcat(cudaStream_t st, const float *wih, const float *kernel_fw, const float *kernel_bw, int D, int H,
+                      float *staging, GemmWeights &w);
+// fp32 [n_windows*T][lda] -> time-major fp16 hi/lo planes [(tile T + t) 128 + window][K] (whole 128-window tiles)
+int gemm_tc_split_timemajor(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, int K, op16_t *hi,
+                            op16_t *lo, int64_t *launches);
 
 }  // namespace ntb
