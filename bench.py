@@ -406,26 +406,26 @@ def roofline_of(cx, stage, n, n_chunks, steps, ms_step):
                                      "achieved_tflops": fused_tf, "frac": fused_tf / peak,
                                      "tensor_pipe_frac_with_3_passes": 3 * fused_tf / peak})
     elif stage4["recurrence"] > 0:
-        # H > 100: one tcgen05 GEMM launch per timestep; where the layer input is a multiple of 64 wide the projection
-        # x_t.W_ih is part of that GEMM's contraction ([W_ih ; W_hh] along K), so its FLOPs belong to this kernel
+        # H > 100: one tcgen05 GEMM launch per timestep; the projection x_t.W_ih is part of that GEMM's contraction
+        # ([W_ih ; W_hh] along K, H % 64 == 0), so its FLOPs belong to this kernel
         kname = "k_gemm_tc<2> (per-timestep GEMM [x_t | h_{t-1}].[W_ih ; W_hh] with fused cell epilogue, tcgen05 fp16x3)"
         inside, d = 0.0, WL["len_x"]
         for l in net:
             if l["type"] == "blstm":
-                if d % 64 == 0 and l["size"] % 64 == 0:
+                if d % 4 == 0 and l["size"] % 64 == 0:          # narrow inputs are zero-padded to one 64-wide k-block
                     inside += 16.0 * T * d * l["size"]
                 d = 2 * l["size"]
         k_ms, k_flops = stage4["recurrence"], flops["recurrence"] + inside
         n_launch_k = n_blstm * T * n_chunks * steps
         tkey = "k_gemm_tc_step_dram_bytes_per_window"
         step_tf = k_flops * n * steps / (k_ms * 1e-3) / 1e12
-        stages["recurrence"].update({"includes": "the projections of the layers whose input width is a multiple of 64",
+        stages["recurrence"].update({"includes": "the input projections (same GEMM)",
                                      "algorithmic_mflop_per_window": k_flops / 1e6, "achieved_tflops": step_tf,
                                      "frac": step_tf / peak, "tensor_pipe_frac_with_3_passes": 3 * step_tf / peak})
         rest = flops["projection"] - inside
         if stage4["projection"] > 0:
             ptf = rest * n * steps / (stage4["projection"] * 1e-3) / 1e12
-            stages["projection"].update({"what": "the remaining projections (len_x = 12: FMA kernel) + operand splits",
+            stages["projection"].update({"what": "operand splits of the layer inputs (and any projection left outside the step GEMM)",
                                          "algorithmic_mflop_per_window": rest / 1e6, "achieved_tflops": ptf, "frac": ptf / peak,
                                          "tensor_pipe_frac_with_3_passes": 3 * ptf / peak})
     else:

@@ -324,7 +324,7 @@ static int64_t model_weight_plan(const ntb_model_desc *d, ntb_model *m, Arena &a
             } else if (Hp == H && gemm_tc_lstm_supported(H)) {
                 gemm_tc_plan_whh(ld.whhw, H, ar, &ld.whh_stage);
                 ld.step_rec = ld.whhw.valid;
-                if (ld.step_rec && ld.wihw.valid && gemm_tc_lstm_fused_supported(H, D) && !ntb_env("NTB_NO_FUSED_STEP")) {
+                if (ld.step_rec && gemm_tc_lstm_fused_supported(H, D) && !ntb_env("NTB_NO_FUSED_STEP")) {
                     gemm_tc_plan_wcat(ld.wcatw, H, D, ar, &ld.wcat_stage);
                     ld.step_fused = ld.wcatw.valid;
                 }
@@ -713,12 +713,13 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
                 if (ld.step_fused) {
                     // the projection rides in the per-timestep GEMM: the layer input goes to time-major operand planes (they
                     // live where the projected gates would have been) and no projected gates exist
+                    const int Dp = gemm_tc_lstm_fused_dpad(dim);       // len_x = 12 -> one zero-padded k-block of 64
                     op16_t *x_hi = reinterpret_cast<op16_t *>(ws.xproj);
-                    op16_t *x_lo = x_hi + align_up(n, LSTM_TC_ROWS) * T * (int64_t)dim;
-                    NTB_TRY(gemm_tc_split_timemajor(cx.st, cur, dim, n, T, dim, x_hi, x_lo, &cx.launches));
+                    op16_t *x_lo = x_hi + align_up(n, LSTM_TC_ROWS) * T * (int64_t)Dp;
+                    NTB_TRY(gemm_tc_split_timemajor(cx.st, cur, dim, n, T, dim, Dp, x_hi, x_lo, &cx.launches));
                     NTB_TRY(mark(2));
                     NTB_TRY(gemm_tc_lstm_layer(cx.st, ld.wcatw, nullptr, N, lens, n, T, ld.size, ws.cstate, out, 2 * ld.size,
-                                               ws.gs, &cx.launches, dim, x_hi, x_lo, ld.bias));
+                                               ws.gs, &cx.launches, Dp, x_hi, x_lo, ld.bias));
                 } else {
                 NTB_TRY(step_rec_projection(cx, cur, dim, n, T, ld.size, ld.wih, ld.bias, ld.wihw, ws.xproj, ws.gs));
                 NTB_TRY(mark(2));
@@ -1554,7 +1555,7 @@ static int64_t plan_blstm_op(Arena &ar, int64_t n, int T, int D, int H, BlstmOpB
         const int64_t step_rows = cdiv(4 * align_up(n, 256) * H, align_up(kcap, 8));
         gemm_tc_plan_scratch(b.gs, rows, T, kcap, ar, step_rows > tile_rows ? step_rows : tile_rows);
         b.step = b.whhw.valid && b.gs.valid;
-        if (b.step && b.wihw.valid && gemm_tc_lstm_fused_supported(H, D) && !ntb_env("NTB_NO_FUSED_STEP")) {
+        if (b.step && gemm_tc_lstm_fused_supported(H, D) && !ntb_env("NTB_NO_FUSED_STEP")) {
             gemm_tc_plan_wcat(b.wcatw, H, D, ar, &b.wcat_stage);
             b.step_fused = b.wcatw.valid;
         }
@@ -1615,11 +1616,12 @@ extern "C" int ntb_blstm(const float *in_dev, const int32_t *len_dev, const floa
         NTB_TRY(gemm_tc_pack_whh(cx.st, kernel_fw_dev, kernel_bw_dev, D, H, b.whh_stage, b.whhw));
         if (b.step_fused) {
             NTB_TRY(gemm_tc_pack_wcat(cx.st, b.wih, kernel_fw_dev, kernel_bw_dev, D, H, b.wcat_stage, b.wcatw));
+            const int Dp = gemm_tc_lstm_fused_dpad(D);
             op16_t *x_hi = reinterpret_cast<op16_t *>(b.xproj);
-            op16_t *x_lo = x_hi + align_up(n_windows, LSTM_TC_ROWS) * T * (int64_t)D;
-            NTB_TRY(gemm_tc_split_timemajor(cx.st, in_dev, D, n_windows, T, D, x_hi, x_lo, &cx.launches));
+            op16_t *x_lo = x_hi + align_up(n_windows, LSTM_TC_ROWS) * T * (int64_t)Dp;
+            NTB_TRY(gemm_tc_split_timemajor(cx.st, in_dev, D, n_windows, T, D, Dp, x_hi, x_lo, &cx.launches));
             return gemm_tc_lstm_layer(cx.st, b.wcatw, nullptr, 8 * Hp, len_dev, n_windows, T, H, b.cstate, out_dev, 2 * H, b.gs,
-                                      &cx.launches, D, x_hi, x_lo, b.bias);
+                                      &cx.launches, Dp, x_hi, x_lo, b.bias);
         }
         NTB_TRY(step_rec_projection(cx, in_dev, D, n_windows, T, H, b.wih, b.bias, b.wihw, b.xproj, b.gs));
         return gemm_tc_lstm_layer(cx.st, b.whhw, b.xproj, 8 * Hp, len_dev, n_windows, T, H, b.cstate, out_dev, 2 * H, b.gs,

@@ -902,6 +902,7 @@ struct SplitParams {
                              // 2: same rows, k-group-major tiles [tile][t][K8p][128][8] (fused BLSTM kernel, ntb_blstm_fused.cuh)
     int K8p;                 // perm 2: 8-channel groups per (tile, t) = 2 * ceil(K / 16); groups >= K / 8 are zero
     int expand;              // 1: A is [rows] (a Cin = 1 conv folded into the affine): v[c] = A[r] * a[g][c] + b[g][c]
+    int Ksrc;                // > 0: the source has only Ksrc (% 4 == 0) channels, the plane's other channels are zero
 };
 
 __global__ void __launch_bounds__(256) k_split_op16(const SplitParams p) {
@@ -930,8 +931,10 @@ __global__ void __launch_bounds__(256) k_split_op16(const SplitParams p) {
         real = real && r < p.rows;
         float v[8];
         if (real) {
-            const float4 x0 = *reinterpret_cast<const float4 *>(p.A + r * p.lda + c);
-            const float4 x1 = *reinterpret_cast<const float4 *>(p.A + r * p.lda + c + 4);
+            const int ks = p.Ksrc > 0 ? p.Ksrc : p.K;
+            const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4 x0 = c < ks ? *reinterpret_cast<const float4 *>(p.A + r * p.lda + c) : zero4;
+            const float4 x1 = c + 4 < ks ? *reinterpret_cast<const float4 *>(p.A + r * p.lda + c + 4) : zero4;
             v[0] = x0.x; v[1] = x0.y; v[2] = x0.z; v[3] = x0.w; v[4] = x1.x; v[5] = x1.y; v[6] = x1.z; v[7] = x1.w;
             if (p.aff_a) {
                 const int g = p.win_group[w];
@@ -1730,40 +1733,44 @@ int64_t gemm_tc_lstm_state_floats(int64_t n_windows, int H) { return 2 * align_u
 
 // [W_ih ; W_hh] along K for the step GEMM that carries the input projection: out [2 dirs][D + H][4H], column u*4 + g,
 // pre-scaled; wih is k_repack_lstm's [D][8H] (prescale = 1), rows D.. come from the TF kernels like k_pack_whh_kn
+// (D = the layer's input width, Dp = D padded to the k-block of 64: the padding rows are zero)
 __global__ void k_pack_wcat_kn(const float *__restrict__ wih, const float *__restrict__ kernel_fw,
-                               const float *__restrict__ kernel_bw, int D, int H, float *__restrict__ out) {
-    const int N = 4 * H, K = D + H;
+                               const float *__restrict__ kernel_bw, int D, int Dp, int H, float *__restrict__ out) {
+    const int N = 4 * H, K = Dp + H;
     const int64_t total = 2LL * K * N;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int n = (int)(i % N), k = (int)((i / N) % K), dir = (int)(i / ((int64_t)N * K));
-        if (k < D) { out[i] = wih[(int64_t)k * 2 * N + dir * N + n]; continue; }
+        if (k < Dp) { out[i] = k < D ? wih[(int64_t)k * 2 * N + dir * N + n] : 0.0f; continue; }
         const int u = n >> 2, g = n & 3;
         const float *kern = dir ? kernel_bw : kernel_fw;
-        out[i] = (g == 1 ? LSTM_PRESCALE_J : LSTM_PRESCALE_IFO) * kern[(int64_t)k * N + g * H + u];
+        out[i] = (g == 1 ? LSTM_PRESCALE_J : LSTM_PRESCALE_IFO) * kern[(int64_t)(D + k - Dp) * N + g * H + u];
     }
 }
 
-bool gemm_tc_lstm_fused_supported(int H, int D) { return gemm_tc_lstm_supported(H) && D % BK == 0 && D >= BK && H % BK == 0; }
+// any input width that is a multiple of 4 floats: the planes and W_ih are zero-padded to whole 64-wide k-blocks
+bool gemm_tc_lstm_fused_supported(int H, int D) { return gemm_tc_lstm_supported(H) && D % 4 == 0 && D >= 4 && H % BK == 0; }
+int gemm_tc_lstm_fused_dpad(int D) { return (int)align_up(D, BK); }
 
 void gemm_tc_plan_wcat(GemmWeights &w, int H, int D, Arena &ar, float **staging) {
-    gemm_tc_plan_weights(w, 2, D + H, 4 * H, ar);
-    *staging = w.valid ? ar.take<float>(2LL * (D + H) * 4 * H) : nullptr;
+    const int Dp = gemm_tc_lstm_fused_dpad(D);
+    gemm_tc_plan_weights(w, 2, Dp + H, 4 * H, ar);
+    *staging = w.valid ? ar.take<float>(2LL * (Dp + H) * 4 * H) : nullptr;
 }
 
 int gemm_tc_pack_wcat(cudaStream_t st, const float *wih, const float *kernel_fw, const float *kernel_bw, int D, int H,
                       float *staging, GemmWeights &w) {
     if (!w.valid) return NTB_OK;
-    k_pack_wcat_kn<<<1024, 256, 0, st>>>(wih, kernel_fw, kernel_bw, D, H, staging);
+    k_pack_wcat_kn<<<1024, 256, 0, st>>>(wih, kernel_fw, kernel_bw, D, gemm_tc_lstm_fused_dpad(D), H, staging);
     NTB_LAUNCH_CHECK();
     return gemm_tc_pack_weights(st, staging, w);
 }
 
-int gemm_tc_split_timemajor(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, int K, op16_t *hi, op16_t *lo,
-                            int64_t *launches) {
-    if (K % 8 || (lda & 3) || (reinterpret_cast<uintptr_t>(A) & 15) || !hi || !lo)
+int gemm_tc_split_timemajor(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, int Ksrc, int K, op16_t *hi,
+                            op16_t *lo, int64_t *launches) {
+    if (K % 8 || Ksrc % 4 || Ksrc > K || (lda & 3) || (reinterpret_cast<uintptr_t>(A) & 15) || !hi || !lo)
         return fail(NTB_EINVAL, "time-major split: operand not supported (K %s%lld)", "", (long long)K);
     SplitParams sp{};
-    sp.A = A; sp.lda = lda; sp.rows = n_windows * T; sp.K = K; sp.T = T; sp.relu = 0; sp.pad = 0; sp.perm = 1;
+    sp.A = A; sp.lda = lda; sp.rows = n_windows * T; sp.K = K; sp.Ksrc = Ksrc; sp.T = T; sp.relu = 0; sp.pad = 0; sp.perm = 1;
     sp.hi = hi; sp.lo = lo; sp.plane_rows = align_up(n_windows, BM) * T;
     return launch_split(st, sp, launches);
 }

@@ -99,8 +99,10 @@ bool gemm_tc_lstm_fused_supported(int H, int D);
 void gemm_tc_plan_wcat(GemmWeights &w, int H, int D, Arena &ar, float **staging);
 int gemm_tc_pack_wcat(cudaStream_t st, const float *wih, const float *kernel_fw, const float *kernel_bw, int D, int H,
                       float *staging, GemmWeights &w);
-// fp32 [n_windows*T][lda] -> time-major fp16 hi/lo planes [(tile T + t) 128 + window][K] (whole 128-window tiles)
-int gemm_tc_split_timemajor(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, int K, op16_t *hi,
+int gemm_tc_lstm_fused_dpad(int D);   // input width padded to whole k-blocks (64): D_fused of gemm_tc_lstm_layer
+// fp32 [n_windows*T][lda] (Ksrc channels) -> time-major fp16 hi/lo planes [(tile T + t) 128 + window][K], K >= Ksrc
+// (channels beyond Ksrc zero; whole 128-window tiles)
+int gemm_tc_split_timemajor(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, int Ksrc, int K, op16_t *hi,
                             op16_t *lo, int64_t *launches);
 
 }  // namespace ntb
