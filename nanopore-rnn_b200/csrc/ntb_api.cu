@@ -637,7 +637,8 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
     const bool small_c = m->C <= 8;
     const LayerDev *fused_fnn = nullptr;
     int planes = 0;   // the GEMM operand planes hold the current activation: 1 plain rows, 2 time-major tiles,
-                      // 3 k-group-major tiles in the scratch planes, 4 the same in the fx planes (fused BLSTM layers)
+                      // 3 k-group-major tiles in the scratch planes, 4 the same in the fx planes (fused BLSTM layers),
+                      // 5 / 6 time-major planes in region 0 / 1 of the projected-gates buffer (H > 100 layers)
     for (size_t li = 0; li < nl; ++li) {
         const LayerDev &ld = m->layers[li];
         float *out = ws.act[flip];
@@ -714,12 +715,27 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
                     // the projection rides in the per-timestep GEMM: the layer input goes to time-major operand planes (they
                     // live where the projected gates would have been) and no projected gates exist
                     const int Dp = gemm_tc_lstm_fused_dpad(dim);       // len_x = 12 -> one zero-padded k-block of 64
-                    op16_t *x_hi = reinterpret_cast<op16_t *>(ws.xproj);
-                    op16_t *x_lo = x_hi + align_up(n, LSTM_TC_ROWS) * T * (int64_t)Dp;
-                    NTB_TRY(gemm_tc_split_timemajor(cx.st, cur, dim, n, T, dim, Dp, x_hi, x_lo, &cx.launches));
+                    // two plane regions inside the (otherwise unused) projected-gates buffer: a layer reads one and, when the
+                    // next layer is of the same kind, writes h_t straight into the other (no fp32 hand-over, no split pass)
+                    const int64_t trows = align_up(n, LSTM_TC_ROWS) * T;
+                    const int64_t region = 2 * trows * (int64_t)(m->max_proj_n / 4);       // elements; 8H/4 = 2H >= any Dp here
+                    op16_t *base = reinterpret_cast<op16_t *>(ws.xproj);
+                    const int rin = planes == 6 ? 1 : 0;
+                    op16_t *x_hi = base + rin * region, *x_lo = x_hi + trows * (int64_t)Dp;
+                    if (planes != 5 && planes != 6)
+                        NTB_TRY(gemm_tc_split_timemajor(cx.st, cur, dim, n, T, dim, Dp, x_hi, x_lo, &cx.launches));
                     NTB_TRY(mark(2));
+                    const bool feed = li + 1 < nl && m->layers[li + 1].type == NTB_LAYER_BLSTM && m->layers[li + 1].step_fused &&
+                                      (2 * ld.size) % 64 == 0 && 2 * ld.size <= m->max_proj_n / 4 && Dp <= m->max_proj_n / 4;
+                    op16_t *nx_hi = feed ? base + (1 - rin) * region : nullptr;
+                    op16_t *nx_lo = feed ? nx_hi + trows * (int64_t)(2 * ld.size) : nullptr;
                     NTB_TRY(gemm_tc_lstm_layer(cx.st, ld.wcatw, nullptr, N, lens, n, T, ld.size, ws.cstate, out, 2 * ld.size,
-                                               ws.gs, &cx.launches, Dp, x_hi, x_lo, ld.bias));
+                                               ws.gs, &cx.launches, Dp, x_hi, x_lo, ld.bias, nx_hi, nx_lo));
+                    dim = 2 * ld.size;
+                    planes = feed ? (rin ? 5 : 6) : 0;
+                    cur = out;
+                    flip ^= 1;
+                    continue;
                 } else {
                 NTB_TRY(step_rec_projection(cx, cur, dim, n, T, ld.size, ld.wih, ld.bias, ld.wihw, ws.xproj, ws.gs));
                 NTB_TRY(mark(2));

@@ -85,6 +85,10 @@ struct TcParams {
     // along K.  No projected gates exist then (lstm_x == null): the epilogue adds lstm_bias [2][4H] instead.
     int lstm_kbx;
     const float *lstm_bias;
+    // lstm_nx_hi != null: h_t goes out as the NEXT layer's time-major operand planes ([(tile T + t) 128 + window][lstm_nx_K],
+    // column dir H + unit) instead of the fp32 layer output: no split pass between two stacked layers
+    op16_t *lstm_nx_hi, *lstm_nx_lo;
+    int lstm_nx_K;
     int a_kmajor;                      // the A planes are [K/8][rows][8] (no swizzle; 3-D TMA box {8, 128, 8}) instead of
                                        // row-major rows with the 128-byte swizzle: the LSTM epilogue's h stores coalesce
 };
@@ -487,14 +491,25 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                             }
                             if (l_active) cg[half * BM] = make_float4(cc[0], cc[1], cc[2], cc[3]);
                         }
-                        float *og = p.out + (l_w * p.T + l_t) * (int64_t)p.ldo + l_dir * H + u0;
-                        *reinterpret_cast<float4 *>(og) = make_float4(hv[0], hv[1], hv[2], hv[3]);
-                        if (nu == 8) *reinterpret_cast<float4 *>(og + 4) = make_float4(hv[4], hv[5], hv[6], hv[7]);
                         uint4 ph, pl;
                         split_pack_op16x2(hv[0], hv[1], ph.x, pl.x);
                         split_pack_op16x2(hv[2], hv[3], ph.y, pl.y);
                         split_pack_op16x2(hv[4], hv[5], ph.z, pl.z);
                         split_pack_op16x2(hv[6], hv[7], ph.w, pl.w);
+                        if (p.lstm_nx_hi) {
+                            const int64_t no = ((l_tile * p.T + l_t) * BM + l_wl) * (int64_t)p.lstm_nx_K + l_dir * H + u0;
+                            if (nu == 8) {
+                                *reinterpret_cast<uint4 *>(p.lstm_nx_hi + no) = ph;
+                                *reinterpret_cast<uint4 *>(p.lstm_nx_lo + no) = pl;
+                            } else {
+                                *reinterpret_cast<uint2 *>(p.lstm_nx_hi + no) = make_uint2(ph.x, ph.y);
+                                *reinterpret_cast<uint2 *>(p.lstm_nx_lo + no) = make_uint2(pl.x, pl.y);
+                            }
+                        } else {
+                            float *og = p.out + (l_w * p.T + l_t) * (int64_t)p.ldo + l_dir * H + u0;
+                            *reinterpret_cast<float4 *>(og) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+                            if (nu == 8) *reinterpret_cast<float4 *>(og + 4) = make_float4(hv[4], hv[5], hv[6], hv[7]);
+                        }
                         if (nu == 8 && (u0 & 7) == 0) {                      // one whole K group: 16 bytes per plane
                             const int64_t po = ((int64_t)(u0 >> 3) * (2 * p.lstm_Mp) + prow) * 8;
                             *reinterpret_cast<uint4 *>(p.lstm_hi + po) = ph;
@@ -1794,7 +1809,8 @@ static int make_map_kmajor(CUtensorMap *m, const void *base, int64_t rows, int K
 // xproj: the unit-major projected-gates buffer gemm_tc_run_xproj writes ([dir][128-window tile x T + t][unit][128] float4)
 int gemm_tc_lstm_layer(cudaStream_t st, const GemmWeights &whh, const float *xproj, int ldx, const int32_t *lens,
                        int64_t n_windows, int T, int H, float *cstate, float *out, int ldo, const GemmScratch &gs,
-                       int64_t *launches, int D_fused, const op16_t *x_hi, const op16_t *x_lo, const float *bias) {
+                       int64_t *launches, int D_fused, const op16_t *x_hi, const op16_t *x_lo, const float *bias,
+                       op16_t *next_hi, op16_t *next_lo) {
     const int cg = gemm_cta_group();
     const int Kw = H + D_fused;                                      // K of the weight planes: [W_ih ;] W_hh
     if (D_fused && (!x_hi || !x_lo || !bias || D_fused % BK || H % BK))
@@ -1831,6 +1847,7 @@ int gemm_tc_lstm_layer(cudaStream_t st, const GemmWeights &whh, const float *xpr
         NTB_TRY(make_map(&mx_lo, x_lo, xrows, D_fused, BM));
         p.lstm_kbx = D_fused / BK; p.lstm_bias = bias; p.lstm_x = nullptr;
     }
+    if (next_hi && next_lo) { p.lstm_nx_hi = next_hi; p.lstm_nx_lo = next_lo; p.lstm_nx_K = 2 * H; }
     for (int s = 0; s < T; ++s) {
         const int rd = s & 1, wr = rd ^ 1;
         p.lstm_s = s;

@@ -94,7 +94,9 @@ int64_t gemm_tc_lstm_state_floats(int64_t n_windows, int H);
 int gemm_tc_lstm_layer(cudaStream_t st, const GemmWeights &whh, const float *xproj, int ldx, const int32_t *lens,
                        int64_t n_windows, int T, int H, float *cstate, float *out, int ldo, const GemmScratch &gs,
                        int64_t *launches, int D_fused = 0, const op16_t *x_hi = nullptr, const op16_t *x_lo = nullptr,
-                       const float *bias = nullptr);
+                       const float *bias = nullptr, op16_t *next_hi = nullptr, op16_t *next_lo = nullptr);
+// next_hi / next_lo: h_t is written as the next stacked layer's time-major operand planes (K = 2H, must be a multiple of
+// 64) instead of the fp32 `out`.
 bool gemm_tc_lstm_fused_supported(int H, int D);
 void gemm_tc_plan_wcat(GemmWeights &w, int H, int D, Arena &ar, float **staging);
 int gemm_tc_pack_wcat(cudaStream_t st, const float *wih, const float *kernel_fw, const float *kernel_bw, int D, int H,
