@@ -297,6 +297,26 @@ NTB_API int ntb_ctc_beam_search(const float *logits_dev, const int32_t *len_dev,
                         void *workspace_dev, int64_t workspace_bytes, int32_t *paths_dev, int32_t *path_len_dev,
                         float *log_prob_dev, void *stream);
 
+/* Allocation-free variant of ntb_ctc_beam_search.  It has NO counterpart in the reference: it was added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same kernel, same arguments and results as ntb_ctc_beam_search, but the scratch (the
+ * prefix trees of the sequences in flight) is a file-scope `static __device__` array of NTB_NOALLOC_SCRATCH_BYTES inside
+ * the library instead of a caller workspace; the call allocates nothing (no cudaMalloc / cudaFree, no library routine that
+ * allocates) and every GPU that loads the library holds the array until the process exits.
+ * Limit: one block of 4 sequences must fit the array, i.e. seq_len * beam_width <= NTB_NOALLOC_MAX_T_TIMES_BEAM
+ * (T = 300 x beam 100 fits, T = 512 x beam 128 does not); larger shapes return NTB_EINVAL with a message that names the
+ * limit -- use ntb_ctc_beam_search with a caller workspace for those.  n_windows is not limited: the grid is sized to the
+ * array (fewer sequences in flight than with a caller workspace, so large jobs run slower).
+ * All calls on a device share the one array: calls that overlap on the GPU (different streams, or different host threads)
+ * race on it -- serialise them.  The array keeps the previous call's contents; nothing in it has to start at zero (the
+ * kernel writes every tree node before reading it), so no clearing happens between calls. */
+#define NTB_NOALLOC_SCRATCH_BYTES (8 * 1024 * 1024)
+#define NTB_NOALLOC_MAX_T_TIMES_BEAM (NTB_NOALLOC_SCRATCH_BYTES / (4 * 12 * 4) - 1)
+NTB_API int ntb_ctc_beam_search_noalloc(const float *logits_dev, const int32_t *len_dev, int64_t n_windows, int32_t T,
+                                int32_t C, int32_t beam_width, int32_t top_paths, int32_t merge_repeated,
+                                int32_t log_softmax, int32_t *paths_dev, int32_t *path_len_dev, float *log_prob_dev,
+                                void *stream);
+
 /* Dense GEMM used by the conv / projection stages, exposed for roofline measurement and
  * parity tests: out[M,N] = A[M,K] @ B[K,N] (+ bias[N]), float32 in/out.
  * impl 0 = fp32 SIMT, 1 = tcgen05 fp16x3 (TMA + TMEM), 2 = tcgen05 single-pass fp16. */

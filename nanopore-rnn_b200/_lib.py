@@ -66,6 +66,7 @@ SIGNATURES = {
     "ntb_ctc_greedy": (C.c_int, [_P, _P, _I64, _I32, _I32, _I32, _P, _P, _P, _P]),
     "ntb_ctc_beam_workspace_bytes": (_I64, [_I64, _I32, _I32]),
     "ntb_ctc_beam_search": (C.c_int, [_P, _P, _I64, _I32, _I32, _I32, _I32, _I32, _I32, _P, _I64, _P, _P, _P, _P]),
+    "ntb_ctc_beam_search_noalloc": (C.c_int, [_P, _P, _I64, _I32, _I32, _I32, _I32, _I32, _I32, _P, _P, _P, _P]),
     "ntb_gemm": (C.c_int, [_P, _P, _P, _I64, _I32, _I32, _I32, _P, _I64, _P, _P]),
     "ntb_gemm_workspace_bytes": (_I64, [_I64, _I32, _I32, _I32]),
 }

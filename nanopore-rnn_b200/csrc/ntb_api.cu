@@ -1716,6 +1716,53 @@ extern "C" int ntb_ctc_beam_search(const float *logits_dev, const int32_t *len_d
     return NTB_OK;
 }
 
+// ---------------------------------------------------------------------- allocation-free variant (no reference counterpart)
+// ntb_ctc_beam_search with its scratch (the prefix trees of the sequences in flight) in a file-scope device array instead of
+// a caller workspace: for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+// Every GPU that loads the library holds the array until exit.  All calls share it: calls that overlap on the GPU race.
+// Nothing has to start at zero -- the kernel writes every tree node (root included) before it reads it -- so the previous
+// call's contents are simply overwritten.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NTB_NOALLOC_SCRATCH_BYTES];
+
+extern "C" int ntb_ctc_beam_search_noalloc(const float *logits_dev, const int32_t *len_dev, int64_t n_windows, int32_t T,
+                                           int32_t C, int32_t beam_width, int32_t top_paths, int32_t merge_repeated,
+                                           int32_t log_softmax, int32_t *paths_dev, int32_t *path_len_dev,
+                                           float *log_prob_dev, void *stream) {
+    if (!logits_dev || !len_dev || !paths_dev || !path_len_dev || !log_prob_dev || n_windows < 0 || T <= 0 || T > 512 ||
+        C < 2 || C > CTC_MAXC || beam_width < 1 || beam_width > CTC_MAXW || top_paths < 1 || top_paths > beam_width)
+        return fail(NTB_EINVAL, "ntb_ctc_beam_search_noalloc: bad argument (2 <= C <= 8, beam_width <= 128, T <= 512, top_paths <= beam_width)%s", "");
+    // one block (CTC_WARPS sequences in flight) must fit the static scratch
+    const int64_t per_block = (int64_t)CTC_WARPS * CTC_NODE_I32 * ((int64_t)T * beam_width + 1) * (int64_t)sizeof(int32_t);
+    if (per_block > (int64_t)NTB_NOALLOC_SCRATCH_BYTES)
+        return fail(NTB_EINVAL, "ntb_ctc_beam_search_noalloc: seq_len * beam_width = %s%lld exceeds the static scratch (limit %lld); "
+                    "use ntb_ctc_beam_search with a caller workspace", "", (long long)T * beam_width,
+                    (long long)NTB_NOALLOC_MAX_T_TIMES_BEAM);
+    NTB_TRY(check_device());
+    if (n_windows == 0) return NTB_OK;
+    // device address of the array, once per device with that device current (the symbol's name is only a host-side handle)
+    static int32_t *scratch_of[64] = {};
+    int dev = 0;
+    NTB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(NTB_EINVAL, "ntb_ctc_beam_search_noalloc: device ordinal %s%lld out of range", "", (long long)dev);
+    const size_t smem = sizeof(CtcBeamSmem) * CTC_WARPS;
+    if (!scratch_of[dev]) {
+        void *ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr)
+            return fail(NTB_ECUDA, "ntb_ctc_beam_search_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        NTB_CUDA(cudaFuncSetAttribute(k_ctc_beam_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        scratch_of[dev] = (int32_t *)ptr;
+    }
+    int64_t blocks = (int64_t)NTB_NOALLOC_SCRATCH_BYTES / per_block;       // the grid strides over the sequences
+    const int64_t want = ctc_beam_blocks(n_windows);
+    if (blocks > want) blocks = want;
+    k_ctc_beam_search<<<(unsigned)blocks, CTC_WARPS * 32, smem, (cudaStream_t)stream>>>(
+        logits_dev, len_dev, n_windows, T, C, beam_width, top_paths, merge_repeated ? 1 : 0, log_softmax ? 1 : 0,
+        scratch_of[dev], paths_dev, path_len_dev, log_prob_dev);
+    NTB_LAUNCH_CHECK();
+    return NTB_OK;
+}
+
 extern "C" int64_t ntb_gemm_workspace_bytes(int64_t M, int32_t N, int32_t K, int32_t impl) {
     if (impl == 0) return 256;
     Arena ar(nullptr, 0);
