@@ -96,24 +96,33 @@ struct TcParams {
 // Column statistics of one staged [32 rows][32 cols] fp32 tile (128-byte swizzled rows): lane = column; rows
 // [0, split) belong to the first window of the block (segment 0), [split, 32) to the next (segment 1); rows whose
 // bit in vmask is clear (padding rows of the 1x3 layout, rows past the end) are skipped.
+// A record is (S, M2) = (sum, sum of squared deviations from the SEGMENT's own mean) of <= 32 values, accumulated around a
+// pivot (the column's value in row 0 of the tile): S = n p + sum(v - p), M2 = sum((v - p)^2) - sum(v - p)^2 / n.  The
+// reference's tf.nn.moments is two-pass (network.py:339-349); sum / sum-of-squares records in fp32 lose
+// mean^2 / var * 6e-8 of the variance, which a channel with |mean| ~ 100 std turns into 1e-3 -- centred records do not,
+// and k_bn_finish merges them exactly (Chan et al.) in fp64.
 __device__ __forceinline__ void bn_partials(const uint8_t *buf, int lane, uint32_t vmask, int split, float2 *part,
                                             int64_t rec0, int N, int n) {
-    // <= 32 values per record: fp32 with four interleaved chains per segment (row i -> chain i & 3), folded in a
-    // fixed order -> bit-stable; the records are combined in fp64 (k_bn_finish)
+    // fp32 with four interleaved chains per segment (row i -> chain i & 3), folded in a fixed order -> bit-stable
     float s0[4] = {0, 0, 0, 0}, q0[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0}, q1[4] = {0, 0, 0, 0};
     const int cj = lane >> 2, ci = (lane & 3) << 2;
+    const float pv = *reinterpret_cast<const float *>(buf + (cj << 4) + ci);       // row 0
+    float n0 = 32.0f, n1 = 0.0f;
     if (vmask == 0xffffffffu && split == 32) {
         // common case (no window boundary, no padding row in the block): same chains, no per-row selects
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-            const float v = *reinterpret_cast<const float *>(buf + i * 128 + ((cj ^ (i & 7)) << 4) + ci);
+            const float v = *reinterpret_cast<const float *>(buf + i * 128 + ((cj ^ (i & 7)) << 4) + ci) - pv;
             s0[i & 3] += v;
             q0[i & 3] = fmaf(v, v, q0[i & 3]);
         }
     } else {
+        const uint32_t low = split >= 32 ? 0xffffffffu : ((1u << split) - 1u);
+        n0 = (float)__popc(vmask & low);
+        n1 = (float)__popc(vmask & ~low);
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-            const float f = *reinterpret_cast<const float *>(buf + i * 128 + ((cj ^ (i & 7)) << 4) + ci);
+            const float f = *reinterpret_cast<const float *>(buf + i * 128 + ((cj ^ (i & 7)) << 4) + ci) - pv;
             const float v = ((vmask >> i) & 1u) ? f : 0.0f;
             if (i < split) {
                 s0[i & 3] += v;
@@ -125,9 +134,12 @@ __device__ __forceinline__ void bn_partials(const uint8_t *buf, int lane, uint32
         }
     }
     if (n < N) {
-        part[rec0 * N + n] = make_float2((s0[0] + s0[1]) + (s0[2] + s0[3]), (q0[0] + q0[1]) + (q0[2] + q0[3]));
-        if (split < 32)
-            part[(rec0 + 1) * N + n] = make_float2((s1[0] + s1[1]) + (s1[2] + s1[3]), (q1[0] + q1[1]) + (q1[2] + q1[3]));
+        const float sa = (s0[0] + s0[1]) + (s0[2] + s0[3]), qa = (q0[0] + q0[1]) + (q0[2] + q0[3]);
+        part[rec0 * N + n] = make_float2(fmaf(n0, pv, sa), n0 > 0.0f ? fmaxf(qa - sa * sa / n0, 0.0f) : 0.0f);
+        if (split < 32) {
+            const float sb = (s1[0] + s1[1]) + (s1[2] + s1[3]), qb = (q1[0] + q1[1]) + (q1[2] + q1[3]);
+            part[(rec0 + 1) * N + n] = make_float2(fmaf(n1, pv, sb), n1 > 0.0f ? fmaxf(qb - sb * sb / n1, 0.0f) : 0.0f);
+        }
     }
 }
 

@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(BN_CH4 * BN_SLICES) k_bn_stats(const float *__
 }
 
 // Same affine from the partial sums the tcgen05 conv epilogue emitted (ntb_gemm_tc.cu, bn_partials): record
-// (block, seg) holds the fp32 (sum, sum of squares) of the rows of plane-row block `block` (32 rows) that belong to
+// (block, seg) holds the fp32 (sum, centred sum of squares) of the rows of plane-row block `block` (32 rows) that belong to
 // the block's first window (seg 0) or to the next one (seg 1); a window occupies Tp plane rows (T, or T + 2 in the
 // padded 1x3 layout whose padding rows were left out).  One thread per channel, records folded in fp64 in block order -> bit-stable.
 __global__ void __launch_bounds__(256) k_bn_finish(const float2 *__restrict__ part, int C, int T, int Tp,
@@ -258,31 +258,38 @@ __global__ void __launch_bounds__(256) k_bn_finish(const float2 *__restrict__ pa
     if (ch >= C) return;
     const int64_t wa = group_off[g], wb = group_off[g + 1];
     const int64_t n = (wb - wa) * T;
-    double ss = 0.0, qq = 0.0;
+    // records are (S_b, M2_b) of n_b <= 32 values (bn_partials): exact merge
+    //   M2 = sum M2_b + sum S_b^2 / n_b - (sum S_b)^2 / n        (fp64: the cancellation costs mean^2 / var * 1e-16)
+    double ss = 0.0, m2 = 0.0, sq = 0.0;
     if (wb > wa) {
         const int64_t b0 = (wa * Tp) >> 5, b1 = (wb * Tp - 1) >> 5;
         // first window of block b and the offset of the block's first row inside it, advanced without divisions
         int64_t w_first = (b0 << 5) / Tp;
         int rem = (int)((b0 << 5) - w_first * Tp);
+        const int lo = Tp != T ? 1 : 0, hi = lo + T;               // real rows of a window inside its Tp plane rows
         const float2 *rec = part + (b0 * 2) * C + ch;
         // unrolled: the (predicated) record loads of 8 blocks are in flight together; the fp64 fold order is unchanged
 #pragma unroll 8
         for (int64_t b = b0; b <= b1; ++b, rec += 2 * C) {
             const bool two = rem + 31 >= Tp;                       // the window changes inside this block (Tp >= 32)
             if (w_first >= wa && w_first < wb) {
+                const int e = rem + 32 < Tp ? rem + 32 : Tp;
+                const int nb = (e < hi ? e : hi) - (rem > lo ? rem : lo);
                 const float2 v = rec[0];
-                ss += (double)v.x; qq += (double)v.y;
+                if (nb > 0) { ss += (double)v.x; m2 += (double)v.y; sq += (double)v.x * (double)v.x / (double)nb; }
             }
             if (two && w_first + 1 >= wa && w_first + 1 < wb) {
+                const int e = rem + 32 - Tp;                       // rows [0, e) of the next window
+                const int nb = (e < hi ? e : hi) - lo;
                 const float2 v = rec[C];
-                ss += (double)v.x; qq += (double)v.y;
+                if (nb > 0) { ss += (double)v.x; m2 += (double)v.y; sq += (double)v.x * (double)v.x / (double)nb; }
             }
             rem += 32;
             if (rem >= Tp) { rem -= Tp; ++w_first; }
         }
     }
     const double mean = n > 0 ? ss / (double)n : 0.0;
-    double var = n > 0 ? qq / (double)n - mean * mean : 0.0;
+    double var = n > 0 ? (m2 + (sq - ss * ss / (double)n)) / (double)n : 0.0;
     var = var < 0.0 ? 0.0 : var;
     const float a = (1.0f / sqrtf((float)var + eps)) * scale[ch];
     aff_a[(int64_t)g * C + ch] = a;
