@@ -1275,6 +1275,10 @@ extern "C" int64_t ntb_event_detect_workspace_bytes(int64_t n_reads, int64_t tot
     return ar.off;
 }
 
+// warps the 8-reads-per-warp form needs to beat the 4-reads form (profiles/r02_ed_lanes_sweep.txt: 32 768 ... 131 072 reads
+// -> R = 8 at 25-26 G samples/s, ahead of 16 and 32; 16 384 and 8192 reads -> R = 4 at 20.7 / 15.8 G; 1024 reads -> one warp per read)
+static const int64_t ED_MIN_WARPS = 3000;
+
 extern "C" int ntb_event_detect(const double *raw_dev, const int64_t *read_off_host, int64_t n_reads, int64_t total_samples,
                                 double sample_rate, const int32_t *window_lengths, const double *thresholds,
                                 double peak_height, void *workspace_dev, int64_t workspace_bytes, int64_t capacity,
@@ -1302,19 +1306,39 @@ extern "C" int ntb_event_detect(const double *raw_dev, const int64_t *read_off_h
     // measured 26 ms vs 39 ms at 32 768 reads, but 78 ms vs 41 ms at 8192), else a warp per read
     // (NTB_ED_LANES=0/1 forces one form: A/B and tests)
     static const char *ed_env = getenv("NTB_ED_LANES");
-    const bool lanes = ed_env ? ed_env[0] == '1' : n_reads >= 20000;
-    const unsigned lgrid = (unsigned)cdiv(n_reads, 64);
-    if (lanes) k_ed_prefix_t<<<lgrid, 64, 0, st>>>(raw_dev, b.read_off, n_reads, b.sums, b.sumsqs);
-    else k_ed_prefix<<<wgrid, 128, 0, st>>>(raw_dev, b.read_off, n_reads, b.sums, b.sumsqs);
+    // reads per warp of the sequential stages: 0 = one warp per read, else R lanes of a warp walk R reads.  Default: the
+    // 8 when that still leaves ED_MIN_WARPS warps, 4 from 4000 reads (measured, tools/sweep_ed_lanes.sh); NTB_ED_LANES=0/1/4/8/16/32 forces
+    // a form (1 = 32): A/B runs and tests
+    int R = 0;
+    if (ed_env) {
+        R = atoi(ed_env);
+        R = R == 1 ? 32 : (R == 4 || R == 8 || R == 16 || R == 32 ? R : 0);
+    } else {
+        R = n_reads / 8 >= ED_MIN_WARPS ? 8 : (n_reads >= 4000 ? 4 : 0);
+    }
+    const unsigned lgrid = (unsigned)cdiv(n_reads, 2 * (R ? R : 1));
+    switch (R) {
+        case 32: k_ed_prefix_t<32><<<lgrid, 64, 0, st>>>(raw_dev, b.read_off, n_reads, b.sums, b.sumsqs); break;
+        case 16: k_ed_prefix_t<16><<<lgrid, 64, 0, st>>>(raw_dev, b.read_off, n_reads, b.sums, b.sumsqs); break;
+        case 8: k_ed_prefix_t<8><<<lgrid, 64, 0, st>>>(raw_dev, b.read_off, n_reads, b.sums, b.sumsqs); break;
+        case 4: k_ed_prefix_t<4><<<lgrid, 64, 0, st>>>(raw_dev, b.read_off, n_reads, b.sums, b.sumsqs); break;
+        default: k_ed_prefix<<<wgrid, 128, 0, st>>>(raw_dev, b.read_off, n_reads, b.sums, b.sumsqs);
+    }
     const int64_t per_read = total_samples / n_reads + 1;
     const unsigned ychunks = (unsigned)std::min<int64_t>(std::max<int64_t>(per_read / 4096, 1), 64);
     k_ed_tstat<<<dim3((unsigned)n_reads, ychunks), 256, 0, st>>>(b.sums, b.sumsqs, b.read_off, w_short, w_long, b.t_short, b.t_long);
-    if (lanes)
-        k_ed_peaks_t<<<lgrid, 64, 0, st>>>(b.t_short, b.t_long, b.read_off, n_reads, w_short, w_long, th_short, th_long,
-                                            peak_height, b.peaks, b.n_events);
-    else
-        k_ed_peaks<<<wgrid, 128, 0, st>>>(b.t_short, b.t_long, b.read_off, n_reads, w_short, w_long, th_short, th_long,
-                                          peak_height, b.peaks, b.n_events);
+#define NTB_ED_PEAKS(RR) k_ed_peaks_t<RR><<<lgrid, 64, 0, st>>>(b.t_short, b.t_long, b.read_off, n_reads, w_short, w_long, \
+                                                                th_short, th_long, peak_height, b.peaks, b.n_events)
+    switch (R) {
+        case 32: NTB_ED_PEAKS(32); break;
+        case 16: NTB_ED_PEAKS(16); break;
+        case 8: NTB_ED_PEAKS(8); break;
+        case 4: NTB_ED_PEAKS(4); break;
+        default:
+            k_ed_peaks<<<wgrid, 128, 0, st>>>(b.t_short, b.t_long, b.read_off, n_reads, w_short, w_long, th_short, th_long,
+                                              peak_height, b.peaks, b.n_events);
+    }
+#undef NTB_ED_PEAKS
     k_asm_read_offsets<<<1, 1024, 0, st>>>(b.n_events, b.n_events, n_reads, capacity, b.tmp_off, event_off_dev, status_dev);
     k_ed_events<<<(unsigned)n_reads, 256, 0, st>>>(b.sums, b.sumsqs, b.peaks, b.read_off, event_off_dev, sample_rate, capacity,
                                                    events_dev);

@@ -133,27 +133,29 @@ __global__ void __launch_bounds__(128) k_ed_peaks(const double *__restrict__ t_s
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// LANE-PER-READ forms of the two sequential stages.  One warp-instruction then advances 32 reads instead of one, which
+// LANE-PER-READ forms of the two sequential stages.  One warp-instruction then advances R reads instead of one, which
 // is what the sequential float64 chains need: the warp-per-read forms above spend ~60 issue slots per sample on a
-// single read.  A warp owns 32 consecutive reads; for every chunk of 32 samples it loads each read's chunk with one
-// coalesced access into a padded shared-memory tile, and each lane then walks its own read's row.
+// single read.  A warp owns R consecutive reads (R = 4, 8, 16 or 32: the host picks the largest R that still leaves
+// enough warps to fill the schedulers); for every chunk of 32 samples it loads each read's chunk with one coalesced
+// access of the whole warp into a padded shared-memory tile, and lanes 0 .. R-1 then walk their own read's row.
 constexpr int ED_TILE = 33;     // row pitch in doubles: lane r reading column k hits bank (33 r + k) % 32, conflict-free
 
+template <int R>
 __global__ void __launch_bounds__(64) k_ed_prefix_t(const double *__restrict__ raw, const int64_t *__restrict__ read_off,
                                                      int64_t n_reads, double *__restrict__ sums, double *__restrict__ sumsqs) {
-    __shared__ double tile[2][2][32 * ED_TILE];
+    __shared__ double tile[2][2][R * ED_TILE];
     const int wi = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t r0 = ((int64_t)blockIdx.x * 2 + wi) * 32;
+    const int64_t r0 = ((int64_t)blockIdx.x * 2 + wi) * R;
     if (r0 >= n_reads) return;
     double *tx = tile[wi][0], *tq = tile[wi][1];
-    const int64_t my_r = min(r0 + lane, n_reads - 1);
-    const int64_t my_a = read_off[my_r], my_n = r0 + lane < n_reads ? read_off[my_r + 1] - my_a : 0;
+    const int64_t my_r = min(r0 + (lane < R ? lane : R - 1), n_reads - 1);
+    const int64_t my_a = read_off[my_r], my_n = (lane < R && r0 + lane < n_reads) ? read_off[my_r + 1] - my_a : 0;
     int64_t longest = my_n;
 #pragma unroll
     for (int o = 16; o; o >>= 1) longest = max(longest, __shfl_xor_sync(0xffffffffu, longest, o));
     double s = 0.0, q = 0.0;
     for (int64_t base = 0; base < longest; base += 32) {
-        for (int rr = 0; rr < 32; ++rr) {                       // coalesced loads, one read at a time
+        for (int rr = 0; rr < R; ++rr) {                       // coalesced loads, one read at a time
             const int64_t a = __shfl_sync(0xffffffffu, my_a, rr), n = __shfl_sync(0xffffffffu, my_n, rr);
             if (base + lane < n) tx[rr * ED_TILE + lane] = raw[a + base + lane];
         }
@@ -167,7 +169,7 @@ __global__ void __launch_bounds__(64) k_ed_prefix_t(const double *__restrict__ r
             tq[lane * ED_TILE + k] = q;
         }
         __syncwarp();
-        for (int rr = 0; rr < 32; ++rr) {                       // coalesced stores
+        for (int rr = 0; rr < R; ++rr) {                       // coalesced stores
             const int64_t a = __shfl_sync(0xffffffffu, my_a, rr), n = __shfl_sync(0xffffffffu, my_n, rr);
             if (base + lane < n) {
                 sums[a + base + lane] = tx[rr * ED_TILE + lane];
@@ -178,17 +180,18 @@ __global__ void __launch_bounds__(64) k_ed_prefix_t(const double *__restrict__ r
     }
 }
 
+template <int R>
 __global__ void __launch_bounds__(64) k_ed_peaks_t(const double *__restrict__ t_short, const double *__restrict__ t_long,
                                                     const int64_t *__restrict__ read_off, int64_t n_reads, int w_short,
                                                     int w_long, double th_short, double th_long, double peak_height,
                                                     int32_t *__restrict__ peaks, int64_t *__restrict__ n_events) {
-    __shared__ double tile[2][2][32 * ED_TILE];
+    __shared__ double tile[2][2][R * ED_TILE];
     const int wi = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t r0 = ((int64_t)blockIdx.x * 2 + wi) * 32;
+    const int64_t r0 = ((int64_t)blockIdx.x * 2 + wi) * R;
     if (r0 >= n_reads) return;
     double *ts = tile[wi][0], *tl = tile[wi][1];
-    const int64_t my_r = min(r0 + lane, n_reads - 1);
-    const int64_t my_a = read_off[my_r], my_n = r0 + lane < n_reads ? read_off[my_r + 1] - my_a : 0;
+    const int64_t my_r = min(r0 + (lane < R ? lane : R - 1), n_reads - 1);
+    const int64_t my_a = read_off[my_r], my_n = (lane < R && r0 + lane < n_reads) ? read_off[my_r + 1] - my_a : 0;
     int64_t longest = my_n;
 #pragma unroll
     for (int o = 16; o; o >>= 1) longest = max(longest, __shfl_xor_sync(0xffffffffu, longest, o));
@@ -198,7 +201,7 @@ __global__ void __launch_bounds__(64) k_ed_peaks_t(const double *__restrict__ t_
     int32_t *out = peaks + my_a;
     int count = 0;
     for (int64_t base = 0; base < longest; base += 32) {
-        for (int rr = 0; rr < 32; ++rr) {
+        for (int rr = 0; rr < R; ++rr) {
             const int64_t a = __shfl_sync(0xffffffffu, my_a, rr), n = __shfl_sync(0xffffffffu, my_n, rr);
             if (base + lane < n) {
                 ts[rr * ED_TILE + lane] = t_short[a + base + lane];
@@ -238,7 +241,7 @@ __global__ void __launch_bounds__(64) k_ed_peaks_t(const double *__restrict__ t_
         }
         __syncwarp();
     }
-    if (r0 + lane < n_reads) n_events[r0 + lane] = my_n > 0 ? count + 1 : 0;
+    if (lane < R && r0 + lane < n_reads) n_events[r0 + lane] = my_n > 0 ? count + 1 : 0;
 }
 
 // K4: events from the edges (filters.py:180-204); one CTA per read; events [*, 4] = start, length, mean, stdv

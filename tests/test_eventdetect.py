@@ -113,9 +113,9 @@ def test_gpu_matches_reference_golden(lib, golden, p):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("lanes", ["0", "1"])
+@pytest.mark.parametrize("lanes", ["0", "1", "4", "8", "16"])
 def test_both_kernel_forms_agree_with_the_golden(golden, lanes):
-    """The warp-per-read and lane-per-read forms of the sequential stages (the library picks by read count; the switch is
+    """The warp-per-read and the R-reads-per-warp forms (R = 4, 8, 16, 32) of the sequential stages (the library picks by read count; the switch is
     read once per process, hence the subprocess)."""
     import subprocess
     import sys
