@@ -558,10 +558,12 @@ static int residual_forward(Ctx &cx, ntb_model *m, const LayerDev &ld, const flo
             // BN statistics ride in the GEMM epilogue (partials) and are folded per group right after
             float2 *part = ld.bn_scale[c] ? ws.bn_part : nullptr;
             // conv2b / conv2c: the producer's BN + ReLU + operand split run inside the GEMM (transform warps)
-            const bool fused = src_of[c] >= 0 && !expand && gemm_tc_conv_fused_supported(ld.convw[c], K, T, C);
+            // (a Cin = 1 layer's conv2b makes its operand from x itself: 4 bytes per row instead of padded planes)
+            const bool fused = src_of[c] >= 0 && gemm_tc_conv_fused_supported(ld.convw[c], K, T, C);
             int tp = taps[c] == 3 ? T + 2 : T;
             if (fused) {
-                NTB_TRY(gemm_tc_conv_fused(cx.st, A, K, rows, T, fa, fb, ws.win_group, 1, ld.convw[c], ys[c], C, &cx.launches, part));
+                NTB_TRY(gemm_tc_conv_fused(cx.st, A, K, rows, T, fa, fb, ws.win_group, 1, ld.convw[c], ys[c], C, &cx.launches, part,
+                                           expand ? in : nullptr));
                 tp = T;
             } else {
                 NTB_TRY(gemm_tc_conv(cx.st, expand ? in : A, K, rows, T, fa, fb, ws.win_group, src_of[c] >= 0, ld.convw[c],

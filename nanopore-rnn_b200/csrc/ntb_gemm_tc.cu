@@ -103,20 +103,53 @@ struct TcParams {
 // and k_bn_finish merges them exactly (Chan et al.) in fp64.
 __device__ __forceinline__ void bn_partials(const uint8_t *buf, int lane, uint32_t vmask, int split, float2 *part,
                                             int64_t rec0, int N, int n) {
-    // fp32 with four interleaved chains per segment (row i -> chain i & 3), folded in a fixed order -> bit-stable
-    float s0[4] = {0, 0, 0, 0}, q0[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0}, q1[4] = {0, 0, 0, 0};
+    // fp32, fixed order -> bit-stable
     const int cj = lane >> 2, ci = (lane & 3) << 2;
     const float pv = *reinterpret_cast<const float *>(buf + (cj << 4) + ci);       // row 0
     float n0 = 32.0f, n1 = 0.0f;
+    float sa, qa, sb = 0.0f, qb = 0.0f;
     if (vmask == 0xffffffffu && split == 32) {
-        // common case (no window boundary, no padding row in the block): same chains, no per-row selects
+        // common case (no window boundary, no padding row in the block): rows in pairs through the packed f32x2 pipe
+        // (three instructions per two values), two interleaved chains of pairs
+        float2 s2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)}, q2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+        const float2 np2 = make_float2(-pv, -pv);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-            const float v = *reinterpret_cast<const float *>(buf + i * 128 + ((cj ^ (i & 7)) << 4) + ci) - pv;
-            s0[i & 3] += v;
-            q0[i & 3] = fmaf(v, v, q0[i & 3]);
+        for (int i = 0; i < 32; i += 2) {
+            const float2 v = make_float2(*reinterpret_cast<const float *>(buf + i * 128 + ((cj ^ (i & 7)) << 4) + ci),
+                                         *reinterpret_cast<const float *>(buf + (i + 1) * 128 + ((cj ^ ((i + 1) & 7)) << 4) + ci));
+            const float2 d = __fadd2_rn(v, np2);
+            s2[(i >> 1) & 1] = __fadd2_rn(s2[(i >> 1) & 1], d);
+            q2[(i >> 1) & 1] = __ffma2_rn(d, d, q2[(i >> 1) & 1]);
         }
+        sa = (s2[0].x + s2[0].y) + (s2[1].x + s2[1].y);
+        qa = (q2[0].x + q2[0].y) + (q2[1].x + q2[1].y);
+    } else if (vmask == 0xffffffffu) {
+        // a window boundary inside the block (with T = 100 every third block): the same packed loop over ALL rows plus, for
+        // the pairs in front of the boundary (warp-uniform predicate), segment 0 on its own; segment 1 = all - segment 0
+        // (sums of deviations from the pivot: the subtraction costs an ulp of a small number)
+        float2 s2 = make_float2(0.f, 0.f), q2 = make_float2(0.f, 0.f), t2 = make_float2(0.f, 0.f), u2 = make_float2(0.f, 0.f);
+        const float2 np2 = make_float2(-pv, -pv);
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+            const float2 v = make_float2(*reinterpret_cast<const float *>(buf + i * 128 + ((cj ^ (i & 7)) << 4) + ci),
+                                         *reinterpret_cast<const float *>(buf + (i + 1) * 128 + ((cj ^ ((i + 1) & 7)) << 4) + ci));
+            const float2 d = __fadd2_rn(v, np2);
+            s2 = __fadd2_rn(s2, d);
+            q2 = __ffma2_rn(d, d, q2);
+            if (i < split) {
+                const float2 d0 = make_float2(d.x, i + 1 < split ? d.y : 0.0f);
+                t2 = __fadd2_rn(t2, d0);
+                u2 = __ffma2_rn(d0, d0, u2);
+            }
+        }
+        n0 = (float)split;
+        n1 = (float)(32 - split);
+        sa = t2.x + t2.y; qa = u2.x + u2.y;
+        sb = (s2.x + s2.y) - sa; qb = fmaxf((q2.x + q2.y) - qa, 0.0f);
     } else {
+        // padded plane rows / rows past the end in the block (the layouts without the fused operand transform): per-row
+        // selects, four interleaved chains per segment (row i -> chain i & 3)
+        float s0[4] = {0, 0, 0, 0}, q0[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0}, q1[4] = {0, 0, 0, 0};
         const uint32_t low = split >= 32 ? 0xffffffffu : ((1u << split) - 1u);
         n0 = (float)__popc(vmask & low);
         n1 = (float)__popc(vmask & ~low);
@@ -132,14 +165,13 @@ __device__ __forceinline__ void bn_partials(const uint8_t *buf, int lane, uint32
                 q1[i & 3] = fmaf(v, v, q1[i & 3]);
             }
         }
+        sa = (s0[0] + s0[1]) + (s0[2] + s0[3]); qa = (q0[0] + q0[1]) + (q0[2] + q0[3]);
+        sb = (s1[0] + s1[1]) + (s1[2] + s1[3]); qb = (q1[0] + q1[1]) + (q1[2] + q1[3]);
     }
     if (n < N) {
-        const float sa = (s0[0] + s0[1]) + (s0[2] + s0[3]), qa = (q0[0] + q0[1]) + (q0[2] + q0[3]);
         part[rec0 * N + n] = make_float2(fmaf(n0, pv, sa), n0 > 0.0f ? fmaxf(qa - sa * sa / n0, 0.0f) : 0.0f);
-        if (split < 32) {
-            const float sb = (s1[0] + s1[1]) + (s1[2] + s1[3]), qb = (q1[0] + q1[1]) + (q1[2] + q1[3]);
+        if (split < 32)
             part[(rec0 + 1) * N + n] = make_float2(fmaf(n1, pv, sb), n1 > 0.0f ? fmaxf(qb - sb * sb / n1, 0.0f) : 0.0f);
-        }
     }
 }
 
@@ -675,6 +707,8 @@ struct ConvFusedParams {
     const float *aff_a, *aff_b;
     const int32_t *win_group;
     float2 *bn_part;
+    const float *xs;   // != null: the producer conv had ONE input channel and is folded into (aff_a, aff_b) (k_k1_affine): the
+                       // operand is relu(xs[row] * a[g][c] + b[g][c]) -- no raw tile exists, the transform warps make it from xs
     int abl;       // timing ablations (NTB_CF_ABL): 1 = no BN partials, 2 = no output store, 4 = transform warps skip their work
     int l2pf;      // the producer pulls the NEXT tile's raw rows into L2 while this tile runs: only one or two 33 KB raw
                    // stages are in flight per SM, so every k-block otherwise waits a full DRAM latency
@@ -725,15 +759,17 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
             int rs = 0, os = 0; uint32_t rph = 0, oph = 0;
             for (int64_t it = first; it < pairs; it += step) {
                 const int64_t m_tile = it * 2 + rank;
-                if (p.l2pf && it + step < pairs) {
+                if (p.l2pf && !p.xs && it + step < pairs) {
                     const int r2 = (int)(((it + step) * 2 + rank) * BM) - left;
                     for (int kb = 0; kb < p.k_blocks; ++kb) tma_prefetch_2d(&map_raw, kb * BK, r2);
                 }
                 for (int kb = 0; kb < p.k_blocks; ++kb) {
-                    mbar_wait_backoff<128>(&raw_empty[rs], rph ^ 1, 100);
-                    mbar_expect_tx(&raw_full[rs], (uint32_t)(raw_rows * BK * 4));
-                    tma_load_2d(raw_base + rs * CF_RAW_STAGE, &map_raw, &raw_full[rs], kb * BK, (int)(m_tile * BM) - left);
-                    if (++rs == CF_RAW_STAGES) { rs = 0; rph ^= 1; }
+                    if (!p.xs) {
+                        mbar_wait_backoff<128>(&raw_empty[rs], rph ^ 1, 100);
+                        mbar_expect_tx(&raw_full[rs], (uint32_t)(raw_rows * BK * 4));
+                        tma_load_2d(raw_base + rs * CF_RAW_STAGE, &map_raw, &raw_full[rs], kb * BK, (int)(m_tile * BM) - left);
+                        if (++rs == CF_RAW_STAGES) { rs = 0; rph ^= 1; }
+                    }
                     for (int tap = 0; tap < p.taps; ++tap) {
                         mbar_wait_backoff<128>(&op_empty[os], oph ^ 1, 101);
                         uint8_t *s = op_base + os * op_stage_bytes + 2 * A_TILE_BYTES;
@@ -800,8 +836,19 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
                     tpos[i] = -1000; grp[i] = 0;
                 }
             }
+            float xv[RPT][3];                                     // scalar-input form: x of the row's taps, once per tile
+            if (p.xs) {
+#pragma unroll
+                for (int i = 0; i < RPT; ++i)
+#pragma unroll
+                    for (int tap = 0; tap < 3; ++tap) {
+                        const int64_t grow = m_tile * BM + tw * (4 * RPT) + (i >> 1) * 8 + (i & 1) * 2 + rlane + tap - left;
+                        const int tt = tpos[i] + tap - left;
+                        xv[i][tap] = (tap < p.taps && tt >= 0 && tt < p.T) ? __ldg(p.xs + grow) : 0.0f;
+                    }
+            }
             for (int kb = 0; kb < p.k_blocks; ++kb) {
-                mbar_wait(&raw_full[rs], rph, 200);
+                if (!p.xs) mbar_wait(&raw_full[rs], rph, 200);
                 const uint8_t *raw = raw_base + rs * CF_RAW_STAGE;
                 const int c = kb * BK + j * 4;                    // first of this thread's channels (second group: c + 32)
                 int gcur = -1;                                    // (a, b) of group gcur for the 8 channels stay in registers
@@ -816,9 +863,14 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
                         const int tt = tpos[i] + tap - left;
                         float v[8];
                         if (tt >= 0 && tt < p.T) {                // same window as the output row: SAME padding otherwise
-                            const float4 x0 = *reinterpret_cast<const float4 *>(raw + (row + tap) * (BK * 4) + j * 16);
-                            const float4 x1 = *reinterpret_cast<const float4 *>(raw + (row + tap) * (BK * 4) + 128 + j * 16);
-                            v[0] = x0.x; v[1] = x0.y; v[2] = x0.z; v[3] = x0.w; v[4] = x1.x; v[5] = x1.y; v[6] = x1.z; v[7] = x1.w;
+                            if (p.xs) {
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) v[q] = tap == 0 ? xv[i][0] : (tap == 1 ? xv[i][1] : xv[i][2]);
+                            } else {
+                                const float4 x0 = *reinterpret_cast<const float4 *>(raw + (row + tap) * (BK * 4) + j * 16);
+                                const float4 x1 = *reinterpret_cast<const float4 *>(raw + (row + tap) * (BK * 4) + 128 + j * 16);
+                                v[0] = x0.x; v[1] = x0.y; v[2] = x0.z; v[3] = x0.w; v[4] = x1.x; v[5] = x1.y; v[6] = x1.z; v[7] = x1.w;
+                            }
                             if (p.aff_a) {
                                 if (grp[i] != gcur) {
                                     gcur = grp[i];
@@ -855,9 +907,11 @@ k_conv_fused(const __grid_constant__ CUtensorMap map_raw, const __grid_constant_
                     if (lane == 0) { if (rank == 0) mbar_arrive(&op_full[os]); else mbar_arrive_cluster(&op_full[os], 0); }
                     if (++os == CF_OP_STAGES) { os = 0; oph ^= 1; }
                 }
-                __syncwarp();                                     // every lane is done reading the raw stage
-                if (lane == 0) mbar_arrive(&raw_empty[rs]);
-                if (++rs == CF_RAW_STAGES) { rs = 0; rph ^= 1; }
+                if (!p.xs) {
+                    __syncwarp();                                 // every lane is done reading the raw stage
+                    if (lane == 0) mbar_arrive(&raw_empty[rs]);
+                    if (++rs == CF_RAW_STAGES) { rs = 0; rph ^= 1; }
+                }
             }
         }
     } else if (warp >= 4) {
@@ -1639,9 +1693,10 @@ bool gemm_tc_conv_fused_supported(const GemmWeights &w, int K, int T, int ldo) {
 
 int gemm_tc_conv_fused(cudaStream_t st, const float *y, int K, int64_t rows, int T, const float *aff_a,
                        const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
-                       int ldo, int64_t *launches, float2 *bn_part) {
+                       int ldo, int64_t *launches, float2 *bn_part, const float *x_scalar) {
+    if (x_scalar) y = out;      // no raw activation exists: the tensor map only needs a valid base, it is never used
     if (!gemm_tc_conv_fused_supported(w, K, T, ldo) || rows % T || (reinterpret_cast<uintptr_t>(y) & 15) ||
-        (reinterpret_cast<uintptr_t>(out) & 15) || (aff_a && !win_group))
+        (reinterpret_cast<uintptr_t>(out) & 15) || (aff_a && !win_group) || (x_scalar && !aff_a))
         return fail(NTB_EINVAL, "tcgen05 fused conv: operand not supported (rows %s%lld, K %lld)", "", (long long)rows,
                     (long long)K);
     CUtensorMap m_raw, mb_hi, mb_lo, mo;
@@ -1652,6 +1707,7 @@ int gemm_tc_conv_fused(cudaStream_t st, const float *y, int K, int64_t rows, int
     ConvFusedParams p{};
     p.m_tiles = (rows + BM - 1) / BM; p.rows = rows; p.N = w.N; p.K = K; p.taps = w.taps; p.T = T;
     p.k_blocks = K / BK; p.relu = relu_in; p.aff_a = aff_a; p.aff_b = aff_b; p.win_group = win_group; p.bn_part = bn_part;
+    p.xs = x_scalar;
     // opt-in: measured neutral to slightly slower (conv stage 56.5 vs 55.8 ms per 65 536 windows)
     static const int cf_l2pf = ntb_env("NTB_CF_L2PF") ? atoi(ntb_env("NTB_CF_L2PF")) : 0;
     p.l2pf = cf_l2pf;

@@ -70,7 +70,9 @@ int64_t gemm_tc_bn_part_elems(const GemmScratch &gs, int C);
 bool gemm_tc_conv_fused_supported(const GemmWeights &w, int K, int T, int ldo);
 int gemm_tc_conv_fused(cudaStream_t st, const float *y, int K, int64_t rows, int T, const float *aff_a,
                        const float *aff_b, const int32_t *win_group, int relu_in, const GemmWeights &w, float *out,
-                       int ldo, int64_t *launches, float2 *bn_part);
+                       int ldo, int64_t *launches, float2 *bn_part, const float *x_scalar = nullptr);
+// x_scalar != null: the producer was a conv of ONE input channel folded into its BN affine (k_k1_affine): the operand is
+// relu(x_scalar[row] * aff_a[g][c] + aff_b[g][c]), made by the transform warps from 4 bytes per row; `y` is ignored.
 // residual_layer tail relu(bn?(branch1) + bn(conv2c)) written as fp32 (`out`, may be null) and/or straight into the
 // operand planes of the next GEMM: layout 0 = none, 1 = plain rows (next 1x1 convs), 2 = time-major tiles (projection),
 // 3 = the fused BLSTM kernel's k-group-major tiles (gemm_tc_split_kmajor's layout; `kmajor_hi/lo` name the planes).

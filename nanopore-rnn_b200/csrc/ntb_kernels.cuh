@@ -249,6 +249,13 @@ __global__ void __launch_bounds__(BN_CH4 * BN_SLICES) k_bn_stats(const float *__
 // (block, seg) holds the fp32 (sum, centred sum of squares) of the rows of plane-row block `block` (32 rows) that belong to
 // the block's first window (seg 0) or to the next one (seg 1); a window occupies Tp plane rows (T, or T + 2 in the
 // padded 1x3 layout whose padding rows were left out).  One thread per channel, records folded in fp64 in block order -> bit-stable.
+// 1 / nb for 1 <= nb <= 32 without an fp64 division: float reciprocal + one Newton step (relative error < 1e-14, exact for
+// powers of two; deterministic)
+__device__ __forceinline__ double bn_rcp(int nb) {
+    const double r0 = (double)__frcp_rn((float)nb);
+    return r0 * (2.0 - (double)nb * r0);
+}
+
 __global__ void __launch_bounds__(256) k_bn_finish(const float2 *__restrict__ part, int C, int T, int Tp,
                                                    const int32_t *__restrict__ group_off,
                                                    const float *__restrict__ scale, const float *__restrict__ offset,
@@ -276,13 +283,13 @@ __global__ void __launch_bounds__(256) k_bn_finish(const float2 *__restrict__ pa
                 const int e = rem + 32 < Tp ? rem + 32 : Tp;
                 const int nb = (e < hi ? e : hi) - (rem > lo ? rem : lo);
                 const float2 v = rec[0];
-                if (nb > 0) { ss += (double)v.x; m2 += (double)v.y; sq += (double)v.x * (double)v.x / (double)nb; }
+                if (nb > 0) { ss += (double)v.x; m2 += (double)v.y; sq = fma((double)v.x * (double)v.x, bn_rcp(nb), sq); }
             }
             if (two && w_first + 1 >= wa && w_first + 1 < wb) {
                 const int e = rem + 32 - Tp;                       // rows [0, e) of the next window
                 const int nb = (e < hi ? e : hi) - lo;
                 const float2 v = rec[C];
-                if (nb > 0) { ss += (double)v.x; m2 += (double)v.y; sq += (double)v.x * (double)v.x / (double)nb; }
+                if (nb > 0) { ss += (double)v.x; m2 += (double)v.y; sq = fma((double)v.x * (double)v.x, bn_rcp(nb), sq); }
             }
             rem += 32;
             if (rem >= Tp) { rem -= Tp; ++w_first; }
