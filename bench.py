@@ -648,12 +648,15 @@ def bench_reads(cx, args):
         for _ in range(2):
             e2e_step(False)
         cx.barrier()
+        sampler_e = ClockSampler(cx.local)       # the cap moves the clock with the board's temperature: say what this leg saw
+        sampler_e.start()
         t0 = time.perf_counter()
         for _ in range(steps):
             e2e_step(True)
         torch.cuda.synchronize()
         cx.barrier()
         dt = cx.max_over_ranks(time.perf_counter() - t0) / steps
+        clocks_e = sampler_e.finish()
         d2h = sum(len(c) for c in called[0]) + 16 * len(lengths) + 8 if rank == 0 else 0
         e2e = {"value": total_samples / dt, "unit": UNIT, "ms_per_step": dt * 1e3,
                "h2d_bytes_per_step": int(cx.sum_over_ranks(host.nbytes + 16 * (plan.n_reads + 1) + 4 * len(plan.group_off))),
@@ -663,6 +666,7 @@ def bench_reads(cx, args):
                "gather_ms_per_step": cx.all_values(gather_s[0])[0] / steps * 1e3,
                "gather_ms_per_step_min_rank": min(cx.all_values(gather_s[0])) / steps * 1e3,
                "enqueue_ms_per_step": cx.max_over_ranks(enq_s[0]) / steps * 1e3,
+               "sm_mhz": clocks_e.get("sm_mhz"), "reasons": clocks_e.get("reasons"),
                "called_bases_per_step": int(sum(len(c) for c in called[0])) if rank == 0 else None,
                "what": "pinned int16 samples -> H2D -> z-score/windows -> forward -> consensus assembly -> NCCL gather "
                        "of the called reads to rank 0 -> one D2H -> original read order"}

@@ -178,12 +178,16 @@ __device__ __forceinline__ void bn_partials(const uint8_t *buf, int lane, uint32
 // CG = 1: one CTA per tile (M = 128).  CG = 2: CTA pair (cluster of 2, tcgen05 cta_group::2, M = 256): each CTA loads
 // its own 128 A rows and HALF of the B tile, the leader issues the MMAs for both SMs, so the B operand
 // traffic per output halves -- these GEMMs are operand-bandwidth bound (hi + lo planes of both operands).
-template <int CG>
+// LSTM = true: the per-timestep mode of gemm_tc_lstm_layer (its own instantiation, so that the cell-update epilogue and its
+// prefetch registers do not weigh on the conv / projection GEMMs)
+template <int CG, bool LSTM>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
           const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
           const __grid_constant__ CUtensorMap map_out, const __grid_constant__ CUtensorMap map_out2, const TcParams p) {
     using namespace ptx;
+    const int lstm_kbx = LSTM ? p.lstm_kbx : 0;
+    const bool a_kmajor = LSTM && p.a_kmajor;
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint64_t full_bar[8], empty_bar[8], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_base_smem;
@@ -225,8 +229,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&map_a_hi); prefetch_tmap(&map_a_lo); prefetch_tmap(&map_b_hi); prefetch_tmap(&map_b_lo);
-        if (p.tma_store || p.xproj_tma || p.lstm_kbx) prefetch_tmap(&map_out);
-        if (p.n_split > 0 || p.lstm_kbx) prefetch_tmap(&map_out2);
+        if (p.tma_store || p.xproj_tma || lstm_kbx) prefetch_tmap(&map_out);
+        if (p.n_split > 0 || lstm_kbx) prefetch_tmap(&map_out2);
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
@@ -265,7 +269,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
             }
             for (int64_t it = 0; item(it, mg, n_tile); ++it) {
                 const int64_t m_tile = mg * CG + rank;
-                const int dir_rows = (p.lstm_H > 0 && m_tile >= p.lstm_mt_dir) ? p.Np : 0;   // W_hh of the bw direction
+                const int dir_rows = (LSTM && m_tile >= p.lstm_mt_dir) ? p.Np : 0;   // W_hh of the bw direction
                 if (p.l2pf) {
                     int64_t mg2; int nt2;
                     if (item(it + 1, mg2, nt2) && mg2 != mg) {
@@ -299,7 +303,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                         } else {
                             // both CTAs' bytes are credited to the LEADER's full barrier
                             if (rank == 0) mbar_expect_tx(&full_bar[stage], (uint32_t)(2 * stage_bytes));
-                            const bool xk = p.lstm_kbx > 0 && kb < p.lstm_kbx;      // an x_t k-block of the fused step GEMM
+                            const bool xk = lstm_kbx > 0 && kb < lstm_kbx;      // an x_t k-block of the fused step GEMM
                             int xrow = 0;
                             if (xk) {
                                 const int dirx = m_tile >= p.lstm_mt_dir ? 1 : 0;
@@ -307,12 +311,12 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                                 xrow = (int)((tl * p.T + (dirx ? p.T - 1 - p.lstm_s : p.lstm_s)) * BM);
                             }
                             if (xk) tma_load_2d_pair(s, &map_out, &full_bar[stage], kb * BK, xrow);
-                            else if (p.a_kmajor) tma_load_3d_pair(s, &map_a_hi, &full_bar[stage], 0, row0, (kb - p.lstm_kbx) * (BK / 8));
+                            else if (a_kmajor) tma_load_3d_pair(s, &map_a_hi, &full_bar[stage], 0, row0, (kb - lstm_kbx) * (BK / 8));
                             else tma_load_2d_pair(s, &map_a_hi, &full_bar[stage], kb * BK, row0);
                             tma_load_2d_pair(s + A_TILE_BYTES, &map_b_hi, &full_bar[stage], kb * BK, brow0);
                             if (p.passes == 3) {
                                 if (xk) tma_load_2d_pair(s + A_TILE_BYTES + b_tile_bytes, &map_out2, &full_bar[stage], kb * BK, xrow);
-                                else if (p.a_kmajor) tma_load_3d_pair(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], 0, row0, (kb - p.lstm_kbx) * (BK / 8));
+                                else if (a_kmajor) tma_load_3d_pair(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], 0, row0, (kb - lstm_kbx) * (BK / 8));
                                 else
                                 tma_load_2d_pair(s + A_TILE_BYTES + b_tile_bytes, &map_a_lo, &full_bar[stage], kb * BK, row0);
                                 tma_load_2d_pair(s + 2 * A_TILE_BYTES + b_tile_bytes, &map_b_lo, &full_bar[stage], kb * BK, brow0);
@@ -359,7 +363,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                             } else if (p.passes == 2) {     // a_lo's slot holds B'' here
                                 umma_f16(d_tmem, desc_advance_k16(a_hi, k), desc_advance_k16(a_lo, k), idesc, 1);
                             }
-                        } else if (p.a_kmajor && kb >= p.lstm_kbx) {
+                        } else if (a_kmajor && kb >= lstm_kbx) {
                             // A tile = [8 K groups][128 rows][8]: k16 step k starts at group 2k; LBO = one group (2 KB), SBO = 128 B
                             const uint64_t ah = smem_desc_nosw(s + (uint32_t)k * 4096u, 2048, 128);
                             const uint64_t al = smem_desc_nosw(s + A_TILE_BYTES + b_tile_bytes + (uint32_t)k * 4096u, 2048, 128);
@@ -421,7 +425,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                 cpre[0] = cgp[0];
                 if (nuf == 8) cpre[1] = cgp[BM];
             };
-            if (p.lstm_H > 0) {
+            if (LSTM) {
                 l_dir = m_tile >= p.lstm_mt_dir ? 1 : 0;
                 l_w = prow - l_dir * p.lstm_Mp;
                 l_live = l_w < p.lstm_n;
@@ -502,7 +506,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                         bulk_commit_group();
                     }
                     if (bn_dst) bn_partials(buf, lane, bn_vmask, bn_split, bn_dst, (m_tile * 4 + q) * 2, bn_N, nb - n_org + lane);
-                } else if (p.lstm_H > 0) {
+                } else if (LSTM) {
                     // thread = one window of one direction; this chunk = 8 hidden units x (i, j, f, o).  Every global access
                     // of a warp is contiguous: projected gates unit-major ([..][unit][128 windows] float4, the layout the
                     // projection's epilogue writes), cell state [..][unit / 4][128][4], h planes k-group-major -- with
@@ -1436,14 +1440,16 @@ int do_launch(cudaStream_t st, const CUtensorMap &ma_hi, const CUtensorMap &ma_l
     const size_t smem = (size_t)p.stages * stage_bytes + (p.bstat ? p.k_blocks * 2 * b_tile_bytes : 0) + 1024 + p.epi_bytes;
     static bool attr_set = false;
     if (!attr_set) {
-        NTB_CUDA(cudaFuncSetAttribute(k_gemm_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET + 1024 + EPI_STAGE_BYTES));
-        NTB_CUDA(cudaFuncSetAttribute(k_gemm_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET + 1024 + EPI_STAGE_BYTES));
+        NTB_CUDA(cudaFuncSetAttribute(k_gemm_tc<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET + 1024 + EPI_STAGE_BYTES));
+        NTB_CUDA(cudaFuncSetAttribute(k_gemm_tc<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET + 1024 + EPI_STAGE_BYTES));
+        NTB_CUDA(cudaFuncSetAttribute(k_gemm_tc<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET + 1024 + EPI_STAGE_BYTES));
         attr_set = true;
     }
     if (cg == 1) {
         const int64_t tiles = p.m_tiles * p.n_tiles;
         const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-        k_gemm_tc<1><<<grid, TC_THREADS, smem, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, mo, mo2 ? *mo2 : mo, p);
+        if (p.lstm_H > 0) return fail(NTB_EINVAL, "tcgen05 GEMM: the LSTM timestep mode needs the CTA-pair kernel%s", "");
+        k_gemm_tc<1, false><<<grid, TC_THREADS, smem, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, mo, mo2 ? *mo2 : mo, p);
     } else {
         const int64_t items = ((p.m_tiles + 1) / 2) * p.n_tiles;            // pairs of M tiles x N tiles
         int64_t pairs_hw = sm_count() / 2;
@@ -1457,7 +1463,8 @@ int do_launch(cudaStream_t st, const CUtensorMap &ma_hi, const CUtensorMap &ma_l
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr; cfg.numAttrs = 1;
-        NTB_CUDA(cudaLaunchKernelEx(&cfg, k_gemm_tc<2>, ma_hi, ma_lo, mb_hi, mb_lo, mo, mo2 ? *mo2 : mo, p));
+        if (p.lstm_H > 0) NTB_CUDA(cudaLaunchKernelEx(&cfg, k_gemm_tc<2, true>, ma_hi, ma_lo, mb_hi, mb_lo, mo, mo2 ? *mo2 : mo, p));
+        else NTB_CUDA(cudaLaunchKernelEx(&cfg, k_gemm_tc<2, false>, ma_hi, ma_lo, mb_hi, mb_lo, mo, mo2 ? *mo2 : mo, p));
     }
     if (launches) ++*launches;
     NTB_LAUNCH_CHECK();
