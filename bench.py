@@ -633,13 +633,21 @@ def bench_reads(cx, args):
 
         enq_s = [0.0]
 
+        gpu_ms = [0.0]
+        gpu_steps = []
+        ge0, ge1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
         def e2e_step(timed):
             t_a = time.perf_counter()
+            ge0.record()
             raw_e.copy_(host_t, non_blocking=True)
             cons, cons_off, status = job.run_device(raw_e, plan)
+            ge1.record()
             if timed:
                 enq_s[0] += time.perf_counter() - t_a          # host time to enqueue the chain (the assembly's table upload waits for the forward)
                 torch.cuda.current_stream(dev).synchronize()
+                gpu_ms[0] += ge0.elapsed_time(ge1)             # device time of copy + chain inside this step
+                gpu_steps.append(round(ge0.elapsed_time(ge1), 1))
                 t = time.perf_counter()
             called[0] = gather_consensus(cons, cons_off, plan.n_reads, read_ids, len(lengths), rank, world, dev)
             if timed:
@@ -651,12 +659,17 @@ def bench_reads(cx, args):
         sampler_e = ClockSampler(cx.local)       # the cap moves the clock with the board's temperature: say what this leg saw
         sampler_e.start()
         t0 = time.perf_counter()
+        step_s = []
         for _ in range(steps):
+            t_s = time.perf_counter()
             e2e_step(True)
+            step_s.append(time.perf_counter() - t_s)
         torch.cuda.synchronize()
         cx.barrier()
         dt = cx.max_over_ranks(time.perf_counter() - t0) / steps
         clocks_e = sampler_e.finish()
+        if os.environ.get("NTB_BENCH_DEBUG"):
+            sys.stderr.write("e2e step wall ms: %s device ms: %s\n" % ([round(v * 1e3, 1) for v in step_s], gpu_steps))
         d2h = sum(len(c) for c in called[0]) + 16 * len(lengths) + 8 if rank == 0 else 0
         e2e = {"value": total_samples / dt, "unit": UNIT, "ms_per_step": dt * 1e3,
                "h2d_bytes_per_step": int(cx.sum_over_ranks(host.nbytes + 16 * (plan.n_reads + 1) + 4 * len(plan.group_off))),
@@ -667,6 +680,7 @@ def bench_reads(cx, args):
                "gather_ms_per_step_min_rank": min(cx.all_values(gather_s[0])) / steps * 1e3,
                "enqueue_ms_per_step": cx.max_over_ranks(enq_s[0]) / steps * 1e3,
                "sm_mhz": clocks_e.get("sm_mhz"), "reasons": clocks_e.get("reasons"),
+               "device_ms_per_step": cx.max_over_ranks(gpu_ms[0]) / steps,
                "called_bases_per_step": int(sum(len(c) for c in called[0])) if rank == 0 else None,
                "what": "pinned int16 samples -> H2D -> z-score/windows -> forward -> consensus assembly -> NCCL gather "
                        "of the called reads to rank 0 -> one D2H -> original read order"}
