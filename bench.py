@@ -46,6 +46,12 @@ WORKLOADS = {
     "stress_blstm256": {"graph": "CrossEntropy", "T": 100, "batch": 0, "n_classes": 1025, "len_x": 12, "windows": 262144,
                         "weights_seed": 32, "what": "BASELINE configs[4]: 5 x BLSTM(256), CrossEntropy C=1025, len_x 12, "
                                                     "synthetic N(0,1) windows"},
+    # SURVEY.md 8(d), the Chiron shape: chiron/chiron/entry.py:32-33 (segment_len 300, batch_size 1100); same layer stack,
+    # 5 classes (4 bases + blank); BN moments over a batch of 1100 segments (330 000 rows per group)
+    "chiron_T300": {"graph": "CtcLoss", "T": 300, "batch": 1100, "n_classes": 5, "len_x": 1, "windows": 349800,
+                    "weights_seed": 301, "net": "run_nanotensor",
+                    "what": "Chiron shape (SURVEY 8d): 3 residual(256) + 3 BLSTM(100) + chiron_fnn, T = 300, CTC C=5, BN "
+                            "groups of 1100 windows, synthetic windows (use --step 300 for non-overlapping windows)"},
 }
 WL = dict(WORKLOADS["run_nanotensor"], name="run_nanotensor")
 T, BATCH, NCLASS = WL["T"], WL["batch"], WL["n_classes"]
@@ -146,7 +152,7 @@ def make_workload(n_windows, seed):
 
 def network_and_weights():
     from nanopore_rnn_b200 import synthetic as syn
-    net = syn.NETWORKS[WL["name"]]
+    net = syn.NETWORKS[WL.get("net", WL["name"])]
     return net, syn.random_weights(net, WL["len_x"], NCLASS, seed=WL["weights_seed"], graph=WL["graph"])
 
 
