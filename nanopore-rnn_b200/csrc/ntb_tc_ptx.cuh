@@ -445,18 +445,18 @@ __device__ __forceinline__ void split_op16(float x, op16_t &hi, op16_t &lo) {
 }
 
 // Same split for 8 values at once with packed conversions (F2FP packs two floats per instruction): 16-byte hi and lo
-// chunks ready for a uint4 store.  hi saturates at the fp16 range (upper clamp only when the values are >= 0).
+// chunks ready for a uint4 store.  hi saturates at the fp16 range (NONNEG is kept for the call sites: it no longer matters).
 template <bool NONNEG = false>
 __device__ __forceinline__ void split_op16x8(const float (&v)[8], uint4 &hi, uint4 &lo) {
     uint32_t h[4], l[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        float a = fminf(v[2 * i], 65504.0f), b = fminf(v[2 * i + 1], 65504.0f);
-        if (!NONNEG) { a = fmaxf(a, -65504.0f); b = fmaxf(b, -65504.0f); }
-        const __half2 hh = __floats2half2_rn(a, b);
-        const float2 hf = __half22float2(hh);
+        // the saturating conversion IS the clamp to the fp16 range (F2FP.SATFINITE): no separate min / max
+        uint32_t hh;
+        asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(hh) : "f"(v[2 * i + 1]), "f"(v[2 * i]));
+        const float2 hf = __half22float2(*reinterpret_cast<const __half2 *>(&hh));
         const __half2 ll = __floats2half2_rn(v[2 * i] - hf.x, v[2 * i + 1] - hf.y);
-        h[i] = *reinterpret_cast<const uint32_t *>(&hh);
+        h[i] = hh;
         l[i] = *reinterpret_cast<const uint32_t *>(&ll);
     }
     hi = make_uint4(h[0], h[1], h[2], h[3]);
