@@ -691,7 +691,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
 // K2b'  conv GEMM with the operand transform fused in (conv2b / conv2c of residual_layer, network.py:385-400):
 //   out = conv( relu( y * a[g] + b[g] ) )        y = the previous conv's raw fp32 output, (a, b) its BN affine
 // The standalone split pass (read y, write fp16 hi/lo planes, read them back) is gone: warp 0 TMA-loads raw fp32
-// tiles of y, eight TRANSFORM warps apply affine + ReLU, split to fp16 hi/lo and write the 128-byte-swizzled UMMA
+// tiles of y, sixteen TRANSFORM warps apply affine + ReLU, split to fp16 hi/lo and write the 128-byte-swizzled UMMA
 // operand tiles in shared memory, the MMA warp of the pair's leader consumes them.  A 1x3 conv loads ONE raw tile of
 // 130 rows per k-block (rows r0-1 .. r0+128) and produces its three taps from it (zero rows outside the window =
 // SAME padding), so the padded plane layout is not needed either and the output goes out through TMA stores with the
@@ -699,8 +699,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
 // CTA pair (cta_group::2, M = 256): each CTA transforms its own 128 rows and loads half of the weight tile.
 // Shared memory: 2 raw stages (33 KB) + 2 operand stages (A hi/lo 32 KB + B hi/lo <= 32 KB) + 16 KB staging.
 // ------------------------------------------------------------------------------------------
-constexpr int CF_THREADS = 512;                 // warps: 0 TMA, 1 MMA, 2 TMEM, 3 idle, 4-7 epilogue, 8-15 transform
-constexpr int CF_TWARPS = 8;
+constexpr int CF_THREADS = 768;                 // warps: 0 TMA, 1 MMA, 2 TMEM, 3 idle, 4-7 epilogue, 8-23 transform
+constexpr int CF_TWARPS = 16;
 constexpr int CF_RAW_STAGE = 33792;             // 130 rows x 64 fp32 = 33280, rounded to 1 KB
 constexpr int CF_RAW_STAGES = 2, CF_OP_STAGES = 2;
 constexpr int CF_EPI_BYTES = 4 * 4096;
