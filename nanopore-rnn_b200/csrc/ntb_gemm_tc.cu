@@ -33,7 +33,8 @@ namespace {
 
 constexpr int BM = 128;        // rows per tile (TMEM lanes)
 constexpr int BK = 64;         // fp16 per smem row = one 128-byte swizzle span
-constexpr int TC_THREADS = 256;
+constexpr int TC_THREADS = 256;         // LSTM timestep instantiation: 4 control + 4 epilogue warps
+constexpr int TC_THREADS_EW8 = 384;     // conv / projection GEMMs: 8 epilogue warps (two per TMEM lane quarter, alternate column chunks)
 constexpr int TMEM_COLS = 512;
 constexpr int A_TILE_BYTES = BM * BK * 2;     // 16 KB
 constexpr int EPI_STAGE_BYTES = 4 * 2 * 4096;   // 4 epilogue warps x 2 buffers x [32 rows][32 fp32], TMA-store staging
@@ -181,11 +182,12 @@ __device__ __forceinline__ void bn_partials(const uint8_t *buf, int lane, uint32
 // LSTM = true: the per-timestep mode of gemm_tc_lstm_layer (its own instantiation, so that the cell-update epilogue and its
 // prefetch registers do not weigh on the conv / projection GEMMs)
 template <int CG, bool LSTM>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(LSTM ? TC_THREADS : TC_THREADS_EW8, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
           const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
           const __grid_constant__ CUtensorMap map_out, const __grid_constant__ CUtensorMap map_out2, const TcParams p) {
     using namespace ptx;
+    constexpr int EW = LSTM ? 4 : 8;        // epilogue warps: the accumulator's column chunks are dealt round-robin to EW / 4 warps per lane quarter
     const int lstm_kbx = LSTM ? p.lstm_kbx : 0;
     const bool a_kmajor = LSTM && p.a_kmajor;
     extern __shared__ uint8_t smem_raw[];
@@ -234,7 +236,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4 * CG); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], EW * CG); }
         mbar_init(&b_full, 1);
         fence_barrier_init();
     }
@@ -246,7 +248,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
     float *bias_s = reinterpret_cast<float *>(stages_base + (size_t)p.stages * stage_bytes + (p.xproj_tma ? EPI_STAGE_BYTES : 0));
     const bool bias_in_smem = p.xproj_H > 0 && p.bias && p.Np * 4 <= p.epi_bytes - (p.xproj_tma ? EPI_STAGE_BYTES : 0);
     if (bias_in_smem)
-        for (int i = threadIdx.x; i < p.Np; i += TC_THREADS) bias_s[i] = i < p.N ? p.bias[i] : 0.0f;
+        for (int i = threadIdx.x; i < p.Np; i += (int)blockDim.x) bias_s[i] = i < p.N ? p.bias[i] : 0.0f;
     tc_fence_before();
     if (CG == 2) cluster_sync_all(); else __syncthreads();     // peer barriers are initialised before anyone signals them
     tc_fence_after();
@@ -393,7 +395,9 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
         const int q = warp & 3;                                // TMEM lane quarter this warp may access
         int acc = 0; uint32_t acc_phase = 0;
         const bool vec_ok = ((p.ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
-        uint8_t *stage_buf = stages_base + (size_t)p.stages * stage_bytes + (size_t)q * 8192;   // 1024-B aligned
+        // staging: 4 warps -> two 4 KB buffers each (the TMA store of one chunk overlaps the next chunk), 8 warps -> one each
+        const int eh = (warp - 4) >> 2;                         // which of the EW / 4 warps of this lane quarter
+        uint8_t *stage_buf = stages_base + (size_t)p.stages * stage_bytes + (EW == 4 ? (size_t)q * 8192 : (size_t)(warp - 4) * 4096);   // 1024-B aligned
         int stage_it = 0;
         int64_t mg; int n_tile;
         for (int64_t it = 0; item(it, mg, n_tile); ++it) {
@@ -469,7 +473,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                 const uint32_t diff = __ballot_sync(0xffffffffu, w_lane != w_first);
                 bn_split = diff ? __ffs(diff) - 1 : 32;
             }
-            for (int c0 = 0; c0 < p.BN; c0 += 32) {
+            for (int c0 = eh * 32; c0 < p.BN; c0 += 32 * (EW / 4)) {
                 uint32_t r[32];
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256 + c0);
                 if (c0 + 32 <= p.BN) {
@@ -483,9 +487,9 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                 tmem_ld_wait();
                 if (p.tma_store) {
                     // registers -> 128B-swizzled [32 rows][32 cols] staging tile -> one TMA store per warp
-                    uint8_t *buf = stage_buf + (stage_it & 1) * 4096;
+                    uint8_t *buf = stage_buf + (EW == 4 ? (stage_it & 1) * 4096 : 0);
                     ++stage_it;
-                    if (lane == 0) bulk_wait_group_read<1>();       // the store that last read `buf` is done
+                    if (lane == 0) { if (EW == 4) bulk_wait_group_read<1>(); else bulk_wait_group_read<0>(); }   // the store that last read `buf` is done
                     __syncwarp();
                     const int nb = n0 + c0;
 #pragma unroll
@@ -587,9 +591,9 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                     if (lim == 32 && u + 8 <= H && bias_in_smem && p.xproj_tma) {
                         // common case, TMA form: [8 units][32 rows] float4 staging tile (4 KB, conflict-free) -> ONE
                         // 3-D tensor store {128 floats, 1, 8 units} per warp and chunk
-                        uint8_t *buf = stage_buf + (stage_it & 1) * 4096;
+                        uint8_t *buf = stage_buf + (EW == 4 ? (stage_it & 1) * 4096 : 0);
                         ++stage_it;
-                        if (lane == 0) bulk_wait_group_read<1>();
+                        if (lane == 0) { if (EW == 4) bulk_wait_group_read<1>(); else bulk_wait_group_read<0>(); }
                         __syncwarp();
                         const float4 *b4 = reinterpret_cast<const float4 *>(bias_s + nb);
 #pragma unroll
@@ -635,7 +639,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                 } else {
                   if (p.bn_part) {
                     // statistics of the tile (direct-store path, e.g. the padded-row 1x3 conv): stage, reduce columns
-                    uint8_t *buf = stage_buf + (stage_it & 1) * 4096;
+                    uint8_t *buf = stage_buf + (EW == 4 ? (stage_it & 1) * 4096 : 0);
                     ++stage_it;
                     __syncwarp();
 #pragma unroll
@@ -1449,14 +1453,14 @@ int do_launch(cudaStream_t st, const CUtensorMap &ma_hi, const CUtensorMap &ma_l
         const int64_t tiles = p.m_tiles * p.n_tiles;
         const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
         if (p.lstm_H > 0) return fail(NTB_EINVAL, "tcgen05 GEMM: the LSTM timestep mode needs the CTA-pair kernel%s", "");
-        k_gemm_tc<1, false><<<grid, TC_THREADS, smem, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, mo, mo2 ? *mo2 : mo, p);
+        k_gemm_tc<1, false><<<grid, TC_THREADS_EW8, smem, st>>>(ma_hi, ma_lo, mb_hi, mb_lo, mo, mo2 ? *mo2 : mo, p);
     } else {
         const int64_t items = ((p.m_tiles + 1) / 2) * p.n_tiles;            // pairs of M tiles x N tiles
         int64_t pairs_hw = sm_count() / 2;
         if (p.bstat) pairs_hw = pairs_hw / p.n_tiles * p.n_tiles;          // every pair owns one N tile for the whole launch
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)(2 * (items < pairs_hw ? items : pairs_hw)));
-        cfg.blockDim = dim3(TC_THREADS);
+        cfg.blockDim = dim3(p.lstm_H > 0 ? TC_THREADS : TC_THREADS_EW8);
         cfg.dynamicSmemBytes = smem;
         cfg.stream = st;
         cudaLaunchAttribute attr[1];
