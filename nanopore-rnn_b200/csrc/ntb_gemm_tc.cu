@@ -15,8 +15,9 @@
 //               k-step into one of two TMEM accumulators; tcgen05.commit frees the smem stage /
 //               publishes the accumulator
 //   warp 2      TMEM allocator (512 columns = 2 accumulators of up to 256 columns)
-//   warps 4-7   epilogue: tcgen05.ld 32 lanes x 32 columns -> registers -> (+bias) -> global fp32,
-//               overlapping the next tile's main loop through the second accumulator
+//   warps 4-11  epilogue: tcgen05.ld 32 lanes x 32 columns -> registers -> (+bias) -> global fp32,
+//               overlapping the next tile's main loop through the second accumulator; two warps per TMEM lane
+//               quarter take alternate 32-column chunks (with four warps the epilogue paced the conv GEMMs)
 // 1x3 convs run as 3 taps accumulated into the same accumulator: the A planes use a row layout
 // padded per window ([window][T+2][K], zero rows at both ends) so a tap is a row offset of the
 // TMA coordinate and SAME zero padding falls out of the layout.
@@ -33,8 +34,7 @@ namespace {
 
 constexpr int BM = 128;        // rows per tile (TMEM lanes)
 constexpr int BK = 64;         // fp16 per smem row = one 128-byte swizzle span
-constexpr int TC_THREADS = 256;         // LSTM timestep instantiation: 4 control + 4 epilogue warps
-constexpr int TC_THREADS_EW8 = 384;     // conv / projection GEMMs: 8 epilogue warps (two per TMEM lane quarter, alternate column chunks)
+constexpr int TC_THREADS_EW8 = 384;     // 4 control warps + 8 epilogue warps (two per TMEM lane quarter, alternate column chunks)
 constexpr int TMEM_COLS = 512;
 constexpr int A_TILE_BYTES = BM * BK * 2;     // 16 KB
 constexpr int EPI_STAGE_BYTES = 4 * 2 * 4096;   // 4 epilogue warps x 2 buffers x [32 rows][32 fp32], TMA-store staging
@@ -182,12 +182,12 @@ __device__ __forceinline__ void bn_partials(const uint8_t *buf, int lane, uint32
 // LSTM = true: the per-timestep mode of gemm_tc_lstm_layer (its own instantiation, so that the cell-update epilogue and its
 // prefetch registers do not weigh on the conv / projection GEMMs)
 template <int CG, bool LSTM>
-__global__ void __launch_bounds__(LSTM ? TC_THREADS : TC_THREADS_EW8, 1)
+__global__ void __launch_bounds__(TC_THREADS_EW8, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
           const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
           const __grid_constant__ CUtensorMap map_out, const __grid_constant__ CUtensorMap map_out2, const TcParams p) {
     using namespace ptx;
-    constexpr int EW = LSTM ? 4 : 8;        // epilogue warps: the accumulator's column chunks are dealt round-robin to EW / 4 warps per lane quarter
+    constexpr int EW = 8;        // epilogue warps: the accumulator's column chunks are dealt round-robin to EW / 4 warps per lane quarter
     const int lstm_kbx = LSTM ? p.lstm_kbx : 0;
     const bool a_kmajor = LSTM && p.a_kmajor;
     extern __shared__ uint8_t smem_raw[];
@@ -444,7 +444,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                         l_x = reinterpret_cast<const float4 *>(p.lstm_x) + ((l_dir * p.lstm_xmt + l_tile * p.T + l_t) * p.lstm_H) * (int64_t)BM + l_wl;
                     l_c = reinterpret_cast<float4 *>(p.lstm_c) + ((l_dir * n_tiles + l_tile) * (p.lstm_H >> 2)) * (int64_t)BM + l_wl;
                 }
-                lstm_fetch(0);
+                lstm_fetch(((warp - 4) >> 2) * 32);
             }
             mbar_wait(&acc_full[acc], acc_phase);
             tc_fence_after();
@@ -525,7 +525,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                         for (int k = 0; k < 8; ++k) xcur[k] = xpre[k];
                         ccur[0] = cpre[0]; ccur[1] = cpre[1];
                         float4 *cg = l_c + (int64_t)(u0 >> 2) * BM;
-                        lstm_fetch(c0 + 32);              // the next chunk's operands fly during this chunk's cell updates
+                        lstm_fetch(c0 + 32 * (EW / 4));   // the next chunk's operands fly during this chunk's cell updates
                         float hv[8];
 #pragma unroll
                         for (int half = 0; half < 2; ++half) {
@@ -1460,7 +1460,7 @@ int do_launch(cudaStream_t st, const CUtensorMap &ma_hi, const CUtensorMap &ma_l
         if (p.bstat) pairs_hw = pairs_hw / p.n_tiles * p.n_tiles;          // every pair owns one N tile for the whole launch
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)(2 * (items < pairs_hw ? items : pairs_hw)));
-        cfg.blockDim = dim3(p.lstm_H > 0 ? TC_THREADS : TC_THREADS_EW8);
+        cfg.blockDim = dim3(TC_THREADS_EW8);
         cfg.dynamicSmemBytes = smem;
         cfg.stream = st;
         cudaLaunchAttribute attr[1];
