@@ -283,13 +283,13 @@ __global__ void __launch_bounds__(256) k_bn_finish(const float2 *__restrict__ pa
                 const int e = rem + 32 < Tp ? rem + 32 : Tp;
                 const int nb = (e < hi ? e : hi) - (rem > lo ? rem : lo);
                 const float2 v = rec[0];
-                if (nb > 0) { ss += (double)v.x; m2 += (double)v.y; sq = fma((double)v.x * (double)v.x, bn_rcp(nb), sq); }
+                if (nb > 0) { const double S = (double)v.x; ss += S; m2 += (double)v.y; sq = fma(S * S, nb == 32 ? 0.03125 : bn_rcp(nb), sq); }
             }
             if (two && w_first + 1 >= wa && w_first + 1 < wb) {
                 const int e = rem + 32 - Tp;                       // rows [0, e) of the next window
                 const int nb = (e < hi ? e : hi) - lo;
                 const float2 v = rec[C];
-                if (nb > 0) { ss += (double)v.x; m2 += (double)v.y; sq = fma((double)v.x * (double)v.x, bn_rcp(nb), sq); }
+                if (nb > 0) { const double S = (double)v.x; ss += S; m2 += (double)v.y; sq = fma(S * S, nb == 32 ? 0.03125 : bn_rcp(nb), sq); }
             }
             rem += 32;
             if (rem >= Tp) { rem -= Tp; ++w_first; }
