@@ -641,6 +641,7 @@ def bench_reads(cx, args):
 
         gpu_ms = [0.0]
         gpu_steps = []
+        phases = []
         ge0, ge1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
         def e2e_step(timed):
@@ -650,14 +651,17 @@ def bench_reads(cx, args):
             cons, cons_off, status = job.run_device(raw_e, plan)
             ge1.record()
             if timed:
-                enq_s[0] += time.perf_counter() - t_a          # host time to enqueue the chain (the assembly's table upload waits for the forward)
+                t_b = time.perf_counter()
+                enq_s[0] += t_b - t_a                          # host time to enqueue the chain (the assembly's table upload waits for the forward)
                 torch.cuda.current_stream(dev).synchronize()
+                t = time.perf_counter()
                 gpu_ms[0] += ge0.elapsed_time(ge1)             # device time of copy + chain inside this step
                 gpu_steps.append(round(ge0.elapsed_time(ge1), 1))
-                t = time.perf_counter()
             called[0] = gather_consensus(cons, cons_off, plan.n_reads, read_ids, len(lengths), rank, world, dev)
             if timed:
-                gather_s[0] += time.perf_counter() - t
+                t_c = time.perf_counter()
+                gather_s[0] += t_c - t
+                phases.append((round((t_b - t_a) * 1e3, 1), round((t - t_b) * 1e3, 1), round((t_c - t) * 1e3, 1)))
 
         for _ in range(2):
             e2e_step(False)
@@ -671,11 +675,13 @@ def bench_reads(cx, args):
             e2e_step(True)
             step_s.append(time.perf_counter() - t_s)
         torch.cuda.synchronize()
+        t1 = time.perf_counter()                 # this rank's K steps are done; the slowest rank's elapsed time is the job's
         cx.barrier()
-        dt = cx.max_over_ranks(time.perf_counter() - t0) / steps
+        t2 = time.perf_counter()
+        dt = cx.max_over_ranks(t1 - t0) / steps
         clocks_e = sampler_e.finish()
         if os.environ.get("NTB_BENCH_DEBUG"):
-            sys.stderr.write("e2e step wall ms: %s device ms: %s\n" % ([round(v * 1e3, 1) for v in step_s], gpu_steps))
+            sys.stderr.write("e2e step wall ms: %s device ms: %s (enqueue, wait, gather) ms: %s; loop %.1f ms, closing barrier %.1f ms\n" % ([round(v * 1e3, 1) for v in step_s], gpu_steps, phases, (t1 - t0) * 1e3, (t2 - t1) * 1e3))
         d2h = sum(len(c) for c in called[0]) + 16 * len(lengths) + 8 if rank == 0 else 0
         e2e = {"value": total_samples / dt, "unit": UNIT, "ms_per_step": dt * 1e3,
                "h2d_bytes_per_step": int(cx.sum_over_ranks(host.nbytes + 16 * (plan.n_reads + 1) + 4 * len(plan.group_off))),
