@@ -191,6 +191,20 @@ class ClockSampler(threading.Thread):
                 pass
             self._stop_evt.wait(self.period)
 
+    def sample_once(self):
+        """One sample from the calling thread (the end-to-end leg: a polling thread's NVML queries were measured to delay the
+        host's wake-up from the stream synchronisation by 0.1-0.9 s now and then, tools/hic.sh)."""
+        if self.nv is None:
+            return
+        try:
+            self.sm.append(int(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+            mask = int(self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+            for bit, name in self.REASONS.items():
+                if mask & bit:
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
     def finish(self):
         self._stop_evt.set()
         if self.is_alive():
@@ -653,6 +667,9 @@ def bench_reads(cx, args):
             if timed:
                 t_b = time.perf_counter()
                 enq_s[0] += t_b - t_a                          # host time to enqueue the chain (the assembly's table upload waits for the forward)
+                if e2e_mode == "step":
+                    time.sleep(min(0.3, 0.4e-3 * my_ms))       # (well inside this rank's step: the GPU is under load when sampled)
+                    sampler_e.sample_once()
                 torch.cuda.current_stream(dev).synchronize()
                 t = time.perf_counter()
                 gpu_ms[0] += ge0.elapsed_time(ge1)             # device time of copy + chain inside this step
@@ -666,8 +683,16 @@ def bench_reads(cx, args):
         for _ in range(2):
             e2e_step(False)
         cx.barrier()
-        sampler_e = ClockSampler(cx.local)       # the cap moves the clock with the board's temperature: say what this leg saw
-        sampler_e.start()
+        # No NVML polling in this leg: its queries were measured to take up to a second now and then while the GPU is under
+        # load, and -- from a polling thread as well as from this one -- to delay the host's wake-up from the stream
+        # synchronisation by 0.1-0.9 s (profiles/r02_e2e_nvml_hiccups.txt, tools/hic.sh).  The device-resident leg above is
+        # timed with CUDA events and keeps its sampler; this leg reports the device time of its own steps instead
+        # (NTB_E2E_SAMPLER=thread|step re-enables the sampling for A/B runs).
+        sampler_e = ClockSampler(cx.local)
+        e2e_mode = os.environ.get("NTB_E2E_SAMPLER", "none")
+        e2e_thread = e2e_mode == "thread"
+        if e2e_thread:
+            sampler_e.start()
         t0 = time.perf_counter()
         step_s = []
         for _ in range(steps):
