@@ -1452,10 +1452,21 @@ extern "C" int ntb_parse_signal(const uint8_t *text_dev, const int64_t *file_off
     NTB_CUDA(cudaMemcpyAsync(b.chunk_lo, chunk_lo.data(), sizeof(int64_t) * n_chunks, cudaMemcpyHostToDevice, st));
     NTB_CUDA(cudaMemcpyAsync(b.chunk_file, chunk_file.data(), sizeof(int32_t) * n_chunks, cudaMemcpyHostToDevice, st));
     NTB_CUDA(cudaStreamSynchronize(st));
-    k_parse_count<<<(unsigned)n_chunks, PARSE_THREADS, 0, st>>>(text_dev, b.chunk_lo, b.chunk_file, b.file_off, total_bytes, b.counts);
-    k_asm_read_offsets<<<1, 1024, 0, st>>>(b.counts, b.counts, n_chunks, capacity, b.tmp, b.chunk_out, status_dev);
-    k_parse_emit<<<(unsigned)n_chunks, PARSE_THREADS, 0, st>>>(text_dev, b.chunk_lo, b.chunk_file, b.file_off, total_bytes, b.chunk_out,
-                                                               capacity, samples_dev, status_dev);
+    static const bool two_pass = ntb_env("NTB_PARSE_2PASS") != nullptr;      // ablation builds: the round-1 pair of passes
+    if (two_pass) {
+        k_parse_count<<<(unsigned)n_chunks, PARSE_THREADS, 0, st>>>(text_dev, b.chunk_lo, b.chunk_file, b.file_off, total_bytes, b.counts);
+        k_asm_read_offsets<<<1, 1024, 0, st>>>(b.counts, b.counts, n_chunks, capacity, b.tmp, b.chunk_out, status_dev);
+        k_parse_emit<<<(unsigned)n_chunks, PARSE_THREADS, 0, st>>>(text_dev, b.chunk_lo, b.chunk_file, b.file_off, total_bytes,
+                                                                   b.chunk_out, capacity, samples_dev, status_dev);
+    } else {
+        // one pass: state words (in `counts`) and the ticket (in `tmp`) start at zero
+        NTB_CUDA(cudaMemsetAsync(b.counts, 0, sizeof(int64_t) * n_chunks, st));
+        NTB_CUDA(cudaMemsetAsync(b.tmp, 0, sizeof(int64_t), st));
+        k_parse_fused<<<(unsigned)n_chunks, PARSE_THREADS, 0, st>>>(text_dev, b.chunk_lo, b.chunk_file, b.file_off, total_bytes, n_chunks,
+                                                                   reinterpret_cast<unsigned long long *>(b.counts),
+                                                                   reinterpret_cast<unsigned int *>(b.tmp), capacity, b.chunk_out,
+                                                                   samples_dev, status_dev);
+    }
     k_parse_read_off<<<(unsigned)cdiv(n_files + 1, 256), 256, 0, st>>>(b.chunk_out, b.first_chunk, n_files, read_off_dev);
     NTB_LAUNCH_CHECK();
     return NTB_OK;
