@@ -1252,8 +1252,8 @@ static EdBufs ed_carve(Arena &ar, int64_t n_reads, int64_t total) {
     b.read_off = ar.take<int64_t>(n_reads + 1);
     b.n_events = ar.take<int64_t>(n_reads);
     b.tmp_off = ar.take<int64_t>(n_reads + 1);
-    b.sums = ar.take<double>(total);
-    b.sumsqs = ar.take<double>(total);
+    b.sums = ar.take<double>(2 * total);       // sums | sumsqs in one block: the fused form keeps (sum, sumsq) pairs there
+    b.sumsqs = b.sums + total;
     b.t_short = ar.take<double>(total);
     b.t_long = ar.take<double>(total);
     b.peaks = ar.take<int32_t>(total);
@@ -1319,6 +1319,24 @@ extern "C" int ntb_event_detect(const double *raw_dev, const int64_t *read_off_h
         R = n_reads / 8 >= ED_MIN_WARPS ? 8 : (n_reads >= 4000 ? 4 : 0);
     }
     const unsigned lgrid = (unsigned)cdiv(n_reads, 2 * (R ? R : 1));
+    // Opt-in (NTB_ED_FUSED=1, with 4 or 8 reads per warp and windows that fit the ring): cumulative sums, t-statistics and
+    // peaks in ONE kernel.  It moves 2.4x fewer bytes (the t-statistics never reach memory) but measured SLOWER than the
+    // separate kernels (27.2 vs 25.9 ms at 8192 reads, 26.9 vs 16.2 ms at 32 768): the t-statistics' float64 divisions run
+    // at the fused kernel's low occupancy and in series with the sequential stages, so the default stays unfused.
+    static const char *fused_env = getenv("NTB_ED_FUSED");
+    if ((R == 4 || R == 8) && w_long <= 31 && fused_env && fused_env[0] == '1') {
+        double2 *sq = reinterpret_cast<double2 *>(b.sums);     // sums | sumsqs are adjacent in the workspace: one array of pairs
+        if (R == 8)
+            k_ed_fused<8><<<lgrid, 64, 0, st>>>(raw_dev, b.read_off, n_reads, w_short, w_long, th_short, th_long, peak_height, sq,
+                                                b.peaks, b.n_events);
+        else
+            k_ed_fused<4><<<lgrid, 64, 0, st>>>(raw_dev, b.read_off, n_reads, w_short, w_long, th_short, th_long, peak_height, sq,
+                                                b.peaks, b.n_events);
+        k_asm_read_offsets<<<1, 1024, 0, st>>>(b.n_events, b.n_events, n_reads, capacity, b.tmp_off, event_off_dev, status_dev);
+        k_ed_events_sq<<<(unsigned)n_reads, 256, 0, st>>>(sq, b.peaks, b.read_off, event_off_dev, sample_rate, capacity, events_dev);
+        NTB_LAUNCH_CHECK();
+        return NTB_OK;
+    }
     switch (R) {
         case 32: k_ed_prefix_t<32><<<lgrid, 64, 0, st>>>(raw_dev, b.read_off, n_reads, b.sums, b.sumsqs); break;
         case 16: k_ed_prefix_t<16><<<lgrid, 64, 0, st>>>(raw_dev, b.read_off, n_reads, b.sums, b.sumsqs); break;

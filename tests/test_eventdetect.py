@@ -113,7 +113,7 @@ def test_gpu_matches_reference_golden(lib, golden, p):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("lanes", ["0", "1", "4", "8", "16"])
+@pytest.mark.parametrize("lanes", ["0", "1", "4", "8", "16", "4:fused", "8:fused"])
 def test_both_kernel_forms_agree_with_the_golden(golden, lanes):
     """The warp-per-read and the R-reads-per-warp forms (R = 4, 8, 16, 32) of the sequential stages (the library picks by read count; the switch is
     read once per process, hence the subprocess)."""
@@ -125,9 +125,56 @@ def test_both_kernel_forms_agree_with_the_golden(golden, lanes):
             "m = np.concatenate([e['mean'] for e in ev]); s = np.concatenate([e['start'] for e in ev]); "
             "assert np.array_equal(m, g['events_0'][:, 2]) and np.array_equal(s, g['events_0'][:, 0]); print('ok')"
             % (ROOT, os.path.join(ROOT, "oracle"), os.path.join(GOLDEN, "event_detect.npz")))
-    out = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, NTB_ED_LANES=lanes), capture_output=True,
+    env = dict(os.environ, NTB_ED_LANES=lanes.split(":")[0])
+    if lanes.endswith(":fused"):                    # the opt-in one-kernel form of cumulative sums + t-statistics + peaks
+        env["NTB_ED_FUSED"] = "1"
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True,
                          text=True, timeout=300)
     assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
+
+
+RAGGED_CODE = """
+import sys, numpy as np
+sys.path[:0] = [%r, %r]
+import nanopore_rnn_b200
+from nanopore_rnn_b200 import eventdetection as E
+rng = np.random.default_rng(19)
+def squiggle(n, dwell=9.0, noise=1.2):
+    out = np.empty(n); i = 0
+    while i < n:
+        d = 1 + int(rng.geometric(1.0 / dwell)); out[i:i + d] = rng.uniform(55.0, 125.0); i += d
+    return out + rng.normal(0.0, noise, n)
+raws = [squiggle(int(n)) for n in rng.integers(1, 3000, 257)] + [squiggle(70000, dwell=12.0), np.full(500, 80.0), squiggle(33)]
+res = {}
+for tag, wl, th in (("a", [3, 6], [1.4, 1.1]), ("b", [5, 31], [1.2, 1.0]), ("c", [6, 3], [1.1, 1.4])):
+    evs = E.minknow_event_detect_batch(raws, 4000.0, wl, th, 0.2)
+    res["n_" + tag] = np.array([len(e) for e in evs])
+    for k in ("start", "length", "mean", "stdv"):
+        res[k + "_" + tag] = np.concatenate([e[k] for e in evs])
+np.savez(sys.argv[1], **res)
+print("ok")
+"""
+
+
+@pytest.mark.gpu
+def test_fused_kernel_equals_the_separate_kernels_on_ragged_reads(tmp_path):
+    """k_ed_fused (opt-in: cumulative sums + t-statistics + peaks in one kernel, 4 / 8 reads per warp) against the warp-per-read
+    chain of separate kernels: 260 ragged reads (1 ... 70 000 samples, a flat one, one shorter than the windows), three
+    parameter sets incl. the largest window the fused form takes (31) and the reversed argument order.  Bit-identical."""
+    import subprocess
+    import sys
+    outs = {}
+    for tag, env in (("sep", {"NTB_ED_LANES": "0"}), ("f4", {"NTB_ED_LANES": "4", "NTB_ED_FUSED": "1"}),
+                     ("f8", {"NTB_ED_LANES": "8", "NTB_ED_FUSED": "1"}), ("u8", {"NTB_ED_LANES": "8"})):
+        path = str(tmp_path / (tag + ".npz"))
+        r = subprocess.run([sys.executable, "-c", RAGGED_CODE % (ROOT, os.path.join(ROOT, "oracle")), path],
+                           env=dict(os.environ, **env), capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-2000:]
+        outs[tag] = np.load(path)
+    for tag in ("f4", "f8", "u8"):
+        for k in outs["sep"].files:
+            assert np.array_equal(outs[tag][k], outs["sep"][k]), (tag, k)
+    assert int(outs["sep"]["n_a"].sum()) > 5000
 
 
 @pytest.mark.gpu
