@@ -795,6 +795,16 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
     } else {
         float *lg = logits_out ? logits_out : ws.logits;
         if (!lg) return fail(NTB_ENOMEM, "forward: no logits buffer for a large-C readout%s", "");
+        if (!logits_out && m->outw.valid && ws.gs.valid && !ntb_env("NTB_NO_ARGMAX_EPILOGUE")) {
+            // labels only: dense layer + argmax in ONE GEMM epilogue (the logits are never written; the scratch holds 8 bytes
+            // per row of (value, column) keys instead of C floats), then the collapse / copy of the winners
+            unsigned long long *keys = reinterpret_cast<unsigned long long *>(ws.logits);
+            NTB_TRY(gemm_tc_run_argmax(cx.st, cur, dim, rows, m->outw, m->out_b, keys, ws.gs, &cx.launches));
+            const int64_t threads = m->graph == NTB_GRAPH_CROSS_ENTROPY ? rows : n;
+            k_decode_keys<<<cdiv(threads, 256), 256, 0, st>>>(keys, lens, n, T, m->C, m->graph, labels, label_len);
+            cx.count();
+            NTB_LAUNCH_CHECK();
+        } else {
         // the caller's logits are dense [rows][C]; the internal scratch (labels only) pads the row stride to a multiple of 4
         // floats: with C = 1025 the dense layer's epilogue otherwise falls back to scalar stores
         const int ldl = logits_out ? m->C : (int)align_up(m->C, 4);
@@ -803,6 +813,7 @@ static int forward_impl(ntb_model *m, const float *x, const int32_t *lens, const
         k_decode<<<cdiv(warps, 8), 256, 0, st>>>(lg, lens, n, T, m->C, m->graph, labels, label_len, ldl);
         cx.count();
         NTB_LAUNCH_CHECK();
+        }
     }
     if (m->profile) {
         cudaEvent_t e;

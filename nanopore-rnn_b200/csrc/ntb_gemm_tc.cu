@@ -90,6 +90,11 @@ struct TcParams {
     // column dir H + unit) instead of the fp32 layer output: no split pass between two stacked layers
     op16_t *lstm_nx_hi, *lstm_nx_lo;
     int lstm_nx_K;
+    // amax != null: no output at all -- the epilogue keeps, per row, the best (value, column) of the tile's columns (+ bias) and
+    // merges it into amax[row] with one atomicMax per warp and tile: key = orderable(value) << 32 | ~column, so the maximum
+    // key is the largest value and, among equal values, the FIRST column (tf.argmax); the dense readout of a large class
+    // count (fulconn_layer, network.py:291-309 + tf.argmax :208-211) then never materialises its logits
+    unsigned long long *amax;
     int a_kmajor;                      // the A planes are [K/8][rows][8] (no swizzle; 3-D TMA box {8, 128, 8}) instead of
                                        // row-major rows with the 128-byte swizzle: the LSTM epilogue's h stores coalesce
 };
@@ -473,6 +478,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                 const uint32_t diff = __ballot_sync(0xffffffffu, w_lane != w_first);
                 bn_split = diff ? __ffs(diff) - 1 : 32;
             }
+            float am_v = -INFINITY;                            // argmax mode: this row's best value / column over the warp's chunks
+            int am_i = -1;
             for (int c0 = eh * 32; c0 < p.BN; c0 += 32 * (EW / 4)) {
                 uint32_t r[32];
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 256 + c0);
@@ -578,6 +585,18 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                             }
                         }
                     }
+                } else if (!LSTM && p.amax) {
+                    if (row_ok) {
+                        const int nb = n0 + c0;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            const int n = nb + i;
+                            if (n < p.N && c0 + i < p.BN) {
+                                const float v = __uint_as_float(r[i]) + (p.bias ? __ldg(p.bias + n) : 0.0f);
+                                if (v > am_v) { am_v = v; am_i = n; }       // strict: the first maximum stays
+                            }
+                        }
+                    }
                 } else if (p.xproj_H > 0 && m_tile < p.m_tiles) {
                     if (p.abl & 1) continue;
                     // xproj[dir][m_tile][unit][row] float4 (i,j,f,o): a warp's 32 rows are contiguous (512 B per unit).
@@ -673,6 +692,11 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ 
                     }
                   }
                 }
+            }
+            if (!LSTM && p.amax && am_i >= 0) {
+                const uint32_t u = __float_as_uint(am_v + 0.0f);                            // (-0.0 and +0.0 compare equal: one key)
+                const uint32_t ord = u ^ ((u >> 31) ? 0xffffffffu : 0x80000000u);          // monotonic in the float order
+                atomicMax(p.amax + orow, ((unsigned long long)ord << 32) | (unsigned long long)(0xffffffffu - (uint32_t)am_i));
             }
             tc_fence_before();
             __syncwarp();
@@ -1493,7 +1517,7 @@ int make_map_xproj_store(CUtensorMap *m, const float *xproj, int64_t units_total
 
 int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, int64_t plane_rows, int T, int pad,
                 int64_t out_rows, const float *bias, float *out, int ldo, int64_t *launches, int xproj_H = 0,
-                float2 *bn_part = nullptr, float *out2 = nullptr, float2 *bn_part2 = nullptr) {
+                float2 *bn_part = nullptr, float *out2 = nullptr, float2 *bn_part2 = nullptr, unsigned long long *amax = nullptr) {
     const int cg = gemm_cta_group();
     CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
     NTB_TRY(make_map(&ma_hi, gs.a_hi, plane_rows, w.K, BM));
@@ -1517,8 +1541,9 @@ int launch_gemm(cudaStream_t st, const GemmWeights &w, const GemmScratch &gs, in
     static const int l2pf = ntb_env("NTB_GEMM_L2PF") ? atoi(ntb_env("NTB_GEMM_L2PF")) : 0;
     p.l2pf = l2pf;
     // coalesced TMA-store epilogue for plain row-major outputs (N tiles of whole 32-column chunks)
-    p.tma_store = (!pad && xproj_H == 0 && w.BN % 32 == 0 && (ldo & 3) == 0 &&
+    p.tma_store = (!amax && !pad && xproj_H == 0 && w.BN % 32 == 0 && (ldo & 3) == 0 &&
                    (reinterpret_cast<uintptr_t>(out) & 15) == 0) ? 1 : 0;
+    p.amax = amax;
     CUtensorMap mo = ma_hi;
     if (p.tma_store) NTB_TRY(make_map_out(&mo, out, out_rows, w.N, ldo));
     if (p.xproj_tma) NTB_TRY(make_map_xproj_store(&mo, out, 2 * p.m_tiles * (int64_t)xproj_H));
@@ -1635,6 +1660,20 @@ int gemm_tc_run(cudaStream_t st, const float *A, int lda, int64_t rows, const Ge
     sp.hi = gs.a_hi; sp.lo = w.single_pass ? nullptr : gs.a_lo; sp.plane_rows = rows;
     NTB_TRY(launch_split(st, sp, launches));
     return launch_gemm(st, w, gs, rows, 1, 0, rows, bias, out, ldo, launches);
+}
+
+int gemm_tc_run_argmax(cudaStream_t st, const float *A, int lda, int64_t rows, const GemmWeights &w, const float *bias,
+                       unsigned long long *keys, const GemmScratch &gs, int64_t *launches) {
+    if (!w.valid || !gs.valid || rows > gs.rows_cap || w.K > gs.kp_cap || (lda & 3) || w.taps != 1 || w.single_pass || w.ilv ||
+        (reinterpret_cast<uintptr_t>(A) & 15) || !keys)
+        return fail(NTB_EINVAL, "tcgen05 GEMM (argmax epilogue): operand not supported (rows %s%lld, K %lld)", "", (long long)rows,
+                    (long long)w.K);
+    NTB_CUDA(cudaMemsetAsync(keys, 0, sizeof(unsigned long long) * (size_t)rows, st));
+    SplitParams sp{};
+    sp.A = A; sp.lda = lda; sp.rows = rows; sp.K = w.K; sp.T = 1; sp.relu = 0; sp.pad = 0;
+    sp.hi = gs.a_hi; sp.lo = gs.a_lo; sp.plane_rows = rows;
+    NTB_TRY(launch_split(st, sp, launches));
+    return launch_gemm(st, w, gs, rows, 1, 0, rows, bias, nullptr, 0, launches, 0, nullptr, nullptr, nullptr, keys);
 }
 
 int gemm_tc_run_xproj(cudaStream_t st, const float *A, int lda, int64_t n_windows, int T, const GemmWeights &w,

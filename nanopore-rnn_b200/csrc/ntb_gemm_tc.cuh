@@ -32,6 +32,11 @@ int gemm_tc_pack_weights(cudaStream_t st, const float *w_kn, GemmWeights &w);
 void gemm_tc_plan_scratch(GemmScratch &gs, int64_t rows, int T, int maxk, Arena &ar, int64_t min_rows = 0);
 int gemm_tc_run(cudaStream_t st, const float *A, int lda, int64_t rows, const GemmWeights &w, const float *bias,
                 float *out, int ldo, const GemmScratch &gs, int64_t *launches);
+// Same GEMM with an argmax epilogue instead of an output: keys[row] = max over columns of (orderable(out + bias) << 32 |
+// ~column) -- the row's largest value and, among equals, its FIRST column (tf.argmax); the logits are never written.
+// keys [rows] uint64 (zeroed by the call); column = 0xffffffff - (key & 0xffffffff), key 0 = no finite value (all NaN).
+int gemm_tc_run_argmax(cudaStream_t st, const float *A, int lda, int64_t rows, const GemmWeights &w, const float *bias,
+                       unsigned long long *keys, const GemmScratch &gs, int64_t *launches);
 // LSTM input projection for the tensor-core recurrence: A rows are permuted to time-major tiles
 // ([tile][t][128 windows]) and the output is the unit-major projected-gates layout of ntb_lstm_tc.cuh
 // (xproj must hold ceil(n_windows/128)*128*T*8H floats).

@@ -745,6 +745,32 @@ __global__ void __launch_bounds__(256) k_decode(const float *__restrict__ logits
     if (lane == 0 && label_len) label_len[gw] = cnt;
 }
 
+// Same decode from the argmax keys of the dense GEMM's epilogue (gemm_tc_run_argmax): no logits exist.
+// argmax: one thread per row; CTC: one thread per window walking t (reads of 8 bytes per step).
+__global__ void __launch_bounds__(256) k_decode_keys(const unsigned long long *__restrict__ keys,
+                                                     const int32_t *__restrict__ lens, int64_t n_windows, int T, int C,
+                                                     int graph, int32_t *__restrict__ labels, int32_t *__restrict__ label_len) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    auto col = [&](int64_t row) -> int {
+        const unsigned long long k = keys[row];
+        return k ? (int)(0xffffffffu - (uint32_t)(k & 0xffffffffull)) : 0;       // all-NaN row -> 0 like a first-max scan
+    };
+    if (graph == NTB_GRAPH_CROSS_ENTROPY) {
+        if (i < n_windows * T) labels[i] = col(i);
+        return;
+    }
+    if (i >= n_windows) return;
+    const int len = lens[i];
+    int prev = -1, cnt = 0;
+    for (int t = 0; t < len && t < T; ++t) {
+        const int best = col(i * T + t);
+        if (best != C - 1 && best != prev) labels[i * T + cnt++] = best;
+        prev = best;
+    }
+    for (int k = cnt; k < T; ++k) labels[i * T + k] = -1;
+    if (label_len) label_len[i] = cnt;
+}
+
 // ------------------------------------------------------------------------------------------
 // LSTM input projection for inputs the tensor-core GEMM does not take (len_x = 12: K % 8 != 0 or K < 64), written
 // straight in the unit-major projected-gates layout the per-timestep recurrence reads:

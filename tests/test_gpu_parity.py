@@ -247,6 +247,37 @@ def test_event_fixture_model_matches_golden(golden_dir):
     assert m.last_launches() > 0
 
 
+@pytest.mark.parametrize("graph,Cc", [("CrossEntropy", 1025), ("CtcLoss", 1025), ("CtcLoss", 40), ("CrossEntropy", 9)])
+def test_large_class_count_labels_without_logits_equal_the_logits_path(graph, Cc):
+    """fulconn_layer + tf.argmax (network.py:291-309, 208-211) for a class count beyond the fused small-C readout: when the
+    caller wants labels only, the dense GEMM's epilogue keeps each row's (value, first column) and the logits are never
+    written; when logits are wanted they are materialised and decoded.  Same labels from both, ties included (weights with
+    duplicated output columns make every row's maximum appear twice: the FIRST column must win)."""
+    net = syn.NETWORKS["stress_blstm256"]                            # 512 features into the dense layer: the tcgen05 GEMM takes it
+    T, len_x, n = 30, 12, 70
+    w = syn.random_weights(net, len_x, Cc, seed=77, graph=graph)
+    ow = np.array(w["out_w"], copy=True)
+    ob = np.array(w["out_b"], copy=True)
+    dup = np.arange(0, Cc - 1 - (Cc - 1) % 2, 2)                     # column 2k+1 := column 2k (the blank / last class untouched)
+    ow[:, dup + 1] = ow[:, dup]
+    ob[dup + 1] = ob[dup]
+    w = dict(w, out_w=ow, out_b=ob)
+    rng = np.random.default_rng(78)
+    x = rng.standard_normal((n, T, len_x)).astype(np.float32)
+    lens = rng.integers(0, T + 1, n).astype(np.int32)
+    lens[:2] = [T, 0]
+    m = engine.Model(net, w, graph, T, len_x, Cc, device=DEV)
+    l_log, k_log, logits = m.forward_host(x, lens, None, want_logits=True)
+    l_key, k_key, none = m.forward_host(x, lens, None, want_logits=False)
+    assert none is None
+    assert np.array_equal(l_key, l_log)
+    if graph == "CtcLoss":
+        assert np.array_equal(k_key, k_log)
+    # and the logits path itself is first-max: every winner of a duplicated pair is the even column
+    am = logits.reshape(n, T, Cc).argmax(-1)
+    assert np.all((am % 2 == 0) | (am >= len(dup) * 2))
+
+
 @pytest.mark.parametrize("name,key", [("crnn_signal", "signal_CRNN"), ("crnn_run_nanotensor", "run_nanotensor")])
 def test_crnn_model_matches_golden(golden_dir, name, key):
     g = np.load(os.path.join(golden_dir, name + ".npz"))
